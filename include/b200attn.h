@@ -1,0 +1,194 @@
+/*
+ * b200attn.h — C ABI of the B200-native (sm_100a) attention hot path.
+ *
+ * This is the drop-in boundary for SGLang's attention path.  Every entry point
+ * names the reference interface it replaces (paths relative to the SGLang tree).
+ *
+ * Conventions (all entry points):
+ *   - extern "C", plain pointers and sizes; no torch / C++ types.
+ *   - return 0 on success, nonzero B200ATTN_ERR_* on failure; the message of the
+ *     last failure on the calling thread is b200attn_last_error().
+ *   - every launcher takes the CUDA stream as an opaque `void*` (cudaStream_t);
+ *     nothing allocates, nothing synchronises, nothing is copied to the host:
+ *     all launchers are CUDA-graph capturable.
+ *   - all pointers are DEVICE pointers unless the name ends in `_host`.
+ *   - strides are in ELEMENTS of the tensor's dtype unless the name says bytes.
+ *   - caller owns every buffer, including workspaces (b200attn_*_workspace_*).
+ */
+#ifndef B200ATTN_H_
+#define B200ATTN_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200ATTN_OK 0
+#define B200ATTN_ERR_INVALID 1     /* bad argument (shape, alignment, dtype) */
+#define B200ATTN_ERR_UNSUPPORTED 2 /* valid but not implemented (head_dim, ...) */
+#define B200ATTN_ERR_CUDA 3        /* a CUDA runtime / driver call failed      */
+
+/* element types of q/k/v/o and of the KV pool */
+#define B200ATTN_BF16 0
+#define B200ATTN_FP16 1
+#define B200ATTN_FP32 2 /* merge_state only */
+
+/* index dtypes */
+#define B200ATTN_I32 0
+#define B200ATTN_I64 1
+
+/* ABI version: bumped whenever a signature below changes. */
+int b200attn_abi_version(void);
+
+/* Message of the last error raised on this thread ("" if none). */
+const char* b200attn_last_error(void);
+
+/* Number of SMs of the current device (grid sizing for callers; 148 on B200). */
+int b200attn_sm_count(void);
+
+/* --------------------------------------------------------------------------
+ * (a1) KV store.  Replaces MHATokenToKVPool.set_kv_buffer -> _set_kv_buffer_impl
+ *   python/sglang/srt/mem_cache/memory_pool.py:141-192, 2331-2456
+ * and the JIT kernel it calls,
+ *   python/sglang/kernels/jit/csrc/elementwise/kvcache.cuh:186-318 (store_kvcache)
+ *   python/sglang/kernels/ops/kvcache/kvcache.py:56-110 (store_cache wrapper).
+ *
+ *   k_cache[loc[t]] = k[t];  v_cache[loc[t]] = v[t]   for t in [0, T)
+ *
+ * Rows are raw bytes (bit-exact copy, dtype agnostic).  `skip_index` mirrors the
+ * reference kernel's `reserved_skip_index` (kvcache.cuh:215): rows whose loc ==
+ * skip_index are not written; pass -1 to write every row (the naive
+ * `k_cache[loc] = k` branch, memory_pool.py:190-192).  Slots outside
+ * [0, size_limit) are never written; if `oob_count` is non-null the number of
+ * such rows is atomically added to it (the reference device-asserts instead,
+ * kvcache.cuh:207-209).
+ * -------------------------------------------------------------------------- */
+int b200attn_kv_store(const void* k, const void* v, void* k_cache, void* v_cache,
+                      const void* loc, int loc_dtype, int64_t T,
+                      int64_t k_row_bytes, int64_t v_row_bytes,
+                      int64_t k_src_stride_bytes, int64_t v_src_stride_bytes,
+                      int64_t k_cache_stride_bytes, int64_t v_cache_stride_bytes,
+                      int64_t size_limit, int64_t skip_index, int32_t* oob_count,
+                      void* stream);
+
+/* --------------------------------------------------------------------------
+ * (a3) Metadata.  Replaces TritonAttnBackend._fill_kv_indptr_and_indices
+ *   python/sglang/srt/layers/attention/triton_backend.py:438-456
+ *   python/sglang/kernels/ops/kvcache/kv_indices.py:8-44
+ *     (create_flashinfer_kv_indices_triton)
+ * and the oracle's gather req_to_token[req, start:end]
+ *   python/sglang/srt/layers/attention/torch_native_backend.py:138-139,239-240.
+ *
+ *   kv_indptr[0] = 0; kv_indptr[b+1] = kv_indptr[b] + kv_lens[b]
+ *   kv_indices[kv_indptr[b] + j] = req_to_token[req_pool_indices[b], kv_start[b] + j]
+ *   qo_indptr (optional): same exclusive scan over qo_lens.
+ *
+ * kv_lens / qo_lens / req_pool_indices / kv_start may be int32 or int64
+ * (`*_dtype`); kv_start and qo_lens/qo_indptr may be null.  kv_indices is int32
+ * or int64 (`kv_indices_dtype`); kv_indptr / qo_indptr are int32.
+ * `kv_indices_capacity` bounds the writes (entries beyond it are dropped).
+ * -------------------------------------------------------------------------- */
+int b200attn_build_kv_indices(const int32_t* req_to_token, int64_t req_to_token_stride,
+                              const void* req_pool_indices, int req_pool_dtype,
+                              const void* kv_lens, int kv_lens_dtype,
+                              const void* kv_start, int kv_start_dtype,
+                              const void* qo_lens, int qo_lens_dtype,
+                              int32_t B,
+                              int32_t* kv_indptr, void* kv_indices, int kv_indices_dtype,
+                              int64_t kv_indices_capacity,
+                              int32_t* qo_indptr, void* stream);
+
+/* Page-table form.  Replaces build_trtllm_mha_page_table
+ *   python/sglang/kernels/ops/kvcache/trtllm_mha_page_table.py:40-120
+ *   page_table[b, j] = req_to_token[req_pool_indices[b], j*page_size] / page_size
+ * for j < ceil(seq_lens[b] / page_size); other entries are left untouched
+ * (same as the reference, whose programs past the page count are guarded out). */
+int b200attn_build_page_table(const int32_t* req_to_token, int64_t req_to_token_stride,
+                              const void* req_pool_indices, int req_pool_dtype,
+                              const void* seq_lens, int seq_lens_dtype, int32_t B,
+                              int32_t page_size, int32_t* page_table,
+                              int64_t page_table_stride, int32_t max_pages,
+                              void* stream);
+
+/* --------------------------------------------------------------------------
+ * (a4) Paged GQA split-KV decode.  Replaces forward_decode of
+ *   python/sglang/srt/layers/attention/torch_native_backend.py:176-277,338-398
+ *   (oracle) and the production kernels
+ *   python/sglang/kernels/ops/attention/decode_attention.py:539-775,910-994,1163-1239.
+ *
+ *   o[r, h, :] = softmax(sm_scale * q[r, h, :] . K_r[:, h/G, :]^T) . V_r[:, h/G, :]
+ *   K_r = k_cache[kv_indices[kv_indptr[r] : kv_indptr[r+1]]]   (token-granular slots)
+ *
+ * q: [B, Hq, D] (row stride q_stride, head stride D); o likewise.
+ * k_cache/v_cache: [slots, Hkv, D] NHD (token stride kv_stride, head stride D).
+ * `q_rows` (nullable int32[B]): row of q/o used by request r (identity if null);
+ * `req_ids` (nullable int32[B]): kv_indptr entry used by work item r (identity
+ * if null) — together they let a MIXED batch route its extend_len==1 rows here.
+ * `lse` (nullable float[B*Hq], indexed like o rows): natural-log LSE.
+ * Workspace: b200attn_decode_workspace_bytes(B, Hq, D, max_splits) bytes, only
+ * touched when max_splits > 1.  The split policy is a pure function of
+ * (kv length, max_splits, min_chunk) evaluated on the device, so CUDA-graph
+ * replay needs no host-side recomputation.
+ * -------------------------------------------------------------------------- */
+int64_t b200attn_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t D, int32_t max_splits);
+
+int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
+                    const void* v_cache, int64_t kv_stride, void* o, int64_t o_stride,
+                    float* lse, const int32_t* kv_indptr, const int32_t* kv_indices,
+                    const int32_t* q_rows, const int32_t* req_ids, int32_t B,
+                    int32_t Hq, int32_t Hkv, int32_t D, int dtype, float sm_scale,
+                    int32_t max_splits, int32_t min_chunk, void* workspace,
+                    int64_t workspace_bytes, void* stream);
+
+/* --------------------------------------------------------------------------
+ * (a5) Ragged extend / prefill over cached prefix + new tokens.  Replaces
+ *   python/sglang/srt/layers/attention/torch_native_backend.py:61-174,279-336
+ *   (oracle) and python/sglang/kernels/ops/attention/extend_attention.py:304-923,
+ *   963-1410 (unified single-pass variant).
+ *
+ * Request b owns q rows [qo_indptr[b], qo_indptr[b+1]) and keys
+ * kv_indices[kv_indptr[b] : kv_indptr[b+1]] (prefix AND the new tokens, which
+ * the caller has already stored into the pool — single KV source, like the
+ * oracle, torch_native_backend.py:298-301,139-141).  With E = #q rows and
+ * L = #keys, query j sits at absolute position L - E + j and attends keys
+ * 0..L-E+j when `causal`, else all L keys (ENCODER_ONLY / bidirectional).
+ *
+ * The QK^T and PV contractions run on tcgen05 tensor cores with TMEM
+ * accumulators; `page_size` > 1 promises the paged-allocator invariant
+ * (python/sglang/srt/mem_cache/allocator/paged.py:163-166: a logical page lies
+ * in one physical page) and enables TMA page boxes; page_size == 1 gathers rows.
+ * `lse` nullable float[T*Hq] natural log.  `max_qo_len_host` / `total_q_host`
+ * are host-side upper bounds used only to size the grid (graph-safe).
+ * -------------------------------------------------------------------------- */
+int64_t b200attn_extend_workspace_bytes(int32_t B, int64_t total_q, int32_t Hq);
+
+int b200attn_extend(const void* q, int64_t q_stride, const void* k_cache,
+                    const void* v_cache, int64_t kv_stride, int64_t num_slots,
+                    void* o, int64_t o_stride, float* lse, const int32_t* qo_indptr,
+                    const int32_t* kv_indptr, const int32_t* kv_indices, int32_t B,
+                    int64_t total_q_host, int32_t max_qo_len_host, int32_t Hq,
+                    int32_t Hkv, int32_t D, int32_t page_size, int dtype, int causal,
+                    float sm_scale, void* workspace, int64_t workspace_bytes,
+                    void* stream);
+
+/* --------------------------------------------------------------------------
+ * (a6) merge_state.  Replaces merge_state / merge_state_v2
+ *   python/sglang/srt/layers/attention/merge_state.py:26-46
+ *   python/sglang/kernels/aot/csrc/attention/merge_attn_states.cu:31-206
+ *
+ *   m = max(sa, sb); wa = e^(sa-m); wb = e^(sb-m)
+ *   v = (wa*va + wb*vb) / (wa + wb);  s = log(wa + wb) + m      (natural log)
+ *   +inf LSE is treated as -inf (merge_attn_states.cu:66-67).
+ *
+ * v_*: [T, H, D] contiguous, dtype bf16/fp16/fp32; s_*: float [T, H];
+ * s_out nullable.  In-place (v_out == v_a, s_out == s_a) is allowed.
+ * -------------------------------------------------------------------------- */
+int b200attn_merge_state(const void* v_a, const float* s_a, const void* v_b,
+                         const float* s_b, void* v_out, float* s_out, int64_t T,
+                         int32_t H, int32_t D, int dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ATTN_H_ */

@@ -1,0 +1,422 @@
+// (a4) Paged GQA split-KV flash-decode for B200 (sm_100a).
+//
+// Semantics follow the oracle python/sglang/srt/layers/attention/torch_native_backend.py:
+// 176-277 (per request: gather K/V rows through req_to_token, softmax(q K^T * scale) V,
+// non-causal, GQA head h -> kv head h / G).  The design is HBM-first:
+//
+//   * one CTA owns (request, kv head, kv split): all G query heads of the kv head
+//     share every K/V byte that is fetched -> each KV byte crosses HBM exactly once;
+//   * K/V rows are gathered token-granular (page_size agnostic) with 16-byte
+//     cp.async.cg into a 3-stage shared-memory ring, 32 KB per stage and two
+//     resident CTAs per SM => 128 KB of loads in flight per SM;
+//   * the G x D query block is padded to the M=16 of mma.sync.m16n8k16; each of the
+//     four warps takes 16 keys of a 64-key tile, S = Q K^T and O += P V run on the
+//     tensor pipe straight out of XOR-swizzled shared memory (ldmatrix / .trans),
+//     the online softmax runs in fp32 with quad shuffles;
+//   * warps are merged through shared memory, splits through a fp32 workspace and
+//     a tiny merge kernel.  The split policy is a device-side pure function of
+//     the kv length, so a captured CUDA graph replays with new lengths untouched.
+//
+// Algorithmic bytes per (request, kv head): 2 * L * D * sizeof(T) (K and V rows)
+// + 4 * L (int32 slot ids).
+#include "common.cuh"
+
+namespace b200attn {
+
+constexpr int kDecTile = 64;     // keys per pipeline stage
+constexpr int kDecStages = 3;    // cp.async ring depth
+constexpr int kDecThreads = 128; // 4 warps x 16 keys
+constexpr int kDecMaxG = 16;     // q heads per CTA (M of the mma)
+
+struct DecodeParams {
+  const void* q;
+  const void* k_cache;
+  const void* v_cache;
+  void* o;
+  float* lse;
+  const int32_t* kv_indptr;
+  const int32_t* kv_indices;
+  const int32_t* q_rows;
+  const int32_t* req_ids;
+  float* ws_o;    // [B, Hq, max_splits, D]
+  float* ws_lse;  // [B, Hq, max_splits]   (log2 domain)
+  int64_t q_stride, kv_stride, o_stride;
+  int B, Hq, Hkv, G, groups_per_kvh;
+  int max_splits, min_chunk;
+  float scale_log2;
+};
+
+template <int D>
+__device__ __forceinline__ uint32_t swz_off(int row, int chunk) {
+  // byte offset of 16-byte chunk `chunk` of row `row` in a [rows][D] 2-byte tile;
+  // chunks are XOR-swizzled with the row so that ldmatrix (8 rows x 16 B) is conflict free.
+  constexpr int kChunks = D / 8;
+  return (uint32_t)(row * (D * 2) + (((chunk ^ (row & 7)) & (kChunks - 1)) << 4));
+}
+
+template <int D, bool kBf16>
+__global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodeParams p) {
+  using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
+  constexpr int kChunks = D / 8;                   // 16-byte chunks per row
+  constexpr int kTileBytes = kDecTile * D * 2;     // one operand, one stage
+  constexpr int kStageBytes = 2 * kTileBytes;      // K + V
+  constexpr int kLoadsPerThread = kDecTile * kChunks / kDecThreads;  // per operand
+  constexpr int kRowsPerPass = kDecThreads / kChunks;
+  extern __shared__ __align__(128) uint8_t smem[];
+
+  const int split = blockIdx.x;
+  const int hg = blockIdx.y;  // kv head * groups_per_kvh + group
+  const int item = blockIdx.z;
+  const int kvh = hg / p.groups_per_kvh;
+  const int grp = hg - kvh * p.groups_per_kvh;
+  const int req = p.req_ids ? p.req_ids[item] : item;
+  const int qrow = p.q_rows ? p.q_rows[item] : item;
+  const int kv_beg = p.kv_indptr[req];
+  const int L = p.kv_indptr[req + 1] - kv_beg;
+  int nsplit, chunk;
+  split_policy(L, p.max_splits, p.min_chunk, kDecTile, nsplit, chunk);
+  if (split >= nsplit) return;
+  const int k_lo = split * chunk;
+  const int k_hi = min(L, k_lo + chunk);
+  const int ntiles = (k_hi - k_lo + kDecTile - 1) / kDecTile;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int h0 = kvh * p.G + grp * kDecMaxG;             // first q head of this CTA
+  const int gcount = min(kDecMaxG, p.G - grp * kDecMaxG); // valid q heads (rows of M)
+
+  // ---- Q fragments (A operand, 16 x D), rows >= gcount are zero -----------
+  uint32_t qf[D / 16][4];
+  {
+    const T* qbase = reinterpret_cast<const T*>(p.q) + (int64_t)qrow * p.q_stride + (int64_t)h0 * D;
+    const int r0 = lane >> 2, c0 = (lane & 3) * 2;
+#pragma unroll
+    for (int ks = 0; ks < D / 16; ++ks) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int r = r0 + (j & 1) * 8;
+        const int c = ks * 16 + c0 + (j >> 1) * 8;
+        qf[ks][j] = (r < gcount) ? *reinterpret_cast<const uint32_t*>(qbase + (int64_t)r * D + c) : 0u;
+      }
+    }
+  }
+
+  // ---- producer state -------------------------------------------------------
+  const int ld_chunk = tid % kChunks;
+  const int ld_row0 = tid / kChunks;
+  const uint8_t* kc = reinterpret_cast<const uint8_t*>(p.k_cache) + (int64_t)kvh * D * 2 + ld_chunk * 16;
+  const uint8_t* vc = reinterpret_cast<const uint8_t*>(p.v_cache) + (int64_t)kvh * D * 2 + ld_chunk * 16;
+  const int64_t row_bytes = p.kv_stride * 2;
+  const int32_t* idx = p.kv_indices + kv_beg;
+  const uint32_t smem_base = smem_u32(smem);
+
+  int32_t slots[kLoadsPerThread];  // slot ids of the NEXT tile to issue
+  auto fetch_slots = [&](int tile) {
+    const int base = k_lo + tile * kDecTile + ld_row0;
+#pragma unroll
+    for (int i = 0; i < kLoadsPerThread; ++i) {
+      const int key = base + i * kRowsPerPass;
+      slots[i] = (tile < ntiles && key < k_hi) ? __ldg(idx + key) : -1;
+    }
+  };
+  auto issue_tile = [&](int stage) {
+    const uint32_t ks = smem_base + stage * kStageBytes;
+    const uint32_t vs = ks + kTileBytes;
+#pragma unroll
+    for (int i = 0; i < kLoadsPerThread; ++i) {
+      const int row = ld_row0 + i * kRowsPerPass;
+      const uint32_t off = swz_off<D>(row, ld_chunk);
+      const bool ok = slots[i] >= 0;
+      const int64_t g = ok ? (int64_t)slots[i] * row_bytes : 0;
+      cp_async16(ks + off, kc + g, ok ? 16 : 0);  // invalid rows are zero-filled
+      cp_async16(vs + off, vc + g, ok ? 16 : 0);
+    }
+  };
+
+  fetch_slots(0);
+#pragma unroll
+  for (int s = 0; s < kDecStages - 1; ++s) {
+    if (s < ntiles) issue_tile(s);
+    cp_async_commit();
+    fetch_slots(s + 1);
+  }
+
+  // ---- per-warp online-softmax state ---------------------------------------
+  float o_acc[D / 8][4];
+#pragma unroll
+  for (int n = 0; n < D / 8; ++n) o_acc[n][0] = o_acc[n][1] = o_acc[n][2] = o_acc[n][3] = 0.f;
+  float m_run[2] = {-INFINITY, -INFINITY};  // rows lane/4 and lane/4 + 8
+  float l_run[2] = {0.f, 0.f};              // per-thread partial row sums
+
+  const int lm = lane >> 3, lr = lane & 7;  // ldmatrix: matrix id / row in matrix
+
+  for (int t = 0; t < ntiles; ++t) {
+    cp_async_wait<kDecStages - 2>();
+    __syncthreads();
+    {
+      const int nt = t + kDecStages - 1;
+      if (nt < ntiles) issue_tile(nt % kDecStages);
+      cp_async_commit();
+      fetch_slots(nt + 1);
+    }
+    const uint32_t ks = smem_base + (t % kDecStages) * kStageBytes;
+    const uint32_t vs = ks + kTileBytes;
+    const int key0 = k_lo + t * kDecTile + warp * 16;  // first key of this warp
+    if (key0 < k_hi) {                                 // warp-uniform
+      // S = Q K^T for 16 keys (two 8-key n-blocks)
+      float s[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+      {
+        const int krow = warp * 16 + (lm >> 1) * 8 + lr;
+#pragma unroll
+        for (int ksp = 0; ksp < D / 16; ++ksp) {
+          uint32_t b0, b1, b2, b3;
+          ldmatrix_x4(b0, b1, b2, b3, ks + swz_off<D>(krow, 2 * ksp + (lm & 1)));
+          mma_16816<kBf16>(s[0], qf[ksp], b0, b1);
+          mma_16816<kBf16>(s[1], qf[ksp], b2, b3);
+        }
+      }
+      // scale, mask the ragged tail, online softmax (rows r and r+8 of the quad)
+      const int kcol = key0 + (lane & 3) * 2;
+      float tmax[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+      for (int nb = 0; nb < 2; ++nb) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int key = kcol + nb * 8 + (j & 1);
+          const float x = (key < k_hi) ? s[nb][j] * p.scale_log2 : -INFINITY;
+          s[nb][j] = x;
+          tmax[j >> 1] = fmaxf(tmax[j >> 1], x);
+        }
+      }
+      float alpha[2];
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        tmax[r] = fmaxf(tmax[r], __shfl_xor_sync(0xffffffffu, tmax[r], 1));
+        tmax[r] = fmaxf(tmax[r], __shfl_xor_sync(0xffffffffu, tmax[r], 2));
+        const float m_new = fmaxf(m_run[r], tmax[r]);  // finite: key0 < k_hi => >= 1 valid key
+        alpha[r] = fast_exp2(m_run[r] - m_new);
+        m_run[r] = m_new;
+        l_run[r] *= alpha[r];
+      }
+      uint32_t pf[4];
+#pragma unroll
+      for (int nb = 0; nb < 2; ++nb) {
+        const float p0 = fast_exp2(s[nb][0] - m_run[0]);
+        const float p1 = fast_exp2(s[nb][1] - m_run[0]);
+        const float p2 = fast_exp2(s[nb][2] - m_run[1]);
+        const float p3 = fast_exp2(s[nb][3] - m_run[1]);
+        l_run[0] += p0 + p1;
+        l_run[1] += p2 + p3;
+        pf[nb * 2 + 0] = pack2<kBf16>(p0, p1);
+        pf[nb * 2 + 1] = pack2<kBf16>(p2, p3);
+      }
+      // O = alpha * O + P V
+      const int vrow = warp * 16 + (lm & 1) * 8 + lr;
+#pragma unroll
+      for (int np = 0; np < D / 16; ++np) {
+        uint32_t b0, b1, b2, b3;
+        ldmatrix_x4_trans(b0, b1, b2, b3, vs + swz_off<D>(vrow, 2 * np + (lm >> 1)));
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          float(&acc)[4] = o_acc[2 * np + h];
+          acc[0] *= alpha[0];
+          acc[1] *= alpha[0];
+          acc[2] *= alpha[1];
+          acc[3] *= alpha[1];
+        }
+        mma_16816<kBf16>(o_acc[2 * np], pf, b0, b1);
+        mma_16816<kBf16>(o_acc[2 * np + 1], pf, b2, b3);
+      }
+    }
+  }
+  cp_async_wait<0>();
+  __syncthreads();  // ring is dead; reuse it for the cross-warp merge
+
+  // ---- merge the four warps (fp32, shared memory) ---------------------------
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 1);
+    l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
+  }
+  float* sm_o = reinterpret_cast<float*>(smem);           // [4][16][D]
+  float* sm_m = sm_o + 4 * 16 * D;                        // [4][16]
+  float* sm_l = sm_m + 64;                                // [4][16]
+  {
+    const int r0 = lane >> 2, c0 = (lane & 3) * 2;
+#pragma unroll
+    for (int n = 0; n < D / 8; ++n) {
+      float* dst = sm_o + (warp * 16 + r0) * D + n * 8 + c0;
+      *reinterpret_cast<float2*>(dst) = make_float2(o_acc[n][0], o_acc[n][1]);
+      *reinterpret_cast<float2*>(dst + 8 * D) = make_float2(o_acc[n][2], o_acc[n][3]);
+    }
+    if ((lane & 3) == 0) {
+      sm_m[warp * 16 + r0] = m_run[0];
+      sm_m[warp * 16 + r0 + 8] = m_run[1];
+      sm_l[warp * 16 + r0] = l_run[0];
+      sm_l[warp * 16 + r0 + 8] = l_run[1];
+    }
+  }
+  __syncthreads();
+  const bool direct = (nsplit == 1);
+  for (int e = tid; e < gcount * (D / 4); e += kDecThreads) {
+    const int r = e / (D / 4), c = (e - r * (D / 4)) * 4;
+    float m = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) m = fmaxf(m, sm_m[w * 16 + r]);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    float l = 0.f;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const float mw = sm_m[w * 16 + r];
+      const float f = (mw == -INFINITY) ? 0.f : fast_exp2(mw - m);
+      const float4 x = *reinterpret_cast<const float4*>(sm_o + (w * 16 + r) * D + c);
+      acc.x += f * x.x;
+      acc.y += f * x.y;
+      acc.z += f * x.z;
+      acc.w += f * x.w;
+      l += f * sm_l[w * 16 + r];
+    }
+    const float inv = (l > 0.f) ? 1.f / l : 0.f;
+    acc.x *= inv;
+    acc.y *= inv;
+    acc.z *= inv;
+    acc.w *= inv;
+    const float lse2 = (l > 0.f) ? m + log2f(l) : -INFINITY;
+    const int h = h0 + r;
+    if (direct) {
+      T* dst = reinterpret_cast<T*>(p.o) + (int64_t)qrow * p.o_stride + (int64_t)h * D + c;
+      uint2 pk;
+      pk.x = pack2<kBf16>(acc.x, acc.y);
+      pk.y = pack2<kBf16>(acc.z, acc.w);
+      *reinterpret_cast<uint2*>(dst) = pk;
+      if (p.lse != nullptr && c == 0) p.lse[(int64_t)qrow * p.Hq + h] = lse2 * kLn2;
+    } else {
+      const int64_t w = ((int64_t)item * p.Hq + h) * p.max_splits + split;
+      *reinterpret_cast<float4*>(p.ws_o + w * D + c) = acc;
+      if (c == 0) p.ws_lse[w] = lse2;
+    }
+  }
+}
+
+// Merge the split partials of one (request, q head): grid (Hq, B), D/4 threads.
+template <int D, bool kBf16>
+__global__ void __launch_bounds__(D / 4) decode_merge_kernel(const DecodeParams p) {
+  using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
+  const int h = blockIdx.x, item = blockIdx.y;
+  const int req = p.req_ids ? p.req_ids[item] : item;
+  const int qrow = p.q_rows ? p.q_rows[item] : item;
+  const int L = p.kv_indptr[req + 1] - p.kv_indptr[req];
+  int nsplit, chunk;
+  split_policy(L, p.max_splits, p.min_chunk, kDecTile, nsplit, chunk);
+  if (nsplit == 1) return;  // the attention kernel wrote the output directly
+  const int64_t w0 = ((int64_t)item * p.Hq + h) * p.max_splits;
+  const int c = threadIdx.x * 4;
+  float m = -INFINITY;
+  for (int s = 0; s < nsplit; ++s) m = fmaxf(m, __ldg(p.ws_lse + w0 + s));
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  float l = 0.f;
+  for (int s = 0; s < nsplit; ++s) {
+    const float ls = __ldg(p.ws_lse + w0 + s);
+    const float f = (ls == -INFINITY) ? 0.f : fast_exp2(ls - m);
+    const float4 x = *reinterpret_cast<const float4*>(p.ws_o + (w0 + s) * D + c);
+    acc.x += f * x.x;
+    acc.y += f * x.y;
+    acc.z += f * x.z;
+    acc.w += f * x.w;
+    l += f;
+  }
+  const float inv = (l > 0.f) ? 1.f / l : 0.f;
+  T* dst = reinterpret_cast<T*>(p.o) + (int64_t)qrow * p.o_stride + (int64_t)h * D + c;
+  uint2 pk;
+  pk.x = pack2<kBf16>(acc.x * inv, acc.y * inv);
+  pk.y = pack2<kBf16>(acc.z * inv, acc.w * inv);
+  *reinterpret_cast<uint2*>(dst) = pk;
+  if (p.lse != nullptr && c == 0)
+    p.lse[(int64_t)qrow * p.Hq + h] = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
+}
+
+template <int D, bool kBf16>
+static int launch_decode(const DecodeParams& p, cudaStream_t st) {
+  constexpr int kRing = kDecStages * 2 * kDecTile * D * 2;
+  constexpr int kMerge = (4 * 16 * D + 128) * 4;
+  constexpr int kSmem = kRing > kMerge ? kRing : kMerge;
+  static bool configured = false;  // idempotent attribute; races are benign
+  if (!configured) {
+    B2_CUDA(cudaFuncSetAttribute(decode_kernel<D, kBf16>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+    B2_CUDA(cudaFuncSetAttribute(decode_kernel<D, kBf16>,
+                                 cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    configured = true;
+  }
+  dim3 grid((unsigned)p.max_splits, (unsigned)(p.Hkv * p.groups_per_kvh), (unsigned)p.B);
+  decode_kernel<D, kBf16><<<grid, kDecThreads, kSmem, st>>>(p);
+  B2_LAUNCH_CHECK();
+  if (p.max_splits > 1) {
+    dim3 mgrid((unsigned)p.Hq, (unsigned)p.B);
+    decode_merge_kernel<D, kBf16><<<mgrid, D / 4, 0, st>>>(p);
+    B2_LAUNCH_CHECK();
+  }
+  return B200ATTN_OK;
+}
+
+}  // namespace b200attn
+
+extern "C" int64_t b200attn_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t D,
+                                                   int32_t max_splits) {
+  if (max_splits <= 1) return 0;
+  return (int64_t)B * Hq * max_splits * (D + 1) * 4;
+}
+
+extern "C" int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
+                               const void* v_cache, int64_t kv_stride, void* o, int64_t o_stride,
+                               float* lse, const int32_t* kv_indptr, const int32_t* kv_indices,
+                               const int32_t* q_rows, const int32_t* req_ids, int32_t B,
+                               int32_t Hq, int32_t Hkv, int32_t D, int dtype, float sm_scale,
+                               int32_t max_splits, int32_t min_chunk, void* workspace,
+                               int64_t workspace_bytes, void* stream) {
+  using namespace b200attn;
+  B2_CHECK_ARG(B >= 0, "decode: negative batch");
+  if (B == 0) return B200ATTN_OK;
+  B2_CHECK_ARG(q && k_cache && v_cache && o && kv_indptr && kv_indices, "decode: null pointer");
+  B2_CHECK_ARG(Hq > 0 && Hkv > 0 && Hq % Hkv == 0, "decode: Hq=%d must be a multiple of Hkv=%d",
+               Hq, Hkv);
+  B2_CHECK_ARG(B <= 65535 && Hq <= 65535, "decode: grid too large");
+  B2_CHECK_ARG(max_splits >= 1 && max_splits <= 1024 && min_chunk >= 1, "decode: bad split policy");
+  B2_CHECK_ARG(q_stride % 8 == 0 && kv_stride % 8 == 0 && o_stride % 4 == 0,
+               "decode: strides must keep rows 16-byte aligned");
+  B2_CHECK_ARG((((uintptr_t)q | (uintptr_t)k_cache | (uintptr_t)v_cache | (uintptr_t)o) & 15) == 0,
+               "decode: tensors must be 16-byte aligned");
+  if (dtype != B200ATTN_BF16 && dtype != B200ATTN_FP16) B2_UNSUPPORTED("decode: dtype %d", dtype);
+  if (D != 64 && D != 128) B2_UNSUPPORTED("decode: head_dim %d (supported: 64, 128)", D);
+  const int64_t need = b200attn_decode_workspace_bytes(B, Hq, D, max_splits);
+  B2_CHECK_ARG(need == 0 || (workspace && workspace_bytes >= need),
+               "decode: workspace too small (%lld < %lld)", (long long)workspace_bytes,
+               (long long)need);
+  DecodeParams p;
+  p.q = q;
+  p.k_cache = k_cache;
+  p.v_cache = v_cache;
+  p.o = o;
+  p.lse = lse;
+  p.kv_indptr = kv_indptr;
+  p.kv_indices = kv_indices;
+  p.q_rows = q_rows;
+  p.req_ids = req_ids;
+  p.ws_o = reinterpret_cast<float*>(workspace);
+  p.ws_lse = p.ws_o ? p.ws_o + (int64_t)B * Hq * max_splits * D : nullptr;
+  p.q_stride = q_stride;
+  p.kv_stride = kv_stride;
+  p.o_stride = o_stride;
+  p.B = B;
+  p.Hq = Hq;
+  p.Hkv = Hkv;
+  p.G = Hq / Hkv;
+  p.groups_per_kvh = (p.G + kDecMaxG - 1) / kDecMaxG;
+  p.max_splits = max_splits;
+  p.min_chunk = min_chunk;
+  p.scale_log2 = sm_scale * kLog2e;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (D == 128) {
+    return dtype == B200ATTN_BF16 ? launch_decode<128, true>(p, st) : launch_decode<128, false>(p, st);
+  }
+  return dtype == B200ATTN_BF16 ? launch_decode<64, true>(p, st) : launch_decode<64, false>(p, st);
+}
