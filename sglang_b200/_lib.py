@@ -1,0 +1,105 @@
+"""ctypes binding of libb200attn.so (the C ABI declared in include/b200attn.h).
+
+There is deliberately no fallback: if the shared library is missing or a call
+fails, the error is raised to the caller.  The library is built in-tree by
+``sglang_b200/csrc/Makefile`` (see ``__graft_entry__.build``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import re
+from typing import Dict, List
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200attn.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "b200attn.h")
+
+BF16, FP16, FP32 = 0, 1, 2
+I32, I64 = 0, 1
+
+_vp, _i32, _i64, _f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
+
+# name -> (restype, argtypes); must match include/b200attn.h
+SIGNATURES = {
+    "b200attn_abi_version": (C.c_int, []),
+    "b200attn_last_error": (C.c_char_p, []),
+    "b200attn_sm_count": (C.c_int, []),
+    "b200attn_kv_store": (
+        C.c_int,
+        [_vp, _vp, _vp, _vp, _vp, C.c_int, _i64, _i64, _i64, _i64, _i64, _i64, _i64, _i64, _i64, _vp, _vp],
+    ),
+    "b200attn_build_kv_indices": (
+        C.c_int,
+        [_vp, _i64, _vp, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, C.c_int, _i32, _vp, _vp, C.c_int, _i64, _vp, _vp],
+    ),
+    "b200attn_build_page_table": (
+        C.c_int,
+        [_vp, _i64, _vp, C.c_int, _vp, C.c_int, _i32, _i32, _vp, _i64, _i32, _vp],
+    ),
+    "b200attn_decode_workspace_bytes": (_i64, [_i32, _i32, _i32, _i32]),
+    "b200attn_decode": (
+        C.c_int,
+        [_vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, C.c_int,
+         _f32, _i32, _i32, _vp, _i64, _vp],
+    ),
+    "b200attn_extend_workspace_bytes": (_i64, [_i32, _i64, _i32]),
+    "b200attn_extend": (
+        C.c_int,
+        [_vp, _i64, _vp, _vp, _i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _i32, _i32,
+         _i32, _i32, C.c_int, C.c_int, _f32, _vp, _i64, _vp],
+    ),
+    "b200attn_merge_state": (
+        C.c_int,
+        [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, C.c_int, _vp],
+    ),
+}
+
+
+class B200AttnError(RuntimeError):
+    """A C-ABI call returned nonzero (message from b200attn_last_error)."""
+
+
+_lib = None
+
+
+def header_symbols() -> List[str]:
+    """Every function name declared in include/b200attn.h."""
+    with open(HEADER_PATH) as f:
+        text = f.read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200attn_[a-z0-9_]+)\s*\(", text)))
+
+
+def load() -> C.CDLL:
+    """Load the shared library (once) and type every entry point."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build it with `make -C sglang_b200/csrc` "
+            "(or `python -c 'import __graft_entry__ as g; g.build()'`). "
+            "There is no CPU / PyTorch fallback for this backend."
+        )
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = load().b200attn_last_error().decode("utf-8", "replace")
+        kind = {1: "invalid argument", 2: "unsupported", 3: "CUDA error"}.get(rc, f"error {rc}")
+        if rc == 2:
+            raise NotImplementedError(f"{what}: {msg}")
+        raise B200AttnError(f"{what}: {kind}: {msg}")
+
+
+def exported() -> Dict[str, bool]:
+    lib = load()
+    return {name: hasattr(lib, name) for name in header_symbols()}

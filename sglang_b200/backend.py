@@ -1,0 +1,300 @@
+"""B200AttnBackend — the drop-in for SGLang's ``AttentionBackend`` plugin API.
+
+Reference interface mirrored here (same method names, argument meaning, return
+shapes and error behaviour):
+  python/sglang/srt/layers/attention/base_attn_backend.py:36-308   (AttentionBackend ABC)
+  python/sglang/srt/layers/attention/torch_native_backend.py:19-401 (oracle semantics)
+  python/sglang/srt/layers/attention/triton_backend.py:766-1115     (metadata + graph hooks)
+
+Every compute step is a call into libb200attn.so (hand-written sm_100a CUDA);
+there is no Triton, no per-arch dispatch and no CPU / PyTorch fallback.
+"""
+from __future__ import annotations
+
+import dataclasses
+from types import SimpleNamespace
+from typing import Dict, Optional
+
+import torch
+
+from . import ops
+
+try:  # inside SGLang the real ABC is used so isinstance checks in the runners pass
+    from sglang.srt.layers.attention.base_attn_backend import AttentionBackend as _Base  # type: ignore
+except Exception:  # standalone: same contract, defined locally
+
+    class _Base:  # type: ignore
+        """Stand-in with the reference ABC's dispatcher (base_attn_backend.py:215-258)."""
+
+        def init_forward_metadata(self, forward_batch):
+            self.init_forward_metadata_out_graph(forward_batch)
+            self.init_forward_metadata_in_graph(forward_batch)
+
+        def init_forward_metadata_in_graph(self, forward_batch):
+            pass
+
+        def forward(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, **kwargs):
+            mode = forward_batch.forward_mode
+            if mode.is_idle():
+                return q.new_empty(q.shape[0], layer.tp_q_head_num * layer.v_head_dim)
+            if mode.is_decode():
+                return self.forward_decode(q, k, v, layer, forward_batch, save_kv_cache=save_kv_cache, **kwargs)
+            return self.forward_extend(q, k, v, layer, forward_batch, save_kv_cache=save_kv_cache, **kwargs)
+
+
+@dataclasses.dataclass
+class ForwardMetadata:
+    """Per-forward metadata; field names chosen to satisfy the reference's
+    metadata invariants kit (runner_modes/metadata_invariants.py:22-103)."""
+
+    kv_indptr: torch.Tensor                  # int32 [B+1]
+    kv_indices: torch.Tensor                 # int32 [sum kv_len], token-granular slots
+    cache_seqlens_int32: Optional[torch.Tensor] = None
+    qo_indptr: Optional[torch.Tensor] = None  # int32 [B+1] (extend only)
+    page_table: Optional[torch.Tensor] = None  # int32 [B, max_pages] (exported, page_size > 1)
+    max_extend_len: int = 0
+    num_extend_tokens: int = 0
+    max_splits: int = 1
+    min_chunk: int = 256
+    workspace: Optional[torch.Tensor] = None
+    batch_size: int = 0
+
+
+def _attn_type_value(layer) -> str:
+    t = getattr(layer, "attn_type", None)
+    return str(getattr(t, "value", t))
+
+
+class B200AttnBackend(_Base):
+    """Attention backend for B200 behind the reference plugin API."""
+
+    # decode kv splits never finer than this many keys
+    MIN_CHUNK = 256
+
+    def __init__(self, model_runner, skip_padding_slot: bool = True, export_page_table: bool = False):
+        super().__init__()
+        if not torch.cuda.is_available():
+            raise AssertionError("B200AttnBackend needs a CUDA device (sm_100a); no CPU fallback")
+        from . import _lib
+
+        _lib.load()  # fail loudly now if libb200attn.so is missing
+        self.device = model_runner.device
+        self.page_size = int(getattr(model_runner, "page_size", 1) or 1)
+        self.req_to_token_pool = model_runner.req_to_token_pool
+        self.token_to_kv_pool = model_runner.token_to_kv_pool
+        self.req_to_token = self.req_to_token_pool.req_to_token
+        self.max_context_len = int(self.req_to_token.shape[1])
+        if getattr(model_runner, "sliding_window_size", None) not in (None, -1):
+            raise NotImplementedError("b200 backend: sliding-window models are not supported")
+        self.skip_padding_slot = skip_padding_slot
+        self.export_page_table = export_page_table
+        self.forward_metadata: Optional[ForwardMetadata] = None
+        self.num_sms = ops.sm_count()
+        # CUDA-graph state (init_cuda_graph_state)
+        self._graph: Optional[SimpleNamespace] = None
+        self._graph_splits: Dict[int, int] = {}
+        # eager-mode scratch that survives across forwards (grown on demand)
+        self._ws: Optional[torch.Tensor] = None
+
+    # ------------------------------------------------------------------ helpers
+    def support_triton(self) -> bool:  # base_attn_backend.py:298
+        return False
+
+    def _workspace(self, nbytes: int) -> Optional[torch.Tensor]:
+        if nbytes <= 0:
+            return None
+        if self._ws is None or self._ws.numel() < nbytes:
+            self._ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        return self._ws
+
+    def _check_layer(self, layer, kwargs) -> None:
+        if getattr(layer, "sliding_window_size", -1) not in (None, -1, 0):
+            raise NotImplementedError("b200 backend: sliding_window_size is not supported")
+        if getattr(layer, "logit_cap", 0.0):
+            raise NotImplementedError("b200 backend: logit_cap is not supported")
+        if getattr(layer, "is_cross_attention", False):
+            raise NotImplementedError("b200 backend: cross attention is not supported")
+        if getattr(layer, "v_head_dim", layer.head_dim) != layer.head_dim:
+            raise NotImplementedError("b200 backend: v_head_dim != head_dim is not supported")
+        if getattr(layer, "k_scale", None) is not None or getattr(layer, "v_scale", None) is not None:
+            raise NotImplementedError("b200 backend: fp8 KV cache scales are not supported")
+        if kwargs.get("sinks") is not None:
+            raise NotImplementedError("b200 backend: attention sinks are not supported")
+
+    def _store(self, layer, forward_batch, k, v) -> None:
+        """KV pool write path (memory_pool.py:2331-2456) through the sm_100a store kernel."""
+        pool = self.token_to_kv_pool
+        kbuf, vbuf = pool.get_kv_buffer(layer.layer_id)
+        k = k.view(-1, layer.tp_k_head_num, layer.head_dim)
+        v = v.view(-1, layer.tp_v_head_num, layer.v_head_dim)
+        if k.dtype != kbuf.dtype:  # memory_pool.py:2365-2371
+            k, v = k.to(kbuf.dtype), v.to(vbuf.dtype)
+        ops.store_cache(k, v, kbuf, vbuf, forward_batch.out_cache_loc,
+                        reserved_skip_index=0 if self.skip_padding_slot else -1)
+
+    # ------------------------------------------------------------------ metadata
+    def _build(self, fb, kv_lens, kv_indptr, kv_indices, qo_lens=None, qo_indptr=None) -> None:
+        ops.build_kv_indices(self.req_to_token, fb.req_pool_indices, kv_lens, kv_indptr, kv_indices,
+                             qo_lens=qo_lens, qo_indptr=qo_indptr)
+
+    def _page_table(self, fb, B: int) -> Optional[torch.Tensor]:
+        if not self.export_page_table or self.page_size <= 1:
+            return None
+        max_pages = -(-self.max_context_len // self.page_size)
+        pt = torch.zeros((B, max_pages), dtype=torch.int32, device=self.device)
+        ops.build_page_table(self.req_to_token, fb.req_pool_indices, fb.seq_lens, pt, self.page_size)
+        return pt
+
+    def init_forward_metadata(self, forward_batch) -> None:
+        """Eager entry point (base_attn_backend.py:65-71)."""
+        fb = forward_batch
+        mode = fb.forward_mode
+        if mode.is_idle():
+            self.forward_metadata = None
+            return
+        B = int(fb.batch_size)
+        dev = self.device
+        total = getattr(fb, "seq_lens_sum", 0) or 0
+        if total <= 0:
+            cpu = getattr(fb, "seq_lens_cpu", None)
+            total = int(cpu.sum()) if cpu is not None else B * self.max_context_len
+        kv_indptr = torch.empty(B + 1, dtype=torch.int32, device=dev)
+        kv_indices = torch.empty(max(int(total), 1), dtype=torch.int32, device=dev)
+        if mode.is_decode():
+            self._build(fb, fb.seq_lens, kv_indptr, kv_indices)
+            md = ForwardMetadata(kv_indptr=kv_indptr, kv_indices=kv_indices, batch_size=B,
+                                 cache_seqlens_int32=fb.seq_lens.to(torch.int32),
+                                 page_table=self._page_table(fb, B), min_chunk=self.MIN_CHUNK)
+            cpu = getattr(fb, "seq_lens_cpu", None)
+            md._max_kv_len = int(cpu.max()) if cpu is not None else self.max_context_len
+            self.forward_metadata = md
+            return
+        if mode.is_target_verify() or mode.is_draft_extend_v2() or getattr(fb, "spec_info", None) is not None:
+            raise NotImplementedError("b200 backend: speculative modes (custom masks) are not supported")
+        if getattr(fb, "encoder_lens", None) is not None:
+            raise NotImplementedError("b200 backend: encoder_lens (cross attention) is not supported")
+        qo_indptr = torch.empty(B + 1, dtype=torch.int32, device=dev)
+        self._build(fb, fb.seq_lens, kv_indptr, kv_indices, qo_lens=fb.extend_seq_lens, qo_indptr=qo_indptr)
+        ext_cpu = getattr(fb, "extend_seq_lens_cpu", None)
+        if ext_cpu is not None:
+            max_ext, tot_ext = max(ext_cpu), sum(ext_cpu)
+        else:  # gpu-only mode: one sync, eager path only
+            max_ext, tot_ext = int(fb.extend_seq_lens.max()), int(fb.extend_seq_lens.sum())
+        self.forward_metadata = ForwardMetadata(
+            kv_indptr=kv_indptr, kv_indices=kv_indices, qo_indptr=qo_indptr, batch_size=B,
+            cache_seqlens_int32=fb.seq_lens.to(torch.int32), page_table=self._page_table(fb, B),
+            max_extend_len=int(max_ext), num_extend_tokens=int(tot_ext))
+
+    # --- CUDA-graph hooks (base_attn_backend.py:73-107,159-197; triton_backend.py:1014-1115)
+    def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int, *, num_q_heads: Optional[int] = None,
+                              head_dim: Optional[int] = None, max_splits_cap: int = 16) -> None:
+        dev = self.device
+        g = SimpleNamespace()
+        g.max_bs = max_bs
+        g.kv_indptr = torch.zeros(max_bs + 1, dtype=torch.int32, device=dev)
+        g.kv_indices = torch.zeros(max_bs * self.max_context_len, dtype=torch.int32, device=dev)
+        g.cache_seqlens_int32 = torch.zeros(max_bs, dtype=torch.int32, device=dev)
+        g.max_splits_cap = max_splits_cap
+        g.workspace = None
+        if num_q_heads is not None and head_dim is not None:
+            nbytes = ops.decode_workspace_bytes(max_bs, num_q_heads, head_dim, max_splits_cap)
+            g.workspace = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
+        self._graph = g
+
+    def get_cuda_graph_seq_len_fill_value(self) -> int:
+        return 1  # padded rows read slot 0 with one key (triton_backend.py:1257-1258)
+
+    def init_forward_metadata_out_graph(self, forward_batch, in_capture: bool = False) -> None:
+        """Refill the static decode metadata before capture / replay (sync-free)."""
+        fb = forward_batch
+        mode = fb.forward_mode
+        if self._graph is None or not mode.is_decode_or_idle():
+            if in_capture:
+                raise NotImplementedError("b200 backend: only DECODE can be captured in a CUDA graph")
+            return B200AttnBackend.init_forward_metadata(self, fb)
+        if mode.is_idle():
+            self.forward_metadata = None
+            return
+        g = self._graph
+        B = int(fb.batch_size)
+        if B > g.max_bs:
+            raise ValueError(f"b200 backend: batch {B} exceeds cuda-graph max_bs {g.max_bs}")
+        self._build(fb, fb.seq_lens, g.kv_indptr, g.kv_indices)
+        g.cache_seqlens_int32[:B].copy_(fb.seq_lens[:B])
+        self.forward_metadata = ForwardMetadata(
+            kv_indptr=g.kv_indptr, kv_indices=g.kv_indices, batch_size=B,
+            cache_seqlens_int32=g.cache_seqlens_int32[:B], min_chunk=self.MIN_CHUNK,
+            workspace=g.workspace)
+        self.forward_metadata._graph = True
+
+    def init_forward_metadata_in_graph(self, forward_batch) -> None:
+        pass  # nothing is recomputed inside the graph: the kernels read the static buffers
+
+    # ------------------------------------------------------------------ forward
+    def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, **kwargs):
+        self._check_layer(layer, kwargs)
+        md = self.forward_metadata
+        Hq, Hkv, D = layer.tp_q_head_num, layer.tp_k_head_num, layer.head_dim
+        q2 = q.reshape(-1, Hq * D)
+        o = q2.new_empty(q2.shape[0], Hq * D)
+        if save_kv_cache and k is not None:  # store BEFORE the read: the new token attends to itself
+            self._store(layer, forward_batch, k, v)
+        kbuf, vbuf = self.token_to_kv_pool.get_kv_buffer(layer.layer_id)
+        B = md.batch_size
+        G = Hq // Hkv
+        if getattr(md, "_graph", False):
+            # the split cap is baked into the captured grid: fix it per batch size
+            ms = self._graph_splits.get(B)
+            if ms is None:
+                ms = min(self._graph.max_splits_cap,
+                         ops.pick_max_splits(B, Hkv, G, self.max_context_len, md.min_chunk, num_sms=self.num_sms))
+                self._graph_splits[B] = ms
+            ws = md.workspace
+            need = ops.decode_workspace_bytes(B, Hq, D, ms)
+            if need > 0 and (ws is None or ws.numel() < need):
+                if torch.cuda.is_current_stream_capturing():
+                    raise RuntimeError("b200 backend: pass num_q_heads/head_dim to init_cuda_graph_state")
+                ws = self._graph.workspace = torch.empty(
+                    ops.decode_workspace_bytes(self._graph.max_bs, Hq, D, self._graph.max_splits_cap),
+                    dtype=torch.uint8, device=self.device)
+                md.workspace = ws
+        else:
+            ms = ops.pick_max_splits(B, Hkv, G, getattr(md, "_max_kv_len", self.max_context_len),
+                                     md.min_chunk, num_sms=self.num_sms)
+            ws = self._workspace(ops.decode_workspace_bytes(B, Hq, D, ms))
+        ops.decode_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.kv_indptr, md.kv_indices,
+                             layer.scaling, max_splits=ms, min_chunk=md.min_chunk, workspace=ws, num_items=B)
+        return o
+
+    def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, **kwargs):
+        self._check_layer(layer, kwargs)
+        md = self.forward_metadata
+        Hq, D = layer.tp_q_head_num, layer.head_dim
+        q2 = q.reshape(-1, Hq * D)
+        o = getattr(forward_batch, "_attn_output", None)
+        if o is None or o.shape != q2.shape or o.dtype != q2.dtype:
+            o = q2.new_empty(q2.shape[0], Hq * D)
+        if save_kv_cache and k is not None:  # torch_native_backend.py:298-301
+            self._store(layer, forward_batch, k, v)
+        # torch_native_backend.py:308-310 — DECODER_BIDIRECTIONAL stays causal in the oracle
+        causal = not (getattr(layer, "is_cross_attention", False) or _attn_type_value(layer) == "encoder_only")
+        kbuf, vbuf = self.token_to_kv_pool.get_kv_buffer(layer.layer_id)
+        B = md.batch_size
+        ws = self._workspace(ops.extend_workspace_bytes(B, q2.shape[0], Hq))
+        ops.extend_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.qo_indptr, md.kv_indptr,
+                             md.kv_indices, layer.scaling, causal=causal, page_size=self.page_size,
+                             max_qo_len=md.max_extend_len, total_q=md.num_extend_tokens, workspace=ws)
+        return o
+
+
+def register(name: str = "b200") -> None:
+    """Register with SGLang's backend registry (attention_registry.py:31-39) and CLI
+    choices (server_args.py:416-417).  Call from an ``sglang.srt.plugins`` entry point."""
+    from sglang.srt.layers.attention.attention_registry import register_attention_backend  # type: ignore
+    from sglang.srt.server_args import add_attention_backend_choices  # type: ignore
+
+    add_attention_backend_choices([name])
+
+    @register_attention_backend(name)
+    def _create(runner):
+        return B200AttnBackend(runner)

@@ -1,0 +1,315 @@
+"""Tensor-level wrappers over the C ABI (include/b200attn.h).
+
+Each wrapper mirrors the reference operator it replaces (same argument meaning
+and error behaviour) and only turns ``torch.Tensor`` arguments into raw device
+pointers + the current CUDA stream.  No wrapper allocates on the hot path
+except for the output when the caller did not pass one; none synchronises.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import BF16, FP16, FP32, I32, I64, check
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _fdtype(t: torch.Tensor) -> int:
+    if t.dtype == torch.bfloat16:
+        return BF16
+    if t.dtype == torch.float16:
+        return FP16
+    if t.dtype == torch.float32:
+        return FP32
+    raise NotImplementedError(f"b200attn: unsupported dtype {t.dtype}")
+
+
+def _idtype(t: torch.Tensor) -> int:
+    if t.dtype == torch.int32:
+        return I32
+    if t.dtype == torch.int64:
+        return I64
+    raise TypeError(f"b200attn: index tensor must be int32 or int64, got {t.dtype}")
+
+
+def _require_cuda(*ts: Optional[torch.Tensor]) -> None:
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError(
+                "b200attn kernels need CUDA tensors (there is no CPU fallback); got a "
+                f"{t.device} tensor"
+            )
+
+
+def sm_count() -> int:
+    return _lib.load().b200attn_sm_count()
+
+
+# --------------------------------------------------------------------------- store
+def store_cache(
+    k: torch.Tensor,
+    v: torch.Tensor,
+    k_cache: torch.Tensor,
+    v_cache: torch.Tensor,
+    indices: torch.Tensor,
+    *,
+    reserved_skip_index: int = 0,
+    oob_count: Optional[torch.Tensor] = None,
+) -> None:
+    """``k_cache[indices] = k; v_cache[indices] = v`` (bit-exact row scatter).
+
+    Mirrors ``store_cache`` (python/sglang/kernels/ops/kvcache/kvcache.py:56-110):
+    ``k``/``v`` are ``[T, ...]`` with contiguous rows (the token stride may be
+    larger than the row, e.g. views of the fused qkv output); caches are
+    ``[slots, ...]``; rows whose index equals ``reserved_skip_index`` are skipped
+    (pass ``-1`` to write every row, the reference's naive branch).
+    """
+    _require_cuda(k, v, k_cache, v_cache, indices)
+    T = k.shape[0]
+    if v.shape[0] != T or indices.numel() != T:
+        raise ValueError("store_cache: k, v and indices disagree on the number of tokens")
+    if T == 0:
+        return
+    if k.dtype != k_cache.dtype or v.dtype != v_cache.dtype:
+        raise TypeError("store_cache: cache dtype must equal the row dtype (cast before the store)")
+    k2, v2 = k.reshape(T, -1), v.reshape(T, -1)
+    kc, vc = k_cache.reshape(k_cache.shape[0], -1), v_cache.reshape(v_cache.shape[0], -1)
+    if k2.stride(1) != 1 or v2.stride(1) != 1 or kc.stride(1) != 1 or vc.stride(1) != 1:
+        raise ValueError("store_cache: rows must be contiguous")
+    if k2.shape[1] != kc.shape[1] or v2.shape[1] != vc.shape[1]:
+        raise ValueError("store_cache: row width differs between input and cache")
+    if not indices.is_contiguous():
+        indices = indices.contiguous()
+    ke, ve = k.element_size(), v.element_size()
+    rc = _lib.load().b200attn_kv_store(
+        k2.data_ptr(), v2.data_ptr(), kc.data_ptr(), vc.data_ptr(), indices.data_ptr(),
+        _idtype(indices), T, k2.shape[1] * ke, v2.shape[1] * ve, k2.stride(0) * ke,
+        v2.stride(0) * ve, kc.stride(0) * ke, vc.stride(0) * ve,
+        min(kc.shape[0], vc.shape[0]), reserved_skip_index, _ptr(oob_count), _stream(),
+    )
+    check(rc, "b200attn_kv_store")
+
+
+# ------------------------------------------------------------------------ metadata
+def build_kv_indices(
+    req_to_token: torch.Tensor,
+    req_pool_indices: torch.Tensor,
+    kv_lens: torch.Tensor,
+    kv_indptr: torch.Tensor,
+    kv_indices: Optional[torch.Tensor],
+    *,
+    kv_start: Optional[torch.Tensor] = None,
+    qo_lens: Optional[torch.Tensor] = None,
+    qo_indptr: Optional[torch.Tensor] = None,
+) -> None:
+    """Fill ``kv_indptr`` (int32 ``[B+1]``), ``kv_indices`` (flat slot ids) and optionally ``qo_indptr``.
+
+    Mirrors ``create_flashinfer_kv_indices_triton`` + the cumsum around it
+    (python/sglang/srt/layers/attention/triton_backend.py:438-456).
+    """
+    _require_cuda(req_to_token, req_pool_indices, kv_lens, kv_indptr, kv_indices, kv_start, qo_lens, qo_indptr)
+    B = kv_lens.numel()
+    if req_to_token.dtype != torch.int32 or req_to_token.stride(1) != 1:
+        raise TypeError("build_kv_indices: req_to_token must be int32 with contiguous rows")
+    if kv_indptr.dtype != torch.int32 or kv_indptr.numel() < B + 1:
+        raise ValueError("build_kv_indices: kv_indptr must be int32[B+1]")
+    if qo_indptr is not None and (qo_indptr.dtype != torch.int32 or qo_indptr.numel() < B + 1):
+        raise ValueError("build_kv_indices: qo_indptr must be int32[B+1]")
+    rc = _lib.load().b200attn_build_kv_indices(
+        req_to_token.data_ptr(), req_to_token.stride(0),
+        req_pool_indices.data_ptr(), _idtype(req_pool_indices),
+        kv_lens.data_ptr(), _idtype(kv_lens),
+        _ptr(kv_start), _idtype(kv_start) if kv_start is not None else I32,
+        _ptr(qo_lens), _idtype(qo_lens) if qo_lens is not None else I32,
+        B, kv_indptr.data_ptr(), _ptr(kv_indices),
+        _idtype(kv_indices) if kv_indices is not None else I32,
+        kv_indices.numel() if kv_indices is not None else 0, _ptr(qo_indptr), _stream(),
+    )
+    check(rc, "b200attn_build_kv_indices")
+
+
+def build_page_table(
+    req_to_token: torch.Tensor,
+    req_pool_indices: torch.Tensor,
+    seq_lens: torch.Tensor,
+    page_table: torch.Tensor,
+    page_size: int,
+) -> None:
+    """``page_table[b, j] = req_to_token[req[b], j*page] // page`` for ``j < ceil(len/page)``.
+
+    Mirrors ``build_trtllm_mha_page_table``
+    (python/sglang/kernels/ops/kvcache/trtllm_mha_page_table.py:96-120).
+    """
+    _require_cuda(req_to_token, req_pool_indices, seq_lens, page_table)
+    if page_table.dtype != torch.int32 or page_table.dim() != 2 or page_table.stride(1) != 1:
+        raise TypeError("build_page_table: page_table must be int32 [B, max_pages] with contiguous rows")
+    B = seq_lens.numel()
+    rc = _lib.load().b200attn_build_page_table(
+        req_to_token.data_ptr(), req_to_token.stride(0), req_pool_indices.data_ptr(),
+        _idtype(req_pool_indices), seq_lens.data_ptr(), _idtype(seq_lens), B, page_size,
+        page_table.data_ptr(), page_table.stride(0), page_table.shape[1], _stream(),
+    )
+    check(rc, "b200attn_build_page_table")
+
+
+# -------------------------------------------------------------------------- decode
+def decode_workspace_bytes(B: int, Hq: int, D: int, max_splits: int) -> int:
+    return _lib.load().b200attn_decode_workspace_bytes(B, Hq, D, max_splits)
+
+
+def pick_max_splits(B: int, Hkv: int, G: int, max_kv_len: int, min_chunk: int = 256,
+                    waves: int = 4, ctas_per_sm: int = 2, num_sms: Optional[int] = None) -> int:
+    """Host-side choice of the split cap: enough CTAs for `waves` full waves, never
+    finer than `min_chunk` keys per split.  The per-request split count itself is
+    computed on the device (split_policy in csrc/common.cuh)."""
+    if num_sms is None:
+        num_sms = sm_count()
+    groups = (G + 15) // 16
+    items = max(1, B * Hkv * groups)
+    want = -(-waves * ctas_per_sm * num_sms // items)
+    cap = max(1, -(-max_kv_len // min_chunk))
+    return int(max(1, min(want, cap, 64)))
+
+
+def decode_attention(
+    q: torch.Tensor,
+    k_cache: torch.Tensor,
+    v_cache: torch.Tensor,
+    o: torch.Tensor,
+    kv_indptr: torch.Tensor,
+    kv_indices: torch.Tensor,
+    sm_scale: float,
+    *,
+    max_splits: int = 1,
+    min_chunk: int = 256,
+    workspace: Optional[torch.Tensor] = None,
+    lse: Optional[torch.Tensor] = None,
+    q_rows: Optional[torch.Tensor] = None,
+    req_ids: Optional[torch.Tensor] = None,
+    num_items: Optional[int] = None,
+) -> torch.Tensor:
+    """Paged GQA decode: ``q [B,Hq,D]``, caches ``[slots,Hkv,D]`` -> ``o [B,Hq,D]``.
+
+    Mirrors ``decode_attention_fwd`` (python/sglang/kernels/ops/attention/
+    decode_attention.py:1163-1239) with token-granular ``kv_indices`` (int32).
+    """
+    _require_cuda(q, k_cache, v_cache, o, kv_indptr, kv_indices, workspace, lse, q_rows, req_ids)
+    if q.dim() != 3 or k_cache.dim() != 3:
+        raise ValueError("decode_attention: q must be [B,Hq,D] and caches [slots,Hkv,D]")
+    _, Hq, D = q.shape
+    B = num_items if num_items is not None else (q_rows.numel() if q_rows is not None else q.shape[0])
+    Hkv = k_cache.shape[1]
+    if k_cache.shape[2] != D or v_cache.shape[2] != D:
+        raise NotImplementedError("decode_attention: v_head_dim != head_dim is not supported")
+    if q.dtype != k_cache.dtype or q.dtype != v_cache.dtype:
+        raise TypeError("decode_attention: q and the KV pool must share a dtype")
+    if q.stride(2) != 1 or q.stride(1) != D or o.stride(2) != 1 or o.stride(1) != D:
+        raise ValueError("decode_attention: q/o heads must be densely packed")
+    if k_cache.stride(2) != 1 or k_cache.stride(1) != D or v_cache.stride() != k_cache.stride():
+        raise ValueError("decode_attention: KV pool must be NHD contiguous")
+    if kv_indptr.dtype != torch.int32 or kv_indices.dtype != torch.int32:
+        raise TypeError("decode_attention: kv_indptr / kv_indices must be int32")
+    ws_bytes = 0 if workspace is None else workspace.numel() * workspace.element_size()
+    rc = _lib.load().b200attn_decode(
+        q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
+        o.data_ptr(), o.stride(0), _ptr(lse), kv_indptr.data_ptr(), kv_indices.data_ptr(),
+        _ptr(q_rows), _ptr(req_ids), B, Hq, Hkv, D, _fdtype(q), float(sm_scale), max_splits,
+        min_chunk, _ptr(workspace), ws_bytes, _stream(),
+    )
+    check(rc, "b200attn_decode")
+    return o
+
+
+# -------------------------------------------------------------------------- extend
+def extend_workspace_bytes(B: int, total_q: int, Hq: int) -> int:
+    return _lib.load().b200attn_extend_workspace_bytes(B, total_q, Hq)
+
+
+def extend_attention(
+    q: torch.Tensor,
+    k_cache: torch.Tensor,
+    v_cache: torch.Tensor,
+    o: torch.Tensor,
+    qo_indptr: torch.Tensor,
+    kv_indptr: torch.Tensor,
+    kv_indices: torch.Tensor,
+    sm_scale: float,
+    *,
+    causal: bool,
+    page_size: int,
+    max_qo_len: int,
+    total_q: Optional[int] = None,
+    workspace: Optional[torch.Tensor] = None,
+    lse: Optional[torch.Tensor] = None,
+) -> torch.Tensor:
+    """Ragged prefix+extend attention: ``q [T,Hq,D]`` -> ``o [T,Hq,D]``.
+
+    Mirrors ``extend_attention_fwd_unified`` (python/sglang/kernels/ops/attention/
+    extend_attention.py:963-1410): one KV source (the pool) indexed by
+    ``kv_indices`` over prefix + new tokens; causal by absolute position.
+    """
+    _require_cuda(q, k_cache, v_cache, o, qo_indptr, kv_indptr, kv_indices, workspace, lse)
+    if q.dim() != 3 or k_cache.dim() != 3:
+        raise ValueError("extend_attention: q must be [T,Hq,D] and caches [slots,Hkv,D]")
+    T, Hq, D = q.shape
+    B = qo_indptr.numel() - 1
+    Hkv = k_cache.shape[1]
+    if k_cache.shape[2] != D or v_cache.shape[2] != D:
+        raise NotImplementedError("extend_attention: v_head_dim != head_dim is not supported")
+    if q.dtype != k_cache.dtype or q.dtype != v_cache.dtype:
+        raise TypeError("extend_attention: q and the KV pool must share a dtype")
+    if q.stride(2) != 1 or q.stride(1) != D or o.stride(2) != 1 or o.stride(1) != D:
+        raise ValueError("extend_attention: q/o heads must be densely packed")
+    if k_cache.stride(2) != 1 or k_cache.stride(1) != D or v_cache.stride() != k_cache.stride():
+        raise ValueError("extend_attention: KV pool must be NHD contiguous")
+    if qo_indptr.dtype != torch.int32 or kv_indptr.dtype != torch.int32 or kv_indices.dtype != torch.int32:
+        raise TypeError("extend_attention: indptr / indices must be int32")
+    ws_bytes = 0 if workspace is None else workspace.numel() * workspace.element_size()
+    rc = _lib.load().b200attn_extend(
+        q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
+        min(k_cache.shape[0], v_cache.shape[0]), o.data_ptr(), o.stride(0), _ptr(lse),
+        qo_indptr.data_ptr(), kv_indptr.data_ptr(), kv_indices.data_ptr(), B,
+        T if total_q is None else total_q, max_qo_len, Hq, Hkv, D, page_size, _fdtype(q),
+        1 if causal else 0, float(sm_scale), _ptr(workspace), ws_bytes, _stream(),
+    )
+    check(rc, "b200attn_extend")
+    return o
+
+
+# --------------------------------------------------------------------------- merge
+def merge_state(
+    v_a: torch.Tensor,
+    s_a: torch.Tensor,
+    v_b: torch.Tensor,
+    s_b: torch.Tensor,
+    v_merged: Optional[torch.Tensor] = None,
+    s_merged: Optional[torch.Tensor] = None,
+) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Mirrors ``merge_state`` (python/sglang/srt/layers/attention/merge_state.py:26-46):
+    ``v_* [T,H,D]``, ``s_* [T,H]`` fp32 natural-log LSE; returns ``(v_merged, s_merged)``."""
+    _require_cuda(v_a, s_a, v_b, s_b, v_merged, s_merged)
+    if v_a.shape != v_b.shape or s_a.shape != s_b.shape or v_a.dim() != 3:
+        raise ValueError("merge_state: shape mismatch")
+    if s_a.dtype != torch.float32 or s_b.dtype != torch.float32:
+        raise TypeError("merge_state: LSE tensors must be float32")
+    v_a, v_b, s_a, s_b = v_a.contiguous(), v_b.contiguous(), s_a.contiguous(), s_b.contiguous()
+    T, H, D = v_a.shape
+    if v_merged is None:
+        v_merged = torch.empty_like(v_a)
+    if s_merged is None:
+        s_merged = torch.empty_like(s_a)
+    rc = _lib.load().b200attn_merge_state(
+        v_a.data_ptr(), s_a.data_ptr(), v_b.data_ptr(), s_b.data_ptr(), v_merged.data_ptr(),
+        s_merged.data_ptr(), T, H, D, _fdtype(v_a), _stream(),
+    )
+    check(rc, "b200attn_merge_state")
+    return v_merged, s_merged

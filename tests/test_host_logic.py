@@ -1,0 +1,56 @@
+"""Host-side mirror of the reference data contract (no GPU)."""
+import numpy as np
+import torch
+
+from oracle import torch_native_port as oracle
+from sglang_b200 import host, ops
+
+
+def test_forward_mode_predicates():
+    M = host.ForwardMode
+    assert M.DECODE.is_decode() and not M.DECODE.is_extend()
+    assert M.MIXED.is_extend() and M.MIXED.is_mixed()
+    assert M.EXTEND.is_extend() and M.TARGET_VERIFY.is_extend()
+    assert M.IDLE.is_idle() and M.IDLE.is_decode_or_idle()
+    assert not M.DRAFT_EXTEND_V2.is_extend() and M.DRAFT_EXTEND_V2.is_extend(include_draft_extend_v2=True)
+
+
+def test_compute_position_matches_oracle():
+    pre, ext = [0, 5, 17, 3], [4, 1, 9, 0]
+    pos, start = host.compute_position(pre, ext)
+    opos, ostart = oracle.positions(pre, ext)
+    assert np.array_equal(pos.numpy(), opos) and np.array_equal(start.numpy(), ostart)
+
+
+def test_alloc_extend_naive_page_invariant():
+    page = 16
+    free = list(range(1, 40))
+    prefix, seq = [0, 20, 32], [37, 45, 33]
+    last = [-1, 3 * page + 3, 5 * page + 15]  # last slot of each prefix
+    loc = host.alloc_extend_naive(prefix, seq, last, free, page).tolist()
+    assert len(loc) == sum(s - p for p, s in zip(prefix, seq))
+    t = 0
+    for p, s, l in zip(prefix, seq, last):
+        seg = loc[t:t + s - p]
+        t += s - p
+        for j, slot in enumerate(seg):
+            assert slot % page == (p + j) % page          # slot = page*P + pos % P
+            if (p + j) % page != 0:
+                prev = seg[j - 1] if j else l
+                assert slot == prev + 1                   # continues the partial page
+    assert len(set(loc)) == len(loc)
+
+
+def test_pool_shapes_and_padding_row():
+    r = host.ReqToTokenPool(4, 32, "cpu")
+    assert r.req_to_token.shape == (5, 32) and r.req_to_token.dtype == torch.int32
+    assert r.alloc(2) == [1, 2] and r.available_size() == 2
+    p = host.MHATokenToKVPool(64, 16, torch.bfloat16, 2, 8, 3, "cpu", start_layer=1)
+    assert p.get_key_buffer(1).shape == (80, 2, 8) and float(p.get_key_buffer(3).abs().sum()) == 0
+
+
+def test_pick_max_splits_bounds():
+    assert ops.pick_max_splits(64, 8, 4, 4096, num_sms=148) >= 2
+    assert ops.pick_max_splits(4096, 8, 4, 4096, num_sms=148) == 1   # enough CTAs already
+    assert ops.pick_max_splits(1, 1, 4, 100, num_sms=148) == 1       # never finer than min_chunk
+    assert ops.pick_max_splits(1, 8, 4, 1 << 20, num_sms=148) <= 64

@@ -1,0 +1,108 @@
+"""Shared scenario builders for the parity tests (seeded, device agnostic)."""
+from __future__ import annotations
+
+import glob
+import os
+from dataclasses import dataclass
+from typing import List, Sequence
+
+import torch
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def golden_files() -> List[str]:
+    return sorted(glob.glob(os.path.join(GOLDEN_DIR, "*.pt")))
+
+
+def load_golden(path: str) -> dict:
+    return torch.load(path, map_location="cpu", weights_only=False)
+
+
+@dataclass
+class Scenario:
+    """A paged KV pool + req_to_token table + one forward's worth of inputs (CPU tensors)."""
+
+    Hq: int
+    Hkv: int
+    D: int
+    page_size: int
+    prefix_lens: List[int]
+    extend_lens: List[int]
+    seq_lens: List[int]
+    req_to_token: torch.Tensor      # int32 [B+1, ctx]
+    req_pool_indices: torch.Tensor  # int64 [B]
+    out_cache_loc: torch.Tensor     # int64 [T]
+    k_cache: torch.Tensor           # [slots, Hkv, D]
+    v_cache: torch.Tensor
+    q: torch.Tensor                 # [T, Hq*D]
+    k: torch.Tensor                 # [T, Hkv, D]
+    v: torch.Tensor
+    scaling: float
+
+    def to(self, device):
+        out = Scenario(**self.__dict__)
+        for name, val in self.__dict__.items():
+            if isinstance(val, torch.Tensor):
+                setattr(out, name, val.to(device))
+        return out
+
+
+def make_scenario(prefix_lens: Sequence[int], extend_lens: Sequence[int], Hq: int, Hkv: int, D: int,
+                  page_size: int, dtype=torch.bfloat16, seed: int = 0, shared_prefix_pages: int = 0,
+                  pool_slack: float = 1.25) -> Scenario:
+    """Random pages per request (the reference kit's `shuffled_pages` layout,
+    dense_attention.py:663-674); slot 0 / page 0 is reserved and never referenced.
+    `shared_prefix_pages` > 0 makes the first pages of every request the SAME
+    physical pages (a radix-cache hit)."""
+    g = torch.Generator().manual_seed(seed)
+    B = len(prefix_lens)
+    seq_lens = [p + e for p, e in zip(prefix_lens, extend_lens)]
+    ctx = max(max(seq_lens), 1)
+    ctx = -(-ctx // page_size) * page_size
+    pages_per_req = [-(-s // page_size) for s in seq_lens]
+    need = sum(pages_per_req) + shared_prefix_pages
+    num_pages = int(need * pool_slack) + 2
+    perm = (torch.randperm(num_pages - 1, generator=g) + 1).tolist()  # page 0 reserved
+    shared = [perm.pop() for _ in range(shared_prefix_pages)]
+    req_to_token = torch.zeros((B + 1, ctx), dtype=torch.int32)
+    offs = torch.arange(page_size, dtype=torch.int32)
+    for b in range(B):
+        pages = []
+        for j in range(pages_per_req[b]):
+            pages.append(shared[j] if j < shared_prefix_pages else perm.pop())
+        for j, pg in enumerate(pages):
+            lo = j * page_size
+            hi = min(lo + page_size, ctx)
+            req_to_token[b + 1, lo:hi] = pg * page_size + offs[: hi - lo]
+    req_pool_indices = torch.arange(1, B + 1, dtype=torch.int64)
+    loc = []
+    for b in range(B):
+        loc.append(req_to_token[b + 1, prefix_lens[b]:seq_lens[b]].long())
+    out_cache_loc = torch.cat(loc) if loc else torch.zeros(0, dtype=torch.int64)
+    slots = num_pages * page_size
+    k_cache = torch.randn((slots, Hkv, D), generator=g, dtype=torch.float32).to(dtype)
+    v_cache = torch.randn((slots, Hkv, D), generator=g, dtype=torch.float32).to(dtype)
+    k_cache[:page_size] = 0
+    v_cache[:page_size] = 0
+    T = sum(extend_lens)
+    q = torch.randn((T, Hq * D), generator=g, dtype=torch.float32).to(dtype)
+    k = torch.randn((T, Hkv, D), generator=g, dtype=torch.float32).to(dtype)
+    v = torch.randn((T, Hkv, D), generator=g, dtype=torch.float32).to(dtype)
+    return Scenario(Hq=Hq, Hkv=Hkv, D=D, page_size=page_size, prefix_lens=list(prefix_lens),
+                    extend_lens=list(extend_lens), seq_lens=seq_lens, req_to_token=req_to_token,
+                    req_pool_indices=req_pool_indices, out_cache_loc=out_cache_loc, k_cache=k_cache,
+                    v_cache=v_cache, q=q, k=k, v=v, scaling=D ** -0.5)
+
+
+def assert_close_attn(actual: torch.Tensor, expected: torch.Tensor, what: str = "",
+                      rtol: float = 1e-2, atol: float = 2e-2) -> None:
+    """BASELINE tolerance for bf16 attention outputs: 1e-2 relative / 2e-2 absolute."""
+    a, e = actual.float().cpu(), expected.float().cpu()
+    assert a.shape == e.shape, f"{what}: shape {tuple(a.shape)} vs {tuple(e.shape)}"
+    assert torch.isfinite(a).all(), f"{what}: non-finite output"
+    err = (a - e).abs()
+    tol = atol + rtol * e.abs()
+    bad = err > tol
+    assert not bad.any(), (f"{what}: {int(bad.sum())}/{bad.numel()} elements out of tolerance, "
+                           f"max abs err {float(err.max()):.4e}")
