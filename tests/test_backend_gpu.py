@@ -1,0 +1,139 @@
+"""B200AttnBackend behind the reference plugin API: golden cases end to end + CUDA-graph decode."""
+import pytest
+import torch
+
+from oracle import torch_native_port as oracle
+from sglang_b200 import (AttentionType, B200AttnBackend, ForwardBatch, ForwardMode, MHATokenToKVPool,
+                         RadixAttention, ReqToTokenPool)
+from tests.util import assert_close_attn, golden_files, load_golden, make_scenario
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+class _Runner:
+    def __init__(self, req_pool, kv_pool, page_size):
+        self.device = DEV
+        self.page_size = page_size
+        self.req_to_token_pool = req_pool
+        self.token_to_kv_pool = kv_pool
+        self.sliding_window_size = None
+
+
+def _setup(g_or_sc, golden):
+    if golden:
+        g = g_or_sc
+        Hq, Hkv, D, page = g["num_heads"], g["num_kv_heads"], g["head_dim"], g["page_size"]
+        table, kc, vc = g["req_to_token"], g["k_pool_before"], g["v_pool_before"]
+    else:
+        sc = g_or_sc
+        Hq, Hkv, D, page = sc.Hq, sc.Hkv, sc.D, sc.page_size
+        table, kc, vc = sc.req_to_token, sc.k_cache, sc.v_cache
+    req_pool = ReqToTokenPool(table.shape[0] - 1, table.shape[1], DEV)
+    req_pool.req_to_token.copy_(table)
+    kv_pool = MHATokenToKVPool(kc.shape[0] - page, page, kc.dtype, Hkv, D, 1, DEV, skip_padding_slot=False)
+    kv_pool.k_buffer[0].copy_(kc)
+    kv_pool.v_buffer[0].copy_(vc)
+    backend = B200AttnBackend(_Runner(req_pool, kv_pool, page), skip_padding_slot=False)
+    return backend, req_pool, kv_pool
+
+
+@pytest.mark.parametrize("path", golden_files(), ids=lambda p: p.split("/")[-1][:-3])
+def test_backend_matches_reference_backend(path):
+    g = load_golden(path)
+    Hq, Hkv, D = g["num_heads"], g["num_kv_heads"], g["head_dim"]
+    backend, req_pool, kv_pool = _setup(g, True)
+    layer = RadixAttention(Hq, D, g["scaling"], Hkv, 0,
+                           attn_type=AttentionType.DECODER if g["causal"] else AttentionType.ENCODER_ONLY)
+    mode = ForwardMode[g["mode"]]
+    B = len(g["seq_lens"])
+    fb = ForwardBatch(forward_mode=mode, batch_size=B, req_pool_indices=g["req_pool_indices"].to(DEV),
+                      seq_lens=torch.tensor(g["seq_lens"], dtype=torch.int32, device=DEV),
+                      out_cache_loc=g["out_cache_loc"].to(DEV), seq_lens_sum=sum(g["seq_lens"]),
+                      seq_lens_cpu=torch.tensor(g["seq_lens"], dtype=torch.int32), positions=g["positions"].to(DEV),
+                      attn_backend=backend)
+    if mode.is_extend():
+        fb.extend_prefix_lens = torch.tensor(g["prefix_lens"], dtype=torch.int32, device=DEV)
+        fb.extend_seq_lens = torch.tensor(g["extend_lens"], dtype=torch.int32, device=DEV)
+        fb.extend_prefix_lens_cpu, fb.extend_seq_lens_cpu = g["prefix_lens"], g["extend_lens"]
+        fb.extend_num_tokens = sum(g["extend_lens"])
+    backend.init_forward_metadata(fb)
+    o = layer(g["q"].to(DEV), g["k"].to(DEV), g["v"].to(DEV), fb)
+    assert o.shape == g["o_ref"].shape and o.dtype == g["o_ref"].dtype
+    assert_close_attn(o, g["o_ref"], g["name"])
+    loc = g["out_cache_loc"].long()
+    assert torch.equal(kv_pool.k_buffer[0].cpu()[loc], g["k_rows_after"])  # store is bit-exact
+    assert torch.equal(kv_pool.v_buffer[0].cpu()[loc], g["v_rows_after"])
+
+
+def test_backend_idle_and_unsupported_features():
+    sc = make_scenario([4], [0], 8, 2, 128, 16)
+    backend, _, _ = _setup(sc, False)
+    layer = RadixAttention(8, 128, 0.1, 2, 0)
+    fb = ForwardBatch(forward_mode=ForwardMode.IDLE, batch_size=0, req_pool_indices=torch.zeros(0, device=DEV),
+                      seq_lens=torch.zeros(0, device=DEV), out_cache_loc=torch.zeros(0, device=DEV),
+                      attn_backend=backend)
+    backend.init_forward_metadata(fb)
+    q = torch.zeros((0, 8 * 128), dtype=torch.bfloat16, device=DEV)
+    assert layer(q, None, None, fb).shape == (0, 8 * 128)
+    fb.forward_mode = ForwardMode.DECODE
+    for kw in (dict(logit_cap=30.0), dict(sliding_window_size=128), dict(is_cross_attention=True), dict(v_head_dim=64)):
+        bad = RadixAttention(8, 128, 0.1, 2, 0, **kw)
+        with pytest.raises(NotImplementedError):
+            backend.forward_decode(q, None, None, bad, fb)
+
+
+def test_backend_cuda_graph_decode_replay():
+    """Capture one decode step, then replay it with new lengths / slots (base_attn_backend.py:73-107)."""
+    Hq, Hkv, D, page, B = 32, 8, 128, 16, 8
+    lens0 = [100, 37, 512, 64, 900, 3, 258, 777]
+    sc = make_scenario([l - 1 for l in lens0], [1] * B, Hq, Hkv, D, page, seed=77, pool_slack=3.0)
+    backend, req_pool, kv_pool = _setup(sc, False)
+    backend.init_cuda_graph_state(B, B, num_q_heads=Hq, head_dim=D)
+    assert backend.get_cuda_graph_seq_len_fill_value() == 1
+    layer = RadixAttention(Hq, D, sc.scaling, Hkv, 0)
+    # static input buffers, as the reference graph runner keeps them (runner_utils/buffers.py:113-117)
+    s_req = sc.req_pool_indices.to(DEV)
+    s_seq = torch.tensor(lens0, dtype=torch.int64, device=DEV)
+    s_loc = sc.out_cache_loc.to(DEV)
+    s_q = sc.q.to(DEV)
+    s_k, s_v = sc.k.to(DEV), sc.v.to(DEV)
+    fb = ForwardBatch(forward_mode=ForwardMode.DECODE, batch_size=B, req_pool_indices=s_req, seq_lens=s_seq,
+                      out_cache_loc=s_loc, seq_lens_sum=sum(lens0), attn_backend=backend)
+    stream = torch.cuda.Stream()
+    stream.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(stream):
+        backend.init_forward_metadata_out_graph(fb, in_capture=True)
+        layer(s_q, s_k, s_v, fb)  # warm-up outside capture
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=stream):
+            backend.init_forward_metadata_in_graph(fb)
+            s_out = layer(s_q, s_k, s_v, fb)
+    torch.cuda.current_stream().wait_stream(stream)
+
+    def check(lens, seed):
+        sc2 = make_scenario([l - 1 for l in lens], [1] * B, Hq, Hkv, D, page, seed=seed, pool_slack=1.0)
+        # new request state: table rows, slots, inputs (pool contents stay: slots are re-used)
+        n = min(req_pool.req_to_token.shape[1], sc2.req_to_token.shape[1])
+        req_pool.req_to_token.zero_()
+        req_pool.req_to_token[:, :n].copy_(sc2.req_to_token[:, :n] % kv_pool.k_buffer[0].shape[0])
+        s_seq.copy_(torch.tensor(lens))
+        loc = torch.stack([req_pool.req_to_token[b + 1, lens[b] - 1] for b in range(B)]).long()
+        s_loc.copy_(loc)
+        s_q.copy_(sc2.q)
+        s_k.copy_(sc2.k)
+        s_v.copy_(sc2.v)
+        backend.init_forward_metadata_out_graph(fb)  # replay-time refill, no capture
+        graph.replay()
+        torch.cuda.synchronize()
+        kc, vc = kv_pool.k_buffer[0], kv_pool.v_buffer[0]
+        ref = oracle.attention_fp32(s_q, kc, vc, req_pool.req_to_token, s_req, torch.tensor(lens),
+                                    torch.ones(B, dtype=torch.int64), Hq, Hkv, D, sc.scaling, causal=False)
+        assert_close_attn(s_out, ref, f"graph replay seed {seed}")
+        assert torch.equal(kc[loc], s_k.view(B, Hkv, D))  # the captured store ran with the new slots
+
+    check(lens0, 5)
+    check([1, 1000, 17, 16, 333, 640, 2, 45], 6)
+    md = backend.forward_metadata
+    assert int(md.kv_indptr[0]) == 0 and bool((md.kv_indptr[1:B + 1] >= md.kv_indptr[:B]).all())

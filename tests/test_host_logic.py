@@ -26,7 +26,7 @@ def test_alloc_extend_naive_page_invariant():
     page = 16
     free = list(range(1, 40))
     prefix, seq = [0, 20, 32], [37, 45, 33]
-    last = [-1, 3 * page + 3, 5 * page + 15]  # last slot of each prefix
+    last = [-1, 50 * page + 3, 51 * page + 15]  # last slot of each prefix
     loc = host.alloc_extend_naive(prefix, seq, last, free, page).tolist()
     assert len(loc) == sum(s - p for p, s in zip(prefix, seq))
     t = 0
