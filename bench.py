@@ -1,0 +1,411 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200 attention hot path.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+One "step" = one attention-layer call of the decode hot path (KV store of the new
+tokens + paged GQA split-KV decode + split merge) on BASELINE.json configs[1]:
+Llama-3.1-8B shape, batch 64 x 4096 ctx, GQA 32q/8kv, head_dim 128, page_size 16,
+bf16.  The KV working set of one call (1.07 GB) is 8.5x the 126 MB L2, so every
+timed iteration streams from HBM ("inputs larger than L2").  `value` = algorithmic
+bytes of the call / device time (CUDA events, max over ranks).  The same JSON line
+also carries the extend leg (configs[2], TFLOP/s on tcgen05), the roofline of the
+dominant kernel, the end-to-end number through the AttentionBackend API with host
+buffers, and the CPU baseline (oracle port of torch_native on the host cores).
+
+For --gpus N > 1 (torchrun, one rank per GPU) the batch is head-sharded the way
+tensor parallelism does it: every rank owns the same number of KV heads (8) of a
+model N times as wide and runs the same kernels on its own pool; no collective is
+on the data path (o_proj's all-reduce stays the reference's), scaling is weak.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# ---- workload (BASELINE.json configs[1] and configs[2]) ------------------------
+CFG2 = dict(B=64, ctx=4096, Hq=32, Hkv=8, D=128, page=16, layers=32)
+CFG3 = dict(B=32, prefix=2048, ext=512, Hq=32, Hkv=8, D=128, page=16)
+SEED = 20261104
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            d = json.load(f)
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sustained=d["bf16_tflops_sustained"],
+                    src="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, src="fallback")
+
+
+def decode_bytes(c, B=None):
+    """Algorithmic bytes of one decode layer-call: K+V rows read once,
+    q read, o written, int32 slot ids read once per kv head group... counted once, new-token store."""
+    B = c["B"] if B is None else B
+    kv = B * c["ctx"] * c["Hkv"] * c["D"] * 2 * 2
+    qo = 2 * B * c["Hq"] * c["D"] * 2
+    idx = B * c["ctx"] * 4
+    store = 2 * 2 * B * c["Hkv"] * c["D"] * 2
+    return kv + qo + idx + store
+
+
+def extend_flops(c):
+    pairs = c["B"] * (c["ext"] * c["prefix"] + c["ext"] * (c["ext"] + 1) // 2)
+    return 4 * c["D"] * c["Hq"] * pairs
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.idx}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower() == "active"})
+        return dict(sm_mhz=statistics.median(sm) if sm else None, sm_max_mhz=max(mx) if mx else None,
+                    reasons=reasons, samples=len(sm))
+
+
+# ---- synthetic state ------------------------------------------------------------
+def build_decode_state(c, device, gen):
+    """Pool, req_to_token (random pages per request, page 0 reserved) and one step's inputs."""
+    from sglang_b200 import MHATokenToKVPool, ReqToTokenPool
+
+    B, ctx, page = c["B"], c["ctx"], c["page"]
+    pages_per_req = ctx // page
+    num_pages = int(B * pages_per_req * 1.25) + 1
+    req_pool = ReqToTokenPool(B, ctx, device)
+    perm = (torch.randperm(num_pages - 1, generator=gen) + 1)[: B * pages_per_req].view(B, pages_per_req)
+    table = (perm[:, :, None] * page + torch.arange(page)[None, None, :]).view(B, ctx).to(torch.int32)
+    req_pool.req_to_token[1:] = table.to(device)
+    kv_pool = MHATokenToKVPool(num_pages * page - page, page, torch.bfloat16, c["Hkv"], c["D"], 1, device)
+    for buf in (kv_pool.k_buffer[0], kv_pool.v_buffer[0]):
+        buf.normal_(0, 1, generator=None)
+        buf[:page].zero_()
+    host = dict(
+        q=torch.randn((B, c["Hq"] * c["D"]), generator=gen).to(torch.bfloat16).pin_memory(),
+        k=torch.randn((B, c["Hkv"] * c["D"]), generator=gen).to(torch.bfloat16).pin_memory(),
+        v=torch.randn((B, c["Hkv"] * c["D"]), generator=gen).to(torch.bfloat16).pin_memory(),
+        seq_lens=torch.full((B,), ctx, dtype=torch.int64).pin_memory(),
+        req_pool_indices=torch.arange(1, B + 1, dtype=torch.int64).pin_memory(),
+        out_cache_loc=table[:, ctx - 1].to(torch.int64).pin_memory(),
+    )
+    return req_pool, kv_pool, host
+
+
+class Runner:
+    def __init__(self, device, req_pool, kv_pool, page):
+        self.device, self.page_size = device, page
+        self.req_to_token_pool, self.token_to_kv_pool = req_pool, kv_pool
+        self.sliding_window_size = None
+
+
+def time_steps(fn, steps, warmup, barrier=None):
+    """W warm-up calls, then K calls bracketed by (barrier +) synchronize; CUDA events on the
+    launching (current) stream.  Returns total milliseconds on this rank."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if barrier is not None:
+        barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    if barrier is not None:
+        barrier()
+    return e0.elapsed_time(e1)
+
+
+def cpu_decode_sample(c, sample_B, reps, threads):
+    """The oracle port of torch_native forward_decode on the host cores over `sample_B`
+    requests of the cfg2 workload (full 4096-key contexts).  Returns (seconds per call, bytes)."""
+    from oracle import torch_native_port as oracle
+
+    torch.set_num_threads(threads)
+    g = torch.Generator().manual_seed(SEED)
+    ctx, page, Hkv, D, Hq = c["ctx"], c["page"], c["Hkv"], c["D"], c["Hq"]
+    pages = ctx // page
+    num_pages = sample_B * pages + 1
+    perm = (torch.randperm(num_pages - 1, generator=g) + 1).view(sample_B, pages)
+    table = torch.zeros((sample_B + 1, ctx), dtype=torch.int32)
+    table[1:] = (perm[:, :, None] * page + torch.arange(page)[None, None, :]).view(sample_B, ctx).to(torch.int32)
+    kc = torch.randn((num_pages * page, Hkv, D), generator=g).to(torch.bfloat16)
+    vc = torch.randn((num_pages * page, Hkv, D), generator=g).to(torch.bfloat16)
+    q = torch.randn((sample_B, Hq * D), generator=g).to(torch.bfloat16)
+    k = torch.randn((sample_B, Hkv, D), generator=g).to(torch.bfloat16)
+    v = torch.randn((sample_B, Hkv, D), generator=g).to(torch.bfloat16)
+    req = torch.arange(1, sample_B + 1)
+    seq = torch.full((sample_B,), ctx)
+    loc = table[1:, ctx - 1].long()
+
+    def call():
+        oracle.store_kv(kc, vc, loc, k, v)
+        return oracle.decode(q, kc, vc, table, req, seq, Hq, Hkv, D, D ** -0.5)
+
+    call()
+    ts = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        call()
+        ts.append(time.perf_counter() - t0)
+    return statistics.median(ts), decode_bytes(c, sample_B)
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU implementation of the path (torch_native; the oracle
+    port, since /root/reference does not exist on the GPU box) on all host threads."""
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    sample_B = 64
+    for _ in range(max(args.warmup - 1, 0)):
+        cpu_decode_sample(CFG2, sample_B, 1, threads)
+    sec, nbytes = cpu_decode_sample(CFG2, sample_B, max(args.steps, 1), threads)
+    gbs = nbytes / sec / 1e9
+    line = dict(
+        impl="reference", metric="decode_attn_hbm_gbs", value=gbs, unit="GB/s", n_gpus=args.gpus, steps=args.steps,
+        warmup=args.warmup, ms_per_step=sec * 1e3, higher_is_better=True, scaling="weak", vs_baseline=None,
+        dtype="bf16", data="synthetic",
+        config=dict(workload="llama-3.1-8b decode attention layer-call: batch 64 x 4096 ctx, GQA 32q/8kv, "
+                             "head_dim 128, page_size 16 (BASELINE configs[1])",
+                    sample=f"{sample_B} of 64 requests per step, full 4096-key contexts (the whole workload)"),
+        cpu_baseline=dict(value=gbs, unit="GB/s", cores=threads, kind="port",
+                          sample=f"{sample_B} of 64 requests x 4096 ctx per call, median of {max(args.steps, 1)}"),
+        e2e=dict(value=gbs, unit="GB/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+    )
+    print(json.dumps(line), flush=True)
+
+
+def run_b200(args, rank, world, local_rank):
+    from sglang_b200 import B200AttnBackend, ForwardBatch, ForwardMode, RadixAttention, ops
+
+    dev = f"cuda:{local_rank}"
+    torch.cuda.set_device(dev)
+    barrier = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device(dev))
+        barrier = lambda: dist.barrier()
+    peaks = measured_peaks()
+    gen = torch.Generator().manual_seed(SEED + rank)
+    c = CFG2
+    B, Hq, Hkv, D = c["B"], c["Hq"], c["Hkv"], c["D"]
+    req_pool, kv_pool, host = build_decode_state(c, dev, gen)
+    backend = B200AttnBackend(Runner(dev, req_pool, kv_pool, c["page"]))
+    layer = RadixAttention(Hq, D, D ** -0.5, Hkv, 0)
+    devt = {k: v.to(dev) for k, v in host.items()}
+    fb = ForwardBatch(forward_mode=ForwardMode.DECODE, batch_size=B, req_pool_indices=devt["req_pool_indices"],
+                      seq_lens=devt["seq_lens"], out_cache_loc=devt["out_cache_loc"], seq_lens_sum=B * c["ctx"],
+                      seq_lens_cpu=host["seq_lens"], attn_backend=backend)
+    backend.init_forward_metadata(fb)
+    md = backend.forward_metadata
+    kbuf, vbuf = kv_pool.get_kv_buffer(0)
+    max_splits = ops.pick_max_splits(B, Hkv, Hq // Hkv, c["ctx"], md.min_chunk)
+    launches_per_step = 2 + (1 if max_splits > 1 else 0)
+
+    # (1) the step: store + decode attention (+ merge), inputs resident in HBM
+    def step():
+        return layer(devt["q"], devt["k"], devt["v"], fb)
+
+    with ClockSampler(local_rank) as clk:
+        total_ms = time_steps(step, args.steps, args.warmup, barrier)
+    clocks = clk.summary()
+    if world > 1:
+        t = torch.tensor([total_ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t)
+    ms_step = total_ms / args.steps
+    nbytes = decode_bytes(c)
+    value = world * nbytes / (ms_step * 1e-3) / 1e9
+
+    # (2) the dominant kernel alone (decode attention, without the store) for the roofline
+    q3 = devt["q"].view(B, Hq, D)
+    o3 = torch.empty_like(q3)
+    ws = torch.empty(max(ops.decode_workspace_bytes(B, Hq, D, max_splits), 16), dtype=torch.uint8, device=dev)
+
+    def kern():
+        ops.decode_attention(q3, kbuf, vbuf, o3, md.kv_indptr, md.kv_indices, layer.scaling, max_splits=max_splits,
+                             min_chunk=md.min_chunk, workspace=ws)
+
+    kern_ms = time_steps(kern, args.steps, args.warmup) / args.steps
+    kern_bytes = nbytes - 2 * 2 * B * Hkv * D * 2  # without the store's read+write
+    achieved = kern_bytes / (kern_ms * 1e-3) / 1e9
+
+    # (3) end to end through the AttentionBackend API with HOST buffers (pinned): per step the new
+    #     q/k/v rows and the batch metadata go host->device, metadata is rebuilt, the layer runs,
+    #     and the attention output comes back device->host.
+    o_host = torch.empty((B, Hq * D), dtype=torch.bfloat16).pin_memory()
+    h2d = sum(t.numel() * t.element_size() for t in host.values())
+    d2h = o_host.numel() * o_host.element_size()
+
+    def e2e_step():
+        for k_, t in host.items():
+            devt[k_].copy_(t, non_blocking=True)
+        backend.init_forward_metadata(fb)
+        o_host.copy_(layer(devt["q"], devt["k"], devt["v"], fb), non_blocking=True)
+
+    e2e_ms = time_steps(e2e_step, args.steps, args.warmup, barrier)
+    if world > 1:
+        t = torch.tensor([e2e_ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t)
+    e2e_ms /= args.steps
+    e2e_val = world * nbytes / (e2e_ms * 1e-3) / 1e9
+
+    # (4) extend leg (configs[2]): 32 requests sharing a 2048-token prefix + 512 new tokens, causal
+    ext = run_extend_leg(args, dev, gen, peaks)
+
+    if rank != 0:
+        return
+    # (5) CPU baseline on the host cores (rank 0, N=1 only): bounded sample of the same workload
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        sec, sb = cpu_decode_sample(c, 64, 3, threads)
+        cpu = dict(value=sb / sec / 1e9, unit="GB/s", cores=threads, kind="port",
+                   sample="all 64 requests x 4096 ctx per call (oracle port of torch_native forward_decode), median of 3")
+    line = dict(
+        metric="decode_attn_hbm_gbs", value=value, unit="GB/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
+        ms_per_step=ms_step, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="bf16", data="synthetic",
+        config=dict(workload="llama-3.1-8b decode attention layer-call (KV store + paged GQA split-KV decode + merge): "
+                             "batch 64 x 4096 ctx, GQA 32q/8kv, head_dim 128, page_size 16 (BASELINE configs[1])",
+                    parallelism=f"kv-head sharded x{world} (8 kv heads per GPU), no collective",
+                    l2="inputs larger than L2 (1.07 GB KV per call vs 126 MB)", max_splits=max_splits),
+        roofline=dict(bound="hbm", achieved=achieved, peak=peaks["hbm"], unit="GB/s", frac=achieved / peaks["hbm"],
+                      traffic=None, kernel="decode_kernel<128,bf16> (+merge)", kernel_ms=kern_ms,
+                      peak_source=peaks["src"], frac_of_8tbs=achieved / 8000.0),
+        cpu_baseline=cpu,
+        e2e=dict(value=e2e_val, unit="GB/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h, ms_per_step=e2e_ms),
+        gpu_launches=launches_per_step * args.steps,
+        clocks=clocks,
+        extend=ext,
+        tokens_per_s_attention_only=world * B / (c["layers"] * ms_step * 1e-3),
+    )
+    print(json.dumps(line), flush=True)
+
+
+def run_extend_leg(args, dev, gen, peaks):
+    from sglang_b200 import ops
+
+    c = CFG3
+    B, P, E, Hq, Hkv, D, page = c["B"], c["prefix"], c["ext"], c["Hq"], c["Hkv"], c["D"], c["page"]
+    shared = P // page
+    own = E // page
+    num_pages = shared + B * own + 8
+    perm = torch.randperm(num_pages - 1, generator=gen) + 1
+    table = torch.zeros((B + 1, P + E), dtype=torch.int32)
+    offs = torch.arange(page)
+    pre = (perm[:shared, None] * page + offs[None]).reshape(-1)
+    for b in range(B):
+        mine = perm[shared + b * own: shared + (b + 1) * own]
+        table[b + 1, :P] = pre
+        table[b + 1, P:] = (mine[:, None] * page + offs[None]).reshape(-1)
+    table = table.to(dev)
+    kc = torch.randn((num_pages * page, Hkv, D), device=dev).to(torch.bfloat16)
+    vc = torch.randn((num_pages * page, Hkv, D), device=dev).to(torch.bfloat16)
+    T = B * E
+    q = torch.randn((T, Hq, D), device=dev).to(torch.bfloat16)
+    k = torch.randn((T, Hkv, D), device=dev).to(torch.bfloat16)
+    v = torch.randn((T, Hkv, D), device=dev).to(torch.bfloat16)
+    o = torch.empty_like(q)
+    loc = table[1:, P:].reshape(-1).long()
+    req = torch.arange(1, B + 1, device=dev)
+    seq = torch.full((B,), P + E, device=dev)
+    extl = torch.full((B,), E, dtype=torch.int32, device=dev)
+    kv_indptr = torch.zeros(B + 1, dtype=torch.int32, device=dev)
+    qo_indptr = torch.zeros(B + 1, dtype=torch.int32, device=dev)
+    kv_indices = torch.zeros(B * (P + E), dtype=torch.int32, device=dev)
+    ops.build_kv_indices(table, req, seq, kv_indptr, kv_indices, qo_lens=extl, qo_indptr=qo_indptr)
+
+    def step():
+        ops.store_cache(k, v, kc, vc, loc, reserved_skip_index=0)
+        ops.extend_attention(q, kc, vc, o, qo_indptr, kv_indptr, kv_indices, D ** -0.5, causal=True,
+                             page_size=page, max_qo_len=E)
+
+    def kern():
+        ops.extend_attention(q, kc, vc, o, qo_indptr, kv_indptr, kv_indices, D ** -0.5, causal=True,
+                             page_size=page, max_qo_len=E)
+
+    steps = max(args.steps // 4, 3)
+    ms = time_steps(step, steps, args.warmup) / steps
+    kms = time_steps(kern, steps, args.warmup) / steps
+    fl = extend_flops(c)
+    tf = fl / (kms * 1e-3) / 1e12
+    return dict(workload="llama-3.1-8b extend: 32 req x (2048 shared prefix + 512 new), causal (BASELINE configs[2])",
+                ms_per_step=ms, kernel_ms=kms, tflops=tf, flops=fl, tokens_per_s_attention_only=T / (32 * ms * 1e-3),
+                roofline=dict(bound="tensor", achieved=tf, peak=peaks["tf_burst"], unit="TFLOP/s",
+                              frac=tf / peaks["tf_burst"], frac_of_2250=tf / 2250.0, peak_source=peaks["src"]))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the b200 arm has no CPU fallback (use --impl reference)")
+    run_b200(args, rank, world, local_rank)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
