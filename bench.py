@@ -82,6 +82,9 @@ class ClockSampler:
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
+            t0 = time.time()
+            while not self.rows and time.time() - t0 < 3.0:  # first sample before the timed region starts
+                time.sleep(0.02)
         except Exception:
             self.proc = None
         return self
@@ -253,9 +256,8 @@ def run_b200(args, rank, world, local_rank):
     def step():
         return layer(devt["q"], devt["k"], devt["v"], fb)
 
-    with ClockSampler(local_rank) as clk:
-        total_ms = time_steps(step, args.steps, args.warmup, barrier)
-    clocks = clk.summary()
+    clk = ClockSampler(local_rank).__enter__()
+    total_ms = time_steps(step, args.steps, args.warmup, barrier)
     if world > 1:
         t = torch.tensor([total_ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -300,6 +302,8 @@ def run_b200(args, rank, world, local_rank):
 
     # (4) extend leg (configs[2]): 32 requests sharing a 2048-token prefix + 512 new tokens, causal
     ext = run_extend_leg(args, dev, gen, peaks)
+    clk.__exit__()
+    clocks = clk.summary()
 
     if rank != 0:
         return

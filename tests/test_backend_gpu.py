@@ -134,6 +134,6 @@ def test_backend_cuda_graph_decode_replay():
         assert torch.equal(kc[loc], s_k.view(B, Hkv, D))  # the captured store ran with the new slots
 
     check(lens0, 5)
-    check([1, 1000, 17, 16, 333, 640, 2, 45], 6)
+    check([1, 900, 17, 16, 333, 640, 2, 45], 6)
     md = backend.forward_metadata
     assert int(md.kv_indptr[0]) == 0 and bool((md.kv_indptr[1:B + 1] >= md.kv_indptr[:B]).all())
