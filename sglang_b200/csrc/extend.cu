@@ -5,11 +5,14 @@
 // with L keys and E query rows sits at absolute position L-E+j; causal or not).
 //
 // One CTA = one 128-row query tile of one (request, q head):
-//   warp 4      TMA producer: Q tile (2 boxes of 128 x 64) and, per 128-key step, K and V tiles
-//               gathered token-granular from the paged pool with cp.async.bulk.tensor
-//               tile::gather4 (4 pool rows per instruction, hardware 128B swizzle, OOB rows
-//               zero-filled) -> page_size agnostic, no page-contiguity assumption.
-//   warp 5      MMA issuer (one elected lane): S = Q K^T as 8 x tcgen05.mma M128 N128 K16 into a
+//   warp 4/5    TMA producers (4: Q + K tiles, 5: V tiles).  Per 128-key step the warp reads the
+//               128 slot ids and checks on the fly that every aligned 16-key group sits in 16
+//               consecutive pool slots (true under the paged allocator for page_size >= 16):
+//                 yes -> 16 tiled TMA boxes (16 rows x 64 cols) from one elected lane;
+//                 no / ragged last step -> cp.async.bulk.tensor tile::gather4 (4 pool rows per
+//                 instruction, OOB rows zero-filled): any page size, no contiguity assumption.
+//               Both land in the same 128B-swizzled K-major layout.
+//   warp 6      MMA issuer (one elected lane): S = Q K^T as 8 x tcgen05.mma M128 N128 K16 into a
 //               double-buffered TMEM accumulator, O += P V as 8 x tcgen05.mma (V is the MN-major
 //               B operand straight from the gathered tile).  QK^T of step j+1 is issued before
 //               P V of step j so the tensor pipe works under the softmax.
@@ -26,7 +29,8 @@ namespace b200attn {
 constexpr int kExtM = 128;        // query rows per CTA
 constexpr int kExtN = 128;        // keys per step
 constexpr int kExtStages = 2;     // K and V ring depth
-constexpr int kExtThreads = 192;  // 4 softmax warps + producer + MMA
+constexpr int kExtThreads = 224;  // 4 softmax warps + 2 producers + MMA
+constexpr int kExtBoxRows = 16;   // rows of one tiled K/V TMA box
 constexpr float kRescaleThreshold = 8.f;  // log2 domain
 
 struct ExtendParams {
@@ -70,7 +74,8 @@ enum ExtBar {
 template <int D, bool kBf16>
 __global__ void __launch_bounds__(kExtThreads, 1)
     extend_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
-                  const __grid_constant__ CUtensorMap tm_v, const ExtendParams p) {
+                  const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_kbox,
+                  const __grid_constant__ CUtensorMap tm_vbox, const ExtendParams p) {
   using namespace sm100;
   using S = ExtSmem<D>;
   constexpr int kHalves = D / 64;  // 64-column halves of the head dim
@@ -118,20 +123,25 @@ __global__ void __launch_bounds__(kExtThreads, 1)
     mbar_init(bar(kBarPVDone), 1);
     mbar_fence_init();
   }
-  if (warp == 5) tmem_alloc<kTmemCols>(smem_u32(tmem_slot));
+  if (warp == 6) tmem_alloc<kTmemCols>(smem_u32(tmem_slot));
   if (warp == 4 && lane == 0) {
     tma_prefetch_desc(&tm_q);
     tma_prefetch_desc(&tm_k);
+    tma_prefetch_desc(&tm_kbox);
+  }
+  if (warp == 5 && lane == 0) {
     tma_prefetch_desc(&tm_v);
+    tma_prefetch_desc(&tm_vbox);
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
-  if (warp == 4) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
+  if (warp == 4 || warp == 5) {
+    // ===================== TMA producers (warp 4: Q + K, warp 5: V) =====================
+    const bool is_k = (warp == 4);
+    if (is_k && lane == 0) {
       mbar_arrive_expect_tx(bar(kBarQ), S::kTile);
 #pragma unroll
       for (int hf = 0; hf < kHalves; ++hf)
@@ -139,34 +149,51 @@ __global__ void __launch_bounds__(kExtThreads, 1)
     }
     const int32_t* idx = p.kv_indices + kv_beg;
     const int col = kvh * D;
-    for (int j = 0; j < ntiles; ++j) {
-      const int st = j % kExtStages;
-      const uint32_t par_empty = ((j / kExtStages) + 1) & 1;
-      int r[4];
+    const CUtensorMap* tm_g = is_k ? &tm_k : &tm_v;
+    const CUtensorMap* tm_b = is_k ? &tm_kbox : &tm_vbox;
+    const uint32_t tile0 = smem0 + (is_k ? S::kK : S::kV);
+    const int bar_full = is_k ? kBarKFull : kBarVFull, bar_empty = is_k ? kBarKEmpty : kBarVEmpty;
+    int r[4];
+    auto load_slots = [&](int j) {
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int key = j * kExtN + lane * 4 + i;
-        r[i] = (key < kv_end) ? __ldg(idx + key) : p.num_slots;  // OOB row -> zero fill
+        r[i] = (j < ntiles && key < kv_end) ? __ldg(idx + key) : p.num_slots;  // OOB row -> zero fill
       }
-      const uint32_t row_off = lane * 4 * 128;
-      // K tile
-      if (j >= kExtStages) mbar_wait(bar(kBarKEmpty + st), par_empty);
-      if (lane == 0) mbar_arrive_expect_tx(bar(kBarKFull + st), S::kTile);
+    };
+    load_slots(0);
+    for (int j = 0; j < ntiles; ++j) {
+      const int st = j % kExtStages;
+      const uint32_t dst = tile0 + st * S::kTile;
+      // every aligned 16-key group in 16 consecutive slots?  (4 lanes x 4 keys per group)
+      const int g0 = __shfl_sync(0xffffffffu, r[0], lane & ~3);
+      bool contig = (r[1] == r[0] + 1) && (r[2] == r[0] + 2) && (r[3] == r[0] + 3) &&
+                    (r[0] == g0 + 4 * (lane & 3));
+      contig = __all_sync(0xffffffffu, contig) && ((j + 1) * kExtN <= kv_end);
+      if (j >= kExtStages) mbar_wait(bar(bar_empty + st), ((j / kExtStages) + 1) & 1);
+      if (lane == 0) mbar_arrive_expect_tx(bar(bar_full + st), S::kTile);
       __syncwarp();
+      if (contig) {
+        int rows[kExtN / kExtBoxRows];
 #pragma unroll
-      for (int hf = 0; hf < kHalves; ++hf)
-        tma_gather4(smem0 + S::kK + st * S::kTile + hf * S::kHalf + row_off, &tm_k,
-                    bar(kBarKFull + st), col + hf * 64, r[0], r[1], r[2], r[3]);
-      // V tile
-      if (j >= kExtStages) mbar_wait(bar(kBarVEmpty + st), par_empty);
-      if (lane == 0) mbar_arrive_expect_tx(bar(kBarVFull + st), S::kTile);
-      __syncwarp();
+        for (int g = 0; g < kExtN / kExtBoxRows; ++g) rows[g] = __shfl_sync(0xffffffffu, r[0], g * 4);
+        if (lane == 0) {
 #pragma unroll
-      for (int hf = 0; hf < kHalves; ++hf)
-        tma_gather4(smem0 + S::kV + st * S::kTile + hf * S::kHalf + row_off, &tm_v,
-                    bar(kBarVFull + st), col + hf * 64, r[0], r[1], r[2], r[3]);
+          for (int g = 0; g < kExtN / kExtBoxRows; ++g)
+#pragma unroll
+            for (int hf = 0; hf < kHalves; ++hf)
+              tma_load_2d(dst + hf * S::kHalf + g * kExtBoxRows * 128, tm_b, bar(bar_full + st),
+                          col + hf * 64, rows[g]);
+        }
+      } else {
+#pragma unroll
+        for (int hf = 0; hf < kHalves; ++hf)
+          tma_gather4(dst + hf * S::kHalf + lane * 4 * 128, tm_g, bar(bar_full + st), col + hf * 64,
+                      r[0], r[1], r[2], r[3]);
+      }
+      load_slots(j + 1);
     }
-  } else if (warp == 5) {
+  } else if (warp == 6) {
     // ===================== MMA issuer =====================
     constexpr uint32_t idesc_qk = idesc_f16(kBf16 ? 1 : 0, kExtM, kExtN, 0, 0);
     constexpr uint32_t idesc_pv = idesc_f16(kBf16 ? 1 : 0, kExtM, D, 0, 1);
@@ -245,10 +272,15 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         for (int i = 0; i < kExtN; ++i)
           if (n0 + i >= limit) s[i] = -INFINITY;
       }
-      float mx = s[0];
+      float mx4[4] = {s[0], s[1], s[2], s[3]};
 #pragma unroll
-      for (int i = 1; i < kExtN; ++i) mx = fmaxf(mx, s[i]);
-      mx *= p.scale_log2;
+      for (int i = 4; i < kExtN; i += 4) {
+        mx4[0] = fmaxf(mx4[0], s[i]);
+        mx4[1] = fmaxf(mx4[1], s[i + 1]);
+        mx4[2] = fmaxf(mx4[2], s[i + 2]);
+        mx4[3] = fmaxf(mx4[3], s[i + 3]);
+      }
+      float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2;
       float alpha = 1.f;
       bool rescale = false;
       if (m_used == -INFINITY) {
@@ -259,15 +291,15 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         rescale = true;
       }
       uint32_t pk[kExtN / 2];
-      float sum = 0.f;
+      float sum4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int i = 0; i < kExtN; i += 2) {
         const float p0 = fast_exp2(fmaf(s[i], p.scale_log2, -m_used));
         const float p1 = fast_exp2(fmaf(s[i + 1], p.scale_log2, -m_used));
-        sum += p0 + p1;
+        sum4[(i / 2) & 3] += p0 + p1;
         pk[i / 2] = pack2<kBf16>(p0, p1);
       }
-      l_run = l_run * alpha + sum;
+      l_run = l_run * alpha + ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));
       // P buffer and O are free once P V of the previous step has completed
       if (j > 0) {
         mbar_wait(bar(kBarPVDone), (j - 1) & 1);
@@ -324,7 +356,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
     tc_fence_before();
   }
   __syncthreads();
-  if (warp == 5) {
+  if (warp == 6) {
     tc_fence_after();
     tmem_dealloc<kTmemCols>(tmem);
   }
@@ -378,7 +410,8 @@ int make_tensor_map_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64
 
 template <int D, bool kBf16>
 static int launch_extend(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
-                         const ExtendParams& p, int max_qtiles, cudaStream_t st) {
+                         const CUtensorMap& tkb, const CUtensorMap& tvb, const ExtendParams& p,
+                         int max_qtiles, cudaStream_t st) {
   constexpr int kSmem = ExtSmem<D>::kTotal + 1024;  // + alignment slack
   static bool configured = false;
   if (!configured) {
@@ -387,7 +420,7 @@ static int launch_extend(const CUtensorMap& tq, const CUtensorMap& tk, const CUt
     configured = true;
   }
   dim3 grid((unsigned)p.Hq, (unsigned)max_qtiles, (unsigned)p.B);
-  extend_kernel<D, kBf16><<<grid, kExtThreads, kSmem, st>>>(tq, tk, tv, p);
+  extend_kernel<D, kBf16><<<grid, kExtThreads, kSmem, st>>>(tq, tk, tv, tkb, tvb, p);
   B2_LAUNCH_CHECK();
   return B200ATTN_OK;
 }
@@ -422,7 +455,7 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
                "extend: tensors must be 16-byte aligned");
   if (dtype != B200ATTN_BF16 && dtype != B200ATTN_FP16) B2_UNSUPPORTED("extend: dtype %d", dtype);
   if (D != 64 && D != 128) B2_UNSUPPORTED("extend: head_dim %d (supported: 64, 128)", D);
-  CUtensorMap tq, tk, tv;
+  CUtensorMap tq, tk, tv, tkb, tvb;
   int rc = make_tensor_map_2d(&tq, q, (uint64_t)total_q_host, (uint64_t)Hq * D,
                               (uint64_t)q_stride * 2, 64, kExtM);
   if (rc) return rc;
@@ -431,6 +464,12 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
   if (rc) return rc;
   rc = make_tensor_map_2d(&tv, v_cache, (uint64_t)num_slots, (uint64_t)Hkv * D,
                           (uint64_t)kv_stride * 2, 64, 1);
+  if (rc) return rc;
+  rc = make_tensor_map_2d(&tkb, k_cache, (uint64_t)num_slots, (uint64_t)Hkv * D,
+                          (uint64_t)kv_stride * 2, 64, kExtBoxRows);
+  if (rc) return rc;
+  rc = make_tensor_map_2d(&tvb, v_cache, (uint64_t)num_slots, (uint64_t)Hkv * D,
+                          (uint64_t)kv_stride * 2, 64, kExtBoxRows);
   if (rc) return rc;
   ExtendParams p;
   p.o = o;
@@ -449,8 +488,8 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
   const int max_qtiles = (max_qo_len_host + kExtM - 1) / kExtM;
   cudaStream_t st = (cudaStream_t)stream;
   if (D == 128)
-    return dtype == B200ATTN_BF16 ? launch_extend<128, true>(tq, tk, tv, p, max_qtiles, st)
-                                  : launch_extend<128, false>(tq, tk, tv, p, max_qtiles, st);
-  return dtype == B200ATTN_BF16 ? launch_extend<64, true>(tq, tk, tv, p, max_qtiles, st)
-                                : launch_extend<64, false>(tq, tk, tv, p, max_qtiles, st);
+    return dtype == B200ATTN_BF16 ? launch_extend<128, true>(tq, tk, tv, tkb, tvb, p, max_qtiles, st)
+                                  : launch_extend<128, false>(tq, tk, tv, tkb, tvb, p, max_qtiles, st);
+  return dtype == B200ATTN_BF16 ? launch_extend<64, true>(tq, tk, tv, tkb, tvb, p, max_qtiles, st)
+                                : launch_extend<64, false>(tq, tk, tv, tkb, tvb, p, max_qtiles, st);
 }

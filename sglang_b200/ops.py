@@ -167,17 +167,21 @@ def decode_workspace_bytes(B: int, Hq: int, D: int, max_splits: int) -> int:
 
 
 def pick_max_splits(B: int, Hkv: int, G: int, max_kv_len: int, min_chunk: int = 256,
-                    waves: int = 4, ctas_per_sm: int = 2, num_sms: Optional[int] = None) -> int:
-    """Host-side choice of the split cap: enough CTAs for `waves` full waves, never
-    finer than `min_chunk` keys per split.  The per-request split count itself is
-    computed on the device (split_policy in csrc/common.cuh)."""
+                    ctas_per_sm: int = 2, num_sms: Optional[int] = None) -> int:
+    """Host-side choice of the split cap.  The decode grid is (splits x kv-head groups x batch)
+    CTAs over `ctas_per_sm * num_sms` resident slots.  Measured on B200 (profiles/r01_decode_
+    split_sweep.txt): the kernel is HBM-bound, a partly filled last wave costs nothing because
+    the remaining CTAs inherit the bandwidth, while every extra split costs workspace traffic
+    and the merge launch -> split only as far as needed to put one CTA on every slot, never
+    finer than `min_chunk` keys.  The per-request split count itself is computed on the device
+    (split_policy in csrc/common.cuh)."""
     if num_sms is None:
         num_sms = sm_count()
     groups = (G + 15) // 16
     items = max(1, B * Hkv * groups)
-    want = -(-waves * ctas_per_sm * num_sms // items)
-    cap = max(1, -(-max_kv_len // min_chunk))
-    return int(max(1, min(want, cap, 64)))
+    slots = ctas_per_sm * num_sms
+    cap = int(max(1, min(-(-max_kv_len // min_chunk), 32)))
+    return int(max(1, min(cap, -(-slots // items))))
 
 
 def decode_attention(

@@ -84,7 +84,7 @@ def test_decode_full_size_cfg2_vs_fp32_reference():
     lens[0] = 4096
     sc = make_scenario(lens, [0] * 64, 32, 8, 128, 16, seed=20261106)
     sc.q = torch.randn((64, 32 * 128), generator=g).to(torch.bfloat16)
-    o, _ = _run_decode(sc, ops.pick_max_splits(64, 8, 4, 4096), min_chunk=256)
+    o, _ = _run_decode(sc, 4, min_chunk=256)
     d = sc.to(DEV)
     ref = oracle.attention_fp32(d.q, d.k_cache, d.v_cache, d.req_to_token, d.req_pool_indices,
                                 torch.tensor(lens), torch.ones(64, dtype=torch.int64), 32, 8, 128, sc.scaling,
