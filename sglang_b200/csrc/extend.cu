@@ -4,34 +4,40 @@
 // (prefix + new tokens all read from the pool through req_to_token; query j of a request
 // with L keys and E query rows sits at absolute position L-E+j; causal or not).
 //
-// One CTA = one 128-row query tile of one (request, q head):
-//   warp 4/5    TMA producers (4: Q + K tiles, 5: V tiles).  Per 128-key step the warp reads the
-//               128 slot ids and checks on the fly that every aligned 16-key group sits in 16
-//               consecutive pool slots (true under the paged allocator for page_size >= 16):
-//                 yes -> 16 tiled TMA boxes (16 rows x 64 cols) from one elected lane;
-//                 no / ragged last step -> cp.async.bulk.tensor tile::gather4 (4 pool rows per
-//                 instruction, OOB rows zero-filled): any page size, no contiguity assumption.
-//               Both land in the same 128B-swizzled K-major layout.
-//   warp 6      MMA issuer (one elected lane): S = Q K^T as 8 x tcgen05.mma M128 N128 K16 into a
-//               double-buffered TMEM accumulator, O += P V as 8 x tcgen05.mma (V is the MN-major
-//               B operand straight from the gathered tile).  QK^T of step j+1 is issued before
-//               P V of step j so the tensor pipe works under the softmax.
-//   warps 0-3   softmax: thread = query row (TMEM lane); tcgen05.ld S, causal / ragged masking,
-//               exp2 online softmax with lazy rescaling (O in TMEM is only rescaled when the row
-//               max grew by > 2^8), P written as bf16 into a 128B-swizzled smem tile for the
-//               second GEMM; epilogue O / l -> global.
-// TMEM: S0 [0,128) S1 [128,256) O [256,384) fp32 columns.
+// One CTA = TWO 128-row query tiles that share one kv head of one request, so every K/V tile
+// fetched into shared memory feeds two S = Q K^T and two O += P V contractions.  The two tiles
+// are consecutive entries of the request's "virtual tile" list v = qtile * G + g (g = q head
+// inside the GQA group): for even G they are two q heads over the same query rows, for odd G
+// (and MHA) a pair may straddle two row tiles.  Each tile has its own length bookkeeping.
+//
+//   warps 0-3   softmax of tile 0      thread = query row = TMEM lane: tcgen05.ld S, masking,
+//   warps 4-7   softmax of tile 1      exp2 online softmax (packed f32x2 FMAs, 3-input max, lazy
+//                                      rescale of O in TMEM when the row max grew by > 2^8), P
+//                                      written back as bf16 INTO the S columns (tcgen05.st), so the
+//                                      second GEMM reads its A operand from TMEM; epilogue O / l.
+//   warp 8      TMA producer: Q tiles + K tiles      Per 128-key step the warp reads the 128 slot
+//   warp 9      TMA producer: V tiles                ids and checks that every aligned 16-key group
+//               sits in 16 consecutive pool slots (true under the paged allocator for page_size >=
+//               16): yes -> 16-row tiled TMA boxes; no / ragged tail -> tile::gather4 (4 arbitrary
+//               pool rows per instruction, OOB rows zero-filled).  Same 128B-swizzled layout.
+//   warp 10     MMA issuer (one elected lane).  Order per step j: PV0(j) QK0(j+1) PV1(j) QK1(j+1):
+//               while one softmax warpgroup works on its S the tensor pipe runs the other tile.
+//               P(j) aliases S(j): correctness relies on the tensor pipe executing one thread's
+//               tcgen05.mma in issue order (PV_i(j) reads P before QK_i(j+1) overwrites it).
+//   warp 11     idle (keeps the third warpgroup whole for setmaxnreg).
+// TMEM (512 columns): S0/P0 [0,128)  S1/P1 [128,256)  O0 [256,384)  O1 [384,512).
 // Algorithmic FLOPs per (request, q head): 4 * D * sum_j (#visible keys of row j).
 #include "sm100.cuh"
 
 namespace b200attn {
 
-constexpr int kExtM = 128;        // query rows per CTA
+constexpr int kExtM = 128;        // query rows per tile (two tiles per CTA)
 constexpr int kExtN = 128;        // keys per step
 constexpr int kExtStages = 2;     // K and V ring depth
-constexpr int kExtThreads = 224;  // 4 softmax warps + 2 producers + MMA
+constexpr int kExtThreads = 384;  // 2 softmax warpgroups + {K producer, V producer, MMA, idle}
 constexpr int kExtBoxRows = 16;   // rows of one tiled K/V TMA box
 constexpr float kRescaleThreshold = 8.f;  // log2 domain
+constexpr int kRegsSoftmax = 208, kRegsOther = 80;
 
 struct ExtendParams {
   void* o;
@@ -50,26 +56,59 @@ template <int D>
 struct ExtSmem {
   static constexpr int kTile = kExtN * D * 2;  // one 128 x D operand tile (bf16)
   static constexpr int kHalf = kExtN * 128;    // one 64-column half: 128 rows x 128 B
-  static constexpr int kQ = 0;
-  static constexpr int kK = kQ + kTile;
+  static constexpr int kQ = 0;                 // [2] query tiles
+  static constexpr int kK = kQ + 2 * kTile;
   static constexpr int kV = kK + kExtStages * kTile;
-  static constexpr int kP = kV + kExtStages * kTile;
-  static constexpr int kBar = kP + kExtM * kExtN * 2;
+  static constexpr int kBar = kV + kExtStages * kTile;
   static constexpr int kTotal = kBar + 256;
 };
 
 enum ExtBar {
-  kBarQ = 0,
-  kBarKFull = 1,                       // [stages]
+  kBarQ = 0,                            // [2]
+  kBarKFull = kBarQ + 2,                // [stages]
   kBarKEmpty = kBarKFull + kExtStages,
   kBarVFull = kBarKEmpty + kExtStages,
   kBarVEmpty = kBarVFull + kExtStages,
-  kBarSFull = kBarVEmpty + kExtStages,  // [2]
-  kBarSEmpty = kBarSFull + 2,           // [2]
-  kBarPFull = kBarSEmpty + 2,
-  kBarPVDone = kBarPFull + 1,
-  kBarCount = kBarPVDone + 1
+  kBarSFull = kBarVEmpty + kExtStages,  // [2]  MMA -> softmax_i : S_i(j) is in TMEM
+  kBarPFull = kBarSFull + 2,            // [2]  softmax_i -> MMA : P_i(j) is in TMEM, O_i rescaled
+  kBarOFinal = kBarPFull + 2,           // [2]  MMA -> softmax_i : last PV_i done
+  kBarCount = kBarOFinal + 2
 };
+
+// ---- packed fp32x2 helpers (FFMA2 / FADD2 / FMNMX3 on sm_100) ----
+__device__ __forceinline__ uint64_t f2_pack(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t f2_mul(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+  float r;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 
 template <int D, bool kBf16>
 __global__ void __launch_bounds__(kExtThreads, 1)
@@ -80,23 +119,34 @@ __global__ void __launch_bounds__(kExtThreads, 1)
   using S = ExtSmem<D>;
   constexpr int kHalves = D / 64;  // 64-column halves of the head dim
   constexpr uint32_t kTmemCols = 512;
-  constexpr uint32_t kColS = 0, kColO = 256;
+  constexpr uint32_t kColS = 0, kColO = 256;  // + i * 128
 
-  const int h = blockIdx.x;
+  // ---- which two tiles does this CTA own? ----
+  const int kvh = blockIdx.y;
   const int b = blockIdx.z;
   const int q_beg = p.qo_indptr[b];
   const int E = p.qo_indptr[b + 1] - q_beg;
   const int num_qtiles = (E + kExtM - 1) / kExtM;
-  if ((int)blockIdx.y >= num_qtiles) return;
-  const int qt = num_qtiles - 1 - blockIdx.y;  // heavy (late) causal tiles first
-  const int m0 = qt * kExtM;
-  const int rows_valid = min(kExtM, E - m0);
+  const int nv = num_qtiles * p.G;  // virtual tiles of this (request, kv head)
+  const int npairs = (nv + 1) >> 1;
+  if ((int)blockIdx.x >= npairs) return;
+  const int pair = npairs - 1 - blockIdx.x;  // heavy (late) causal tiles first
   const int kv_beg = p.kv_indptr[b];
   const int L = p.kv_indptr[b + 1] - kv_beg;
   const int prefix = L - E;
-  const int kv_end = p.causal ? min(L, prefix + m0 + rows_valid) : L;
-  const int ntiles = (kv_end + kExtN - 1) / kExtN;
-  const int kvh = h / p.G;
+  int t_h[2], t_m0[2], t_rows[2], t_kvend[2], t_n[2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int v = 2 * pair + i;
+    const bool ok = v < nv;
+    t_h[i] = kvh * p.G + (ok ? v % p.G : 0);
+    t_m0[i] = (ok ? v / p.G : 0) * kExtM;
+    t_rows[i] = ok ? min(kExtM, E - t_m0[i]) : 0;
+    t_kvend[i] = !ok ? 0 : (p.causal ? min(L, prefix + t_m0[i] + t_rows[i]) : L);
+    t_n[i] = (t_kvend[i] + kExtN - 1) / kExtN;
+  }
+  const int kv_end = max(t_kvend[0], t_kvend[1]);
+  const int ntiles = max(t_n[0], t_n[1]);
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -108,28 +158,27 @@ __global__ void __launch_bounds__(kExtThreads, 1)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    mbar_init(bar(kBarQ), 1);
     for (int s = 0; s < kExtStages; ++s) {
       mbar_init(bar(kBarKFull + s), 1);
       mbar_init(bar(kBarKEmpty + s), 1);
       mbar_init(bar(kBarVFull + s), 1);
       mbar_init(bar(kBarVEmpty + s), 1);
     }
-    for (int s = 0; s < 2; ++s) {
-      mbar_init(bar(kBarSFull + s), 1);
-      mbar_init(bar(kBarSEmpty + s), 128);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar(kBarQ + i), 1);
+      mbar_init(bar(kBarSFull + i), 1);
+      mbar_init(bar(kBarPFull + i), 128);
+      mbar_init(bar(kBarOFinal + i), 1);
     }
-    mbar_init(bar(kBarPFull), 128);
-    mbar_init(bar(kBarPVDone), 1);
     mbar_fence_init();
   }
-  if (warp == 6) tmem_alloc<kTmemCols>(smem_u32(tmem_slot));
-  if (warp == 4 && lane == 0) {
+  if (warp == 10) tmem_alloc<kTmemCols>(smem_u32(tmem_slot));
+  if (warp == 8 && lane == 0) {
     tma_prefetch_desc(&tm_q);
     tma_prefetch_desc(&tm_k);
     tma_prefetch_desc(&tm_kbox);
   }
-  if (warp == 5 && lane == 0) {
+  if (warp == 9 && lane == 0) {
     tma_prefetch_desc(&tm_v);
     tma_prefetch_desc(&tm_vbox);
   }
@@ -138,225 +187,252 @@ __global__ void __launch_bounds__(kExtThreads, 1)
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
-  if (warp == 4 || warp == 5) {
-    // ===================== TMA producers (warp 4: Q + K, warp 5: V) =====================
-    const bool is_k = (warp == 4);
-    if (is_k && lane == 0) {
-      mbar_arrive_expect_tx(bar(kBarQ), S::kTile);
+  if (warp >= 8) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" ::"n"(kRegsOther));
+    if (warp == 8 || warp == 9) {
+      // ===================== TMA producers (warp 8: Q + K, warp 9: V) =====================
+      const bool is_k = (warp == 8);
+      if (is_k && lane == 0) {
 #pragma unroll
-      for (int hf = 0; hf < kHalves; ++hf)
-        tma_load_2d(smem0 + S::kQ + hf * S::kHalf, &tm_q, bar(kBarQ), h * D + hf * 64, q_beg + m0);
-    }
-    const int32_t* idx = p.kv_indices + kv_beg;
-    const int col = kvh * D;
-    const CUtensorMap* tm_g = is_k ? &tm_k : &tm_v;
-    const CUtensorMap* tm_b = is_k ? &tm_kbox : &tm_vbox;
-    const uint32_t tile0 = smem0 + (is_k ? S::kK : S::kV);
-    const int bar_full = is_k ? kBarKFull : kBarVFull, bar_empty = is_k ? kBarKEmpty : kBarVEmpty;
-    int r[4];
-    auto load_slots = [&](int j) {
+        for (int i = 0; i < 2; ++i) {
+          if (t_n[i] == 0) continue;
+          mbar_arrive_expect_tx(bar(kBarQ + i), S::kTile);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int key = j * kExtN + lane * 4 + i;
-        r[i] = (j < ntiles && key < kv_end) ? __ldg(idx + key) : p.num_slots;  // OOB row -> zero fill
+          for (int hf = 0; hf < kHalves; ++hf)
+            tma_load_2d(smem0 + S::kQ + i * S::kTile + hf * S::kHalf, &tm_q, bar(kBarQ + i),
+                        t_h[i] * D + hf * 64, q_beg + t_m0[i]);
+        }
       }
-    };
-    load_slots(0);
-    for (int j = 0; j < ntiles; ++j) {
-      const int st = j % kExtStages;
-      const uint32_t dst = tile0 + st * S::kTile;
-      // every aligned 16-key group in 16 consecutive slots?  (4 lanes x 4 keys per group)
-      const int g0 = __shfl_sync(0xffffffffu, r[0], lane & ~3);
-      bool contig = (r[1] == r[0] + 1) && (r[2] == r[0] + 2) && (r[3] == r[0] + 3) &&
-                    (r[0] == g0 + 4 * (lane & 3));
-      contig = __all_sync(0xffffffffu, contig) && ((j + 1) * kExtN <= kv_end);
-      if (j >= kExtStages) mbar_wait(bar(bar_empty + st), ((j / kExtStages) + 1) & 1);
-      if (lane == 0) mbar_arrive_expect_tx(bar(bar_full + st), S::kTile);
-      __syncwarp();
-      if (contig) {
-        int rows[kExtN / kExtBoxRows];
+      const int32_t* idx = p.kv_indices + kv_beg;
+      const int col = kvh * D;
+      const CUtensorMap* tm_g = is_k ? &tm_k : &tm_v;
+      const CUtensorMap* tm_b = is_k ? &tm_kbox : &tm_vbox;
+      const uint32_t tile0 = smem0 + (is_k ? S::kK : S::kV);
+      const int bar_full = is_k ? kBarKFull : kBarVFull, bar_empty = is_k ? kBarKEmpty : kBarVEmpty;
+      int r[4];
+      auto load_slots = [&](int j) {
 #pragma unroll
-        for (int g = 0; g < kExtN / kExtBoxRows; ++g) rows[g] = __shfl_sync(0xffffffffu, r[0], g * 4);
+        for (int i = 0; i < 4; ++i) {
+          const int key = j * kExtN + lane * 4 + i;
+          r[i] = (j < ntiles && key < kv_end) ? __ldg(idx + key) : p.num_slots;  // OOB row -> zeros
+        }
+      };
+      load_slots(0);
+      for (int j = 0; j < ntiles; ++j) {
+        const int st = j % kExtStages;
+        const uint32_t dst = tile0 + st * S::kTile;
+        // every aligned 16-key group in 16 consecutive slots?  (4 lanes x 4 keys per group)
+        const int g0 = __shfl_sync(0xffffffffu, r[0], lane & ~3);
+        bool contig = (r[1] == r[0] + 1) && (r[2] == r[0] + 2) && (r[3] == r[0] + 3) &&
+                      (r[0] == g0 + 4 * (lane & 3));
+        contig = __all_sync(0xffffffffu, contig) && ((j + 1) * kExtN <= kv_end);
+        if (j >= kExtStages) mbar_wait(bar(bar_empty + st), ((j / kExtStages) + 1) & 1);
+        if (lane == 0) mbar_arrive_expect_tx(bar(bar_full + st), S::kTile);
+        __syncwarp();
+        if (contig) {
+          int rows[kExtN / kExtBoxRows];
+#pragma unroll
+          for (int g = 0; g < kExtN / kExtBoxRows; ++g) rows[g] = __shfl_sync(0xffffffffu, r[0], g * 4);
+          if (lane == 0) {
+#pragma unroll
+            for (int g = 0; g < kExtN / kExtBoxRows; ++g)
+#pragma unroll
+              for (int hf = 0; hf < kHalves; ++hf)
+                tma_load_2d(dst + hf * S::kHalf + g * kExtBoxRows * 128, tm_b, bar(bar_full + st),
+                            col + hf * 64, rows[g]);
+          }
+        } else {
+#pragma unroll
+          for (int hf = 0; hf < kHalves; ++hf)
+            tma_gather4(dst + hf * S::kHalf + lane * 4 * 128, tm_g, bar(bar_full + st), col + hf * 64,
+                        r[0], r[1], r[2], r[3]);
+        }
+        load_slots(j + 1);
+      }
+    } else if (warp == 10) {
+      // ===================== MMA issuer =====================
+      constexpr uint32_t idesc_qk = idesc_f16(kBf16 ? 1 : 0, kExtM, kExtN, 0, 0);
+      constexpr uint32_t idesc_pv = idesc_f16(kBf16 ? 1 : 0, kExtM, D, 0, 1);
+      // S_i(j) = Q_i K_j^T  (both operands K-major from smem)
+      auto issue_qk = [&](int i, int j) {
         if (lane == 0) {
+          const int st = j % kExtStages;
 #pragma unroll
-          for (int g = 0; g < kExtN / kExtBoxRows; ++g)
-#pragma unroll
-            for (int hf = 0; hf < kHalves; ++hf)
-              tma_load_2d(dst + hf * S::kHalf + g * kExtBoxRows * 128, tm_b, bar(bar_full + st),
-                          col + hf * 64, rows[g]);
+          for (int ks = 0; ks < D / 16; ++ks) {
+            const uint32_t off = (ks / 4) * S::kHalf + (ks % 4) * 32;
+            const uint64_t a = smem_desc_sw128(smem0 + S::kQ + i * S::kTile + off, 16, 1024);
+            const uint64_t bd = smem_desc_sw128(smem0 + S::kK + st * S::kTile + off, 16, 1024);
+            umma_ss(tmem + kColS + i * kExtN, a, bd, idesc_qk, ks > 0 ? 1u : 0u);
+          }
+          umma_commit(bar(kBarSFull + i));
         }
-      } else {
+        __syncwarp();
+      };
+      // O_i (+)= P_i(j) V_j  (A = bf16 P in the S_i columns of TMEM, B = V MN-major from smem)
+      auto issue_pv = [&](int i, int j) {
+        if (lane == 0) {
+          const int st = j % kExtStages;
 #pragma unroll
-        for (int hf = 0; hf < kHalves; ++hf)
-          tma_gather4(dst + hf * S::kHalf + lane * 4 * 128, tm_g, bar(bar_full + st), col + hf * 64,
-                      r[0], r[1], r[2], r[3]);
-      }
-      load_slots(j + 1);
-    }
-  } else if (warp == 6) {
-    // ===================== MMA issuer =====================
-    constexpr uint32_t idesc_qk = idesc_f16(kBf16 ? 1 : 0, kExtM, kExtN, 0, 0);
-    constexpr uint32_t idesc_pv = idesc_f16(kBf16 ? 1 : 0, kExtM, D, 0, 1);
-    mbar_wait(bar(kBarQ), 0);
-    tc_fence_after();
-    auto issue_pv = [&](int j) {
-      const int st = j % kExtStages;
-      mbar_wait(bar(kBarPFull), j & 1);
-      mbar_wait(bar(kBarVFull + st), (j / kExtStages) & 1);
+          for (int ks = 0; ks < kExtN / 16; ++ks) {
+            // 16 keys per step = 8 packed TMEM columns of A; 2 KB down the V tile; d-halves 16 KB apart
+            const uint64_t bd = smem_desc_sw128(smem0 + S::kV + st * S::kTile + ks * 2048, S::kHalf, 1024);
+            umma_ts(tmem + kColO + i * 128, tmem + kColS + i * kExtN + ks * 8, bd, idesc_pv,
+                    (j > 0 || ks > 0) ? 1u : 0u);
+          }
+          if (j == t_n[i] - 1) umma_commit(bar(kBarOFinal + i));
+        }
+        __syncwarp();
+      };
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+        if (t_n[i] > 0) mbar_wait(bar(kBarQ + i), 0);
+      mbar_wait(bar(kBarKFull + 0), 0);
       tc_fence_after();
-      if (lane == 0) {
 #pragma unroll
-        for (int ks = 0; ks < kExtN / 16; ++ks) {
-          // A = P (K-major, keys): 64-key halves of 128 rows x 128 B
-          const uint64_t a = smem_desc_sw128(
-              smem0 + S::kP + (ks / 4) * (kExtM * 128) + (ks % 4) * 32, 16, 1024);
-          // B = V (MN-major): 16 keys per step = 2 KB down the tile; d-halves 16 KB apart
-          const uint64_t bd = smem_desc_sw128(smem0 + S::kV + st * S::kTile + ks * 2048,
-                                              S::kHalf, 1024);
-          umma_ss(tmem + kColO, a, bd, idesc_pv, (j > 0 || ks > 0) ? 1u : 0u);
-        }
-        umma_commit(bar(kBarVEmpty + st));
-        umma_commit(bar(kBarPVDone));
-      }
-      __syncwarp();
-    };
-    for (int j = 0; j < ntiles; ++j) {
-      const int st = j % kExtStages, sb = j & 1;
-      mbar_wait(bar(kBarKFull + st), (j / kExtStages) & 1);
-      if (j >= 2) mbar_wait(bar(kBarSEmpty + sb), ((j / 2) + 1) & 1);
-      tc_fence_after();
-      if (lane == 0) {
+      for (int i = 0; i < 2; ++i)
+        if (t_n[i] > 0) issue_qk(i, 0);
+      if (lane == 0) umma_commit(bar(kBarKEmpty + 0));
+      for (int j = 0; j < ntiles; ++j) {
+        const int st = j % kExtStages, st1 = (j + 1) % kExtStages;
+        mbar_wait(bar(kBarVFull + st), (j / kExtStages) & 1);
+        if (j + 1 < ntiles) mbar_wait(bar(kBarKFull + st1), ((j + 1) / kExtStages) & 1);
 #pragma unroll
-        for (int ks = 0; ks < D / 16; ++ks) {
-          const uint32_t off = (ks / 4) * S::kHalf + (ks % 4) * 32;
-          const uint64_t a = smem_desc_sw128(smem0 + S::kQ + off, 16, 1024);
-          const uint64_t bd = smem_desc_sw128(smem0 + S::kK + st * S::kTile + off, 16, 1024);
-          umma_ss(tmem + kColS + sb * kExtN, a, bd, idesc_qk, ks > 0 ? 1u : 0u);
+        for (int i = 0; i < 2; ++i) {
+          if (j >= t_n[i]) continue;
+          mbar_wait(bar(kBarPFull + i), j & 1);
+          tc_fence_after();
+          issue_pv(i, j);
+          if (j + 1 < t_n[i]) issue_qk(i, j + 1);
         }
-        umma_commit(bar(kBarKEmpty + st));
-        umma_commit(bar(kBarSFull + sb));
+        if (lane == 0) {
+          umma_commit(bar(kBarVEmpty + st));
+          if (j + 1 < ntiles) umma_commit(bar(kBarKEmpty + st1));
+        }
+        __syncwarp();
       }
-      __syncwarp();
-      if (j > 0) issue_pv(j - 1);
     }
-    issue_pv(ntiles - 1);
   } else {
-    // ===================== softmax + epilogue (thread = query row) =====================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(kRegsSoftmax));
+    // ===================== softmax + epilogue (thread = query row of tile i) =====================
     using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
-    const int row = threadIdx.x;  // 0..127 == TMEM lane
-    const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
-    // keys visible to this row: [0, limit)
-    int limit = p.causal ? min(L, prefix + m0 + row + 1) : L;
-    limit = max(1, min(limit, kv_end));
-    float m_used = -INFINITY;  // reference max (log2 domain) the running sums are expressed in
-    float l_run = 0.f;
-    uint8_t* p_row = smem + S::kP + row * 128;
-    for (int j = 0; j < ntiles; ++j) {
-      const int sb = j & 1;
-      mbar_wait(bar(kBarSFull + sb), (j / 2) & 1);
-      tc_fence_after();
-      float s[kExtN];
-#pragma unroll
-      for (int c = 0; c < kExtN / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld32(lane_addr + kColS + sb * kExtN + c * 32, v);
-        tmem_wait_ld();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(v[i]);
-      }
-      tc_fence_before();
-      mbar_arrive(bar(kBarSEmpty + sb));
-      const int n0 = j * kExtN;
-      if (n0 + kExtN > limit) {
-#pragma unroll
-        for (int i = 0; i < kExtN; ++i)
-          if (n0 + i >= limit) s[i] = -INFINITY;
-      }
-      float mx4[4] = {s[0], s[1], s[2], s[3]};
-#pragma unroll
-      for (int i = 4; i < kExtN; i += 4) {
-        mx4[0] = fmaxf(mx4[0], s[i]);
-        mx4[1] = fmaxf(mx4[1], s[i + 1]);
-        mx4[2] = fmaxf(mx4[2], s[i + 2]);
-        mx4[3] = fmaxf(mx4[3], s[i + 3]);
-      }
-      float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2;
-      float alpha = 1.f;
-      bool rescale = false;
-      if (m_used == -INFINITY) {
-        m_used = (mx == -INFINITY) ? 0.f : mx;  // j == 0 (limit >= 1 => finite)
-      } else if (mx > m_used + kRescaleThreshold) {
-        alpha = fast_exp2(m_used - mx);
-        m_used = mx;
-        rescale = true;
-      }
-      uint32_t pk[kExtN / 2];
-      float sum4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-      for (int i = 0; i < kExtN; i += 2) {
-        const float p0 = fast_exp2(fmaf(s[i], p.scale_log2, -m_used));
-        const float p1 = fast_exp2(fmaf(s[i + 1], p.scale_log2, -m_used));
-        sum4[(i / 2) & 3] += p0 + p1;
-        pk[i / 2] = pack2<kBf16>(p0, p1);
-      }
-      l_run = l_run * alpha + ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));
-      // P buffer and O are free once P V of the previous step has completed
-      if (j > 0) {
-        mbar_wait(bar(kBarPVDone), (j - 1) & 1);
+    const int i = warp >> 2;           // tile of this warpgroup
+    const int row = threadIdx.x & 127;  // == TMEM lane
+    const int n_i = t_n[i];
+    if (n_i > 0) {
+      const uint32_t lane_addr = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+      const uint32_t col_s = lane_addr + kColS + i * kExtN, col_o = lane_addr + kColO + i * 128;
+      const int m0 = t_m0[i];
+      // keys visible to this row: [0, limit)
+      int limit = p.causal ? min(L, prefix + m0 + row + 1) : L;
+      limit = max(1, min(limit, t_kvend[i]));
+      float m_used = -INFINITY;  // reference max (log2 domain) the running sums are expressed in
+      float l_run = 0.f;
+      const uint64_t scale2 = f2_pack(p.scale_log2, p.scale_log2);
+      for (int j = 0; j < n_i; ++j) {
+        mbar_wait(bar(kBarSFull + i), j & 1);
         tc_fence_after();
+        float s[kExtN];
+#pragma unroll
+        for (int c = 0; c < kExtN / 32; ++c) {
+          uint32_t v[32];
+          tmem_ld32(col_s + c * 32, v);
+#pragma unroll
+          for (int e = 0; e < 32; ++e) s[c * 32 + e] = __uint_as_float(v[e]);
+        }
+        tmem_wait_ld();
+        const int n0 = j * kExtN;
+        if (n0 + kExtN > limit) {
+#pragma unroll
+          for (int e = 0; e < kExtN; ++e)
+            if (n0 + e >= limit) s[e] = -INFINITY;
+        }
+        float mx4[4] = {s[0], s[1], s[2], s[3]};
+#pragma unroll
+        for (int e = 4; e < kExtN; e += 8) {
+          mx4[0] = fmax3(mx4[0], s[e], s[e + 1]);
+          mx4[1] = fmax3(mx4[1], s[e + 2], s[e + 3]);
+          if (e + 4 < kExtN) {
+            mx4[2] = fmax3(mx4[2], s[e + 4], s[e + 5]);
+            mx4[3] = fmax3(mx4[3], s[e + 6], s[e + 7]);
+          }
+        }
+        const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2;
+        float alpha = 1.f;
+        bool rescale = false;
+        if (m_used == -INFINITY) {
+          m_used = (mx == -INFINITY) ? 0.f : mx;  // j == 0 (limit >= 1 => finite)
+        } else if (mx > m_used + kRescaleThreshold) {
+          alpha = ex2_approx(m_used - mx);
+          m_used = mx;
+          rescale = true;
+        }
+        // S_i(j) landed => PV_i(j-1) has completed (commit order), so O_i is quiescent here.
         if (__any_sync(0xffffffffu, rescale)) {
+          l_run *= alpha;
 #pragma unroll
           for (int c = 0; c < D / 32; ++c) {
             uint32_t v[32];
-            tmem_ld32(lane_addr + kColO + c * 32, v);
+            tmem_ld32(col_o + c * 32, v);
             tmem_wait_ld();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
-            tmem_st32(lane_addr + kColO + c * 32, v);
+            for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(__uint_as_float(v[e]) * alpha);
+            tmem_st32(col_o + c * 32, v);
           }
-          tmem_wait_st();
+        }
+        // p = exp2(s * scale - m); packed bf16 pairs go back into the first 64 columns of S_i
+        const uint64_t negm2 = f2_pack(-m_used, -m_used);
+        uint64_t sum2[2] = {0ull, 0ull};
+#pragma unroll
+        for (int c = 0; c < kExtN / 64; ++c) {
+          uint32_t pk[32];
+#pragma unroll
+          for (int e = 0; e < 64; e += 2) {
+            float x0, x1;
+            f2_unpack(f2_fma(f2_pack(s[c * 64 + e], s[c * 64 + e + 1]), scale2, negm2), x0, x1);
+            const float p0 = ex2_approx(x0), p1 = ex2_approx(x1);
+            sum2[(e >> 1) & 1] = f2_add(sum2[(e >> 1) & 1], f2_pack(p0, p1));
+            pk[e >> 1] = pack2<kBf16>(p0, p1);
+          }
+          tmem_st32(col_s + c * 32, pk);
+        }
+        float a0, a1;
+        f2_unpack(f2_add(sum2[0], sum2[1]), a0, a1);
+        l_run += a0 + a1;
+        tmem_wait_st();
+        tc_fence_before();
+        mbar_arrive(bar(kBarPFull + i));
+      }
+      // ---- epilogue ----
+      mbar_wait(bar(kBarOFinal + i), 0);
+      tc_fence_after();
+      const float inv = 1.f / l_run;
+      const bool valid = row < t_rows[i];
+      const int h = t_h[i];
+      T* dst = reinterpret_cast<T*>(p.o) + (int64_t)(q_beg + m0 + row) * p.o_stride + (int64_t)h * D;
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld32(col_o + c * 32, v);
+        tmem_wait_ld();
+        if (valid) {
+#pragma unroll
+          for (int e = 0; e < 32; e += 8) {
+            uint4 w;
+            w.x = pack2<kBf16>(__uint_as_float(v[e]) * inv, __uint_as_float(v[e + 1]) * inv);
+            w.y = pack2<kBf16>(__uint_as_float(v[e + 2]) * inv, __uint_as_float(v[e + 3]) * inv);
+            w.z = pack2<kBf16>(__uint_as_float(v[e + 4]) * inv, __uint_as_float(v[e + 5]) * inv);
+            w.w = pack2<kBf16>(__uint_as_float(v[e + 6]) * inv, __uint_as_float(v[e + 7]) * inv);
+            *reinterpret_cast<uint4*>(dst + c * 32 + e) = w;
+          }
         }
       }
-      // P[row][key] -> K-major 128B-swizzled smem (two 64-key halves)
-#pragma unroll
-      for (int c = 0; c < kExtN / 8; ++c) {
-        const int half = c / 8, chunk = c % 8;
-        uint4 val = make_uint4(pk[c * 4], pk[c * 4 + 1], pk[c * 4 + 2], pk[c * 4 + 3]);
-        *reinterpret_cast<uint4*>(p_row + half * (kExtM * 128) + ((chunk ^ (row & 7)) << 4)) = val;
-      }
-      fence_proxy_async_smem();
+      if (valid && p.lse != nullptr)
+        p.lse[(int64_t)(q_beg + m0 + row) * p.Hq + h] = (m_used + log2f(l_run)) * kLn2;
       tc_fence_before();
-      mbar_arrive(bar(kBarPFull));
     }
-    // ---- epilogue ----
-    mbar_wait(bar(kBarPVDone), (ntiles - 1) & 1);
-    tc_fence_after();
-    const float inv = 1.f / l_run;
-    const bool valid = row < rows_valid;
-    T* dst = reinterpret_cast<T*>(p.o) + (int64_t)(q_beg + m0 + row) * p.o_stride + (int64_t)h * D;
-#pragma unroll
-    for (int c = 0; c < D / 32; ++c) {
-      uint32_t v[32];
-      tmem_ld32(lane_addr + kColO + c * 32, v);
-      tmem_wait_ld();
-      if (valid) {
-#pragma unroll
-        for (int i = 0; i < 32; i += 8) {
-          uint4 w;
-          w.x = pack2<kBf16>(__uint_as_float(v[i]) * inv, __uint_as_float(v[i + 1]) * inv);
-          w.y = pack2<kBf16>(__uint_as_float(v[i + 2]) * inv, __uint_as_float(v[i + 3]) * inv);
-          w.z = pack2<kBf16>(__uint_as_float(v[i + 4]) * inv, __uint_as_float(v[i + 5]) * inv);
-          w.w = pack2<kBf16>(__uint_as_float(v[i + 6]) * inv, __uint_as_float(v[i + 7]) * inv);
-          *reinterpret_cast<uint4*>(dst + c * 32 + i) = w;
-        }
-      }
-    }
-    if (valid && p.lse != nullptr)
-      p.lse[(int64_t)(q_beg + m0 + row) * p.Hq + h] = (m_used + log2f(l_run)) * kLn2;
-    tc_fence_before();
   }
   __syncthreads();
-  if (warp == 6) {
+  if (warp == 10) {
     tc_fence_after();
     tmem_dealloc<kTmemCols>(tmem);
   }
@@ -419,7 +495,9 @@ static int launch_extend(const CUtensorMap& tq, const CUtensorMap& tk, const CUt
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     configured = true;
   }
-  dim3 grid((unsigned)p.Hq, (unsigned)max_qtiles, (unsigned)p.B);
+  // x: pairs of virtual tiles (q tile x GQA-group head) of one (request, kv head); fastest, so
+  // the CTAs that share a kv head's K/V tiles run together and hit them in L2
+  dim3 grid((unsigned)((max_qtiles * p.G + 1) / 2), (unsigned)p.Hkv, (unsigned)p.B);
   extend_kernel<D, kBf16><<<grid, kExtThreads, kSmem, st>>>(tq, tk, tv, tkb, tvb, p);
   B2_LAUNCH_CHECK();
   return B200ATTN_OK;
@@ -447,7 +525,7 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
                "extend: null pointer");
   B2_CHECK_ARG(Hq > 0 && Hkv > 0 && Hq % Hkv == 0, "extend: Hq=%d must be a multiple of Hkv=%d",
                Hq, Hkv);
-  B2_CHECK_ARG(B <= 65535, "extend: batch too large");
+  B2_CHECK_ARG(B <= 65535 && Hkv <= 65535, "extend: batch / kv head count too large");
   B2_CHECK_ARG(num_slots > 0 && num_slots < (1ll << 31), "extend: bad num_slots");
   B2_CHECK_ARG(q_stride % 8 == 0 && kv_stride % 8 == 0 && o_stride % 8 == 0,
                "extend: strides must keep rows 16-byte aligned");
