@@ -49,6 +49,9 @@ struct ExtendParams {
   int B, Hq, Hkv, G, num_slots;
   int causal;
   float scale_log2;
+#ifdef EXT_TRACE
+  long long* trace;  // dev-only timeline of CTA (0,0,0): [role 0..2][step 0..31][8]
+#endif
 };
 
 // shared memory carve-up (bytes, from a 1024-aligned base)
@@ -104,6 +107,17 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
   asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
   return r;
 }
+#ifdef EXT_TRACE
+__device__ __forceinline__ long long clk() {
+  long long t;
+  asm volatile("mov.u64 %0, %%clock64;" : "=l"(t)::"memory");
+  return t;
+}
+#define TRACE(role, step, slot)                                                              \
+  if (trace_on && (step) < 32) p.trace[((role) * 32 + (step)) * 8 + (slot)] = clk()
+#else
+#define TRACE(role, step, slot)
+#endif
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -156,6 +170,10 @@ __global__ void __launch_bounds__(kExtThreads, 1)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::kBar + 8 * kBarCount);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#ifdef EXT_TRACE
+  const bool trace_on = p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 &&
+                        (threadIdx.x == 0 || threadIdx.x == 128 || warp == 10);
+#endif
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kExtStages; ++s) {
@@ -251,65 +269,78 @@ __global__ void __launch_bounds__(kExtThreads, 1)
       }
     } else if (warp == 10) {
       // ===================== MMA issuer =====================
+      // One elected thread runs the whole loop (waits, tcgen05.mma, commits).  Every value that
+      // feeds a descriptor is made provably warp-uniform (shuffle broadcast) so the compiler keeps
+      // descriptors in uniform registers instead of wrapping each UTCHMMA in an elect/broadcast loop.
       constexpr uint32_t idesc_qk = idesc_f16(kBf16 ? 1 : 0, kExtM, kExtN, 0, 0);
       constexpr uint32_t idesc_pv = idesc_f16(kBf16 ? 1 : 0, kExtM, D, 0, 1);
-      // S_i(j) = Q_i K_j^T  (both operands K-major from smem)
-      auto issue_qk = [&](int i, int j) {
-        if (lane == 0) {
-          const int st = j % kExtStages;
+      const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
+      const uint32_t smem_u = __shfl_sync(0xffffffffu, smem0, 0);
+      const int n0 = __shfl_sync(0xffffffffu, t_n[0], 0), n1 = __shfl_sync(0xffffffffu, t_n[1], 0);
+      const int nt = max(n0, n1);
+      if (elect_one()) {
+        const uint32_t barb = smem_u + S::kBar;
+        // descriptor = constant high word | (address >> 4) in the low 14 bits
+        constexpr uint64_t kDescKMajor = smem_desc_sw128_hi(16, 1024);       // Q, K: K-major
+        constexpr uint64_t kDescVMn = smem_desc_sw128_hi(S::kHalf, 1024);    // V: MN-major
+        auto desc = [](uint64_t hi, uint32_t addr) { return hi | (uint64_t)((addr & 0x3FFFF) >> 4); };
+        // S_i(j) = Q_i K_j^T  (both operands K-major from smem)
+        auto issue_qk = [&](int i, int j) {
+          const uint32_t qa = smem_u + S::kQ + i * S::kTile;
+          const uint32_t ka = smem_u + S::kK + (j % kExtStages) * S::kTile;
 #pragma unroll
           for (int ks = 0; ks < D / 16; ++ks) {
             const uint32_t off = (ks / 4) * S::kHalf + (ks % 4) * 32;
-            const uint64_t a = smem_desc_sw128(smem0 + S::kQ + i * S::kTile + off, 16, 1024);
-            const uint64_t bd = smem_desc_sw128(smem0 + S::kK + st * S::kTile + off, 16, 1024);
-            umma_ss(tmem + kColS + i * kExtN, a, bd, idesc_qk, ks > 0 ? 1u : 0u);
+            umma_ss(tmem_u + kColS + i * kExtN, desc(kDescKMajor, qa + off), desc(kDescKMajor, ka + off),
+                    idesc_qk, ks > 0 ? 1u : 0u);
           }
-          umma_commit(bar(kBarSFull + i));
-        }
-        __syncwarp();
-      };
-      // O_i (+)= P_i(j) V_j  (A = bf16 P in the S_i columns of TMEM, B = V MN-major from smem)
-      auto issue_pv = [&](int i, int j) {
-        if (lane == 0) {
-          const int st = j % kExtStages;
+          umma_commit(barb + 8u * (kBarSFull + i));
+        };
+        // O_i (+)= P_i(j) V_j  (A = bf16 P in the S_i columns of TMEM, B = V MN-major from smem)
+        auto issue_pv = [&](int i, int j, int n_i) {
+          const uint32_t va = smem_u + S::kV + (j % kExtStages) * S::kTile;
 #pragma unroll
           for (int ks = 0; ks < kExtN / 16; ++ks) {
             // 16 keys per step = 8 packed TMEM columns of A; 2 KB down the V tile; d-halves 16 KB apart
-            const uint64_t bd = smem_desc_sw128(smem0 + S::kV + st * S::kTile + ks * 2048, S::kHalf, 1024);
-            umma_ts(tmem + kColO + i * 128, tmem + kColS + i * kExtN + ks * 8, bd, idesc_pv,
-                    (j > 0 || ks > 0) ? 1u : 0u);
+            umma_ts(tmem_u + kColO + i * 128, tmem_u + kColS + i * kExtN + ks * 8,
+                    desc(kDescVMn, va + ks * 2048), idesc_pv, (j > 0 || ks > 0) ? 1u : 0u);
           }
-          if (j == t_n[i] - 1) umma_commit(bar(kBarOFinal + i));
+          if (j == n_i - 1) umma_commit(barb + 8u * (kBarOFinal + i));
+        };
+        mbar_wait(barb + 8u * (kBarQ + 0), 0);
+        if (n1 > 0) mbar_wait(barb + 8u * (kBarQ + 1), 0);
+        mbar_wait(barb + 8u * (kBarKFull + 0), 0);
+        tc_fence_after();
+        issue_qk(0, 0);
+        if (n1 > 0) issue_qk(1, 0);
+        umma_commit(barb + 8u * (kBarKEmpty + 0));
+        for (int j = 0; j < nt; ++j) {
+          const int st = j % kExtStages, st1 = (j + 1) % kExtStages;
+          mbar_wait(barb + 8u * (kBarVFull + st), (j / kExtStages) & 1);
+          if (j + 1 < nt) mbar_wait(barb + 8u * (kBarKFull + st1), ((j + 1) / kExtStages) & 1);
+          if (j < n0) {
+            TRACE(2, j, 0);
+            mbar_wait(barb + 8u * (kBarPFull + 0), j & 1);
+            tc_fence_after();
+            TRACE(2, j, 1);
+            issue_pv(0, j, n0);
+            if (j + 1 < n0) issue_qk(0, j + 1);
+            TRACE(2, j, 2);
+          }
+          if (j < n1) {
+            TRACE(2, j, 3);
+            mbar_wait(barb + 8u * (kBarPFull + 1), j & 1);
+            tc_fence_after();
+            TRACE(2, j, 4);
+            issue_pv(1, j, n1);
+            if (j + 1 < n1) issue_qk(1, j + 1);
+            TRACE(2, j, 5);
+          }
+          umma_commit(barb + 8u * (kBarVEmpty + st));
+          if (j + 1 < nt) umma_commit(barb + 8u * (kBarKEmpty + st1));
         }
-        __syncwarp();
-      };
-#pragma unroll
-      for (int i = 0; i < 2; ++i)
-        if (t_n[i] > 0) mbar_wait(bar(kBarQ + i), 0);
-      mbar_wait(bar(kBarKFull + 0), 0);
-      tc_fence_after();
-#pragma unroll
-      for (int i = 0; i < 2; ++i)
-        if (t_n[i] > 0) issue_qk(i, 0);
-      if (lane == 0) umma_commit(bar(kBarKEmpty + 0));
-      for (int j = 0; j < ntiles; ++j) {
-        const int st = j % kExtStages, st1 = (j + 1) % kExtStages;
-        mbar_wait(bar(kBarVFull + st), (j / kExtStages) & 1);
-        if (j + 1 < ntiles) mbar_wait(bar(kBarKFull + st1), ((j + 1) / kExtStages) & 1);
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          if (j >= t_n[i]) continue;
-          mbar_wait(bar(kBarPFull + i), j & 1);
-          tc_fence_after();
-          issue_pv(i, j);
-          if (j + 1 < t_n[i]) issue_qk(i, j + 1);
-        }
-        if (lane == 0) {
-          umma_commit(bar(kBarVEmpty + st));
-          if (j + 1 < ntiles) umma_commit(bar(kBarKEmpty + st1));
-        }
-        __syncwarp();
       }
+      __syncwarp();
     }
   } else {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(kRegsSoftmax));
@@ -329,8 +360,10 @@ __global__ void __launch_bounds__(kExtThreads, 1)
       float l_run = 0.f;
       const uint64_t scale2 = f2_pack(p.scale_log2, p.scale_log2);
       for (int j = 0; j < n_i; ++j) {
+        TRACE(i, j, 0);
         mbar_wait(bar(kBarSFull + i), j & 1);
         tc_fence_after();
+        TRACE(i, j, 1);
         float s[kExtN];
 #pragma unroll
         for (int c = 0; c < kExtN / 32; ++c) {
@@ -340,6 +373,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
           for (int e = 0; e < 32; ++e) s[c * 32 + e] = __uint_as_float(v[e]);
         }
         tmem_wait_ld();
+        TRACE(i, j, 2);
         const int n0 = j * kExtN;
         if (n0 + kExtN > limit) {
 #pragma unroll
@@ -379,6 +413,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
             tmem_st32(col_o + c * 32, v);
           }
         }
+        TRACE(i, j, 3);
         // p = exp2(s * scale - m); packed bf16 pairs go back into the first 64 columns of S_i
         const uint64_t negm2 = f2_pack(-m_used, -m_used);
         uint64_t sum2[2] = {0ull, 0ull};
@@ -398,9 +433,11 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         float a0, a1;
         f2_unpack(f2_add(sum2[0], sum2[1]), a0, a1);
         l_run += a0 + a1;
+        TRACE(i, j, 4);
         tmem_wait_st();
         tc_fence_before();
         mbar_arrive(bar(kBarPFull + i));
+        TRACE(i, j, 5);
       }
       // ---- epilogue ----
       mbar_wait(bar(kBarOFinal + i), 0);
@@ -516,8 +553,10 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
                                float sm_scale, void* workspace, int64_t workspace_bytes,
                                void* stream) {
   using namespace b200attn;
+#ifndef EXT_TRACE
   (void)workspace;
   (void)workspace_bytes;
+#endif
   (void)page_size;  // rows are gathered token-granular: any page size, no contiguity assumption
   B2_CHECK_ARG(B >= 0 && total_q_host >= 0 && max_qo_len_host >= 0, "extend: negative size");
   if (B == 0 || total_q_host == 0 || max_qo_len_host == 0) return B200ATTN_OK;
@@ -563,6 +602,9 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
   p.num_slots = (int)num_slots;
   p.causal = causal ? 1 : 0;
   p.scale_log2 = sm_scale * kLog2e;
+#ifdef EXT_TRACE
+  p.trace = workspace_bytes >= 3 * 32 * 8 * 8 ? (long long*)workspace : nullptr;
+#endif
   const int max_qtiles = (max_qo_len_host + kExtM - 1) / kExtM;
   cudaStream_t st = (cudaStream_t)stream;
   if (D == 128)
