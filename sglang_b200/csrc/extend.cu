@@ -10,21 +10,25 @@
 // inside the GQA group): for even G they are two q heads over the same query rows, for odd G
 // (and MHA) a pair may straddle two row tiles.  Each tile has its own length bookkeeping.
 //
-//   warps 0-3   softmax of tile 0      thread = query row = TMEM lane: tcgen05.ld S, masking,
-//   warps 4-7   softmax of tile 1      exp2 online softmax (packed f32x2 FMAs, 3-input max, lazy
-//                                      rescale of O in TMEM when the row max grew by > 2^8), P
-//                                      written back as bf16 INTO the S columns (tcgen05.st), so the
-//                                      second GEMM reads its A operand from TMEM; epilogue O / l.
-//   warp 8      TMA producer: Q tiles + K tiles      Per 128-key step the warp reads the 128 slot
+// K/V arrive in 128-key smem tiles; S/P live in TMEM as two 64-key halves per tile (double buffer),
+// so S(c+1) is computed while the softmax warpgroup still works on chunk c.
+//
+//   warps 0-3   softmax of tile 0      thread = query row = TMEM lane, per 64-key chunk c: tcgen05.ld
+//   warps 4-7   softmax of tile 1      S, masking, exp2 online softmax (packed f32x2 FMAs, 3-input max,
+//                                      40 % of the exp2 on the FMA pipe by polynomial, lazy rescale of O
+//                                      in TMEM when the row max grew by > 2^8), P written back as bf16
+//                                      INTO its S half (tcgen05.st), so the second GEMM reads its A
+//                                      operand from TMEM; epilogue O / l.
+//   warp 8      TMA producer: Q tiles + K tiles      Per 128-key tile the warp reads the 128 slot
 //   warp 9      TMA producer: V tiles                ids and checks that every aligned 16-key group
 //               sits in 16 consecutive pool slots (true under the paged allocator for page_size >=
 //               16): yes -> 16-row tiled TMA boxes; no / ragged tail -> tile::gather4 (4 arbitrary
 //               pool rows per instruction, OOB rows zero-filled).  Same 128B-swizzled layout.
-//   warp 10     MMA issuer (one elected lane).  Order per step j: PV0(j) QK0(j+1) PV1(j) QK1(j+1):
-//               while one softmax warpgroup works on its S the tensor pipe runs the other tile.
-//               P(j) aliases S(j): correctness relies on the tensor pipe executing one thread's
-//               tcgen05.mma in issue order (PV_i(j) reads P before QK_i(j+1) overwrites it).
-//   warp 11     idle (keeps the third warpgroup whole for setmaxnreg).
+//   warp 10/11  MMA issuers of tile 0 / tile 1 (one elected lane each; a single thread sustains only
+//               ~1 UTCHMMA per 45 cycles).  Per chunk c: wait P_i(c); O_i += P_i(c) V_c (4 x M128 N128
+//               K16, A from TMEM); S_i(c+2) = Q_i K_{c+2}^T (8 x M128 N64 K16) into the half P_i(c) just
+//               vacated: correctness relies on the tensor pipe executing one thread's tcgen05.mma in
+//               issue order (PV_i(c) reads P before QK_i(c+2) overwrites it).
 // TMEM (512 columns): S0/P0 [0,128)  S1/P1 [128,256)  O0 [256,384)  O1 [384,512).
 // Algorithmic FLOPs per (request, q head): 4 * D * sum_j (#visible keys of row j).
 #include "sm100.cuh"
@@ -32,7 +36,8 @@
 namespace b200attn {
 
 constexpr int kExtM = 128;        // query rows per tile (two tiles per CTA)
-constexpr int kExtN = 128;        // keys per step
+constexpr int kExtN = 128;        // keys per K/V smem tile (one TMA stage)
+constexpr int kExtC = 64;         // keys per softmax / MMA chunk (S/P double-buffered in two 64-column halves)
 constexpr int kExtStages = 2;     // K and V ring depth
 constexpr int kExtThreads = 384;  // 2 softmax warpgroups + {K producer, V producer, MMA, idle}
 constexpr int kExtBoxRows = 16;   // rows of one tiled K/V TMA box
@@ -72,9 +77,10 @@ enum ExtBar {
   kBarKEmpty = kBarKFull + kExtStages,
   kBarVFull = kBarKEmpty + kExtStages,
   kBarVEmpty = kBarVFull + kExtStages,
-  kBarSFull = kBarVEmpty + kExtStages,  // [2]  MMA -> softmax_i : S_i(j) is in TMEM
-  kBarPFull = kBarSFull + 2,            // [2]  softmax_i -> MMA : P_i(j) is in TMEM, O_i rescaled
-  kBarOFinal = kBarPFull + 2,           // [2]  MMA -> softmax_i : last PV_i done
+  kBarSFull = kBarVEmpty + kExtStages,  // [2 tiles][2 halves]  MMA -> softmax_i : S_i(c) is in TMEM
+  kBarPFull = kBarSFull + 4,            // [2][2]  softmax_i -> MMA : P_i(c) is in TMEM, O_i rescaled
+  kBarPVDone = kBarPFull + 4,           // [2]  MMA -> softmax_i : PV_i(c) done (only waited on before a rescale)
+  kBarOFinal = kBarPVDone + 2,          // [2]  MMA -> softmax_i : last PV_i done
   kBarCount = kBarOFinal + 2
 };
 
@@ -124,6 +130,30 @@ __device__ __forceinline__ float ex2_approx(float x) {
   return y;
 }
 
+// exp2 of two values on the FMA pipe (no MUFU): round-to-nearest range reduction x = j + f,
+// f in [-0.5, 0.5], degree-3 minimax polynomial for 2^f (max relative error 7.5e-5, far below the
+// bf16 rounding of P), then j is added into the exponent field.  x is clamped at -125 so that
+// masked (-inf) and far-below-max scores give ~1e-38 instead of wrapping the exponent.
+constexpr int kEmuPeriod = 5, kEmuCount = 2;  // pairs q with q % 5 < 2 are emulated (40 %)
+__device__ __forceinline__ void exp2_emu2(float x0, float x1, float& p0, float& p1) {
+  constexpr float kMagic = 12582912.f;  // 1.5 * 2^23: low mantissa bits of (x + kMagic) = round(x)
+  x0 = fmaxf(x0, -125.f);
+  x1 = fmaxf(x1, -125.f);
+  const uint64_t x = f2_pack(x0, x1);
+  const uint64_t t = f2_add(x, f2_pack(kMagic, kMagic));
+  const uint64_t fl = f2_add(t, f2_pack(-kMagic, -kMagic));
+  const uint64_t f = f2_fma(fl, f2_pack(-1.f, -1.f), x);
+  uint64_t r = f2_fma(f2_pack(0.055171459913253784f, 0.055171459913253784f), f,
+                      f2_pack(0.2426108568906784f, 0.2426108568906784f));
+  r = f2_fma(r, f, f2_pack(0.6932609677314758f, 0.6932609677314758f));
+  r = f2_fma(r, f, f2_pack(0.9999281167984009f, 0.9999281167984009f));
+  float t0, t1, r0, r1;
+  f2_unpack(t, t0, t1);
+  f2_unpack(r, r0, r1);
+  p0 = __uint_as_float(__float_as_uint(r0) + (__float_as_uint(t0) << 23));
+  p1 = __uint_as_float(__float_as_uint(r1) + (__float_as_uint(t1) << 23));
+}
+
 template <int D, bool kBf16>
 __global__ void __launch_bounds__(kExtThreads, 1)
     extend_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
@@ -148,7 +178,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
   const int kv_beg = p.kv_indptr[b];
   const int L = p.kv_indptr[b + 1] - kv_beg;
   const int prefix = L - E;
-  int t_h[2], t_m0[2], t_rows[2], t_kvend[2], t_n[2];
+  int t_h[2], t_m0[2], t_rows[2], t_kvend[2], t_n[2], t_nc[2];
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
     const int v = 2 * pair + i;
@@ -157,7 +187,8 @@ __global__ void __launch_bounds__(kExtThreads, 1)
     t_m0[i] = (ok ? v / p.G : 0) * kExtM;
     t_rows[i] = ok ? min(kExtM, E - t_m0[i]) : 0;
     t_kvend[i] = !ok ? 0 : (p.causal ? min(L, prefix + t_m0[i] + t_rows[i]) : L);
-    t_n[i] = (t_kvend[i] + kExtN - 1) / kExtN;
+    t_n[i] = (t_kvend[i] + kExtN - 1) / kExtN;   // K/V tiles
+    t_nc[i] = (t_kvend[i] + kExtC - 1) / kExtC;  // 64-key chunks
   }
   const int kv_end = max(t_kvend[0], t_kvend[1]);
   const int ntiles = max(t_n[0], t_n[1]);
@@ -172,20 +203,23 @@ __global__ void __launch_bounds__(kExtThreads, 1)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 #ifdef EXT_TRACE
   const bool trace_on = p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 &&
-                        (threadIdx.x == 0 || threadIdx.x == 128 || warp == 10);
+                        (threadIdx.x == 0 || threadIdx.x == 128 || warp >= 10);
 #endif
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kExtStages; ++s) {
       mbar_init(bar(kBarKFull + s), 1);
-      mbar_init(bar(kBarKEmpty + s), 1);
+      mbar_init(bar(kBarKEmpty + s), t_nc[1] > 0 ? 2 : 1);  // one release per MMA issuer
       mbar_init(bar(kBarVFull + s), 1);
-      mbar_init(bar(kBarVEmpty + s), 1);
+      mbar_init(bar(kBarVEmpty + s), t_nc[1] > 0 ? 2 : 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar(kBarQ + i), 1);
-      mbar_init(bar(kBarSFull + i), 1);
-      mbar_init(bar(kBarPFull + i), 128);
+      for (int hb = 0; hb < 2; ++hb) {
+        mbar_init(bar(kBarSFull + i * 2 + hb), 1);
+        mbar_init(bar(kBarPFull + i * 2 + hb), 128);
+      }
+      mbar_init(bar(kBarPVDone + i), 1);
       mbar_init(bar(kBarOFinal + i), 1);
     }
     mbar_fence_init();
@@ -267,77 +301,74 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         }
         load_slots(j + 1);
       }
-    } else if (warp == 10) {
-      // ===================== MMA issuer =====================
-      // One elected thread runs the whole loop (waits, tcgen05.mma, commits).  Every value that
-      // feeds a descriptor is made provably warp-uniform (shuffle broadcast) so the compiler keeps
-      // descriptors in uniform registers instead of wrapping each UTCHMMA in an elect/broadcast loop.
-      constexpr uint32_t idesc_qk = idesc_f16(kBf16 ? 1 : 0, kExtM, kExtN, 0, 0);
+    } else {
+      // ===================== MMA issuers (warp 10: tile 0, warp 11: tile 1) =====================
+      // One elected thread per tile runs the whole loop (waits, tcgen05.mma, commits): a single thread
+      // sustains only one UTCHMMA per ~45 cycles, so each tile gets its own issuing thread.  Every
+      // value that feeds a descriptor is made provably warp-uniform (shuffle broadcast) so the compiler
+      // keeps descriptors in uniform registers instead of wrapping each UTCHMMA in an elect loop.
+      constexpr uint32_t idesc_qk = idesc_f16(kBf16 ? 1 : 0, kExtM, kExtC, 0, 0);
       constexpr uint32_t idesc_pv = idesc_f16(kBf16 ? 1 : 0, kExtM, D, 0, 1);
+      const int i = __shfl_sync(0xffffffffu, warp - 10, 0);
       const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
       const uint32_t smem_u = __shfl_sync(0xffffffffu, smem0, 0);
-      const int n0 = __shfl_sync(0xffffffffu, t_n[0], 0), n1 = __shfl_sync(0xffffffffu, t_n[1], 0);
-      const int nt = max(n0, n1);
-      if (elect_one()) {
+      const int nc_i = __shfl_sync(0xffffffffu, t_nc[i], 0);
+      const int nc = __shfl_sync(0xffffffffu, max(t_nc[0], t_nc[1]), 0);
+      if (nc_i > 0 && elect_one()) {
         const uint32_t barb = smem_u + S::kBar;
         // descriptor = constant high word | (address >> 4) in the low 14 bits
         constexpr uint64_t kDescKMajor = smem_desc_sw128_hi(16, 1024);       // Q, K: K-major
         constexpr uint64_t kDescVMn = smem_desc_sw128_hi(S::kHalf, 1024);    // V: MN-major
         auto desc = [](uint64_t hi, uint32_t addr) { return hi | (uint64_t)((addr & 0x3FFFF) >> 4); };
-        // S_i(j) = Q_i K_j^T  (both operands K-major from smem)
-        auto issue_qk = [&](int i, int j) {
-          const uint32_t qa = smem_u + S::kQ + i * S::kTile;
-          const uint32_t ka = smem_u + S::kK + (j % kExtStages) * S::kTile;
+        const uint32_t qa = smem_u + S::kQ + i * S::kTile;
+        const uint32_t ts = tmem_u + kColS + i * 128, to = tmem_u + kColO + i * 128;
+        // S_i[c & 1] = Q_i K_c^T over the 64 keys of chunk c (both operands K-major from smem)
+        auto issue_qk = [&](int c) {
+          const uint32_t ka = smem_u + S::kK + ((c >> 1) % kExtStages) * S::kTile + (c & 1) * (kExtC * 128);
 #pragma unroll
           for (int ks = 0; ks < D / 16; ++ks) {
             const uint32_t off = (ks / 4) * S::kHalf + (ks % 4) * 32;
-            umma_ss(tmem_u + kColS + i * kExtN, desc(kDescKMajor, qa + off), desc(kDescKMajor, ka + off),
-                    idesc_qk, ks > 0 ? 1u : 0u);
+            umma_ss(ts + (c & 1) * kExtC, desc(kDescKMajor, qa + off), desc(kDescKMajor, ka + off), idesc_qk,
+                    ks > 0 ? 1u : 0u);
           }
-          umma_commit(barb + 8u * (kBarSFull + i));
+          umma_commit(barb + 8u * (kBarSFull + i * 2 + (c & 1)));
         };
-        // O_i (+)= P_i(j) V_j  (A = bf16 P in the S_i columns of TMEM, B = V MN-major from smem)
-        auto issue_pv = [&](int i, int j, int n_i) {
-          const uint32_t va = smem_u + S::kV + (j % kExtStages) * S::kTile;
+        // O_i (+)= P_i(c) V_c  (A = bf16 P in the S_i[c & 1] columns of TMEM, B = V MN-major from smem)
+        auto issue_pv = [&](int c) {
+          const uint32_t va = smem_u + S::kV + ((c >> 1) % kExtStages) * S::kTile + (c & 1) * (kExtC * 128);
 #pragma unroll
-          for (int ks = 0; ks < kExtN / 16; ++ks) {
+          for (int ks = 0; ks < kExtC / 16; ++ks) {
             // 16 keys per step = 8 packed TMEM columns of A; 2 KB down the V tile; d-halves 16 KB apart
-            umma_ts(tmem_u + kColO + i * 128, tmem_u + kColS + i * kExtN + ks * 8,
-                    desc(kDescVMn, va + ks * 2048), idesc_pv, (j > 0 || ks > 0) ? 1u : 0u);
+            umma_ts(to, ts + (c & 1) * kExtC + ks * 8, desc(kDescVMn, va + ks * 2048), idesc_pv,
+                    (c > 0 || ks > 0) ? 1u : 0u);
           }
-          if (j == n_i - 1) umma_commit(barb + 8u * (kBarOFinal + i));
+          umma_commit(barb + 8u * (kBarPVDone + i));
+          if (c == nc_i - 1) umma_commit(barb + 8u * (kBarOFinal + i));
         };
-        mbar_wait(barb + 8u * (kBarQ + 0), 0);
-        if (n1 > 0) mbar_wait(barb + 8u * (kBarQ + 1), 0);
+        mbar_wait(barb + 8u * (kBarQ + i), 0);
         mbar_wait(barb + 8u * (kBarKFull + 0), 0);
         tc_fence_after();
-        issue_qk(0, 0);
-        if (n1 > 0) issue_qk(1, 0);
+        issue_qk(0);
+        if (nc_i > 1) issue_qk(1);
         umma_commit(barb + 8u * (kBarKEmpty + 0));
-        for (int j = 0; j < nt; ++j) {
-          const int st = j % kExtStages, st1 = (j + 1) % kExtStages;
-          mbar_wait(barb + 8u * (kBarVFull + st), (j / kExtStages) & 1);
-          if (j + 1 < nt) mbar_wait(barb + 8u * (kBarKFull + st1), ((j + 1) / kExtStages) & 1);
-          if (j < n0) {
-            TRACE(2, j, 0);
-            mbar_wait(barb + 8u * (kBarPFull + 0), j & 1);
-            tc_fence_after();
-            TRACE(2, j, 1);
-            issue_pv(0, j, n0);
-            if (j + 1 < n0) issue_qk(0, j + 1);
-            TRACE(2, j, 2);
+        // loops over the CTA's chunk count so that both issuers release every K/V stage
+        for (int c = 0; c < nc; ++c) {
+          const int t = c >> 1, st = t % kExtStages, st1 = (t + 1) % kExtStages;
+          if ((c & 1) == 0) {
+            mbar_wait(barb + 8u * (kBarVFull + st), (t / kExtStages) & 1);
+            if (c + 2 < nc) mbar_wait(barb + 8u * (kBarKFull + st1), ((t + 1) / kExtStages) & 1);
           }
-          if (j < n1) {
-            TRACE(2, j, 3);
-            mbar_wait(barb + 8u * (kBarPFull + 1), j & 1);
+          if (c < nc_i) {
+            TRACE(2, c, 3 * i + 0);
+            mbar_wait(barb + 8u * (kBarPFull + i * 2 + (c & 1)), (c >> 1) & 1);
             tc_fence_after();
-            TRACE(2, j, 4);
-            issue_pv(1, j, n1);
-            if (j + 1 < n1) issue_qk(1, j + 1);
-            TRACE(2, j, 5);
+            TRACE(2, c, 3 * i + 1);
+            issue_pv(c);
+            if (c + 2 < nc_i) issue_qk(c + 2);
+            TRACE(2, c, 3 * i + 2);
           }
-          umma_commit(barb + 8u * (kBarVEmpty + st));
-          if (j + 1 < nt) umma_commit(barb + 8u * (kBarKEmpty + st1));
+          if ((c & 1) == 1 || c == nc - 1) umma_commit(barb + 8u * (kBarVEmpty + st));
+          if ((c & 1) == 1 && c + 1 < nc) umma_commit(barb + 8u * (kBarKEmpty + st1));
         }
       }
       __syncwarp();
@@ -348,10 +379,10 @@ __global__ void __launch_bounds__(kExtThreads, 1)
     using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
     const int i = warp >> 2;           // tile of this warpgroup
     const int row = threadIdx.x & 127;  // == TMEM lane
-    const int n_i = t_n[i];
-    if (n_i > 0) {
+    const int nc_i = t_nc[i];
+    if (nc_i > 0) {
       const uint32_t lane_addr = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-      const uint32_t col_s = lane_addr + kColS + i * kExtN, col_o = lane_addr + kColO + i * 128;
+      const uint32_t col_s = lane_addr + kColS + i * 128, col_o = lane_addr + kColO + i * 128;
       const int m0 = t_m0[i];
       // keys visible to this row: [0, limit)
       int limit = p.causal ? min(L, prefix + m0 + row + 1) : L;
@@ -359,33 +390,34 @@ __global__ void __launch_bounds__(kExtThreads, 1)
       float m_used = -INFINITY;  // reference max (log2 domain) the running sums are expressed in
       float l_run = 0.f;
       const uint64_t scale2 = f2_pack(p.scale_log2, p.scale_log2);
-      for (int j = 0; j < n_i; ++j) {
-        TRACE(i, j, 0);
-        mbar_wait(bar(kBarSFull + i), j & 1);
+      for (int c = 0; c < nc_i; ++c) {
+        const uint32_t col_c = col_s + (c & 1) * kExtC;  // S/P half of this chunk
+        TRACE(i, c, 0);
+        mbar_wait(bar(kBarSFull + i * 2 + (c & 1)), (c >> 1) & 1);
         tc_fence_after();
-        TRACE(i, j, 1);
-        float s[kExtN];
+        TRACE(i, c, 1);
+        float s[kExtC];
 #pragma unroll
-        for (int c = 0; c < kExtN / 32; ++c) {
+        for (int q = 0; q < kExtC / 32; ++q) {
           uint32_t v[32];
-          tmem_ld32(col_s + c * 32, v);
+          tmem_ld32(col_c + q * 32, v);
 #pragma unroll
-          for (int e = 0; e < 32; ++e) s[c * 32 + e] = __uint_as_float(v[e]);
+          for (int e = 0; e < 32; ++e) s[q * 32 + e] = __uint_as_float(v[e]);
         }
         tmem_wait_ld();
-        TRACE(i, j, 2);
-        const int n0 = j * kExtN;
-        if (n0 + kExtN > limit) {
+        TRACE(i, c, 2);
+        const int n0 = c * kExtC;
+        if (n0 + kExtC > limit) {
 #pragma unroll
-          for (int e = 0; e < kExtN; ++e)
+          for (int e = 0; e < kExtC; ++e)
             if (n0 + e >= limit) s[e] = -INFINITY;
         }
         float mx4[4] = {s[0], s[1], s[2], s[3]};
 #pragma unroll
-        for (int e = 4; e < kExtN; e += 8) {
+        for (int e = 4; e < kExtC; e += 8) {
           mx4[0] = fmax3(mx4[0], s[e], s[e + 1]);
           mx4[1] = fmax3(mx4[1], s[e + 2], s[e + 3]);
-          if (e + 4 < kExtN) {
+          if (e + 4 < kExtC) {
             mx4[2] = fmax3(mx4[2], s[e + 4], s[e + 5]);
             mx4[3] = fmax3(mx4[3], s[e + 6], s[e + 7]);
           }
@@ -394,50 +426,54 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         float alpha = 1.f;
         bool rescale = false;
         if (m_used == -INFINITY) {
-          m_used = (mx == -INFINITY) ? 0.f : mx;  // j == 0 (limit >= 1 => finite)
+          m_used = (mx == -INFINITY) ? 0.f : mx;  // c == 0 (limit >= 1 => finite)
         } else if (mx > m_used + kRescaleThreshold) {
           alpha = ex2_approx(m_used - mx);
           m_used = mx;
           rescale = true;
         }
-        // S_i(j) landed => PV_i(j-1) has completed (commit order), so O_i is quiescent here.
         if (__any_sync(0xffffffffu, rescale)) {
+          // rare: O_i must be quiescent, i.e. PV_i(c-1) (possibly still in flight) has completed
+          mbar_wait(bar(kBarPVDone + i), (c - 1) & 1);
+          tc_fence_after();
           l_run *= alpha;
 #pragma unroll
-          for (int c = 0; c < D / 32; ++c) {
+          for (int q = 0; q < D / 32; ++q) {
             uint32_t v[32];
-            tmem_ld32(col_o + c * 32, v);
+            tmem_ld32(col_o + q * 32, v);
             tmem_wait_ld();
 #pragma unroll
             for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(__uint_as_float(v[e]) * alpha);
-            tmem_st32(col_o + c * 32, v);
+            tmem_st32(col_o + q * 32, v);
           }
         }
-        TRACE(i, j, 3);
-        // p = exp2(s * scale - m); packed bf16 pairs go back into the first 64 columns of S_i
+        TRACE(i, c, 3);
+        // p = exp2(s * scale - m); packed bf16 pairs go back into the first 32 columns of this S half
         const uint64_t negm2 = f2_pack(-m_used, -m_used);
         uint64_t sum2[2] = {0ull, 0ull};
+        uint32_t pk[32];
 #pragma unroll
-        for (int c = 0; c < kExtN / 64; ++c) {
-          uint32_t pk[32];
-#pragma unroll
-          for (int e = 0; e < 64; e += 2) {
-            float x0, x1;
-            f2_unpack(f2_fma(f2_pack(s[c * 64 + e], s[c * 64 + e + 1]), scale2, negm2), x0, x1);
-            const float p0 = ex2_approx(x0), p1 = ex2_approx(x1);
-            sum2[(e >> 1) & 1] = f2_add(sum2[(e >> 1) & 1], f2_pack(p0, p1));
-            pk[e >> 1] = pack2<kBf16>(p0, p1);
+        for (int e = 0; e < kExtC; e += 2) {
+          float x0, x1, p0, p1;
+          f2_unpack(f2_fma(f2_pack(s[e], s[e + 1]), scale2, negm2), x0, x1);
+          if (((e >> 1) % kEmuPeriod) < kEmuCount) {
+            exp2_emu2(x0, x1, p0, p1);  // FMA-pipe polynomial: takes load off the 16-lane MUFU
+          } else {
+            p0 = ex2_approx(x0);
+            p1 = ex2_approx(x1);
           }
-          tmem_st32(col_s + c * 32, pk);
+          sum2[(e >> 1) & 1] = f2_add(sum2[(e >> 1) & 1], f2_pack(p0, p1));
+          pk[e >> 1] = pack2<kBf16>(p0, p1);
         }
+        tmem_st32(col_c, pk);
         float a0, a1;
         f2_unpack(f2_add(sum2[0], sum2[1]), a0, a1);
         l_run += a0 + a1;
-        TRACE(i, j, 4);
+        TRACE(i, c, 4);
         tmem_wait_st();
         tc_fence_before();
-        mbar_arrive(bar(kBarPFull + i));
-        TRACE(i, j, 5);
+        mbar_arrive(bar(kBarPFull + i * 2 + (c & 1)));
+        TRACE(i, c, 5);
       }
       // ---- epilogue ----
       mbar_wait(bar(kBarOFinal + i), 0);
