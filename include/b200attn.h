@@ -153,6 +153,10 @@ int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
  * oracle, torch_native_backend.py:298-301,139-141).  With E = #q rows and
  * L = #keys, query j sits at absolute position L - E + j and attends keys
  * 0..L-E+j when `causal`, else all L keys (ENCODER_ONLY / bidirectional).
+ * `causal` is a bit field: bit 0 = causal mask (B200ATTN_EXT_CAUSAL); bit 1 =
+ * skip requests with exactly one query row (B200ATTN_EXT_SKIP_SINGLE): the
+ * running-decode rows of a MIXED batch (schedule_batch.py:2758-2788), which the
+ * caller sends through b200attn_decode (q_rows / req_ids) instead.
  *
  * The QK^T and PV contractions run on tcgen05 tensor cores with TMEM
  * accumulators; `page_size` > 1 promises the paged-allocator invariant
@@ -161,6 +165,9 @@ int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
  * `lse` nullable float[T*Hq] natural log.  `max_qo_len_host` / `total_q_host`
  * are host-side upper bounds used only to size the grid (graph-safe).
  * -------------------------------------------------------------------------- */
+#define B200ATTN_EXT_CAUSAL 1
+#define B200ATTN_EXT_SKIP_SINGLE 2
+
 int64_t b200attn_extend_workspace_bytes(int32_t B, int64_t total_q, int32_t Hq);
 
 int b200attn_extend(const void* q, int64_t q_stride, const void* k_cache,

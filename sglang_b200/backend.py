@@ -58,6 +58,12 @@ class ForwardMetadata:
     min_chunk: int = 256
     workspace: Optional[torch.Tensor] = None
     batch_size: int = 0
+    # MIXED batches: requests with extend_len == 1 (running decodes, schedule_batch.py:2758-2788)
+    # are routed to the HBM-bound decode kernel instead of a 128-row tensor-core tile
+    dec_q_rows: Optional[torch.Tensor] = None   # int32 [num_dec] row of q/o
+    dec_req_ids: Optional[torch.Tensor] = None  # int32 [num_dec] request index (kv_indptr entry)
+    num_dec: int = 0
+    dec_max_kv_len: int = 0
 
 
 def _attn_type_value(layer) -> str:
@@ -180,10 +186,23 @@ class B200AttnBackend(_Base):
             max_ext, tot_ext = max(ext_cpu), sum(ext_cpu)
         else:  # gpu-only mode: one sync, eager path only
             max_ext, tot_ext = int(fb.extend_seq_lens.max()), int(fb.extend_seq_lens.sum())
-        self.forward_metadata = ForwardMetadata(
+        md = ForwardMetadata(
             kv_indptr=kv_indptr, kv_indices=kv_indices, qo_indptr=qo_indptr, batch_size=B,
             cache_seqlens_int32=fb.seq_lens.to(torch.int32), page_table=self._page_table(fb, B),
-            max_extend_len=int(max_ext), num_extend_tokens=int(tot_ext))
+            max_extend_len=int(max_ext), num_extend_tokens=int(tot_ext), min_chunk=self.MIN_CHUNK)
+        if ext_cpu is not None and 1 in ext_cpu:
+            rows, reqs, off = [], [], 0
+            for b, e in enumerate(ext_cpu):
+                if e == 1:
+                    rows.append(off)
+                    reqs.append(b)
+                off += e
+            both = torch.tensor([rows, reqs], dtype=torch.int32).pin_memory().to(dev, non_blocking=True)
+            md.dec_q_rows, md.dec_req_ids, md.num_dec = both[0], both[1], len(rows)
+            md.max_extend_len = max([e for e in ext_cpu if e != 1], default=0)
+            pre_cpu = getattr(fb, "extend_prefix_lens_cpu", None)
+            md.dec_max_kv_len = (max(pre_cpu[b] for b in reqs) + 1) if pre_cpu is not None else self.max_context_len
+        self.forward_metadata = md
 
     # --- CUDA-graph hooks (base_attn_backend.py:73-107,159-197; triton_backend.py:1014-1115)
     def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int, *, num_q_heads: Optional[int] = None,
@@ -280,10 +299,20 @@ class B200AttnBackend(_Base):
         causal = not (getattr(layer, "is_cross_attention", False) or _attn_type_value(layer) == "encoder_only")
         kbuf, vbuf = self.token_to_kv_pool.get_kv_buffer(layer.layer_id)
         B = md.batch_size
-        ws = self._workspace(ops.extend_workspace_bytes(B, q2.shape[0], Hq))
-        ops.extend_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.qo_indptr, md.kv_indptr,
-                             md.kv_indices, layer.scaling, causal=causal, page_size=self.page_size,
-                             max_qo_len=md.max_extend_len, total_q=md.num_extend_tokens, workspace=ws)
+        if md.max_extend_len > 0:
+            ws = self._workspace(ops.extend_workspace_bytes(B, q2.shape[0], Hq))
+            ops.extend_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.qo_indptr, md.kv_indptr,
+                                 md.kv_indices, layer.scaling, causal=causal, page_size=self.page_size,
+                                 max_qo_len=md.max_extend_len, total_q=md.num_extend_tokens, workspace=ws,
+                                 skip_single_rows=md.num_dec > 0)
+        if md.num_dec > 0:  # a single query row sees all of its keys, causal or not
+            Hkv = layer.tp_k_head_num
+            ms = ops.pick_max_splits(md.num_dec, Hkv, Hq // Hkv, md.dec_max_kv_len, md.min_chunk,
+                                     num_sms=self.num_sms)
+            ws = self._workspace(ops.decode_workspace_bytes(md.num_dec, Hq, D, ms))
+            ops.decode_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.kv_indptr, md.kv_indices,
+                                 layer.scaling, max_splits=ms, min_chunk=md.min_chunk, workspace=ws,
+                                 q_rows=md.dec_q_rows, req_ids=md.dec_req_ids, num_items=md.num_dec)
         return o
 
 

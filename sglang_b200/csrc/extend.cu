@@ -53,6 +53,7 @@ struct ExtendParams {
   int64_t o_stride;
   int B, Hq, Hkv, G, num_slots;
   int causal;
+  int skip_single;  // requests with one query row are left to the decode kernel
   float scale_log2;
 #ifdef EXT_TRACE
   long long* trace;  // dev-only timeline of CTA (0,0,0): [role 0..2][step 0..31][8]
@@ -170,6 +171,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
   const int b = blockIdx.z;
   const int q_beg = p.qo_indptr[b];
   const int E = p.qo_indptr[b + 1] - q_beg;
+  if (p.skip_single && E == 1) return;
   const int num_qtiles = (E + kExtM - 1) / kExtM;
   const int nv = num_qtiles * p.G;  // virtual tiles of this (request, kv head)
   const int npairs = (nv + 1) >> 1;
@@ -636,7 +638,8 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
   p.Hkv = Hkv;
   p.G = Hq / Hkv;
   p.num_slots = (int)num_slots;
-  p.causal = causal ? 1 : 0;
+  p.causal = (causal & B200ATTN_EXT_CAUSAL) ? 1 : 0;
+  p.skip_single = (causal & B200ATTN_EXT_SKIP_SINGLE) ? 1 : 0;
   p.scale_log2 = sm_scale * kLog2e;
 #ifdef EXT_TRACE
   p.trace = workspace_bytes >= 3 * 32 * 8 * 8 ? (long long*)workspace : nullptr;

@@ -254,12 +254,15 @@ def extend_attention(
     total_q: Optional[int] = None,
     workspace: Optional[torch.Tensor] = None,
     lse: Optional[torch.Tensor] = None,
+    skip_single_rows: bool = False,
 ) -> torch.Tensor:
     """Ragged prefix+extend attention: ``q [T,Hq,D]`` -> ``o [T,Hq,D]``.
 
     Mirrors ``extend_attention_fwd_unified`` (python/sglang/kernels/ops/attention/
     extend_attention.py:963-1410): one KV source (the pool) indexed by
     ``kv_indices`` over prefix + new tokens; causal by absolute position.
+    ``skip_single_rows`` leaves requests with one query row untouched (MIXED batches:
+    the caller runs them through ``decode_attention`` with ``q_rows`` / ``req_ids``).
     """
     _require_cuda(q, k_cache, v_cache, o, qo_indptr, kv_indptr, kv_indices, workspace, lse)
     if q.dim() != 3 or k_cache.dim() != 3:
@@ -283,7 +286,8 @@ def extend_attention(
         min(k_cache.shape[0], v_cache.shape[0]), o.data_ptr(), o.stride(0), _ptr(lse),
         qo_indptr.data_ptr(), kv_indptr.data_ptr(), kv_indices.data_ptr(), B,
         T if total_q is None else total_q, max_qo_len, Hq, Hkv, D, page_size, _fdtype(q),
-        1 if causal else 0, float(sm_scale), _ptr(workspace), ws_bytes, _stream(),
+        (1 if causal else 0) | (2 if skip_single_rows else 0), float(sm_scale), _ptr(workspace), ws_bytes,
+        _stream(),
     )
     check(rc, "b200attn_extend")
     return o

@@ -137,3 +137,56 @@ def test_backend_cuda_graph_decode_replay():
     check([1, 900, 17, 16, 333, 640, 2, 45], 6)
     md = backend.forward_metadata
     assert int(md.kv_indptr[0]) == 0 and bool((md.kv_indptr[1:B + 1] >= md.kv_indptr[:B]).all())
+
+
+def _extend_fb(sc, backend, mode):
+    B = len(sc.seq_lens)
+    return ForwardBatch(forward_mode=mode, batch_size=B, req_pool_indices=sc.req_pool_indices.to(DEV),
+                        seq_lens=torch.tensor(sc.seq_lens, dtype=torch.int64, device=DEV),
+                        out_cache_loc=sc.out_cache_loc.to(DEV), seq_lens_sum=sum(sc.seq_lens),
+                        extend_seq_lens=torch.tensor(sc.extend_lens, dtype=torch.int32, device=DEV),
+                        extend_prefix_lens=torch.tensor(sc.prefix_lens, dtype=torch.int32, device=DEV),
+                        extend_seq_lens_cpu=list(sc.extend_lens), extend_prefix_lens_cpu=list(sc.prefix_lens),
+                        attn_backend=backend)
+
+
+@pytest.mark.parametrize("causal", [True, False])
+def test_backend_mixed_routes_single_rows_to_decode(causal):
+    """MIXED = chunked prefill rows + running decodes as extend_len == 1 rows (schedule_batch.py:2758-2788):
+    the backend sends the single rows through the decode kernel (q_rows / req_ids) and the extend kernel skips
+    them; interleaved order and G = 7 (Qwen2.5-VL-7B head layout, BASELINE configs[3] scaled down)."""
+    prefix = [0, 700, 300, 1279, 0, 63]
+    ext = [320, 1, 200, 1, 1, 1]
+    sc = make_scenario(prefix, ext, 28, 4, 128, 16, seed=91)
+    backend, req_pool, kv_pool = _setup(sc, False)
+    layer = RadixAttention(28, 128, sc.scaling, 4, 0,
+                           attn_type=AttentionType.DECODER if causal else AttentionType.ENCODER_ONLY)
+    fb = _extend_fb(sc, backend, ForwardMode.MIXED)
+    backend.init_forward_metadata(fb)
+    md = backend.forward_metadata
+    assert md.num_dec == 4 and md.max_extend_len == 320
+    assert md.dec_q_rows.tolist() == [320, 521, 522, 523] and md.dec_req_ids.tolist() == [1, 3, 4, 5]
+    o = layer(sc.q.to(DEV), sc.k.to(DEV), sc.v.to(DEV), fb)
+    kc, vc = sc.k_cache.clone(), sc.v_cache.clone()
+    oracle.store_kv(kc, vc, sc.out_cache_loc, sc.k, sc.v)
+    assert torch.equal(kv_pool.k_buffer[0].cpu(), kc) and torch.equal(kv_pool.v_buffer[0].cpu(), vc)
+    ref = oracle.attention_fp32(sc.q, kc, vc, sc.req_to_token, sc.req_pool_indices, torch.tensor(sc.seq_lens),
+                                torch.tensor(ext), 28, 4, 128, sc.scaling, causal=causal)
+    assert_close_attn(o, ref, f"mixed routed causal={causal}")
+
+
+def test_backend_extend_all_single_rows():
+    """EXTEND batch in which every request brings one token: nothing left for the tensor-core kernel."""
+    prefix, ext = [5, 130, 0, 64], [1, 1, 1, 1]
+    sc = make_scenario(prefix, ext, 8, 2, 128, 16, seed=92)
+    backend, _, _ = _setup(sc, False)
+    layer = RadixAttention(8, 128, sc.scaling, 2, 0)
+    fb = _extend_fb(sc, backend, ForwardMode.EXTEND)
+    backend.init_forward_metadata(fb)
+    assert backend.forward_metadata.max_extend_len == 0 and backend.forward_metadata.num_dec == 4
+    o = layer(sc.q.to(DEV), sc.k.to(DEV), sc.v.to(DEV), fb)
+    kc, vc = sc.k_cache.clone(), sc.v_cache.clone()
+    oracle.store_kv(kc, vc, sc.out_cache_loc, sc.k, sc.v)
+    ref = oracle.attention_fp32(sc.q, kc, vc, sc.req_to_token, sc.req_pool_indices, torch.tensor(sc.seq_lens),
+                                torch.tensor(ext), 8, 2, 128, sc.scaling, causal=True)
+    assert_close_attn(o, ref, "all-single extend")
