@@ -302,6 +302,23 @@ def run_b200(args, rank, world, local_rank):
 
     # (4) extend leg (configs[2]): 32 requests sharing a 2048-token prefix + 512 new tokens, causal
     ext = run_extend_leg(args, dev, gen, peaks)
+    extra = {}
+    if not args.headline_only:
+        del req_pool, kv_pool, backend, fb, md, kbuf, vbuf
+        torch.cuda.empty_cache()
+        # configs[3]: Qwen2.5-VL-7B LLM side, 16 x (1024 image + 256 text) extend rows + 16 decode rows, MIXED
+        for causal in (True, False):
+            extra["cfg4_mixed_" + ("causal" if causal else "bidirectional")] = run_backend_case(
+                dev, gen, peaks, "qwen2.5-vl-7b MIXED: 16 req x 1280 new tokens + 16 decode rows (prefix 1279), "
+                "Hq 28 / Hkv 4 (BASELINE configs[3])", [0] * 16 + [1279] * 16, [1280] * 16 + [1] * 16, 28, 4, 128,
+                16, causal, "MIXED")
+        # configs[4]: Llama-3.1-70B attention shape, this rank's KV-head shard
+        extra["cfg5_decode"] = run_cfg5_decode(dev, gen, peaks, world)
+        torch.cuda.empty_cache()
+        extra["cfg5_chunked_prefill"] = run_backend_case(
+            dev, gen, peaks, f"llama-3.1-70b chunked prefill shard: prefix 8192 + 8192 new, causal, Hq {64 // world} "
+            f"/ Hkv {max(1, 8 // world)} per GPU of {world} (BASELINE configs[4])", [8192], [8192], 64 // world,
+            max(1, 8 // world), 128, 16, True, "EXTEND")
     clk.__exit__()
     clocks = clk.summary()
 
@@ -329,6 +346,7 @@ def run_b200(args, rank, world, local_rank):
         gpu_launches=launches_per_step * args.steps,
         clocks=clocks,
         extend=ext,
+        other_configs=extra,
         tokens_per_s_attention_only=world * B / (c["layers"] * ms_step * 1e-3),
     )
     print(json.dumps(line), flush=True)
@@ -387,6 +405,89 @@ def run_extend_leg(args, dev, gen, peaks):
                               frac=tf / peaks["tf_burst"], frac_of_2250=tf / 2250.0, peak_source=peaks["src"]))
 
 
+def run_backend_case(dev, gen, peaks, label, prefix_lens, ext_lens, Hq, Hkv, D, page, causal, mode_name,
+                     shared_prefix=0, steps=6, warmup=3):
+    """One ragged extend / MIXED layer-call through B200AttnBackend (store + attention), inputs resident in
+    HBM.  `shared_prefix` leading tokens of every request map to the SAME physical pages (radix hit).
+    FLOPs are algorithmic: 4*D per (q head, query, visible key); rows with extend_len 1 count as bytes."""
+    from sglang_b200 import (AttentionType, B200AttnBackend, ForwardBatch, ForwardMode, MHATokenToKVPool,
+                             RadixAttention, ReqToTokenPool)
+
+    B = len(prefix_lens)
+    seq = [p_ + e for p_, e in zip(prefix_lens, ext_lens)]
+    ctx = -(-max(seq) // page) * page
+    own_pages = [-(-(s - shared_prefix) // page) for s in seq]
+    num_pages = shared_prefix // page + sum(own_pages) + 8
+    perm = (torch.randperm(num_pages - 1, generator=gen) + 1).tolist()
+    shared = [perm.pop() for _ in range(shared_prefix // page)]
+    table = torch.zeros((B + 1, ctx), dtype=torch.int32)
+    offs = torch.arange(page, dtype=torch.int32)
+    for b in range(B):
+        pages = torch.tensor(shared + [perm.pop() for _ in range(own_pages[b])], dtype=torch.int32)
+        row = (pages[:, None] * page + offs[None]).reshape(-1)
+        table[b + 1, :row.numel()] = row[:ctx]
+    req_pool = ReqToTokenPool(B, ctx, dev)
+    req_pool.req_to_token.copy_(table.to(dev))
+    kv_pool = MHATokenToKVPool(num_pages * page - page, page, torch.bfloat16, Hkv, D, 1, dev)
+    for buf in (kv_pool.k_buffer[0], kv_pool.v_buffer[0]):
+        buf.normal_(0, 1)
+        buf[:page].zero_()
+    T = sum(ext_lens)
+    q = torch.randn((T, Hq * D), device=dev).to(torch.bfloat16)
+    k = torch.randn((T, Hkv * D), device=dev).to(torch.bfloat16)
+    v = torch.randn((T, Hkv * D), device=dev).to(torch.bfloat16)
+    loc = torch.cat([table[b + 1, prefix_lens[b]:seq[b]] for b in range(B)]).long().to(dev)
+    backend = B200AttnBackend(Runner(dev, req_pool, kv_pool, page))
+    layer = RadixAttention(Hq, D, D ** -0.5, Hkv, 0,
+                           attn_type=AttentionType.DECODER if causal else AttentionType.ENCODER_ONLY)
+    fb = ForwardBatch(forward_mode=ForwardMode[mode_name], batch_size=B,
+                      req_pool_indices=torch.arange(1, B + 1, device=dev),
+                      seq_lens=torch.tensor(seq, dtype=torch.int64, device=dev), out_cache_loc=loc,
+                      seq_lens_sum=sum(seq), extend_seq_lens=torch.tensor(ext_lens, dtype=torch.int32, device=dev),
+                      extend_prefix_lens=torch.tensor(prefix_lens, dtype=torch.int32, device=dev),
+                      extend_seq_lens_cpu=list(ext_lens), extend_prefix_lens_cpu=list(prefix_lens),
+                      attn_backend=backend)
+    backend.init_forward_metadata(fb)
+    ms = time_steps(lambda: layer(q, k, v, fb), steps, warmup) / steps
+    pairs = 0
+    dec_bytes = 0
+    for p_, e in zip(prefix_lens, ext_lens):
+        if e == 1:
+            dec_bytes += (p_ + 1) * Hkv * D * 2 * 2
+        else:
+            pairs += e * p_ + e * (e + 1) // 2 if causal else e * (p_ + e)
+    fl = 4 * D * Hq * pairs
+    tf = fl / (ms * 1e-3) / 1e12
+    return dict(workload=label, ms_per_step=ms, flops=fl, tflops=tf, decode_row_kv_bytes=dec_bytes, tokens=T,
+                frac_of_measured_bf16=tf / peaks["tf_burst"], frac_of_2250=tf / 2250.0)
+
+
+def run_cfg5_decode(dev, gen, peaks, world, steps=10, warmup=3):
+    """BASELINE configs[4](i): Llama-3.1-70B decode, batch 256 x 8192 ctx, this rank's KV-head shard (Hkv 8/N)."""
+    from sglang_b200 import ops
+
+    c = dict(B=256, ctx=8192, Hq=64 // world, Hkv=max(1, 8 // world), D=128, page=16, layers=80)
+    req_pool, kv_pool, host = build_decode_state(c, dev, gen)
+    B, Hq, Hkv, D = c["B"], c["Hq"], c["Hkv"], c["D"]
+    kv_indptr = torch.zeros(B + 1, dtype=torch.int32, device=dev)
+    kv_indices = torch.zeros(B * c["ctx"], dtype=torch.int32, device=dev)
+    ops.build_kv_indices(req_pool.req_to_token, host["req_pool_indices"].to(dev), host["seq_lens"].to(dev), kv_indptr,
+                         kv_indices)
+    q = host["q"].to(dev).view(B, Hq, D)
+    o = torch.empty_like(q)
+    kbuf, vbuf = kv_pool.get_kv_buffer(0)
+    ms_ = ops.pick_max_splits(B, Hkv, Hq // Hkv, c["ctx"], 256)
+    ws = torch.empty(max(ops.decode_workspace_bytes(B, Hq, D, ms_), 16), dtype=torch.uint8, device=dev)
+    f = lambda: ops.decode_attention(q, kbuf, vbuf, o, kv_indptr, kv_indices, D ** -0.5, max_splits=ms_,
+                                     min_chunk=256, workspace=ws)
+    t = time_steps(f, steps, warmup) / steps
+    nbytes = decode_bytes(c) - 2 * 2 * B * Hkv * D * 2
+    gbs = nbytes / (t * 1e-3) / 1e9
+    return dict(workload=f"llama-3.1-70b decode shard: batch 256 x 8192 ctx, Hq {Hq} / Hkv {Hkv} per GPU of {world} "
+                         "(BASELINE configs[4])", kernel_ms=t, bytes=nbytes, gbs=gbs, max_splits=ms_,
+                frac_of_measured_hbm=gbs / peaks["hbm"], frac_of_8tbs=gbs / 8000.0)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -394,6 +495,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--headline-only", action="store_true", help="skip the configs[3]/[4] legs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
