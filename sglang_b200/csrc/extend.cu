@@ -19,6 +19,11 @@
 //                                      in TMEM when the row max grew by > 2^8), P written back as bf16
 //                                      INTO its S half (tcgen05.st), so the second GEMM reads its A
 //                                      operand from TMEM; epilogue O / l.
+// The kernel is persistent: one CTA per SM walks a static round-robin slice of the item list (item =
+// (request, kv head, tile pair), heavy causal pairs first), and every role keeps its pipeline state
+// (K/V ring position, S/P half parity, Q/O phases) across items, so the TMA producers run ahead
+// into the next item while the softmax warps still finish the current one.
+//
 //   warp 8      TMA producer: Q tiles + K tiles      Per 128-key tile the warp reads the 128 slot
 //   warp 9      TMA producer: V tiles                ids and checks that every aligned 16-key group
 //               sits in 16 consecutive pool slots (true under the paged allocator for page_size >=
@@ -43,6 +48,8 @@ constexpr int kExtThreads = 384;  // 2 softmax warpgroups + {K producer, V produ
 constexpr int kExtBoxRows = 16;   // rows of one tiled K/V TMA box
 constexpr float kRescaleThreshold = 8.f;  // log2 domain
 constexpr int kRegsSoftmax = 208, kRegsOther = 80;
+constexpr int kExtMaxItems = 64;  // work items described per round
+constexpr int kExtMaxB = 2048;    // requests per launch (the host slices larger batches)
 
 struct ExtendParams {
   void* o;
@@ -69,7 +76,20 @@ struct ExtSmem {
   static constexpr int kK = kQ + 2 * kTile;
   static constexpr int kV = kK + kExtStages * kTile;
   static constexpr int kBar = kV + kExtStages * kTile;
-  static constexpr int kTotal = kBar + 256;
+  static constexpr int kItems = kBar + 256;                                // ItemDesc[kExtMaxItems]
+  static constexpr int kCum = kItems + kExtMaxItems * 32;                  // int[kExtMaxB + 1] pair prefix sums
+  static constexpr int kTotal = kCum + (kExtMaxB + 1) * 4 + 12;
+};
+
+// One work item = two query tiles of one (request, kv head); built per round into shared memory.
+struct ItemDesc {
+  int q_beg, E, kv_beg, L, kvh, pair, pad0, pad1;
+};
+
+// what every role derives from an ItemDesc
+struct ItemTiles {
+  int h[2], m0[2], rows[2], kvend[2], nc[2];  // per tile: q head, first row, valid rows, keys, 64-key chunks
+  int prefix, kv_end, ntiles, nc_max;
 };
 
 enum ExtBar {
@@ -81,8 +101,9 @@ enum ExtBar {
   kBarSFull = kBarVEmpty + kExtStages,  // [2 tiles][2 halves]  MMA -> softmax_i : S_i(c) is in TMEM
   kBarPFull = kBarSFull + 4,            // [2][2]  softmax_i -> MMA : P_i(c) is in TMEM, O_i rescaled
   kBarPVDone = kBarPFull + 4,           // [2]  MMA -> softmax_i : PV_i(c) done (only waited on before a rescale)
-  kBarOFinal = kBarPVDone + 2,          // [2]  MMA -> softmax_i : last PV_i done
-  kBarCount = kBarOFinal + 2
+  kBarOFinal = kBarPVDone + 2,          // [2]  MMA -> softmax_i : last PV_i of the item done
+  kBarQEmpty = kBarOFinal + 2,          // [2]  MMA -> producer : last QK_i of the item done, Q_i tile is free
+  kBarCount = kBarQEmpty + 2
 };
 
 // ---- packed fp32x2 helpers (FFMA2 / FADD2 / FMNMX3 on sm_100) ----
@@ -155,6 +176,25 @@ __device__ __forceinline__ void exp2_emu2(float x0, float x1, float& p0, float& 
   p1 = __uint_as_float(__float_as_uint(r1) + (__float_as_uint(t1) << 23));
 }
 
+__device__ __forceinline__ void derive_tiles(const ItemDesc& d, const ExtendParams& p, ItemTiles& t) {
+  const int num_qtiles = (d.E + kExtM - 1) / kExtM;
+  const int nv = num_qtiles * p.G;  // virtual tiles v = qtile * G + g of this (request, kv head)
+  t.prefix = d.L - d.E;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int v = 2 * d.pair + i;
+    const bool ok = v < nv;
+    t.h[i] = d.kvh * p.G + (ok ? v % p.G : 0);
+    t.m0[i] = (ok ? v / p.G : 0) * kExtM;
+    t.rows[i] = ok ? min(kExtM, d.E - t.m0[i]) : 0;
+    t.kvend[i] = !ok ? 0 : (p.causal ? min(d.L, t.prefix + t.m0[i] + t.rows[i]) : d.L);
+    t.nc[i] = (t.kvend[i] + kExtC - 1) / kExtC;
+  }
+  t.kv_end = max(t.kvend[0], t.kvend[1]);
+  t.ntiles = (t.kv_end + kExtN - 1) / kExtN;
+  t.nc_max = max(t.nc[0], t.nc[1]);
+}
+
 template <int D, bool kBf16>
 __global__ void __launch_bounds__(kExtThreads, 1)
     extend_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
@@ -166,54 +206,35 @@ __global__ void __launch_bounds__(kExtThreads, 1)
   constexpr uint32_t kTmemCols = 512;
   constexpr uint32_t kColS = 0, kColO = 256;  // + i * 128
 
-  // ---- which two tiles does this CTA own? ----
-  const int kvh = blockIdx.y;
-  const int b = blockIdx.z;
-  const int q_beg = p.qo_indptr[b];
-  const int E = p.qo_indptr[b + 1] - q_beg;
-  if (p.skip_single && E == 1) return;
-  const int num_qtiles = (E + kExtM - 1) / kExtM;
-  const int nv = num_qtiles * p.G;  // virtual tiles of this (request, kv head)
-  const int npairs = (nv + 1) >> 1;
-  if ((int)blockIdx.x >= npairs) return;
-  const int pair = npairs - 1 - blockIdx.x;  // heavy (late) causal tiles first
-  const int kv_beg = p.kv_indptr[b];
-  const int L = p.kv_indptr[b + 1] - kv_beg;
-  const int prefix = L - E;
-  int t_h[2], t_m0[2], t_rows[2], t_kvend[2], t_n[2], t_nc[2];
-#pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const int v = 2 * pair + i;
-    const bool ok = v < nv;
-    t_h[i] = kvh * p.G + (ok ? v % p.G : 0);
-    t_m0[i] = (ok ? v / p.G : 0) * kExtM;
-    t_rows[i] = ok ? min(kExtM, E - t_m0[i]) : 0;
-    t_kvend[i] = !ok ? 0 : (p.causal ? min(L, prefix + t_m0[i] + t_rows[i]) : L);
-    t_n[i] = (t_kvend[i] + kExtN - 1) / kExtN;   // K/V tiles
-    t_nc[i] = (t_kvend[i] + kExtC - 1) / kExtC;  // 64-key chunks
-  }
-  const int kv_end = max(t_kvend[0], t_kvend[1]);
-  const int ntiles = max(t_n[0], t_n[1]);
-
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (smem0 - smem_u32(smem_raw));
   const uint32_t bar0 = smem0 + S::kBar;
   auto bar = [&](int i) { return bar0 + 8u * i; };
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::kBar + 8 * kBarCount);
+  ItemDesc* items = reinterpret_cast<ItemDesc*>(smem + S::kItems);
+  int* cum = reinterpret_cast<int*>(smem + S::kCum);  // cum[b] = tile pairs of requests < b
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 #ifdef EXT_TRACE
-  const bool trace_on = p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 &&
-                        (threadIdx.x == 0 || threadIdx.x == 128 || warp >= 10);
+  const bool trace_on = p.trace != nullptr && blockIdx.x == 0 &&
+                        (threadIdx.x == 0 || threadIdx.x == 128 || (warp >= 10 && lane == 0));
 #endif
 
+#ifdef EXT_TRACE
+  if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+    long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    p.trace[(3 * 32 + 0) * 8 + 0] = clk();
+    p.trace[(3 * 32 + 0) * 8 + 1] = gt;
+  }
+#endif
   if (threadIdx.x == 0) {
     for (int s = 0; s < kExtStages; ++s) {
       mbar_init(bar(kBarKFull + s), 1);
-      mbar_init(bar(kBarKEmpty + s), t_nc[1] > 0 ? 2 : 1);  // one release per MMA issuer
+      mbar_init(bar(kBarKEmpty + s), 2);  // one release per MMA issuer
       mbar_init(bar(kBarVFull + s), 1);
-      mbar_init(bar(kBarVEmpty + s), t_nc[1] > 0 ? 2 : 1);
+      mbar_init(bar(kBarVEmpty + s), 2);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar(kBarQ + i), 1);
@@ -223,6 +244,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
       }
       mbar_init(bar(kBarPVDone + i), 1);
       mbar_init(bar(kBarOFinal + i), 1);
+      mbar_init(bar(kBarQEmpty + i), 1);
     }
     mbar_fence_init();
   }
@@ -236,277 +258,398 @@ __global__ void __launch_bounds__(kExtThreads, 1)
     tma_prefetch_desc(&tm_v);
     tma_prefetch_desc(&tm_vbox);
   }
+  // ---- tile-pair prefix sums over the batch (every CTA builds the same table) ----
+  for (int b = threadIdx.x; b < p.B; b += kExtThreads) {
+    const int E = p.qo_indptr[b + 1] - p.qo_indptr[b];
+    const int nv = ((E + kExtM - 1) / kExtM) * p.G;
+    cum[b + 1] = (E <= 0 || (p.skip_single && E == 1)) ? 0 : (nv + 1) >> 1;
+  }
+  if (threadIdx.x == 0) cum[0] = 0;
+  __syncthreads();
+  if (warp == 0) {
+    int carry = 0;
+    for (int base = 0; base < p.B; base += 32) {
+      int v = (base + lane < p.B) ? cum[base + lane + 1] : 0;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += u;
+      }
+      if (base + lane < p.B) cum[base + lane + 1] = v + carry;
+      carry += __shfl_sync(0xffffffffu, v, 31);
+    }
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  const int total_items = cum[p.B] * p.Hkv;
+  const int n_my = total_items > (int)blockIdx.x
+                       ? (total_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
 
+  // ---- per-role pipeline state, carried across items and rounds ----
+  int kt = 0;              // K/V tiles consumed / produced so far (ring position)
+  int g_my = 0;            // softmax WG i / issuer i: 64-key chunks of tile i so far (S/P half parity, PVDone phase)
+  int nq_my = 0;           // softmax WG i / issuer i: items in which tile i was valid (Q / OFinal phases)
+  int nq_p[2] = {0, 0};    // K producer: same count per tile (Q / QEmpty phases)
+
+  // Role branch outermost (ptxas sizes registers per setmaxnreg region); both sides run the same
+  // round loop and meet at the two barriers of every round.
   if (warp >= 8) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" ::"n"(kRegsOther));
-    if (warp == 8 || warp == 9) {
-      // ===================== TMA producers (warp 8: Q + K, warp 9: V) =====================
-      const bool is_k = (warp == 8);
-      if (is_k && lane == 0) {
+    for (int r0 = 0; r0 < n_my; r0 += kExtMaxItems) {
+      const int n_round = min(kExtMaxItems, n_my - r0);
+      __syncthreads();  // this round's descriptors are in shared memory
+      if (warp == 8 || warp == 9) {
+        // ===================== TMA producers (warp 8: Q + K, warp 9: V) =====================
+        const bool is_k = (warp == 8);
+        const CUtensorMap* tm_g = is_k ? &tm_k : &tm_v;
+        const CUtensorMap* tm_b = is_k ? &tm_kbox : &tm_vbox;
+        const uint32_t tile0 = smem0 + (is_k ? S::kK : S::kV);
+        const int bar_full = is_k ? kBarKFull : kBarVFull, bar_empty = is_k ? kBarKEmpty : kBarVEmpty;
+        for (int it = 0; it < n_round; ++it) {
+          const ItemDesc d = items[it];
+          ItemTiles t;
+          derive_tiles(d, p, t);
+          if (is_k) {
 #pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          if (t_n[i] == 0) continue;
-          mbar_arrive_expect_tx(bar(kBarQ + i), S::kTile);
+            for (int i = 0; i < 2; ++i) {
+              if (t.nc[i] == 0) continue;
+              if (lane == 0) {
+                if (nq_p[i] > 0) mbar_wait(bar(kBarQEmpty + i), (nq_p[i] - 1) & 1);  // previous item's QK_i done
+                mbar_arrive_expect_tx(bar(kBarQ + i), S::kTile);
 #pragma unroll
-          for (int hf = 0; hf < kHalves; ++hf)
-            tma_load_2d(smem0 + S::kQ + i * S::kTile + hf * S::kHalf, &tm_q, bar(kBarQ + i),
-                        t_h[i] * D + hf * 64, q_beg + t_m0[i]);
-        }
-      }
-      const int32_t* idx = p.kv_indices + kv_beg;
-      const int col = kvh * D;
-      const CUtensorMap* tm_g = is_k ? &tm_k : &tm_v;
-      const CUtensorMap* tm_b = is_k ? &tm_kbox : &tm_vbox;
-      const uint32_t tile0 = smem0 + (is_k ? S::kK : S::kV);
-      const int bar_full = is_k ? kBarKFull : kBarVFull, bar_empty = is_k ? kBarKEmpty : kBarVEmpty;
-      int r[4];
-      auto load_slots = [&](int j) {
+                for (int hf = 0; hf < kHalves; ++hf)
+                  tma_load_2d(smem0 + S::kQ + i * S::kTile + hf * S::kHalf, &tm_q, bar(kBarQ + i),
+                              t.h[i] * D + hf * 64, d.q_beg + t.m0[i]);
+              }
+              ++nq_p[i];
+            }
+            __syncwarp();
+          }
+          const int32_t* idx = p.kv_indices + d.kv_beg;
+          const int col = d.kvh * D;
+          int r[4];
+          auto load_slots = [&](int j) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int key = j * kExtN + lane * 4 + i;
-          r[i] = (j < ntiles && key < kv_end) ? __ldg(idx + key) : p.num_slots;  // OOB row -> zeros
-        }
-      };
-      load_slots(0);
-      for (int j = 0; j < ntiles; ++j) {
-        const int st = j % kExtStages;
-        const uint32_t dst = tile0 + st * S::kTile;
-        // every aligned 16-key group in 16 consecutive slots?  (4 lanes x 4 keys per group)
-        const int g0 = __shfl_sync(0xffffffffu, r[0], lane & ~3);
-        bool contig = (r[1] == r[0] + 1) && (r[2] == r[0] + 2) && (r[3] == r[0] + 3) &&
-                      (r[0] == g0 + 4 * (lane & 3));
-        contig = __all_sync(0xffffffffu, contig) && ((j + 1) * kExtN <= kv_end);
-        if (j >= kExtStages) mbar_wait(bar(bar_empty + st), ((j / kExtStages) + 1) & 1);
-        if (lane == 0) mbar_arrive_expect_tx(bar(bar_full + st), S::kTile);
-        __syncwarp();
-        if (contig) {
-          int rows[kExtN / kExtBoxRows];
+            for (int i = 0; i < 4; ++i) {
+              const int key = j * kExtN + lane * 4 + i;
+              r[i] = (j < t.ntiles && key < t.kv_end) ? __ldg(idx + key) : p.num_slots;  // OOB row -> zeros
+            }
+          };
+          load_slots(0);
+          for (int j = 0; j < t.ntiles; ++j, ++kt) {
+            const int st = kt % kExtStages;
+            const uint32_t dst = tile0 + st * S::kTile;
+            // every aligned 16-key group in 16 consecutive slots?  (4 lanes x 4 keys per group)
+            const int g0 = __shfl_sync(0xffffffffu, r[0], lane & ~3);
+            bool contig = (r[1] == r[0] + 1) && (r[2] == r[0] + 2) && (r[3] == r[0] + 3) &&
+                          (r[0] == g0 + 4 * (lane & 3));
+            contig = __all_sync(0xffffffffu, contig) && ((j + 1) * kExtN <= t.kv_end);
+            if (kt >= kExtStages) mbar_wait(bar(bar_empty + st), ((kt / kExtStages) + 1) & 1);
+            if (lane == 0) mbar_arrive_expect_tx(bar(bar_full + st), S::kTile);
+            __syncwarp();
+            if (contig) {
+              int rows[kExtN / kExtBoxRows];
 #pragma unroll
-          for (int g = 0; g < kExtN / kExtBoxRows; ++g) rows[g] = __shfl_sync(0xffffffffu, r[0], g * 4);
-          if (lane == 0) {
+              for (int g = 0; g < kExtN / kExtBoxRows; ++g) rows[g] = __shfl_sync(0xffffffffu, r[0], g * 4);
+              if (lane == 0) {
 #pragma unroll
-            for (int g = 0; g < kExtN / kExtBoxRows; ++g)
+                for (int g = 0; g < kExtN / kExtBoxRows; ++g)
+#pragma unroll
+                  for (int hf = 0; hf < kHalves; ++hf)
+                    tma_load_2d(dst + hf * S::kHalf + g * kExtBoxRows * 128, tm_b, bar(bar_full + st),
+                                col + hf * 64, rows[g]);
+              }
+            } else {
 #pragma unroll
               for (int hf = 0; hf < kHalves; ++hf)
-                tma_load_2d(dst + hf * S::kHalf + g * kExtBoxRows * 128, tm_b, bar(bar_full + st),
-                            col + hf * 64, rows[g]);
+                tma_gather4(dst + hf * S::kHalf + lane * 4 * 128, tm_g, bar(bar_full + st), col + hf * 64,
+                            r[0], r[1], r[2], r[3]);
+            }
+            load_slots(j + 1);
           }
-        } else {
-#pragma unroll
-          for (int hf = 0; hf < kHalves; ++hf)
-            tma_gather4(dst + hf * S::kHalf + lane * 4 * 128, tm_g, bar(bar_full + st), col + hf * 64,
-                        r[0], r[1], r[2], r[3]);
         }
-        load_slots(j + 1);
-      }
-    } else {
-      // ===================== MMA issuers (warp 10: tile 0, warp 11: tile 1) =====================
-      // One elected thread per tile runs the whole loop (waits, tcgen05.mma, commits): a single thread
-      // sustains only one UTCHMMA per ~45 cycles, so each tile gets its own issuing thread.  Every
-      // value that feeds a descriptor is made provably warp-uniform (shuffle broadcast) so the compiler
-      // keeps descriptors in uniform registers instead of wrapping each UTCHMMA in an elect loop.
-      constexpr uint32_t idesc_qk = idesc_f16(kBf16 ? 1 : 0, kExtM, kExtC, 0, 0);
-      constexpr uint32_t idesc_pv = idesc_f16(kBf16 ? 1 : 0, kExtM, D, 0, 1);
-      const int i = __shfl_sync(0xffffffffu, warp - 10, 0);
-      const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
-      const uint32_t smem_u = __shfl_sync(0xffffffffu, smem0, 0);
-      const int nc_i = __shfl_sync(0xffffffffu, t_nc[i], 0);
-      const int nc = __shfl_sync(0xffffffffu, max(t_nc[0], t_nc[1]), 0);
-      if (nc_i > 0 && elect_one()) {
+      } else {
+        // ===================== MMA issuers (warp 10: tile 0, warp 11: tile 1) =====================
+        // One elected thread per tile runs the whole loop (waits, tcgen05.mma, commits): a single thread
+        // sustains only one UTCHMMA per ~45 cycles, so each tile gets its own issuing thread.  Every
+        // value that feeds a descriptor is made provably warp-uniform (shuffle broadcast) so the compiler
+        // keeps descriptors in uniform registers instead of wrapping each UTCHMMA in an elect loop.
+        constexpr uint32_t idesc_qk = idesc_f16(kBf16 ? 1 : 0, kExtM, kExtC, 0, 0);
+        constexpr uint32_t idesc_pv = idesc_f16(kBf16 ? 1 : 0, kExtM, D, 0, 1);
+        const int i = __shfl_sync(0xffffffffu, warp - 10, 0);
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
+        const uint32_t smem_u = __shfl_sync(0xffffffffu, smem0, 0);
         const uint32_t barb = smem_u + S::kBar;
         // descriptor = constant high word | (address >> 4) in the low 14 bits
-        constexpr uint64_t kDescKMajor = smem_desc_sw128_hi(16, 1024);       // Q, K: K-major
-        constexpr uint64_t kDescVMn = smem_desc_sw128_hi(S::kHalf, 1024);    // V: MN-major
+        constexpr uint64_t kDescKMajor = smem_desc_sw128_hi(16, 1024);     // Q, K: K-major
+        constexpr uint64_t kDescVMn = smem_desc_sw128_hi(S::kHalf, 1024);  // V: MN-major
         auto desc = [](uint64_t hi, uint32_t addr) { return hi | (uint64_t)((addr & 0x3FFFF) >> 4); };
         const uint32_t qa = smem_u + S::kQ + i * S::kTile;
         const uint32_t ts = tmem_u + kColS + i * 128, to = tmem_u + kColO + i * 128;
-        // S_i[c & 1] = Q_i K_c^T over the 64 keys of chunk c (both operands K-major from smem)
-        auto issue_qk = [&](int c) {
-          const uint32_t ka = smem_u + S::kK + ((c >> 1) % kExtStages) * S::kTile + (c & 1) * (kExtC * 128);
+        for (int it = 0; it < n_round; ++it) {
+          const ItemDesc d = items[it];
+          ItemTiles t;
+          derive_tiles(d, p, t);
+          const int nc_i = __shfl_sync(0xffffffffu, i == 0 ? t.nc[0] : t.nc[1], 0);
+          const int nc = __shfl_sync(0xffffffffu, t.nc_max, 0);
+          const int ntl = __shfl_sync(0xffffffffu, t.ntiles, 0);
+          const int ktl = __shfl_sync(0xffffffffu, kt, 0);
+          const int g = __shfl_sync(0xffffffffu, g_my, 0);
+          const int nqi = __shfl_sync(0xffffffffu, nq_my, 0);
+          if (elect_one()) {
+            // S_i[(g + c) & 1] = Q_i K_c^T over the 64 keys of chunk c (both operands K-major from smem)
+            auto issue_qk = [&](int c) {
+              const uint32_t ka =
+                  smem_u + S::kK + ((ktl + (c >> 1)) % kExtStages) * S::kTile + (c & 1) * (kExtC * 128);
+              const int hb = (g + c) & 1;
 #pragma unroll
-          for (int ks = 0; ks < D / 16; ++ks) {
-            const uint32_t off = (ks / 4) * S::kHalf + (ks % 4) * 32;
-            umma_ss(ts + (c & 1) * kExtC, desc(kDescKMajor, qa + off), desc(kDescKMajor, ka + off), idesc_qk,
-                    ks > 0 ? 1u : 0u);
-          }
-          umma_commit(barb + 8u * (kBarSFull + i * 2 + (c & 1)));
-        };
-        // O_i (+)= P_i(c) V_c  (A = bf16 P in the S_i[c & 1] columns of TMEM, B = V MN-major from smem)
-        auto issue_pv = [&](int c) {
-          const uint32_t va = smem_u + S::kV + ((c >> 1) % kExtStages) * S::kTile + (c & 1) * (kExtC * 128);
+#ifdef EXT_ABL_NOQK
+              for (int ks = 0; ks < 1; ++ks) {
+#else
+              for (int ks = 0; ks < D / 16; ++ks) {
+#endif
+                const uint32_t off = (ks / 4) * S::kHalf + (ks % 4) * 32;
+                umma_ss(ts + hb * kExtC, desc(kDescKMajor, qa + off), desc(kDescKMajor, ka + off), idesc_qk,
+                        ks > 0 ? 1u : 0u);
+              }
+              umma_commit(barb + 8u * (kBarSFull + i * 2 + hb));
+              if (c == nc_i - 1) umma_commit(barb + 8u * (kBarQEmpty + i));  // Q_i tile is free
+            };
+            // O_i (+)= P_i(c) V_c  (A = bf16 P in its S half of TMEM, B = V MN-major from smem)
+            auto issue_pv = [&](int c) {
+              const uint32_t va =
+                  smem_u + S::kV + ((ktl + (c >> 1)) % kExtStages) * S::kTile + (c & 1) * (kExtC * 128);
+              const int hb = (g + c) & 1;
 #pragma unroll
-          for (int ks = 0; ks < kExtC / 16; ++ks) {
-            // 16 keys per step = 8 packed TMEM columns of A; 2 KB down the V tile; d-halves 16 KB apart
-            umma_ts(to, ts + (c & 1) * kExtC + ks * 8, desc(kDescVMn, va + ks * 2048), idesc_pv,
-                    (c > 0 || ks > 0) ? 1u : 0u);
-          }
-          umma_commit(barb + 8u * (kBarPVDone + i));
-          if (c == nc_i - 1) umma_commit(barb + 8u * (kBarOFinal + i));
-        };
-        mbar_wait(barb + 8u * (kBarQ + i), 0);
-        mbar_wait(barb + 8u * (kBarKFull + 0), 0);
-        tc_fence_after();
-        issue_qk(0);
-        if (nc_i > 1) issue_qk(1);
-        umma_commit(barb + 8u * (kBarKEmpty + 0));
-        // loops over the CTA's chunk count so that both issuers release every K/V stage
-        for (int c = 0; c < nc; ++c) {
-          const int t = c >> 1, st = t % kExtStages, st1 = (t + 1) % kExtStages;
-          if ((c & 1) == 0) {
-            mbar_wait(barb + 8u * (kBarVFull + st), (t / kExtStages) & 1);
-            if (c + 2 < nc) mbar_wait(barb + 8u * (kBarKFull + st1), ((t + 1) / kExtStages) & 1);
-          }
-          if (c < nc_i) {
-            TRACE(2, c, 3 * i + 0);
-            mbar_wait(barb + 8u * (kBarPFull + i * 2 + (c & 1)), (c >> 1) & 1);
+#ifdef EXT_ABL_NOPV
+              for (int ks = 0; ks < 1; ++ks) {
+#else
+              for (int ks = 0; ks < kExtC / 16; ++ks) {
+#endif
+                // 16 keys per step = 8 packed TMEM columns of A; 2 KB down the V tile; d-halves 16 KB apart
+                umma_ts(to, ts + hb * kExtC + ks * 8, desc(kDescVMn, va + ks * 2048), idesc_pv,
+                        (c > 0 || ks > 0) ? 1u : 0u);
+              }
+              umma_commit(barb + 8u * (kBarPVDone + i));
+              if (c == nc_i - 1) umma_commit(barb + 8u * (kBarOFinal + i));
+            };
+            if (nc_i > 0) mbar_wait(barb + 8u * (kBarQ + i), nqi & 1);
+            mbar_wait(barb + 8u * (kBarKFull + ktl % kExtStages), (ktl / kExtStages) & 1);
             tc_fence_after();
-            TRACE(2, c, 3 * i + 1);
-            issue_pv(c);
-            if (c + 2 < nc_i) issue_qk(c + 2);
-            TRACE(2, c, 3 * i + 2);
+            if (nc_i > 0) issue_qk(0);
+            if (nc_i > 1) issue_qk(1);
+            umma_commit(barb + 8u * (kBarKEmpty + ktl % kExtStages));
+            // loops over the ITEM's chunk count so that both issuers release every K/V stage
+            for (int c = 0; c < nc; ++c) {
+              const int tt = ktl + (c >> 1), st = tt % kExtStages, st1 = (tt + 1) % kExtStages;
+              if ((c & 1) == 0) {
+                mbar_wait(barb + 8u * (kBarVFull + st), (tt / kExtStages) & 1);
+                if (c + 2 < nc) mbar_wait(barb + 8u * (kBarKFull + st1), ((tt + 1) / kExtStages) & 1);
+              }
+              if (c < nc_i) {
+                TRACE(2, c, 3 * i + 0);
+                mbar_wait(barb + 8u * (kBarPFull + i * 2 + ((g + c) & 1)), ((g + c) >> 1) & 1);
+                tc_fence_after();
+                TRACE(2, c, 3 * i + 1);
+                issue_pv(c);
+                if (c + 2 < nc_i) issue_qk(c + 2);
+                TRACE(2, c, 3 * i + 2);
+              }
+              if ((c & 1) == 1 || c == nc - 1) umma_commit(barb + 8u * (kBarVEmpty + st));
+              if ((c & 1) == 1 && c + 1 < nc) umma_commit(barb + 8u * (kBarKEmpty + st1));
+            }
           }
-          if ((c & 1) == 1 || c == nc - 1) umma_commit(barb + 8u * (kBarVEmpty + st));
-          if ((c & 1) == 1 && c + 1 < nc) umma_commit(barb + 8u * (kBarKEmpty + st1));
+          __syncwarp();
+          kt += ntl;
+          g_my += nc_i;
+          nq_my += nc_i > 0 ? 1 : 0;
         }
       }
-      __syncwarp();
+      __syncthreads();  // every role is done with this round's descriptors
     }
   } else {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(kRegsSoftmax));
-    // ===================== softmax + epilogue (thread = query row of tile i) =====================
-    using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
-    const int i = warp >> 2;           // tile of this warpgroup
-    const int row = threadIdx.x & 127;  // == TMEM lane
-    const int nc_i = t_nc[i];
-    if (nc_i > 0) {
+    for (int r0 = 0; r0 < n_my; r0 += kExtMaxItems) {
+      const int n_round = min(kExtMaxItems, n_my - r0);
+      // ---- describe this round's items: id -> (request, kv head, pair), heavy pairs first ----
+      if ((int)threadIdx.x < n_round) {
+        const int id = (int)blockIdx.x + (r0 + (int)threadIdx.x) * (int)gridDim.x;
+        int lo = 0, hi = p.B;  // largest b with cum[b] * Hkv <= id
+        while (hi - lo > 1) {
+          const int mid = (lo + hi) >> 1;
+          if (cum[mid] * p.Hkv <= id) lo = mid; else hi = mid;
+        }
+        const int b = lo;
+        const int np = cum[b + 1] - cum[b];
+        const int rem = id - cum[b] * p.Hkv;
+        ItemDesc d;
+        d.q_beg = p.qo_indptr[b];
+        d.E = p.qo_indptr[b + 1] - d.q_beg;
+        d.kv_beg = p.kv_indptr[b];
+        d.L = p.kv_indptr[b + 1] - d.kv_beg;
+        d.kvh = rem / np;
+        d.pair = np - 1 - rem % np;
+        d.pad0 = d.pad1 = 0;
+        items[threadIdx.x] = d;
+      }
+      __syncthreads();
+      // ===================== softmax + epilogue (thread = query row of tile i) =====================
+      using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
+      const int i = warp >> 2;            // tile of this warpgroup
+      const int row = threadIdx.x & 127;  // == TMEM lane
       const uint32_t lane_addr = tmem + ((uint32_t)((warp & 3) * 32) << 16);
       const uint32_t col_s = lane_addr + kColS + i * 128, col_o = lane_addr + kColO + i * 128;
-      const int m0 = t_m0[i];
-      // keys visible to this row: [0, limit)
-      int limit = p.causal ? min(L, prefix + m0 + row + 1) : L;
-      limit = max(1, min(limit, t_kvend[i]));
-      float m_used = -INFINITY;  // reference max (log2 domain) the running sums are expressed in
-      float l_run = 0.f;
       const uint64_t scale2 = f2_pack(p.scale_log2, p.scale_log2);
-      for (int c = 0; c < nc_i; ++c) {
-        const uint32_t col_c = col_s + (c & 1) * kExtC;  // S/P half of this chunk
-        TRACE(i, c, 0);
-        mbar_wait(bar(kBarSFull + i * 2 + (c & 1)), (c >> 1) & 1);
-        tc_fence_after();
-        TRACE(i, c, 1);
-        float s[kExtC];
-#pragma unroll
-        for (int q = 0; q < kExtC / 32; ++q) {
-          uint32_t v[32];
-          tmem_ld32(col_c + q * 32, v);
-#pragma unroll
-          for (int e = 0; e < 32; ++e) s[q * 32 + e] = __uint_as_float(v[e]);
-        }
-        tmem_wait_ld();
-        TRACE(i, c, 2);
-        const int n0 = c * kExtC;
-        if (n0 + kExtC > limit) {
-#pragma unroll
-          for (int e = 0; e < kExtC; ++e)
-            if (n0 + e >= limit) s[e] = -INFINITY;
-        }
-        float mx4[4] = {s[0], s[1], s[2], s[3]};
-#pragma unroll
-        for (int e = 4; e < kExtC; e += 8) {
-          mx4[0] = fmax3(mx4[0], s[e], s[e + 1]);
-          mx4[1] = fmax3(mx4[1], s[e + 2], s[e + 3]);
-          if (e + 4 < kExtC) {
-            mx4[2] = fmax3(mx4[2], s[e + 4], s[e + 5]);
-            mx4[3] = fmax3(mx4[3], s[e + 6], s[e + 7]);
-          }
-        }
-        const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2;
-        float alpha = 1.f;
-        bool rescale = false;
-        if (m_used == -INFINITY) {
-          m_used = (mx == -INFINITY) ? 0.f : mx;  // c == 0 (limit >= 1 => finite)
-        } else if (mx > m_used + kRescaleThreshold) {
-          alpha = ex2_approx(m_used - mx);
-          m_used = mx;
-          rescale = true;
-        }
-        if (__any_sync(0xffffffffu, rescale)) {
-          // rare: O_i must be quiescent, i.e. PV_i(c-1) (possibly still in flight) has completed
-          mbar_wait(bar(kBarPVDone + i), (c - 1) & 1);
+      for (int it = 0; it < n_round; ++it) {
+        const ItemDesc d = items[it];
+        ItemTiles t;
+        derive_tiles(d, p, t);
+        const int nc_i = i == 0 ? t.nc[0] : t.nc[1];
+        if (nc_i == 0) continue;
+        const int m0 = i == 0 ? t.m0[0] : t.m0[1];
+        const int kvend_i = i == 0 ? t.kvend[0] : t.kvend[1];
+        // keys visible to this row: [0, limit)
+        int limit = p.causal ? min(d.L, t.prefix + m0 + row + 1) : d.L;
+        limit = max(1, min(limit, kvend_i));
+        float m_used = -INFINITY;  // reference max (log2 domain) the running sums are expressed in
+        float l_run = 0.f;
+        for (int c = 0; c < nc_i; ++c) {
+          const int gc = g_my + c;                          // chunk count of this tile since kernel start
+          const uint32_t col_c = col_s + (gc & 1) * kExtC;  // S/P half of this chunk
+          TRACE(i, c, 0);
+          mbar_wait(bar(kBarSFull + i * 2 + (gc & 1)), (gc >> 1) & 1);
           tc_fence_after();
-          l_run *= alpha;
+          TRACE(i, c, 1);
+          float s[kExtC];
 #pragma unroll
-          for (int q = 0; q < D / 32; ++q) {
+          for (int q = 0; q < kExtC / 32; ++q) {
             uint32_t v[32];
-            tmem_ld32(col_o + q * 32, v);
-            tmem_wait_ld();
+            tmem_ld32(col_c + q * 32, v);
 #pragma unroll
-            for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(__uint_as_float(v[e]) * alpha);
-            tmem_st32(col_o + q * 32, v);
+            for (int e = 0; e < 32; ++e) s[q * 32 + e] = __uint_as_float(v[e]);
+          }
+          tmem_wait_ld();
+          TRACE(i, c, 2);
+          const int n0 = c * kExtC;
+          if (n0 + kExtC > limit) {
+#pragma unroll
+            for (int e = 0; e < kExtC; ++e)
+              if (n0 + e >= limit) s[e] = -INFINITY;
+          }
+          float mx4[4] = {s[0], s[1], s[2], s[3]};
+#pragma unroll
+          for (int e = 4; e < kExtC; e += 8) {
+            mx4[0] = fmax3(mx4[0], s[e], s[e + 1]);
+            mx4[1] = fmax3(mx4[1], s[e + 2], s[e + 3]);
+            if (e + 4 < kExtC) {
+              mx4[2] = fmax3(mx4[2], s[e + 4], s[e + 5]);
+              mx4[3] = fmax3(mx4[3], s[e + 6], s[e + 7]);
+            }
+          }
+          const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2;
+          float alpha = 1.f;
+          bool rescale = false;
+          if (m_used == -INFINITY) {
+            m_used = (mx == -INFINITY) ? 0.f : mx;  // c == 0 (limit >= 1 => finite)
+          } else if (mx > m_used + kRescaleThreshold) {
+            alpha = ex2_approx(m_used - mx);
+            m_used = mx;
+            rescale = true;
+          }
+          if (__any_sync(0xffffffffu, rescale)) {
+            // rare: O_i must be quiescent, i.e. PV_i(c-1) (possibly still in flight) has completed
+            mbar_wait(bar(kBarPVDone + i), (gc - 1) & 1);
+            tc_fence_after();
+            l_run *= alpha;
+#pragma unroll
+            for (int q = 0; q < D / 32; ++q) {
+              uint32_t v[32];
+              tmem_ld32(col_o + q * 32, v);
+              tmem_wait_ld();
+#pragma unroll
+              for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(__uint_as_float(v[e]) * alpha);
+              tmem_st32(col_o + q * 32, v);
+            }
+          }
+          TRACE(i, c, 3);
+          // p = exp2(s * scale - m); packed bf16 pairs go back into the first 32 columns of this S half
+          const uint64_t negm2 = f2_pack(-m_used, -m_used);
+          uint64_t sum2[2] = {0ull, 0ull};
+          uint32_t pk[32];
+#pragma unroll
+          for (int e = 0; e < kExtC; e += 2) {
+            float x0, x1, p0, p1;
+            f2_unpack(f2_fma(f2_pack(s[e], s[e + 1]), scale2, negm2), x0, x1);
+#ifdef EXT_ABL_NOEXP
+            if (true) {
+              p0 = x0;
+              p1 = x1;
+            } else
+#endif
+            if (((e >> 1) % kEmuPeriod) < kEmuCount) {
+              exp2_emu2(x0, x1, p0, p1);  // FMA-pipe polynomial: takes load off the 16-lane MUFU
+            } else {
+              p0 = ex2_approx(x0);
+              p1 = ex2_approx(x1);
+            }
+            sum2[(e >> 1) & 1] = f2_add(sum2[(e >> 1) & 1], f2_pack(p0, p1));
+            pk[e >> 1] = pack2<kBf16>(p0, p1);
+          }
+          tmem_st32(col_c, pk);
+          float a0, a1;
+          f2_unpack(f2_add(sum2[0], sum2[1]), a0, a1);
+          l_run += a0 + a1;
+          TRACE(i, c, 4);
+          tmem_wait_st();
+          tc_fence_before();
+          mbar_arrive(bar(kBarPFull + i * 2 + (gc & 1)));
+          TRACE(i, c, 5);
+        }
+        // ---- epilogue of this item (the issuer already runs QK of the next one) ----
+        mbar_wait(bar(kBarOFinal + i), nq_my & 1);
+        tc_fence_after();
+        const float inv = 1.f / l_run;
+        const bool valid = row < (i == 0 ? t.rows[0] : t.rows[1]);
+        const int h = i == 0 ? t.h[0] : t.h[1];
+        T* dst = reinterpret_cast<T*>(p.o) + (int64_t)(d.q_beg + m0 + row) * p.o_stride + (int64_t)h * D;
+#pragma unroll
+        for (int c = 0; c < D / 32; ++c) {
+          uint32_t v[32];
+          tmem_ld32(col_o + c * 32, v);
+          tmem_wait_ld();
+          if (valid) {
+#pragma unroll
+            for (int e = 0; e < 32; e += 8) {
+              uint4 w;
+              w.x = pack2<kBf16>(__uint_as_float(v[e]) * inv, __uint_as_float(v[e + 1]) * inv);
+              w.y = pack2<kBf16>(__uint_as_float(v[e + 2]) * inv, __uint_as_float(v[e + 3]) * inv);
+              w.z = pack2<kBf16>(__uint_as_float(v[e + 4]) * inv, __uint_as_float(v[e + 5]) * inv);
+              w.w = pack2<kBf16>(__uint_as_float(v[e + 6]) * inv, __uint_as_float(v[e + 7]) * inv);
+              *reinterpret_cast<uint4*>(dst + c * 32 + e) = w;
+            }
           }
         }
-        TRACE(i, c, 3);
-        // p = exp2(s * scale - m); packed bf16 pairs go back into the first 32 columns of this S half
-        const uint64_t negm2 = f2_pack(-m_used, -m_used);
-        uint64_t sum2[2] = {0ull, 0ull};
-        uint32_t pk[32];
-#pragma unroll
-        for (int e = 0; e < kExtC; e += 2) {
-          float x0, x1, p0, p1;
-          f2_unpack(f2_fma(f2_pack(s[e], s[e + 1]), scale2, negm2), x0, x1);
-          if (((e >> 1) % kEmuPeriod) < kEmuCount) {
-            exp2_emu2(x0, x1, p0, p1);  // FMA-pipe polynomial: takes load off the 16-lane MUFU
-          } else {
-            p0 = ex2_approx(x0);
-            p1 = ex2_approx(x1);
-          }
-          sum2[(e >> 1) & 1] = f2_add(sum2[(e >> 1) & 1], f2_pack(p0, p1));
-          pk[e >> 1] = pack2<kBf16>(p0, p1);
-        }
-        tmem_st32(col_c, pk);
-        float a0, a1;
-        f2_unpack(f2_add(sum2[0], sum2[1]), a0, a1);
-        l_run += a0 + a1;
-        TRACE(i, c, 4);
-        tmem_wait_st();
+        if (valid && p.lse != nullptr)
+          p.lse[(int64_t)(d.q_beg + m0 + row) * p.Hq + h] = (m_used + log2f(l_run)) * kLn2;
         tc_fence_before();
-        mbar_arrive(bar(kBarPFull + i * 2 + (c & 1)));
-        TRACE(i, c, 5);
+        g_my += nc_i;
+        ++nq_my;
       }
-      // ---- epilogue ----
-      mbar_wait(bar(kBarOFinal + i), 0);
-      tc_fence_after();
-      const float inv = 1.f / l_run;
-      const bool valid = row < t_rows[i];
-      const int h = t_h[i];
-      T* dst = reinterpret_cast<T*>(p.o) + (int64_t)(q_beg + m0 + row) * p.o_stride + (int64_t)h * D;
-#pragma unroll
-      for (int c = 0; c < D / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld32(col_o + c * 32, v);
-        tmem_wait_ld();
-        if (valid) {
-#pragma unroll
-          for (int e = 0; e < 32; e += 8) {
-            uint4 w;
-            w.x = pack2<kBf16>(__uint_as_float(v[e]) * inv, __uint_as_float(v[e + 1]) * inv);
-            w.y = pack2<kBf16>(__uint_as_float(v[e + 2]) * inv, __uint_as_float(v[e + 3]) * inv);
-            w.z = pack2<kBf16>(__uint_as_float(v[e + 4]) * inv, __uint_as_float(v[e + 5]) * inv);
-            w.w = pack2<kBf16>(__uint_as_float(v[e + 6]) * inv, __uint_as_float(v[e + 7]) * inv);
-            *reinterpret_cast<uint4*>(dst + c * 32 + e) = w;
-          }
-        }
-      }
-      if (valid && p.lse != nullptr)
-        p.lse[(int64_t)(q_beg + m0 + row) * p.Hq + h] = (m_used + log2f(l_run)) * kLn2;
-      tc_fence_before();
+      __syncthreads();  // every role is done with this round's descriptors
     }
   }
+  tc_fence_before();
   __syncthreads();
+#ifdef EXT_TRACE
+  if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+    long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    p.trace[(3 * 32 + 0) * 8 + 2] = clk();
+    p.trace[(3 * 32 + 0) * 8 + 3] = gt;
+  }
+#endif
   if (warp == 10) {
     tc_fence_after();
     tmem_dealloc<kTmemCols>(tmem);
@@ -570,11 +713,21 @@ static int launch_extend(const CUtensorMap& tq, const CUtensorMap& tk, const CUt
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     configured = true;
   }
-  // x: pairs of virtual tiles (q tile x GQA-group head) of one (request, kv head); fastest, so
-  // the CTAs that share a kv head's K/V tiles run together and hit them in L2
-  dim3 grid((unsigned)((max_qtiles * p.G + 1) / 2), (unsigned)p.Hkv, (unsigned)p.B);
-  extend_kernel<D, kBf16><<<grid, kExtThreads, kSmem, st>>>(tq, tk, tv, tkb, tvb, p);
-  B2_LAUNCH_CHECK();
+  // Persistent: one CTA per SM, static round-robin over the item list (request, kv head, tile pair);
+  // consecutive items share a kv head's K/V tiles, run at the same time on neighbouring SMs and hit
+  // them in L2.  The host only knows an upper bound of the item count (sizes the grid, graph-safe).
+  const long long upper = (long long)((max_qtiles * p.G + 1) / 2) * p.Hkv;
+  const int sms = sm_count();
+  for (int b0 = 0; b0 < p.B; b0 += kExtMaxB) {  // the in-kernel prefix table holds kExtMaxB requests
+    ExtendParams ps = p;
+    ps.B = p.B - b0 < kExtMaxB ? p.B - b0 : kExtMaxB;
+    ps.qo_indptr = p.qo_indptr + b0;
+    ps.kv_indptr = p.kv_indptr + b0;
+    const long long items = upper * ps.B;
+    dim3 grid((unsigned)(items < sms ? items : sms));
+    extend_kernel<D, kBf16><<<grid, kExtThreads, kSmem, st>>>(tq, tk, tv, tkb, tvb, ps);
+    B2_LAUNCH_CHECK();
+  }
   return B200ATTN_OK;
 }
 
@@ -602,7 +755,7 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
                "extend: null pointer");
   B2_CHECK_ARG(Hq > 0 && Hkv > 0 && Hq % Hkv == 0, "extend: Hq=%d must be a multiple of Hkv=%d",
                Hq, Hkv);
-  B2_CHECK_ARG(B <= 65535 && Hkv <= 65535, "extend: batch / kv head count too large");
+  B2_CHECK_ARG(Hkv <= 65535, "extend: kv head count too large");
   B2_CHECK_ARG(num_slots > 0 && num_slots < (1ll << 31), "extend: bad num_slots");
   B2_CHECK_ARG(q_stride % 8 == 0 && kv_stride % 8 == 0 && o_stride % 8 == 0,
                "extend: strides must keep rows 16-byte aligned");
@@ -642,7 +795,7 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
   p.skip_single = (causal & B200ATTN_EXT_SKIP_SINGLE) ? 1 : 0;
   p.scale_log2 = sm_scale * kLog2e;
 #ifdef EXT_TRACE
-  p.trace = workspace_bytes >= 3 * 32 * 8 * 8 ? (long long*)workspace : nullptr;
+  p.trace = workspace_bytes >= 4 * 32 * 8 * 8 ? (long long*)workspace : nullptr;
 #endif
   const int max_qtiles = (max_qo_len_host + kExtM - 1) / kExtM;
   cudaStream_t st = (cudaStream_t)stream;

@@ -39,12 +39,12 @@ kv_indptr = torch.zeros(B + 1, dtype=torch.int32, device=dev)
 qo_indptr = torch.zeros(B + 1, dtype=torch.int32, device=dev)
 kv_indices = torch.zeros(B * (P + E), dtype=torch.int32, device=dev)
 ops.build_kv_indices(table, req, seq, kv_indptr, kv_indices, qo_lens=extl, qo_indptr=qo_indptr)
-ws = torch.zeros(3 * 32 * 8, dtype=torch.int64, device=dev)
-for _ in range(3):
+ws = torch.zeros(4 * 32 * 8, dtype=torch.int64, device=dev)
+for _ in range(30):
     ops.extend_attention(q, kc, vc, o, qo_indptr, kv_indptr, kv_indices, D ** -0.5, causal=True, page_size=page,
                          max_qo_len=E, workspace=ws)
 torch.cuda.synchronize()
-t = ws.cpu().view(3, 32, 8)
+t = ws.cpu().view(4, 32, 8)
 t0 = int(t[2, 0, 0])
 print("softmax WG i: [wait_start, S_seen, ld_done, max_done, exp_done, arrived]; "
       "MMA: [w0, P0_seen, issued0, w1, P1_seen, issued1]")
@@ -53,3 +53,6 @@ for j in range(20):
     for r in range(3):
         row.append(" ".join(f"{int(t[r, j, k]) - t0:6d}" for k in range(6)))
     print(f"j={j:2d} | WG0 {row[0]} | WG1 {row[1]} | MMA {row[2]}")
+
+c0, g0, c1, g1 = (int(t[3, 0, k]) for k in range(4))
+print(f"CTA 0 lifetime: {c1 - c0} cycles in {g1 - g0} ns -> SM clock {(c1 - c0) / max(g1 - g0, 1) * 1e3:.0f} MHz (30th back-to-back launch)")
