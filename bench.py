@@ -50,6 +50,16 @@ def measured_peaks():
     return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, src="fallback")
 
 
+def ncu_traffic(key):
+    """DRAM bytes per launch of the named kernel from the committed ncu --set full capture (profiles/), or None."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        with open(path) as f:
+            return json.load(f)[key]["bytes"]
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def decode_bytes(c, B=None):
     """Algorithmic bytes of one decode layer-call: K+V rows read once,
     q read, o written, int32 slot ids read once per kv head group... counted once, new-token store."""
@@ -339,7 +349,8 @@ def run_b200(args, rank, world, local_rank):
                     parallelism=f"kv-head sharded x{world} (8 kv heads per GPU), no collective",
                     l2="inputs larger than L2 (1.07 GB KV per call vs 126 MB)", max_splits=max_splits),
         roofline=dict(bound="hbm", achieved=achieved, peak=peaks["hbm"], unit="GB/s", frac=achieved / peaks["hbm"],
-                      traffic=None, kernel="decode_kernel<128,bf16> (+merge)", kernel_ms=kern_ms,
+                      traffic=ncu_traffic("decode_kernel<128,bf16> cfg2") if world == 1 else None,
+                      kernel="decode_kernel<128,bf16> (+merge)", kernel_ms=kern_ms,
                       peak_source=peaks["src"], frac_of_8tbs=achieved / 8000.0),
         cpu_baseline=cpu,
         e2e=dict(value=e2e_val, unit="GB/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h, ms_per_step=e2e_ms),
@@ -402,7 +413,8 @@ def run_extend_leg(args, dev, gen, peaks):
     return dict(workload="llama-3.1-8b extend: 32 req x (2048 shared prefix + 512 new), causal (BASELINE configs[2])",
                 ms_per_step=ms, kernel_ms=kms, tflops=tf, flops=fl, tokens_per_s_attention_only=T / (32 * ms * 1e-3),
                 roofline=dict(bound="tensor", achieved=tf, peak=peaks["tf_burst"], unit="TFLOP/s",
-                              frac=tf / peaks["tf_burst"], frac_of_2250=tf / 2250.0, peak_source=peaks["src"]))
+                              frac=tf / peaks["tf_burst"], frac_of_2250=tf / 2250.0, peak_source=peaks["src"],
+                              traffic=ncu_traffic("extend_kernel<128,bf16> cfg3")))
 
 
 def run_backend_case(dev, gen, peaks, label, prefix_lens, ext_lens, Hq, Hkv, D, page, causal, mode_name,
