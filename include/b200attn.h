@@ -195,6 +195,46 @@ int b200attn_merge_state(const void* v_a, const float* s_a, const void* v_b,
                          const float* s_b, void* v_out, float* s_out, int64_t T,
                          int32_t H, int32_t D, int dtype, void* stream);
 
+/* --------------------------------------------------------------------------
+ * (f1) Fused RoPE / M-RoPE + KV store.  Replaces, in one pass over q/k/v,
+ *   RotaryEmbedding.forward_native / forward_cuda
+ *     python/sglang/srt/layers/rotary_embedding/base.py:236-276, 365-436
+ *   MRotaryEmbedding.forward_native (sectioned and interleaved M-RoPE)
+ *     python/sglang/srt/layers/rotary_embedding/mrope.py:47-51, 173-217
+ *   apply_rope_with_cos_sin_cache_inplace(..., fused_args=FusedSetKVBufferArg)
+ *     python/sglang/kernels/ops/attention/rope.py:98-113, 183-225
+ *     python/sglang/kernels/jit/csrc/elementwise/rope.cuh:56-110, 178-260
+ *   followed by the (a1) store of the rotated k and of v.
+ *
+ *   q[t,h,:rot], k[t,h,:rot] rotated IN PLACE by cos/sin of positions[t]
+ *   (neox: pairs (i, i+rot/2); gpt-j: pairs (2i, 2i+1)); columns >= rot pass through.
+ *   If k_cache != NULL: k_cache[loc[t]] = rotated k[t]; v_cache[loc[t]] = v[t]
+ *   with the (a1) skip_index / size_limit / oob_count semantics.
+ *
+ * cos_sin_cache: [cache_rows, rot] = (cos | sin) halves per row, fp32 or the element
+ * dtype (base.py:173-182).  positions: [T] (pos_axis_stride = 0, mrope_section_host
+ * NULL) or [3, T] with `pos_axis_stride` elements between the t/h/w rows and
+ * mrope_section_host = 3 HOST ints summing to rot/2 (captured by value at launch).
+ * Out-of-range positions are clamped to [0, cache_rows).
+ *
+ * mode: B200ATTN_ROPE_F32    fp32 products and sum, one rounding (rope.cuh:96-99)
+ *       B200ATTN_ROPE_NATIVE cos/sin and every intermediate rounded to the element
+ *                            dtype (torch bf16 arithmetic of utils.py:50-58)
+ * Both are bit-exact against the oracle restatement of the respective reference path.
+ * -------------------------------------------------------------------------- */
+#define B200ATTN_ROPE_F32 0
+#define B200ATTN_ROPE_NATIVE 1
+int b200attn_rope_store(void* q, void* k, const void* v, void* k_cache, void* v_cache,
+                        const void* loc, int loc_dtype, const void* cos_sin_cache,
+                        int cache_dtype, int64_t cache_rows, const void* positions,
+                        int pos_dtype, int64_t pos_axis_stride,
+                        const int32_t* mrope_section_host, int mrope_interleaved, int64_t T,
+                        int32_t Hq, int32_t Hkv, int32_t D, int32_t Dv, int32_t rotary_dim,
+                        int is_neox, int64_t q_stride, int64_t k_stride, int64_t v_stride,
+                        int64_t k_cache_stride, int64_t v_cache_stride, int64_t size_limit,
+                        int64_t skip_index, int32_t* oob_count, int elem_dtype, int mode,
+                        void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,344 @@
+// (f1) Fused RoPE / M-RoPE + KV store: rotate q and k in place and scatter the rotated k and the
+// untouched v rows into the paged pool in ONE pass over q/k/v (the step immediately before attention).
+//
+// Behaviour follows
+//   python/sglang/srt/layers/rotary_embedding/base.py:236-276   (RotaryEmbedding.forward_native)
+//   python/sglang/srt/layers/rotary_embedding/utils.py:36-62    (apply_rotary_emb, neox / gpt-j pairing)
+//   python/sglang/srt/layers/rotary_embedding/mrope.py:47-51,173-217 (M-RoPE section / interleaved select)
+//   python/sglang/kernels/ops/attention/rope.py:183-225 + jit/csrc/elementwise/rope.cuh:56-110,178-260
+//     (apply_rope_with_cos_sin_cache_inplace, fused K/V cache store = FusedSetKVBufferArg)
+//   python/sglang/kernels/jit/csrc/elementwise/kvcache.cuh:186-218 (store semantics, reserved slot skip)
+//
+// Two arithmetic modes, each bit-exact against its oracle restatement:
+//   B200ATTN_ROPE_F32    : cos/sin read as stored (fp32 cache), x widened to fp32,
+//                          o = rn(rn(x1*cos) - rn(x2*sin)) in fp32, ONE rounding to the element type
+//                          (the production CUDA kernel's arithmetic, rope.cuh:96-99, without FMA contraction)
+//   B200ATTN_ROPE_NATIVE : cos/sin first rounded to the element type, every product and the sum rounded to the
+//                          element type (what torch does for bf16 tensors in forward_native: utils.py:50-58)
+//
+// HBM-bound: per token (Hq+2*Hkv)*D*2 B read + (Hq+Hkv)*D*2 B written in place + 2*Hkv*D*2 B into the pool.
+// One thread owns VEC (<= 8) rotation pairs of one head: two 16-byte loads (x1 | x2 halves for neox, 32
+// contiguous bytes for gpt-j), the cos/sin chunk through the read-only path (shared by every head of the
+// token => L1/L2 resident), two 16-byte stores in place and, for k, two more into the pool row.  Pass-through
+// columns of k (rotary_dim < head_dim) and all of v are plain 16-byte copies done by the trailing work items.
+#include "common.cuh"
+
+namespace b200attn {
+
+struct RopeParams {
+  uint8_t* q;
+  uint8_t* k;
+  const uint8_t* v;
+  uint8_t* k_cache;
+  uint8_t* v_cache;
+  const void* loc;
+  const void* cos_sin;
+  const void* pos;
+  int64_t pos_axis_stride;  // elements between the t/h/w rows of positions[3,T]; 0 = 1-D positions
+  int64_t T, cache_rows;
+  int64_t q_stride, k_stride, v_stride, kc_stride, vc_stride;  // elements
+  int64_t size_limit, skip_index;
+  int32_t* oob_count;
+  int Hq, Hkv, D, Dv, rot;
+  int sec0, sec1, sec2;  // M-RoPE sections (pairs per axis); sec0 < 0 = none
+  int loc_dtype, pos_dtype;
+  int interleaved, neox, store;
+};
+
+template <bool kBf16>
+__device__ __forceinline__ float to_f(uint16_t x) {
+  if constexpr (kBf16) return __uint_as_float((uint32_t)x << 16);
+  return __half2float(__ushort_as_half(x));
+}
+template <bool kBf16>
+__device__ __forceinline__ uint16_t from_f(float x) {
+  if constexpr (kBf16) return __bfloat16_as_ushort(__float2bfloat16_rn(x));
+  return __half_as_ushort(__float2half_rn(x));
+}
+template <bool kBf16>
+__device__ __forceinline__ float round_elem(float x) {
+  return to_f<kBf16>(from_f<kBf16>(x));
+}
+
+template <int VEC>
+struct VecOf;
+template <>
+struct VecOf<8> { using type = uint4; };
+template <>
+struct VecOf<4> { using type = uint2; };
+template <>
+struct VecOf<2> { using type = uint32_t; };
+template <>
+struct VecOf<1> { using type = uint16_t; };
+
+template <int VEC>
+union Pack {
+  typename VecOf<VEC>::type v;
+  uint16_t e[VEC];
+};
+
+// axis of rotation pair i under M-RoPE (mrope.py:47-51 interleaved, :190-199 sectioned)
+__device__ __forceinline__ int mrope_axis(const RopeParams& p, int i) {
+  if (p.interleaved) {
+    const int m = i % 3;
+    if (m == 1 && i < p.sec1 * 3) return 1;
+    if (m == 2 && i < p.sec2 * 3) return 2;
+    return 0;
+  }
+  return i < p.sec0 ? 0 : (i < p.sec0 + p.sec1 ? 1 : 2);
+}
+
+template <int VEC, bool kBf16, bool kCacheF32, bool kNative>
+__global__ void __launch_bounds__(256) rope_store_kernel(const RopeParams p) {
+  using V = typename VecOf<VEC>::type;
+  const int half = p.rot >> 1;
+  const int rot_items = half / VEC;                 // per head
+  const int pass_items = (p.D - p.rot) / VEC;       // per k head (pool copy only)
+  const int v_items = p.Dv / VEC;                   // per v head
+  const int nq = p.Hq * rot_items, nk = p.Hkv * rot_items;
+  const int nkp = p.store ? p.Hkv * pass_items : 0;
+  const int nv = p.store ? p.Hkv * v_items : 0;
+  const int per_tok = nq + nk + nkp + nv;
+  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= p.T * per_tok) return;
+  const int64_t t = gid / per_tok;
+  int it = (int)(gid - t * per_tok);
+
+  int64_t slot = -1;
+  bool do_store = false;
+  if (p.store && it >= nq) {
+    slot = load_index(p.loc, p.loc_dtype, t);
+    if (slot == p.skip_index) {
+      do_store = false;  // kvcache.cuh:215
+    } else if (slot < 0 || slot >= p.size_limit) {
+      if (it == nq && p.oob_count != nullptr) atomicAdd(p.oob_count, 1);
+    } else {
+      do_store = true;
+    }
+  }
+
+  if (it >= nq + nk) {  // plain copies into the pool
+    if (!do_store) return;
+    it -= nq + nk;
+    const uint8_t* src;
+    uint8_t* dst;
+    if (it < nkp) {
+      const int h = it / pass_items, c = it - h * pass_items;
+      const int64_t col = (int64_t)h * p.D + p.rot + c * VEC;
+      src = p.k + (t * p.k_stride + col) * 2;
+      dst = p.k_cache + (slot * p.kc_stride + col) * 2;
+    } else {
+      it -= nkp;
+      const int64_t col = (int64_t)it * VEC;
+      src = p.v + (t * p.v_stride + col) * 2;
+      dst = p.v_cache + (slot * p.vc_stride + col) * 2;
+    }
+    *reinterpret_cast<V*>(dst) = *reinterpret_cast<const V*>(src);
+    return;
+  }
+
+  const bool is_k = it >= nq;
+  if (is_k) it -= nq;
+  const int h = it / rot_items, c = it - h * rot_items;
+  const int i0 = c * VEC;  // first rotation pair of this thread
+  uint8_t* row = is_k ? p.k + (t * p.k_stride + (int64_t)h * p.D) * 2
+                      : p.q + (t * p.q_stride + (int64_t)h * p.D) * 2;
+  // neox: pair i = (x[i], x[i+half]);  gpt-j: pair i = (x[2i], x[2i+1])
+  V* pa = reinterpret_cast<V*>(row + (p.neox ? i0 : 2 * i0) * 2);
+  V* pb = reinterpret_cast<V*>(row + (p.neox ? i0 + half : 2 * i0 + VEC) * 2);
+  Pack<VEC> a, b;
+  a.v = *pa;
+  b.v = *pb;
+
+  float cs[VEC], sn[VEC];
+  if (p.sec0 < 0) {
+    int64_t pos = load_index(p.pos, p.pos_dtype, t);
+    pos = pos < 0 ? 0 : (pos >= p.cache_rows ? p.cache_rows - 1 : pos);
+    if constexpr (kCacheF32) {
+      const float* cr = reinterpret_cast<const float*>(p.cos_sin) + pos * p.rot;
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        cs[j] = __ldg(cr + i0 + j);
+        sn[j] = __ldg(cr + half + i0 + j);
+      }
+    } else {
+      const uint16_t* cr = reinterpret_cast<const uint16_t*>(p.cos_sin) + pos * p.rot;
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        cs[j] = to_f<kBf16>(__ldg(cr + i0 + j));
+        sn[j] = to_f<kBf16>(__ldg(cr + half + i0 + j));
+      }
+    }
+  } else {
+    int64_t pos3[3];
+#pragma unroll
+    for (int ax = 0; ax < 3; ++ax) {
+      int64_t pos = load_index(p.pos, p.pos_dtype, ax * p.pos_axis_stride + t);
+      pos3[ax] = pos < 0 ? 0 : (pos >= p.cache_rows ? p.cache_rows - 1 : pos);
+    }
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      const int ax = mrope_axis(p, i0 + j);
+      const int64_t pos = ax == 0 ? pos3[0] : (ax == 1 ? pos3[1] : pos3[2]);
+      if constexpr (kCacheF32) {
+        const float* cr = reinterpret_cast<const float*>(p.cos_sin) + pos * p.rot;
+        cs[j] = __ldg(cr + i0 + j);
+        sn[j] = __ldg(cr + half + i0 + j);
+      } else {
+        const uint16_t* cr = reinterpret_cast<const uint16_t*>(p.cos_sin) + pos * p.rot;
+        cs[j] = to_f<kBf16>(__ldg(cr + i0 + j));
+        sn[j] = to_f<kBf16>(__ldg(cr + half + i0 + j));
+      }
+    }
+  }
+
+  // element j of the thread: neox -> x1 = a.e[j], x2 = b.e[j]; gpt-j -> the 2*VEC contiguous values
+  // (a | b) hold pairs (2j, 2j+1)
+  Pack<VEC> oa, ob;
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) {
+    uint16_t r1, r2;
+    if (p.neox) {
+      r1 = a.e[j];
+      r2 = b.e[j];
+    } else {
+      const int e1 = 2 * j, e2 = 2 * j + 1;
+      r1 = e1 < VEC ? a.e[e1 % VEC] : b.e[e1 % VEC];
+      r2 = e2 < VEC ? a.e[e2 % VEC] : b.e[e2 % VEC];
+    }
+    const float x1 = to_f<kBf16>(r1), x2 = to_f<kBf16>(r2);
+    float c_ = cs[j], s_ = sn[j];
+    float o1, o2;
+    if constexpr (kNative) {
+      c_ = round_elem<kBf16>(c_);
+      s_ = round_elem<kBf16>(s_);
+      o1 = __fsub_rn(round_elem<kBf16>(__fmul_rn(x1, c_)), round_elem<kBf16>(__fmul_rn(x2, s_)));
+      o2 = __fadd_rn(round_elem<kBf16>(__fmul_rn(x2, c_)), round_elem<kBf16>(__fmul_rn(x1, s_)));
+    } else {
+      o1 = __fsub_rn(__fmul_rn(x1, c_), __fmul_rn(x2, s_));
+      o2 = __fadd_rn(__fmul_rn(x2, c_), __fmul_rn(x1, s_));
+    }
+    const uint16_t w1 = from_f<kBf16>(o1), w2 = from_f<kBf16>(o2);
+    if (p.neox) {
+      oa.e[j] = w1;
+      ob.e[j] = w2;
+    } else {
+      const int e1 = 2 * j, e2 = 2 * j + 1;
+      if (e1 < VEC) oa.e[e1 % VEC] = w1; else ob.e[e1 % VEC] = w1;
+      if (e2 < VEC) oa.e[e2 % VEC] = w2; else ob.e[e2 % VEC] = w2;
+    }
+  }
+  *pa = oa.v;
+  *pb = ob.v;
+  if (is_k && do_store) {
+    uint8_t* crow = p.k_cache + (slot * p.kc_stride + (int64_t)h * p.D) * 2;
+    *reinterpret_cast<V*>(crow + (p.neox ? i0 : 2 * i0) * 2) = oa.v;
+    *reinterpret_cast<V*>(crow + (p.neox ? i0 + half : 2 * i0 + VEC) * 2) = ob.v;
+  }
+}
+
+template <int VEC>
+static int launch_rope(const RopeParams& p, int elem_dtype, int cache_dtype, int mode,
+                       cudaStream_t st) {
+  const int half = p.rot / 2;
+  const int64_t per_tok = (int64_t)(p.Hq + p.Hkv) * (half / VEC) +
+                          (p.store ? (int64_t)p.Hkv * ((p.D - p.rot) / VEC + p.Dv / VEC) : 0);
+  const int64_t threads = p.T * per_tok;
+  const int64_t blocks = (threads + 255) / 256;
+  B2_CHECK_ARG(blocks < (1ll << 31), "rope_store: too many work items");
+  const bool bf16 = elem_dtype == B200ATTN_BF16;
+  const bool cf32 = cache_dtype == B200ATTN_FP32;
+  const bool native = mode == B200ATTN_ROPE_NATIVE;
+#define B2_ROPE(BF, CF, NA)                                                                  \
+  if (bf16 == BF && cf32 == CF && native == NA) {                                            \
+    rope_store_kernel<VEC, BF, CF, NA><<<(unsigned)blocks, 256, 0, st>>>(p);                 \
+    B2_LAUNCH_CHECK();                                                                       \
+    return B200ATTN_OK;                                                                      \
+  }
+  B2_ROPE(true, true, false)
+  B2_ROPE(true, true, true)
+  B2_ROPE(true, false, false)
+  B2_ROPE(true, false, true)
+  B2_ROPE(false, true, false)
+  B2_ROPE(false, true, true)
+  B2_ROPE(false, false, false)
+  B2_ROPE(false, false, true)
+#undef B2_ROPE
+  return B200ATTN_ERR_INVALID;
+}
+
+}  // namespace b200attn
+
+extern "C" int b200attn_rope_store(void* q, void* k, const void* v, void* k_cache, void* v_cache,
+                                   const void* loc, int loc_dtype, const void* cos_sin_cache,
+                                   int cache_dtype, int64_t cache_rows, const void* positions,
+                                   int pos_dtype, int64_t pos_axis_stride,
+                                   const int32_t* mrope_section_host, int mrope_interleaved,
+                                   int64_t T, int32_t Hq, int32_t Hkv, int32_t D, int32_t Dv,
+                                   int32_t rotary_dim, int is_neox, int64_t q_stride,
+                                   int64_t k_stride, int64_t v_stride, int64_t k_cache_stride,
+                                   int64_t v_cache_stride, int64_t size_limit, int64_t skip_index,
+                                   int32_t* oob_count, int elem_dtype, int mode, void* stream) {
+  using namespace b200attn;
+  B2_CHECK_ARG(T >= 0, "rope_store: negative T");
+  if (T == 0) return B200ATTN_OK;
+  B2_CHECK_ARG(q && k && cos_sin_cache && positions, "rope_store: null pointer");
+  B2_CHECK_ARG(elem_dtype == B200ATTN_BF16 || elem_dtype == B200ATTN_FP16,
+               "rope_store: q/k must be bf16 or fp16");
+  B2_CHECK_ARG(cache_dtype == B200ATTN_FP32 || cache_dtype == elem_dtype,
+               "rope_store: cos_sin_cache must be fp32 or the element dtype");
+  B2_CHECK_ARG(mode == B200ATTN_ROPE_F32 || mode == B200ATTN_ROPE_NATIVE, "rope_store: bad mode");
+  B2_CHECK_ARG(Hq > 0 && Hkv > 0 && D > 0 && rotary_dim > 0 && rotary_dim <= D &&
+                   (rotary_dim & 1) == 0,
+               "rope_store: bad head geometry (Hq %d Hkv %d D %d rot %d)", Hq, Hkv, D, rotary_dim);
+  B2_CHECK_ARG(cache_rows > 0, "rope_store: empty cos_sin_cache");
+  B2_CHECK_ARG(q_stride >= (int64_t)Hq * D && k_stride >= (int64_t)Hkv * D,
+               "rope_store: q/k stride smaller than row");
+  const bool store = k_cache != nullptr;
+  if (store) {
+    B2_CHECK_ARG(v && v_cache && loc && Dv > 0, "rope_store: store needs v, v_cache, loc");
+    B2_CHECK_ARG(loc_dtype == B200ATTN_I32 || loc_dtype == B200ATTN_I64, "rope_store: bad loc dtype");
+    B2_CHECK_ARG(v_stride >= (int64_t)Hkv * Dv && k_cache_stride >= (int64_t)Hkv * D &&
+                     v_cache_stride >= (int64_t)Hkv * Dv,
+                 "rope_store: stride smaller than row");
+  }
+  RopeParams p{};
+  p.q = (uint8_t*)q; p.k = (uint8_t*)k; p.v = (const uint8_t*)v;
+  p.k_cache = (uint8_t*)k_cache; p.v_cache = (uint8_t*)v_cache;
+  p.loc = loc; p.cos_sin = cos_sin_cache; p.pos = positions;
+  p.pos_axis_stride = pos_axis_stride; p.T = T; p.cache_rows = cache_rows;
+  p.q_stride = q_stride; p.k_stride = k_stride; p.v_stride = v_stride;
+  p.kc_stride = k_cache_stride; p.vc_stride = v_cache_stride;
+  p.size_limit = size_limit; p.skip_index = skip_index; p.oob_count = oob_count;
+  p.Hq = Hq; p.Hkv = Hkv; p.D = D; p.Dv = store ? Dv : 0; p.rot = rotary_dim;
+  p.loc_dtype = loc_dtype; p.pos_dtype = pos_dtype;
+  p.interleaved = mrope_interleaved; p.neox = is_neox; p.store = store;
+  if (mrope_section_host != nullptr) {
+    p.sec0 = mrope_section_host[0]; p.sec1 = mrope_section_host[1]; p.sec2 = mrope_section_host[2];
+    B2_CHECK_ARG(p.sec0 >= 0 && p.sec1 >= 0 && p.sec2 >= 0 &&
+                     p.sec0 + p.sec1 + p.sec2 == rotary_dim / 2,
+                 "rope_store: mrope_section must sum to rotary_dim/2");
+    B2_CHECK_ARG(pos_axis_stride >= T, "rope_store: positions[3,T] axis stride < T");
+  } else {
+    p.sec0 = -1;
+    B2_CHECK_ARG(pos_axis_stride == 0, "rope_store: 2-D positions need mrope_section");
+  }
+  B2_CHECK_ARG(pos_dtype == B200ATTN_I32 || pos_dtype == B200ATTN_I64, "rope_store: bad pos dtype");
+  // widest vector (in elements) dividing the rotation half, the pass-through width, every stride and
+  // every base address
+  uint64_t bits = (uint64_t)(rotary_dim / 2) | (uint64_t)D | (uint64_t)q_stride | (uint64_t)k_stride |
+                  ((uint64_t)(uintptr_t)q >> 1) | ((uint64_t)(uintptr_t)k >> 1);
+  B2_CHECK_ARG((((uintptr_t)q | (uintptr_t)k) & 1) == 0, "rope_store: unaligned q/k");
+  if (store) {
+    bits |= (uint64_t)Dv | (uint64_t)(D - rotary_dim) | (uint64_t)v_stride | (uint64_t)k_cache_stride |
+            (uint64_t)v_cache_stride | ((uint64_t)(uintptr_t)v >> 1) |
+            ((uint64_t)(uintptr_t)k_cache >> 1) | ((uint64_t)(uintptr_t)v_cache >> 1);
+  } else {
+    bits |= (uint64_t)(D - rotary_dim);
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if ((bits & 7) == 0) return launch_rope<8>(p, elem_dtype, cache_dtype, mode, st);
+  if ((bits & 3) == 0) return launch_rope<4>(p, elem_dtype, cache_dtype, mode, st);
+  if ((bits & 1) == 0) return launch_rope<2>(p, elem_dtype, cache_dtype, mode, st);
+  return launch_rope<1>(p, elem_dtype, cache_dtype, mode, st);
+}

@@ -7,7 +7,7 @@ except for the output when the caller did not pass one; none synchronises.
 """
 from __future__ import annotations
 
-from typing import Optional, Tuple
+from typing import Optional, Sequence, Tuple
 
 import torch
 
@@ -97,6 +97,110 @@ def store_cache(
         min(kc.shape[0], vc.shape[0]), reserved_skip_index, _ptr(oob_count), _stream(),
     )
     check(rc, "b200attn_kv_store")
+
+
+# -------------------------------------------------------------------- rope + store
+ROPE_F32, ROPE_NATIVE = 0, 1
+
+
+def apply_rope_with_cos_sin_cache_inplace(
+    positions: torch.Tensor,
+    q: torch.Tensor,
+    k: torch.Tensor,
+    cos_sin_cache: torch.Tensor,
+    *,
+    head_size: int,
+    is_neox: bool = True,
+    rope_dim: int = 0,
+    mrope_section: Optional[Sequence[int]] = None,
+    mrope_interleaved: bool = False,
+    v: Optional[torch.Tensor] = None,
+    k_buffer: Optional[torch.Tensor] = None,
+    v_buffer: Optional[torch.Tensor] = None,
+    cache_loc: Optional[torch.Tensor] = None,
+    reserved_skip_index: int = 0,
+    oob_count: Optional[torch.Tensor] = None,
+    native_rounding: bool = False,
+) -> None:
+    """Rotate ``q`` and ``k`` in place; with ``k_buffer/v_buffer/cache_loc/v`` also scatter the rotated k
+    and v into the pool (one kernel).
+
+    Mirrors ``apply_rope_with_cos_sin_cache_inplace(q, k, cos_sin_cache, positions, is_neox=, rope_dim=,
+    fused_args=FusedSetKVBufferArg(value, k_buffer, v_buffer, cache_loc))``
+    (python/sglang/kernels/ops/attention/rope.py:98-113,183-225) and adds the M-RoPE select of
+    ``MRotaryEmbedding.forward_native`` (python/sglang/srt/layers/rotary_embedding/mrope.py:173-217):
+    ``positions`` is ``[T]`` or ``[3, T]`` (then ``mrope_section`` is required).  ``q``/``k`` are
+    ``[T, H*head_size]`` or ``[T, H, head_size]`` with contiguous rows (token stride free).
+    ``native_rounding`` selects torch's element-dtype arithmetic (bit-exact with ``forward_native``),
+    otherwise fp32 arithmetic with one rounding (the reference CUDA kernel's).
+    """
+    _require_cuda(positions, q, k, cos_sin_cache, v, k_buffer, v_buffer, cache_loc)
+    T = q.shape[0]
+    if k.shape[0] != T:
+        raise ValueError("rope: q and k disagree on the number of tokens")
+    rot = rope_dim or cos_sin_cache.shape[-1]
+    if cos_sin_cache.dim() != 2 or cos_sin_cache.shape[1] != rot or not cos_sin_cache.is_contiguous():
+        raise ValueError("rope: cos_sin_cache must be contiguous [max_position, rope_dim]")
+    if q.dtype != k.dtype:
+        raise TypeError("rope: q and k must share a dtype")
+    if cos_sin_cache.dtype not in (torch.float32, q.dtype):
+        raise TypeError("rope: cos_sin_cache must be float32 or q's dtype")
+    q2, k2 = q.reshape(T, -1) if q.dim() != 2 else q, k.reshape(T, -1) if k.dim() != 2 else k
+    if T and (q2.data_ptr() != q.data_ptr() or k2.data_ptr() != k.data_ptr()):
+        raise ValueError("rope: q/k rows must be viewable as [T, H*head_size] without a copy (in-place op)")
+    if q2.stride(1) != 1 or k2.stride(1) != 1:
+        raise ValueError("rope: rows must be contiguous")
+    if q2.shape[1] % head_size or k2.shape[1] % head_size:
+        raise ValueError("rope: row width is not a multiple of head_size")
+    Hq, Hkv = q2.shape[1] // head_size, k2.shape[1] // head_size
+    if positions.dim() == 2:
+        if positions.shape[0] != 3 or mrope_section is None:
+            raise ValueError("rope: 2-D positions must be [3, T] and need mrope_section")
+        if positions.stride(1) != 1:
+            positions = positions.contiguous()
+        if positions.shape[1] != T:
+            raise ValueError("rope: positions and q disagree on the number of tokens")
+        pos_axis_stride = max(positions.stride(0), T)
+        import ctypes as C
+        sec = (C.c_int32 * 3)(*[int(x) for x in mrope_section])
+    else:
+        if positions.numel() != T:
+            raise ValueError("rope: positions and q disagree on the number of tokens")
+        if not positions.is_contiguous():
+            positions = positions.contiguous()
+        pos_axis_stride, sec = 0, None
+        mrope_interleaved = False
+    store = k_buffer is not None
+    Dv = 0
+    kc = vc = v2 = None
+    if store:
+        if v is None or v_buffer is None or cache_loc is None:
+            raise ValueError("rope: fused store needs v, k_buffer, v_buffer and cache_loc")
+        if k.dtype != k_buffer.dtype or v.dtype != v_buffer.dtype or v.dtype != k.dtype:
+            raise TypeError("rope: cache dtype must equal the row dtype")
+        v2 = v.reshape(T, -1)
+        kc, vc = k_buffer.reshape(k_buffer.shape[0], -1), v_buffer.reshape(v_buffer.shape[0], -1)
+        if v2.stride(1) != 1 or kc.stride(1) != 1 or vc.stride(1) != 1:
+            raise ValueError("rope: rows must be contiguous")
+        if kc.shape[1] != k2.shape[1] or vc.shape[1] != v2.shape[1] or v2.shape[1] % Hkv:
+            raise ValueError("rope: row width differs between input and cache")
+        Dv = v2.shape[1] // Hkv
+        if cache_loc.numel() != T:
+            raise ValueError("rope: cache_loc and q disagree on the number of tokens")
+        if not cache_loc.is_contiguous():
+            cache_loc = cache_loc.contiguous()
+    if T == 0:
+        return
+    rc = _lib.load().b200attn_rope_store(
+        q2.data_ptr(), k2.data_ptr(), _ptr(v2), _ptr(kc), _ptr(vc), _ptr(cache_loc),
+        _idtype(cache_loc) if store else I32, cos_sin_cache.data_ptr(), _fdtype(cos_sin_cache),
+        cos_sin_cache.shape[0], positions.data_ptr(), _idtype(positions), pos_axis_stride, sec,
+        int(bool(mrope_interleaved)), T, Hq, Hkv, head_size, Dv, rot, int(bool(is_neox)), q2.stride(0),
+        k2.stride(0), v2.stride(0) if store else 0, kc.stride(0) if store else 0,
+        vc.stride(0) if store else 0, min(kc.shape[0], vc.shape[0]) if store else 0, reserved_skip_index,
+        _ptr(oob_count), _fdtype(q), ROPE_NATIVE if native_rounding else ROPE_F32, _stream(),
+    )
+    check(rc, "b200attn_rope_store")
 
 
 # ------------------------------------------------------------------------ metadata

@@ -1,0 +1,105 @@
+"""Host-side mirror of the reference rotary layer for the fused RoPE + KV-store step.
+
+``RotaryEmbedding`` / ``MRotaryEmbedding`` keep the reference constructor arguments and call convention
+(python/sglang/srt/layers/rotary_embedding/base.py:78-143,236-276,365-436; mrope.py:54-136,173-251):
+``rope(positions, query, key, fused_set_kv_buffer_arg=None) -> (query, key)``, rotating IN PLACE like the
+reference CUDA path.  All arithmetic runs in ``b200attn_rope_store``; there is no torch fallback.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import ops
+
+
+@dataclass
+class FusedSetKVBufferArg:
+    """python/sglang/kernels/ops/attention/rope.py:98-113."""
+
+    value: torch.Tensor
+    k_buffer: torch.Tensor
+    v_buffer: torch.Tensor
+    cache_loc: torch.Tensor
+
+
+def compute_cos_sin_cache(rotary_dim: int, max_position: int, base: float) -> torch.Tensor:
+    """fp32 ``[max_position, rotary_dim]`` = (cos | sin); base.py:153-182 (computed on the host like the
+    reference's HF-exact path, then moved)."""
+    inv_freq = 1.0 / (base ** (torch.arange(0, rotary_dim, 2, dtype=torch.float) / rotary_dim))
+    t = torch.arange(max_position, dtype=torch.float)
+    freqs = torch.einsum("i,j -> ij", t, inv_freq)
+    return torch.cat((freqs.cos(), freqs.sin()), dim=-1)
+
+
+class RotaryEmbedding:
+    def __init__(self, head_size: int, rotary_dim: int, max_position_embeddings: int, base: float,
+                 is_neox_style: bool, dtype: torch.dtype, device: str = "cuda", native_rounding: bool = False):
+        self.head_size, self.rotary_dim = head_size, rotary_dim
+        self.max_position_embeddings, self.base = max_position_embeddings, base
+        self.is_neox_style, self.dtype = is_neox_style, dtype
+        # fp32 cache as on CUDA in the reference (base.py:107-109); native_rounding reproduces forward_native
+        self.native_rounding = native_rounding
+        self.cos_sin_cache = compute_cos_sin_cache(rotary_dim, max_position_embeddings, base).to(device)
+        self.mrope_section: Optional[List[int]] = None
+        self.mrope_interleaved = False
+
+    def __call__(self, positions, query, key, offsets=None, fused_set_kv_buffer_arg=None):
+        return self.forward(positions, query, key, offsets, fused_set_kv_buffer_arg)
+
+    def forward(self, positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor,
+                offsets: Optional[torch.Tensor] = None,
+                fused_set_kv_buffer_arg: Optional[FusedSetKVBufferArg] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+        if offsets is not None:
+            positions = positions + offsets
+        f = fused_set_kv_buffer_arg
+        if positions.dim() == 2 and not self.mrope_section:
+            raise AssertionError("2D positions (multimodal RoPE) need an MRotaryEmbedding")  # base.py:216-219
+        ops.apply_rope_with_cos_sin_cache_inplace(
+            positions, query, key, self.cos_sin_cache, head_size=self.head_size, is_neox=self.is_neox_style,
+            rope_dim=self.rotary_dim, mrope_section=self.mrope_section if positions.dim() == 2 else None,
+            mrope_interleaved=self.mrope_interleaved, v=None if f is None else f.value,
+            k_buffer=None if f is None else f.k_buffer, v_buffer=None if f is None else f.v_buffer,
+            cache_loc=None if f is None else f.cache_loc, native_rounding=self.native_rounding)
+        return query, key
+
+
+class MRotaryEmbedding(RotaryEmbedding):
+    """Sectioned / interleaved multimodal RoPE (mrope.py:54-136).  The GLM axis-map variant is not on the path."""
+
+    def __init__(self, head_size: int, rotary_dim: int, max_position_embeddings: int, base: float,
+                 is_neox_style: bool, dtype: torch.dtype, mrope_section: Optional[Sequence[int]] = None,
+                 mrope_interleaved: bool = False, mrope_interleaved_glm: bool = False, device: str = "cuda",
+                 native_rounding: bool = False):
+        super().__init__(head_size, rotary_dim, max_position_embeddings, base, is_neox_style, dtype, device,
+                         native_rounding)
+        if mrope_interleaved_glm:
+            raise NotImplementedError("b200 rotary: mrope_interleaved_glm axis map")
+        self.mrope_section = list(mrope_section) if mrope_section else None
+        if self.mrope_section and sum(self.mrope_section) != rotary_dim // 2:
+            raise ValueError(f"mrope_section {self.mrope_section} must sum to rotary_dim // 2 = {rotary_dim // 2}")
+        self.mrope_interleaved = mrope_interleaved
+
+
+def mrope_positions_extend(prefix_lens: Sequence[int], extend_lens: Sequence[int],
+                           mm_positions: Sequence[Optional[torch.Tensor]]) -> torch.Tensor:
+    """``int64[3, T]`` for an extend batch: text-only requests get ``arange(prefix, prefix+extend)`` on all
+    three axes, multimodal ones the slice of their precomputed ``mrope_positions``
+    (forward_batch_info.py:1213-1254)."""
+    out = []
+    for pre, ext, mm in zip(prefix_lens, extend_lens, mm_positions):
+        if mm is None:
+            out.append(torch.arange(pre, pre + ext, dtype=torch.int64).unsqueeze(0).repeat(3, 1))
+        else:
+            out.append(mm[:, pre:pre + ext].to(torch.int64))
+    return torch.cat(out, dim=1) if out else torch.zeros((3, 0), dtype=torch.int64)
+
+
+def mrope_positions_decode(seq_lens: torch.Tensor, deltas: Optional[Sequence[int]] = None) -> torch.Tensor:
+    """``(delta - 1) + seq_len`` on all three axes (forward_batch_info.py:1166-1184)."""
+    p = seq_lens.to(torch.int64) - 1
+    if deltas is not None:
+        p = p + torch.as_tensor(list(deltas), dtype=torch.int64, device=seq_lens.device)
+    return p.unsqueeze(0).repeat(3, 1)

@@ -12,7 +12,13 @@ GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
 def golden_files() -> List[str]:
-    return sorted(glob.glob(os.path.join(GOLDEN_DIR, "*.pt")))
+    """Attention-backend fixtures (oracle/gen_golden.py)."""
+    return sorted(p for p in glob.glob(os.path.join(GOLDEN_DIR, "*.pt")) if not os.path.basename(p).startswith("rope_"))
+
+
+def rope_golden_files() -> List[str]:
+    """Rotary-layer fixtures (oracle/gen_golden_rope.py)."""
+    return sorted(glob.glob(os.path.join(GOLDEN_DIR, "rope_*.pt")))
 
 
 def load_golden(path: str) -> dict:
