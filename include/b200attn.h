@@ -235,6 +235,35 @@ int b200attn_rope_store(void* q, void* k, const void* v, void* k_cache, void* v_
                         int64_t skip_index, int32_t* oob_count, int elem_dtype, int mode,
                         void* stream);
 
+/* --------------------------------------------------------------------------
+ * (f3) Paged KV allocator on the device.  Replaces the Triton kernels
+ *   alloc_extend_kernel  python/sglang/kernels/ops/memory/allocator.py:15-103
+ *   alloc_decode_kernel  python/sglang/kernels/ops/memory/allocator.py:106-140
+ * launched by PagedTokenToKVPoolAllocator.alloc_extend / alloc_decode
+ *   python/sglang/srt/mem_cache/allocator/paged.py:172-260
+ * (oracle: alloc_extend_naive, paged.py:44-102).
+ *
+ * extend: for request b (prefix P_b, new length S_b, last_loc_b = slot of token P_b-1)
+ *   out[start_b + j] = slot of token P_b + j, j < S_b - P_b, start_b = sum_{i<b}(S_i - P_i):
+ *   first the rest of the current partial page (last_loc + 1 + j), then whole pages
+ *   popped in order from free_pages, then the head of one more page.
+ * decode: S_b - 1 tokens are cached; out[b] = last_loc_b + 1 unless S_b - 1 is a
+ *   multiple of page_size, in which case the next free page is opened.
+ * The caller advances its free list by the number of new pages (host arithmetic on
+ * the CPU copies of the lengths, as the reference does).  If fewer than the needed
+ * pages are free, *status is set to 1 (when non-NULL) and the affected rows are left
+ * unwritten; the reference returns None in that case (paged.py:214-215).
+ * prefix_lens/seq_lens/last_loc share len_dtype; free_pages and out have their own.
+ * -------------------------------------------------------------------------- */
+int b200attn_alloc_extend(const void* prefix_lens, const void* seq_lens, const void* last_loc,
+                          int len_dtype, const void* free_pages, int page_dtype, int64_t num_free,
+                          void* out_indices, int out_dtype, int32_t B, int32_t page_size,
+                          int32_t* status, void* stream);
+int b200attn_alloc_decode(const void* seq_lens, const void* last_loc, int len_dtype,
+                          const void* free_pages, int page_dtype, int64_t num_free,
+                          void* out_indices, int out_dtype, int32_t B, int32_t page_size,
+                          int32_t* status, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -53,6 +53,12 @@ SIGNATURES = {
         C.c_int,
         [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, C.c_int, _vp],
     ),
+    "b200attn_alloc_extend": (
+        C.c_int, [_vp, _vp, _vp, C.c_int, _vp, C.c_int, _i64, _vp, C.c_int, _i32, _i32, _vp, _vp],
+    ),
+    "b200attn_alloc_decode": (
+        C.c_int, [_vp, _vp, C.c_int, _vp, C.c_int, _i64, _vp, C.c_int, _i32, _i32, _vp, _vp],
+    ),
     "b200attn_rope_store": (
         C.c_int,
         [_vp, _vp, _vp, _vp, _vp, _vp, C.c_int, _vp, C.c_int, _i64, _vp, C.c_int, _i64, _vp, C.c_int, _i64,

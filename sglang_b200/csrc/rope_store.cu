@@ -43,6 +43,7 @@ struct RopeParams {
   int sec0, sec1, sec2;  // M-RoPE sections (pairs per axis); sec0 < 0 = none
   int loc_dtype, pos_dtype;
   int interleaved, neox, store;
+  int cache_vec16;  // cos/sin rows and halves are 16-byte aligned
 };
 
 template <bool kBf16>
@@ -88,6 +89,52 @@ __device__ __forceinline__ int mrope_axis(const RopeParams& p, int i) {
   return i < p.sec0 ? 0 : (i < p.sec0 + p.sec1 ? 1 : 2);
 }
 
+// cos/sin of VEC consecutive pairs of one cache row; 16-byte loads when the row base allows it
+template <int VEC, bool kBf16, bool kCacheF32>
+__device__ __forceinline__ void load_cos_sin(const RopeParams& p, int64_t pos, int i0, int half,
+                                             float (&cs)[VEC], float (&sn)[VEC]) {
+  if constexpr (kCacheF32) {
+    const float* cr = reinterpret_cast<const float*>(p.cos_sin) + pos * p.rot;
+    if constexpr (VEC % 4 == 0) {
+      if (p.cache_vec16) {
+#pragma unroll
+        for (int j = 0; j < VEC; j += 4) {
+          const float4 c4 = __ldg(reinterpret_cast<const float4*>(cr + i0 + j));
+          const float4 s4 = __ldg(reinterpret_cast<const float4*>(cr + half + i0 + j));
+          cs[j] = c4.x; cs[j + 1] = c4.y; cs[j + 2] = c4.z; cs[j + 3] = c4.w;
+          sn[j] = s4.x; sn[j + 1] = s4.y; sn[j + 2] = s4.z; sn[j + 3] = s4.w;
+        }
+        return;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      cs[j] = __ldg(cr + i0 + j);
+      sn[j] = __ldg(cr + half + i0 + j);
+    }
+  } else {
+    const uint16_t* cr = reinterpret_cast<const uint16_t*>(p.cos_sin) + pos * p.rot;
+    if constexpr (VEC == 8) {
+      if (p.cache_vec16) {
+        Pack<8> c8, s8;
+        c8.v = __ldg(reinterpret_cast<const uint4*>(cr + i0));
+        s8.v = __ldg(reinterpret_cast<const uint4*>(cr + half + i0));
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          cs[j] = to_f<kBf16>(c8.e[j]);
+          sn[j] = to_f<kBf16>(s8.e[j]);
+        }
+        return;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      cs[j] = to_f<kBf16>(__ldg(cr + i0 + j));
+      sn[j] = to_f<kBf16>(__ldg(cr + half + i0 + j));
+    }
+  }
+}
+
 template <int VEC, bool kBf16, bool kCacheF32, bool kNative>
 __global__ void __launch_bounds__(256) rope_store_kernel(const RopeParams p) {
   using V = typename VecOf<VEC>::type;
@@ -99,10 +146,10 @@ __global__ void __launch_bounds__(256) rope_store_kernel(const RopeParams p) {
   const int nkp = p.store ? p.Hkv * pass_items : 0;
   const int nv = p.store ? p.Hkv * v_items : 0;
   const int per_tok = nq + nk + nkp + nv;
-  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid >= p.T * per_tok) return;
-  const int64_t t = gid / per_tok;
-  int it = (int)(gid - t * per_tok);
+  // grid = (T, ceil(per_tok / 256)): no 64-bit division on the index path
+  const int64_t t = blockIdx.x;
+  int it = blockIdx.y * blockDim.x + threadIdx.x;
+  if (it >= per_tok) return;
 
   int64_t slot = -1;
   bool do_store = false;
@@ -154,21 +201,13 @@ __global__ void __launch_bounds__(256) rope_store_kernel(const RopeParams p) {
   if (p.sec0 < 0) {
     int64_t pos = load_index(p.pos, p.pos_dtype, t);
     pos = pos < 0 ? 0 : (pos >= p.cache_rows ? p.cache_rows - 1 : pos);
-    if constexpr (kCacheF32) {
-      const float* cr = reinterpret_cast<const float*>(p.cos_sin) + pos * p.rot;
-#pragma unroll
-      for (int j = 0; j < VEC; ++j) {
-        cs[j] = __ldg(cr + i0 + j);
-        sn[j] = __ldg(cr + half + i0 + j);
-      }
-    } else {
-      const uint16_t* cr = reinterpret_cast<const uint16_t*>(p.cos_sin) + pos * p.rot;
-#pragma unroll
-      for (int j = 0; j < VEC; ++j) {
-        cs[j] = to_f<kBf16>(__ldg(cr + i0 + j));
-        sn[j] = to_f<kBf16>(__ldg(cr + half + i0 + j));
-      }
-    }
+    load_cos_sin<VEC, kBf16, kCacheF32>(p, pos, i0, half, cs, sn);
+  } else if (!p.interleaved && mrope_axis(p, i0) == mrope_axis(p, i0 + VEC - 1)) {
+    // the whole chunk lies in one section: one position, vector loads
+    const int ax = mrope_axis(p, i0);
+    int64_t pos = load_index(p.pos, p.pos_dtype, ax * p.pos_axis_stride + t);
+    pos = pos < 0 ? 0 : (pos >= p.cache_rows ? p.cache_rows - 1 : pos);
+    load_cos_sin<VEC, kBf16, kCacheF32>(p, pos, i0, half, cs, sn);
   } else {
     int64_t pos3[3];
 #pragma unroll
@@ -243,15 +282,14 @@ static int launch_rope(const RopeParams& p, int elem_dtype, int cache_dtype, int
   const int half = p.rot / 2;
   const int64_t per_tok = (int64_t)(p.Hq + p.Hkv) * (half / VEC) +
                           (p.store ? (int64_t)p.Hkv * ((p.D - p.rot) / VEC + p.Dv / VEC) : 0);
-  const int64_t threads = p.T * per_tok;
-  const int64_t blocks = (threads + 255) / 256;
-  B2_CHECK_ARG(blocks < (1ll << 31), "rope_store: too many work items");
+  B2_CHECK_ARG(p.T < (1ll << 31) && per_tok < 65535ll * 256, "rope_store: too many work items");
+  const dim3 blocks((unsigned)p.T, (unsigned)((per_tok + 255) / 256));
   const bool bf16 = elem_dtype == B200ATTN_BF16;
   const bool cf32 = cache_dtype == B200ATTN_FP32;
   const bool native = mode == B200ATTN_ROPE_NATIVE;
 #define B2_ROPE(BF, CF, NA)                                                                  \
   if (bf16 == BF && cf32 == CF && native == NA) {                                            \
-    rope_store_kernel<VEC, BF, CF, NA><<<(unsigned)blocks, 256, 0, st>>>(p);                 \
+    rope_store_kernel<VEC, BF, CF, NA><<<blocks, 256, 0, st>>>(p);                 \
     B2_LAUNCH_CHECK();                                                                       \
     return B200ATTN_OK;                                                                      \
   }
@@ -335,6 +373,10 @@ extern "C" int b200attn_rope_store(void* q, void* k, const void* v, void* k_cach
             ((uint64_t)(uintptr_t)k_cache >> 1) | ((uint64_t)(uintptr_t)v_cache >> 1);
   } else {
     bits |= (uint64_t)(D - rotary_dim);
+  }
+  {
+    const int64_t esz = cache_dtype == B200ATTN_FP32 ? 4 : 2;
+    p.cache_vec16 = ((uintptr_t)cos_sin_cache % 16 == 0) && ((rotary_dim / 2) * esz % 16 == 0);
   }
   cudaStream_t st = (cudaStream_t)stream;
   if ((bits & 7) == 0) return launch_rope<8>(p, elem_dtype, cache_dtype, mode, st);

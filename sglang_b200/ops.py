@@ -203,6 +203,49 @@ def apply_rope_with_cos_sin_cache_inplace(
     check(rc, "b200attn_rope_store")
 
 
+# ---------------------------------------------------------------------- allocator
+def alloc_extend(prefix_lens: torch.Tensor, seq_lens: torch.Tensor, last_loc: torch.Tensor,
+                 free_pages: torch.Tensor, out_indices: torch.Tensor, page_size: int,
+                 status: Optional[torch.Tensor] = None) -> None:
+    """Fill ``out_indices`` (``[sum(seq_lens - prefix_lens)]``) with the KV slots of every new token.
+
+    Mirrors ``alloc_extend_kernel[(bs,)](prefix_lens, seq_lens, last_loc, free_pages, out_indices, ...)``
+    (python/sglang/kernels/ops/memory/allocator.py:15-103); ``status`` (int32[1]) is set to 1 when the free
+    list is too short."""
+    _require_cuda(prefix_lens, seq_lens, last_loc, free_pages, out_indices, status)
+    B = seq_lens.numel()
+    if prefix_lens.numel() != B or last_loc.numel() != B:
+        raise ValueError("alloc_extend: prefix_lens, seq_lens and last_loc disagree on the batch size")
+    if not (prefix_lens.dtype == seq_lens.dtype == last_loc.dtype):
+        raise TypeError("alloc_extend: prefix_lens, seq_lens and last_loc must share a dtype")
+    for t in (prefix_lens, seq_lens, last_loc, free_pages, out_indices):
+        if not t.is_contiguous():
+            raise ValueError("alloc_extend: tensors must be contiguous")
+    rc = _lib.load().b200attn_alloc_extend(
+        prefix_lens.data_ptr(), seq_lens.data_ptr(), last_loc.data_ptr(), _idtype(seq_lens), free_pages.data_ptr(),
+        _idtype(free_pages), free_pages.numel(), out_indices.data_ptr(), _idtype(out_indices), B, page_size,
+        _ptr(status), _stream())
+    check(rc, "b200attn_alloc_extend")
+
+
+def alloc_decode(seq_lens: torch.Tensor, last_loc: torch.Tensor, free_pages: torch.Tensor,
+                 out_indices: torch.Tensor, page_size: int, status: Optional[torch.Tensor] = None) -> None:
+    """One new slot per running request (allocator.py:106-140)."""
+    _require_cuda(seq_lens, last_loc, free_pages, out_indices, status)
+    B = seq_lens.numel()
+    if last_loc.numel() != B or out_indices.numel() != B:
+        raise ValueError("alloc_decode: seq_lens, last_loc and out_indices disagree on the batch size")
+    if seq_lens.dtype != last_loc.dtype:
+        raise TypeError("alloc_decode: seq_lens and last_loc must share a dtype")
+    for t in (seq_lens, last_loc, free_pages, out_indices):
+        if not t.is_contiguous():
+            raise ValueError("alloc_decode: tensors must be contiguous")
+    rc = _lib.load().b200attn_alloc_decode(
+        seq_lens.data_ptr(), last_loc.data_ptr(), _idtype(seq_lens), free_pages.data_ptr(), _idtype(free_pages),
+        free_pages.numel(), out_indices.data_ptr(), _idtype(out_indices), B, page_size, _ptr(status), _stream())
+    check(rc, "b200attn_alloc_decode")
+
+
 # ------------------------------------------------------------------------ metadata
 def build_kv_indices(
     req_to_token: torch.Tensor,

@@ -13,7 +13,7 @@ GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 def golden_files() -> List[str]:
     """Attention-backend fixtures (oracle/gen_golden.py)."""
-    return sorted(p for p in glob.glob(os.path.join(GOLDEN_DIR, "*.pt")) if not os.path.basename(p).startswith("rope_"))
+    return sorted(p for p in glob.glob(os.path.join(GOLDEN_DIR, "*.pt")) if not os.path.basename(p).startswith(("rope_", "alloc_")))
 
 
 def rope_golden_files() -> List[str]:
