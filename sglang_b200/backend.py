@@ -213,6 +213,8 @@ class B200AttnBackend(_Base):
         g.kv_indptr = torch.zeros(max_bs + 1, dtype=torch.int32, device=dev)
         g.kv_indices = torch.zeros(max_bs * self.max_context_len, dtype=torch.int32, device=dev)
         g.cache_seqlens_int32 = torch.zeros(max_bs, dtype=torch.int32, device=dev)
+        g.qo_indptr = torch.zeros(max_bs + 1, dtype=torch.int32, device=dev)  # full-graph / breakable-graph extend
+        g.max_num_tokens = max_num_tokens
         g.max_splits_cap = max_splits_cap
         g.workspace = None
         if num_q_heads is not None and head_dim is not None:
@@ -227,9 +229,10 @@ class B200AttnBackend(_Base):
         """Refill the static decode metadata before capture / replay (sync-free)."""
         fb = forward_batch
         mode = fb.forward_mode
-        if self._graph is None or not mode.is_decode_or_idle():
+        spec = mode.is_target_verify() or mode.is_draft_extend_v2() or getattr(fb, "spec_info", None) is not None
+        if self._graph is None or spec or getattr(fb, "encoder_lens", None) is not None:
             if in_capture:
-                raise NotImplementedError("b200 backend: only DECODE can be captured in a CUDA graph")
+                raise NotImplementedError("b200 backend: only DECODE / EXTEND / MIXED can be captured in a CUDA graph")
             return B200AttnBackend.init_forward_metadata(self, fb)
         if mode.is_idle():
             self.forward_metadata = None
@@ -238,6 +241,21 @@ class B200AttnBackend(_Base):
         B = int(fb.batch_size)
         if B > g.max_bs:
             raise ValueError(f"b200 backend: batch {B} exceeds cuda-graph max_bs {g.max_bs}")
+        if not mode.is_decode():
+            # Full-graph / breakable-graph prefill (prefill_cuda_graph_runner.py:985-1030): the persistent extend
+            # kernel derives its work list from qo_indptr ON THE DEVICE, so one captured launch serves any ragged
+            # batch that fits the static buffers.  Padded requests carry extend_len 0 and are skipped.  No row is
+            # routed to the decode kernel here (that split is a host decision).
+            self._build(fb, fb.seq_lens, g.kv_indptr, g.kv_indices, qo_lens=fb.extend_seq_lens,
+                        qo_indptr=g.qo_indptr)
+            g.cache_seqlens_int32[:B].copy_(fb.seq_lens[:B])
+            md = ForwardMetadata(
+                kv_indptr=g.kv_indptr, kv_indices=g.kv_indices, qo_indptr=g.qo_indptr, batch_size=B,
+                cache_seqlens_int32=g.cache_seqlens_int32[:B], max_extend_len=int(g.max_num_tokens),
+                num_extend_tokens=0, min_chunk=self.MIN_CHUNK)
+            md._graph = True
+            self.forward_metadata = md
+            return
         self._build(fb, fb.seq_lens, g.kv_indptr, g.kv_indices)
         g.cache_seqlens_int32[:B].copy_(fb.seq_lens[:B])
         self.forward_metadata = ForwardMetadata(
@@ -248,6 +266,27 @@ class B200AttnBackend(_Base):
 
     def init_forward_metadata_in_graph(self, forward_batch) -> None:
         pass  # nothing is recomputed inside the graph: the kernels read the static buffers
+
+    # Breakable-CUDA-graph prefill with captured metadata (base_attn_backend.py:124-129,163-188): the metadata
+    # object created at capture keeps its tensor addresses; replay refills them in place.
+    use_captured_forward_metadata_for_breakable_cuda_graph = True
+
+    def init_forward_metadata_for_breakable_cuda_graph_capture(self, forward_batch):
+        if self._graph is None:
+            raise RuntimeError("b200 backend: call init_cuda_graph_state before graph capture")
+        self.init_forward_metadata_out_graph(forward_batch, in_capture=True)
+        return self.forward_metadata
+
+    def prepare_forward_metadata_for_breakable_cuda_graph_replay(self, capture_metadata, forward_batch, *,
+                                                                 static_forward_batch=None) -> None:
+        fb = static_forward_batch if static_forward_batch is not None else forward_batch
+        self.init_forward_metadata_out_graph(fb)
+        md = self.forward_metadata
+        if md is not None and capture_metadata is not None:
+            # same static tensors; refresh the per-replay python fields on the captured object
+            capture_metadata.batch_size = md.batch_size
+            capture_metadata.cache_seqlens_int32 = md.cache_seqlens_int32
+            self.forward_metadata = capture_metadata
 
     # ------------------------------------------------------------------ forward
     def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, **kwargs):
@@ -303,7 +342,9 @@ class B200AttnBackend(_Base):
             ws = self._workspace(ops.extend_workspace_bytes(B, q2.shape[0], Hq))
             ops.extend_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.qo_indptr, md.kv_indptr,
                                  md.kv_indices, layer.scaling, causal=causal, page_size=self.page_size,
-                                 max_qo_len=md.max_extend_len, total_q=md.num_extend_tokens, workspace=ws,
+                                 max_qo_len=md.max_extend_len,
+                                 total_q=q2.shape[0] if getattr(md, "_graph", False) else md.num_extend_tokens,
+                                 workspace=ws,
                                  skip_single_rows=md.num_dec > 0)
         if md.num_dec > 0:  # a single query row sees all of its keys, causal or not
             Hkv = layer.tp_k_head_num

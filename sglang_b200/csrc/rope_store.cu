@@ -21,6 +21,8 @@
 // contiguous bytes for gpt-j), the cos/sin chunk through the read-only path (shared by every head of the
 // token => L1/L2 resident), two 16-byte stores in place and, for k, two more into the pool row.  Pass-through
 // columns of k (rotary_dim < head_dim) and all of v are plain 16-byte copies done by the trailing work items.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace b200attn {
@@ -114,15 +116,15 @@ __device__ __forceinline__ void load_cos_sin(const RopeParams& p, int64_t pos, i
     }
   } else {
     const uint16_t* cr = reinterpret_cast<const uint16_t*>(p.cos_sin) + pos * p.rot;
-    if constexpr (VEC == 8) {
-      if (p.cache_vec16) {
-        Pack<8> c8, s8;
-        c8.v = __ldg(reinterpret_cast<const uint4*>(cr + i0));
-        s8.v = __ldg(reinterpret_cast<const uint4*>(cr + half + i0));
+    if constexpr (VEC == 4) {
+      if (p.cache_vec16) {  // rows / halves 16-byte aligned and i0 % 4 == 0 => 8-byte aligned
+        Pack<4> c4, s4;
+        c4.v = __ldg(reinterpret_cast<const uint2*>(cr + i0));
+        s4.v = __ldg(reinterpret_cast<const uint2*>(cr + half + i0));
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          cs[j] = to_f<kBf16>(c8.e[j]);
-          sn[j] = to_f<kBf16>(s8.e[j]);
+        for (int j = 0; j < 4; ++j) {
+          cs[j] = to_f<kBf16>(c4.e[j]);
+          sn[j] = to_f<kBf16>(s4.e[j]);
         }
         return;
       }
@@ -135,69 +137,21 @@ __device__ __forceinline__ void load_cos_sin(const RopeParams& p, int64_t pos, i
   }
 }
 
-template <int VEC, bool kBf16, bool kCacheF32, bool kNative>
-__global__ void __launch_bounds__(256) rope_store_kernel(const RopeParams p) {
-  using V = typename VecOf<VEC>::type;
-  const int half = p.rot >> 1;
-  const int rot_items = half / VEC;                 // per head
-  const int pass_items = (p.D - p.rot) / VEC;       // per k head (pool copy only)
-  const int v_items = p.Dv / VEC;                   // per v head
-  const int nq = p.Hq * rot_items, nk = p.Hkv * rot_items;
-  const int nkp = p.store ? p.Hkv * pass_items : 0;
-  const int nv = p.store ? p.Hkv * v_items : 0;
-  const int per_tok = nq + nk + nkp + nv;
-  // grid = (T, ceil(per_tok / 256)): no 64-bit division on the index path
-  const int64_t t = blockIdx.x;
-  int it = blockIdx.y * blockDim.x + threadIdx.x;
-  if (it >= per_tok) return;
-
-  int64_t slot = -1;
-  bool do_store = false;
-  if (p.store && it >= nq) {
-    slot = load_index(p.loc, p.loc_dtype, t);
-    if (slot == p.skip_index) {
-      do_store = false;  // kvcache.cuh:215
-    } else if (slot < 0 || slot >= p.size_limit) {
-      if (it == nq && p.oob_count != nullptr) atomicAdd(p.oob_count, 1);
-    } else {
-      do_store = true;
-    }
+// slot of token t for the pool writes; false = skip (reserved slot, kvcache.cuh:215, or out of range)
+__device__ __forceinline__ bool store_slot(const RopeParams& p, int64_t t, bool count_oob,
+                                           int64_t& slot) {
+  slot = load_index(p.loc, p.loc_dtype, t);
+  if (slot == p.skip_index) return false;
+  if (slot < 0 || slot >= p.size_limit) {
+    if (count_oob && p.oob_count != nullptr) atomicAdd(p.oob_count, 1);
+    return false;
   }
+  return true;
+}
 
-  if (it >= nq + nk) {  // plain copies into the pool
-    if (!do_store) return;
-    it -= nq + nk;
-    const uint8_t* src;
-    uint8_t* dst;
-    if (it < nkp) {
-      const int h = it / pass_items, c = it - h * pass_items;
-      const int64_t col = (int64_t)h * p.D + p.rot + c * VEC;
-      src = p.k + (t * p.k_stride + col) * 2;
-      dst = p.k_cache + (slot * p.kc_stride + col) * 2;
-    } else {
-      it -= nkp;
-      const int64_t col = (int64_t)it * VEC;
-      src = p.v + (t * p.v_stride + col) * 2;
-      dst = p.v_cache + (slot * p.vc_stride + col) * 2;
-    }
-    *reinterpret_cast<V*>(dst) = *reinterpret_cast<const V*>(src);
-    return;
-  }
-
-  const bool is_k = it >= nq;
-  if (is_k) it -= nq;
-  const int h = it / rot_items, c = it - h * rot_items;
-  const int i0 = c * VEC;  // first rotation pair of this thread
-  uint8_t* row = is_k ? p.k + (t * p.k_stride + (int64_t)h * p.D) * 2
-                      : p.q + (t * p.q_stride + (int64_t)h * p.D) * 2;
-  // neox: pair i = (x[i], x[i+half]);  gpt-j: pair i = (x[2i], x[2i+1])
-  V* pa = reinterpret_cast<V*>(row + (p.neox ? i0 : 2 * i0) * 2);
-  V* pb = reinterpret_cast<V*>(row + (p.neox ? i0 + half : 2 * i0 + VEC) * 2);
-  Pack<VEC> a, b;
-  a.v = *pa;
-  b.v = *pb;
-
-  float cs[VEC], sn[VEC];
+template <int VEC, bool kBf16, bool kCacheF32>
+__device__ __forceinline__ void token_cos_sin(const RopeParams& p, int64_t t, int i0, int half,
+                                              float (&cs)[VEC], float (&sn)[VEC]) {
   if (p.sec0 < 0) {
     int64_t pos = load_index(p.pos, p.pos_dtype, t);
     pos = pos < 0 ? 0 : (pos >= p.cache_rows ? p.cache_rows - 1 : pos);
@@ -230,23 +184,27 @@ __global__ void __launch_bounds__(256) rope_store_kernel(const RopeParams p) {
       }
     }
   }
+}
 
-  // element j of the thread: neox -> x1 = a.e[j], x2 = b.e[j]; gpt-j -> the 2*VEC contiguous values
-  // (a | b) hold pairs (2j, 2j+1)
-  Pack<VEC> oa, ob;
+// rotate pairs [j0, j0+G) of the thread IN PLACE in (a | b); element j: neox -> x1 = a.e[j], x2 = b.e[j];
+// gpt-j -> the 2*VEC contiguous values (a | b) hold pairs (2j, 2j+1)
+template <int VEC, int G, bool kBf16, bool kNative>
+__device__ __forceinline__ void rotate(Pack<VEC>& a, Pack<VEC>& b, int j0, const float (&cs)[G],
+                                       const float (&sn)[G], bool neox) {
 #pragma unroll
-  for (int j = 0; j < VEC; ++j) {
+  for (int g = 0; g < G; ++g) {
+    const int j = j0 + g;
+    const int e1 = 2 * j, e2 = 2 * j + 1;
     uint16_t r1, r2;
-    if (p.neox) {
+    if (neox) {
       r1 = a.e[j];
       r2 = b.e[j];
     } else {
-      const int e1 = 2 * j, e2 = 2 * j + 1;
       r1 = e1 < VEC ? a.e[e1 % VEC] : b.e[e1 % VEC];
       r2 = e2 < VEC ? a.e[e2 % VEC] : b.e[e2 % VEC];
     }
     const float x1 = to_f<kBf16>(r1), x2 = to_f<kBf16>(r2);
-    float c_ = cs[j], s_ = sn[j];
+    float c_ = cs[g], s_ = sn[g];
     float o1, o2;
     if constexpr (kNative) {
       c_ = round_elem<kBf16>(c_);
@@ -258,21 +216,100 @@ __global__ void __launch_bounds__(256) rope_store_kernel(const RopeParams p) {
       o2 = __fadd_rn(__fmul_rn(x2, c_), __fmul_rn(x1, s_));
     }
     const uint16_t w1 = from_f<kBf16>(o1), w2 = from_f<kBf16>(o2);
-    if (p.neox) {
-      oa.e[j] = w1;
-      ob.e[j] = w2;
+    if (neox) {
+      a.e[j] = w1;
+      b.e[j] = w2;
     } else {
-      const int e1 = 2 * j, e2 = 2 * j + 1;
-      if (e1 < VEC) oa.e[e1 % VEC] = w1; else ob.e[e1 % VEC] = w1;
-      if (e2 < VEC) oa.e[e2 % VEC] = w2; else ob.e[e2 % VEC] = w2;
+      if (e1 < VEC) a.e[e1 % VEC] = w1; else b.e[e1 % VEC] = w1;
+      if (e2 < VEC) a.e[e2 % VEC] = w2; else b.e[e2 % VEC] = w2;
     }
   }
-  *pa = oa.v;
-  *pb = ob.v;
-  if (is_k && do_store) {
-    uint8_t* crow = p.k_cache + (slot * p.kc_stride + (int64_t)h * p.D) * 2;
-    *reinterpret_cast<V*>(crow + (p.neox ? i0 : 2 * i0) * 2) = oa.v;
-    *reinterpret_cast<V*>(crow + (p.neox ? i0 + half : 2 * i0 + VEC) * 2) = ob.v;
+}
+
+// grid = (ceil(T / TOK), ceil(per_tok / 256)).  A thread owns work item `it` of TOK consecutive tokens and issues
+// all of their 16-byte loads before the first dependent instruction (TOK * 32 B in flight per thread).
+template <int VEC, bool kBf16, bool kCacheF32, bool kNative, int TOK>
+__global__ void __launch_bounds__(256, TOK == 1 ? 6 : 4) rope_store_kernel(const RopeParams p) {
+  using V = typename VecOf<VEC>::type;
+  const int half = p.rot >> 1;
+  const int rot_items = half / VEC;                 // per head
+  const int pass_items = (p.D - p.rot) / VEC;       // per k head (pool copy only)
+  const int v_items = p.Dv / VEC;                   // per v head
+  const int nq = p.Hq * rot_items, nk = p.Hkv * rot_items;
+  const int nkp = p.store ? p.Hkv * pass_items : 0;
+  const int nv = p.store ? p.Hkv * v_items : 0;
+  const int per_tok = nq + nk + nkp + nv;
+  const int64_t t0 = (int64_t)blockIdx.x * TOK;
+  int it = blockIdx.y * blockDim.x + threadIdx.x;
+  if (it >= per_tok) return;
+
+  if (it >= nq + nk) {  // plain copies into the pool: k pass-through columns, then v
+    it -= nq + nk;
+    const bool is_kp = it < nkp;
+    int64_t col, sstride, dstride;
+    const uint8_t* sbase;
+    uint8_t* dbase;
+    if (is_kp) {
+      const int h = it / pass_items, c = it - h * pass_items;
+      col = (int64_t)h * p.D + p.rot + c * VEC;
+      sbase = p.k; dbase = p.k_cache; sstride = p.k_stride; dstride = p.kc_stride;
+    } else {
+      col = (int64_t)(it - nkp) * VEC;
+      sbase = p.v; dbase = p.v_cache; sstride = p.v_stride; dstride = p.vc_stride;
+    }
+    V val[TOK];
+    int64_t slot[TOK];
+    bool ok[TOK];
+#pragma unroll
+    for (int u = 0; u < TOK; ++u) {
+      const int64_t t = t0 + u;
+      ok[u] = t < p.T && store_slot(p, t, false, slot[u]);
+      if (ok[u]) val[u] = *reinterpret_cast<const V*>(sbase + (t * sstride + col) * 2);
+    }
+#pragma unroll
+    for (int u = 0; u < TOK; ++u)
+      if (ok[u]) *reinterpret_cast<V*>(dbase + (slot[u] * dstride + col) * 2) = val[u];
+    return;
+  }
+
+  const bool is_k = it >= nq;
+  if (is_k) it -= nq;
+  const int h = it / rot_items, c = it - h * rot_items;
+  const int i0 = c * VEC;  // first rotation pair of this thread
+  // neox: pair i = (x[i], x[i+half]);  gpt-j: pair i = (x[2i], x[2i+1])
+  const int off_a = (p.neox ? i0 : 2 * i0) * 2, off_b = (p.neox ? i0 + half : 2 * i0 + VEC) * 2;
+  uint8_t* const base = is_k ? p.k : p.q;
+  const int64_t stride = is_k ? p.k_stride : p.q_stride;
+  Pack<VEC> a[TOK], b[TOK];
+#pragma unroll
+  for (int u = 0; u < TOK; ++u) {
+    const int64_t t = t0 + u;
+    if (t < p.T) {
+      const uint8_t* row = base + (t * stride + (int64_t)h * p.D) * 2;
+      a[u].v = *reinterpret_cast<const V*>(row + off_a);
+      b[u].v = *reinterpret_cast<const V*>(row + off_b);
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < TOK; ++u) {
+    const int64_t t = t0 + u;
+    if (t >= p.T) break;
+    constexpr int G = VEC < 4 ? VEC : 4;  // cos/sin live 4 pairs at a time (register budget)
+#pragma unroll
+    for (int j0 = 0; j0 < VEC; j0 += G) {
+      float cs[G], sn[G];
+      token_cos_sin<G, kBf16, kCacheF32>(p, t, i0 + j0, half, cs, sn);
+      rotate<VEC, G, kBf16, kNative>(a[u], b[u], j0, cs, sn, p.neox);
+    }
+    uint8_t* row = base + (t * stride + (int64_t)h * p.D) * 2;
+    *reinterpret_cast<V*>(row + off_a) = a[u].v;
+    *reinterpret_cast<V*>(row + off_b) = b[u].v;
+    int64_t slot;
+    if (is_k && p.store && store_slot(p, t, it == 0, slot)) {
+      uint8_t* crow = p.k_cache + (slot * p.kc_stride + (int64_t)h * p.D) * 2;
+      *reinterpret_cast<V*>(crow + off_a) = a[u].v;
+      *reinterpret_cast<V*>(crow + off_b) = b[u].v;
+    }
   }
 }
 
@@ -283,13 +320,18 @@ static int launch_rope(const RopeParams& p, int elem_dtype, int cache_dtype, int
   const int64_t per_tok = (int64_t)(p.Hq + p.Hkv) * (half / VEC) +
                           (p.store ? (int64_t)p.Hkv * ((p.D - p.rot) / VEC + p.Dv / VEC) : 0);
   B2_CHECK_ARG(p.T < (1ll << 31) && per_tok < 65535ll * 256, "rope_store: too many work items");
-  const dim3 blocks((unsigned)p.T, (unsigned)((per_tok + 255) / 256));
+  // measured (tools/bench_rope.py, T = 131072): 2 tokens per thread 4.56 TB/s, 1 token 3.99, 4 tokens 3.48;
+  // small batches keep one token per thread so that every SM gets work
+  int tok = p.T * ((per_tok + 255) / 256) >= 8 * 148 * 2 ? 2 : 1;
+  if (const char* e = getenv("B200ATTN_ROPE_TOK")) tok = atoi(e) == 2 ? 2 : 1;  // dev ablation hook
+  const dim3 blocks((unsigned)((p.T + tok - 1) / tok), (unsigned)((per_tok + 255) / 256));
   const bool bf16 = elem_dtype == B200ATTN_BF16;
   const bool cf32 = cache_dtype == B200ATTN_FP32;
   const bool native = mode == B200ATTN_ROPE_NATIVE;
 #define B2_ROPE(BF, CF, NA)                                                                  \
   if (bf16 == BF && cf32 == CF && native == NA) {                                            \
-    rope_store_kernel<VEC, BF, CF, NA><<<blocks, 256, 0, st>>>(p);                 \
+    if (tok == 2) rope_store_kernel<VEC, BF, CF, NA, 2><<<blocks, 256, 0, st>>>(p);          \
+    else rope_store_kernel<VEC, BF, CF, NA, 1><<<blocks, 256, 0, st>>>(p);                   \
     B2_LAUNCH_CHECK();                                                                       \
     return B200ATTN_OK;                                                                      \
   }

@@ -190,3 +190,69 @@ def test_backend_extend_all_single_rows():
     ref = oracle.attention_fp32(sc.q, kc, vc, sc.req_to_token, sc.req_pool_indices, torch.tensor(sc.seq_lens),
                                 torch.tensor(ext), 8, 2, 128, sc.scaling, causal=True)
     assert_close_attn(o, ref, "all-single extend")
+
+
+def test_backend_cuda_graph_extend_replay():
+    """Full-graph prefill: capture ONE extend step over static buffers, replay it with other ragged batches
+    (fewer real requests, zero-length padded rows, a single-token row) — prefill_cuda_graph_runner.py:985-1030."""
+    Hq, Hkv, D, page, B, TCAP = 8, 2, 128, 16, 4, 1024
+    pre0, ext0 = [64, 0, 300, 17], [200, 128, 40, 333]
+    sc = make_scenario([0] * B, [TCAP] * B, Hq, Hkv, D, page, seed=91, pool_slack=1.5)  # sizes the table and the pool
+    backend, req_pool, kv_pool = _setup(sc, False)
+    backend.init_cuda_graph_state(B, TCAP, num_q_heads=Hq, head_dim=D)
+    layer = RadixAttention(Hq, D, sc.scaling, Hkv, 0)
+    g = torch.Generator().manual_seed(1)
+    s_req = sc.req_pool_indices.to(DEV)
+    s_seq = torch.zeros(B, dtype=torch.int64, device=DEV)
+    s_pre = torch.zeros(B, dtype=torch.int64, device=DEV)
+    s_ext = torch.zeros(B, dtype=torch.int32, device=DEV)
+    s_loc = torch.zeros(TCAP, dtype=torch.int64, device=DEV)   # padded tokens write the reserved slot 0
+    s_q = torch.zeros((TCAP, Hq * D), dtype=torch.bfloat16, device=DEV)
+    s_k = torch.zeros((TCAP, Hkv, D), dtype=torch.bfloat16, device=DEV)
+    s_v = torch.zeros((TCAP, Hkv, D), dtype=torch.bfloat16, device=DEV)
+    fb = ForwardBatch(forward_mode=ForwardMode.EXTEND, batch_size=B, req_pool_indices=s_req, seq_lens=s_seq,
+                      out_cache_loc=s_loc, seq_lens_sum=0, extend_seq_lens=s_ext, extend_prefix_lens=s_pre,
+                      attn_backend=backend)
+
+    def fill(pre, ext, seed):
+        sc2 = make_scenario(pre, ext, Hq, Hkv, D, page, seed=seed, pool_slack=1.0)
+        n = min(req_pool.req_to_token.shape[1], sc2.req_to_token.shape[1])
+        req_pool.req_to_token.zero_()
+        req_pool.req_to_token[:, :n].copy_(sc2.req_to_token[:, :n] % kv_pool.k_buffer[0].shape[0])
+        T = sum(ext)
+        s_seq.copy_(torch.tensor([p + e for p, e in zip(pre, ext)]))
+        s_pre.copy_(torch.tensor(pre))
+        s_ext.copy_(torch.tensor(ext, dtype=torch.int32))
+        loc = torch.cat([req_pool.req_to_token[b + 1, pre[b]:pre[b] + ext[b]] for b in range(B)]).long()
+        s_loc.zero_()
+        s_loc[:T].copy_(loc)
+        s_q.zero_(); s_k.zero_(); s_v.zero_()
+        s_q[:T].copy_(sc2.q); s_k[:T].copy_(sc2.k); s_v[:T].copy_(sc2.v)
+        return T, loc
+
+    fill(pre0, ext0, 91)
+    stream = torch.cuda.Stream()
+    stream.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(stream):
+        md0 = backend.init_forward_metadata_for_breakable_cuda_graph_capture(fb)
+        layer(s_q, s_k, s_v, fb)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=stream):
+            backend.init_forward_metadata_in_graph(fb)
+            s_out = layer(s_q, s_k, s_v, fb)
+    torch.cuda.current_stream().wait_stream(stream)
+    assert backend.use_captured_forward_metadata_for_breakable_cuda_graph
+
+    for pre, ext, seed in [(pre0, ext0, 92), ([0, 5, 0, 0], [700, 1, 0, 0], 93), ([511, 0, 40, 0], [1, 0, 129, 600], 94),
+                           ([10, 20, 30, 40], [128, 256, 128, 512], 95)]:
+        T, loc = fill(pre, ext, seed)
+        backend.prepare_forward_metadata_for_breakable_cuda_graph_replay(md0, fb)
+        assert backend.forward_metadata is md0
+        graph.replay()
+        torch.cuda.synchronize()
+        kc, vc = kv_pool.k_buffer[0], kv_pool.v_buffer[0]
+        ref = oracle.attention_fp32(s_q[:T], kc, vc, req_pool.req_to_token, s_req, s_seq.cpu(), s_ext.cpu(), Hq, Hkv, D,
+                                    sc.scaling, causal=True)
+        assert_close_attn(s_out[:T], ref, f"extend graph replay {ext}")
+        assert torch.equal(kc[loc], s_k[:T])
