@@ -130,6 +130,15 @@ int b200attn_build_page_table(const int32_t* req_to_token, int64_t req_to_token_
  * touched when max_splits > 1.  The split policy is a pure function of
  * (kv length, max_splits, min_chunk) evaluated on the device, so CUDA-graph
  * replay needs no host-side recomputation.
+ *
+ * Feature flags shared with b200attn_extend (triton_backend.py:1405-1416,
+ * decode_attention.py:986-988, extend_attention.py:480-486,546-547,721-723):
+ *   window_left >= 0 : a query at position q_id sees only keys kv_id >= q_id -
+ *                      window_left (window_left + 1 keys; decode: q_id = L - 1);
+ *                      whole tiles outside the window are never loaded.  -1 = off.
+ *   logit_cap  > 0   : scores become logit_cap * tanh(sm_scale * qk / logit_cap).  0 = off.
+ *   sinks (nullable float[Hq]): exp(sinks[h] - max) is added to the softmax
+ *                      denominator of q head h (attention sinks).
  * -------------------------------------------------------------------------- */
 int64_t b200attn_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t D, int32_t max_splits);
 
@@ -138,7 +147,8 @@ int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
                     float* lse, const int32_t* kv_indptr, const int32_t* kv_indices,
                     const int32_t* q_rows, const int32_t* req_ids, int32_t B,
                     int32_t Hq, int32_t Hkv, int32_t D, int dtype, float sm_scale,
-                    int32_t max_splits, int32_t min_chunk, void* workspace,
+                    int32_t max_splits, int32_t min_chunk, int32_t window_left,
+                    float logit_cap, const float* sinks, void* workspace,
                     int64_t workspace_bytes, void* stream);
 
 /* --------------------------------------------------------------------------
@@ -176,7 +186,8 @@ int b200attn_extend(const void* q, int64_t q_stride, const void* k_cache,
                     const int32_t* kv_indptr, const int32_t* kv_indices, int32_t B,
                     int64_t total_q_host, int32_t max_qo_len_host, int32_t Hq,
                     int32_t Hkv, int32_t D, int32_t page_size, int dtype, int causal,
-                    float sm_scale, void* workspace, int64_t workspace_bytes,
+                    float sm_scale, int32_t window_left, float logit_cap,
+                    const float* sinks, void* workspace, int64_t workspace_bytes,
                     void* stream);
 
 /* --------------------------------------------------------------------------

@@ -200,7 +200,7 @@ def merge_state(v_a: torch.Tensor, s_a: torch.Tensor, v_b: torch.Tensor, s_b: to
 def attention_fp32(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, req_to_token: torch.Tensor,
                    req_pool_indices: torch.Tensor, seq_lens: torch.Tensor, extend_seq_lens: torch.Tensor,
                    num_q_heads: int, num_kv_heads: int, head_dim: int, scaling: float, causal: bool,
-                   return_lse: bool = False):
+                   return_lse: bool = False, window_left: int = -1, logit_cap: float = 0.0, sinks=None):
     """Independent fp32-softmax reference (works on any device, used at large sizes).
 
     Restates the reference kit's ``_dense_attention_reference``
@@ -208,6 +208,11 @@ def attention_fp32(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor
     and ``decode_attention_fwd_torch`` (test/registered/attention/
     test_triton_attention_kernels.py:106-151): per request, scores in fp32,
     query j (absolute position ``L - E + j``) sees keys ``<= L - E + j`` when causal.
+
+    Feature flags restate the production kernels: ``window_left`` = the kit's extend-window rule
+    ``kv_id >= q_id - window`` (dense_attention.py:831-840, extend_attention.py:480-486); ``logit_cap``:
+    ``cap * tanh(qk / cap)`` (extend_attention.py:546-547); ``sinks`` [Hq]: ``exp(sink - max)`` joins the
+    denominator (extend_attention.py:721-723, decode_attention.py:986-988).
     """
     T = q.shape[0]
     G = num_q_heads // num_kv_heads
@@ -221,12 +226,22 @@ def attention_fp32(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor
         k = k_cache[tokens].float().repeat_interleave(G, dim=1)   # [L, Hq, D]
         v = v_cache[tokens].float().repeat_interleave(G, dim=1)
         s = torch.einsum("ehd,lhd->hel", qf[start:start + E], k) * scaling
+        if logit_cap > 0:
+            s = logit_cap * torch.tanh(s / logit_cap)
+        qpos = torch.arange(L - E, L, device=q.device).view(1, E, 1)
+        kpos = torch.arange(L, device=q.device).view(1, 1, L)
         if causal:
-            qpos = torch.arange(L - E, L, device=q.device).view(1, E, 1)
-            kpos = torch.arange(L, device=q.device).view(1, 1, L)
             s = s.masked_fill(kpos > qpos, -math.inf)
-        lse[start:start + E] = torch.logsumexp(s, dim=-1).transpose(0, 1)
-        p = torch.softmax(s, dim=-1)
+        if window_left >= 0:
+            s = s.masked_fill(kpos < qpos - window_left, -math.inf)
+        if sinks is not None:
+            sk = sinks.to(s.device).float().view(-1, 1, 1).expand(-1, E, 1)
+            full = torch.cat([s, sk], dim=-1)
+            lse[start:start + E] = torch.logsumexp(full, dim=-1).transpose(0, 1)
+            p = torch.softmax(full, dim=-1)[..., :L]
+        else:
+            lse[start:start + E] = torch.logsumexp(s, dim=-1).transpose(0, 1)
+            p = torch.softmax(s, dim=-1)
         out[start:start + E] = torch.einsum("hel,lhd->ehd", p, v)
         start += E
     out = out.view(T, num_q_heads * head_dim)

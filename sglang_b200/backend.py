@@ -114,18 +114,26 @@ class B200AttnBackend(_Base):
         return self._ws
 
     def _check_layer(self, layer, kwargs) -> None:
-        if getattr(layer, "sliding_window_size", -1) not in (None, -1, 0):
-            raise NotImplementedError("b200 backend: sliding_window_size is not supported")
-        if getattr(layer, "logit_cap", 0.0):
-            raise NotImplementedError("b200 backend: logit_cap is not supported")
         if getattr(layer, "is_cross_attention", False):
             raise NotImplementedError("b200 backend: cross attention is not supported")
         if getattr(layer, "v_head_dim", layer.head_dim) != layer.head_dim:
             raise NotImplementedError("b200 backend: v_head_dim != head_dim is not supported")
         if getattr(layer, "k_scale", None) is not None or getattr(layer, "v_scale", None) is not None:
             raise NotImplementedError("b200 backend: fp8 KV cache scales are not supported")
-        if kwargs.get("sinks") is not None:
-            raise NotImplementedError("b200 backend: attention sinks are not supported")
+
+    @staticmethod
+    def _features(layer, kwargs) -> dict:
+        """Per-layer flags of the kernels (triton_backend.py:1405-1416,1515-1530): sliding window, logit cap,
+        attention sinks.  The window rule is the extend kernel's for BOTH modes — a query at q_id sees keys
+        kv_id >= q_id - sliding_window_size (window + 1 keys, extend_attention.py:480-486; the same rule as
+        flashinfer's decode metadata, dense_attention.py:40-48) — so that a running decode computes the same row
+        whether it arrives in a DECODE batch or as an extend_len == 1 row of a MIXED batch."""
+        w = getattr(layer, "sliding_window_size", None)
+        sinks = kwargs.get("sinks")
+        if sinks is not None and sinks.dtype != torch.float32:
+            sinks = sinks.float()
+        return dict(window_left=int(w) if w is not None and w > -1 else -1,
+                    logit_cap=float(getattr(layer, "logit_cap", 0.0) or 0.0), sinks=sinks)
 
     def _store(self, layer, forward_batch, k, v) -> None:
         """KV pool write path (memory_pool.py:2331-2456) through the sm_100a store kernel."""
@@ -321,7 +329,8 @@ class B200AttnBackend(_Base):
                                      md.min_chunk, num_sms=self.num_sms)
             ws = self._workspace(ops.decode_workspace_bytes(B, Hq, D, ms))
         ops.decode_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.kv_indptr, md.kv_indices,
-                             layer.scaling, max_splits=ms, min_chunk=md.min_chunk, workspace=ws, num_items=B)
+                             layer.scaling, max_splits=ms, min_chunk=md.min_chunk, workspace=ws, num_items=B,
+                             **self._features(layer, kwargs))
         return o
 
     def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, **kwargs):
@@ -345,7 +354,7 @@ class B200AttnBackend(_Base):
                                  max_qo_len=md.max_extend_len,
                                  total_q=q2.shape[0] if getattr(md, "_graph", False) else md.num_extend_tokens,
                                  workspace=ws,
-                                 skip_single_rows=md.num_dec > 0)
+                                 skip_single_rows=md.num_dec > 0, **self._features(layer, kwargs))
         if md.num_dec > 0:  # a single query row sees all of its keys, causal or not
             Hkv = layer.tp_k_head_num
             ms = ops.pick_max_splits(md.num_dec, Hkv, Hq // Hkv, md.dec_max_kv_len, md.min_chunk,
@@ -353,7 +362,8 @@ class B200AttnBackend(_Base):
             ws = self._workspace(ops.decode_workspace_bytes(md.num_dec, Hq, D, ms))
             ops.decode_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.kv_indptr, md.kv_indices,
                                  layer.scaling, max_splits=ms, min_chunk=md.min_chunk, workspace=ws,
-                                 q_rows=md.dec_q_rows, req_ids=md.dec_req_ids, num_items=md.num_dec)
+                                 q_rows=md.dec_q_rows, req_ids=md.dec_req_ids, num_items=md.num_dec,
+                                 **self._features(layer, kwargs))
         return o
 
 

@@ -44,7 +44,22 @@ struct DecodeParams {
   int B, Hq, Hkv, G, groups_per_kvh;
   int max_splits, min_chunk;
   float scale_log2;
+  // feature flags: triton_backend.py:1405-1416, decode_attention.py:986-988
+  int window_left;      // >= 0: only keys kv_id >= q_id - window_left (q_id = L - 1); < 0: off
+  float cap_pre;        // logit cap c > 0: x = c * tanh(s * sm_scale / c); cap_pre = sm_scale / c
+  float cap_post;       // c * log2(e); 0 = no cap
+  const float* sinks;   // per q head sink logit (natural units) added to the softmax denominator, or null
 };
+
+// keys of a request that the (single) query row sees: [kv_lo, L)
+__device__ __forceinline__ int window_lo(int L, int window_left) {
+  return window_left >= 0 ? max(0, L - 1 - window_left) : 0;
+}
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 
 template <int D>
 __device__ __forceinline__ uint32_t swz_off(int row, int chunk) {
@@ -71,8 +86,13 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodePara
   const int grp = hg - kvh * p.groups_per_kvh;
   const int req = p.req_ids ? p.req_ids[item] : item;
   const int qrow = p.q_rows ? p.q_rows[item] : item;
-  const int kv_beg = p.kv_indptr[req];
-  const int L = p.kv_indptr[req + 1] - kv_beg;
+  int kv_beg = p.kv_indptr[req];
+  int L = p.kv_indptr[req + 1] - kv_beg;
+  {
+    const int lo = window_lo(L, p.window_left);  // sliding window: drop the keys before it
+    kv_beg += lo;
+    L -= lo;
+  }
   int nsplit, chunk;
   split_policy(L, p.max_splits, p.min_chunk, kDecTile, nsplit, chunk);
   if (split >= nsplit) return;
@@ -182,7 +202,8 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodePara
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const int key = kcol + nb * 8 + (j & 1);
-          const float x = (key < k_hi) ? s[nb][j] * p.scale_log2 : -INFINITY;
+          float x = p.cap_post > 0.f ? p.cap_post * tanh_approx(s[nb][j] * p.cap_pre) : s[nb][j] * p.scale_log2;
+          x = (key < k_hi) ? x : -INFINITY;
           s[nb][j] = x;
           tmax[j >> 1] = fmaxf(tmax[j >> 1], x);
         }
@@ -275,6 +296,7 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodePara
       acc.w += f * x.w;
       l += f * sm_l[w * 16 + r];
     }
+    if (direct && p.sinks != nullptr && l > 0.f) l += fast_exp2(__ldg(p.sinks + h0 + r) * kLog2e - m);
     const float inv = (l > 0.f) ? 1.f / l : 0.f;
     acc.x *= inv;
     acc.y *= inv;
@@ -304,7 +326,8 @@ __global__ void __launch_bounds__(D / 4) decode_merge_kernel(const DecodeParams 
   const int h = blockIdx.x, item = blockIdx.y;
   const int req = p.req_ids ? p.req_ids[item] : item;
   const int qrow = p.q_rows ? p.q_rows[item] : item;
-  const int L = p.kv_indptr[req + 1] - p.kv_indptr[req];
+  int L = p.kv_indptr[req + 1] - p.kv_indptr[req];
+  L -= window_lo(L, p.window_left);
   int nsplit, chunk;
   split_policy(L, p.max_splits, p.min_chunk, kDecTile, nsplit, chunk);
   if (nsplit == 1) return;  // the attention kernel wrote the output directly
@@ -324,6 +347,7 @@ __global__ void __launch_bounds__(D / 4) decode_merge_kernel(const DecodeParams 
     acc.w += f * x.w;
     l += f;
   }
+  if (p.sinks != nullptr && l > 0.f) l += fast_exp2(__ldg(p.sinks + h) * kLog2e - m);
   const float inv = (l > 0.f) ? 1.f / l : 0.f;
   T* dst = reinterpret_cast<T*>(p.o) + (int64_t)qrow * p.o_stride + (int64_t)h * D + c;
   uint2 pk;
@@ -371,10 +395,12 @@ extern "C" int b200attn_decode(const void* q, int64_t q_stride, const void* k_ca
                                float* lse, const int32_t* kv_indptr, const int32_t* kv_indices,
                                const int32_t* q_rows, const int32_t* req_ids, int32_t B,
                                int32_t Hq, int32_t Hkv, int32_t D, int dtype, float sm_scale,
-                               int32_t max_splits, int32_t min_chunk, void* workspace,
+                               int32_t max_splits, int32_t min_chunk, int32_t window_left,
+                               float logit_cap, const float* sinks, void* workspace,
                                int64_t workspace_bytes, void* stream) {
   using namespace b200attn;
   B2_CHECK_ARG(B >= 0, "decode: negative batch");
+  B2_CHECK_ARG(logit_cap >= 0.f, "decode: negative logit_cap");
   if (B == 0) return B200ATTN_OK;
   B2_CHECK_ARG(q && k_cache && v_cache && o && kv_indptr && kv_indices, "decode: null pointer");
   B2_CHECK_ARG(Hq > 0 && Hkv > 0 && Hq % Hkv == 0, "decode: Hq=%d must be a multiple of Hkv=%d",
@@ -414,6 +440,10 @@ extern "C" int b200attn_decode(const void* q, int64_t q_stride, const void* k_ca
   p.max_splits = max_splits;
   p.min_chunk = min_chunk;
   p.scale_log2 = sm_scale * kLog2e;
+  p.window_left = window_left;
+  p.cap_pre = logit_cap > 0.f ? sm_scale / logit_cap : 0.f;
+  p.cap_post = logit_cap > 0.f ? logit_cap * kLog2e : 0.f;
+  p.sinks = sinks;
   cudaStream_t st = (cudaStream_t)stream;
   if (D == 128) {
     return dtype == B200ATTN_BF16 ? launch_decode<128, true>(p, st) : launch_decode<128, false>(p, st);

@@ -62,6 +62,10 @@ struct ExtendParams {
   int causal;
   int skip_single;  // requests with one query row are left to the decode kernel
   float scale_log2;
+  // feature flags: extend_attention.py:480-486,546-547,721-723
+  int window_left;     // >= 0: query q_id sees only keys kv_id >= q_id - window_left; < 0: off
+  float cap_pre;       // logit cap c > 0: s <- tanh(s * cap_pre) / cap_pre with cap_pre = sm_scale / c; 0 = off
+  const float* sinks;  // per q head sink logit (natural units) added to the softmax denominator, or null
 #ifdef EXT_TRACE
   long long* trace;  // dev-only timeline of CTA (0,0,0): [role 0..2][step 0..31][8]
 #endif
@@ -90,6 +94,7 @@ struct ItemDesc {
 struct ItemTiles {
   int h[2], m0[2], rows[2], kvend[2], nc[2];  // per tile: q head, first row, valid rows, keys, 64-key chunks
   int prefix, kv_end, ntiles, nc_max;
+  int kbase;  // first key any row of the pair can see, rounded down to a K/V tile (0 without a sliding window)
 };
 
 enum ExtBar {
@@ -146,6 +151,11 @@ __device__ __forceinline__ long long clk() {
 #else
 #define TRACE(role, step, slot)
 #endif
+__device__ __forceinline__ float tanh_approx_f(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -180,6 +190,7 @@ __device__ __forceinline__ void derive_tiles(const ItemDesc& d, const ExtendPara
   const int num_qtiles = (d.E + kExtM - 1) / kExtM;
   const int nv = num_qtiles * p.G;  // virtual tiles v = qtile * G + g of this (request, kv head)
   t.prefix = d.L - d.E;
+  int lo = d.L;
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
     const int v = 2 * d.pair + i;
@@ -188,10 +199,13 @@ __device__ __forceinline__ void derive_tiles(const ItemDesc& d, const ExtendPara
     t.m0[i] = (ok ? v / p.G : 0) * kExtM;
     t.rows[i] = ok ? min(kExtM, d.E - t.m0[i]) : 0;
     t.kvend[i] = !ok ? 0 : (p.causal ? min(d.L, t.prefix + t.m0[i] + t.rows[i]) : d.L);
-    t.nc[i] = (t.kvend[i] + kExtC - 1) / kExtC;
+    if (ok) lo = min(lo, t.prefix + t.m0[i] - p.window_left);
   }
+  t.kbase = p.window_left >= 0 ? max(0, lo) / kExtN * kExtN : 0;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) t.nc[i] = max(0, t.kvend[i] - t.kbase + kExtC - 1) / kExtC;
   t.kv_end = max(t.kvend[0], t.kvend[1]);
-  t.ntiles = (t.kv_end + kExtN - 1) / kExtN;
+  t.ntiles = max(0, t.kv_end - t.kbase + kExtN - 1) / kExtN;
   t.nc_max = max(t.nc[0], t.nc[1]);
 }
 
@@ -333,7 +347,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
           auto load_slots = [&](int j) {
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-              const int key = j * kExtN + lane * 4 + i;
+              const int key = t.kbase + j * kExtN + lane * 4 + i;
               r[i] = (j < t.ntiles && key < t.kv_end) ? __ldg(idx + key) : p.num_slots;  // OOB row -> zeros
             }
           };
@@ -345,7 +359,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
             const int g0 = __shfl_sync(0xffffffffu, r[0], lane & ~3);
             bool contig = (r[1] == r[0] + 1) && (r[2] == r[0] + 2) && (r[3] == r[0] + 3) &&
                           (r[0] == g0 + 4 * (lane & 3));
-            contig = __all_sync(0xffffffffu, contig) && ((j + 1) * kExtN <= t.kv_end);
+            contig = __all_sync(0xffffffffu, contig) && (t.kbase + (j + 1) * kExtN <= t.kv_end);
             if (kt >= kExtStages) mbar_wait(bar(bar_empty + st), ((kt / kExtStages) + 1) & 1);
             if (lane == 0) mbar_arrive_expect_tx(bar(bar_full + st), S::kTile);
             __syncwarp();
@@ -513,6 +527,8 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         // keys visible to this row: [0, limit)
         int limit = p.causal ? min(d.L, t.prefix + m0 + row + 1) : d.L;
         limit = max(1, min(limit, kvend_i));
+        // sliding window: keys below `lower` are masked (whole tiles below kbase are never loaded)
+        const int lower = p.window_left >= 0 ? min(limit - 1, max(0, t.prefix + m0 + row - p.window_left)) : 0;
         float m_used = -INFINITY;  // reference max (log2 domain) the running sums are expressed in
         float l_run = 0.f;
         for (int c = 0; c < nc_i; ++c) {
@@ -532,11 +548,21 @@ __global__ void __launch_bounds__(kExtThreads, 1)
           }
           tmem_wait_ld();
           TRACE(i, c, 2);
-          const int n0 = c * kExtC;
+          const int n0 = t.kbase + c * kExtC;
+          if (p.cap_pre > 0.f) {  // logit cap (uniform branch): s <- c/sm_scale * tanh(s * sm_scale / c)
+            const float inv_pre = 1.f / p.cap_pre;
+#pragma unroll
+            for (int e = 0; e < kExtC; ++e) s[e] = tanh_approx_f(s[e] * p.cap_pre) * inv_pre;
+          }
           if (n0 + kExtC > limit) {
 #pragma unroll
             for (int e = 0; e < kExtC; ++e)
               if (n0 + e >= limit) s[e] = -INFINITY;
+          }
+          if (n0 < lower) {
+#pragma unroll
+            for (int e = 0; e < kExtC; ++e)
+              if (n0 + e < lower) s[e] = -INFINITY;
           }
           float mx4[4] = {s[0], s[1], s[2], s[3]};
 #pragma unroll
@@ -552,7 +578,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
           float alpha = 1.f;
           bool rescale = false;
           if (m_used == -INFINITY) {
-            m_used = (mx == -INFINITY) ? 0.f : mx;  // c == 0 (limit >= 1 => finite)
+            m_used = mx;  // first chunk with a visible key (a sliding window can mask whole leading chunks)
           } else if (mx > m_used + kRescaleThreshold) {
             alpha = ex2_approx(m_used - mx);
             m_used = mx;
@@ -575,7 +601,8 @@ __global__ void __launch_bounds__(kExtThreads, 1)
           }
           TRACE(i, c, 3);
           // p = exp2(s * scale - m); packed bf16 pairs go back into the first 32 columns of this S half
-          const uint64_t negm2 = f2_pack(-m_used, -m_used);
+          const float m_eff = (m_used == -INFINITY) ? 0.f : m_used;  // all keys so far masked: p = exp2(-inf) = 0
+          const uint64_t negm2 = f2_pack(-m_eff, -m_eff);
           uint64_t sum2[2] = {0ull, 0ull};
           uint32_t pk[32];
 #pragma unroll
@@ -610,9 +637,10 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         // ---- epilogue of this item (the issuer already runs QK of the next one) ----
         mbar_wait(bar(kBarOFinal + i), nq_my & 1);
         tc_fence_after();
+        const int h = i == 0 ? t.h[0] : t.h[1];
+        if (p.sinks != nullptr) l_run += ex2_approx(__ldg(p.sinks + h) * kLog2e - m_used);
         const float inv = 1.f / l_run;
         const bool valid = row < (i == 0 ? t.rows[0] : t.rows[1]);
-        const int h = i == 0 ? t.h[0] : t.h[1];
         T* dst = reinterpret_cast<T*>(p.o) + (int64_t)(d.q_beg + m0 + row) * p.o_stride + (int64_t)h * D;
 #pragma unroll
         for (int c = 0; c < D / 32; ++c) {
@@ -741,9 +769,11 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
                                const int32_t* kv_indptr, const int32_t* kv_indices, int32_t B,
                                int64_t total_q_host, int32_t max_qo_len_host, int32_t Hq,
                                int32_t Hkv, int32_t D, int32_t page_size, int dtype, int causal,
-                               float sm_scale, void* workspace, int64_t workspace_bytes,
+                               float sm_scale, int32_t window_left, float logit_cap,
+                               const float* sinks, void* workspace, int64_t workspace_bytes,
                                void* stream) {
   using namespace b200attn;
+  B2_CHECK_ARG(logit_cap >= 0.f, "extend: negative logit_cap");
 #ifndef EXT_TRACE
   (void)workspace;
   (void)workspace_bytes;
@@ -794,6 +824,9 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
   p.causal = (causal & B200ATTN_EXT_CAUSAL) ? 1 : 0;
   p.skip_single = (causal & B200ATTN_EXT_SKIP_SINGLE) ? 1 : 0;
   p.scale_log2 = sm_scale * kLog2e;
+  p.window_left = window_left;
+  p.cap_pre = logit_cap > 0.f ? sm_scale / logit_cap : 0.f;
+  p.sinks = sinks;
 #ifdef EXT_TRACE
   p.trace = workspace_bytes >= 4 * 32 * 8 * 8 ? (long long*)workspace : nullptr;
 #endif

@@ -50,6 +50,16 @@ def _require_cuda(*ts: Optional[torch.Tensor]) -> None:
             )
 
 
+def _sinks_ptr(sinks: Optional[torch.Tensor], Hq: int) -> Optional[int]:
+    """Attention sinks: float32 [Hq] on the device (triton_backend.py:1416, decode_attention.py:986-988)."""
+    if sinks is None:
+        return None
+    _require_cuda(sinks)
+    if sinks.dtype != torch.float32 or sinks.numel() != Hq or not sinks.is_contiguous():
+        raise ValueError("sinks must be a contiguous float32 tensor with one entry per q head")
+    return sinks.data_ptr()
+
+
 def sm_count() -> int:
     return _lib.load().b200attn_sm_count()
 
@@ -347,6 +357,9 @@ def decode_attention(
     q_rows: Optional[torch.Tensor] = None,
     req_ids: Optional[torch.Tensor] = None,
     num_items: Optional[int] = None,
+    window_left: int = -1,
+    logit_cap: float = 0.0,
+    sinks: Optional[torch.Tensor] = None,
 ) -> torch.Tensor:
     """Paged GQA decode: ``q [B,Hq,D]``, caches ``[slots,Hkv,D]`` -> ``o [B,Hq,D]``.
 
@@ -374,7 +387,7 @@ def decode_attention(
         q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
         o.data_ptr(), o.stride(0), _ptr(lse), kv_indptr.data_ptr(), kv_indices.data_ptr(),
         _ptr(q_rows), _ptr(req_ids), B, Hq, Hkv, D, _fdtype(q), float(sm_scale), max_splits,
-        min_chunk, _ptr(workspace), ws_bytes, _stream(),
+        min_chunk, int(window_left), float(logit_cap), _sinks_ptr(sinks, Hq), _ptr(workspace), ws_bytes, _stream(),
     )
     check(rc, "b200attn_decode")
     return o
@@ -402,6 +415,9 @@ def extend_attention(
     workspace: Optional[torch.Tensor] = None,
     lse: Optional[torch.Tensor] = None,
     skip_single_rows: bool = False,
+    window_left: int = -1,
+    logit_cap: float = 0.0,
+    sinks: Optional[torch.Tensor] = None,
 ) -> torch.Tensor:
     """Ragged prefix+extend attention: ``q [T,Hq,D]`` -> ``o [T,Hq,D]``.
 
@@ -433,7 +449,8 @@ def extend_attention(
         min(k_cache.shape[0], v_cache.shape[0]), o.data_ptr(), o.stride(0), _ptr(lse),
         qo_indptr.data_ptr(), kv_indptr.data_ptr(), kv_indices.data_ptr(), B,
         T if total_q is None else total_q, max_qo_len, Hq, Hkv, D, page_size, _fdtype(q),
-        (1 if causal else 0) | (2 if skip_single_rows else 0), float(sm_scale), _ptr(workspace), ws_bytes,
+        (1 if causal else 0) | (2 if skip_single_rows else 0), float(sm_scale), int(window_left),
+        float(logit_cap), _sinks_ptr(sinks, Hq), _ptr(workspace), ws_bytes,
         _stream(),
     )
     check(rc, "b200attn_extend")

@@ -77,7 +77,7 @@ def test_backend_idle_and_unsupported_features():
     q = torch.zeros((0, 8 * 128), dtype=torch.bfloat16, device=DEV)
     assert layer(q, None, None, fb).shape == (0, 8 * 128)
     fb.forward_mode = ForwardMode.DECODE
-    for kw in (dict(logit_cap=30.0), dict(sliding_window_size=128), dict(is_cross_attention=True), dict(v_head_dim=64)):
+    for kw in (dict(is_cross_attention=True), dict(v_head_dim=64)):
         bad = RadixAttention(8, 128, 0.1, 2, 0, **kw)
         with pytest.raises(NotImplementedError):
             backend.forward_decode(q, None, None, bad, fb)
