@@ -46,6 +46,7 @@ struct RopeParams {
   int loc_dtype, pos_dtype;
   int interleaved, neox, store;
   int cache_vec16;  // cos/sin rows and halves are 16-byte aligned
+  int abl_copy_only;  // dev ablation (B200ATTN_ROPE_ABL=copy): staged copy without the rotation
 };
 
 template <bool kBf16>
@@ -78,7 +79,28 @@ template <int VEC>
 union Pack {
   typename VecOf<VEC>::type v;
   uint16_t e[VEC];
+  uint32_t w[VEC >= 2 ? VEC / 2 : 1];
 };
+
+// packed fp32x2 arithmetic (FMUL2 / FADD2 on sm_100): same round-to-nearest per lane as the scalar ops
+__device__ __forceinline__ uint64_t rp_pack(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void rp_unpack(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t rp_mul(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t rp_add(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
 
 // axis of rotation pair i under M-RoPE (mrope.py:47-51 interleaved, :190-199 sectioned)
 __device__ __forceinline__ int mrope_axis(const RopeParams& p, int i) {
@@ -313,6 +335,48 @@ __global__ void __launch_bounds__(256, TOK == 1 ? 6 : 4) rope_store_kernel(const
   }
 }
 
+
+// the (clamped) cache rows of token t: one for 1-D positions, three (t/h/w) for M-RoPE
+__device__ __forceinline__ void resolve_pos(const RopeParams& p, int64_t t, int64_t (&pos3)[3]) {
+  if (p.sec0 < 0) {
+    int64_t pos = load_index(p.pos, p.pos_dtype, t);
+    pos = pos < 0 ? 0 : (pos >= p.cache_rows ? p.cache_rows - 1 : pos);
+    pos3[0] = pos3[1] = pos3[2] = pos;
+  } else {
+#pragma unroll
+    for (int ax = 0; ax < 3; ++ax) {
+      int64_t pos = load_index(p.pos, p.pos_dtype, ax * p.pos_axis_stride + t);
+      pos3[ax] = pos < 0 ? 0 : (pos >= p.cache_rows ? p.cache_rows - 1 : pos);
+    }
+  }
+}
+
+template <int VEC, bool kBf16, bool kCacheF32>
+__device__ __forceinline__ void cos_sin_at(const RopeParams& p, const int64_t (&pos3)[3], int i0, int half,
+                                           float (&cs)[VEC], float (&sn)[VEC]) {
+  if (p.sec0 < 0) {
+    load_cos_sin<VEC, kBf16, kCacheF32>(p, pos3[0], i0, half, cs, sn);
+  } else if (!p.interleaved && mrope_axis(p, i0) == mrope_axis(p, i0 + VEC - 1)) {
+    const int ax = mrope_axis(p, i0);
+    load_cos_sin<VEC, kBf16, kCacheF32>(p, ax == 0 ? pos3[0] : (ax == 1 ? pos3[1] : pos3[2]), i0, half, cs, sn);
+  } else {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      const int ax = mrope_axis(p, i0 + j);
+      const int64_t pos = ax == 0 ? pos3[0] : (ax == 1 ? pos3[1] : pos3[2]);
+      if constexpr (kCacheF32) {
+        const float* cr = reinterpret_cast<const float*>(p.cos_sin) + pos * p.rot;
+        cs[j] = __ldg(cr + i0 + j);
+        sn[j] = __ldg(cr + half + i0 + j);
+      } else {
+        const uint16_t* cr = reinterpret_cast<const uint16_t*>(p.cos_sin) + pos * p.rot;
+        cs[j] = to_f<kBf16>(__ldg(cr + i0 + j));
+        sn[j] = to_f<kBf16>(__ldg(cr + half + i0 + j));
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Bulk-copy pipeline variant (large batches, every row 16-byte aligned).  The register kernel above is latency
 // bound (ncu: DRAM 46 %, L1 36 %, nothing saturated): its bytes in flight are capped by registers.  Here the
@@ -353,15 +417,62 @@ __device__ __forceinline__ void rope_mbar_wait(uint32_t bar, uint32_t parity) {
       : "memory");
 }
 
+// cos/sin of G consecutive pairs from the cache rows staged in shared memory ([1 or 3][rot] of the cache dtype)
+template <int G, bool kBf16, bool kCacheF32>
+__device__ __forceinline__ void cos_sin_smem(const RopeParams& p, const uint8_t* rows, int i0, int half,
+                                             float (&cs)[G], float (&sn)[G]) {
+  constexpr int kEsz = kCacheF32 ? 4 : 2;
+  const int row_bytes = p.rot * kEsz;
+  const bool uniform = p.sec0 < 0 || (!p.interleaved && mrope_axis(p, i0) == mrope_axis(p, i0 + G - 1));
+  if (uniform) {
+    const uint8_t* r = rows + (p.sec0 < 0 ? 0 : mrope_axis(p, i0)) * row_bytes;
+    if constexpr (kCacheF32 && G == 4) {
+      const float4 c4 = *reinterpret_cast<const float4*>(r + i0 * 4);
+      const float4 s4 = *reinterpret_cast<const float4*>(r + (half + i0) * 4);
+      cs[0] = c4.x; cs[1] = c4.y; cs[2] = c4.z; cs[3] = c4.w;
+      sn[0] = s4.x; sn[1] = s4.y; sn[2] = s4.z; sn[3] = s4.w;
+      return;
+    }
+#pragma unroll
+    for (int j = 0; j < G; ++j) {
+      if constexpr (kCacheF32) {
+        cs[j] = reinterpret_cast<const float*>(r)[i0 + j];
+        sn[j] = reinterpret_cast<const float*>(r)[half + i0 + j];
+      } else {
+        cs[j] = to_f<kBf16>(reinterpret_cast<const uint16_t*>(r)[i0 + j]);
+        sn[j] = to_f<kBf16>(reinterpret_cast<const uint16_t*>(r)[half + i0 + j]);
+      }
+    }
+    return;
+  }
+#pragma unroll
+  for (int j = 0; j < G; ++j) {
+    const uint8_t* r = rows + mrope_axis(p, i0 + j) * row_bytes;
+    if constexpr (kCacheF32) {
+      cs[j] = reinterpret_cast<const float*>(r)[i0 + j];
+      sn[j] = reinterpret_cast<const float*>(r)[half + i0 + j];
+    } else {
+      cs[j] = to_f<kBf16>(reinterpret_cast<const uint16_t*>(r)[i0 + j]);
+      sn[j] = to_f<kBf16>(reinterpret_cast<const uint16_t*>(r)[half + i0 + j]);
+    }
+  }
+}
+
+// Stage layout: [q row | k row | v row | cos/sin cache row(s) of the token].  The cache rows ride along with the
+// token (the producer thread knows the position three tokens ahead), so the rotation reads cos/sin from shared
+// memory: no global-memory latency on the per-token critical path of the CTA.
 template <bool kBf16, bool kCacheF32, bool kNative>
-__global__ void __launch_bounds__(kRopeBulkThreads)
+__global__ void __launch_bounds__(kRopeBulkThreads, 4)
     rope_store_bulk_kernel(const RopeParams p, const int stages) {
   constexpr int VEC = 8;
   using V = uint4;
   extern __shared__ __align__(128) uint8_t rope_smem[];
   const uint32_t q_bytes = (uint32_t)p.Hq * p.D * 2, k_bytes = (uint32_t)p.Hkv * p.D * 2;
   const uint32_t v_bytes = p.store ? (uint32_t)p.Hkv * p.Dv * 2 : 0;
-  const uint32_t stage_bytes = q_bytes + k_bytes + v_bytes;
+  const uint32_t cs_row = (uint32_t)p.rot * (kCacheF32 ? 4 : 2);
+  const int n_cs = p.sec0 < 0 ? 1 : 3;
+  const uint32_t cs_off = q_bytes + k_bytes + v_bytes;
+  const uint32_t stage_bytes = cs_off + n_cs * cs_row;
   uint8_t* ring = rope_smem + 128;  // first 128 B: mbarriers
   const uint32_t bar0 = smem_u32(rope_smem);
   const uint32_t ring0 = smem_u32(ring);
@@ -374,7 +485,7 @@ __global__ void __launch_bounds__(kRopeBulkThreads)
   // tokens of this CTA: blockIdx.x, blockIdx.x + gridDim.x, ...
   const int64_t n_my = p.T > blockIdx.x ? (p.T - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
   auto token = [&](int64_t i) { return (int64_t)blockIdx.x + i * gridDim.x; };
-  auto issue_load = [&](int64_t i) {  // thread 0 only
+  auto issue_load = [&](int64_t i, const int64_t (&pos3)[3]) {  // thread 0 only
     const int s = (int)(i % stages);
     const int64_t t = token(i);
     const uint32_t dst = ring0 + s * stage_bytes, bar = bar0 + 8 * s;
@@ -382,9 +493,17 @@ __global__ void __launch_bounds__(kRopeBulkThreads)
     bulk_g2s(dst, p.q + t * p.q_stride * 2, q_bytes, bar);
     bulk_g2s(dst + q_bytes, p.k + t * p.k_stride * 2, k_bytes, bar);
     if (v_bytes) bulk_g2s(dst + q_bytes + k_bytes, p.v + t * p.v_stride * 2, v_bytes, bar);
+    for (int a = 0; a < n_cs; ++a)
+      bulk_g2s(dst + cs_off + a * cs_row, reinterpret_cast<const uint8_t*>(p.cos_sin) + pos3[a] * cs_row, cs_row, bar);
   };
-  if (tid == 0)
-    for (int64_t i = 0; i < stages - 1 && i < n_my; ++i) issue_load(i);
+  int64_t pos_pref[3] = {0, 0, 0};  // thread 0: cache rows of the next token to load (fetched one iteration early)
+  if (tid == 0) {
+    for (int64_t i = 0; i < stages - 1 && i < n_my; ++i) {
+      resolve_pos(p, token(i), pos_pref);
+      issue_load(i, pos_pref);
+    }
+    if (stages - 1 < n_my) resolve_pos(p, token(stages - 1), pos_pref);
+  }
 
   const int half = p.rot >> 1;
   const int rot_items = half / VEC;
@@ -393,8 +512,10 @@ __global__ void __launch_bounds__(kRopeBulkThreads)
     const int s = (int)(i % stages);
     const int64_t t = token(i);
     uint8_t* st = ring + s * stage_bytes;
+    int64_t pos_next[3] = {0, 0, 0};
+    if (tid == 0 && i + stages < n_my) resolve_pos(p, token(i + stages), pos_next);  // in flight during the rotation
     rope_mbar_wait(bar0 + 8 * s, (uint32_t)((i / stages) & 1));
-    for (int it = tid; it < n_rot; it += kRopeBulkThreads) {
+    for (int it = tid; it < (p.abl_copy_only ? 0 : n_rot); it += blockDim.x) {
       const int h = it / rot_items, c = it - h * rot_items;  // h indexes q heads then k heads
       const int i0 = c * VEC;
       uint8_t* row = st + (size_t)h * p.D * 2;
@@ -406,7 +527,7 @@ __global__ void __launch_bounds__(kRopeBulkThreads)
 #pragma unroll
       for (int j0 = 0; j0 < VEC; j0 += 4) {
         float cs[4], sn[4];
-        token_cos_sin<4, kBf16, kCacheF32>(p, t, i0 + j0, half, cs, sn);
+        cos_sin_smem<4, kBf16, kCacheF32>(p, st + cs_off, i0 + j0, half, cs, sn);
         rotate<VEC, 4, kBf16, kNative>(a, b, j0, cs, sn, p.neox);
       }
       *pa = a.v;
@@ -426,7 +547,10 @@ __global__ void __launch_bounds__(kRopeBulkThreads)
       bulk_commit();
       // the stage of token i-1 is re-filled next: all but the group just committed must have read their smem
       bulk_wait_read<1>();
-      if (i + stages - 1 < n_my) issue_load(i + stages - 1);
+      if (i + stages - 1 < n_my) issue_load(i + stages - 1, pos_pref);
+      pos_pref[0] = pos_next[0];
+      pos_pref[1] = pos_next[1];
+      pos_pref[2] = pos_next[2];
     }
   }
   if (tid == 0) bulk_wait_read<0>();  // smem must outlive the last stores
@@ -434,15 +558,22 @@ __global__ void __launch_bounds__(kRopeBulkThreads)
 
 // Returns B200ATTN_OK after launching, or -1 when the shape is not eligible (caller falls back).
 static int launch_rope_bulk(const RopeParams& p, int elem_dtype, int cache_dtype, int mode, cudaStream_t st) {
-  const int64_t stage_bytes = ((int64_t)p.Hq * p.D + (int64_t)p.Hkv * p.D + (p.store ? (int64_t)p.Hkv * p.Dv : 0)) * 2;
+  const int64_t cs_row = (int64_t)p.rot * (cache_dtype == B200ATTN_FP32 ? 4 : 2);
+  if (!p.cache_vec16 || cs_row % 16 != 0) return -1;  // the cache rows are bulk-copied too
+  const int64_t stage_bytes =
+      ((int64_t)p.Hq * p.D + (int64_t)p.Hkv * p.D + (p.store ? (int64_t)p.Hkv * p.Dv : 0)) * 2 +
+      (p.sec0 < 0 ? 1 : 3) * cs_row;
   if (stage_bytes > 96 * 1024 || p.T >= (1ll << 31)) return -1;
-  int stages = (int)(56 * 1024 / stage_bytes);
+  // measured (tools/bench_rope.py, T = 131072): 128 threads x 2 stages x 8 CTAs/SM 6.24 TB/s; 256 threads x 4 stages
+  // x 4 CTAs/SM 4.92 TB/s: many small CTAs interleave their load -> rotate -> store chains better
+  int budget_kb = 27, threads = 128;
+  if (const char* e = getenv("B200ATTN_ROPE_STAGE_KB")) budget_kb = atoi(e);   // dev sweep hooks
+  if (const char* e = getenv("B200ATTN_ROPE_THREADS")) threads = atoi(e);
+  if (threads != 64 && threads != 128 && threads != 256) threads = 128;
+  int stages = (int)((int64_t)budget_kb * 1024 / stage_bytes);
   stages = stages < 2 ? 2 : (stages > 8 ? 8 : stages);
   const int smem = 128 + stages * (int)stage_bytes;
   const int sms = sm_count();
-  int ctas_per_sm = (200 * 1024) / (smem + 1024);
-  ctas_per_sm = ctas_per_sm < 1 ? 1 : (ctas_per_sm > 4 ? 4 : ctas_per_sm);
-  const int64_t grid = p.T < (int64_t)sms * ctas_per_sm ? p.T : (int64_t)sms * ctas_per_sm;
   const bool bf16 = elem_dtype == B200ATTN_BF16;
   const bool cf32 = cache_dtype == B200ATTN_FP32;
   const bool native = mode == B200ATTN_ROPE_NATIVE;
@@ -450,7 +581,13 @@ static int launch_rope_bulk(const RopeParams& p, int elem_dtype, int cache_dtype
   if (bf16 == BF && cf32 == CF && native == NA) {                                                     \
     B2_CUDA(cudaFuncSetAttribute(rope_store_bulk_kernel<BF, CF, NA>,                                  \
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));           \
-    rope_store_bulk_kernel<BF, CF, NA><<<(unsigned)grid, kRopeBulkThreads, smem, st>>>(p, stages);    \
+    int occ = 0; /* persistent grid = exactly the resident CTAs (registers may bind before smem) */   \
+    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, rope_store_bulk_kernel<BF, CF, NA>,   \
+                                                          threads, smem));                            \
+    if (occ < 1) return -1;                                                                           \
+    const int64_t full = (int64_t)sms * occ;                                                          \
+    const int64_t grid = p.T < full ? p.T : full;                                                     \
+    rope_store_bulk_kernel<BF, CF, NA><<<(unsigned)grid, threads, smem, st>>>(p, stages);             \
     B2_LAUNCH_CHECK();                                                                                \
     return B200ATTN_OK;                                                                               \
   }
@@ -572,6 +709,10 @@ extern "C" int b200attn_rope_store(void* q, void* k, const void* v, void* k_cach
   {
     const int64_t esz = cache_dtype == B200ATTN_FP32 ? 4 : 2;
     p.cache_vec16 = ((uintptr_t)cos_sin_cache % 16 == 0) && ((rotary_dim / 2) * esz % 16 == 0);
+  }
+  {
+    const char* e = getenv("B200ATTN_ROPE_ABL");
+    p.abl_copy_only = e != nullptr && e[0] == 'c';
   }
   cudaStream_t st = (cudaStream_t)stream;
   if ((bits & 7) == 0) {

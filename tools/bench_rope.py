@@ -44,6 +44,13 @@ def main():
             ops.apply_rope_with_cos_sin_cache_inplace(pos, q, k, cache, head_size=D, mrope_section=sec)
             ops.store_cache(k.view(T, Hkv, D), v.view(T, Hkv, D), kc, vc, loc)
 
+        rope_only = lambda: ops.apply_rope_with_cos_sin_cache_inplace(pos, q, k, cache, head_size=D, mrope_section=sec)
+        store_only = lambda: ops.store_cache(k.view(T, Hkv, D), v.view(T, Hkv, D), kc, vc, loc)
+        inplace = lambda: qkv.mul_(1.0)
+        tr, tso, ti = timeit(rope_only), timeit(store_only), timeit(inplace)
+        print(json.dumps(dict(case=name, rope_only_us=tr * 1e3, rope_only_gbs=T * 2 * (Hq + Hkv) * D * 2 / tr / 1e6,
+                              store_only_us=tso * 1e3, store_only_gbs=T * 4 * Hkv * D * 2 / tso / 1e6,
+                              torch_inplace_mul_qkv_us=ti * 1e3, torch_inplace_gbs=2 * qkv.numel() * 2 / ti / 1e6)), flush=True)
         by = T * ((Hq + 2 * Hkv) * D * 2 + (Hq + Hkv) * D * 2 + 2 * Hkv * D * 2 + 16)
         tf, ts = timeit(fused), timeit(separate)
         res.append(dict(case=name, bytes=by, fused_us=tf * 1e3, fused_gbs=by / tf / 1e6, separate_us=ts * 1e3))
