@@ -130,6 +130,11 @@ int b200attn_build_page_table(const int32_t* req_to_token, int64_t req_to_token_
  * touched when max_splits > 1.  The split policy is a pure function of
  * (kv length, max_splits, min_chunk) evaluated on the device, so CUDA-graph
  * replay needs no host-side recomputation.
+ * `tail_begin` >= 0 restricts splitting to the units (request-major, then kv head
+ * group) of rank >= tail_begin: the caller passes the number of units that fill whole
+ * waves of resident CTAs (2 per SM), so that only the last, partial wave is split
+ * `max_splits` ways and no SM idles for a whole unit (a function of B and the head
+ * counts only => graph-safe).  -1: every unit uses the length-based policy.
  *
  * Feature flags shared with b200attn_extend (triton_backend.py:1405-1416,
  * decode_attention.py:986-988, extend_attention.py:480-486,546-547,721-723):
@@ -147,8 +152,8 @@ int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
                     float* lse, const int32_t* kv_indptr, const int32_t* kv_indices,
                     const int32_t* q_rows, const int32_t* req_ids, int32_t B,
                     int32_t Hq, int32_t Hkv, int32_t D, int dtype, float sm_scale,
-                    int32_t max_splits, int32_t min_chunk, int32_t window_left,
-                    float logit_cap, const float* sinks, void* workspace,
+                    int32_t max_splits, int32_t min_chunk, int32_t tail_begin,
+                    int32_t window_left, float logit_cap, const float* sinks, void* workspace,
                     int64_t workspace_bytes, void* stream);
 
 /* --------------------------------------------------------------------------

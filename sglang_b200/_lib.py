@@ -41,7 +41,7 @@ SIGNATURES = {
     "b200attn_decode": (
         C.c_int,
         [_vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, C.c_int,
-         _f32, _i32, _i32, _i32, _f32, _vp, _vp, _i64, _vp],
+         _f32, _i32, _i32, _i32, _i32, _f32, _vp, _vp, _i64, _vp],
     ),
     "b200attn_extend_workspace_bytes": (_i64, [_i32, _i64, _i32]),
     "b200attn_extend": (

@@ -328,9 +328,21 @@ class B200AttnBackend(_Base):
             ms = ops.pick_max_splits(B, Hkv, G, getattr(md, "_max_kv_len", self.max_context_len),
                                      md.min_chunk, num_sms=self.num_sms)
             ws = self._workspace(ops.decode_workspace_bytes(B, Hq, D, ms))
+        tail_begin = -1
+        if ms == 1:  # whole waves stay unsplit; a nearly empty last wave is split (ops.pick_tail_split)
+            tail_begin, k = ops.pick_tail_split(B, Hkv, G, num_sms=self.num_sms)
+            if k > 1:
+                need = ops.decode_workspace_bytes(B, Hq, D, k)
+                if getattr(md, "_graph", False):
+                    if ws is not None and ws.numel() >= need:
+                        ms = k
+                    else:
+                        tail_begin = -1
+                else:
+                    ms, ws = k, self._workspace(need)
         ops.decode_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.kv_indptr, md.kv_indices,
                              layer.scaling, max_splits=ms, min_chunk=md.min_chunk, workspace=ws, num_items=B,
-                             **self._features(layer, kwargs))
+                             tail_begin=tail_begin, **self._features(layer, kwargs))
         return o
 
     def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, **kwargs):

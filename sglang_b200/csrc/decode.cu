@@ -49,7 +49,17 @@ struct DecodeParams {
   float cap_pre;        // logit cap c > 0: x = c * tanh(s * sm_scale / c); cap_pre = sm_scale / c
   float cap_post;       // c * log2(e); 0 = no cap
   const float* sinks;   // per q head sink logit (natural units) added to the softmax denominator, or null
+  // Tail splitting: units (request, kv head group) are launched in rank order, `tail_begin` of them fill whole
+  // waves of resident CTAs and stay unsplit; the remainder would leave SMs idle for up to a whole unit, so only
+  // THOSE units are split `max_splits` ways.  tail_begin < 0: every unit uses the length-based policy.
+  int tail_begin;
 };
+
+// split cap of one unit (shared by the attention and the merge kernel)
+__device__ __forceinline__ int unit_max_splits(const DecodeParams& p, int item, int hg) {
+  if (p.tail_begin < 0) return p.max_splits;
+  return item * (p.Hkv * p.groups_per_kvh) + hg >= p.tail_begin ? p.max_splits : 1;
+}
 
 // keys of a request that the (single) query row sees: [kv_lo, L)
 __device__ __forceinline__ int window_lo(int L, int window_left) {
@@ -94,7 +104,7 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodePara
     L -= lo;
   }
   int nsplit, chunk;
-  split_policy(L, p.max_splits, p.min_chunk, kDecTile, nsplit, chunk);
+  split_policy(L, unit_max_splits(p, item, hg), p.min_chunk, kDecTile, nsplit, chunk);
   if (split >= nsplit) return;
   const int k_lo = split * chunk;
   const int k_hi = min(L, k_lo + chunk);
@@ -329,7 +339,8 @@ __global__ void __launch_bounds__(D / 4) decode_merge_kernel(const DecodeParams 
   int L = p.kv_indptr[req + 1] - p.kv_indptr[req];
   L -= window_lo(L, p.window_left);
   int nsplit, chunk;
-  split_policy(L, p.max_splits, p.min_chunk, kDecTile, nsplit, chunk);
+  split_policy(L, unit_max_splits(p, item, (h / p.G) * p.groups_per_kvh + (h % p.G) / kDecMaxG), p.min_chunk, kDecTile,
+               nsplit, chunk);
   if (nsplit == 1) return;  // the attention kernel wrote the output directly
   const int64_t w0 = ((int64_t)item * p.Hq + h) * p.max_splits;
   const int c = threadIdx.x * 4;
@@ -395,7 +406,8 @@ extern "C" int b200attn_decode(const void* q, int64_t q_stride, const void* k_ca
                                float* lse, const int32_t* kv_indptr, const int32_t* kv_indices,
                                const int32_t* q_rows, const int32_t* req_ids, int32_t B,
                                int32_t Hq, int32_t Hkv, int32_t D, int dtype, float sm_scale,
-                               int32_t max_splits, int32_t min_chunk, int32_t window_left,
+                               int32_t max_splits, int32_t min_chunk, int32_t tail_begin,
+                               int32_t window_left,
                                float logit_cap, const float* sinks, void* workspace,
                                int64_t workspace_bytes, void* stream) {
   using namespace b200attn;
@@ -444,6 +456,7 @@ extern "C" int b200attn_decode(const void* q, int64_t q_stride, const void* k_ca
   p.cap_pre = logit_cap > 0.f ? sm_scale / logit_cap : 0.f;
   p.cap_post = logit_cap > 0.f ? logit_cap * kLog2e : 0.f;
   p.sinks = sinks;
+  p.tail_begin = max_splits > 1 ? tail_begin : -1;
   cudaStream_t st = (cudaStream_t)stream;
   if (D == 128) {
     return dtype == B200ATTN_BF16 ? launch_decode<128, true>(p, st) : launch_decode<128, false>(p, st);

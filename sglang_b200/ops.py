@@ -341,6 +341,24 @@ def pick_max_splits(B: int, Hkv: int, G: int, max_kv_len: int, min_chunk: int = 
     return int(max(1, min(cap, -(-slots // items))))
 
 
+def pick_tail_split(B: int, Hkv: int, G: int, num_sms: Optional[int] = None, ctas_per_sm: int = 2,
+                    max_k: int = 8) -> Tuple[int, int]:
+    """Tail splitting for batches whose units do not fill whole waves of resident CTAs.
+
+    Units = B * Hkv * ceil(G / 16) equal-priority CTAs, ``W = ctas_per_sm * SMs`` run at a time.  A last wave of
+    only R << W units leaves most SMs idle for a whole unit, so ONLY those R units are split k ways (k = W // R:
+    the split tail is one wave).  Measured on B200 (tools/decode_waves.py, ctx 4096): R/W = 0.08 -> 158.5 us ->
+    117.0 us; R/W = 0.73 -> 171 us -> 177 us (the shorter CTAs and the merge launch cost more than the idle
+    slots), hence the R <= W/2 gate.  Returns ``(tail_begin, k)``; ``(-1, 1)`` when nothing is gained."""
+    W = ctas_per_sm * (num_sms or sm_count())
+    U = B * Hkv * (-(-G // 16))
+    F, R = divmod(U, W)
+    if F == 0 or R == 0 or 2 * R > W:
+        return -1, 1
+    k = min(max_k, W // R)
+    return (F * W, k) if k >= 2 else (-1, 1)
+
+
 def decode_attention(
     q: torch.Tensor,
     k_cache: torch.Tensor,
@@ -360,6 +378,7 @@ def decode_attention(
     window_left: int = -1,
     logit_cap: float = 0.0,
     sinks: Optional[torch.Tensor] = None,
+    tail_begin: int = -1,
 ) -> torch.Tensor:
     """Paged GQA decode: ``q [B,Hq,D]``, caches ``[slots,Hkv,D]`` -> ``o [B,Hq,D]``.
 
@@ -387,7 +406,8 @@ def decode_attention(
         q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
         o.data_ptr(), o.stride(0), _ptr(lse), kv_indptr.data_ptr(), kv_indices.data_ptr(),
         _ptr(q_rows), _ptr(req_ids), B, Hq, Hkv, D, _fdtype(q), float(sm_scale), max_splits,
-        min_chunk, int(window_left), float(logit_cap), _sinks_ptr(sinks, Hq), _ptr(workspace), ws_bytes, _stream(),
+        min_chunk, int(tail_begin), int(window_left), float(logit_cap), _sinks_ptr(sinks, Hq), _ptr(workspace),
+        ws_bytes, _stream(),
     )
     check(rc, "b200attn_decode")
     return o

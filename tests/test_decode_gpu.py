@@ -116,3 +116,36 @@ def test_decode_q_rows_and_req_ids_routing():
                                     torch.ones(1, dtype=torch.int64), 8, 2, 128, sc.scaling, causal=False)
         assert_close_attn(o[row].reshape(1, -1), ref, f"routed row {row}")
     assert float(o[[1, 2, 3, 4, 6]].abs().sum()) == 0
+
+
+@pytest.mark.parametrize("tail_begin,k", [(0, 4), (5, 3), (16, 8), (1000, 4)])
+def test_decode_tail_split_matches_oracle(tail_begin, k):
+    """Only the units of rank >= tail_begin are split (ops.pick_tail_split); results must not depend on it."""
+    from sglang_b200 import ops
+    Hq, Hkv, D = 8, 2, 128
+    lens = [700, 64, 1, 2049, 513, 300, 1500, 128, 65, 900]
+    sc = make_scenario([l - 1 for l in lens], [1] * len(lens), Hq, Hkv, D, 16, seed=5)
+    kc, vc = sc.k_cache.clone(), sc.v_cache.clone()
+    kc[sc.out_cache_loc] = sc.k
+    vc[sc.out_cache_loc] = sc.v
+    B = len(lens)
+    kv_indptr = torch.zeros(B + 1, dtype=torch.int32, device=DEV)
+    kv_indices = torch.zeros(sum(lens), dtype=torch.int32, device=DEV)
+    ops.build_kv_indices(sc.req_to_token.to(DEV), sc.req_pool_indices.to(DEV), torch.tensor(lens, device=DEV), kv_indptr,
+                         kv_indices)
+    q = sc.q.to(DEV).view(B, Hq, D)
+    o = torch.empty_like(q)
+    ws = torch.empty(ops.decode_workspace_bytes(B, Hq, D, k), dtype=torch.uint8, device=DEV)
+    ops.decode_attention(q, kc.to(DEV), vc.to(DEV), o, kv_indptr, kv_indices, sc.scaling, max_splits=k, min_chunk=64,
+                         workspace=ws, tail_begin=tail_begin)
+    ref = oracle.attention_fp32(sc.q, kc, vc, sc.req_to_token, sc.req_pool_indices, torch.tensor(lens),
+                                torch.ones(B, dtype=torch.int64), Hq, Hkv, D, sc.scaling, causal=False)
+    assert_close_attn(o.view(B, -1), ref, f"tail split {tail_begin}/{k}")
+
+
+def test_pick_tail_split_policy():
+    from sglang_b200 import ops
+    assert ops.pick_tail_split(64, 8, 4, num_sms=148) == (-1, 1)      # 512 units: tail 216/296 too full to split
+    assert ops.pick_tail_split(74, 8, 4, num_sms=148) == (-1, 1)      # exactly two waves
+    assert ops.pick_tail_split(40, 8, 4, num_sms=148) == (296, 8)     # 24-unit tail
+    assert ops.pick_tail_split(8, 8, 4, num_sms=148) == (-1, 1)       # below one wave: length-based policy
