@@ -279,7 +279,7 @@ def run_b200(args, rank, world, local_rank):
     # (2) the dominant kernel alone (decode attention, without the store) for the roofline
     q3 = devt["q"].view(B, Hq, D)
     o3 = torch.empty_like(q3)
-    ws = torch.empty(max(ops.decode_workspace_bytes(B, Hq, D, max_splits), 16), dtype=torch.uint8, device=dev)
+    ws = torch.zeros(max(ops.decode_workspace_bytes(B, Hq, D, max_splits), 16), dtype=torch.uint8, device=dev)
 
     def kern():
         ops.decode_attention(q3, kbuf, vbuf, o3, md.kv_indptr, md.kv_indices, layer.scaling, max_splits=max_splits,
@@ -489,7 +489,7 @@ def run_cfg5_decode(dev, gen, peaks, world, steps=10, warmup=3):
     o = torch.empty_like(q)
     kbuf, vbuf = kv_pool.get_kv_buffer(0)
     ms_ = ops.pick_max_splits(B, Hkv, Hq // Hkv, c["ctx"], 256)
-    ws = torch.empty(max(ops.decode_workspace_bytes(B, Hq, D, ms_), 16), dtype=torch.uint8, device=dev)
+    ws = torch.zeros(max(ops.decode_workspace_bytes(B, Hq, D, ms_), 16), dtype=torch.uint8, device=dev)
     f = lambda: ops.decode_attention(q, kbuf, vbuf, o, kv_indptr, kv_indices, D ** -0.5, max_splits=ms_,
                                      min_chunk=256, workspace=ws)
     t = time_steps(f, steps, warmup) / steps

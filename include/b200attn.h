@@ -127,7 +127,10 @@ int b200attn_build_page_table(const int32_t* req_to_token, int64_t req_to_token_
  * if null) — together they let a MIXED batch route its extend_len==1 rows here.
  * `lse` (nullable float[B*Hq], indexed like o rows): natural-log LSE.
  * Workspace: b200attn_decode_workspace_bytes(B, Hq, D, max_splits) bytes, only
- * touched when max_splits > 1.  The split policy is a pure function of
+ * touched when max_splits > 1: fp32 partials + per-unit arrival counters.  The split
+ * partials are merged INSIDE the kernel by the last CTA of a unit to arrive (no
+ * second launch).  The workspace must be ZERO-INITIALISED ONCE by the caller before
+ * its first use; every launch leaves the counters at zero again.  The split policy is a pure function of
  * (kv length, max_splits, min_chunk) evaluated on the device, so CUDA-graph
  * replay needs no host-side recomputation.
  * `tail_begin` >= 0 restricts splitting to the units (request-major, then kv head

@@ -110,7 +110,9 @@ class B200AttnBackend(_Base):
         if nbytes <= 0:
             return None
         if self._ws is None or self._ws.numel() < nbytes:
-            self._ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+            # zero-initialised ONCE: the decode kernel's split arrival counters live here and are left at zero by
+            # every launch (include/b200attn.h, b200attn_decode)
+            self._ws = torch.zeros(nbytes, dtype=torch.uint8, device=self.device)
         return self._ws
 
     def _check_layer(self, layer, kwargs) -> None:
@@ -227,7 +229,7 @@ class B200AttnBackend(_Base):
         g.workspace = None
         if num_q_heads is not None and head_dim is not None:
             nbytes = ops.decode_workspace_bytes(max_bs, num_q_heads, head_dim, max_splits_cap)
-            g.workspace = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
+            g.workspace = torch.zeros(max(nbytes, 16), dtype=torch.uint8, device=dev)
         self._graph = g
 
     def get_cuda_graph_seq_len_fill_value(self) -> int:
@@ -320,7 +322,7 @@ class B200AttnBackend(_Base):
             if need > 0 and (ws is None or ws.numel() < need):
                 if torch.cuda.is_current_stream_capturing():
                     raise RuntimeError("b200 backend: pass num_q_heads/head_dim to init_cuda_graph_state")
-                ws = self._graph.workspace = torch.empty(
+                ws = self._graph.workspace = torch.zeros(
                     ops.decode_workspace_bytes(self._graph.max_bs, Hq, D, self._graph.max_splits_cap),
                     dtype=torch.uint8, device=self.device)
                 md.workspace = ws

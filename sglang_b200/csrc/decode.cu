@@ -40,6 +40,7 @@ struct DecodeParams {
   const int32_t* req_ids;
   float* ws_o;    // [B, Hq, max_splits, D]
   float* ws_lse;  // [B, Hq, max_splits]   (log2 domain)
+  int* ws_cnt;    // [B, Hkv * groups] arrival counters of the split CTAs of a unit; zero on entry, zero on exit
   int64_t q_stride, kv_stride, o_stride;
   int B, Hq, Hkv, G, groups_per_kvh;
   int max_splits, min_chunk;
@@ -327,46 +328,50 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodePara
       if (c == 0) p.ws_lse[w] = lse2;
     }
   }
-}
-
-// Merge the split partials of one (request, q head): grid (Hq, B), D/4 threads.
-template <int D, bool kBf16>
-__global__ void __launch_bounds__(D / 4) decode_merge_kernel(const DecodeParams p) {
-  using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
-  const int h = blockIdx.x, item = blockIdx.y;
-  const int req = p.req_ids ? p.req_ids[item] : item;
-  const int qrow = p.q_rows ? p.q_rows[item] : item;
-  int L = p.kv_indptr[req + 1] - p.kv_indptr[req];
-  L -= window_lo(L, p.window_left);
-  int nsplit, chunk;
-  split_policy(L, unit_max_splits(p, item, (h / p.G) * p.groups_per_kvh + (h % p.G) / kDecMaxG), p.min_chunk, kDecTile,
-               nsplit, chunk);
-  if (nsplit == 1) return;  // the attention kernel wrote the output directly
-  const int64_t w0 = ((int64_t)item * p.Hq + h) * p.max_splits;
-  const int c = threadIdx.x * 4;
-  float m = -INFINITY;
-  for (int s = 0; s < nsplit; ++s) m = fmaxf(m, __ldg(p.ws_lse + w0 + s));
-  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-  float l = 0.f;
-  for (int s = 0; s < nsplit; ++s) {
-    const float ls = __ldg(p.ws_lse + w0 + s);
-    const float f = (ls == -INFINITY) ? 0.f : fast_exp2(ls - m);
-    const float4 x = *reinterpret_cast<const float4*>(p.ws_o + (w0 + s) * D + c);
-    acc.x += f * x.x;
-    acc.y += f * x.y;
-    acc.z += f * x.z;
-    acc.w += f * x.w;
-    l += f;
+  if (direct) return;
+  // ---- split merge by the LAST CTA of the unit to arrive (no second launch) ----
+  // writers: partials -> fence -> barrier -> one relaxed atomic ticket; the CTA that draws the last ticket sees
+  // every partial (fence after the ticket) and reads them through L2 (ld.global.cg, never the read-only path).
+  __shared__ int s_last;
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    int* cnt = p.ws_cnt + (int64_t)item * (p.Hkv * p.groups_per_kvh) + hg;
+    const int ticket = atomicAdd(cnt, 1);
+    s_last = (ticket == nsplit - 1);
+    if (s_last) *cnt = 0;  // self-cleaning: the next launch finds zeros again
   }
-  if (p.sinks != nullptr && l > 0.f) l += fast_exp2(__ldg(p.sinks + h) * kLog2e - m);
-  const float inv = (l > 0.f) ? 1.f / l : 0.f;
-  T* dst = reinterpret_cast<T*>(p.o) + (int64_t)qrow * p.o_stride + (int64_t)h * D + c;
-  uint2 pk;
-  pk.x = pack2<kBf16>(acc.x * inv, acc.y * inv);
-  pk.y = pack2<kBf16>(acc.z * inv, acc.w * inv);
-  *reinterpret_cast<uint2*>(dst) = pk;
-  if (p.lse != nullptr && c == 0)
-    p.lse[(int64_t)qrow * p.Hq + h] = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  for (int e = tid; e < gcount * (D / 4); e += kDecThreads) {
+    const int r = e / (D / 4), c = (e - r * (D / 4)) * 4;
+    const int h = h0 + r;
+    const int64_t w0 = ((int64_t)item * p.Hq + h) * p.max_splits;
+    float m = -INFINITY;
+    for (int sp = 0; sp < nsplit; ++sp) m = fmaxf(m, __ldcg(p.ws_lse + w0 + sp));
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    float l = 0.f;
+    for (int sp = 0; sp < nsplit; ++sp) {
+      const float ls = __ldcg(p.ws_lse + w0 + sp);
+      const float f = (ls == -INFINITY) ? 0.f : fast_exp2(ls - m);
+      const float4 x = __ldcg(reinterpret_cast<const float4*>(p.ws_o + (w0 + sp) * D + c));
+      acc.x += f * x.x;
+      acc.y += f * x.y;
+      acc.z += f * x.z;
+      acc.w += f * x.w;
+      l += f;
+    }
+    if (p.sinks != nullptr && l > 0.f) l += fast_exp2(__ldg(p.sinks + h) * kLog2e - m);
+    const float inv = (l > 0.f) ? 1.f / l : 0.f;
+    T* dst = reinterpret_cast<T*>(p.o) + (int64_t)qrow * p.o_stride + (int64_t)h * D + c;
+    uint2 pk;
+    pk.x = pack2<kBf16>(acc.x * inv, acc.y * inv);
+    pk.y = pack2<kBf16>(acc.z * inv, acc.w * inv);
+    *reinterpret_cast<uint2*>(dst) = pk;
+    if (p.lse != nullptr && c == 0)
+      p.lse[(int64_t)qrow * p.Hq + h] = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
+  }
 }
 
 template <int D, bool kBf16>
@@ -385,11 +390,6 @@ static int launch_decode(const DecodeParams& p, cudaStream_t st) {
   dim3 grid((unsigned)p.max_splits, (unsigned)(p.Hkv * p.groups_per_kvh), (unsigned)p.B);
   decode_kernel<D, kBf16><<<grid, kDecThreads, kSmem, st>>>(p);
   B2_LAUNCH_CHECK();
-  if (p.max_splits > 1) {
-    dim3 mgrid((unsigned)p.Hq, (unsigned)p.B);
-    decode_merge_kernel<D, kBf16><<<mgrid, D / 4, 0, st>>>(p);
-    B2_LAUNCH_CHECK();
-  }
   return B200ATTN_OK;
 }
 
@@ -398,7 +398,7 @@ static int launch_decode(const DecodeParams& p, cudaStream_t st) {
 extern "C" int64_t b200attn_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t D,
                                                    int32_t max_splits) {
   if (max_splits <= 1) return 0;
-  return (int64_t)B * Hq * max_splits * (D + 1) * 4;
+  return (int64_t)B * Hq * max_splits * (D + 1) * 4 + (int64_t)B * Hq * 4;  // partials + arrival counters
 }
 
 extern "C" int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
@@ -441,6 +441,7 @@ extern "C" int b200attn_decode(const void* q, int64_t q_stride, const void* k_ca
   p.req_ids = req_ids;
   p.ws_o = reinterpret_cast<float*>(workspace);
   p.ws_lse = p.ws_o ? p.ws_o + (int64_t)B * Hq * max_splits * D : nullptr;
+  p.ws_cnt = p.ws_o ? reinterpret_cast<int*>(p.ws_lse + (int64_t)B * Hq * max_splits) : nullptr;
   p.q_stride = q_stride;
   p.kv_stride = kv_stride;
   p.o_stride = o_stride;

@@ -325,20 +325,20 @@ def decode_workspace_bytes(B: int, Hq: int, D: int, max_splits: int) -> int:
 
 def pick_max_splits(B: int, Hkv: int, G: int, max_kv_len: int, min_chunk: int = 256,
                     ctas_per_sm: int = 2, num_sms: Optional[int] = None) -> int:
-    """Host-side choice of the split cap.  The decode grid is (splits x kv-head groups x batch)
-    CTAs over `ctas_per_sm * num_sms` resident slots.  Measured on B200 (profiles/r01_decode_
-    split_sweep.txt): the kernel is HBM-bound, a partly filled last wave costs nothing because
-    the remaining CTAs inherit the bandwidth, while every extra split costs workspace traffic
-    and the merge launch -> split only as far as needed to put one CTA on every slot, never
-    finer than `min_chunk` keys.  The per-request split count itself is computed on the device
-    (split_policy in csrc/common.cuh)."""
+    """Host-side choice of the split cap.  The decode grid is (splits x kv-head groups x batch) CTAs over
+    ``W = ctas_per_sm * num_sms`` resident slots.  Measured on B200 (tools/compare_small_decode.py, 8 kv heads,
+    W = 296): the best cap is the LARGEST one that keeps every CTA in the first wave, ``floor(W / units)`` —
+    B=4 x 8K: 9 -> 33.5 us (10 spills into a second wave: 41.8 us); B=8 x 8K: 4 -> 51.8 us (5: 68.7); B=16 x 4K:
+    2 -> 53.0 us (3: 64.2); units >= W/2: 1 (B=32 x 8K: 167 us vs 178 at 2) — and never finer than ``min_chunk``
+    keys.  The per-request split count itself is computed on the device (split_policy in csrc/common.cuh); a nearly
+    empty LAST wave is handled by pick_tail_split."""
     if num_sms is None:
         num_sms = sm_count()
     groups = (G + 15) // 16
     items = max(1, B * Hkv * groups)
     slots = ctas_per_sm * num_sms
-    cap = int(max(1, min(-(-max_kv_len // min_chunk), 32)))
-    return int(max(1, min(cap, -(-slots // items))))
+    cap = int(max(1, min(-(-max_kv_len // min_chunk), 64)))
+    return int(max(1, min(cap, slots // items)))
 
 
 def pick_tail_split(B: int, Hkv: int, G: int, num_sms: Optional[int] = None, ctas_per_sm: int = 2,

@@ -19,7 +19,7 @@ def _run_decode(sc, max_splits, min_chunk=64, lse=False):
     ops.build_kv_indices(d.req_to_token, d.req_pool_indices, seq, kv_indptr, kv_indices)
     q = d.q.view(B, sc.Hq, sc.D)
     o = torch.full_like(q, float("nan"))
-    ws = torch.empty(max(ops.decode_workspace_bytes(B, sc.Hq, sc.D, max_splits), 16), dtype=torch.uint8, device=DEV)
+    ws = torch.zeros(max(ops.decode_workspace_bytes(B, sc.Hq, sc.D, max_splits), 16), dtype=torch.uint8, device=DEV)
     lse_t = torch.empty((B, sc.Hq), dtype=torch.float32, device=DEV) if lse else None
     ops.decode_attention(q, d.k_cache, d.v_cache, o, kv_indptr, kv_indices, sc.scaling, max_splits=max_splits,
                          min_chunk=min_chunk, workspace=ws, lse=lse_t)
@@ -71,7 +71,7 @@ def test_decode_matches_reference_golden(path):
     q = g["q"].to(DEV).view(B, Hq, D)
     for ms in (1, 3):
         o = torch.empty_like(q)
-        ws = torch.empty(max(ops.decode_workspace_bytes(B, Hq, D, ms), 16), dtype=torch.uint8, device=DEV)
+        ws = torch.zeros(max(ops.decode_workspace_bytes(B, Hq, D, ms), 16), dtype=torch.uint8, device=DEV)
         ops.decode_attention(q, kc, vc, o, kv_indptr, kv_indices, g["scaling"], max_splits=ms, min_chunk=16,
                              workspace=ws)
         assert_close_attn(o.view(B, -1), g["o_ref"], f"{g['name']} splits{ms}")
@@ -135,7 +135,7 @@ def test_decode_tail_split_matches_oracle(tail_begin, k):
                          kv_indices)
     q = sc.q.to(DEV).view(B, Hq, D)
     o = torch.empty_like(q)
-    ws = torch.empty(ops.decode_workspace_bytes(B, Hq, D, k), dtype=torch.uint8, device=DEV)
+    ws = torch.zeros(ops.decode_workspace_bytes(B, Hq, D, k), dtype=torch.uint8, device=DEV)
     ops.decode_attention(q, kc.to(DEV), vc.to(DEV), o, kv_indptr, kv_indices, sc.scaling, max_splits=k, min_chunk=64,
                          workspace=ws, tail_begin=tail_begin)
     ref = oracle.attention_fp32(sc.q, kc, vc, sc.req_to_token, sc.req_pool_indices, torch.tensor(lens),

@@ -55,7 +55,7 @@ def test_decode_features(feat, Hq, Hkv, D):
                                 sinks=sinks, **f)
     for max_splits in (1, 8):
         o = torch.empty_like(q)
-        ws = torch.empty(max(ops.decode_workspace_bytes(len(lens), Hq, D, max_splits), 16), dtype=torch.uint8,
+        ws = torch.zeros(max(ops.decode_workspace_bytes(len(lens), Hq, D, max_splits), 16), dtype=torch.uint8,
                          device=DEV)
         ops.decode_attention(q, kc.to(DEV), vc.to(DEV), o, kv_indptr, kv_indices, sc.scaling, max_splits=max_splits,
                              min_chunk=128, workspace=ws, sinks=None if sinks is None else sinks.to(DEV), **f)

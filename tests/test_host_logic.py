@@ -51,7 +51,8 @@ def test_pool_shapes_and_padding_row():
 
 def test_pick_max_splits_bounds():
     assert ops.pick_max_splits(64, 8, 4, 4096, num_sms=148) == 1     # 512 CTAs already cover 296 slots
-    assert ops.pick_max_splits(8, 8, 4, 4096, num_sms=148) == 5      # 64 items -> 5 splits fill the slots
+    assert ops.pick_max_splits(8, 8, 4, 4096, num_sms=148) == 4      # 64 units -> 256 CTAs stay in the first wave
     assert ops.pick_max_splits(4096, 8, 4, 4096, num_sms=148) == 1   # enough CTAs already
     assert ops.pick_max_splits(1, 1, 4, 100, num_sms=148) == 1       # never finer than min_chunk
-    assert ops.pick_max_splits(1, 8, 4, 1 << 20, num_sms=148) <= 32
+    assert ops.pick_max_splits(1, 8, 4, 1 << 20, num_sms=148) == 37
+    assert ops.pick_max_splits(16, 8, 4, 16384, num_sms=148) == 2

@@ -36,7 +36,7 @@ for B in (64, 100, 40):
     o = torch.empty_like(q)
     nbytes = B * ctx * Hkv * D * 4 + 2 * B * Hq * D * 2 + B * ctx * 4
     for tb, k in [(-1, 1), ops.pick_tail_split(B, Hkv, Hq // Hkv), (296 * (B * Hkv // 296), 2), (296 * (B * Hkv // 296), 3), (296 * (B * Hkv // 296), 4), (296 * (B * Hkv // 296), 6)]:
-        ws = torch.empty(max(ops.decode_workspace_bytes(B, Hq, D, k), 16), dtype=torch.uint8, device=dev)
+        ws = torch.zeros(max(ops.decode_workspace_bytes(B, Hq, D, k), 16), dtype=torch.uint8, device=dev)
         f = lambda: ops.decode_attention(q, kc, vc, o, kv_indptr, kv_indices, D ** -0.5, max_splits=k, min_chunk=64, workspace=ws, tail_begin=tb)
         t = bench.time_steps(f, 100, 10) / 100
         print(f"B={B:4d} tail_begin={tb:5d} k={k}  {t*1e3:8.1f} us  {nbytes / t / 1e6:8.1f} GB/s", flush=True)

@@ -19,7 +19,7 @@ o = torch.empty_like(q)
 kbuf, vbuf = kv_pool.get_kv_buffer(0)
 nbytes = bench.decode_bytes(c) - 2 * 2 * B * Hkv * D * 2
 for ms in (1, 2, 3, 4, 5, 6, 7, 8, 11, 12, 16):
-    ws = torch.empty(max(ops.decode_workspace_bytes(B, Hq, D, ms), 16), dtype=torch.uint8, device=dev)
+    ws = torch.zeros(max(ops.decode_workspace_bytes(B, Hq, D, ms), 16), dtype=torch.uint8, device=dev)
     f = lambda: ops.decode_attention(q, kbuf, vbuf, o, kv_indptr, kv_indices, D ** -0.5, max_splits=ms, min_chunk=64, workspace=ws)
     t = bench.time_steps(f, 200, 10) / 200
     print(f"max_splits={ms:3d}  {t*1e3:8.1f} us  {nbytes / t / 1e6:8.1f} GB/s", flush=True)
