@@ -48,8 +48,8 @@ constexpr int kExtThreads = 384;  // 2 softmax warpgroups + {K producer, V produ
 constexpr int kExtBoxRows = 16;   // rows of one tiled K/V TMA box
 constexpr float kRescaleThreshold = 8.f;  // log2 domain
 constexpr int kRegsSoftmax = 208, kRegsOther = 80;
-constexpr int kExtMaxItems = 64;  // work items described per round
-constexpr int kExtMaxB = 2048;    // requests per launch (the host slices larger batches)
+constexpr int kExtMaxItems = 32;  // work items described per round
+constexpr int kExtOSlabCols = 32; // epilogue: O leaves through shared memory in 128 x 32 slabs (TMA store)
 
 struct ExtendParams {
   void* o;
@@ -66,6 +66,7 @@ struct ExtendParams {
   int window_left;     // >= 0: query q_id sees only keys kv_id >= q_id - window_left; < 0: off
   float cap_pre;       // logit cap c > 0: s <- tanh(s * cap_pre) / cap_pre with cap_pre = sm_scale / c; 0 = off
   const float* sinks;  // per q head sink logit (natural units) added to the softmax denominator, or null
+  int o_tma;           // full output tiles leave through shared memory + TMA store (o is 16-byte aligned)
 #ifdef EXT_TRACE
   long long* trace;  // dev-only timeline of CTA (0,0,0): [role 0..2][step 0..31][8]
 #endif
@@ -79,10 +80,14 @@ struct ExtSmem {
   static constexpr int kQ = 0;                 // [2] query tiles
   static constexpr int kK = kQ + 2 * kTile;
   static constexpr int kV = kK + kExtStages * kTile;
-  static constexpr int kBar = kV + kExtStages * kTile;
+  static constexpr int kOSlab = kExtM * kExtOSlabCols * 2;                 // one 128 x 32 output slab (8 KB)
+  static constexpr int kO = kV + kExtStages * kTile;                       // [2 tiles][2 buffers] output slabs
+  static constexpr int kBar = kO + 4 * kOSlab;
   static constexpr int kItems = kBar + 256;                                // ItemDesc[kExtMaxItems]
-  static constexpr int kCum = kItems + kExtMaxItems * 32;                  // int[kExtMaxB + 1] pair prefix sums
-  static constexpr int kTotal = kCum + (kExtMaxB + 1) * 4 + 12;
+  static constexpr int kCum = kItems + kExtMaxItems * 32;                  // int[kMaxB + 1] pair prefix sums
+  // requests per launch (the host slices larger batches); D = 128 leaves room for 128 (227 KB shared memory)
+  static constexpr int kMaxB = D == 128 ? 128 : 2048;
+  static constexpr int kTotal = kCum + (kMaxB + 1) * 4 + 12;
 };
 
 // One work item = two query tiles of one (request, kv head); built per round into shared memory.
@@ -213,7 +218,8 @@ template <int D, bool kBf16>
 __global__ void __launch_bounds__(kExtThreads, 1)
     extend_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                   const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_kbox,
-                  const __grid_constant__ CUtensorMap tm_vbox, const ExtendParams p) {
+                  const __grid_constant__ CUtensorMap tm_vbox, const __grid_constant__ CUtensorMap tm_o,
+                  const ExtendParams p) {
   using namespace sm100;
   using S = ExtSmem<D>;
   constexpr int kHalves = D / 64;  // 64-column halves of the head dim
@@ -264,11 +270,11 @@ __global__ void __launch_bounds__(kExtThreads, 1)
   }
   if (warp == 10) tmem_alloc<kTmemCols>(smem_u32(tmem_slot));
   if (warp == 8 && lane == 0) {
-    tma_prefetch_desc(&tm_q);
     tma_prefetch_desc(&tm_k);
     tma_prefetch_desc(&tm_kbox);
   }
   if (warp == 9 && lane == 0) {
+    tma_prefetch_desc(&tm_q);
     tma_prefetch_desc(&tm_v);
     tma_prefetch_desc(&tm_vbox);
   }
@@ -325,7 +331,11 @@ __global__ void __launch_bounds__(kExtThreads, 1)
           const ItemDesc d = items[it];
           ItemTiles t;
           derive_tiles(d, p, t);
-          if (is_k) {
+          // The Q tiles are loaded by the V producer: the K producer must NOT wait for the previous item's last
+          // QK (QEmpty) — it runs ahead into this item's first K tiles (ring permitting) while the previous item
+          // drains, so QK(0) can issue as soon as Q lands.  V tiles are needed a softmax later than K tiles, so the
+          // V producer has the slack to sit on that barrier.
+          if (!is_k) {
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
               if (t.nc[i] == 0) continue;
@@ -449,9 +459,12 @@ __global__ void __launch_bounds__(kExtThreads, 1)
               umma_commit(barb + 8u * (kBarPVDone + i));
               if (c == nc_i - 1) umma_commit(barb + 8u * (kBarOFinal + i));
             };
+            if (i == 0) { TRACE(5, it, 0); }
             if (nc_i > 0) mbar_wait(barb + 8u * (kBarQ + i), nqi & 1);
+            if (i == 0) { TRACE(5, it, 1); }
             mbar_wait(barb + 8u * (kBarKFull + ktl % kExtStages), (ktl / kExtStages) & 1);
             tc_fence_after();
+            if (i == 0) { TRACE(5, it, 2); }
             if (nc_i > 0) issue_qk(0);
             if (nc_i > 1) issue_qk(1);
             umma_commit(barb + 8u * (kBarKEmpty + ktl % kExtStages));
@@ -474,6 +487,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
               if ((c & 1) == 1 || c == nc - 1) umma_commit(barb + 8u * (kBarVEmpty + st));
               if ((c & 1) == 1 && c + 1 < nc) umma_commit(barb + 8u * (kBarKEmpty + st1));
             }
+            if (i == 0) { TRACE(5, it, 3); }
           }
           __syncwarp();
           kt += ntl;
@@ -522,6 +536,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         derive_tiles(d, p, t);
         const int nc_i = i == 0 ? t.nc[0] : t.nc[1];
         if (nc_i == 0) continue;
+        if (i == 0) { TRACE(4, it, 0); }
         const int m0 = i == 0 ? t.m0[0] : t.m0[1];
         const int kvend_i = i == 0 ? t.kvend[0] : t.kvend[1];
         // keys visible to this row: [0, limit)
@@ -538,6 +553,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
           mbar_wait(bar(kBarSFull + i * 2 + (gc & 1)), (gc >> 1) & 1);
           tc_fence_after();
           TRACE(i, c, 1);
+          if (i == 0 && c == 0) { TRACE(4, it, 1); }
           float s[kExtC];
 #pragma unroll
           for (int q = 0; q < kExtC / 32; ++q) {
@@ -635,19 +651,30 @@ __global__ void __launch_bounds__(kExtThreads, 1)
           TRACE(i, c, 5);
         }
         // ---- epilogue of this item (the issuer already runs QK of the next one) ----
+        if (i == 0) { TRACE(4, it, 2); }
         mbar_wait(bar(kBarOFinal + i), nq_my & 1);
         tc_fence_after();
+        if (i == 0) { TRACE(4, it, 3); }
         const int h = i == 0 ? t.h[0] : t.h[1];
         if (p.sinks != nullptr) l_run += ex2_approx(__ldg(p.sinks + h) * kLog2e - m_used);
         const float inv = 1.f / l_run;
-        const bool valid = row < (i == 0 ? t.rows[0] : t.rows[1]);
-        T* dst = reinterpret_cast<T*>(p.o) + (int64_t)(d.q_beg + m0 + row) * p.o_stride + (int64_t)h * D;
+        const int rows_i = i == 0 ? t.rows[0] : t.rows[1];
+        const bool valid = row < rows_i;
+        if (rows_i == kExtM && p.o_tma) {
+          // Full tile: O leaves through shared memory and the copy engine.  A thread owns a ROW, so direct stores
+          // are 32 scattered 16-byte pieces per warp instruction (measured: 4.7 k cycles per item, LSU-bound);
+          // here each 128 x 32 slab is written to a 64B-swizzled staging buffer (conflict free) and one thread
+          // issues a 2-D TMA store.  Two buffers per tile: slab j waits only for the store of slab j-2.
+          const uint32_t obuf = smem0 + S::kO + i * 2 * S::kOSlab;
+          const int bar_id = 1 + i;  // named barrier of this warpgroup
 #pragma unroll
-        for (int c = 0; c < D / 32; ++c) {
-          uint32_t v[32];
-          tmem_ld32(col_o + c * 32, v);
-          tmem_wait_ld();
-          if (valid) {
+          for (int c = 0; c < D / kExtOSlabCols; ++c) {
+            uint32_t v[32];
+            tmem_ld32(col_o + c * 32, v);
+            if (row == 0) asm volatile("cp.async.bulk.wait_group.read 1;\n" ::: "memory");
+            tmem_wait_ld();
+            asm volatile("bar.sync %0, 128;\n" ::"r"(bar_id) : "memory");  // buffer (c & 1) is free again
+            const uint32_t dst = obuf + (c & 1) * S::kOSlab + row * 64;
 #pragma unroll
             for (int e = 0; e < 32; e += 8) {
               uint4 w;
@@ -655,18 +682,52 @@ __global__ void __launch_bounds__(kExtThreads, 1)
               w.y = pack2<kBf16>(__uint_as_float(v[e + 2]) * inv, __uint_as_float(v[e + 3]) * inv);
               w.z = pack2<kBf16>(__uint_as_float(v[e + 4]) * inv, __uint_as_float(v[e + 5]) * inv);
               w.w = pack2<kBf16>(__uint_as_float(v[e + 6]) * inv, __uint_as_float(v[e + 7]) * inv);
-              *reinterpret_cast<uint4*>(dst + c * 32 + e) = w;
+              const uint32_t chunk = (uint32_t)(e >> 3) ^ ((uint32_t)(row >> 1) & 3u);  // CU_TENSOR_MAP_SWIZZLE_64B
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(dst + chunk * 16), "r"(w.x),
+                           "r"(w.y), "r"(w.z), "r"(w.w)
+                           : "memory");
+            }
+            fence_proxy_async_smem();
+            asm volatile("bar.sync %0, 128;\n" ::"r"(bar_id) : "memory");
+            if (row == 0) {
+              asm volatile(
+                  "cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];\n" ::"l"(&tm_o),
+                  "r"(obuf + (c & 1) * S::kOSlab), "r"(h * D + c * kExtOSlabCols), "r"(d.q_beg + m0)
+                  : "memory");
+              asm volatile("cp.async.bulk.commit_group;\n" ::: "memory");
+            }
+          }
+        } else {
+          T* dst = reinterpret_cast<T*>(p.o) + (int64_t)(d.q_beg + m0 + row) * p.o_stride + (int64_t)h * D;
+#pragma unroll
+          for (int c = 0; c < D / 32; ++c) {
+            uint32_t v[32];
+            tmem_ld32(col_o + c * 32, v);
+            tmem_wait_ld();
+            if (valid) {
+#pragma unroll
+              for (int e = 0; e < 32; e += 8) {
+                uint4 w;
+                w.x = pack2<kBf16>(__uint_as_float(v[e]) * inv, __uint_as_float(v[e + 1]) * inv);
+                w.y = pack2<kBf16>(__uint_as_float(v[e + 2]) * inv, __uint_as_float(v[e + 3]) * inv);
+                w.z = pack2<kBf16>(__uint_as_float(v[e + 4]) * inv, __uint_as_float(v[e + 5]) * inv);
+                w.w = pack2<kBf16>(__uint_as_float(v[e + 6]) * inv, __uint_as_float(v[e + 7]) * inv);
+                *reinterpret_cast<uint4*>(dst + c * 32 + e) = w;
+              }
             }
           }
         }
         if (valid && p.lse != nullptr)
           p.lse[(int64_t)(d.q_beg + m0 + row) * p.Hq + h] = (m_used + log2f(l_run)) * kLn2;
         tc_fence_before();
+        if (i == 0) { TRACE(4, it, 4); }
         g_my += nc_i;
         ++nq_my;
       }
       __syncthreads();  // every role is done with this round's descriptors
     }
+    // the staged output slabs must have left shared memory (and be globally visible) before the CTA retires
+    if ((threadIdx.x & 127) == 0) asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
@@ -708,7 +769,8 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 int make_tensor_map_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
-                       uint64_t row_stride_bytes, uint32_t box_cols, uint32_t box_rows) {
+                       uint64_t row_stride_bytes, uint32_t box_cols, uint32_t box_rows,
+                       CUtensorMapSwizzle swizzle) {
   EncodeTiledFn fn = get_encode_fn();
   if (fn == nullptr) {
     set_error("cuTensorMapEncodeTiled is not available from the driver");
@@ -719,7 +781,7 @@ int make_tensor_map_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64
   cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void*>(base), dims, strides,
-                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%llu cols=%llu stride=%llu)",
@@ -732,8 +794,8 @@ int make_tensor_map_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64
 
 template <int D, bool kBf16>
 static int launch_extend(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
-                         const CUtensorMap& tkb, const CUtensorMap& tvb, const ExtendParams& p,
-                         int max_qtiles, cudaStream_t st) {
+                         const CUtensorMap& tkb, const CUtensorMap& tvb, const CUtensorMap& to,
+                         const ExtendParams& p, int max_qtiles, cudaStream_t st) {
   constexpr int kSmem = ExtSmem<D>::kTotal + 1024;  // + alignment slack
   static bool configured = false;
   if (!configured) {
@@ -746,14 +808,15 @@ static int launch_extend(const CUtensorMap& tq, const CUtensorMap& tk, const CUt
   // them in L2.  The host only knows an upper bound of the item count (sizes the grid, graph-safe).
   const long long upper = (long long)((max_qtiles * p.G + 1) / 2) * p.Hkv;
   const int sms = sm_count();
-  for (int b0 = 0; b0 < p.B; b0 += kExtMaxB) {  // the in-kernel prefix table holds kExtMaxB requests
+  constexpr int kExtMaxB = ExtSmem<D>::kMaxB;
+  for (int b0 = 0; b0 < p.B; b0 += kExtMaxB) {  // the in-kernel prefix table holds kMaxB requests
     ExtendParams ps = p;
     ps.B = p.B - b0 < kExtMaxB ? p.B - b0 : kExtMaxB;
     ps.qo_indptr = p.qo_indptr + b0;
     ps.kv_indptr = p.kv_indptr + b0;
     const long long items = upper * ps.B;
     dim3 grid((unsigned)(items < sms ? items : sms));
-    extend_kernel<D, kBf16><<<grid, kExtThreads, kSmem, st>>>(tq, tk, tv, tkb, tvb, ps);
+    extend_kernel<D, kBf16><<<grid, kExtThreads, kSmem, st>>>(tq, tk, tv, tkb, tvb, to, ps);
     B2_LAUNCH_CHECK();
   }
   return B200ATTN_OK;
@@ -793,7 +856,7 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
                "extend: tensors must be 16-byte aligned");
   if (dtype != B200ATTN_BF16 && dtype != B200ATTN_FP16) B2_UNSUPPORTED("extend: dtype %d", dtype);
   if (D != 64 && D != 128) B2_UNSUPPORTED("extend: head_dim %d (supported: 64, 128)", D);
-  CUtensorMap tq, tk, tv, tkb, tvb;
+  CUtensorMap tq, tk, tv, tkb, tvb, to;
   int rc = make_tensor_map_2d(&tq, q, (uint64_t)total_q_host, (uint64_t)Hq * D,
                               (uint64_t)q_stride * 2, 64, kExtM);
   if (rc) return rc;
@@ -809,7 +872,12 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
   rc = make_tensor_map_2d(&tvb, v_cache, (uint64_t)num_slots, (uint64_t)Hkv * D,
                           (uint64_t)kv_stride * 2, 64, kExtBoxRows);
   if (rc) return rc;
+  rc = make_tensor_map_2d(&to, o, (uint64_t)total_q_host, (uint64_t)Hq * D, (uint64_t)o_stride * 2,
+                          kExtOSlabCols, kExtM, CU_TENSOR_MAP_SWIZZLE_64B);
+  if (rc) return rc;
   ExtendParams p;
+  p.o_tma = 1;
+  if (const char* e = getenv("B200ATTN_EXT_OTMA")) p.o_tma = atoi(e) != 0;  // dev ablation hook
   p.o = o;
   p.lse = lse;
   p.qo_indptr = qo_indptr;
@@ -828,13 +896,13 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
   p.cap_pre = logit_cap > 0.f ? sm_scale / logit_cap : 0.f;
   p.sinks = sinks;
 #ifdef EXT_TRACE
-  p.trace = workspace_bytes >= 4 * 32 * 8 * 8 ? (long long*)workspace : nullptr;
+  p.trace = workspace_bytes >= 6 * 32 * 8 * 8 ? (long long*)workspace : nullptr;
 #endif
   const int max_qtiles = (max_qo_len_host + kExtM - 1) / kExtM;
   cudaStream_t st = (cudaStream_t)stream;
   if (D == 128)
-    return dtype == B200ATTN_BF16 ? launch_extend<128, true>(tq, tk, tv, tkb, tvb, p, max_qtiles, st)
-                                  : launch_extend<128, false>(tq, tk, tv, tkb, tvb, p, max_qtiles, st);
-  return dtype == B200ATTN_BF16 ? launch_extend<64, true>(tq, tk, tv, tkb, tvb, p, max_qtiles, st)
-                                : launch_extend<64, false>(tq, tk, tv, tkb, tvb, p, max_qtiles, st);
+    return dtype == B200ATTN_BF16 ? launch_extend<128, true>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st)
+                                  : launch_extend<128, false>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st);
+  return dtype == B200ATTN_BF16 ? launch_extend<64, true>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st)
+                                : launch_extend<64, false>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st);
 }

@@ -181,6 +181,7 @@ __host__ __device__ constexpr uint32_t idesc_f16(int fmt, int M, int N, int a_mn
 
 // Host: encode a 2D row-major tensor map ([rows][cols] of 2-byte elements, 128B swizzle).
 int make_tensor_map_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
-                       uint64_t row_stride_bytes, uint32_t box_cols, uint32_t box_rows);
+                       uint64_t row_stride_bytes, uint32_t box_cols, uint32_t box_rows,
+                       CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B);
 
 }  // namespace b200attn
