@@ -182,6 +182,11 @@ int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
  * in one physical page) and enables TMA page boxes; page_size == 1 gathers rows.
  * `lse` nullable float[T*Hq] natural log.  `max_qo_len_host` / `total_q_host`
  * are host-side upper bounds used only to size the grid (graph-safe).
+ * `custom_mask` (nullable uint8, nonzero = visible) with `mask_indptr` int32[B+1]:
+ * TARGET_VERIFY tree masks of speculative decoding (extend_attention.py:467-479,
+ * triton_backend.py:911-917): request b owns the row-major block
+ * custom_mask[mask_indptr[b] + j * L_b + n]; `mask_skip_prefix` keeps the prefix
+ * keys (n < L_b - E_b) always visible.  Combine with causal = 0.
  * -------------------------------------------------------------------------- */
 #define B200ATTN_EXT_CAUSAL 1
 #define B200ATTN_EXT_SKIP_SINGLE 2
@@ -195,7 +200,8 @@ int b200attn_extend(const void* q, int64_t q_stride, const void* k_cache,
                     int64_t total_q_host, int32_t max_qo_len_host, int32_t Hq,
                     int32_t Hkv, int32_t D, int32_t page_size, int dtype, int causal,
                     float sm_scale, int32_t window_left, float logit_cap,
-                    const float* sinks, void* workspace, int64_t workspace_bytes,
+                    const float* sinks, const uint8_t* custom_mask, const int32_t* mask_indptr,
+                    int mask_skip_prefix, void* workspace, int64_t workspace_bytes,
                     void* stream);
 
 /* --------------------------------------------------------------------------

@@ -200,7 +200,8 @@ def merge_state(v_a: torch.Tensor, s_a: torch.Tensor, v_b: torch.Tensor, s_b: to
 def attention_fp32(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, req_to_token: torch.Tensor,
                    req_pool_indices: torch.Tensor, seq_lens: torch.Tensor, extend_seq_lens: torch.Tensor,
                    num_q_heads: int, num_kv_heads: int, head_dim: int, scaling: float, causal: bool,
-                   return_lse: bool = False, window_left: int = -1, logit_cap: float = 0.0, sinks=None):
+                   return_lse: bool = False, window_left: int = -1, logit_cap: float = 0.0, sinks=None,
+                   custom_masks=None, skip_prefix_custom_mask: bool = True):
     """Independent fp32-softmax reference (works on any device, used at large sizes).
 
     Restates the reference kit's ``_dense_attention_reference``
@@ -212,7 +213,10 @@ def attention_fp32(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor
     Feature flags restate the production kernels: ``window_left`` = the kit's extend-window rule
     ``kv_id >= q_id - window`` (dense_attention.py:831-840, extend_attention.py:480-486); ``logit_cap``:
     ``cap * tanh(qk / cap)`` (extend_attention.py:546-547); ``sinks`` [Hq]: ``exp(sink - max)`` joins the
-    denominator (extend_attention.py:721-723, decode_attention.py:986-988).
+    denominator (extend_attention.py:721-723, decode_attention.py:986-988).  ``custom_masks``: per request a bool
+    ``[E, L]`` block (True = visible), the TARGET_VERIFY tree mask of ``dense_attention_reference_with_custom_mask``
+    (dense_attention.py:858-905); with ``skip_prefix_custom_mask`` the prefix keys stay visible
+    (extend_attention.py:467-479).
     """
     T = q.shape[0]
     G = num_q_heads // num_kv_heads
@@ -234,6 +238,11 @@ def attention_fp32(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor
             s = s.masked_fill(kpos > qpos, -math.inf)
         if window_left >= 0:
             s = s.masked_fill(kpos < qpos - window_left, -math.inf)
+        if custom_masks is not None:
+            allowed = custom_masks[i].to(q.device).bool().view(1, E, L).clone()
+            if skip_prefix_custom_mask:
+                allowed[..., :L - E] = True
+            s = s.masked_fill(~allowed, -math.inf)
         if sinks is not None:
             sk = sinks.to(s.device).float().view(-1, 1, 1).expand(-1, E, 1)
             full = torch.cat([s, sk], dim=-1)

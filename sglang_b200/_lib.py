@@ -47,7 +47,7 @@ SIGNATURES = {
     "b200attn_extend": (
         C.c_int,
         [_vp, _i64, _vp, _vp, _i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _i32, _i32,
-         _i32, _i32, C.c_int, C.c_int, _f32, _i32, _f32, _vp, _vp, _i64, _vp],
+         _i32, _i32, C.c_int, C.c_int, _f32, _i32, _f32, _vp, _vp, _vp, C.c_int, _vp, _i64, _vp],
     ),
     "b200attn_merge_state": (
         C.c_int,

@@ -64,6 +64,9 @@ class ForwardMetadata:
     dec_req_ids: Optional[torch.Tensor] = None  # int32 [num_dec] request index (kv_indptr entry)
     num_dec: int = 0
     dec_max_kv_len: int = 0
+    # TARGET_VERIFY (speculative decoding): flat tree mask + int32 offsets (triton_backend.py:911-917)
+    custom_mask: Optional[torch.Tensor] = None
+    mask_indptr: Optional[torch.Tensor] = None
 
 
 def _attn_type_value(layer) -> str:
@@ -185,8 +188,10 @@ class B200AttnBackend(_Base):
             md._max_kv_len = int(cpu.max()) if cpu is not None else self.max_context_len
             self.forward_metadata = md
             return
-        if mode.is_target_verify() or mode.is_draft_extend_v2() or getattr(fb, "spec_info", None) is not None:
-            raise NotImplementedError("b200 backend: speculative modes (custom masks) are not supported")
+        if mode.is_target_verify():
+            return self._init_target_verify(fb, B, kv_indptr)
+        if mode.is_draft_extend_v2() or getattr(fb, "spec_info", None) is not None:
+            raise NotImplementedError("b200 backend: draft-extend speculative modes are not supported")
         if getattr(fb, "encoder_lens", None) is not None:
             raise NotImplementedError("b200 backend: encoder_lens (cross attention) is not supported")
         qo_indptr = torch.empty(B + 1, dtype=torch.int32, device=dev)
@@ -213,6 +218,34 @@ class B200AttnBackend(_Base):
             pre_cpu = getattr(fb, "extend_prefix_lens_cpu", None)
             md.dec_max_kv_len = (max(pre_cpu[b] for b in reqs) + 1) if pre_cpu is not None else self.max_context_len
         self.forward_metadata = md
+
+    def _init_target_verify(self, fb, B: int, kv_indptr: torch.Tensor) -> None:
+        """TARGET_VERIFY (triton_backend.py:859-917): every request verifies ``draft_token_num`` tokens under the
+        tree mask ``spec_info.custom_mask`` (row-major ``[draft, seq_len + draft]`` blocks, prefix keys always
+        visible).  ``seq_lens`` counts the cached tokens only; the draft tokens' K/V are stored by forward_extend at
+        ``out_cache_loc`` and appended to ``kv_indices`` here, so the kernels still see one KV source."""
+        spec = fb.spec_info
+        nd = int(spec.draft_token_num)
+        dev = self.device
+        seq = fb.seq_lens.to(torch.int64)
+        kv_lens = seq + nd
+        total = getattr(fb, "seq_lens_sum", None)
+        total = (int(total) if total else B * self.max_context_len) + B * nd
+        kv_indices = torch.zeros(total, dtype=torch.int32, device=dev)
+        qo_lens = torch.full((B,), nd, dtype=torch.int32, device=dev)
+        qo_indptr = torch.empty(B + 1, dtype=torch.int32, device=dev)
+        self._build(fb, kv_lens, kv_indptr, kv_indices, qo_lens=qo_lens, qo_indptr=qo_indptr)
+        tail = (kv_indptr[:B].to(torch.int64) + seq)[:, None] + torch.arange(nd, device=dev)[None, :]
+        kv_indices[tail.reshape(-1)] = fb.out_cache_loc[:B * nd].to(torch.int32)
+        mask_indptr = torch.zeros(B + 1, dtype=torch.int32, device=dev)
+        mask_indptr[1:] = torch.cumsum(nd * kv_lens, 0).to(torch.int32)
+        mask = spec.custom_mask
+        if mask.dtype not in (torch.bool, torch.uint8):
+            mask = mask != 0
+        self.forward_metadata = ForwardMetadata(
+            kv_indptr=kv_indptr, kv_indices=kv_indices, qo_indptr=qo_indptr, batch_size=B,
+            cache_seqlens_int32=kv_lens.to(torch.int32), max_extend_len=nd, num_extend_tokens=B * nd,
+            min_chunk=self.MIN_CHUNK, custom_mask=mask.contiguous(), mask_indptr=mask_indptr)
 
     # --- CUDA-graph hooks (base_attn_backend.py:73-107,159-197; triton_backend.py:1014-1115)
     def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int, *, num_q_heads: Optional[int] = None,
@@ -359,6 +392,10 @@ class B200AttnBackend(_Base):
             self._store(layer, forward_batch, k, v)
         # torch_native_backend.py:308-310 — DECODER_BIDIRECTIONAL stays causal in the oracle
         causal = not (getattr(layer, "is_cross_attention", False) or _attn_type_value(layer) == "encoder_only")
+        mask_kw = {}
+        if md.custom_mask is not None:  # TARGET_VERIFY: the tree mask replaces the causal mask (triton_backend.py:1376-1379)
+            causal = False
+            mask_kw = dict(custom_mask=md.custom_mask, mask_indptr=md.mask_indptr, skip_prefix_custom_mask=True)
         kbuf, vbuf = self.token_to_kv_pool.get_kv_buffer(layer.layer_id)
         B = md.batch_size
         if md.max_extend_len > 0:
@@ -368,7 +405,7 @@ class B200AttnBackend(_Base):
                                  max_qo_len=md.max_extend_len,
                                  total_q=q2.shape[0] if getattr(md, "_graph", False) else md.num_extend_tokens,
                                  workspace=ws,
-                                 skip_single_rows=md.num_dec > 0, **self._features(layer, kwargs))
+                                 skip_single_rows=md.num_dec > 0, **mask_kw, **self._features(layer, kwargs))
         if md.num_dec > 0:  # a single query row sees all of its keys, causal or not
             Hkv = layer.tp_k_head_num
             ms = ops.pick_max_splits(md.num_dec, Hkv, Hq // Hkv, md.dec_max_kv_len, md.min_chunk,

@@ -60,6 +60,18 @@ def _sinks_ptr(sinks: Optional[torch.Tensor], Hq: int) -> Optional[int]:
     return sinks.data_ptr()
 
 
+def _mask_ptr(custom_mask: Optional[torch.Tensor], mask_indptr: Optional[torch.Tensor], B: int) -> Optional[int]:
+    """TARGET_VERIFY custom mask: flat bool / uint8 on the device + int32 mask_indptr[B+1] (triton_backend.py:911-917)."""
+    if custom_mask is None:
+        return None
+    _require_cuda(custom_mask, mask_indptr)
+    if custom_mask.dtype not in (torch.bool, torch.uint8) or not custom_mask.is_contiguous():
+        raise TypeError("custom_mask must be a contiguous bool / uint8 tensor")
+    if mask_indptr is None or mask_indptr.dtype != torch.int32 or mask_indptr.numel() < B + 1:
+        raise ValueError("custom_mask needs an int32 mask_indptr with B + 1 entries")
+    return custom_mask.data_ptr()
+
+
 def sm_count() -> int:
     return _lib.load().b200attn_sm_count()
 
@@ -438,6 +450,9 @@ def extend_attention(
     window_left: int = -1,
     logit_cap: float = 0.0,
     sinks: Optional[torch.Tensor] = None,
+    custom_mask: Optional[torch.Tensor] = None,
+    mask_indptr: Optional[torch.Tensor] = None,
+    skip_prefix_custom_mask: bool = True,
 ) -> torch.Tensor:
     """Ragged prefix+extend attention: ``q [T,Hq,D]`` -> ``o [T,Hq,D]``.
 
@@ -470,7 +485,8 @@ def extend_attention(
         qo_indptr.data_ptr(), kv_indptr.data_ptr(), kv_indices.data_ptr(), B,
         T if total_q is None else total_q, max_qo_len, Hq, Hkv, D, page_size, _fdtype(q),
         (1 if causal else 0) | (2 if skip_single_rows else 0), float(sm_scale), int(window_left),
-        float(logit_cap), _sinks_ptr(sinks, Hq), _ptr(workspace), ws_bytes,
+        float(logit_cap), _sinks_ptr(sinks, Hq), _mask_ptr(custom_mask, mask_indptr, B), _ptr(mask_indptr),
+        int(bool(skip_prefix_custom_mask)), _ptr(workspace), ws_bytes,
         _stream(),
     )
     check(rc, "b200attn_extend")

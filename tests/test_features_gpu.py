@@ -118,3 +118,74 @@ def test_backend_layer_flags_decode_equals_mixed_row():
     backend.init_forward_metadata(fb2)
     o_dec = layer(sc.q[rows].to(DEV), sc.k[rows].to(DEV), sc.v[rows].to(DEV), fb2, sinks=sinks)
     assert torch.equal(o_dec, o_mixed[rows])
+
+
+@pytest.mark.parametrize("skip_prefix", [True, False])
+@pytest.mark.parametrize("Hq,Hkv,D", [(8, 2, 128), (14, 2, 64)])
+def test_extend_custom_mask_target_verify(skip_prefix, Hq, Hkv, D):
+    """TARGET_VERIFY tree masks: request b owns the row-major block custom_mask[mask_indptr[b] + j * L + n]."""
+    from sglang_b200 import ops
+    pre, ext = [37, 0, 300, 1000, 129], [8, 8, 8, 8, 8]   # 8 draft tokens per request
+    sc = make_scenario(pre, ext, Hq, Hkv, D, 16, seed=23)
+    kc, vc = _filled(sc)
+    kv_indptr, kv_indices, qo_indptr = _meta(sc, ops)
+    g = torch.Generator().manual_seed(7)
+    masks, flat = [], []
+    for p_, e in zip(pre, ext):
+        L = p_ + e
+        m = torch.rand((e, L), generator=g) < 0.6
+        tri = torch.tril(torch.ones(e, e, dtype=torch.bool))          # a draft token never sees later draft tokens
+        m[:, p_:] &= tri
+        m[torch.arange(e), p_ + torch.arange(e)] = True               # ... and always sees itself
+        masks.append(m)
+        flat.append(m.reshape(-1))
+    flat = torch.cat(flat)
+    mask_indptr = torch.tensor([0] + [int(x) for x in torch.cumsum(torch.tensor([m.numel() for m in masks]), 0)],
+                               dtype=torch.int32)
+    q = sc.q.to(DEV).view(-1, Hq, D)
+    o = torch.zeros_like(q)
+    ops.extend_attention(q, kc.to(DEV), vc.to(DEV), o, qo_indptr, kv_indptr, kv_indices, sc.scaling, causal=False,
+                         page_size=16, max_qo_len=max(ext), custom_mask=flat.to(DEV), mask_indptr=mask_indptr.to(DEV),
+                         skip_prefix_custom_mask=skip_prefix)
+    ref = oracle.attention_fp32(sc.q, kc, vc, sc.req_to_token, sc.req_pool_indices, torch.tensor(sc.seq_lens),
+                                torch.tensor(ext), Hq, Hkv, D, sc.scaling, causal=False, custom_masks=masks,
+                                skip_prefix_custom_mask=skip_prefix)
+    assert_close_attn(o.view(sum(ext), -1), ref, f"custom mask skip_prefix={skip_prefix}")
+
+
+def test_backend_target_verify_tree_mask():
+    """ForwardMode.TARGET_VERIFY through B200AttnBackend: seq_lens counts cached tokens only, the draft tokens are
+    stored at out_cache_loc and appended to the KV index list, the tree mask replaces the causal mask."""
+    from types import SimpleNamespace
+
+    from sglang_b200 import ForwardBatch, ForwardMode, RadixAttention
+    from tests.test_backend_gpu import _setup
+    Hq, Hkv, D, page, nd = 8, 2, 128, 16, 6
+    pre = [50, 0, 333, 16]
+    sc = make_scenario(pre, [nd] * len(pre), Hq, Hkv, D, page, seed=29)
+    B = len(pre)
+    g = torch.Generator().manual_seed(9)
+    masks = []
+    for p_ in pre:
+        m = torch.ones((nd, p_ + nd), dtype=torch.bool)
+        tree = torch.tril(torch.rand((nd, nd), generator=g) < 0.5)
+        tree[torch.arange(nd), torch.arange(nd)] = True
+        m[:, p_:] = tree
+        masks.append(m)
+    flat = torch.cat([m.reshape(-1) for m in masks])
+    backend, req_pool, kv_pool = _setup(sc, False)
+    # the verify batch has NOT written its draft slots into req_to_token: wipe them to prove out_cache_loc is used
+    for b, p_ in enumerate(pre):
+        req_pool.req_to_token[b + 1, p_:p_ + nd] = 0
+    layer = RadixAttention(Hq, D, sc.scaling, Hkv, 0)
+    fb = ForwardBatch(forward_mode=ForwardMode.TARGET_VERIFY, batch_size=B, req_pool_indices=sc.req_pool_indices.to(DEV),
+                      seq_lens=torch.tensor(pre, device=DEV), out_cache_loc=sc.out_cache_loc.to(DEV),
+                      seq_lens_sum=sum(pre), attn_backend=backend,
+                      spec_info=SimpleNamespace(custom_mask=flat.to(DEV), draft_token_num=nd))
+    backend.init_forward_metadata(fb)
+    o = layer(sc.q.to(DEV), sc.k.to(DEV), sc.v.to(DEV), fb)
+    kc, vc = _filled(sc)
+    ref = oracle.attention_fp32(sc.q, kc, vc, sc.req_to_token, sc.req_pool_indices, torch.tensor(sc.seq_lens),
+                                torch.tensor([nd] * B), Hq, Hkv, D, sc.scaling, causal=False, custom_masks=masks)
+    assert_close_attn(o, ref, "target verify")
+    assert torch.equal(kv_pool.k_buffer[0][sc.out_cache_loc.to(DEV)], sc.k.to(DEV))

@@ -50,3 +50,5 @@ run(64, 0, 256, 32, 8)
 run(128, 0, 128, 32, 8)
 run(1, 8192, 8192, 64, 8)
 run(4, 0, 4096, 32, 8)
+run(1, 8192, 8192, 8, 1)
+run(1, 8192, 8192, 16, 2)
