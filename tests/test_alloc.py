@@ -97,3 +97,24 @@ def test_device_alloc_reports_exhaustion():
     ops.alloc_extend(torch.tensor([0], device="cuda"), torch.tensor([48], device="cuda"),
                      torch.tensor([-1], device="cuda"), torch.tensor([5, 6], device="cuda"), out, 16, status)
     assert int(status) == 1 and int(out[0]) == -7
+
+
+@pytest.mark.gpu
+def test_device_alloc_extend_large_ragged_batch():
+    """4096 requests, ragged prefixes / extends, page 16: bit-exact against the numpy oracle; every slot unique."""
+    from sglang_b200 import ops
+    g = torch.Generator().manual_seed(99)
+    B, page = 4096, 16
+    pre = torch.randint(0, 3000, (B,), generator=g)
+    ext = torch.randint(1, 200, (B,), generator=g)
+    seq = pre + ext
+    n_new = int(((seq + page - 1) // page - (pre + page - 1) // page).sum())
+    perm = torch.randperm(B + n_new + 64, generator=g) + 1
+    last = torch.where(pre > 0, perm[:B] * page + (pre - 1) % page, torch.full_like(pre, -1))
+    free = perm[B:B + n_new + 8]
+    want = alloc_port.alloc_extend(pre, seq, last, free, page)
+    out = torch.full((int(ext.sum()),), -7, dtype=torch.int64, device="cuda")
+    status = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ops.alloc_extend(pre.cuda(), seq.cuda(), last.cuda(), free.cuda(), out, page, status)
+    assert np.array_equal(out.cpu().numpy(), want) and int(status) == 0
+    assert len(np.unique(want)) == len(want)

@@ -139,3 +139,34 @@ def test_errors_and_empty():
                                                   mrope_section=[8, 8, 8])
     with pytest.raises(TypeError):
         ops.apply_rope_with_cos_sin_cache_inplace(pos, q, q.clone(), cache.double(), head_size=64)
+
+
+def test_full_size_cfg3_properties():
+    """BASELINE configs[2] token count (16,384 tokens, Llama-3.1-8B heads) through the bulk-copy pipeline:
+    (1) sampled rows bit-exact against the oracle, (2) rotation preserves every pair's norm up to the output rounding,
+    (3) position 0 is the identity, (4) the pool holds exactly the rotated k and the untouched v."""
+    from sglang_b200 import ops
+    T, Hq, Hkv, D = 16384, 32, 8, 128
+    g = torch.Generator(device=DEV).manual_seed(11)
+    qkv = torch.randn((T, (Hq + 2 * Hkv) * D), device=DEV, generator=g).bfloat16()
+    q, k, v = qkv.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+    q0, k0, v0 = q.clone(), k.clone(), v.clone()
+    pos = torch.randint(0, 8192, (T,), device=DEV, generator=g)
+    pos[::97] = 0
+    cache = rope_port.cos_sin_cache(D, 8192, 500000.0).to(DEV)
+    slots = 2 * T + 16
+    kc = torch.zeros((slots, Hkv, D), device=DEV).bfloat16()
+    vc = torch.zeros_like(kc)
+    loc = torch.randperm(slots - 16, device=DEV, generator=g)[:T] + 16
+    ops.apply_rope_with_cos_sin_cache_inplace(pos, q, k, cache, head_size=D, v=v, k_buffer=kc, v_buffer=vc, cache_loc=loc)
+    rows = torch.arange(0, T, 331, device=DEV)
+    want_q = rope_port.rope_f32(pos[rows].cpu(), q0[rows].cpu().contiguous(), cache.cpu(), D, D, True)
+    want_k = rope_port.rope_f32(pos[rows].cpu(), k0[rows].cpu().contiguous(), cache.cpu(), D, D, True)
+    assert torch.equal(_bits(q[rows].cpu()), _bits(want_q)) and torch.equal(_bits(k[rows].cpu()), _bits(want_k))
+    a, b = q0.view(T, Hq, D).float(), q.view(T, Hq, D).float()
+    n0 = a[..., :64] ** 2 + a[..., 64:] ** 2
+    n1 = b[..., :64] ** 2 + b[..., 64:] ** 2
+    assert float(((n1 - n0).abs() / (n0 + 1e-3)).max()) < 3e-2            # bf16 output rounding of both components
+    ident = pos == 0
+    assert torch.equal(q[ident], q0[ident]) and torch.equal(k[ident], k0[ident])
+    assert torch.equal(kc[loc].view(T, -1), k) and torch.equal(vc[loc].view(T, -1), v0) and torch.equal(v, v0)
