@@ -15,6 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200attn.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "b200attn.h")
 
+ABI_VERSION = 6  # b200attn_abi_version() of the library this binding matches (api.cu)
 BF16, FP16, FP32 = 0, 1, 2
 I32, I64 = 0, 1
 
