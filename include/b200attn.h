@@ -160,6 +160,54 @@ int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
                     int64_t workspace_bytes, void* stream);
 
 /* --------------------------------------------------------------------------
+ * (f4) FP8 (e4m3) KV cache.  Pool dtype float8_e4m3fn stored as bytes
+ *   python/sglang/srt/mem_cache/memory_pool.py:2365-2375 (div by k_scale/v_scale in
+ *     the input dtype, .to(float8_e4m3fn), uint8 view)
+ *   python/sglang/srt/layers/attention/triton_backend.py:1344-1365 (store with
+ *     layer.k_scale), :1418-1420 (k_descale / v_descale = layer.k_scale_float).
+ *
+ * b200attn_kv_store_fp8: k_cache[loc[t]] = e4m3(round_src(k[t] / k_scale)) (same for v),
+ *   bit-exact against `(k / k_scale).to(torch.float8_e4m3fn)` on the CPU (true division,
+ *   quotient rounded to the source dtype, c10 conversion: RNE, > 464 -> 0x7f, no
+ *   saturation).  k_scale / v_scale <= 0: no division.  Row sizes and strides are in
+ *   ELEMENTS; src_dtype is B200ATTN_BF16 or B200ATTN_FP16; loc / skip_index /
+ *   size_limit / oob_count as in b200attn_kv_store.
+ *
+ * b200attn_decode_fp8kv: b200attn_decode over a byte pool (`kv_stride` in elements =
+ *   bytes, multiple of 16).  q / o stay `dtype` (bf16 or fp16); scores are
+ *   q . k8 * k_descale * sm_scale, the output is (softmax . v8) * v_descale.  The mma
+ *   runs in f16 (e4m3 -> f16 is exact), accumulation and softmax in fp32.  Same
+ *   workspace, split policy and feature flags as b200attn_decode.
+ *
+ * b200attn_kv_dequant_gather: out_k[i] = dtype(k8[kv_indices[i]] * k_mul), out_v[i] =
+ *   dtype(v8[kv_indices[i]] * v_mul) for i in [0, n): the 16-bit K/V operand scratch the
+ *   extend kernel reads when the pool is fp8 (call b200attn_extend on the scratch with
+ *   kv_indices = 0..n-1 and sm_scale * k_descale when k_mul = 1).
+ * -------------------------------------------------------------------------- */
+int b200attn_kv_store_fp8(const void* k, const void* v, void* k_cache, void* v_cache,
+                          const void* loc, int loc_dtype, int64_t T, int64_t k_row_elems,
+                          int64_t v_row_elems, int64_t k_src_stride, int64_t v_src_stride,
+                          int64_t k_cache_stride, int64_t v_cache_stride, int src_dtype,
+                          float k_scale, float v_scale, int64_t size_limit,
+                          int64_t skip_index, int32_t* oob_count, void* stream);
+
+int b200attn_decode_fp8kv(const void* q, int64_t q_stride, const void* k_cache,
+                          const void* v_cache, int64_t kv_stride, void* o,
+                          int64_t o_stride, float* lse, const int32_t* kv_indptr,
+                          const int32_t* kv_indices, const int32_t* q_rows,
+                          const int32_t* req_ids, int32_t B, int32_t Hq, int32_t Hkv,
+                          int32_t D, int dtype, float sm_scale, float k_descale,
+                          float v_descale, int32_t max_splits, int32_t min_chunk,
+                          int32_t tail_begin, int32_t window_left, float logit_cap,
+                          const float* sinks, void* workspace, int64_t workspace_bytes,
+                          void* stream);
+
+int b200attn_kv_dequant_gather(const void* k_cache, const void* v_cache, int64_t cache_stride,
+                               const int32_t* kv_indices, int64_t n, int64_t row_elems,
+                               void* out_k, void* out_v, int64_t out_stride, int out_dtype,
+                               float k_mul, float v_mul, void* stream);
+
+/* --------------------------------------------------------------------------
  * (a5) Ragged extend / prefill over cached prefix + new tokens.  Replaces
  *   python/sglang/srt/layers/attention/torch_native_backend.py:61-174,279-336
  *   (oracle) and python/sglang/kernels/ops/attention/extend_attention.py:304-923,

@@ -104,6 +104,8 @@ class B200AttnBackend(_Base):
         self._graph_splits: Dict[int, int] = {}
         # eager-mode scratch that survives across forwards (grown on demand)
         self._ws: Optional[torch.Tensor] = None
+        self._fp8_scratch: Optional[torch.Tensor] = None  # [2, n, Hkv, D] 16-bit K/V operands of extend over an fp8 pool
+        self._fp8_iota: Optional[torch.Tensor] = None
 
     # ------------------------------------------------------------------ helpers
     def support_triton(self) -> bool:  # base_attn_backend.py:298
@@ -123,8 +125,23 @@ class B200AttnBackend(_Base):
             raise NotImplementedError("b200 backend: cross attention is not supported")
         if getattr(layer, "v_head_dim", layer.head_dim) != layer.head_dim:
             raise NotImplementedError("b200 backend: v_head_dim != head_dim is not supported")
-        if getattr(layer, "k_scale", None) is not None or getattr(layer, "v_scale", None) is not None:
-            raise NotImplementedError("b200 backend: fp8 KV cache scales are not supported")
+        if ((getattr(layer, "k_scale", None) is not None or getattr(layer, "v_scale", None) is not None)
+                and not self._fp8_pool()):
+            raise NotImplementedError("b200 backend: k_scale / v_scale need a float8_e4m3fn KV pool")
+
+    def _fp8_pool(self) -> bool:
+        return getattr(self.token_to_kv_pool, "dtype", None) == torch.float8_e4m3fn
+
+    @staticmethod
+    def _descales(layer) -> dict:
+        """k_descale / v_descale of an fp8 pool (triton_backend.py:1418-1420: layer.k_scale_float)."""
+        def one(name):
+            f = getattr(layer, name + "_float", None)
+            if f is None:
+                t = getattr(layer, name, None)
+                f = 1.0 if t is None else float(t)
+            return float(f)
+        return dict(k_descale=one("k_scale"), v_descale=one("v_scale"))
 
     @staticmethod
     def _features(layer, kwargs) -> dict:
@@ -146,6 +163,13 @@ class B200AttnBackend(_Base):
         kbuf, vbuf = pool.get_kv_buffer(layer.layer_id)
         k = k.view(-1, layer.tp_k_head_num, layer.head_dim)
         v = v.view(-1, layer.tp_v_head_num, layer.v_head_dim)
+        if self._fp8_pool():  # quantising store: div by the scale in the input dtype, then e4m3 (memory_pool.py:2365-2375)
+            sc = self._descales(layer)
+            ops.store_cache_fp8(k, v, kbuf, vbuf, forward_batch.out_cache_loc,
+                                sc["k_descale"] if getattr(layer, "k_scale", None) is not None else None,
+                                sc["v_descale"] if getattr(layer, "v_scale", None) is not None else None,
+                                reserved_skip_index=0 if self.skip_padding_slot else -1)
+            return
         if k.dtype != kbuf.dtype:  # memory_pool.py:2365-2371
             k, v = k.to(kbuf.dtype), v.to(vbuf.dtype)
         ops.store_cache(k, v, kbuf, vbuf, forward_batch.out_cache_loc,
@@ -377,7 +401,8 @@ class B200AttnBackend(_Base):
                     ms, ws = k, self._workspace(need)
         ops.decode_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.kv_indptr, md.kv_indices,
                              layer.scaling, max_splits=ms, min_chunk=md.min_chunk, workspace=ws, num_items=B,
-                             tail_begin=tail_begin, **self._features(layer, kwargs))
+                             tail_begin=tail_begin, **self._features(layer, kwargs),
+                             **(self._descales(layer) if self._fp8_pool() else {}))
         return o
 
     def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, **kwargs):
@@ -398,10 +423,27 @@ class B200AttnBackend(_Base):
             mask_kw = dict(custom_mask=md.custom_mask, mask_indptr=md.mask_indptr, skip_prefix_custom_mask=True)
         kbuf, vbuf = self.token_to_kv_pool.get_kv_buffer(layer.layer_id)
         B = md.batch_size
+        fp8 = self._fp8_pool()
+        dsc = self._descales(layer) if fp8 else {}
         if md.max_extend_len > 0:
             ws = self._workspace(ops.extend_workspace_bytes(B, q2.shape[0], Hq))
-            ops.extend_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.qo_indptr, md.kv_indptr,
-                                 md.kv_indices, layer.scaling, causal=causal, page_size=self.page_size,
+            ek, ev, eidx, escale = kbuf, vbuf, md.kv_indices, layer.scaling
+            if fp8:
+                # the tcgen05 kernel takes 16-bit K/V operands: gather the batch's rows once into a 16-bit scratch
+                # (K exact, k_descale on the score scale; v_descale folded into the V rows), slot ids become 0..n-1
+                if getattr(md, "_graph", False):
+                    raise NotImplementedError("b200 backend: graph-captured extend over an fp8 KV pool")
+                n = md.kv_indices.numel()
+                Hkv = layer.tp_k_head_num
+                if self._fp8_scratch is None or self._fp8_scratch.shape[1] < n or self._fp8_scratch.dtype != q2.dtype \
+                        or self._fp8_scratch.shape[2:] != (Hkv, D):
+                    self._fp8_scratch = torch.empty((2, n, Hkv, D), dtype=q2.dtype, device=self.device)
+                    self._fp8_iota = torch.arange(n, dtype=torch.int32, device=self.device)
+                ek, ev, eidx = self._fp8_scratch[0], self._fp8_scratch[1], self._fp8_iota
+                ops.kv_dequant_gather(kbuf, vbuf, md.kv_indices, n, ek, ev, 1.0, dsc["v_descale"])
+                escale = layer.scaling * dsc["k_descale"]
+            ops.extend_attention(q2.view(-1, Hq, D), ek, ev, o.view(-1, Hq, D), md.qo_indptr, md.kv_indptr,
+                                 eidx, escale, causal=causal, page_size=self.page_size,
                                  max_qo_len=md.max_extend_len,
                                  total_q=q2.shape[0] if getattr(md, "_graph", False) else md.num_extend_tokens,
                                  workspace=ws,
@@ -414,7 +456,7 @@ class B200AttnBackend(_Base):
             ops.decode_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.kv_indptr, md.kv_indices,
                                  layer.scaling, max_splits=ms, min_chunk=md.min_chunk, workspace=ws,
                                  q_rows=md.dec_q_rows, req_ids=md.dec_req_ids, num_items=md.num_dec,
-                                 **self._features(layer, kwargs))
+                                 **self._features(layer, kwargs), **dsc)
         return o
 
 

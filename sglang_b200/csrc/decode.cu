@@ -54,6 +54,7 @@ struct DecodeParams {
   // waves of resident CTAs and stay unsplit; the remainder would leave SMs idle for up to a whole unit, so only
   // THOSE units are split `max_splits` ways.  tail_begin < 0: every unit uses the length-based policy.
   int tail_begin;
+  float out_scale;  // fp8 KV only: v_descale * 2^8 applied to the normalised output (decode_fp8_kernel)
 };
 
 // split cap of one unit (shared by the attention and the merge kernel)
@@ -374,6 +375,354 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodePara
   }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// FP8 (e4m3) KV cache variant (pool dtype float8_e4m3fn stored as bytes,
+// memory_pool.py:2365-2375; k/v descale as in triton_backend.py:1418-1420).
+//
+// Same CTA shape and split machinery as decode_kernel; what changes is the byte path:
+//   * a K/V row is D BYTES, a 64-key tile 64*D bytes per operand, so the ring is 6 stages deep for the
+//     same 96 KB of loads in flight per CTA;
+//   * ldmatrix (b16) moves byte PAIRS; the contraction index of QK^T is permuted so that the four
+//     bytes a lane receives are its k-slots {0,1} and {8,9} of one m16n8k16 (the Q fragment is loaded
+//     with the same permutation), and for PV the transposed b16 load hands a lane V[key, d..d+1] for
+//     two keys, which two byte permutes turn into the B fragments of an "even d" and an "odd d" mma;
+//     a lane ends up owning 4 consecutive output dims per 16-d chunk;
+//   * e4m3 -> f16 is exact and branch-free: (b & 0x7f) << 7 reinterpreted as f16 is value * 2^-8
+//     (denormals included), so the mma runs in f16 (bf16 queries are converted once; P in f16) and the
+//     2^8 goes into the score scale with k_descale, and into the output scale with v_descale.
+__device__ __forceinline__ uint32_t e4m3x2_to_h2(uint32_t w, uint32_t sel) {
+  const uint32_t t = __byte_perm(w, 0u, sel);  // the two selected bytes in the high byte of each half
+  return (t & 0x80008000u) | ((t & 0x7f007f00u) >> 1);
+}
+
+template <int D>
+__device__ __forceinline__ uint32_t swz8_off(int row, int chunk) {
+  // byte offset of 16-byte chunk `chunk` of row `row` in a [rows][D] 1-byte tile (row pitch D bytes)
+  constexpr int kChunks = D / 16;
+  const int x = (kChunks >= 8) ? (row & 7) : ((row >> 1) & (kChunks - 1));
+  return (uint32_t)(row * D + ((chunk ^ x) << 4));
+}
+
+constexpr int kDec8Stages = 6;
+
+template <int D, bool kBf16>
+__global__ void __launch_bounds__(kDecThreads, 2) decode_fp8_kernel(const DecodeParams p) {
+  using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
+  constexpr int kChunks = D / 16;                  // 16-byte chunks per row
+  constexpr int kTileBytes = kDecTile * D;         // one operand, one stage
+  constexpr int kStageBytes = 2 * kTileBytes;      // K + V
+  constexpr int kLoadsPerThread = kDecTile * kChunks / kDecThreads;
+  constexpr int kRowsPerPass = kDecThreads / kChunks;
+  extern __shared__ __align__(128) uint8_t smem[];
+
+  const int split = blockIdx.x;
+  const int hg = blockIdx.y;
+  const int item = blockIdx.z;
+  const int kvh = hg / p.groups_per_kvh;
+  const int grp = hg - kvh * p.groups_per_kvh;
+  const int req = p.req_ids ? p.req_ids[item] : item;
+  const int qrow = p.q_rows ? p.q_rows[item] : item;
+  int kv_beg = p.kv_indptr[req];
+  int L = p.kv_indptr[req + 1] - kv_beg;
+  {
+    const int lo = window_lo(L, p.window_left);
+    kv_beg += lo;
+    L -= lo;
+  }
+  int nsplit, chunk;
+  split_policy(L, unit_max_splits(p, item, hg), p.min_chunk, kDecTile, nsplit, chunk);
+  if (split >= nsplit) return;
+  const int k_lo = split * chunk;
+  const int k_hi = min(L, k_lo + chunk);
+  const int ntiles = (k_hi - k_lo + kDecTile - 1) / kDecTile;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int h0 = kvh * p.G + grp * kDecMaxG;
+  const int gcount = min(kDecMaxG, p.G - grp * kDecMaxG);
+
+  // ---- Q fragments in f16, contraction index permuted: chunk kc, lane quad slot t holds d = 16kc + 4t + {0,1}
+  // (k-slots 2t,2t+1) and d = 16kc + 4t + {2,3} (k-slots 2t+8, 2t+9) -----------------------------------------
+  uint32_t qf[D / 16][4];
+  {
+    const T* qbase = reinterpret_cast<const T*>(p.q) + (int64_t)qrow * p.q_stride + (int64_t)h0 * D;
+    const int r0 = lane >> 2, c0 = (lane & 3) * 4;
+#pragma unroll
+    for (int kc = 0; kc < D / 16; ++kc) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int r = r0 + (j & 1) * 8;
+        const int c = kc * 16 + c0 + (j >> 1) * 2;
+        uint32_t w = (r < gcount) ? *reinterpret_cast<const uint32_t*>(qbase + (int64_t)r * D + c) : 0u;
+        if constexpr (kBf16) {
+          const float2 f = unpack2<true>(w);
+          w = pack2<false>(f.x, f.y);
+        }
+        qf[kc][j] = w;
+      }
+    }
+  }
+
+  const int ld_chunk = tid % kChunks;
+  const int ld_row0 = tid / kChunks;
+  const uint8_t* kc8 = reinterpret_cast<const uint8_t*>(p.k_cache) + (int64_t)kvh * D + ld_chunk * 16;
+  const uint8_t* vc8 = reinterpret_cast<const uint8_t*>(p.v_cache) + (int64_t)kvh * D + ld_chunk * 16;
+  const int64_t row_bytes = p.kv_stride;
+  const int32_t* idx = p.kv_indices + kv_beg;
+  const uint32_t smem_base = smem_u32(smem);
+
+  int32_t slots[kLoadsPerThread];
+  auto fetch_slots = [&](int tile) {
+    const int base = k_lo + tile * kDecTile + ld_row0;
+#pragma unroll
+    for (int i = 0; i < kLoadsPerThread; ++i) {
+      const int key = base + i * kRowsPerPass;
+      slots[i] = (tile < ntiles && key < k_hi) ? __ldg(idx + key) : -1;
+    }
+  };
+  auto issue_tile = [&](int stage) {
+    const uint32_t ks = smem_base + stage * kStageBytes;
+    const uint32_t vs = ks + kTileBytes;
+#pragma unroll
+    for (int i = 0; i < kLoadsPerThread; ++i) {
+      const int row = ld_row0 + i * kRowsPerPass;
+      const uint32_t off = swz8_off<D>(row, ld_chunk);
+      const bool ok = slots[i] >= 0;
+      const int64_t g = ok ? (int64_t)slots[i] * row_bytes : 0;
+      cp_async16(ks + off, kc8 + g, ok ? 16 : 0);
+      cp_async16(vs + off, vc8 + g, ok ? 16 : 0);
+    }
+  };
+
+  fetch_slots(0);
+#pragma unroll
+  for (int s = 0; s < kDec8Stages - 1; ++s) {
+    if (s < ntiles) issue_tile(s);
+    cp_async_commit();
+    fetch_slots(s + 1);
+  }
+
+  // o_acc[2c + e]: chunk c (16 output dims), e = 0: dims 16c + 4t + {0,2}, e = 1: dims 16c + 4t + {1,3}
+  float o_acc[D / 8][4];
+#pragma unroll
+  for (int n = 0; n < D / 8; ++n) o_acc[n][0] = o_acc[n][1] = o_acc[n][2] = o_acc[n][3] = 0.f;
+  float m_run[2] = {-INFINITY, -INFINITY};
+  float l_run[2] = {0.f, 0.f};
+
+  const int lm = lane >> 3, lr = lane & 7;
+
+  for (int t = 0; t < ntiles; ++t) {
+    cp_async_wait<kDec8Stages - 2>();
+    __syncthreads();
+    {
+      const int nt = t + kDec8Stages - 1;
+      if (nt < ntiles) issue_tile(nt % kDec8Stages);
+      cp_async_commit();
+      fetch_slots(nt + 1);
+    }
+    const uint32_t ks = smem_base + (t % kDec8Stages) * kStageBytes;
+    const uint32_t vs = ks + kTileBytes;
+    const int key0 = k_lo + t * kDecTile + warp * 16;
+    if (key0 < k_hi) {
+      float s[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+      {
+        const int krow = warp * 16 + (lm >> 1) * 8 + lr;
+#pragma unroll
+        for (int kp = 0; kp < D / 32; ++kp) {
+          uint32_t m0, m1, m2, m3;  // (keys 0-7, chunk 2kp), (keys 0-7, 2kp+1), (keys 8-15, 2kp), (keys 8-15, 2kp+1)
+          ldmatrix_x4(m0, m1, m2, m3, ks + swz8_off<D>(krow, 2 * kp + (lm & 1)));
+          mma_16816<false>(s[0], qf[2 * kp], e4m3x2_to_h2(m0, 0x1404), e4m3x2_to_h2(m0, 0x3424));
+          mma_16816<false>(s[0], qf[2 * kp + 1], e4m3x2_to_h2(m1, 0x1404), e4m3x2_to_h2(m1, 0x3424));
+          mma_16816<false>(s[1], qf[2 * kp], e4m3x2_to_h2(m2, 0x1404), e4m3x2_to_h2(m2, 0x3424));
+          mma_16816<false>(s[1], qf[2 * kp + 1], e4m3x2_to_h2(m3, 0x1404), e4m3x2_to_h2(m3, 0x3424));
+        }
+      }
+      const int kcol = key0 + (lane & 3) * 2;
+      float tmax[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+      for (int nb = 0; nb < 2; ++nb) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int key = kcol + nb * 8 + (j & 1);
+          float x = p.cap_post > 0.f ? p.cap_post * tanh_approx(s[nb][j] * p.cap_pre) : s[nb][j] * p.scale_log2;
+          x = (key < k_hi) ? x : -INFINITY;
+          s[nb][j] = x;
+          tmax[j >> 1] = fmaxf(tmax[j >> 1], x);
+        }
+      }
+      float alpha[2];
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        tmax[r] = fmaxf(tmax[r], __shfl_xor_sync(0xffffffffu, tmax[r], 1));
+        tmax[r] = fmaxf(tmax[r], __shfl_xor_sync(0xffffffffu, tmax[r], 2));
+        const float m_new = fmaxf(m_run[r], tmax[r]);
+        alpha[r] = fast_exp2(m_run[r] - m_new);
+        m_run[r] = m_new;
+        l_run[r] *= alpha[r];
+      }
+      uint32_t pf[4];
+#pragma unroll
+      for (int nb = 0; nb < 2; ++nb) {
+        const float p0 = fast_exp2(s[nb][0] - m_run[0]);
+        const float p1 = fast_exp2(s[nb][1] - m_run[0]);
+        const float p2 = fast_exp2(s[nb][2] - m_run[1]);
+        const float p3 = fast_exp2(s[nb][3] - m_run[1]);
+        l_run[0] += p0 + p1;
+        l_run[1] += p2 + p3;
+        pf[nb * 2 + 0] = pack2<false>(p0, p1);
+        pf[nb * 2 + 1] = pack2<false>(p2, p3);
+      }
+      const int vrow = warp * 16 + (lm & 1) * 8 + lr;
+#pragma unroll
+      for (int np = 0; np < D / 32; ++np) {
+        uint32_t m0, m1, m2, m3;  // (keys 0-7, chunk 2np), (keys 8-15, 2np), (keys 0-7, 2np+1), (keys 8-15, 2np+1)
+        ldmatrix_x4_trans(m0, m1, m2, m3, vs + swz8_off<D>(vrow, 2 * np + (lm >> 1)));
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          float(&acc)[4] = o_acc[4 * np + h];
+          acc[0] *= alpha[0];
+          acc[1] *= alpha[0];
+          acc[2] *= alpha[1];
+          acc[3] *= alpha[1];
+        }
+        // a lane's word: byte0 = V[k0][d], byte1 = V[k0][d+1], byte2 = V[k0+1][d], byte3 = V[k0+1][d+1]
+        mma_16816<false>(o_acc[4 * np + 0], pf, e4m3x2_to_h2(m0, 0x2404), e4m3x2_to_h2(m1, 0x2404));
+        mma_16816<false>(o_acc[4 * np + 1], pf, e4m3x2_to_h2(m0, 0x3414), e4m3x2_to_h2(m1, 0x3414));
+        mma_16816<false>(o_acc[4 * np + 2], pf, e4m3x2_to_h2(m2, 0x2404), e4m3x2_to_h2(m3, 0x2404));
+        mma_16816<false>(o_acc[4 * np + 3], pf, e4m3x2_to_h2(m2, 0x3414), e4m3x2_to_h2(m3, 0x3414));
+      }
+    }
+  }
+  cp_async_wait<0>();
+  __syncthreads();
+
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 1);
+    l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
+  }
+  float* sm_o = reinterpret_cast<float*>(smem);
+  float* sm_m = sm_o + 4 * 16 * D;
+  float* sm_l = sm_m + 64;
+  {
+    const int r0 = lane >> 2, c0 = (lane & 3) * 4;
+#pragma unroll
+    for (int c = 0; c < D / 16; ++c) {
+      float* dst = sm_o + (warp * 16 + r0) * D + c * 16 + c0;
+      *reinterpret_cast<float4*>(dst) =
+          make_float4(o_acc[2 * c][0], o_acc[2 * c + 1][0], o_acc[2 * c][1], o_acc[2 * c + 1][1]);
+      *reinterpret_cast<float4*>(dst + 8 * D) =
+          make_float4(o_acc[2 * c][2], o_acc[2 * c + 1][2], o_acc[2 * c][3], o_acc[2 * c + 1][3]);
+    }
+    if ((lane & 3) == 0) {
+      sm_m[warp * 16 + r0] = m_run[0];
+      sm_m[warp * 16 + r0 + 8] = m_run[1];
+      sm_l[warp * 16 + r0] = l_run[0];
+      sm_l[warp * 16 + r0 + 8] = l_run[1];
+    }
+  }
+  __syncthreads();
+  const bool direct = (nsplit == 1);
+  for (int e = tid; e < gcount * (D / 4); e += kDecThreads) {
+    const int r = e / (D / 4), c = (e - r * (D / 4)) * 4;
+    float m = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) m = fmaxf(m, sm_m[w * 16 + r]);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    float l = 0.f;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const float mw = sm_m[w * 16 + r];
+      const float f = (mw == -INFINITY) ? 0.f : fast_exp2(mw - m);
+      const float4 x = *reinterpret_cast<const float4*>(sm_o + (w * 16 + r) * D + c);
+      acc.x += f * x.x;
+      acc.y += f * x.y;
+      acc.z += f * x.z;
+      acc.w += f * x.w;
+      l += f * sm_l[w * 16 + r];
+    }
+    if (direct && p.sinks != nullptr && l > 0.f) l += fast_exp2(__ldg(p.sinks + h0 + r) * kLog2e - m);
+    const float inv = (l > 0.f) ? p.out_scale / l : 0.f;  // v_descale * 2^8 rides on the normalisation
+    acc.x *= inv;
+    acc.y *= inv;
+    acc.z *= inv;
+    acc.w *= inv;
+    const float lse2 = (l > 0.f) ? m + log2f(l) : -INFINITY;
+    const int h = h0 + r;
+    if (direct) {
+      T* dst = reinterpret_cast<T*>(p.o) + (int64_t)qrow * p.o_stride + (int64_t)h * D + c;
+      uint2 pk;
+      pk.x = pack2<kBf16>(acc.x, acc.y);
+      pk.y = pack2<kBf16>(acc.z, acc.w);
+      *reinterpret_cast<uint2*>(dst) = pk;
+      if (p.lse != nullptr && c == 0) p.lse[(int64_t)qrow * p.Hq + h] = lse2 * kLn2;
+    } else {
+      const int64_t w = ((int64_t)item * p.Hq + h) * p.max_splits + split;
+      *reinterpret_cast<float4*>(p.ws_o + w * D + c) = acc;
+      if (c == 0) p.ws_lse[w] = lse2;
+    }
+  }
+  if (direct) return;
+  __shared__ int s_last;
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    int* cnt = p.ws_cnt + (int64_t)item * (p.Hkv * p.groups_per_kvh) + hg;
+    const int ticket = atomicAdd(cnt, 1);
+    s_last = (ticket == nsplit - 1);
+    if (s_last) *cnt = 0;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  for (int e = tid; e < gcount * (D / 4); e += kDecThreads) {
+    const int r = e / (D / 4), c = (e - r * (D / 4)) * 4;
+    const int h = h0 + r;
+    const int64_t w0 = ((int64_t)item * p.Hq + h) * p.max_splits;
+    float m = -INFINITY;
+    for (int sp = 0; sp < nsplit; ++sp) m = fmaxf(m, __ldcg(p.ws_lse + w0 + sp));
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    float l = 0.f;
+    for (int sp = 0; sp < nsplit; ++sp) {
+      const float ls = __ldcg(p.ws_lse + w0 + sp);
+      const float f = (ls == -INFINITY) ? 0.f : fast_exp2(ls - m);
+      const float4 x = __ldcg(reinterpret_cast<const float4*>(p.ws_o + (w0 + sp) * D + c));
+      acc.x += f * x.x;
+      acc.y += f * x.y;
+      acc.z += f * x.z;
+      acc.w += f * x.w;
+      l += f;
+    }
+    if (p.sinks != nullptr && l > 0.f) l += fast_exp2(__ldg(p.sinks + h) * kLog2e - m);
+    const float inv = (l > 0.f) ? 1.f / l : 0.f;  // the partials already carry out_scale
+    T* dst = reinterpret_cast<T*>(p.o) + (int64_t)qrow * p.o_stride + (int64_t)h * D + c;
+    uint2 pk;
+    pk.x = pack2<kBf16>(acc.x * inv, acc.y * inv);
+    pk.y = pack2<kBf16>(acc.z * inv, acc.w * inv);
+    *reinterpret_cast<uint2*>(dst) = pk;
+    if (p.lse != nullptr && c == 0)
+      p.lse[(int64_t)qrow * p.Hq + h] = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
+  }
+}
+
+template <int D, bool kBf16>
+static int launch_decode_fp8(const DecodeParams& p, cudaStream_t st) {
+  constexpr int kRing = kDec8Stages * 2 * kDecTile * D;
+  constexpr int kMerge = (4 * 16 * D + 128) * 4;
+  constexpr int kSmem = kRing > kMerge ? kRing : kMerge;
+  static bool configured = false;
+  if (!configured) {
+    B2_CUDA(cudaFuncSetAttribute(decode_fp8_kernel<D, kBf16>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+    B2_CUDA(cudaFuncSetAttribute(decode_fp8_kernel<D, kBf16>,
+                                 cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    configured = true;
+  }
+  dim3 grid((unsigned)p.max_splits, (unsigned)(p.Hkv * p.groups_per_kvh), (unsigned)p.B);
+  decode_fp8_kernel<D, kBf16><<<grid, kDecThreads, kSmem, st>>>(p);
+  B2_LAUNCH_CHECK();
+  return B200ATTN_OK;
+}
+
 template <int D, bool kBf16>
 static int launch_decode(const DecodeParams& p, cudaStream_t st) {
   constexpr int kRing = kDecStages * 2 * kDecTile * D * 2;
@@ -401,15 +750,16 @@ extern "C" int64_t b200attn_decode_workspace_bytes(int32_t B, int32_t Hq, int32_
   return (int64_t)B * Hq * max_splits * (D + 1) * 4 + (int64_t)B * Hq * 4;  // partials + arrival counters
 }
 
-extern "C" int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
-                               const void* v_cache, int64_t kv_stride, void* o, int64_t o_stride,
-                               float* lse, const int32_t* kv_indptr, const int32_t* kv_indices,
-                               const int32_t* q_rows, const int32_t* req_ids, int32_t B,
-                               int32_t Hq, int32_t Hkv, int32_t D, int dtype, float sm_scale,
-                               int32_t max_splits, int32_t min_chunk, int32_t tail_begin,
-                               int32_t window_left,
-                               float logit_cap, const float* sinks, void* workspace,
-                               int64_t workspace_bytes, void* stream) {
+static int decode_impl(const void* q, int64_t q_stride, const void* k_cache,
+                       const void* v_cache, int64_t kv_stride, void* o, int64_t o_stride,
+                       float* lse, const int32_t* kv_indptr, const int32_t* kv_indices,
+                       const int32_t* q_rows, const int32_t* req_ids, int32_t B,
+                       int32_t Hq, int32_t Hkv, int32_t D, int dtype, float sm_scale,
+                       int32_t max_splits, int32_t min_chunk, int32_t tail_begin,
+                       int32_t window_left,
+                       float logit_cap, const float* sinks, void* workspace,
+                       int64_t workspace_bytes, void* stream, bool kv_fp8, float k_descale,
+                       float v_descale) {
   using namespace b200attn;
   B2_CHECK_ARG(B >= 0, "decode: negative batch");
   B2_CHECK_ARG(logit_cap >= 0.f, "decode: negative logit_cap");
@@ -419,8 +769,9 @@ extern "C" int b200attn_decode(const void* q, int64_t q_stride, const void* k_ca
                Hq, Hkv);
   B2_CHECK_ARG(B <= 65535 && Hq <= 65535, "decode: grid too large");
   B2_CHECK_ARG(max_splits >= 1 && max_splits <= 1024 && min_chunk >= 1, "decode: bad split policy");
-  B2_CHECK_ARG(q_stride % 8 == 0 && kv_stride % 8 == 0 && o_stride % 4 == 0,
+  B2_CHECK_ARG(q_stride % 8 == 0 && kv_stride % (kv_fp8 ? 16 : 8) == 0 && o_stride % 4 == 0,
                "decode: strides must keep rows 16-byte aligned");
+  B2_CHECK_ARG(!kv_fp8 || (k_descale > 0.f && v_descale > 0.f), "decode: fp8 descales must be positive");
   B2_CHECK_ARG((((uintptr_t)q | (uintptr_t)k_cache | (uintptr_t)v_cache | (uintptr_t)o) & 15) == 0,
                "decode: tensors must be 16-byte aligned");
   if (dtype != B200ATTN_BF16 && dtype != B200ATTN_FP16) B2_UNSUPPORTED("decode: dtype %d", dtype);
@@ -452,6 +803,9 @@ extern "C" int b200attn_decode(const void* q, int64_t q_stride, const void* k_ca
   p.groups_per_kvh = (p.G + kDecMaxG - 1) / kDecMaxG;
   p.max_splits = max_splits;
   p.min_chunk = min_chunk;
+  // fp8 KV: the kernel's e4m3 -> f16 reinterpretation yields value * 2^-8, so 2^8 rides on both scales
+  if (kv_fp8) sm_scale *= k_descale * 256.f;
+  p.out_scale = kv_fp8 ? v_descale * 256.f : 1.f;
   p.scale_log2 = sm_scale * kLog2e;
   p.window_left = window_left;
   p.cap_pre = logit_cap > 0.f ? sm_scale / logit_cap : 0.f;
@@ -459,8 +813,44 @@ extern "C" int b200attn_decode(const void* q, int64_t q_stride, const void* k_ca
   p.sinks = sinks;
   p.tail_begin = max_splits > 1 ? tail_begin : -1;
   cudaStream_t st = (cudaStream_t)stream;
+  if (kv_fp8) {
+    if (D == 128) {
+      return dtype == B200ATTN_BF16 ? launch_decode_fp8<128, true>(p, st) : launch_decode_fp8<128, false>(p, st);
+    }
+    return dtype == B200ATTN_BF16 ? launch_decode_fp8<64, true>(p, st) : launch_decode_fp8<64, false>(p, st);
+  }
   if (D == 128) {
     return dtype == B200ATTN_BF16 ? launch_decode<128, true>(p, st) : launch_decode<128, false>(p, st);
   }
   return dtype == B200ATTN_BF16 ? launch_decode<64, true>(p, st) : launch_decode<64, false>(p, st);
+}
+
+extern "C" int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
+                               const void* v_cache, int64_t kv_stride, void* o, int64_t o_stride,
+                               float* lse, const int32_t* kv_indptr, const int32_t* kv_indices,
+                               const int32_t* q_rows, const int32_t* req_ids, int32_t B,
+                               int32_t Hq, int32_t Hkv, int32_t D, int dtype, float sm_scale,
+                               int32_t max_splits, int32_t min_chunk, int32_t tail_begin,
+                               int32_t window_left,
+                               float logit_cap, const float* sinks, void* workspace,
+                               int64_t workspace_bytes, void* stream) {
+  return decode_impl(q, q_stride, k_cache, v_cache, kv_stride, o, o_stride, lse, kv_indptr, kv_indices,
+                     q_rows, req_ids, B, Hq, Hkv, D, dtype, sm_scale, max_splits, min_chunk, tail_begin,
+                     window_left, logit_cap, sinks, workspace, workspace_bytes, stream, false, 1.f, 1.f);
+}
+
+extern "C" int b200attn_decode_fp8kv(const void* q, int64_t q_stride, const void* k_cache,
+                                     const void* v_cache, int64_t kv_stride, void* o,
+                                     int64_t o_stride, float* lse, const int32_t* kv_indptr,
+                                     const int32_t* kv_indices, const int32_t* q_rows,
+                                     const int32_t* req_ids, int32_t B, int32_t Hq, int32_t Hkv,
+                                     int32_t D, int dtype, float sm_scale, float k_descale,
+                                     float v_descale, int32_t max_splits, int32_t min_chunk,
+                                     int32_t tail_begin, int32_t window_left, float logit_cap,
+                                     const float* sinks, void* workspace, int64_t workspace_bytes,
+                                     void* stream) {
+  return decode_impl(q, q_stride, k_cache, v_cache, kv_stride, o, o_stride, lse, kv_indptr, kv_indices,
+                     q_rows, req_ids, B, Hq, Hkv, D, dtype, sm_scale, max_splits, min_chunk, tail_begin,
+                     window_left, logit_cap, sinks, workspace, workspace_bytes, stream, true, k_descale,
+                     v_descale);
 }

@@ -129,7 +129,8 @@ class MHATokenToKVPool:
         self.size = size
         self.page_size = page_size
         self.dtype = dtype
-        self.store_dtype = dtype
+        # float8 pools are stored as bytes and viewed on read (memory_pool.py:2036-2040, 2292-2329)
+        self.store_dtype = torch.uint8 if dtype in (torch.float8_e4m3fn, torch.float8_e5m2) else dtype
         self.head_num = head_num
         self.head_dim = head_dim
         self.v_head_dim = head_dim if v_head_dim is None else v_head_dim
@@ -139,14 +140,17 @@ class MHATokenToKVPool:
         self.skip_padding_slot = skip_padding_slot
         self.layer_transfer_counter = None
         n = size + page_size
-        self.k_buffer = [torch.zeros((n, head_num, head_dim), dtype=dtype, device=device) for _ in range(layer_num)]
-        self.v_buffer = [torch.zeros((n, head_num, self.v_head_dim), dtype=dtype, device=device) for _ in range(layer_num)]
+        sd = self.store_dtype
+        self.k_buffer = [torch.zeros((n, head_num, head_dim), dtype=sd, device=device) for _ in range(layer_num)]
+        self.v_buffer = [torch.zeros((n, head_num, self.v_head_dim), dtype=sd, device=device) for _ in range(layer_num)]
 
     def get_key_buffer(self, layer_id: int) -> torch.Tensor:
-        return self.k_buffer[layer_id - self.start_layer]
+        b = self.k_buffer[layer_id - self.start_layer]
+        return b.view(self.dtype) if self.store_dtype != self.dtype else b
 
     def get_value_buffer(self, layer_id: int) -> torch.Tensor:
-        return self.v_buffer[layer_id - self.start_layer]
+        b = self.v_buffer[layer_id - self.start_layer]
+        return b.view(self.dtype) if self.store_dtype != self.dtype else b
 
     def get_kv_buffer(self, layer_id: int) -> Tuple[torch.Tensor, torch.Tensor]:
         return self.get_key_buffer(layer_id), self.get_value_buffer(layer_id)
@@ -155,9 +159,16 @@ class MHATokenToKVPool:
                       k_scale: Optional[float] = None, v_scale: Optional[float] = None) -> None:
         if isinstance(loc, KVWriteLoc) or hasattr(loc, "loc"):
             loc = loc.loc
-        if k_scale is not None or v_scale is not None:
-            raise NotImplementedError("b200 KV pool: k_scale / v_scale (fp8 KV cache) are not supported")
         layer_id = layer.layer_id if hasattr(layer, "layer_id") else int(layer)
+        if self.dtype == torch.float8_e4m3fn and cache_k.dtype != self.dtype:  # memory_pool.py:2365-2375
+            ops.store_cache_fp8(
+                cache_k, cache_v, self.get_key_buffer(layer_id), self.get_value_buffer(layer_id), loc,
+                None if k_scale is None else float(k_scale), None if v_scale is None else float(v_scale),
+                reserved_skip_index=0 if self.skip_padding_slot else -1,
+            )
+            return
+        if k_scale is not None or v_scale is not None:
+            raise NotImplementedError("b200 KV pool: k_scale / v_scale need a float8_e4m3fn pool")
         if cache_k.dtype != self.dtype:  # memory_pool.py:2365-2371
             cache_k = cache_k.to(self.dtype)
             cache_v = cache_v.to(self.dtype)
@@ -187,6 +198,8 @@ class RadixAttention:
         self.attn_type = attn_type
         self.k_scale = None
         self.v_scale = None
+        self.k_scale_float = None  # radix_attention.py: python floats of the scales (fp8 KV descale)
+        self.v_scale_float = None
 
     def forward(self, q, k, v, forward_batch, save_kv_cache: bool = True, **kwargs):
         # radix_attention.py:160-167: k/v are viewed [T, Hkv, D] before the backend call

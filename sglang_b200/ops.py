@@ -121,6 +121,81 @@ def store_cache(
     check(rc, "b200attn_kv_store")
 
 
+_FP8 = torch.float8_e4m3fn
+
+
+def _as_bytes(t: torch.Tensor) -> torch.Tensor:
+    """float8 pools are handled as raw bytes (the reference's store dtype, memory_pool.py:2373-2375)."""
+    return t.view(torch.uint8) if t.dtype == _FP8 else t
+
+
+def store_cache_fp8(
+    k: torch.Tensor,
+    v: torch.Tensor,
+    k_cache: torch.Tensor,
+    v_cache: torch.Tensor,
+    indices: torch.Tensor,
+    k_scale: Optional[float] = None,
+    v_scale: Optional[float] = None,
+    *,
+    reserved_skip_index: int = 0,
+    oob_count: Optional[torch.Tensor] = None,
+) -> None:
+    """Quantising store into a float8_e4m3fn (or uint8-viewed) pool.
+
+    ``k_cache[indices] = (k / k_scale).to(float8_e4m3fn)`` with the reference's rounding order
+    (memory_pool.py:2365-2371: ``div_`` in the input dtype, then the cast); bit-exact against that
+    expression evaluated by torch on the CPU.  ``None`` scales skip the division.
+    """
+    _require_cuda(k, v, k_cache, v_cache, indices)
+    T = k.shape[0]
+    if v.shape[0] != T or indices.numel() != T:
+        raise ValueError("store_cache_fp8: k, v and indices disagree on the number of tokens")
+    if T == 0:
+        return
+    if k.dtype not in (torch.bfloat16, torch.float16) or v.dtype != k.dtype:
+        raise TypeError("store_cache_fp8: k/v must be bf16 or fp16")
+    kc, vc = _as_bytes(k_cache), _as_bytes(v_cache)
+    if kc.dtype != torch.uint8 or vc.dtype != torch.uint8:
+        raise TypeError("store_cache_fp8: the pool must be float8_e4m3fn or its uint8 view")
+    k2, v2 = k.reshape(T, -1), v.reshape(T, -1)
+    kc, vc = kc.reshape(kc.shape[0], -1), vc.reshape(vc.shape[0], -1)
+    if k2.stride(1) != 1 or v2.stride(1) != 1 or kc.stride(1) != 1 or vc.stride(1) != 1:
+        raise ValueError("store_cache_fp8: rows must be contiguous")
+    if k2.shape[1] != kc.shape[1] or v2.shape[1] != vc.shape[1]:
+        raise ValueError("store_cache_fp8: row width differs between input and cache")
+    if not indices.is_contiguous():
+        indices = indices.contiguous()
+    rc = _lib.load().b200attn_kv_store_fp8(
+        k2.data_ptr(), v2.data_ptr(), kc.data_ptr(), vc.data_ptr(), indices.data_ptr(), _idtype(indices), T,
+        k2.shape[1], v2.shape[1], k2.stride(0), v2.stride(0), kc.stride(0), vc.stride(0), _fdtype(k),
+        float(k_scale) if k_scale is not None else 0.0, float(v_scale) if v_scale is not None else 0.0,
+        min(kc.shape[0], vc.shape[0]), reserved_skip_index, _ptr(oob_count), _stream(),
+    )
+    check(rc, "b200attn_kv_store_fp8")
+
+
+def kv_dequant_gather(k_cache: torch.Tensor, v_cache: torch.Tensor, kv_indices: torch.Tensor, n: int,
+                      out_k: torch.Tensor, out_v: torch.Tensor, k_mul: float = 1.0, v_mul: float = 1.0) -> None:
+    """``out_k[i] = k_cache[kv_indices[i]] * k_mul`` (same for v) from an fp8 pool into 16-bit rows ``[n, Hkv, D]``:
+    the K/V operand scratch of extend over an fp8 pool (b200attn_kv_dequant_gather)."""
+    _require_cuda(k_cache, v_cache, kv_indices, out_k, out_v)
+    kc, vc = _as_bytes(k_cache), _as_bytes(v_cache)
+    kc, vc = kc.reshape(kc.shape[0], -1), vc.reshape(vc.shape[0], -1)
+    ok, ov = out_k.reshape(out_k.shape[0], -1), out_v.reshape(out_v.shape[0], -1)
+    if kv_indices.dtype != torch.int32:
+        raise TypeError("kv_dequant_gather: kv_indices must be int32")
+    if ok.shape[0] < n or ov.shape[0] < n or kv_indices.numel() < n:
+        raise ValueError("kv_dequant_gather: outputs / indices shorter than n")
+    if kc.stride() != vc.stride() or ok.stride() != ov.stride() or ok.shape[1] != kc.shape[1] or ok.dtype != ov.dtype:
+        raise ValueError("kv_dequant_gather: K and V must share layouts")
+    rc = _lib.load().b200attn_kv_dequant_gather(
+        kc.data_ptr(), vc.data_ptr(), kc.stride(0), kv_indices.data_ptr(), int(n), kc.shape[1],
+        ok.data_ptr(), ov.data_ptr(), ok.stride(0), _fdtype(out_k), float(k_mul), float(v_mul), _stream(),
+    )
+    check(rc, "b200attn_kv_dequant_gather")
+
+
 # -------------------------------------------------------------------- rope + store
 ROPE_F32, ROPE_NATIVE = 0, 1
 
@@ -391,8 +466,13 @@ def decode_attention(
     logit_cap: float = 0.0,
     sinks: Optional[torch.Tensor] = None,
     tail_begin: int = -1,
+    k_descale: float = 1.0,
+    v_descale: float = 1.0,
 ) -> torch.Tensor:
     """Paged GQA decode: ``q [B,Hq,D]``, caches ``[slots,Hkv,D]`` -> ``o [B,Hq,D]``.
+
+    A float8_e4m3fn (or uint8-viewed) pool takes the fp8 kernel (b200attn_decode_fp8kv) with
+    ``k_descale`` / ``v_descale`` (triton_backend.py:1418-1420); 16-bit pools ignore them.
 
     Mirrors ``decode_attention_fwd`` (python/sglang/kernels/ops/attention/
     decode_attention.py:1163-1239) with token-granular ``kv_indices`` (int32).
@@ -405,8 +485,11 @@ def decode_attention(
     Hkv = k_cache.shape[1]
     if k_cache.shape[2] != D or v_cache.shape[2] != D:
         raise NotImplementedError("decode_attention: v_head_dim != head_dim is not supported")
-    if q.dtype != k_cache.dtype or q.dtype != v_cache.dtype:
-        raise TypeError("decode_attention: q and the KV pool must share a dtype")
+    fp8 = k_cache.dtype in (_FP8, torch.uint8)
+    if fp8:
+        k_cache, v_cache = _as_bytes(k_cache), _as_bytes(v_cache)
+    if k_cache.dtype != v_cache.dtype or (not fp8 and q.dtype != k_cache.dtype):
+        raise TypeError("decode_attention: q and the KV pool must share a dtype (or the pool is float8_e4m3fn)")
     if q.stride(2) != 1 or q.stride(1) != D or o.stride(2) != 1 or o.stride(1) != D:
         raise ValueError("decode_attention: q/o heads must be densely packed")
     if k_cache.stride(2) != 1 or k_cache.stride(1) != D or v_cache.stride() != k_cache.stride():
@@ -414,6 +497,16 @@ def decode_attention(
     if kv_indptr.dtype != torch.int32 or kv_indices.dtype != torch.int32:
         raise TypeError("decode_attention: kv_indptr / kv_indices must be int32")
     ws_bytes = 0 if workspace is None else workspace.numel() * workspace.element_size()
+    if fp8:
+        rc = _lib.load().b200attn_decode_fp8kv(
+            q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
+            o.data_ptr(), o.stride(0), _ptr(lse), kv_indptr.data_ptr(), kv_indices.data_ptr(),
+            _ptr(q_rows), _ptr(req_ids), B, Hq, Hkv, D, _fdtype(q), float(sm_scale), float(k_descale),
+            float(v_descale), max_splits, min_chunk, int(tail_begin), int(window_left), float(logit_cap),
+            _sinks_ptr(sinks, Hq), _ptr(workspace), ws_bytes, _stream(),
+        )
+        check(rc, "b200attn_decode_fp8kv")
+        return o
     rc = _lib.load().b200attn_decode(
         q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
         o.data_ptr(), o.stride(0), _ptr(lse), kv_indptr.data_ptr(), kv_indices.data_ptr(),

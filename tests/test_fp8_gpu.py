@@ -1,0 +1,181 @@
+"""(f4) FP8 (e4m3) KV cache: quantising store (bit-exact), fp8 decode kernel, extend over an fp8 pool, backend."""
+import pytest
+import torch
+
+from oracle import fp8_port
+from oracle import torch_native_port as oracle
+from sglang_b200 import (B200AttnBackend, ForwardBatch, ForwardMode, MHATokenToKVPool, RadixAttention,
+                         ReqToTokenPool, ops)
+from tests.util import assert_close_attn, make_scenario
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+FP8 = torch.float8_e4m3fn
+
+
+def _all_16bit(dtype):
+    x = torch.arange(65536, dtype=torch.int32).to(torch.int16).view(dtype)
+    return x[~torch.isnan(x)]
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("scale", [None, 0.5, 0.37, 2.3])
+def test_store_fp8_exhaustive_bit_exact(dtype, scale):
+    """Every finite 16-bit input value, with and without a scale, against the reference expression on the CPU."""
+    x = _all_16bit(dtype)
+    n = x.numel() // 64 * 64
+    x = x[:n].view(-1, 1, 64)
+    T = x.shape[0]
+    loc = torch.randperm(T, generator=torch.Generator().manual_seed(1)) + 1
+    kc = torch.zeros((T + 1, 1, 64), dtype=torch.uint8)
+    vc = torch.zeros_like(kc)
+    fp8_port.store_kv_fp8(kc, vc, loc, x, x.flip(0), scale, None)
+    kg, vg = torch.zeros_like(kc, device=DEV), torch.zeros_like(vc, device=DEV)
+    ops.store_cache_fp8(x.to(DEV), x.flip(0).to(DEV), kg, vg, loc.to(DEV), scale, None)
+    assert torch.equal(kg.cpu(), kc)
+    assert torch.equal(vg.cpu(), vc)
+
+
+@pytest.mark.parametrize("width,stride", [(96, 96), (100, 104), (7, 9), (2048, 6144)])
+def test_store_fp8_odd_widths_strides_and_skip(width, stride):
+    g = torch.Generator().manual_seed(width)
+    T = 37
+    buf = (torch.randn((T, stride), generator=g) * 3).to(torch.bfloat16)
+    buf2 = (buf * 1.5).to(torch.bfloat16)
+    k, v = buf[:, :width], buf2[:, :width]
+    loc = torch.randperm(64, generator=g)[:T]      # contains slot 0 with high probability
+    loc[3] = 0
+    kc = torch.full((64, width), 7, dtype=torch.uint8)
+    vc = torch.full((64, width), 9, dtype=torch.uint8)
+    kg, vg = kc.to(DEV).view(FP8), vc.to(DEV).view(FP8)
+    fp8_port.store_kv_fp8(kc, vc, loc, k, v, 0.8, 1.3, skip_index=0)
+    ops.store_cache_fp8(buf.to(DEV)[:, :width], buf2.to(DEV)[:, :width], kg, vg, loc.to(DEV).int(), 0.8, 1.3)
+    assert torch.equal(kg.view(torch.uint8).cpu(), kc) and torch.equal(vg.view(torch.uint8).cpu(), vc)
+
+
+def _fp8_scenario(lens, ext, Hq, Hkv, D, page, seed, dtype=torch.bfloat16, ks=0.6, vs=0.9):
+    """bf16 scenario whose pool is re-quantised to e4m3 bytes; returns (scenario, k8, v8, dequantised fp32 pools)."""
+    pre = [l - e for l, e in zip(lens, ext)]
+    sc = make_scenario(pre, ext, Hq, Hkv, D, page, dtype=dtype, seed=seed)
+    k8 = fp8_port.quantize(sc.k_cache * 2, ks)
+    v8 = fp8_port.quantize(sc.v_cache * 2, vs)
+    return sc, k8, v8, fp8_port.dequantize(k8, ks), fp8_port.dequantize(v8, vs)
+
+
+@pytest.mark.parametrize("Hq,Hkv,D,page", [(32, 8, 128, 16), (14, 2, 64, 1), (28, 4, 128, 16), (8, 8, 64, 32),
+                                           (16, 1, 128, 1), (64, 2, 128, 16)])
+@pytest.mark.parametrize("max_splits", [1, 4, 16])
+def test_decode_fp8_matches_oracle(Hq, Hkv, D, page, max_splits):
+    lens = [1, 2, 15, 16, 17, 63, 64, 65, 200, 777, 1500]
+    B = len(lens)
+    sc, k8, v8, kf, vf = _fp8_scenario(lens, [0] * B, Hq, Hkv, D, page, seed=Hq + page)
+    q = torch.randn((B, Hq * D), generator=torch.Generator().manual_seed(1)).to(torch.bfloat16)
+    ref, lse_ref = oracle.attention_fp32(q, kf, vf, sc.req_to_token, sc.req_pool_indices, torch.tensor(lens),
+                                         torch.ones(B, dtype=torch.int64), Hq, Hkv, D, sc.scaling, causal=False,
+                                         return_lse=True)
+    d = sc.to(DEV)
+    kv_indptr = torch.zeros(B + 1, dtype=torch.int32, device=DEV)
+    kv_indices = torch.zeros(sum(lens), dtype=torch.int32, device=DEV)
+    ops.build_kv_indices(d.req_to_token, d.req_pool_indices, torch.tensor(lens, device=DEV), kv_indptr, kv_indices)
+    o = torch.full((B, Hq, D), float("nan"), dtype=torch.bfloat16, device=DEV)
+    lse = torch.empty((B, Hq), dtype=torch.float32, device=DEV)
+    ws = torch.zeros(max(ops.decode_workspace_bytes(B, Hq, D, max_splits), 16), dtype=torch.uint8, device=DEV)
+    for _ in range(2):  # second launch: the split arrival counters must have been left at zero
+        ops.decode_attention(q.to(DEV).view(B, Hq, D), k8.to(DEV).view(FP8), v8.to(DEV), o, kv_indptr, kv_indices,
+                             sc.scaling, max_splits=max_splits, min_chunk=64, workspace=ws, lse=lse,
+                             k_descale=0.6, v_descale=0.9)
+    torch.cuda.synchronize()
+    assert_close_attn(o.view(B, -1), ref, f"fp8 decode Hq{Hq} D{D} page{page} splits{max_splits}")
+    torch.testing.assert_close(lse.cpu(), lse_ref, rtol=2e-3, atol=2e-3)
+
+
+def test_decode_fp8_fp16_queries_window_cap_sinks():
+    lens = [5, 130, 1000]
+    Hq, Hkv, D = 8, 2, 128
+    sc, k8, v8, kf, vf = _fp8_scenario(lens, [0] * 3, Hq, Hkv, D, 16, seed=3, dtype=torch.float16)
+    q = torch.randn((3, Hq * D), generator=torch.Generator().manual_seed(2)).to(torch.float16)
+    sinks = torch.randn(Hq, generator=torch.Generator().manual_seed(5))
+    d = sc.to(DEV)
+    kv_indptr = torch.zeros(4, dtype=torch.int32, device=DEV)
+    kv_indices = torch.zeros(sum(lens), dtype=torch.int32, device=DEV)
+    ops.build_kv_indices(d.req_to_token, d.req_pool_indices, torch.tensor(lens, device=DEV), kv_indptr, kv_indices)
+    for kw in (dict(), dict(window_left=100), dict(logit_cap=30.0), dict(sinks=sinks)):
+        ref = oracle.attention_fp32(q, kf, vf, sc.req_to_token, sc.req_pool_indices, torch.tensor(lens),
+                                    torch.ones(3, dtype=torch.int64), Hq, Hkv, D, sc.scaling, causal=False, **kw)
+        for ms in (1, 8):
+            o = torch.empty((3, Hq, D), dtype=torch.float16, device=DEV)
+            ws = torch.zeros(max(ops.decode_workspace_bytes(3, Hq, D, ms), 16), dtype=torch.uint8, device=DEV)
+            gkw = {k: (v.to(DEV) if isinstance(v, torch.Tensor) else v) for k, v in kw.items()}
+            ops.decode_attention(q.to(DEV).view(3, Hq, D), k8.to(DEV), v8.to(DEV), o, kv_indptr, kv_indices,
+                                 sc.scaling, max_splits=ms, min_chunk=64, workspace=ws, k_descale=0.6,
+                                 v_descale=0.9, **gkw)
+            assert_close_attn(o.view(3, -1), ref, f"fp8 decode fp16 {kw} splits{ms}")
+
+
+def test_dequant_gather_exact():
+    g = torch.Generator().manual_seed(0)
+    k8 = torch.randint(0, 256, (300, 4, 128), dtype=torch.uint8, generator=g)
+    k8[(k8 & 0x7F) == 0x7F] = 0      # no NaN patterns
+    v8 = k8.flip(0).contiguous()
+    idx = torch.randint(0, 300, (1000,), generator=g).int()
+    ok = torch.empty((1000, 4, 128), dtype=torch.bfloat16, device=DEV)
+    ov = torch.empty_like(ok)
+    ops.kv_dequant_gather(k8.to(DEV), v8.to(DEV).view(FP8), idx.to(DEV), 1000, ok, ov, 1.0, 0.75)
+    assert torch.equal(ok.cpu().float(), fp8_port.dequantize(k8)[idx.long()])     # every e4m3 value is a bf16 value
+    assert torch.equal(ov.cpu(), (fp8_port.dequantize(v8)[idx.long()] * 0.75).to(torch.bfloat16))
+
+
+def _backend(sc, Hkv, D, page, k8, v8):
+    B = len(sc.seq_lens)
+    ctx = sc.req_to_token.shape[1]
+    req_pool = ReqToTokenPool(B, ctx, DEV)
+    req_pool.req_to_token.copy_(sc.req_to_token)
+    slots = sc.k_cache.shape[0]
+    pool = MHATokenToKVPool(slots - page, page, FP8, Hkv, D, 1, DEV, skip_padding_slot=False)
+    pool.k_buffer[0].copy_(k8)
+    pool.v_buffer[0].copy_(v8)
+
+    class Runner:
+        device, page_size, sliding_window_size = DEV, page, None
+        req_to_token_pool, token_to_kv_pool = req_pool, pool
+
+    return B200AttnBackend(Runner(), skip_padding_slot=False), pool
+
+
+@pytest.mark.parametrize("mode", ["extend", "mixed", "decode"])
+def test_backend_fp8_pool(mode):
+    """Store (quantising) + attention through B200AttnBackend on a float8_e4m3fn pool with layer k/v scales."""
+    Hq, Hkv, D, page = 16, 4, 128, 16
+    ks, vs = 0.6, 0.9
+    if mode == "decode":
+        pre, ext = [300, 17, 1024], [1, 1, 1]
+    elif mode == "mixed":
+        pre, ext = [40, 700, 0, 129], [200, 1, 333, 1]
+    else:
+        pre, ext = [40, 0, 513], [200, 333, 90]
+    lens = [p + e for p, e in zip(pre, ext)]
+    sc, k8, v8, _, _ = _fp8_scenario(lens, ext, Hq, Hkv, D, page, seed=11, ks=ks, vs=vs)
+    backend, pool = _backend(sc, Hkv, D, page, k8, v8)
+    layer = RadixAttention(Hq, D, D ** -0.5, Hkv, 0)
+    layer.k_scale, layer.v_scale = torch.tensor(ks), torch.tensor(vs)
+    layer.k_scale_float, layer.v_scale_float = ks, vs
+    T, B = sum(ext), len(ext)
+    fmode = ForwardMode.DECODE if mode == "decode" else (ForwardMode.MIXED if mode == "mixed" else ForwardMode.EXTEND)
+    kw = dict(forward_mode=fmode, batch_size=B, req_pool_indices=sc.req_pool_indices.to(DEV),
+              seq_lens=torch.tensor(lens, device=DEV), out_cache_loc=sc.out_cache_loc.to(DEV), seq_lens_sum=sum(lens),
+              seq_lens_cpu=torch.tensor(lens), attn_backend=backend)
+    if mode != "decode":
+        kw.update(extend_seq_lens=torch.tensor(ext, dtype=torch.int32, device=DEV),
+                  extend_prefix_lens=torch.tensor(pre, dtype=torch.int32, device=DEV),
+                  extend_seq_lens_cpu=ext, extend_prefix_lens_cpu=pre)
+    fb = ForwardBatch(**kw)
+    backend.init_forward_metadata(fb)
+    o = layer(sc.q.to(DEV), sc.k.to(DEV), sc.v.to(DEV), fb)
+    torch.cuda.synchronize()
+    # oracle: quantising store, then fp32 attention over the dequantised pool
+    fp8_port.store_kv_fp8(k8, v8, sc.out_cache_loc, sc.k.view(T, Hkv, D), sc.v.view(T, Hkv, D), ks, vs)
+    assert torch.equal(pool.k_buffer[0].cpu(), k8) and torch.equal(pool.v_buffer[0].cpu(), v8), "fp8 store not bit-exact"
+    ref = oracle.attention_fp32(sc.q, fp8_port.dequantize(k8, ks), fp8_port.dequantize(v8, vs), sc.req_to_token,
+                                sc.req_pool_indices, torch.tensor(lens), torch.tensor(ext), Hq, Hkv, D, D ** -0.5,
+                                causal=True)
+    assert_close_attn(o, ref, f"backend fp8 {mode}")
