@@ -368,6 +368,9 @@ def run_b200(args, rank, world, local_rank):
                 dev, gen, peaks, "qwen2.5-vl-7b MIXED: 16 req x 1280 new tokens + 16 decode rows (prefix 1279), "
                 "Hq 28 / Hkv 4 (BASELINE configs[3])", [0] * 16 + [1279] * 16, [1280] * 16 + [1] * 16, 28, 4, 128,
                 16, causal, "MIXED")
+        # configs[1] again over a float8_e4m3fn pool: half the KV bytes per call
+        extra["cfg2_decode_fp8kv"] = run_cfg2_decode_fp8(dev, gen, peaks)
+        torch.cuda.empty_cache()
         # configs[4]: Llama-3.1-70B attention shape, this rank's KV-head shard
         extra["cfg5_decode"] = run_cfg5_decode(dev, gen, peaks, world)
         torch.cuda.empty_cache()
@@ -523,6 +526,36 @@ def run_backend_case(dev, gen, peaks, label, prefix_lens, ext_lens, Hq, Hkv, D, 
     tf = fl / (ms * 1e-3) / 1e12
     return dict(workload=label, ms_per_step=ms, flops=fl, tflops=tf, decode_row_kv_bytes=dec_bytes, tokens=T,
                 frac_of_measured_bf16=tf / peaks["tf_burst"], frac_of_2250=tf / 2250.0)
+
+
+def run_cfg2_decode_fp8(dev, gen, peaks, steps=20, warmup=5):
+    """BASELINE configs[1] shape with an e4m3 KV pool (k/v descale 0.5): decode_fp8_kernel alone, CUDA events."""
+    from sglang_b200 import ops
+
+    c = dict(B=64, ctx=4096, Hq=32, Hkv=8, D=128, page=16)
+    req_pool, kv_pool, host = build_decode_state(c, dev, gen)
+    B, Hq, Hkv, D = c["B"], c["Hq"], c["Hkv"], c["D"]
+    k8, v8 = (b.mul(2).to(torch.float8_e4m3fn) for b in kv_pool.get_kv_buffer(0))
+    del kv_pool
+    kv_indptr = torch.zeros(B + 1, dtype=torch.int32, device=dev)
+    kv_indices = torch.zeros(B * c["ctx"], dtype=torch.int32, device=dev)
+    ops.build_kv_indices(req_pool.req_to_token, host["req_pool_indices"].to(dev), host["seq_lens"].to(dev), kv_indptr,
+                         kv_indices)
+    q = host["q"].to(dev).view(B, Hq, D)
+    o = torch.empty_like(q)
+    cps = ops.decode_ctas_per_sm(True)
+    tail_begin, ms_ = ops.pick_tail_split(B, Hkv, Hq // Hkv, ctas_per_sm=cps)  # 512 units on 444 slots: split the tail
+    ws = torch.zeros(max(ops.decode_workspace_bytes(B, Hq, D, ms_), 16), dtype=torch.uint8, device=dev)
+    f = lambda: ops.decode_attention(q, k8, v8, o, kv_indptr, kv_indices, D ** -0.5, max_splits=ms_, min_chunk=256,
+                                     workspace=ws, tail_begin=tail_begin, k_descale=0.5, v_descale=0.5)
+    t = time_steps(f, steps, warmup) / steps
+    nbytes = 2 * B * c["ctx"] * Hkv * D + 2 * B * Hq * D * 2 + 4 * B * c["ctx"]
+    gbs = nbytes / (t * 1e-3) / 1e9
+    return dict(workload="llama-3.1-8b decode over a float8_e4m3fn KV pool: batch 64 x 4096 ctx, GQA 32q/8kv, "
+                         "head_dim 128, page_size 16", kernel="decode_fp8_kernel<128,bf16>", kernel_ms=t, bytes=nbytes,
+                tail_split=[tail_begin, ms_],
+                gbs=gbs, frac_of_measured_hbm=gbs / peaks["hbm"], frac_of_8tbs=gbs / 8000.0,
+                bf16_pool_equivalent_gbs=(nbytes + 2 * B * c["ctx"] * Hkv * D) / (t * 1e-3) / 1e9)
 
 
 def run_cfg5_decode(dev, gen, peaks, world, steps=10, warmup=3):

@@ -367,12 +367,13 @@ class B200AttnBackend(_Base):
         kbuf, vbuf = self.token_to_kv_pool.get_kv_buffer(layer.layer_id)
         B = md.batch_size
         G = Hq // Hkv
+        cps = ops.decode_ctas_per_sm(self._fp8_pool())  # resident CTAs per SM of the kernel that will run
         if getattr(md, "_graph", False):
             # the split cap is baked into the captured grid: fix it per batch size
             ms = self._graph_splits.get(B)
             if ms is None:
                 ms = min(self._graph.max_splits_cap,
-                         ops.pick_max_splits(B, Hkv, G, self.max_context_len, md.min_chunk, num_sms=self.num_sms))
+                         ops.pick_max_splits(B, Hkv, G, self.max_context_len, md.min_chunk, num_sms=self.num_sms, ctas_per_sm=cps))
                 self._graph_splits[B] = ms
             ws = md.workspace
             need = ops.decode_workspace_bytes(B, Hq, D, ms)
@@ -385,11 +386,11 @@ class B200AttnBackend(_Base):
                 md.workspace = ws
         else:
             ms = ops.pick_max_splits(B, Hkv, G, getattr(md, "_max_kv_len", self.max_context_len),
-                                     md.min_chunk, num_sms=self.num_sms)
+                                     md.min_chunk, num_sms=self.num_sms, ctas_per_sm=cps)
             ws = self._workspace(ops.decode_workspace_bytes(B, Hq, D, ms))
         tail_begin = -1
         if ms == 1:  # whole waves stay unsplit; a nearly empty last wave is split (ops.pick_tail_split)
-            tail_begin, k = ops.pick_tail_split(B, Hkv, G, num_sms=self.num_sms)
+            tail_begin, k = ops.pick_tail_split(B, Hkv, G, num_sms=self.num_sms, ctas_per_sm=cps)
             if k > 1:
                 need = ops.decode_workspace_bytes(B, Hq, D, k)
                 if getattr(md, "_graph", False):
@@ -451,7 +452,7 @@ class B200AttnBackend(_Base):
         if md.num_dec > 0:  # a single query row sees all of its keys, causal or not
             Hkv = layer.tp_k_head_num
             ms = ops.pick_max_splits(md.num_dec, Hkv, Hq // Hkv, md.dec_max_kv_len, md.min_chunk,
-                                     num_sms=self.num_sms)
+                                     num_sms=self.num_sms, ctas_per_sm=ops.decode_ctas_per_sm(fp8))
             ws = self._workspace(ops.decode_workspace_bytes(md.num_dec, Hq, D, ms))
             ops.decode_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.kv_indptr, md.kv_indices,
                                  layer.scaling, max_splits=ms, min_chunk=md.min_chunk, workspace=ws,

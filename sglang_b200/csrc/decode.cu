@@ -390,9 +390,48 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodePara
 //   * e4m3 -> f16 is exact and branch-free: (b & 0x7f) << 7 reinterpreted as f16 is value * 2^-8
 //     (denormals included), so the mma runs in f16 (bf16 queries are converted once; P in f16) and the
 //     2^8 goes into the score scale with k_descale, and into the output scale with v_descale.
-__device__ __forceinline__ uint32_t e4m3x2_to_h2(uint32_t w, uint32_t sel) {
+// kFp8HwCvt: cvt.rn.f16x2.e4m3x2 (SASS F2FP.F16.E4M3.UNPACK_B, one instruction per pair, true values) instead of
+// the 4-instruction bit trick (value * 2^-8).  kFp8Bias is the factor the scales must carry.
+#ifndef B200ATTN_FP8_HWCVT
+#define B200ATTN_FP8_HWCVT 1
+#endif
+constexpr bool kFp8HwCvt = B200ATTN_FP8_HWCVT != 0;
+constexpr float kFp8Bias = kFp8HwCvt ? 1.f : 256.f;
+
+__device__ __forceinline__ uint32_t e4m3x2_lo(uint32_t w) {  // bytes 0,1 -> f16x2
+  uint32_t r;
+  asm("{ .reg .b16 lo, hi; mov.b32 {lo, hi}, %1; cvt.rn.f16x2.e4m3x2 %0, lo; }" : "=r"(r) : "r"(w));
+  return r;
+}
+__device__ __forceinline__ uint32_t e4m3x2_hi(uint32_t w) {  // bytes 2,3 -> f16x2
+  uint32_t r;
+  asm("{ .reg .b16 lo, hi; mov.b32 {lo, hi}, %1; cvt.rn.f16x2.e4m3x2 %0, hi; }" : "=r"(r) : "r"(w));
+  return r;
+}
+__device__ __forceinline__ uint32_t e4m3x2_trick(uint32_t w, uint32_t sel) {
   const uint32_t t = __byte_perm(w, 0u, sel);  // the two selected bytes in the high byte of each half
   return (t & 0x80008000u) | ((t & 0x7f007f00u) >> 1);
+}
+// K word (4 consecutive d of one key): {d0,d1} and {d2,d3}
+__device__ __forceinline__ void e4m3x4_pairs(uint32_t w, uint32_t& a, uint32_t& b) {
+  if constexpr (kFp8HwCvt) {
+    a = e4m3x2_lo(w);
+    b = e4m3x2_hi(w);
+  } else {
+    a = e4m3x2_trick(w, 0x1404);
+    b = e4m3x2_trick(w, 0x3424);
+  }
+}
+// V word (byte0 = V[k0][d], byte1 = V[k0][d+1], byte2 = V[k0+1][d], byte3 = V[k0+1][d+1]): {k0,k0+1} at d and at d+1
+__device__ __forceinline__ void e4m3x4_cross(uint32_t w, uint32_t& even, uint32_t& odd) {
+  if constexpr (kFp8HwCvt) {
+    const uint32_t t = __byte_perm(w, 0u, 0x3120);
+    even = e4m3x2_lo(t);
+    odd = e4m3x2_hi(t);
+  } else {
+    even = e4m3x2_trick(w, 0x2404);
+    odd = e4m3x2_trick(w, 0x3414);
+  }
 }
 
 template <int D>
@@ -403,10 +442,16 @@ __device__ __forceinline__ uint32_t swz8_off(int row, int chunk) {
   return (uint32_t)(row * D + ((chunk ^ x) << 4));
 }
 
-constexpr int kDec8Stages = 6;
+#ifndef B200ATTN_FP8_STAGES
+#define B200ATTN_FP8_STAGES 4
+#endif
+#ifndef B200ATTN_FP8_CTAS
+#define B200ATTN_FP8_CTAS 3
+#endif
+constexpr int kDec8Stages = B200ATTN_FP8_STAGES;  // 4 x 16 KB per CTA, 3 CTAs per SM: 144 KB of loads in flight per SM
 
 template <int D, bool kBf16>
-__global__ void __launch_bounds__(kDecThreads, 2) decode_fp8_kernel(const DecodeParams p) {
+__global__ void __launch_bounds__(kDecThreads, B200ATTN_FP8_CTAS) decode_fp8_kernel(const DecodeParams p) {
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
   constexpr int kChunks = D / 16;                  // 16-byte chunks per row
   constexpr int kTileBytes = kDecTile * D;         // one operand, one stage
@@ -530,10 +575,15 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_fp8_kernel(const Decode
         for (int kp = 0; kp < D / 32; ++kp) {
           uint32_t m0, m1, m2, m3;  // (keys 0-7, chunk 2kp), (keys 0-7, 2kp+1), (keys 8-15, 2kp), (keys 8-15, 2kp+1)
           ldmatrix_x4(m0, m1, m2, m3, ks + swz8_off<D>(krow, 2 * kp + (lm & 1)));
-          mma_16816<false>(s[0], qf[2 * kp], e4m3x2_to_h2(m0, 0x1404), e4m3x2_to_h2(m0, 0x3424));
-          mma_16816<false>(s[0], qf[2 * kp + 1], e4m3x2_to_h2(m1, 0x1404), e4m3x2_to_h2(m1, 0x3424));
-          mma_16816<false>(s[1], qf[2 * kp], e4m3x2_to_h2(m2, 0x1404), e4m3x2_to_h2(m2, 0x3424));
-          mma_16816<false>(s[1], qf[2 * kp + 1], e4m3x2_to_h2(m3, 0x1404), e4m3x2_to_h2(m3, 0x3424));
+          uint32_t a, b;
+          e4m3x4_pairs(m0, a, b);
+          mma_16816<false>(s[0], qf[2 * kp], a, b);
+          e4m3x4_pairs(m1, a, b);
+          mma_16816<false>(s[0], qf[2 * kp + 1], a, b);
+          e4m3x4_pairs(m2, a, b);
+          mma_16816<false>(s[1], qf[2 * kp], a, b);
+          e4m3x4_pairs(m3, a, b);
+          mma_16816<false>(s[1], qf[2 * kp + 1], a, b);
         }
       }
       const int kcol = key0 + (lane & 3) * 2;
@@ -572,23 +622,31 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_fp8_kernel(const Decode
         pf[nb * 2 + 1] = pack2<false>(p2, p3);
       }
       const int vrow = warp * 16 + (lm & 1) * 8 + lr;
+      const bool rescale = __any_sync(0xffffffffu, alpha[0] != 1.f || alpha[1] != 1.f);
 #pragma unroll
       for (int np = 0; np < D / 32; ++np) {
         uint32_t m0, m1, m2, m3;  // (keys 0-7, chunk 2np), (keys 8-15, 2np), (keys 0-7, 2np+1), (keys 8-15, 2np+1)
         ldmatrix_x4_trans(m0, m1, m2, m3, vs + swz8_off<D>(vrow, 2 * np + (lm >> 1)));
+        if (rescale) {  // warp-uniform: the running max moved in this tile
 #pragma unroll
-        for (int h = 0; h < 4; ++h) {
-          float(&acc)[4] = o_acc[4 * np + h];
-          acc[0] *= alpha[0];
-          acc[1] *= alpha[0];
-          acc[2] *= alpha[1];
-          acc[3] *= alpha[1];
+          for (int h = 0; h < 4; ++h) {
+            float(&acc)[4] = o_acc[4 * np + h];
+            acc[0] *= alpha[0];
+            acc[1] *= alpha[0];
+            acc[2] *= alpha[1];
+            acc[3] *= alpha[1];
+          }
         }
         // a lane's word: byte0 = V[k0][d], byte1 = V[k0][d+1], byte2 = V[k0+1][d], byte3 = V[k0+1][d+1]
-        mma_16816<false>(o_acc[4 * np + 0], pf, e4m3x2_to_h2(m0, 0x2404), e4m3x2_to_h2(m1, 0x2404));
-        mma_16816<false>(o_acc[4 * np + 1], pf, e4m3x2_to_h2(m0, 0x3414), e4m3x2_to_h2(m1, 0x3414));
-        mma_16816<false>(o_acc[4 * np + 2], pf, e4m3x2_to_h2(m2, 0x2404), e4m3x2_to_h2(m3, 0x2404));
-        mma_16816<false>(o_acc[4 * np + 3], pf, e4m3x2_to_h2(m2, 0x3414), e4m3x2_to_h2(m3, 0x3414));
+        uint32_t e0, o0, e1, o1;
+        e4m3x4_cross(m0, e0, o0);
+        e4m3x4_cross(m1, e1, o1);
+        mma_16816<false>(o_acc[4 * np + 0], pf, e0, e1);
+        mma_16816<false>(o_acc[4 * np + 1], pf, o0, o1);
+        e4m3x4_cross(m2, e0, o0);
+        e4m3x4_cross(m3, e1, o1);
+        mma_16816<false>(o_acc[4 * np + 2], pf, e0, e1);
+        mma_16816<false>(o_acc[4 * np + 3], pf, o0, o1);
       }
     }
   }
@@ -803,9 +861,9 @@ static int decode_impl(const void* q, int64_t q_stride, const void* k_cache,
   p.groups_per_kvh = (p.G + kDecMaxG - 1) / kDecMaxG;
   p.max_splits = max_splits;
   p.min_chunk = min_chunk;
-  // fp8 KV: the kernel's e4m3 -> f16 reinterpretation yields value * 2^-8, so 2^8 rides on both scales
-  if (kv_fp8) sm_scale *= k_descale * 256.f;
-  p.out_scale = kv_fp8 ? v_descale * 256.f : 1.f;
+  // fp8 KV: the bit-trick e4m3 -> f16 conversion yields value * 2^-8 (kFp8Bias = 2^8 then rides on both scales)
+  if (kv_fp8) sm_scale *= k_descale * kFp8Bias;
+  p.out_scale = kv_fp8 ? v_descale * kFp8Bias : 1.f;
   p.scale_log2 = sm_scale * kLog2e;
   p.window_left = window_left;
   p.cap_pre = logit_cap > 0.f ? sm_scale / logit_cap : 0.f;

@@ -410,6 +410,12 @@ def decode_workspace_bytes(B: int, Hq: int, D: int, max_splits: int) -> int:
     return _lib.load().b200attn_decode_workspace_bytes(B, Hq, D, max_splits)
 
 
+def decode_ctas_per_sm(fp8_kv: bool = False) -> int:
+    """Resident CTAs per SM of the decode kernels (their __launch_bounds__): 2 x 96 KB rings for 16-bit pools,
+    3 x 64 KB for e4m3 pools (csrc/decode.cu); the wave arithmetic of the two split heuristics below needs it."""
+    return 3 if fp8_kv else 2
+
+
 def pick_max_splits(B: int, Hkv: int, G: int, max_kv_len: int, min_chunk: int = 256,
                     ctas_per_sm: int = 2, num_sms: Optional[int] = None) -> int:
     """Host-side choice of the split cap.  The decode grid is (splits x kv-head groups x batch) CTAs over
