@@ -23,6 +23,8 @@ class FusedSetKVBufferArg:
     k_buffer: torch.Tensor
     v_buffer: torch.Tensor
     cache_loc: torch.Tensor
+    k_scale: Optional[float] = None  # e4m3 pools only (memory_pool.py:2365-2371)
+    v_scale: Optional[float] = None
 
 
 def compute_cos_sin_cache(rotary_dim: int, max_position: int, base: float) -> torch.Tensor:
@@ -57,6 +59,14 @@ class RotaryEmbedding:
         f = fused_set_kv_buffer_arg
         if positions.dim() == 2 and not self.mrope_section:
             raise AssertionError("2D positions (multimodal RoPE) need an MRotaryEmbedding")  # base.py:216-219
+        if f is not None and f.k_buffer.dtype in (torch.float8_e4m3fn, torch.uint8):
+            # e4m3 pool: rotate in place, then the quantising store of the rotated k and of v (two launches; the
+            # copy-engine pipeline of b200attn_rope_store writes 16-bit rows only)
+            self.forward(positions, query, key)
+            T = key.shape[0]
+            ops.store_cache_fp8(key.view(T, -1), f.value.reshape(T, -1), f.k_buffer, f.v_buffer, f.cache_loc,
+                                f.k_scale, f.v_scale)
+            return query, key
         ops.apply_rope_with_cos_sin_cache_inplace(
             positions, query, key, self.cos_sin_cache, head_size=self.head_size, is_neox=self.is_neox_style,
             rope_dim=self.rotary_dim, mrope_section=self.mrope_section if positions.dim() == 2 else None,

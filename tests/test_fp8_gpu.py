@@ -179,3 +179,84 @@ def test_backend_fp8_pool(mode):
                                 sc.req_pool_indices, torch.tensor(lens), torch.tensor(ext), Hq, Hkv, D, D ** -0.5,
                                 causal=True)
     assert_close_attn(o, ref, f"backend fp8 {mode}")
+
+
+def test_backend_fp8_cuda_graph_decode_replay():
+    """One captured decode step over an e4m3 pool (quantising store + fp8 decode), replayed with new lengths/slots."""
+    Hq, Hkv, D, page, B = 32, 8, 128, 16, 8
+    ks, vs = 0.7, 1.1
+    lens0 = [100, 37, 512, 64, 900, 3, 258, 777]
+    sc, k8, v8, _, _ = _fp8_scenario(lens0, [1] * B, Hq, Hkv, D, page, seed=77, ks=ks, vs=vs)
+    backend, pool = _backend(sc, Hkv, D, page, k8, v8)
+    req_pool = backend.req_to_token_pool
+    backend.init_cuda_graph_state(B, B, num_q_heads=Hq, head_dim=D)
+    layer = RadixAttention(Hq, D, sc.scaling, Hkv, 0)
+    layer.k_scale, layer.v_scale, layer.k_scale_float, layer.v_scale_float = torch.tensor(ks), torch.tensor(vs), ks, vs
+    s_req = sc.req_pool_indices.to(DEV)
+    s_seq = torch.tensor(lens0, dtype=torch.int64, device=DEV)
+    s_loc = sc.out_cache_loc.to(DEV)
+    s_q, s_k, s_v = sc.q.to(DEV), sc.k.to(DEV), sc.v.to(DEV)
+    fb = ForwardBatch(forward_mode=ForwardMode.DECODE, batch_size=B, req_pool_indices=s_req, seq_lens=s_seq,
+                      out_cache_loc=s_loc, seq_lens_sum=sum(lens0), attn_backend=backend)
+    stream = torch.cuda.Stream()
+    stream.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(stream):
+        backend.init_forward_metadata_out_graph(fb, in_capture=True)
+        layer(s_q, s_k, s_v, fb)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=stream):
+            backend.init_forward_metadata_in_graph(fb)
+            s_out = layer(s_q, s_k, s_v, fb)
+    torch.cuda.current_stream().wait_stream(stream)
+
+    def check(lens, seed):
+        sc2 = make_scenario([l - 1 for l in lens], [1] * B, Hq, Hkv, D, page, seed=seed, pool_slack=1.0)
+        n = min(req_pool.req_to_token.shape[1], sc2.req_to_token.shape[1])
+        req_pool.req_to_token.zero_()
+        req_pool.req_to_token[:, :n].copy_(sc2.req_to_token[:, :n] % pool.k_buffer[0].shape[0])
+        s_seq.copy_(torch.tensor(lens))
+        loc = torch.stack([req_pool.req_to_token[b + 1, lens[b] - 1] for b in range(B)]).long()
+        s_loc.copy_(loc)
+        s_q.copy_(sc2.q)
+        s_k.copy_(sc2.k)
+        s_v.copy_(sc2.v)
+        backend.init_forward_metadata_out_graph(fb)
+        graph.replay()
+        torch.cuda.synchronize()
+        kc, vc = pool.k_buffer[0], pool.v_buffer[0]
+        assert torch.equal(kc[loc].cpu(), fp8_port.quantize(s_k.cpu().view(B, Hkv, D), ks))  # captured quantising store
+        ref = oracle.attention_fp32(s_q, fp8_port.dequantize(kc, ks), fp8_port.dequantize(vc, vs),
+                                    req_pool.req_to_token, s_req, torch.tensor(lens),
+                                    torch.ones(B, dtype=torch.int64), Hq, Hkv, D, sc.scaling, causal=False)
+        assert_close_attn(s_out, ref, f"fp8 graph replay seed {seed}")
+
+    check(lens0, 5)
+    check([1, 900, 17, 16, 333, 640, 2, 45], 6)
+
+
+def test_rotary_with_fp8_pool_store():
+    """RotaryEmbedding(..., fused_set_kv_buffer_arg=) over an e4m3 pool: rotate, then the quantising store."""
+    from sglang_b200.rotary import FusedSetKVBufferArg, RotaryEmbedding
+
+    T, Hq, Hkv, D = 50, 8, 2, 128
+    g = torch.Generator().manual_seed(4)
+    q = torch.randn((T, Hq * D), generator=g).to(torch.bfloat16)
+    k = torch.randn((T, Hkv * D), generator=g).to(torch.bfloat16)
+    v = torch.randn((T, Hkv * D), generator=g).to(torch.bfloat16)
+    pos = torch.randint(0, 4096, (T,), generator=g)
+    loc = torch.randperm(200, generator=g)[:T] + 1
+    rope = RotaryEmbedding(D, D, 4096, 10000.0, True, torch.bfloat16, device=DEV, native_rounding=True)
+    k8 = torch.zeros((256, Hkv, D), dtype=FP8, device=DEV)
+    v8 = torch.zeros_like(k8)
+    qg, kg = q.to(DEV), k.to(DEV)
+    rope(pos.to(DEV), qg, kg, fused_set_kv_buffer_arg=FusedSetKVBufferArg(
+        value=v.to(DEV), k_buffer=k8, v_buffer=v8, cache_loc=loc.to(DEV), k_scale=0.5, v_scale=None))
+    q_ref, k_ref = q.clone(), k.clone()
+    rope2 = RotaryEmbedding(D, D, 4096, 10000.0, True, torch.bfloat16, device=DEV, native_rounding=True)
+    rope2(pos.to(DEV), (q_g := q_ref.to(DEV)), (k_g := k_ref.to(DEV)))
+    assert torch.equal(qg, q_g) and torch.equal(kg, k_g)
+    kc = torch.zeros((256, Hkv, D), dtype=torch.uint8)
+    vc = torch.zeros_like(kc)
+    fp8_port.store_kv_fp8(kc, vc, loc, kg.cpu().view(T, Hkv, D), v.view(T, Hkv, D), 0.5, None)
+    assert torch.equal(k8.view(torch.uint8).cpu(), kc) and torch.equal(v8.view(torch.uint8).cpu(), vc)
