@@ -160,6 +160,26 @@ int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
                     int64_t workspace_bytes, void* stream);
 
 /* --------------------------------------------------------------------------
+ * (a4) Decode, flat tile-stream scheduling.  Same contract and arithmetic as
+ * b200attn_decode (16-bit pools), but the batch is ONE stream of 64-key tiles cut
+ * into equal contiguous ranges over 2 CTAs per SM, so every CTA moves the same
+ * number of KV bytes whatever the batch shape; there is no host-side split policy
+ * (`min_chunk` only bounds how finely short batches are cut).  Units cut across
+ * CTAs are merged by the last piece to arrive.  Workspace:
+ * b200attn_decode_sk_workspace_bytes(B, Hq, Hkv, D) bytes, zero-initialised once by
+ * the caller (arrival counters; every launch leaves them at zero).
+ * -------------------------------------------------------------------------- */
+int64_t b200attn_decode_sk_workspace_bytes(int32_t B, int32_t Hq, int32_t Hkv, int32_t D);
+
+int b200attn_decode_sk(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache,
+                       int64_t kv_stride, void* o, int64_t o_stride, float* lse,
+                       const int32_t* kv_indptr, const int32_t* kv_indices, const int32_t* q_rows,
+                       const int32_t* req_ids, int32_t B, int32_t Hq, int32_t Hkv, int32_t D,
+                       int dtype, float sm_scale, int32_t min_chunk, int32_t window_left,
+                       float logit_cap, const float* sinks, void* workspace,
+                       int64_t workspace_bytes, void* stream);
+
+/* --------------------------------------------------------------------------
  * (f4) FP8 (e4m3) KV cache.  Pool dtype float8_e4m3fn stored as bytes
  *   python/sglang/srt/mem_cache/memory_pool.py:2365-2375 (div by k_scale/v_scale in
  *     the input dtype, .to(float8_e4m3fn), uint8 view)

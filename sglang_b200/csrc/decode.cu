@@ -19,67 +19,9 @@
 //
 // Algorithmic bytes per (request, kv head): 2 * L * D * sizeof(T) (K and V rows)
 // + 4 * L (int32 slot ids).
-#include "common.cuh"
+#include "decode.cuh"
 
 namespace b200attn {
-
-constexpr int kDecTile = 64;     // keys per pipeline stage
-constexpr int kDecStages = 3;    // cp.async ring depth
-constexpr int kDecThreads = 128; // 4 warps x 16 keys
-constexpr int kDecMaxG = 16;     // q heads per CTA (M of the mma)
-
-struct DecodeParams {
-  const void* q;
-  const void* k_cache;
-  const void* v_cache;
-  void* o;
-  float* lse;
-  const int32_t* kv_indptr;
-  const int32_t* kv_indices;
-  const int32_t* q_rows;
-  const int32_t* req_ids;
-  float* ws_o;    // [B, Hq, max_splits, D]
-  float* ws_lse;  // [B, Hq, max_splits]   (log2 domain)
-  int* ws_cnt;    // [B, Hkv * groups] arrival counters of the split CTAs of a unit; zero on entry, zero on exit
-  int64_t q_stride, kv_stride, o_stride;
-  int B, Hq, Hkv, G, groups_per_kvh;
-  int max_splits, min_chunk;
-  float scale_log2;
-  // feature flags: triton_backend.py:1405-1416, decode_attention.py:986-988
-  int window_left;      // >= 0: only keys kv_id >= q_id - window_left (q_id = L - 1); < 0: off
-  float cap_pre;        // logit cap c > 0: x = c * tanh(s * sm_scale / c); cap_pre = sm_scale / c
-  float cap_post;       // c * log2(e); 0 = no cap
-  const float* sinks;   // per q head sink logit (natural units) added to the softmax denominator, or null
-  // Tail splitting: units (request, kv head group) are launched in rank order, `tail_begin` of them fill whole
-  // waves of resident CTAs and stay unsplit; the remainder would leave SMs idle for up to a whole unit, so only
-  // THOSE units are split `max_splits` ways.  tail_begin < 0: every unit uses the length-based policy.
-  int tail_begin;
-  float out_scale;  // fp8 KV only: v_descale * 2^8 applied to the normalised output (decode_fp8_kernel)
-};
-
-// split cap of one unit (shared by the attention and the merge kernel)
-__device__ __forceinline__ int unit_max_splits(const DecodeParams& p, int item, int hg) {
-  if (p.tail_begin < 0) return p.max_splits;
-  return item * (p.Hkv * p.groups_per_kvh) + hg >= p.tail_begin ? p.max_splits : 1;
-}
-
-// keys of a request that the (single) query row sees: [kv_lo, L)
-__device__ __forceinline__ int window_lo(int L, int window_left) {
-  return window_left >= 0 ? max(0, L - 1 - window_left) : 0;
-}
-__device__ __forceinline__ float tanh_approx(float x) {
-  float y;
-  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-
-template <int D>
-__device__ __forceinline__ uint32_t swz_off(int row, int chunk) {
-  // byte offset of 16-byte chunk `chunk` of row `row` in a [rows][D] 2-byte tile;
-  // chunks are XOR-swizzled with the row so that ldmatrix (8 rows x 16 B) is conflict free.
-  constexpr int kChunks = D / 8;
-  return (uint32_t)(row * (D * 2) + (((chunk ^ (row & 7)) & (kChunks - 1)) << 4));
-}
 
 template <int D, bool kBf16>
 __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodeParams p) {

@@ -410,6 +410,10 @@ def decode_workspace_bytes(B: int, Hq: int, D: int, max_splits: int) -> int:
     return _lib.load().b200attn_decode_workspace_bytes(B, Hq, D, max_splits)
 
 
+def decode_sk_workspace_bytes(B: int, Hq: int, Hkv: int, D: int) -> int:
+    return int(_lib.load().b200attn_decode_sk_workspace_bytes(B, Hq, Hkv, D))
+
+
 def decode_ctas_per_sm(fp8_kv: bool = False) -> int:
     """Resident CTAs per SM of the decode kernels (their __launch_bounds__): 2 x 96 KB rings for 16-bit pools,
     3 x 64 KB for e4m3 pools (csrc/decode.cu); the wave arithmetic of the two split heuristics below needs it."""
@@ -474,6 +478,7 @@ def decode_attention(
     tail_begin: int = -1,
     k_descale: float = 1.0,
     v_descale: float = 1.0,
+    stream_k: bool = False,
 ) -> torch.Tensor:
     """Paged GQA decode: ``q [B,Hq,D]``, caches ``[slots,Hkv,D]`` -> ``o [B,Hq,D]``.
 
@@ -512,6 +517,15 @@ def decode_attention(
             _sinks_ptr(sinks, Hq), _ptr(workspace), ws_bytes, _stream(),
         )
         check(rc, "b200attn_decode_fp8kv")
+        return o
+    if stream_k:  # flat tile-stream scheduling (b200attn_decode_sk): max_splits / tail_begin do not apply
+        rc = _lib.load().b200attn_decode_sk(
+            q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
+            o.data_ptr(), o.stride(0), _ptr(lse), kv_indptr.data_ptr(), kv_indices.data_ptr(),
+            _ptr(q_rows), _ptr(req_ids), B, Hq, Hkv, D, _fdtype(q), float(sm_scale), min_chunk,
+            int(window_left), float(logit_cap), _sinks_ptr(sinks, Hq), _ptr(workspace), ws_bytes, _stream(),
+        )
+        check(rc, "b200attn_decode_sk")
         return o
     rc = _lib.load().b200attn_decode(
         q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
