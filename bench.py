@@ -368,6 +368,9 @@ def run_b200(args, rank, world, local_rank):
                 dev, gen, peaks, "qwen2.5-vl-7b MIXED: 16 req x 1280 new tokens + 16 decode rows (prefix 1279), "
                 "Hq 28 / Hkv 4 (BASELINE configs[3])", [0] * 16 + [1279] * 16, [1280] * 16 + [1] * 16, 28, 4, 128,
                 16, causal, "MIXED")
+        # configs[0]: the reference's own CPU-runnable case, timed on the host cores beside the GPU path
+        if rank == 0 and not args.no_cpu_baseline:
+            extra["cfg1_qwen2_0p5b_decode"] = run_cfg1(dev, gen)
         # configs[1] again over a float8_e4m3fn pool: half the KV bytes per call
         extra["cfg2_decode_fp8kv"] = run_cfg2_decode_fp8(dev, gen, peaks)
         torch.cuda.empty_cache()
@@ -526,6 +529,54 @@ def run_backend_case(dev, gen, peaks, label, prefix_lens, ext_lens, Hq, Hkv, D, 
     tf = fl / (ms * 1e-3) / 1e12
     return dict(workload=label, ms_per_step=ms, flops=fl, tflops=tf, decode_row_kv_bytes=dec_bytes, tokens=T,
                 frac_of_measured_bf16=tf / peaks["tf_burst"], frac_of_2250=tf / 2250.0)
+
+
+def run_cfg1(dev, gen, steps=50, warmup=5):
+    """BASELINE configs[0]: Qwen2-0.5B shape, decode batch 8 x 1K ctx, page_size 1.  The torch_native port runs on the
+    host cores (the reference's own CPU case); the same tensors go through B200AttnBackend (store + decode) on the GPU
+    and the two outputs are compared (1e-2 rel / 2e-2 abs)."""
+    from oracle import torch_native_port as oracle
+    from sglang_b200 import B200AttnBackend, ForwardBatch, ForwardMode, RadixAttention
+
+    c = dict(B=8, ctx=1024, Hq=14, Hkv=2, D=64, page=1)
+    B, Hq, Hkv, D = c["B"], c["Hq"], c["Hkv"], c["D"]
+    req_pool, kv_pool, host = build_decode_state(c, dev, gen)
+    backend = B200AttnBackend(Runner(dev, req_pool, kv_pool, 1))
+    layer = RadixAttention(Hq, D, D ** -0.5, Hkv, 0)
+    devt = {k: v.to(dev) for k, v in host.items()}
+    fb = ForwardBatch(forward_mode=ForwardMode.DECODE, batch_size=B, req_pool_indices=devt["req_pool_indices"],
+                      seq_lens=devt["seq_lens"], out_cache_loc=devt["out_cache_loc"], seq_lens_sum=B * c["ctx"],
+                      seq_lens_cpu=host["seq_lens"], attn_backend=backend)
+    backend.init_forward_metadata(fb)
+    kc, vc = (b.cpu().clone() for b in kv_pool.get_kv_buffer(0))
+    table = req_pool.req_to_token.cpu()
+    step = lambda: layer(devt["q"], devt["k"], devt["v"], fb)
+    o = step()
+    t_gpu = time_steps(step, steps, warmup) / steps
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    k3, v3 = host["k"].view(B, Hkv, D), host["v"].view(B, Hkv, D)
+
+    def cpu_call():
+        oracle.store_kv(kc, vc, host["out_cache_loc"], k3, v3)
+        return oracle.decode(host["q"], kc, vc, table, host["req_pool_indices"], host["seq_lens"], Hq, Hkv, D, D ** -0.5)
+
+    ref = cpu_call()
+    ts = []
+    for _ in range(20):
+        t0 = time.perf_counter()
+        cpu_call()
+        ts.append(time.perf_counter() - t0)
+    t_cpu = statistics.median(ts) * 1e3
+    err = (o.float().cpu() - ref.float()).abs()
+    ok = bool((err <= 2e-2 + 1e-2 * ref.float().abs()).all())
+    nbytes = decode_bytes(c)
+    return dict(workload="qwen2-0.5b shape decode: batch 8 x 1024 ctx, Hq 14 / Hkv 2, head_dim 64, page_size 1 "
+                         "(BASELINE configs[0])", bytes=nbytes,
+                cpu_torch_native_port=dict(ms=t_cpu, gbs=nbytes / t_cpu / 1e6, cores=threads),
+                gpu_layer_call=dict(ms=t_gpu, gbs=nbytes / t_gpu / 1e6, note="store + decode through B200AttnBackend, "
+                                    "eager launches; 4 MB of KV: launch-latency-bound, not an HBM number"),
+                max_abs_err=float(err.max()), within_tolerance=ok)
 
 
 def run_cfg2_decode_fp8(dev, gen, peaks, steps=20, warmup=5):

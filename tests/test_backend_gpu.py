@@ -256,3 +256,24 @@ def test_backend_cuda_graph_extend_replay():
                                     sc.scaling, causal=True)
         assert_close_attn(s_out[:T], ref, f"extend graph replay {ext}")
         assert torch.equal(kc[loc], s_k[:T])
+
+
+def test_baseline_config0_qwen2_0p5b_decode_page1():
+    """BASELINE configs[0] at its exact shape: Qwen2-0.5B (Hq 14 / Hkv 2 / D 64), decode batch 8 x 1K ctx,
+    page_size 1, through the backend (store + decode) against the torch_native port."""
+    Hq, Hkv, D, B, ctx = 14, 2, 64, 8, 1024
+    sc = make_scenario([ctx - 1] * B, [1] * B, Hq, Hkv, D, 1, seed=20261104)
+    backend, req_pool, kv_pool = _setup(sc, False)
+    layer = RadixAttention(Hq, D, sc.scaling, Hkv, 0)
+    fb = ForwardBatch(forward_mode=ForwardMode.DECODE, batch_size=B, req_pool_indices=sc.req_pool_indices.to(DEV),
+                      seq_lens=torch.full((B,), ctx, dtype=torch.int64, device=DEV),
+                      out_cache_loc=sc.out_cache_loc.to(DEV), seq_lens_sum=B * ctx,
+                      seq_lens_cpu=torch.full((B,), ctx, dtype=torch.int64), attn_backend=backend)
+    backend.init_forward_metadata(fb)
+    o = layer(sc.q.to(DEV), sc.k.to(DEV), sc.v.to(DEV), fb)
+    torch.cuda.synchronize()
+    kc, vc = sc.k_cache.clone(), sc.v_cache.clone()
+    oracle.store_kv(kc, vc, sc.out_cache_loc, sc.k.view(B, Hkv, D), sc.v.view(B, Hkv, D))
+    ref = oracle.decode(sc.q, kc, vc, sc.req_to_token, sc.req_pool_indices, torch.full((B,), ctx), Hq, Hkv, D, sc.scaling)
+    assert torch.equal(kv_pool.k_buffer[0].cpu(), kc) and torch.equal(kv_pool.v_buffer[0].cpu(), vc)
+    assert_close_attn(o, ref, "configs[0] qwen2-0.5b decode")
