@@ -321,13 +321,30 @@ def run_b200(args, rank, world, local_rank):
     aux = torch.cuda.Stream()
     fork = os.environ.get("B200ATTN_BENCH_FORK", "0") == "1"  # measured: no gain (234 vs 235 us), copy latency dominates
 
-    def graph_body():
-        # the metadata refill only needs the index vectors: it runs on a forked stream (a graph branch) beside the
-        # q/k/v copies
+    # Host layout of a step's inputs.  "fused" is the layout the model hands a backend: ONE [B, (Hq+2Hkv)*D] qkv
+    # activation (q/k/v are column views with the fused token stride) and one int64 [3, B] block of
+    # index vectors -> two H2D copies per step.  "separate" keeps six tensors -> six copies.  Same bytes either way.
+    W = (Hq + 2 * Hkv) * D
+    host_qkv = torch.cat([host["q"], host["k"], host["v"]], dim=1).pin_memory()
+    host_idx = torch.stack([host["seq_lens"], host["req_pool_indices"], host["out_cache_loc"]]).pin_memory()
+    dev_qkv = torch.empty((B, W), dtype=torch.bfloat16, device=dev)
+    dev_idx = torch.empty((3, B), dtype=torch.int64, device=dev)
+    assert host_qkv.numel() * 2 + host_idx.numel() * 8 == h2d
+    fbp = ForwardBatch(forward_mode=ForwardMode.DECODE, batch_size=B, req_pool_indices=dev_idx[1], seq_lens=dev_idx[0],
+                       out_cache_loc=dev_idx[2], seq_lens_sum=B * c["ctx"], attn_backend=backend)
+
+    def graph_body(fused):
         cur = torch.cuda.current_stream()
+        if fused:
+            dev_idx.copy_(host_idx, non_blocking=True)
+            backend.init_forward_metadata_out_graph(fbp)
+            dev_qkv.copy_(host_qkv, non_blocking=True)
+            o = layer(dev_qkv[:, :Hq * D], dev_qkv[:, Hq * D:(Hq + Hkv) * D], dev_qkv[:, (Hq + Hkv) * D:], fbp)
+            o_host.copy_(o, non_blocking=True)
+            return
         for k_ in ("seq_lens", "req_pool_indices", "out_cache_loc"):
             devt[k_].copy_(host[k_], non_blocking=True)
-        if fork:
+        if fork:  # the metadata refill only needs the index vectors: a graph branch beside the q/k/v copies
             aux.wait_stream(cur)
             with torch.cuda.stream(aux):
                 backend.init_forward_metadata_out_graph(fbg)
@@ -339,28 +356,36 @@ def run_b200(args, rank, world, local_rank):
             cur.wait_stream(aux)
         o_host.copy_(layer(devt["q"], devt["k"], devt["v"], fbg), non_blocking=True)
 
-    side = torch.cuda.Stream()
-    side.wait_stream(torch.cuda.current_stream())
-    with torch.cuda.stream(side):
-        graph_body()
-        torch.cuda.synchronize()
-        graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph, stream=side):
-            graph_body()
-    torch.cuda.current_stream().wait_stream(side)
-    e2e_graph_ms = time_steps(graph.replay, args.steps, args.warmup, barrier)
-    if world > 1:
-        t = torch.tensor([e2e_graph_ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_graph_ms = float(t)
-    e2e_graph_ms /= args.steps
+    def time_graph(fused):
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            graph_body(fused)
+            torch.cuda.synchronize()
+            g_ = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g_, stream=side):
+                graph_body(fused)
+        torch.cuda.current_stream().wait_stream(side)
+        ms = time_steps(g_.replay, args.steps, args.warmup, barrier)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        return ms / args.steps, g_
+
+    e2e_sep_ms, graph = time_graph(False)
+    o_sep = o_host.clone()
+    e2e_graph_ms, graph2 = time_graph(True)
+    torch.cuda.synchronize()
+    assert torch.equal(o_sep, o_host), "fused-layout e2e step disagrees with the separate-tensor step"
     e2e_graph_val = world * nbytes / (e2e_graph_ms * 1e-3) / 1e9
+    e2e_sep_val = world * nbytes / (e2e_sep_ms * 1e-3) / 1e9
 
     # (4) extend leg (configs[2]): 32 requests sharing a 2048-token prefix + 512 new tokens, causal
     ext = run_extend_leg(args, dev, gen, peaks)
     extra = {}
     if not args.headline_only:
-        del req_pool, kv_pool, backend, fb, fbg, graph, md, kbuf, vbuf
+        del req_pool, kv_pool, backend, fb, fbg, fbp, graph, graph2, md, kbuf, vbuf
         torch.cuda.empty_cache()
         # configs[3]: Qwen2.5-VL-7B LLM side, 16 x (1024 image + 256 text) extend rows + 16 decode rows, MIXED
         for causal in (True, False):
@@ -408,7 +433,11 @@ def run_b200(args, rank, world, local_rank):
         e2e=dict(value=e2e_graph_val, unit="GB/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h,
                  ms_per_step=e2e_graph_ms,
                  mode="B200AttnBackend behind one CUDA graph per step (pinned-host H2D copies, metadata refill, "
-                      "store + decode, D2H read all captured; SGLang's decode-runner path)",
+                      "store + decode, D2H read all captured; SGLang's decode-runner path); inputs in the model's "
+                      "layout: one fused [B, (Hq+2Hkv)*D] qkv activation + one int64 [3, B] index block = 2 H2D copies",
+                 separate_tensors=dict(value=e2e_sep_val, ms_per_step=e2e_sep_ms,
+                                       mode="same graph with q, k, v and the three index vectors as six host "
+                                            "tensors = 6 H2D copies"),
                  eager=dict(value=e2e_val, ms_per_step=e2e_ms,
                             mode="same step launched eagerly from Python (CPU-launch-bound)")),
         gpu_launches=launches_per_step * args.steps,
