@@ -56,3 +56,18 @@ def test_pick_max_splits_bounds():
     assert ops.pick_max_splits(1, 1, 4, 100, num_sms=148) == 1       # never finer than min_chunk
     assert ops.pick_max_splits(1, 8, 4, 1 << 20, num_sms=148) == 37
     assert ops.pick_max_splits(16, 8, 4, 16384, num_sms=148) == 2
+
+
+def test_split_heuristics_follow_the_resident_cta_count():
+    """fp8 pools run 3 CTAs per SM (decode_fp8_kernel), 16-bit pools 2: the wave arithmetic must use the right one."""
+    from sglang_b200 import ops
+
+    assert ops.decode_ctas_per_sm(False) == 2 and ops.decode_ctas_per_sm(True) == 3
+    # cfg2: 512 units.  2 CTAs/SM: 296 slots, 216-unit tail is 73 % of a wave -> left alone; 3 CTAs/SM: 444 slots,
+    # 68-unit tail -> split 6 ways (6 * 68 = 408 <= 444)
+    assert ops.pick_tail_split(64, 8, 4, num_sms=148, ctas_per_sm=2) == (-1, 1)
+    assert ops.pick_tail_split(64, 8, 4, num_sms=148, ctas_per_sm=3) == (444, 6)
+    # split cap = floor(slots / units), bounded by ceil(len / min_chunk)
+    assert ops.pick_max_splits(8, 8, 4, 8192, 256, ctas_per_sm=2, num_sms=148) == 4
+    assert ops.pick_max_splits(8, 8, 4, 8192, 256, ctas_per_sm=3, num_sms=148) == 6
+    assert ops.pick_max_splits(1, 8, 4, 512, 256, ctas_per_sm=3, num_sms=148) == 2
