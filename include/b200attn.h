@@ -328,6 +328,23 @@ int b200attn_rope_store(void* q, void* k, const void* v, void* k_cache, void* v_
                         int64_t skip_index, int32_t* oob_count, int elem_dtype, int mode,
                         void* stream);
 
+/* (f1 + f4) b200attn_rope_store over an e4m3 pool: same arguments plus the pool's scales.  q/k are rotated in
+ * place exactly as b200attn_rope_store does; the pool rows are BYTES (cache strides in elements = bytes) and
+ * receive e4m3(round_src(k_rot / k_scale)) and e4m3(round_src(v / v_scale)) - the bytes b200attn_kv_store_fp8
+ * would write after the rotation (python/sglang/kernels/ops/kvcache/fused_fp8_qkv_kv_cache.py is the
+ * reference's fused fp8 cache write).  k_scale / v_scale <= 0: no division.  k_cache must be non-null. */
+int b200attn_rope_store_fp8(void* q, void* k, const void* v, void* k_cache, void* v_cache,
+                            const void* loc, int loc_dtype, const void* cos_sin_cache,
+                            int cache_dtype, int64_t cache_rows, const void* positions,
+                            int pos_dtype, int64_t pos_axis_stride,
+                            const int32_t* mrope_section_host, int mrope_interleaved,
+                            int64_t T, int32_t Hq, int32_t Hkv, int32_t D, int32_t Dv,
+                            int32_t rotary_dim, int is_neox, int64_t q_stride,
+                            int64_t k_stride, int64_t v_stride, int64_t k_cache_stride,
+                            int64_t v_cache_stride, int64_t size_limit, int64_t skip_index,
+                            int32_t* oob_count, int elem_dtype, int mode, float k_scale,
+                            float v_scale, void* stream);
+
 /* --------------------------------------------------------------------------
  * (f3) Paged KV allocator on the device.  Replaces the Triton kernels
  *   alloc_extend_kernel  python/sglang/kernels/ops/memory/allocator.py:15-103

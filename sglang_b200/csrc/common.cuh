@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
+#include <cuda_fp8.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -122,6 +123,26 @@ __device__ __forceinline__ float2 unpack2(uint32_t x) {
   } else {
     return __half22float2(*reinterpret_cast<__half2*>(&x));
   }
+}
+
+// float -> float8_e4m3fn with c10's semantics (round to nearest even; what would round above 448 becomes the
+// NaN pattern 0x7f, no saturation): 464 is the midpoint of 448 and the non-existent 480, ties go to even (448).
+__device__ __forceinline__ uint8_t to_e4m3_c10(float x) {
+  if (!(fabsf(x) <= 464.f)) return (uint8_t)(0x7f | ((__float_as_uint(x) >> 24) & 0x80));
+  return (uint8_t)__nv_cvt_float_to_fp8(x, __NV_SATFINITE, __NV_E4M3);
+}
+template <bool kBf16>
+__device__ __forceinline__ float round_to_src(float x) {
+  if constexpr (kBf16) return __bfloat162float(__float2bfloat16_rn(x));
+  return __half2float(__float2half_rn(x));
+}
+// one 16-bit element -> e4m3 byte, the pool's rounding order (memory_pool.py:2365-2371): true division by the
+// scale rounded to the source dtype, then the cast; scale <= 0 = no division
+template <bool kBf16>
+__device__ __forceinline__ uint8_t quant_e4m3(uint16_t bits, float scale) {
+  float y = unpack2<kBf16>((uint32_t)bits).x;
+  if (scale > 0.f) y = round_to_src<kBf16>(__fdiv_rn(y, scale));
+  return to_e4m3_c10(y);
 }
 
 __device__ __forceinline__ float fast_exp2(float x) {

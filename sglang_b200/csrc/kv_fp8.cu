@@ -11,23 +11,9 @@
 // `(k / k_scale).to(torch.float8_e4m3fn).view(torch.uint8)` on the CPU.
 //
 // One warp owns one (token, K|V) row; a lane converts 8 elements per step (16 B in, 8 B out).
-#include <cuda_fp8.h>
-
 #include "common.cuh"
 
 namespace b200attn {
-
-__device__ __forceinline__ uint8_t to_e4m3_c10(float x) {
-  // 464 = midpoint of 448 and the (non-existent) next value 480: ties go to the even mantissa (448)
-  if (!(fabsf(x) <= 464.f)) return (uint8_t)(0x7f | ((__float_as_uint(x) >> 24) & 0x80));
-  return (uint8_t)__nv_cvt_float_to_fp8(x, __NV_SATFINITE, __NV_E4M3);
-}
-
-template <bool kBf16>
-__device__ __forceinline__ float round_to_src(float x) {
-  if constexpr (kBf16) return __bfloat162float(__float2bfloat16_rn(x));
-  return __half2float(__float2half_rn(x));
-}
 
 template <bool kBf16>
 __device__ __forceinline__ uint32_t quant4(uint32_t w0, uint32_t w1, float scale, bool has_scale) {

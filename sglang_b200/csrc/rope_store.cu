@@ -47,6 +47,9 @@ struct RopeParams {
   int interleaved, neox, store;
   int cache_vec16;  // cos/sin rows and halves are 16-byte aligned
   int abl_copy_only;  // dev ablation (B200ATTN_ROPE_ABL=copy): staged copy without the rotation
+  // e4m3 pool (b200attn_rope_store_fp8): rows are bytes, rotated k and v are quantised on the way (register kernel)
+  int pool_fp8;
+  float k_scale, v_scale;  // <= 0: no division
 };
 
 template <bool kBf16>
@@ -250,6 +253,19 @@ __device__ __forceinline__ void rotate(Pack<VEC>& a, Pack<VEC>& b, int j0, const
 
 // grid = (ceil(T / TOK), ceil(per_tok / 256)).  A thread owns work item `it` of TOK consecutive tokens and issues
 // all of their 16-byte loads before the first dependent instruction (TOK * 32 B in flight per thread).
+// VEC 16-bit elements of `val` -> VEC e4m3 bytes at dst (dst is VEC-byte aligned by the launcher's vector choice)
+template <int VEC, bool kBf16>
+__device__ __forceinline__ void store_e4m3(uint8_t* dst, const typename VecOf<VEC>::type& val, float scale) {
+  const uint16_t* e = reinterpret_cast<const uint16_t*>(&val);
+  uint8_t out[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) out[i] = quant_e4m3<kBf16>(e[i], scale);
+  if constexpr (VEC == 8) *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<const uint2*>(out);
+  else if constexpr (VEC == 4) *reinterpret_cast<uint32_t*>(dst) = *reinterpret_cast<const uint32_t*>(out);
+  else if constexpr (VEC == 2) *reinterpret_cast<uint16_t*>(dst) = *reinterpret_cast<const uint16_t*>(out);
+  else *dst = out[0];
+}
+
 template <int VEC, bool kBf16, bool kCacheF32, bool kNative, int TOK>
 __global__ void __launch_bounds__(256, TOK == 1 ? 6 : 4) rope_store_kernel(const RopeParams p) {
   using V = typename VecOf<VEC>::type;
@@ -289,8 +305,11 @@ __global__ void __launch_bounds__(256, TOK == 1 ? 6 : 4) rope_store_kernel(const
       if (ok[u]) val[u] = *reinterpret_cast<const V*>(sbase + (t * sstride + col) * 2);
     }
 #pragma unroll
-    for (int u = 0; u < TOK; ++u)
-      if (ok[u]) *reinterpret_cast<V*>(dbase + (slot[u] * dstride + col) * 2) = val[u];
+    for (int u = 0; u < TOK; ++u) {
+      if (!ok[u]) continue;
+      if (p.pool_fp8) store_e4m3<VEC, kBf16>(dbase + slot[u] * dstride + col, val[u], is_kp ? p.k_scale : p.v_scale);
+      else *reinterpret_cast<V*>(dbase + (slot[u] * dstride + col) * 2) = val[u];
+    }
     return;
   }
 
@@ -328,9 +347,15 @@ __global__ void __launch_bounds__(256, TOK == 1 ? 6 : 4) rope_store_kernel(const
     *reinterpret_cast<V*>(row + off_b) = b[u].v;
     int64_t slot;
     if (is_k && p.store && store_slot(p, t, it == 0, slot)) {
-      uint8_t* crow = p.k_cache + (slot * p.kc_stride + (int64_t)h * p.D) * 2;
-      *reinterpret_cast<V*>(crow + off_a) = a[u].v;
-      *reinterpret_cast<V*>(crow + off_b) = b[u].v;
+      if (p.pool_fp8) {
+        uint8_t* crow = p.k_cache + slot * p.kc_stride + (int64_t)h * p.D;
+        store_e4m3<VEC, kBf16>(crow + off_a / 2, a[u].v, p.k_scale);
+        store_e4m3<VEC, kBf16>(crow + off_b / 2, b[u].v, p.k_scale);
+      } else {
+        uint8_t* crow = p.k_cache + (slot * p.kc_stride + (int64_t)h * p.D) * 2;
+        *reinterpret_cast<V*>(crow + off_a) = a[u].v;
+        *reinterpret_cast<V*>(crow + off_b) = b[u].v;
+      }
     }
   }
 }
@@ -639,16 +664,17 @@ static int launch_rope(const RopeParams& p, int elem_dtype, int cache_dtype, int
 
 }  // namespace b200attn
 
-extern "C" int b200attn_rope_store(void* q, void* k, const void* v, void* k_cache, void* v_cache,
-                                   const void* loc, int loc_dtype, const void* cos_sin_cache,
-                                   int cache_dtype, int64_t cache_rows, const void* positions,
-                                   int pos_dtype, int64_t pos_axis_stride,
-                                   const int32_t* mrope_section_host, int mrope_interleaved,
-                                   int64_t T, int32_t Hq, int32_t Hkv, int32_t D, int32_t Dv,
-                                   int32_t rotary_dim, int is_neox, int64_t q_stride,
-                                   int64_t k_stride, int64_t v_stride, int64_t k_cache_stride,
-                                   int64_t v_cache_stride, int64_t size_limit, int64_t skip_index,
-                                   int32_t* oob_count, int elem_dtype, int mode, void* stream) {
+static int rope_store_impl(void* q, void* k, const void* v, void* k_cache, void* v_cache,
+                           const void* loc, int loc_dtype, const void* cos_sin_cache,
+                           int cache_dtype, int64_t cache_rows, const void* positions,
+                           int pos_dtype, int64_t pos_axis_stride,
+                           const int32_t* mrope_section_host, int mrope_interleaved,
+                           int64_t T, int32_t Hq, int32_t Hkv, int32_t D, int32_t Dv,
+                           int32_t rotary_dim, int is_neox, int64_t q_stride,
+                           int64_t k_stride, int64_t v_stride, int64_t k_cache_stride,
+                           int64_t v_cache_stride, int64_t size_limit, int64_t skip_index,
+                           int32_t* oob_count, int elem_dtype, int mode, void* stream, bool pool_fp8,
+                           float k_scale, float v_scale) {
   using namespace b200attn;
   B2_CHECK_ARG(T >= 0, "rope_store: negative T");
   if (T == 0) return B200ATTN_OK;
@@ -683,6 +709,7 @@ extern "C" int b200attn_rope_store(void* q, void* k, const void* v, void* k_cach
   p.Hq = Hq; p.Hkv = Hkv; p.D = D; p.Dv = store ? Dv : 0; p.rot = rotary_dim;
   p.loc_dtype = loc_dtype; p.pos_dtype = pos_dtype;
   p.interleaved = mrope_interleaved; p.neox = is_neox; p.store = store;
+  p.pool_fp8 = pool_fp8 && store; p.k_scale = k_scale; p.v_scale = v_scale;
   if (mrope_section_host != nullptr) {
     p.sec0 = mrope_section_host[0]; p.sec1 = mrope_section_host[1]; p.sec2 = mrope_section_host[2];
     B2_CHECK_ARG(p.sec0 >= 0 && p.sec1 >= 0 && p.sec2 >= 0 &&
@@ -702,7 +729,7 @@ extern "C" int b200attn_rope_store(void* q, void* k, const void* v, void* k_cach
   if (store) {
     bits |= (uint64_t)Dv | (uint64_t)(D - rotary_dim) | (uint64_t)v_stride | (uint64_t)k_cache_stride |
             (uint64_t)v_cache_stride | ((uint64_t)(uintptr_t)v >> 1) |
-            ((uint64_t)(uintptr_t)k_cache >> 1) | ((uint64_t)(uintptr_t)v_cache >> 1);
+            ((uint64_t)(uintptr_t)k_cache >> (pool_fp8 ? 0 : 1)) | ((uint64_t)(uintptr_t)v_cache >> (pool_fp8 ? 0 : 1));
   } else {
     bits |= (uint64_t)(D - rotary_dim);
   }
@@ -719,7 +746,7 @@ extern "C" int b200attn_rope_store(void* q, void* k, const void* v, void* k_cach
     // bulk pipeline: every row start must be 16-byte aligned for cp.async.bulk (bits covers strides / bases) and
     // the pass-through columns ride along in the row; small batches keep the register kernel (more CTAs)
     const char* e = getenv("B200ATTN_ROPE_BULK");  // dev ablation hook: 0 = never, 1 = always
-    const bool want = e ? atoi(e) != 0 : T >= 2 * sm_count();
+    const bool want = (e ? atoi(e) != 0 : T >= 2 * sm_count()) && !p.pool_fp8;  // bulk stores move 16-bit rows only
     if (want && (!store || (D - rotary_dim) % 8 == 0)) {
       const int rc = launch_rope_bulk(p, elem_dtype, cache_dtype, mode, st);
       if (rc >= 0) return rc;
@@ -729,4 +756,41 @@ extern "C" int b200attn_rope_store(void* q, void* k, const void* v, void* k_cach
   if ((bits & 3) == 0) return launch_rope<4>(p, elem_dtype, cache_dtype, mode, st);
   if ((bits & 1) == 0) return launch_rope<2>(p, elem_dtype, cache_dtype, mode, st);
   return launch_rope<1>(p, elem_dtype, cache_dtype, mode, st);
+}
+
+extern "C" int b200attn_rope_store(void* q, void* k, const void* v, void* k_cache, void* v_cache,
+                                   const void* loc, int loc_dtype, const void* cos_sin_cache,
+                                   int cache_dtype, int64_t cache_rows, const void* positions,
+                                   int pos_dtype, int64_t pos_axis_stride,
+                                   const int32_t* mrope_section_host, int mrope_interleaved,
+                                   int64_t T, int32_t Hq, int32_t Hkv, int32_t D, int32_t Dv,
+                                   int32_t rotary_dim, int is_neox, int64_t q_stride,
+                                   int64_t k_stride, int64_t v_stride, int64_t k_cache_stride,
+                                   int64_t v_cache_stride, int64_t size_limit, int64_t skip_index,
+                                   int32_t* oob_count, int elem_dtype, int mode, void* stream) {
+  return rope_store_impl(q, k, v, k_cache, v_cache, loc, loc_dtype, cos_sin_cache, cache_dtype, cache_rows,
+                         positions, pos_dtype, pos_axis_stride, mrope_section_host, mrope_interleaved, T, Hq, Hkv,
+                         D, Dv, rotary_dim, is_neox, q_stride, k_stride, v_stride, k_cache_stride, v_cache_stride,
+                         size_limit, skip_index, oob_count, elem_dtype, mode, stream, false, 0.f, 0.f);
+}
+
+extern "C" int b200attn_rope_store_fp8(void* q, void* k, const void* v, void* k_cache, void* v_cache,
+                                       const void* loc, int loc_dtype, const void* cos_sin_cache,
+                                       int cache_dtype, int64_t cache_rows, const void* positions,
+                                       int pos_dtype, int64_t pos_axis_stride,
+                                       const int32_t* mrope_section_host, int mrope_interleaved,
+                                       int64_t T, int32_t Hq, int32_t Hkv, int32_t D, int32_t Dv,
+                                       int32_t rotary_dim, int is_neox, int64_t q_stride,
+                                       int64_t k_stride, int64_t v_stride, int64_t k_cache_stride,
+                                       int64_t v_cache_stride, int64_t size_limit, int64_t skip_index,
+                                       int32_t* oob_count, int elem_dtype, int mode, float k_scale,
+                                       float v_scale, void* stream) {
+  if (k_cache == nullptr) {
+    b200attn::set_error("rope_store_fp8: the e4m3 pool is required");
+    return B200ATTN_ERR_INVALID;
+  }
+  return rope_store_impl(q, k, v, k_cache, v_cache, loc, loc_dtype, cos_sin_cache, cache_dtype, cache_rows,
+                         positions, pos_dtype, pos_axis_stride, mrope_section_host, mrope_interleaved, T, Hq, Hkv,
+                         D, Dv, rotary_dim, is_neox, q_stride, k_stride, v_stride, k_cache_stride, v_cache_stride,
+                         size_limit, skip_index, oob_count, elem_dtype, mode, stream, true, k_scale, v_scale);
 }

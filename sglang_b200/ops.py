@@ -218,6 +218,8 @@ def apply_rope_with_cos_sin_cache_inplace(
     reserved_skip_index: int = 0,
     oob_count: Optional[torch.Tensor] = None,
     native_rounding: bool = False,
+    k_scale: Optional[float] = None,
+    v_scale: Optional[float] = None,
 ) -> None:
     """Rotate ``q`` and ``k`` in place; with ``k_buffer/v_buffer/cache_loc/v`` also scatter the rotated k
     and v into the pool (one kernel).
@@ -229,7 +231,9 @@ def apply_rope_with_cos_sin_cache_inplace(
     ``positions`` is ``[T]`` or ``[3, T]`` (then ``mrope_section`` is required).  ``q``/``k`` are
     ``[T, H*head_size]`` or ``[T, H, head_size]`` with contiguous rows (token stride free).
     ``native_rounding`` selects torch's element-dtype arithmetic (bit-exact with ``forward_native``),
-    otherwise fp32 arithmetic with one rounding (the reference CUDA kernel's).
+    otherwise fp32 arithmetic with one rounding (the reference CUDA kernel's).  A float8_e4m3fn (or uint8-viewed)
+    pool takes b200attn_rope_store_fp8: the rotated k and v are quantised on the way into the pool with
+    ``k_scale`` / ``v_scale`` (memory_pool.py:2365-2375), same bytes as rotate-then-``store_cache_fp8``.
     """
     _require_cuda(positions, q, k, cos_sin_cache, v, k_buffer, v_buffer, cache_loc)
     T = q.shape[0]
@@ -273,7 +277,12 @@ def apply_rope_with_cos_sin_cache_inplace(
     if store:
         if v is None or v_buffer is None or cache_loc is None:
             raise ValueError("rope: fused store needs v, k_buffer, v_buffer and cache_loc")
-        if k.dtype != k_buffer.dtype or v.dtype != v_buffer.dtype or v.dtype != k.dtype:
+        pool_fp8 = k_buffer.dtype in (_FP8, torch.uint8)
+        if pool_fp8:
+            k_buffer, v_buffer = _as_bytes(k_buffer), _as_bytes(v_buffer)
+            if v_buffer.dtype != torch.uint8 or v.dtype != k.dtype:
+                raise TypeError("rope: K and V pools must both be float8_e4m3fn and k/v share a dtype")
+        elif k.dtype != k_buffer.dtype or v.dtype != v_buffer.dtype or v.dtype != k.dtype:
             raise TypeError("rope: cache dtype must equal the row dtype")
         v2 = v.reshape(T, -1)
         kc, vc = k_buffer.reshape(k_buffer.shape[0], -1), v_buffer.reshape(v_buffer.shape[0], -1)
@@ -287,6 +296,18 @@ def apply_rope_with_cos_sin_cache_inplace(
         if not cache_loc.is_contiguous():
             cache_loc = cache_loc.contiguous()
     if T == 0:
+        return
+    if store and pool_fp8:
+        rc = _lib.load().b200attn_rope_store_fp8(
+            q2.data_ptr(), k2.data_ptr(), _ptr(v2), _ptr(kc), _ptr(vc), _ptr(cache_loc), _idtype(cache_loc),
+            cos_sin_cache.data_ptr(), _fdtype(cos_sin_cache), cos_sin_cache.shape[0], positions.data_ptr(),
+            _idtype(positions), pos_axis_stride, sec, int(bool(mrope_interleaved)), T, Hq, Hkv, head_size, Dv, rot,
+            int(bool(is_neox)), q2.stride(0), k2.stride(0), v2.stride(0), kc.stride(0), vc.stride(0),
+            min(kc.shape[0], vc.shape[0]), reserved_skip_index, _ptr(oob_count), _fdtype(q),
+            ROPE_NATIVE if native_rounding else ROPE_F32, float(k_scale) if k_scale is not None else 0.0,
+            float(v_scale) if v_scale is not None else 0.0, _stream(),
+        )
+        check(rc, "b200attn_rope_store_fp8")
         return
     rc = _lib.load().b200attn_rope_store(
         q2.data_ptr(), k2.data_ptr(), _ptr(v2), _ptr(kc), _ptr(vc), _ptr(cache_loc),

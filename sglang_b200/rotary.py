@@ -59,20 +59,13 @@ class RotaryEmbedding:
         f = fused_set_kv_buffer_arg
         if positions.dim() == 2 and not self.mrope_section:
             raise AssertionError("2D positions (multimodal RoPE) need an MRotaryEmbedding")  # base.py:216-219
-        if f is not None and f.k_buffer.dtype in (torch.float8_e4m3fn, torch.uint8):
-            # e4m3 pool: rotate in place, then the quantising store of the rotated k and of v (two launches; the
-            # copy-engine pipeline of b200attn_rope_store writes 16-bit rows only)
-            self.forward(positions, query, key)
-            T = key.shape[0]
-            ops.store_cache_fp8(key.view(T, -1), f.value.reshape(T, -1), f.k_buffer, f.v_buffer, f.cache_loc,
-                                f.k_scale, f.v_scale)
-            return query, key
         ops.apply_rope_with_cos_sin_cache_inplace(
             positions, query, key, self.cos_sin_cache, head_size=self.head_size, is_neox=self.is_neox_style,
             rope_dim=self.rotary_dim, mrope_section=self.mrope_section if positions.dim() == 2 else None,
             mrope_interleaved=self.mrope_interleaved, v=None if f is None else f.value,
             k_buffer=None if f is None else f.k_buffer, v_buffer=None if f is None else f.v_buffer,
-            cache_loc=None if f is None else f.cache_loc, native_rounding=self.native_rounding)
+            cache_loc=None if f is None else f.cache_loc, native_rounding=self.native_rounding,
+            k_scale=None if f is None else f.k_scale, v_scale=None if f is None else f.v_scale)
         return query, key
 
 

@@ -260,3 +260,45 @@ def test_rotary_with_fp8_pool_store():
     vc = torch.zeros_like(kc)
     fp8_port.store_kv_fp8(kc, vc, loc, kg.cpu().view(T, Hkv, D), v.view(T, Hkv, D), 0.5, None)
     assert torch.equal(k8.view(torch.uint8).cpu(), kc) and torch.equal(v8.view(torch.uint8).cpu(), vc)
+
+
+@pytest.mark.parametrize("T,Hq,Hkv,D,rot,neox,dtype,native,mrope", [
+    (3, 8, 2, 128, 128, True, torch.bfloat16, False, False),      # decode-sized batch, 1 token per thread
+    (700, 32, 8, 128, 128, True, torch.bfloat16, True, False),    # 2 tokens per thread
+    (50, 4, 4, 64, 32, False, torch.float16, False, False),       # gpt-j pairs, partial rotary (pass-through columns)
+    (40, 14, 2, 64, 64, True, torch.bfloat16, False, False),      # Qwen2-0.5B geometry
+    (33, 28, 4, 128, 128, True, torch.bfloat16, True, True),      # M-RoPE [16, 24, 24]
+    (20, 2, 1, 100, 20, True, torch.bfloat16, False, False),      # narrow vectors (4-element alignment)
+])
+def test_rope_store_fp8_fused_equals_rotate_then_quantising_store(T, Hq, Hkv, D, rot, neox, dtype, native, mrope):
+    """b200attn_rope_store_fp8 (one launch) against rotate-only + the store oracle: q/k bit-equal, pool bytes equal."""
+    from sglang_b200.rotary import compute_cos_sin_cache
+
+    g = torch.Generator().manual_seed(T + D)
+    q = (torch.randn((T, Hq * D), generator=g) * 2).to(dtype)
+    k = (torch.randn((T, Hkv * D), generator=g) * 2).to(dtype)
+    v = (torch.randn((T, Hkv * D), generator=g) * 2).to(dtype)
+    cache = compute_cos_sin_cache(rot, 4096, 10000.0).to(DEV)
+    if mrope:
+        pos = torch.randint(0, 4096, (3, T), generator=g)
+        sec = [16, 24, 24]
+    else:
+        pos = torch.randint(0, 4096, (T,), generator=g)
+        sec = None
+    loc = torch.randperm(1000, generator=g)[:T]
+    loc[0] = 0                                           # reserved slot: skipped
+    k8 = torch.full((1024, Hkv, D), 3, dtype=torch.uint8, device=DEV)
+    v8 = torch.full((1024, Hkv, D), 5, dtype=torch.uint8, device=DEV)
+    kw = dict(head_size=D, is_neox=neox, rope_dim=rot, mrope_section=sec, native_rounding=native)
+    q1, k1 = q.to(DEV), k.to(DEV)
+    ops.apply_rope_with_cos_sin_cache_inplace(pos.to(DEV), q1, k1, cache, v=v.to(DEV), k_buffer=k8.view(FP8),
+                                              v_buffer=v8.view(FP8), cache_loc=loc.to(DEV), k_scale=0.7,
+                                              v_scale=None, **kw)
+    q2, k2 = q.to(DEV), k.to(DEV)
+    ops.apply_rope_with_cos_sin_cache_inplace(pos.to(DEV), q2, k2, cache, **kw)
+    assert torch.equal(q1, q2) and torch.equal(k1, k2)
+    kc = torch.full((1024, Hkv, D), 3, dtype=torch.uint8)
+    vc = torch.full((1024, Hkv, D), 5, dtype=torch.uint8)
+    fp8_port.store_kv_fp8(kc, vc, loc, k2.cpu().view(T, Hkv, D), v.view(T, Hkv, D), 0.7, None, skip_index=0)
+    assert torch.equal(k8.cpu(), kc), "fused rope + e4m3 store: K pool bytes differ"
+    assert torch.equal(v8.cpu(), vc), "fused rope + e4m3 store: V pool bytes differ"
