@@ -11,7 +11,9 @@ there is no Triton, no per-arch dispatch and no CPU / PyTorch fallback.
 """
 from __future__ import annotations
 
+import contextlib
 import dataclasses
+import os
 from types import SimpleNamespace
 from typing import Dict, Optional
 
@@ -106,6 +108,9 @@ class B200AttnBackend(_Base):
         self._ws: Optional[torch.Tensor] = None
         self._fp8_scratch: Optional[torch.Tensor] = None  # [2, n, Hkv, D] 16-bit K/V operands of extend over an fp8 pool
         self._fp8_iota: Optional[torch.Tensor] = None
+        # MIXED batches: the decode rows run on a side stream so that they fill the tail of the persistent extend kernel
+        self._side: Optional[torch.cuda.Stream] = None
+        self._ws_dec: Optional[torch.Tensor] = None
 
     # ------------------------------------------------------------------ helpers
     def support_triton(self) -> bool:  # base_attn_backend.py:298
@@ -426,6 +431,14 @@ class B200AttnBackend(_Base):
         B = md.batch_size
         fp8 = self._fp8_pool()
         dsc = self._descales(layer) if fp8 else {}
+        overlap = md.max_extend_len > 0 and md.num_dec > 0 and os.environ.get("B200ATTN_MIXED_OVERLAP", "1") != "0"
+        if overlap:
+            # fork AFTER the store and BEFORE the extend launch: the extend kernel's 148 persistent CTAs take the SMs
+            # first, the decode rows' CTAs (independent rows of o) start as extend CTAs retire
+            cur = torch.cuda.current_stream()
+            if self._side is None:
+                self._side = torch.cuda.Stream()
+            self._side.wait_stream(cur)
         if md.max_extend_len > 0:
             ws = self._workspace(ops.extend_workspace_bytes(B, q2.shape[0], Hq))
             ek, ev, eidx, escale = kbuf, vbuf, md.kv_indices, layer.scaling
@@ -453,11 +466,20 @@ class B200AttnBackend(_Base):
             Hkv = layer.tp_k_head_num
             ms = ops.pick_max_splits(md.num_dec, Hkv, Hq // Hkv, md.dec_max_kv_len, md.min_chunk,
                                      num_sms=self.num_sms, ctas_per_sm=ops.decode_ctas_per_sm(fp8))
-            ws = self._workspace(ops.decode_workspace_bytes(md.num_dec, Hq, D, ms))
-            ops.decode_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.kv_indptr, md.kv_indices,
-                                 layer.scaling, max_splits=ms, min_chunk=md.min_chunk, workspace=ws,
-                                 q_rows=md.dec_q_rows, req_ids=md.dec_req_ids, num_items=md.num_dec,
-                                 **self._features(layer, kwargs), **dsc)
+            need = ops.decode_workspace_bytes(md.num_dec, Hq, D, ms)
+            with (torch.cuda.stream(self._side) if overlap else contextlib.nullcontext()):
+                if overlap:  # its own workspace: the extend kernel is using self._ws concurrently
+                    if need > 0 and (self._ws_dec is None or self._ws_dec.numel() < need):
+                        self._ws_dec = torch.zeros(need, dtype=torch.uint8, device=self.device)
+                    ws = self._ws_dec if need > 0 else None
+                else:
+                    ws = self._workspace(need)
+                ops.decode_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.kv_indptr, md.kv_indices,
+                                     layer.scaling, max_splits=ms, min_chunk=md.min_chunk, workspace=ws,
+                                     q_rows=md.dec_q_rows, req_ids=md.dec_req_ids, num_items=md.num_dec,
+                                     **self._features(layer, kwargs), **dsc)
+            if overlap:
+                cur.wait_stream(self._side)
         return o
 
 
