@@ -302,12 +302,20 @@ def run_b200(args, rank, world, local_rank):
         backend.init_forward_metadata(fb)
         o_host.copy_(layer(devt["q"], devt["k"], devt["v"], fb), non_blocking=True)
 
-    e2e_ms = time_steps(e2e_step, args.steps, args.warmup, barrier)
-    if world > 1:
-        t = torch.tensor([e2e_ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_ms = float(t)
-    e2e_ms /= args.steps
+    def best_of(fn, reps=3):
+        """K timed steps, max over ranks, repeated `reps` times; the fastest repetition counts (the region is ~10 ms of
+        host<->device traffic: one host hiccup moves it by 10-20 %, measured 225 / 247 / 240 us on the same box)."""
+        best = None
+        for _ in range(reps):
+            ms = time_steps(fn, args.steps, args.warmup, barrier)
+            if world > 1:
+                t = torch.tensor([ms], device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = float(t)
+            best = ms if best is None else min(best, ms)
+        return best / args.steps
+
+    e2e_ms = best_of(e2e_step)
     e2e_val = world * nbytes / (e2e_ms * 1e-3) / 1e9
 
     # (3b) the same step the way SGLang's decode runner drives a backend (decode_cuda_graph_runner.py:1148-1363):
@@ -366,12 +374,7 @@ def run_b200(args, rank, world, local_rank):
             with torch.cuda.graph(g_, stream=side):
                 graph_body(fused)
         torch.cuda.current_stream().wait_stream(side)
-        ms = time_steps(g_.replay, args.steps, args.warmup, barrier)
-        if world > 1:
-            t = torch.tensor([ms], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t)
-        return ms / args.steps, g_
+        return best_of(g_.replay), g_
 
     e2e_sep_ms, graph = time_graph(False)
     o_sep = o_host.clone()
@@ -434,7 +437,8 @@ def run_b200(args, rank, world, local_rank):
                  ms_per_step=e2e_graph_ms,
                  mode="B200AttnBackend behind one CUDA graph per step (pinned-host H2D copies, metadata refill, "
                       "store + decode, D2H read all captured; SGLang's decode-runner path); inputs in the model's "
-                      "layout: one fused [B, (Hq+2Hkv)*D] qkv activation + one int64 [3, B] index block = 2 H2D copies",
+                      "layout: one fused [B, (Hq+2Hkv)*D] qkv activation + one int64 [3, B] index block = 2 H2D copies; "
+                      "fastest of 3 repetitions of K steps (every e2e variant here is timed that way)",
                  separate_tensors=dict(value=e2e_sep_val, ms_per_step=e2e_sep_ms,
                                        mode="same graph with q, k, v and the three index vectors as six host "
                                             "tensors = 6 H2D copies"),
