@@ -144,7 +144,17 @@ class B200AttnBackend(_Base):
             f = getattr(layer, name + "_float", None)
             if f is None:
                 t = getattr(layer, name, None)
-                f = 1.0 if t is None else float(t)
+                if t is None:
+                    return 1.0
+                if isinstance(t, torch.Tensor) and t.is_cuda:
+                    # the reference fills k_scale_float when the scales are loaded (radix_attention.py); without
+                    # it this is one device sync per layer, once: the float is kept on the layer
+                    if torch.cuda.is_current_stream_capturing():
+                        raise RuntimeError("b200 backend: set layer.k_scale_float / v_scale_float before graph capture")
+                    f = float(t)
+                    setattr(layer, name + "_float", f)
+                else:
+                    f = float(t)
             return float(f)
         return dict(k_descale=one("k_scale"), v_descale=one("v_scale"))
 

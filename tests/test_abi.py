@@ -31,6 +31,22 @@ def test_argument_validation_without_gpu():
     assert rc == 1 and b"negative" in lib.b200attn_last_error()
     rc = lib.b200attn_merge_state(None, None, None, None, None, None, 0, 1, 8, 0, None)
     assert rc == 0  # empty problem is a no-op
+    # the fp8 / stream-k entry points validate the same way (host checks first, nothing launched)
+    rc = lib.b200attn_kv_store_fp8(None, None, None, None, None, 0, -1, 16, 16, 16, 16, 16, 16, 0, 1.0, 1.0, 8, 0,
+                                   None, None)
+    assert rc == 1 and b"negative" in lib.b200attn_last_error()
+    rc = lib.b200attn_kv_store_fp8(None, None, None, None, None, 0, 4, 16, 16, 16, 16, 16, 16, 0, 1.0, 1.0, 8, 0,
+                                   None, None)
+    assert rc == 1 and b"null pointer" in lib.b200attn_last_error()
+    rc = lib.b200attn_kv_dequant_gather(None, None, 16, None, 0, 16, None, None, 16, 0, 1.0, 1.0, None)
+    assert rc == 0
+    rc = lib.b200attn_decode_sk(None, 0, None, None, 0, None, 0, None, None, None, None, None, 4, 32, 8, 128, 0,
+                                1.0, 256, -1, 0.0, None, None, 0, None)
+    assert rc == 1 and b"null pointer" in lib.b200attn_last_error()
+    rc = lib.b200attn_decode_fp8kv(None, 0, None, None, 0, None, 0, None, None, None, None, None, 0, 32, 8, 128, 0,
+                                   1.0, 1.0, 1.0, 1, 256, -1, -1, 0.0, None, None, 0, None)
+    assert rc == 0  # empty batch
+    assert lib.b200attn_decode_sk_workspace_bytes(0, 32, 8, 128) == 0
 
 
 def test_ops_refuse_cpu_tensors():
