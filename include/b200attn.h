@@ -202,7 +202,9 @@ int b200attn_decode_sk(const void* q, int64_t q_stride, const void* k_cache, con
  * b200attn_kv_dequant_gather: out_k[i] = dtype(k8[kv_indices[i]] * k_mul), out_v[i] =
  *   dtype(v8[kv_indices[i]] * v_mul) for i in [0, n): the 16-bit K/V operand scratch the
  *   extend kernel reads when the pool is fp8 (call b200attn_extend on the scratch with
- *   kv_indices = 0..n-1 and sm_scale * k_descale when k_mul = 1).
+ *   kv_indices = 0..n-1 and sm_scale * k_descale when k_mul = 1).  `n_dev` (nullable, device int32): the live
+ *   row count min(n, *n_dev) is read on the device, so one captured launch sized for the static buffers serves
+ *   every replay (pass &kv_indptr[B]).
  * -------------------------------------------------------------------------- */
 int b200attn_kv_store_fp8(const void* k, const void* v, void* k_cache, void* v_cache,
                           const void* loc, int loc_dtype, int64_t T, int64_t k_row_elems,
@@ -225,7 +227,7 @@ int b200attn_decode_fp8kv(const void* q, int64_t q_stride, const void* k_cache,
 int b200attn_kv_dequant_gather(const void* k_cache, const void* v_cache, int64_t cache_stride,
                                const int32_t* kv_indices, int64_t n, int64_t row_elems,
                                void* out_k, void* out_v, int64_t out_stride, int out_dtype,
-                               float k_mul, float v_mul, void* stream);
+                               float k_mul, float v_mul, const int32_t* n_dev, void* stream);
 
 /* --------------------------------------------------------------------------
  * (a5) Ragged extend / prefill over cached prefix + new tokens.  Replaces

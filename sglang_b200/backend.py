@@ -455,16 +455,19 @@ class B200AttnBackend(_Base):
             if fp8:
                 # the tcgen05 kernel takes 16-bit K/V operands: gather the batch's rows once into a 16-bit scratch
                 # (K exact, k_descale on the score scale; v_descale folded into the V rows), slot ids become 0..n-1
-                if getattr(md, "_graph", False):
-                    raise NotImplementedError("b200 backend: graph-captured extend over an fp8 KV pool")
                 n = md.kv_indices.numel()
                 Hkv = layer.tp_k_head_num
+                graph = getattr(md, "_graph", False)
                 if self._fp8_scratch is None or self._fp8_scratch.shape[1] < n or self._fp8_scratch.dtype != q2.dtype \
                         or self._fp8_scratch.shape[2:] != (Hkv, D):
+                    if torch.cuda.is_current_stream_capturing():
+                        raise RuntimeError("b200 backend: run one eager extend before capturing over an fp8 KV pool")
                     self._fp8_scratch = torch.empty((2, n, Hkv, D), dtype=q2.dtype, device=self.device)
                     self._fp8_iota = torch.arange(n, dtype=torch.int32, device=self.device)
                 ek, ev, eidx = self._fp8_scratch[0], self._fp8_scratch[1], self._fp8_iota
-                ops.kv_dequant_gather(kbuf, vbuf, md.kv_indices, n, ek, ev, 1.0, dsc["v_descale"])
+                # graph mode: the launch covers the static kv_indices buffer, the live row count is kv_indptr[B]
+                ops.kv_dequant_gather(kbuf, vbuf, md.kv_indices, n, ek, ev, 1.0, dsc["v_descale"],
+                                      n_dev=md.kv_indptr[B:B + 1] if graph else None)
                 escale = layer.scaling * dsc["k_descale"]
             ops.extend_attention(q2.view(-1, Hq, D), ek, ev, o.view(-1, Hq, D), md.qo_indptr, md.kv_indptr,
                                  eidx, escale, causal=causal, page_size=self.page_size,

@@ -80,9 +80,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
     kv_dequant_gather_kernel(const uint8_t* __restrict__ k_cache, const uint8_t* __restrict__ v_cache,
                              int64_t cache_stride, const int32_t* __restrict__ kv_indices, int64_t n,
                              int row_elems, uint16_t* __restrict__ out_k, uint16_t* __restrict__ out_v,
-                             int64_t out_stride, float k_mul, float v_mul) {
+                             int64_t out_stride, float k_mul, float v_mul, const int32_t* __restrict__ n_dev) {
   const int lane = threadIdx.x & 31;
   const int64_t warp = (int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+  if (n_dev != nullptr) n = min(n, (int64_t)__ldg(n_dev));  // graph replay: the live row count is device data
   if (warp >= 2 * n) return;
   const int64_t i = warp >> 1;
   const bool is_v = warp & 1;
@@ -154,7 +155,7 @@ extern "C" int b200attn_kv_store_fp8(const void* k, const void* v, void* k_cache
 extern "C" int b200attn_kv_dequant_gather(const void* k_cache, const void* v_cache, int64_t cache_stride,
                                           const int32_t* kv_indices, int64_t n, int64_t row_elems,
                                           void* out_k, void* out_v, int64_t out_stride, int out_dtype,
-                                          float k_mul, float v_mul, void* stream) {
+                                          float k_mul, float v_mul, const int32_t* n_dev, void* stream) {
   using namespace b200attn;
   B2_CHECK_ARG(n >= 0, "kv_dequant_gather: negative n");
   if (n == 0) return B200ATTN_OK;
@@ -172,11 +173,11 @@ extern "C" int b200attn_kv_dequant_gather(const void* k_cache, const void* v_cac
   if (out_dtype == B200ATTN_BF16) {
     kv_dequant_gather_kernel<true, kWarps><<<(unsigned)blocks, kWarps * 32, 0, st>>>(
         (const uint8_t*)k_cache, (const uint8_t*)v_cache, cache_stride, kv_indices, n, (int)row_elems,
-        (uint16_t*)out_k, (uint16_t*)out_v, out_stride, k_mul, v_mul);
+        (uint16_t*)out_k, (uint16_t*)out_v, out_stride, k_mul, v_mul, n_dev);
   } else {
     kv_dequant_gather_kernel<false, kWarps><<<(unsigned)blocks, kWarps * 32, 0, st>>>(
         (const uint8_t*)k_cache, (const uint8_t*)v_cache, cache_stride, kv_indices, n, (int)row_elems,
-        (uint16_t*)out_k, (uint16_t*)out_v, out_stride, k_mul, v_mul);
+        (uint16_t*)out_k, (uint16_t*)out_v, out_stride, k_mul, v_mul, n_dev);
   }
   B2_LAUNCH_CHECK();
   return B200ATTN_OK;

@@ -176,22 +176,24 @@ def store_cache_fp8(
 
 
 def kv_dequant_gather(k_cache: torch.Tensor, v_cache: torch.Tensor, kv_indices: torch.Tensor, n: int,
-                      out_k: torch.Tensor, out_v: torch.Tensor, k_mul: float = 1.0, v_mul: float = 1.0) -> None:
+                      out_k: torch.Tensor, out_v: torch.Tensor, k_mul: float = 1.0, v_mul: float = 1.0,
+                      n_dev: Optional[torch.Tensor] = None) -> None:
     """``out_k[i] = k_cache[kv_indices[i]] * k_mul`` (same for v) from an fp8 pool into 16-bit rows ``[n, Hkv, D]``:
     the K/V operand scratch of extend over an fp8 pool (b200attn_kv_dequant_gather)."""
     _require_cuda(k_cache, v_cache, kv_indices, out_k, out_v)
     kc, vc = _as_bytes(k_cache), _as_bytes(v_cache)
     kc, vc = kc.reshape(kc.shape[0], -1), vc.reshape(vc.shape[0], -1)
     ok, ov = out_k.reshape(out_k.shape[0], -1), out_v.reshape(out_v.shape[0], -1)
-    if kv_indices.dtype != torch.int32:
-        raise TypeError("kv_dequant_gather: kv_indices must be int32")
+    if kv_indices.dtype != torch.int32 or (n_dev is not None and n_dev.dtype != torch.int32):
+        raise TypeError("kv_dequant_gather: kv_indices / n_dev must be int32")
     if ok.shape[0] < n or ov.shape[0] < n or kv_indices.numel() < n:
         raise ValueError("kv_dequant_gather: outputs / indices shorter than n")
     if kc.stride() != vc.stride() or ok.stride() != ov.stride() or ok.shape[1] != kc.shape[1] or ok.dtype != ov.dtype:
         raise ValueError("kv_dequant_gather: K and V must share layouts")
     rc = _lib.load().b200attn_kv_dequant_gather(
         kc.data_ptr(), vc.data_ptr(), kc.stride(0), kv_indices.data_ptr(), int(n), kc.shape[1],
-        ok.data_ptr(), ov.data_ptr(), ok.stride(0), _fdtype(out_k), float(k_mul), float(v_mul), _stream(),
+        ok.data_ptr(), ov.data_ptr(), ok.stride(0), _fdtype(out_k), float(k_mul), float(v_mul), _ptr(n_dev),
+        _stream(),
     )
     check(rc, "b200attn_kv_dequant_gather")
 

@@ -18,7 +18,7 @@ def test_library_exports_every_symbol():
 
 def test_abi_version_and_error_string():
     lib = _lib.load()
-    assert lib.b200attn_abi_version() == _lib.ABI_VERSION == 9
+    assert lib.b200attn_abi_version() == _lib.ABI_VERSION == 10
     assert isinstance(lib.b200attn_last_error(), bytes)
     assert lib.b200attn_decode_workspace_bytes(4, 32, 128, 1) == 0
     assert lib.b200attn_decode_workspace_bytes(4, 32, 128, 3) == 4 * 32 * 3 * 129 * 4 + 4 * 32 * 4
@@ -38,7 +38,7 @@ def test_argument_validation_without_gpu():
     rc = lib.b200attn_kv_store_fp8(None, None, None, None, None, 0, 4, 16, 16, 16, 16, 16, 16, 0, 1.0, 1.0, 8, 0,
                                    None, None)
     assert rc == 1 and b"null pointer" in lib.b200attn_last_error()
-    rc = lib.b200attn_kv_dequant_gather(None, None, 16, None, 0, 16, None, None, 16, 0, 1.0, 1.0, None)
+    rc = lib.b200attn_kv_dequant_gather(None, None, 16, None, 0, 16, None, None, 16, 0, 1.0, 1.0, None, None)
     assert rc == 0
     rc = lib.b200attn_decode_sk(None, 0, None, None, 0, None, 0, None, None, None, None, None, 4, 32, 8, 128, 0,
                                 1.0, 256, -1, 0.0, None, None, 0, None)

@@ -302,3 +302,69 @@ def test_rope_store_fp8_fused_equals_rotate_then_quantising_store(T, Hq, Hkv, D,
     fp8_port.store_kv_fp8(kc, vc, loc, k2.cpu().view(T, Hkv, D), v.view(T, Hkv, D), 0.7, None, skip_index=0)
     assert torch.equal(k8.cpu(), kc), "fused rope + e4m3 store: K pool bytes differ"
     assert torch.equal(v8.cpu(), vc), "fused rope + e4m3 store: V pool bytes differ"
+
+
+def test_backend_fp8_cuda_graph_extend_replay():
+    """Full-graph prefill over an e4m3 pool: ONE captured step (quantising store, device-bounded dequantising gather,
+    extend) replayed over other ragged batches."""
+    Hq, Hkv, D, page, B, TCAP = 8, 2, 128, 16, 4, 1024
+    ks, vs = 0.8, 1.2
+    pre0, ext0 = [64, 0, 300, 17], [200, 128, 40, 333]
+    sc, k8, v8, _, _ = _fp8_scenario([TCAP] * B, [TCAP] * B, Hq, Hkv, D, page, seed=91, ks=ks, vs=vs)
+    backend, pool = _backend(sc, Hkv, D, page, k8, v8)
+    req_pool = backend.req_to_token_pool
+    backend.init_cuda_graph_state(B, TCAP, num_q_heads=Hq, head_dim=D)
+    layer = RadixAttention(Hq, D, sc.scaling, Hkv, 0)
+    layer.k_scale, layer.v_scale, layer.k_scale_float, layer.v_scale_float = torch.tensor(ks), torch.tensor(vs), ks, vs
+    s_req = sc.req_pool_indices.to(DEV)
+    s_seq = torch.zeros(B, dtype=torch.int64, device=DEV)
+    s_pre = torch.zeros(B, dtype=torch.int64, device=DEV)
+    s_ext = torch.zeros(B, dtype=torch.int32, device=DEV)
+    s_loc = torch.zeros(TCAP, dtype=torch.int64, device=DEV)
+    s_q = torch.zeros((TCAP, Hq * D), dtype=torch.bfloat16, device=DEV)
+    s_k = torch.zeros((TCAP, Hkv, D), dtype=torch.bfloat16, device=DEV)
+    s_v = torch.zeros((TCAP, Hkv, D), dtype=torch.bfloat16, device=DEV)
+    fb = ForwardBatch(forward_mode=ForwardMode.EXTEND, batch_size=B, req_pool_indices=s_req, seq_lens=s_seq,
+                      out_cache_loc=s_loc, seq_lens_sum=0, extend_seq_lens=s_ext, extend_prefix_lens=s_pre,
+                      attn_backend=backend)
+
+    def fill(pre, ext, seed):
+        sc2 = make_scenario(pre, ext, Hq, Hkv, D, page, seed=seed, pool_slack=1.0)
+        n = min(req_pool.req_to_token.shape[1], sc2.req_to_token.shape[1])
+        req_pool.req_to_token.zero_()
+        req_pool.req_to_token[:, :n].copy_(sc2.req_to_token[:, :n] % pool.k_buffer[0].shape[0])
+        T = sum(ext)
+        s_seq.copy_(torch.tensor([p + e for p, e in zip(pre, ext)]))
+        s_pre.copy_(torch.tensor(pre))
+        s_ext.copy_(torch.tensor(ext, dtype=torch.int32))
+        loc = torch.cat([req_pool.req_to_token[b + 1, pre[b]:pre[b] + ext[b]] for b in range(B)]).long()
+        s_loc.zero_()
+        s_loc[:T].copy_(loc)
+        s_q.zero_(); s_k.zero_(); s_v.zero_()
+        s_q[:T].copy_(sc2.q); s_k[:T].copy_(sc2.k); s_v[:T].copy_(sc2.v)
+        return T, loc
+
+    fill(pre0, ext0, 91)
+    stream = torch.cuda.Stream()
+    stream.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(stream):
+        md0 = backend.init_forward_metadata_for_breakable_cuda_graph_capture(fb)
+        layer(s_q, s_k, s_v, fb)      # eager warm-up: allocates the 16-bit operand scratch
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=stream):
+            backend.init_forward_metadata_in_graph(fb)
+            s_out = layer(s_q, s_k, s_v, fb)
+    torch.cuda.current_stream().wait_stream(stream)
+
+    for pre, ext, seed in [(pre0, ext0, 92), ([0, 5, 0, 0], [700, 1, 0, 0], 93), ([511, 0, 40, 0], [1, 0, 129, 600], 94)]:
+        T, loc = fill(pre, ext, seed)
+        backend.prepare_forward_metadata_for_breakable_cuda_graph_replay(md0, fb)
+        graph.replay()
+        torch.cuda.synchronize()
+        kc, vc = pool.k_buffer[0], pool.v_buffer[0]
+        assert torch.equal(kc[loc].cpu(), fp8_port.quantize(s_k[:T].cpu(), ks))
+        ref = oracle.attention_fp32(s_q[:T], fp8_port.dequantize(kc, ks), fp8_port.dequantize(vc, vs),
+                                    req_pool.req_to_token, s_req, s_seq.cpu(), s_ext.cpu(), Hq, Hkv, D, sc.scaling,
+                                    causal=True)
+        assert_close_attn(s_out[:T], ref, f"fp8 extend graph replay {ext}")
