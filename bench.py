@@ -402,6 +402,12 @@ def run_b200(args, rank, world, local_rank):
         # configs[1] again over a float8_e4m3fn pool: half the KV bytes per call
         extra["cfg2_decode_fp8kv"] = run_cfg2_decode_fp8(dev, gen, peaks)
         torch.cuda.empty_cache()
+        # configs[2] over the e4m3 pool: quantising store + dequantising gather + extend per layer-call
+        extra["cfg3_extend_fp8kv"] = run_backend_case(
+            dev, gen, peaks, "llama-3.1-8b extend over a float8_e4m3fn KV pool: 32 req x (2048 shared prefix + 512 new), "
+            "causal; layer-call = quantising store + dequantising gather (32 x 2560 rows) + extend",
+            [2048] * 32, [512] * 32, 32, 8, 128, 16, True, "EXTEND", shared_prefix=2048, fp8_kv=True)
+        torch.cuda.empty_cache()
         # configs[4]: Llama-3.1-70B attention shape, this rank's KV-head shard
         extra["cfg5_decode"] = run_cfg5_decode(dev, gen, peaks, world)
         torch.cuda.empty_cache()
@@ -508,7 +514,7 @@ def run_extend_leg(args, dev, gen, peaks):
 
 
 def run_backend_case(dev, gen, peaks, label, prefix_lens, ext_lens, Hq, Hkv, D, page, causal, mode_name,
-                     shared_prefix=0, steps=6, warmup=3):
+                     shared_prefix=0, steps=6, warmup=3, fp8_kv=False):
     """One ragged extend / MIXED layer-call through B200AttnBackend (store + attention), inputs resident in
     HBM.  `shared_prefix` leading tokens of every request map to the SAME physical pages (radix hit).
     FLOPs are algorithmic: 4*D per (q head, query, visible key); rows with extend_len 1 count as bytes."""
@@ -530,9 +536,13 @@ def run_backend_case(dev, gen, peaks, label, prefix_lens, ext_lens, Hq, Hkv, D, 
         table[b + 1, :row.numel()] = row[:ctx]
     req_pool = ReqToTokenPool(B, ctx, dev)
     req_pool.req_to_token.copy_(table.to(dev))
-    kv_pool = MHATokenToKVPool(num_pages * page - page, page, torch.bfloat16, Hkv, D, 1, dev)
+    kv_pool = MHATokenToKVPool(num_pages * page - page, page, torch.float8_e4m3fn if fp8_kv else torch.bfloat16, Hkv,
+                               D, 1, dev)
     for buf in (kv_pool.k_buffer[0], kv_pool.v_buffer[0]):
-        buf.normal_(0, 1)
+        if fp8_kv:  # e4m3 bytes of N(0, 1) values (scale 0.5)
+            buf.copy_(torch.randn(buf.shape, device=dev).mul_(2).to(torch.float8_e4m3fn).view(torch.uint8))
+        else:
+            buf.normal_(0, 1)
         buf[:page].zero_()
     T = sum(ext_lens)
     q = torch.randn((T, Hq * D), device=dev).to(torch.bfloat16)
@@ -542,6 +552,8 @@ def run_backend_case(dev, gen, peaks, label, prefix_lens, ext_lens, Hq, Hkv, D, 
     backend = B200AttnBackend(Runner(dev, req_pool, kv_pool, page))
     layer = RadixAttention(Hq, D, D ** -0.5, Hkv, 0,
                            attn_type=AttentionType.DECODER if causal else AttentionType.ENCODER_ONLY)
+    if fp8_kv:
+        layer.k_scale, layer.v_scale, layer.k_scale_float, layer.v_scale_float = 0.5, 0.5, 0.5, 0.5
     fb = ForwardBatch(forward_mode=ForwardMode[mode_name], batch_size=B,
                       req_pool_indices=torch.arange(1, B + 1, device=dev),
                       seq_lens=torch.tensor(seq, dtype=torch.int64, device=dev), out_cache_loc=loc,
