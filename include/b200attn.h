@@ -229,6 +229,17 @@ int b200attn_kv_dequant_gather(const void* k_cache, const void* v_cache, int64_t
                                void* out_k, void* out_v, int64_t out_stride, int out_dtype,
                                float k_mul, float v_mul, const int32_t* n_dev, void* stream);
 
+/* De-duplicating form: a slot referenced by several rows of kv_indices (a radix-shared prefix) is converted once.
+ * `first_ws` is an int32[num_slots] scratch the call resets itself; out_indices[i] (int32[n]) receives the scratch
+ * row that holds row i's slot (its first referencing row): pass it to b200attn_extend as kv_indices over the scratch.
+ * Rows of out_k / out_v that are not an owner row are left untouched. */
+int b200attn_kv_dequant_gather_unique(const void* k_cache, const void* v_cache, int64_t cache_stride,
+                                      const int32_t* kv_indices, int64_t n, int64_t row_elems,
+                                      void* out_k, void* out_v, int64_t out_stride, int out_dtype,
+                                      float k_mul, float v_mul, const int32_t* n_dev,
+                                      int32_t* first_ws, int64_t num_slots, int32_t* out_indices,
+                                      void* stream);
+
 /* --------------------------------------------------------------------------
  * (a5) Ragged extend / prefill over cached prefix + new tokens.  Replaces
  *   python/sglang/srt/layers/attention/torch_native_backend.py:61-174,279-336

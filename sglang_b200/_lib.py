@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200attn.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "b200attn.h")
 
-ABI_VERSION = 10  # b200attn_abi_version() of the library this binding matches (api.cu)
+ABI_VERSION = 11  # b200attn_abi_version() of the library this binding matches (api.cu)
 BF16, FP16, FP32 = 0, 1, 2
 I32, I64 = 0, 1
 
@@ -63,6 +63,10 @@ SIGNATURES = {
     "b200attn_kv_dequant_gather": (
         C.c_int,
         [_vp, _vp, _i64, _vp, _i64, _i64, _vp, _vp, _i64, C.c_int, _f32, _f32, _vp, _vp],
+    ),
+    "b200attn_kv_dequant_gather_unique": (
+        C.c_int,
+        [_vp, _vp, _i64, _vp, _i64, _i64, _vp, _vp, _i64, C.c_int, _f32, _f32, _vp, _vp, _i64, _vp, _vp],
     ),
     "b200attn_extend_workspace_bytes": (_i64, [_i32, _i64, _i32]),
     "b200attn_extend": (

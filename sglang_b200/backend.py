@@ -107,7 +107,8 @@ class B200AttnBackend(_Base):
         # eager-mode scratch that survives across forwards (grown on demand)
         self._ws: Optional[torch.Tensor] = None
         self._fp8_scratch: Optional[torch.Tensor] = None  # [2, n, Hkv, D] 16-bit K/V operands of extend over an fp8 pool
-        self._fp8_iota: Optional[torch.Tensor] = None
+        self._fp8_iota: Optional[torch.Tensor] = None     # int32 [n]: scratch row of every kv position
+        self._fp8_first: Optional[torch.Tensor] = None    # int32 [slots]: first kv position referencing a slot
         # MIXED batches: the decode rows run on a side stream so that they fill the tail of the persistent extend kernel
         self._side: Optional[torch.cuda.Stream] = None
         self._ws_dec: Optional[torch.Tensor] = None
@@ -463,11 +464,18 @@ class B200AttnBackend(_Base):
                     if torch.cuda.is_current_stream_capturing():
                         raise RuntimeError("b200 backend: run one eager extend before capturing over an fp8 KV pool")
                     self._fp8_scratch = torch.empty((2, n, Hkv, D), dtype=q2.dtype, device=self.device)
-                    self._fp8_iota = torch.arange(n, dtype=torch.int32, device=self.device)
+                    self._fp8_iota = torch.empty(n, dtype=torch.int32, device=self.device)
+                slots = kbuf.shape[0]
+                if self._fp8_first is None or self._fp8_first.numel() < slots:
+                    if torch.cuda.is_current_stream_capturing():
+                        raise RuntimeError("b200 backend: run one eager extend before capturing over an fp8 KV pool")
+                    self._fp8_first = torch.empty(slots, dtype=torch.int32, device=self.device)
                 ek, ev, eidx = self._fp8_scratch[0], self._fp8_scratch[1], self._fp8_iota
-                # graph mode: the launch covers the static kv_indices buffer, the live row count is kv_indptr[B]
-                ops.kv_dequant_gather(kbuf, vbuf, md.kv_indices, n, ek, ev, 1.0, dsc["v_descale"],
-                                      n_dev=md.kv_indptr[B:B + 1] if graph else None)
+                # a slot shared by several requests (radix hit) is converted once; eidx[i] = the scratch row holding
+                # row i's slot.  Graph mode: the launch covers the static kv_indices buffer, the live row count is
+                # kv_indptr[B] on the device
+                ops.kv_dequant_gather_unique(kbuf, vbuf, md.kv_indices, n, ek, ev, self._fp8_first, eidx, 1.0,
+                                             dsc["v_descale"], n_dev=md.kv_indptr[B:B + 1] if graph else None)
                 escale = layer.scaling * dsc["k_descale"]
             ops.extend_attention(q2.view(-1, Hq, D), ek, ev, o.view(-1, Hq, D), md.qo_indptr, md.kv_indptr,
                                  eidx, escale, causal=causal, page_size=self.page_size,

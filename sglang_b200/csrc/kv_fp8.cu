@@ -109,6 +109,61 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
   }
 }
 
+// ---- de-duplicating variant: a slot referenced by several requests (radix-shared prefix) is dequantised ONCE ----
+// first[slot] = smallest row i of kv_indices that references it (atomicMin over a pool-sized int32 map that the
+// launcher resets to 0x7f7f7f7f); row i then reads r = first[slot], publishes out_indices[i] = r and only the
+// owner row (r == i) converts.  The extend kernel reads the scratch through out_indices, so the shared prefix is
+// also shared in L2, exactly as with a 16-bit pool.
+__global__ void kv_first_ref_kernel(const int32_t* __restrict__ kv_indices, int64_t n,
+                                    const int32_t* __restrict__ n_dev, int32_t* __restrict__ first,
+                                    int64_t num_slots) {
+  if (n_dev != nullptr) n = min(n, (int64_t)__ldg(n_dev));
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t slot = kv_indices[i];
+    if (slot >= 0 && slot < num_slots) atomicMin(first + slot, (int32_t)i);
+  }
+}
+
+template <bool kBf16, int kWarpsPerBlock>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+    kv_dequant_gather_unique_kernel(const uint8_t* __restrict__ k_cache, const uint8_t* __restrict__ v_cache,
+                                    int64_t cache_stride, const int32_t* __restrict__ kv_indices, int64_t n,
+                                    int row_elems, uint16_t* __restrict__ out_k, uint16_t* __restrict__ out_v,
+                                    int64_t out_stride, float k_mul, float v_mul, const int32_t* __restrict__ n_dev,
+                                    const int32_t* __restrict__ first, int64_t num_slots,
+                                    int32_t* __restrict__ out_indices) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+  if (n_dev != nullptr) n = min(n, (int64_t)__ldg(n_dev));
+  if (warp >= 2 * n) return;
+  const int64_t i = warp >> 1;
+  const bool is_v = warp & 1;
+  const int64_t slot = kv_indices[i];
+  const bool in_range = slot >= 0 && slot < num_slots;
+  const int64_t r = in_range ? (int64_t)first[slot] : i;
+  if (!is_v && lane == 0) out_indices[i] = (int32_t)r;
+  if (r != i || !in_range) return;  // another row owns this slot's 16-bit copy (out-of-range slots stay unread)
+  const uint8_t* src = (is_v ? v_cache : k_cache) + slot * cache_stride;
+  uint16_t* dst = (is_v ? out_v : out_k) + i * out_stride;
+  const float mul = is_v ? v_mul : k_mul;
+  for (int e = lane * 16; e < row_elems; e += 512) {
+    const uint4 w = *reinterpret_cast<const uint4*>(src + e);
+    const uint32_t ws[4] = {w.x, w.y, w.z, w.w};
+    uint32_t o[8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const __half2_raw lo = __nv_cvt_fp8x2_to_halfraw2((__nv_fp8x2_storage_t)(ws[j] & 0xffff), __NV_E4M3);
+      const __half2_raw hi = __nv_cvt_fp8x2_to_halfraw2((__nv_fp8x2_storage_t)(ws[j] >> 16), __NV_E4M3);
+      const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&lo));
+      const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&hi));
+      o[2 * j] = pack2<kBf16>(a.x * mul, a.y * mul);
+      o[2 * j + 1] = pack2<kBf16>(b.x * mul, b.y * mul);
+    }
+    *reinterpret_cast<uint4*>(dst + e) = make_uint4(o[0], o[1], o[2], o[3]);
+    *reinterpret_cast<uint4*>(dst + e + 8) = make_uint4(o[4], o[5], o[6], o[7]);
+  }
+}
+
 }  // namespace b200attn
 
 extern "C" int b200attn_kv_store_fp8(const void* k, const void* v, void* k_cache, void* v_cache,
@@ -178,6 +233,47 @@ extern "C" int b200attn_kv_dequant_gather(const void* k_cache, const void* v_cac
     kv_dequant_gather_kernel<false, kWarps><<<(unsigned)blocks, kWarps * 32, 0, st>>>(
         (const uint8_t*)k_cache, (const uint8_t*)v_cache, cache_stride, kv_indices, n, (int)row_elems,
         (uint16_t*)out_k, (uint16_t*)out_v, out_stride, k_mul, v_mul, n_dev);
+  }
+  B2_LAUNCH_CHECK();
+  return B200ATTN_OK;
+}
+
+extern "C" int b200attn_kv_dequant_gather_unique(const void* k_cache, const void* v_cache, int64_t cache_stride,
+                                                 const int32_t* kv_indices, int64_t n, int64_t row_elems,
+                                                 void* out_k, void* out_v, int64_t out_stride, int out_dtype,
+                                                 float k_mul, float v_mul, const int32_t* n_dev,
+                                                 int32_t* first_ws, int64_t num_slots, int32_t* out_indices,
+                                                 void* stream) {
+  using namespace b200attn;
+  B2_CHECK_ARG(n >= 0 && n < (1ll << 31), "kv_dequant_gather_unique: bad n");
+  if (n == 0) return B200ATTN_OK;
+  B2_CHECK_ARG(k_cache && v_cache && kv_indices && out_k && out_v && first_ws && out_indices && num_slots > 0,
+               "kv_dequant_gather_unique: null pointer");
+  B2_CHECK_ARG(row_elems > 0 && row_elems % 16 == 0 && row_elems < (1ll << 31) && cache_stride % 16 == 0 &&
+                   out_stride % 8 == 0 && cache_stride >= row_elems && out_stride >= row_elems,
+               "kv_dequant_gather_unique: rows must be multiples of 16 elements with 16-byte aligned strides");
+  B2_CHECK_ARG((((uintptr_t)k_cache | (uintptr_t)v_cache | (uintptr_t)out_k | (uintptr_t)out_v) & 15) == 0,
+               "kv_dequant_gather_unique: tensors must be 16-byte aligned");
+  if (out_dtype != B200ATTN_BF16 && out_dtype != B200ATTN_FP16) B2_UNSUPPORTED("kv_dequant_gather_unique: dtype %d", out_dtype);
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_CUDA(cudaMemsetAsync(first_ws, 0x7f, (size_t)num_slots * sizeof(int32_t), st));
+  {
+    const int64_t blocks = (n + 255) / 256;
+    kv_first_ref_kernel<<<(unsigned)(blocks < 4096 ? blocks : 4096), 256, 0, st>>>(kv_indices, n, n_dev, first_ws,
+                                                                                   num_slots);
+    B2_LAUNCH_CHECK();
+  }
+  constexpr int kWarps = 8;
+  const int64_t blocks = (2 * n + kWarps - 1) / kWarps;
+  B2_CHECK_ARG(blocks < (1ll << 31), "kv_dequant_gather_unique: n too large");
+  if (out_dtype == B200ATTN_BF16) {
+    kv_dequant_gather_unique_kernel<true, kWarps><<<(unsigned)blocks, kWarps * 32, 0, st>>>(
+        (const uint8_t*)k_cache, (const uint8_t*)v_cache, cache_stride, kv_indices, n, (int)row_elems,
+        (uint16_t*)out_k, (uint16_t*)out_v, out_stride, k_mul, v_mul, n_dev, first_ws, num_slots, out_indices);
+  } else {
+    kv_dequant_gather_unique_kernel<false, kWarps><<<(unsigned)blocks, kWarps * 32, 0, st>>>(
+        (const uint8_t*)k_cache, (const uint8_t*)v_cache, cache_stride, kv_indices, n, (int)row_elems,
+        (uint16_t*)out_k, (uint16_t*)out_v, out_stride, k_mul, v_mul, n_dev, first_ws, num_slots, out_indices);
   }
   B2_LAUNCH_CHECK();
   return B200ATTN_OK;

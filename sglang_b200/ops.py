@@ -198,6 +198,33 @@ def kv_dequant_gather(k_cache: torch.Tensor, v_cache: torch.Tensor, kv_indices: 
     check(rc, "b200attn_kv_dequant_gather")
 
 
+def kv_dequant_gather_unique(k_cache: torch.Tensor, v_cache: torch.Tensor, kv_indices: torch.Tensor, n: int,
+                             out_k: torch.Tensor, out_v: torch.Tensor, first_ws: torch.Tensor,
+                             out_indices: torch.Tensor, k_mul: float = 1.0, v_mul: float = 1.0,
+                             n_dev: Optional[torch.Tensor] = None) -> None:
+    """De-duplicating ``kv_dequant_gather``: every referenced slot is converted once, into the scratch row of its
+    first referencing position; ``out_indices[i]`` names that row (b200attn_kv_dequant_gather_unique)."""
+    _require_cuda(k_cache, v_cache, kv_indices, out_k, out_v, first_ws, out_indices)
+    kc, vc = _as_bytes(k_cache), _as_bytes(v_cache)
+    kc, vc = kc.reshape(kc.shape[0], -1), vc.reshape(vc.shape[0], -1)
+    ok, ov = out_k.reshape(out_k.shape[0], -1), out_v.reshape(out_v.shape[0], -1)
+    if any(t.dtype != torch.int32 for t in (kv_indices, first_ws, out_indices)) or \
+            (n_dev is not None and n_dev.dtype != torch.int32):
+        raise TypeError("kv_dequant_gather_unique: index tensors must be int32")
+    if ok.shape[0] < n or ov.shape[0] < n or kv_indices.numel() < n or out_indices.numel() < n:
+        raise ValueError("kv_dequant_gather_unique: outputs / indices shorter than n")
+    if first_ws.numel() < kc.shape[0]:
+        raise ValueError("kv_dequant_gather_unique: first_ws must have one int32 per pool slot")
+    if kc.stride() != vc.stride() or ok.stride() != ov.stride() or ok.shape[1] != kc.shape[1] or ok.dtype != ov.dtype:
+        raise ValueError("kv_dequant_gather_unique: K and V must share layouts")
+    rc = _lib.load().b200attn_kv_dequant_gather_unique(
+        kc.data_ptr(), vc.data_ptr(), kc.stride(0), kv_indices.data_ptr(), int(n), kc.shape[1],
+        ok.data_ptr(), ov.data_ptr(), ok.stride(0), _fdtype(out_k), float(k_mul), float(v_mul), _ptr(n_dev),
+        first_ws.data_ptr(), kc.shape[0], out_indices.data_ptr(), _stream(),
+    )
+    check(rc, "b200attn_kv_dequant_gather_unique")
+
+
 # -------------------------------------------------------------------- rope + store
 ROPE_F32, ROPE_NATIVE = 0, 1
 

@@ -368,3 +368,36 @@ def test_backend_fp8_cuda_graph_extend_replay():
                                     req_pool.req_to_token, s_req, s_seq.cpu(), s_ext.cpu(), Hq, Hkv, D, sc.scaling,
                                     causal=True)
         assert_close_attn(s_out[:T], ref, f"fp8 extend graph replay {ext}")
+
+
+def test_dequant_gather_unique_shares_rows():
+    """Every referenced slot is converted once, into the row of its first reference; out_indices names that row."""
+    g = torch.Generator().manual_seed(0)
+    k8 = torch.randint(0, 256, (300, 4, 128), dtype=torch.uint8, generator=g)
+    k8[(k8 & 0x7F) == 0x7F] = 0
+    v8 = k8.flip(0).contiguous()
+    idx = torch.randint(0, 300, (1000,), generator=g).int()           # many repeated slots
+    ok = torch.full((1000, 4, 128), float("nan"), dtype=torch.bfloat16, device=DEV)
+    ov = torch.full_like(ok, float("nan"))
+    first = torch.empty(300, dtype=torch.int32, device=DEV)
+    out_idx = torch.full((1000,), -1, dtype=torch.int32, device=DEV)
+    for _ in range(2):   # the call resets its own first-reference map
+        ops.kv_dequant_gather_unique(k8.to(DEV), v8.to(DEV).view(FP8), idx.to(DEV), 1000, ok, ov, first, out_idx,
+                                     1.0, 0.75)
+    torch.cuda.synchronize()
+    want_first = {}
+    for i, s_ in enumerate(idx.tolist()):
+        want_first.setdefault(s_, i)
+    want_idx = torch.tensor([want_first[s_] for s_ in idx.tolist()], dtype=torch.int32)
+    assert torch.equal(out_idx.cpu(), want_idx)
+    rows = out_idx.long()
+    assert torch.equal(ok[rows].cpu().float(), fp8_port.dequantize(k8)[idx.long()])
+    assert torch.equal(ov[rows].cpu(), (fp8_port.dequantize(v8)[idx.long()] * 0.75).to(torch.bfloat16))
+    owners = torch.zeros(1000, dtype=torch.bool)
+    owners[want_idx.long()] = True
+    assert torch.isnan(ok.cpu()[~owners].float()).all()               # non-owner rows were not written
+    # device-side bound: only the first 10 rows are live
+    out_idx.fill_(-1)
+    ops.kv_dequant_gather_unique(k8.to(DEV), v8.to(DEV), idx.to(DEV), 1000, ok, ov, first, out_idx, 1.0, 0.75,
+                                 n_dev=torch.tensor([10], dtype=torch.int32, device=DEV))
+    assert (out_idx[10:] == -1).all() and (out_idx[:10] >= 0).all()
