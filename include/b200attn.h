@@ -179,6 +179,16 @@ int b200attn_decode_sk(const void* q, int64_t q_stride, const void* k_cache, con
                        float logit_cap, const float* sinks, void* workspace,
                        int64_t workspace_bytes, void* stream);
 
+/* b200attn_decode_sk over an e4m3 byte pool (the byte path of b200attn_decode_fp8kv, 3 CTAs per SM). */
+int b200attn_decode_sk_fp8kv(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache,
+                             int64_t kv_stride, void* o, int64_t o_stride, float* lse,
+                             const int32_t* kv_indptr, const int32_t* kv_indices,
+                             const int32_t* q_rows, const int32_t* req_ids, int32_t B, int32_t Hq,
+                             int32_t Hkv, int32_t D, int dtype, float sm_scale, float k_descale,
+                             float v_descale, int32_t min_chunk, int32_t window_left, float logit_cap,
+                             const float* sinks, void* workspace, int64_t workspace_bytes,
+                             void* stream);
+
 /* --------------------------------------------------------------------------
  * (f4) FP8 (e4m3) KV cache.  Pool dtype float8_e4m3fn stored as bytes
  *   python/sglang/srt/mem_cache/memory_pool.py:2365-2375 (div by k_scale/v_scale in

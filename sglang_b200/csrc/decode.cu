@@ -332,66 +332,6 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodePara
 //   * e4m3 -> f16 is exact and branch-free: (b & 0x7f) << 7 reinterpreted as f16 is value * 2^-8
 //     (denormals included), so the mma runs in f16 (bf16 queries are converted once; P in f16) and the
 //     2^8 goes into the score scale with k_descale, and into the output scale with v_descale.
-// kFp8HwCvt: cvt.rn.f16x2.e4m3x2 (SASS F2FP.F16.E4M3.UNPACK_B, one instruction per pair, true values) instead of
-// the 4-instruction bit trick (value * 2^-8).  kFp8Bias is the factor the scales must carry.
-#ifndef B200ATTN_FP8_HWCVT
-#define B200ATTN_FP8_HWCVT 1
-#endif
-constexpr bool kFp8HwCvt = B200ATTN_FP8_HWCVT != 0;
-constexpr float kFp8Bias = kFp8HwCvt ? 1.f : 256.f;
-
-__device__ __forceinline__ uint32_t e4m3x2_lo(uint32_t w) {  // bytes 0,1 -> f16x2
-  uint32_t r;
-  asm("{ .reg .b16 lo, hi; mov.b32 {lo, hi}, %1; cvt.rn.f16x2.e4m3x2 %0, lo; }" : "=r"(r) : "r"(w));
-  return r;
-}
-__device__ __forceinline__ uint32_t e4m3x2_hi(uint32_t w) {  // bytes 2,3 -> f16x2
-  uint32_t r;
-  asm("{ .reg .b16 lo, hi; mov.b32 {lo, hi}, %1; cvt.rn.f16x2.e4m3x2 %0, hi; }" : "=r"(r) : "r"(w));
-  return r;
-}
-__device__ __forceinline__ uint32_t e4m3x2_trick(uint32_t w, uint32_t sel) {
-  const uint32_t t = __byte_perm(w, 0u, sel);  // the two selected bytes in the high byte of each half
-  return (t & 0x80008000u) | ((t & 0x7f007f00u) >> 1);
-}
-// K word (4 consecutive d of one key): {d0,d1} and {d2,d3}
-__device__ __forceinline__ void e4m3x4_pairs(uint32_t w, uint32_t& a, uint32_t& b) {
-  if constexpr (kFp8HwCvt) {
-    a = e4m3x2_lo(w);
-    b = e4m3x2_hi(w);
-  } else {
-    a = e4m3x2_trick(w, 0x1404);
-    b = e4m3x2_trick(w, 0x3424);
-  }
-}
-// V word (byte0 = V[k0][d], byte1 = V[k0][d+1], byte2 = V[k0+1][d], byte3 = V[k0+1][d+1]): {k0,k0+1} at d and at d+1
-__device__ __forceinline__ void e4m3x4_cross(uint32_t w, uint32_t& even, uint32_t& odd) {
-  if constexpr (kFp8HwCvt) {
-    const uint32_t t = __byte_perm(w, 0u, 0x3120);
-    even = e4m3x2_lo(t);
-    odd = e4m3x2_hi(t);
-  } else {
-    even = e4m3x2_trick(w, 0x2404);
-    odd = e4m3x2_trick(w, 0x3414);
-  }
-}
-
-template <int D>
-__device__ __forceinline__ uint32_t swz8_off(int row, int chunk) {
-  // byte offset of 16-byte chunk `chunk` of row `row` in a [rows][D] 1-byte tile (row pitch D bytes)
-  constexpr int kChunks = D / 16;
-  const int x = (kChunks >= 8) ? (row & 7) : ((row >> 1) & (kChunks - 1));
-  return (uint32_t)(row * D + ((chunk ^ x) << 4));
-}
-
-#ifndef B200ATTN_FP8_STAGES
-#define B200ATTN_FP8_STAGES 4
-#endif
-#ifndef B200ATTN_FP8_CTAS
-#define B200ATTN_FP8_CTAS 3
-#endif
-constexpr int kDec8Stages = B200ATTN_FP8_STAGES;  // 4 x 16 KB per CTA, 3 CTAs per SM: 144 KB of loads in flight per SM
-
 template <int D, bool kBf16>
 __global__ void __launch_bounds__(kDecThreads, B200ATTN_FP8_CTAS) decode_fp8_kernel(const DecodeParams p) {
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;

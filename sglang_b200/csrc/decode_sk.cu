@@ -40,12 +40,18 @@ __device__ __forceinline__ int sk_owner(int64_t g, int64_t T, int N) {
   return (int)(((g + 1) * N - 1) / T);
 }
 
-template <int D, bool kBf16>
-__global__ void __launch_bounds__(kDecThreads, 2) decode_sk_kernel(const DecodeParams p, const int min_tiles) {
+// kFp8: e4m3 pool (rows of D bytes, the byte path of decode_fp8_kernel: permuted-k ldmatrix, hardware e4m3 -> f16,
+// f16 mma, 4 stages x 3 CTAs per SM); otherwise the 16-bit path of decode_kernel.
+template <int D, bool kBf16, bool kFp8>
+__global__ void __launch_bounds__(kDecThreads, kFp8 ? B200ATTN_FP8_CTAS : 2)
+    decode_sk_kernel(const DecodeParams p, const int min_tiles) {
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
-  constexpr int kChunks = D / 8;
-  constexpr int kTileBytes = kDecTile * D * 2;
+  constexpr int kEsz = kFp8 ? 1 : 2;                 // pool bytes per element
+  constexpr int kChunks = D * kEsz / 16;             // 16-byte chunks per row
+  constexpr int kTileBytes = kDecTile * D * kEsz;
   constexpr int kStageBytes = 2 * kTileBytes;
+  constexpr int kStages = kFp8 ? kDec8Stages : kDecStages;
+  constexpr bool kMmaBf16 = kBf16 && !kFp8;          // the fp8 path multiplies in f16
   constexpr int kLoadsPerThread = kDecTile * kChunks / kDecThreads;
   constexpr int kRowsPerPass = kDecThreads / kChunks;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -106,7 +112,7 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_sk_kernel(const DecodeP
 
   const int ld_chunk = tid % kChunks;
   const int ld_row0 = tid / kChunks;
-  const int64_t row_bytes = p.kv_stride * 2;
+  const int64_t row_bytes = p.kv_stride * kEsz;
   const uint32_t smem_base = smem_u32(smem);
   const int lm = lane >> 3, lr = lane & 7;
   float* sm_o = reinterpret_cast<float*>(smem);  // [4][16][D]   (aliases the ring between segments)
@@ -136,19 +142,24 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_sk_kernel(const DecodeP
     uint32_t qf[D / 16][4];
     {
       const T* qbase = reinterpret_cast<const T*>(p.q) + (int64_t)qrow * p.q_stride + (int64_t)h0 * D;
-      const int r0 = lane >> 2, c0 = (lane & 3) * 2;
+      const int r0 = lane >> 2, c0 = (lane & 3) * (kFp8 ? 4 : 2);
 #pragma unroll
       for (int ks = 0; ks < D / 16; ++ks) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const int r = r0 + (j & 1) * 8;
-          const int cc = ks * 16 + c0 + (j >> 1) * 8;
-          qf[ks][j] = (r < gcount) ? *reinterpret_cast<const uint32_t*>(qbase + (int64_t)r * D + cc) : 0u;
+          const int cc = ks * 16 + c0 + (j >> 1) * (kFp8 ? 2 : 8);  // fp8: contraction index permuted (decode.cu)
+          uint32_t w = (r < gcount) ? *reinterpret_cast<const uint32_t*>(qbase + (int64_t)r * D + cc) : 0u;
+          if constexpr (kFp8 && kBf16) {
+            const float2 f = unpack2<true>(w);
+            w = pack2<false>(f.x, f.y);
+          }
+          qf[ks][j] = w;
         }
       }
     }
-    const uint8_t* kc = reinterpret_cast<const uint8_t*>(p.k_cache) + (int64_t)kvh * D * 2 + ld_chunk * 16;
-    const uint8_t* vc = reinterpret_cast<const uint8_t*>(p.v_cache) + (int64_t)kvh * D * 2 + ld_chunk * 16;
+    const uint8_t* kc = reinterpret_cast<const uint8_t*>(p.k_cache) + (int64_t)kvh * D * kEsz + ld_chunk * 16;
+    const uint8_t* vc = reinterpret_cast<const uint8_t*>(p.v_cache) + (int64_t)kvh * D * kEsz + ld_chunk * 16;
     const int32_t* idx = p.kv_indices + it.kv_beg;
 
     int32_t slots[kLoadsPerThread];
@@ -166,7 +177,7 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_sk_kernel(const DecodeP
 #pragma unroll
       for (int i = 0; i < kLoadsPerThread; ++i) {
         const int row = ld_row0 + i * kRowsPerPass;
-        const uint32_t off = swz_off<D>(row, ld_chunk);
+        const uint32_t off = kFp8 ? swz8_off<D>(row, ld_chunk) : swz_off<D>(row, ld_chunk);
         const bool ok = slots[i] >= 0;
         const int64_t g = ok ? (int64_t)slots[i] * row_bytes : 0;
         cp_async16(ks + off, kc + g, ok ? 16 : 0);
@@ -176,7 +187,7 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_sk_kernel(const DecodeP
 
     fetch_slots(0);
 #pragma unroll
-    for (int s = 0; s < kDecStages - 1; ++s) {
+    for (int s = 0; s < kStages - 1; ++s) {
       if (s < ntiles) issue_tile(s);
       cp_async_commit();
       fetch_slots(s + 1);
@@ -189,27 +200,43 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_sk_kernel(const DecodeP
     float l_run[2] = {0.f, 0.f};
 
     for (int t = 0; t < ntiles; ++t) {
-      cp_async_wait<kDecStages - 2>();
+      cp_async_wait<kStages - 2>();
       __syncthreads();
       {
-        const int nt = t + kDecStages - 1;
-        if (nt < ntiles) issue_tile(nt % kDecStages);
+        const int nt = t + kStages - 1;
+        if (nt < ntiles) issue_tile(nt % kStages);
         cp_async_commit();
         fetch_slots(nt + 1);
       }
-      const uint32_t ks = smem_base + (t % kDecStages) * kStageBytes;
+      const uint32_t ks = smem_base + (t % kStages) * kStageBytes;
       const uint32_t vs = ks + kTileBytes;
       const int key0 = k_lo + t * kDecTile + warp * 16;
       if (key0 < k_hi) {
         float s[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
         {
           const int krow = warp * 16 + (lm >> 1) * 8 + lr;
+          if constexpr (kFp8) {
 #pragma unroll
-          for (int ksp = 0; ksp < D / 16; ++ksp) {
-            uint32_t b0, b1, b2, b3;
-            ldmatrix_x4(b0, b1, b2, b3, ks + swz_off<D>(krow, 2 * ksp + (lm & 1)));
-            mma_16816<kBf16>(s[0], qf[ksp], b0, b1);
-            mma_16816<kBf16>(s[1], qf[ksp], b2, b3);
+            for (int kp = 0; kp < D / 32; ++kp) {
+              uint32_t m0, m1, m2, m3, a, b;
+              ldmatrix_x4(m0, m1, m2, m3, ks + swz8_off<D>(krow, 2 * kp + (lm & 1)));
+              e4m3x4_pairs(m0, a, b);
+              mma_16816<false>(s[0], qf[2 * kp], a, b);
+              e4m3x4_pairs(m1, a, b);
+              mma_16816<false>(s[0], qf[2 * kp + 1], a, b);
+              e4m3x4_pairs(m2, a, b);
+              mma_16816<false>(s[1], qf[2 * kp], a, b);
+              e4m3x4_pairs(m3, a, b);
+              mma_16816<false>(s[1], qf[2 * kp + 1], a, b);
+            }
+          } else {
+#pragma unroll
+            for (int ksp = 0; ksp < D / 16; ++ksp) {
+              uint32_t b0, b1, b2, b3;
+              ldmatrix_x4(b0, b1, b2, b3, ks + swz_off<D>(krow, 2 * ksp + (lm & 1)));
+              mma_16816<kMmaBf16>(s[0], qf[ksp], b0, b1);
+              mma_16816<kMmaBf16>(s[1], qf[ksp], b2, b3);
+            }
           }
         }
         const int kcol = key0 + (lane & 3) * 2;
@@ -244,24 +271,52 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_sk_kernel(const DecodeP
           const float p3 = fast_exp2(s[nb][3] - m_run[1]);
           l_run[0] += p0 + p1;
           l_run[1] += p2 + p3;
-          pf[nb * 2 + 0] = pack2<kBf16>(p0, p1);
-          pf[nb * 2 + 1] = pack2<kBf16>(p2, p3);
+          pf[nb * 2 + 0] = pack2<kMmaBf16>(p0, p1);
+          pf[nb * 2 + 1] = pack2<kMmaBf16>(p2, p3);
         }
         const int vrow = warp * 16 + (lm & 1) * 8 + lr;
+        if constexpr (kFp8) {
+          const bool rescale = __any_sync(0xffffffffu, alpha[0] != 1.f || alpha[1] != 1.f);
 #pragma unroll
-        for (int np = 0; np < D / 16; ++np) {
-          uint32_t b0, b1, b2, b3;
-          ldmatrix_x4_trans(b0, b1, b2, b3, vs + swz_off<D>(vrow, 2 * np + (lm >> 1)));
+          for (int np = 0; np < D / 32; ++np) {
+            uint32_t m0, m1, m2, m3;
+            ldmatrix_x4_trans(m0, m1, m2, m3, vs + swz8_off<D>(vrow, 2 * np + (lm >> 1)));
+            if (rescale) {
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            float(&acc)[4] = o_acc[2 * np + h];
-            acc[0] *= alpha[0];
-            acc[1] *= alpha[0];
-            acc[2] *= alpha[1];
-            acc[3] *= alpha[1];
+              for (int h = 0; h < 4; ++h) {
+                float(&acc)[4] = o_acc[4 * np + h];
+                acc[0] *= alpha[0];
+                acc[1] *= alpha[0];
+                acc[2] *= alpha[1];
+                acc[3] *= alpha[1];
+              }
+            }
+            uint32_t e0, o0, e1, o1;
+            e4m3x4_cross(m0, e0, o0);
+            e4m3x4_cross(m1, e1, o1);
+            mma_16816<false>(o_acc[4 * np + 0], pf, e0, e1);
+            mma_16816<false>(o_acc[4 * np + 1], pf, o0, o1);
+            e4m3x4_cross(m2, e0, o0);
+            e4m3x4_cross(m3, e1, o1);
+            mma_16816<false>(o_acc[4 * np + 2], pf, e0, e1);
+            mma_16816<false>(o_acc[4 * np + 3], pf, o0, o1);
           }
-          mma_16816<kBf16>(o_acc[2 * np], pf, b0, b1);
-          mma_16816<kBf16>(o_acc[2 * np + 1], pf, b2, b3);
+        } else {
+#pragma unroll
+          for (int np = 0; np < D / 16; ++np) {
+            uint32_t b0, b1, b2, b3;
+            ldmatrix_x4_trans(b0, b1, b2, b3, vs + swz_off<D>(vrow, 2 * np + (lm >> 1)));
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              float(&acc)[4] = o_acc[2 * np + h];
+              acc[0] *= alpha[0];
+              acc[1] *= alpha[0];
+              acc[2] *= alpha[1];
+              acc[3] *= alpha[1];
+            }
+            mma_16816<kMmaBf16>(o_acc[2 * np], pf, b0, b1);
+            mma_16816<kMmaBf16>(o_acc[2 * np + 1], pf, b2, b3);
+          }
         }
       }
     }
@@ -275,12 +330,25 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_sk_kernel(const DecodeP
       l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
     }
     {
-      const int r0 = lane >> 2, c0 = (lane & 3) * 2;
+      const int r0 = lane >> 2;
+      if constexpr (kFp8) {  // a lane owns 4 consecutive dims per 16-d chunk (decode_fp8_kernel's layout)
+        const int c0 = (lane & 3) * 4;
 #pragma unroll
-      for (int n = 0; n < D / 8; ++n) {
-        float* dst = sm_o + (warp * 16 + r0) * D + n * 8 + c0;
-        *reinterpret_cast<float2*>(dst) = make_float2(o_acc[n][0], o_acc[n][1]);
-        *reinterpret_cast<float2*>(dst + 8 * D) = make_float2(o_acc[n][2], o_acc[n][3]);
+        for (int cch = 0; cch < D / 16; ++cch) {
+          float* dst = sm_o + (warp * 16 + r0) * D + cch * 16 + c0;
+          *reinterpret_cast<float4*>(dst) =
+              make_float4(o_acc[2 * cch][0], o_acc[2 * cch + 1][0], o_acc[2 * cch][1], o_acc[2 * cch + 1][1]);
+          *reinterpret_cast<float4*>(dst + 8 * D) =
+              make_float4(o_acc[2 * cch][2], o_acc[2 * cch + 1][2], o_acc[2 * cch][3], o_acc[2 * cch + 1][3]);
+        }
+      } else {
+        const int c0 = (lane & 3) * 2;
+#pragma unroll
+        for (int n = 0; n < D / 8; ++n) {
+          float* dst = sm_o + (warp * 16 + r0) * D + n * 8 + c0;
+          *reinterpret_cast<float2*>(dst) = make_float2(o_acc[n][0], o_acc[n][1]);
+          *reinterpret_cast<float2*>(dst + 8 * D) = make_float2(o_acc[n][2], o_acc[n][3]);
+        }
       }
       if ((lane & 3) == 0) {
         sm_m[warp * 16 + r0] = m_run[0];
@@ -310,7 +378,7 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_sk_kernel(const DecodeP
         l += f * sm_l[w * 16 + r];
       }
       if (whole && p.sinks != nullptr && l > 0.f) l += fast_exp2(__ldg(p.sinks + h0 + r) * kLog2e - m);
-      const float inv = (l > 0.f) ? 1.f / l : 0.f;
+      const float inv = (l > 0.f) ? p.out_scale / l : 0.f;  // out_scale: v_descale for e4m3 pools, else 1
       acc.x *= inv;
       acc.y *= inv;
       acc.z *= inv;
@@ -389,23 +457,24 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_sk_kernel(const DecodeP
   }
 }
 
-template <int D, bool kBf16>
+template <int D, bool kBf16, bool kFp8>
 static int launch_decode_sk(const DecodeParams& p, int ctas, int min_tiles, cudaStream_t st) {
-  constexpr int kRing = kDecStages * 2 * kDecTile * D * 2;
+  constexpr int kRing = (kFp8 ? kDec8Stages : kDecStages) * 2 * kDecTile * D * (kFp8 ? 1 : 2);
   constexpr int kMerge = (4 * 16 * D + 128) * 4;
   constexpr int kSmem = kRing > kMerge ? kRing : kMerge;
   static bool configured = false;
   if (!configured) {
-    B2_CUDA(cudaFuncSetAttribute(decode_sk_kernel<D, kBf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-    B2_CUDA(cudaFuncSetAttribute(decode_sk_kernel<D, kBf16>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    B2_CUDA(cudaFuncSetAttribute(decode_sk_kernel<D, kBf16, kFp8>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+    B2_CUDA(cudaFuncSetAttribute(decode_sk_kernel<D, kBf16, kFp8>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     configured = true;
   }
-  decode_sk_kernel<D, kBf16><<<ctas, kDecThreads, kSmem, st>>>(p, min_tiles);
+  decode_sk_kernel<D, kBf16, kFp8><<<ctas, kDecThreads, kSmem, st>>>(p, min_tiles);
   B2_LAUNCH_CHECK();
   return B200ATTN_OK;
 }
 
-static int sk_ctas() { return 2 * sm_count(); }
+static int sk_ctas(bool fp8) { return (fp8 ? B200ATTN_FP8_CTAS : 2) * sm_count(); }
+static int sk_ctas_cap() { return sk_ctas(true) > sk_ctas(false) ? sk_ctas(true) : sk_ctas(false); }  // workspace layout
 
 }  // namespace b200attn
 
@@ -414,16 +483,16 @@ extern "C" int64_t b200attn_decode_sk_workspace_bytes(int32_t B, int32_t Hq, int
   if (B <= 0 || Hq <= 0 || Hkv <= 0) return 0;
   const int groups = (Hq / Hkv + kDecMaxG - 1) / kDecMaxG;
   // two partial slots per CTA ([16][D] fp32 + [16] lse) + one arrival counter per unit
-  return (int64_t)sk_ctas() * 2 * kDecMaxG * (D + 1) * 4 + (int64_t)B * Hkv * groups * 4;
+  return (int64_t)sk_ctas_cap() * 2 * kDecMaxG * (D + 1) * 4 + (int64_t)B * Hkv * groups * 4;
 }
 
-extern "C" int b200attn_decode_sk(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache,
-                                  int64_t kv_stride, void* o, int64_t o_stride, float* lse,
-                                  const int32_t* kv_indptr, const int32_t* kv_indices, const int32_t* q_rows,
-                                  const int32_t* req_ids, int32_t B, int32_t Hq, int32_t Hkv, int32_t D,
-                                  int dtype, float sm_scale, int32_t min_chunk, int32_t window_left,
-                                  float logit_cap, const float* sinks, void* workspace,
-                                  int64_t workspace_bytes, void* stream) {
+static int decode_sk_impl(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache,
+                          int64_t kv_stride, void* o, int64_t o_stride, float* lse,
+                          const int32_t* kv_indptr, const int32_t* kv_indices, const int32_t* q_rows,
+                          const int32_t* req_ids, int32_t B, int32_t Hq, int32_t Hkv, int32_t D,
+                          int dtype, float sm_scale, int32_t min_chunk, int32_t window_left,
+                          float logit_cap, const float* sinks, void* workspace,
+                          int64_t workspace_bytes, void* stream, bool fp8, float k_descale, float v_descale) {
   using namespace b200attn;
   B2_CHECK_ARG(B >= 0, "decode_sk: negative batch");
   B2_CHECK_ARG(logit_cap >= 0.f, "decode_sk: negative logit_cap");
@@ -431,8 +500,9 @@ extern "C" int b200attn_decode_sk(const void* q, int64_t q_stride, const void* k
   B2_CHECK_ARG(q && k_cache && v_cache && o && kv_indptr && kv_indices, "decode_sk: null pointer");
   B2_CHECK_ARG(Hq > 0 && Hkv > 0 && Hq % Hkv == 0, "decode_sk: Hq=%d must be a multiple of Hkv=%d", Hq, Hkv);
   B2_CHECK_ARG(min_chunk >= 1, "decode_sk: bad min_chunk");
-  B2_CHECK_ARG(q_stride % 8 == 0 && kv_stride % 8 == 0 && o_stride % 4 == 0,
+  B2_CHECK_ARG(q_stride % 8 == 0 && kv_stride % (fp8 ? 16 : 8) == 0 && o_stride % 4 == 0,
                "decode_sk: strides must keep rows 16-byte aligned");
+  B2_CHECK_ARG(!fp8 || (k_descale > 0.f && v_descale > 0.f), "decode_sk: fp8 descales must be positive");
   B2_CHECK_ARG((((uintptr_t)q | (uintptr_t)k_cache | (uintptr_t)v_cache | (uintptr_t)o) & 15) == 0,
                "decode_sk: tensors must be 16-byte aligned");
   if (dtype != B200ATTN_BF16 && dtype != B200ATTN_FP16) B2_UNSUPPORTED("decode_sk: dtype %d", dtype);
@@ -440,7 +510,8 @@ extern "C" int b200attn_decode_sk(const void* q, int64_t q_stride, const void* k
   const int64_t need = b200attn_decode_sk_workspace_bytes(B, Hq, Hkv, D);
   B2_CHECK_ARG(workspace && workspace_bytes >= need, "decode_sk: workspace too small (%lld < %lld)",
                (long long)workspace_bytes, (long long)need);
-  const int ctas = sk_ctas();
+  const int ctas = sk_ctas(fp8);
+  const int cap = sk_ctas_cap();
   DecodeParams p;
   p.q = q;
   p.k_cache = k_cache;
@@ -452,8 +523,8 @@ extern "C" int b200attn_decode_sk(const void* q, int64_t q_stride, const void* k
   p.q_rows = q_rows;
   p.req_ids = req_ids;
   p.ws_o = reinterpret_cast<float*>(workspace);
-  p.ws_lse = p.ws_o + (int64_t)ctas * 2 * kDecMaxG * D;
-  p.ws_cnt = reinterpret_cast<int*>(p.ws_lse + (int64_t)ctas * 2 * kDecMaxG);
+  p.ws_lse = p.ws_o + (int64_t)cap * 2 * kDecMaxG * D;
+  p.ws_cnt = reinterpret_cast<int*>(p.ws_lse + (int64_t)cap * 2 * kDecMaxG);
   p.q_stride = q_stride;
   p.kv_stride = kv_stride;
   p.o_stride = o_stride;
@@ -464,19 +535,49 @@ extern "C" int b200attn_decode_sk(const void* q, int64_t q_stride, const void* k
   p.groups_per_kvh = (p.G + kDecMaxG - 1) / kDecMaxG;
   p.max_splits = 1;
   p.min_chunk = min_chunk;
+  if (fp8) sm_scale *= k_descale * kFp8Bias;
   p.scale_log2 = sm_scale * kLog2e;
   p.window_left = window_left;
   p.cap_pre = logit_cap > 0.f ? sm_scale / logit_cap : 0.f;
   p.cap_post = logit_cap > 0.f ? logit_cap * kLog2e : 0.f;
   p.sinks = sinks;
   p.tail_begin = -1;
-  p.out_scale = 1.f;
+  p.out_scale = fp8 ? v_descale * kFp8Bias : 1.f;
   const int min_tiles = (min_chunk + kDecTile - 1) / kDecTile;
   cudaStream_t st = (cudaStream_t)stream;
-  if (D == 128) {
-    return dtype == B200ATTN_BF16 ? launch_decode_sk<128, true>(p, ctas, min_tiles, st)
-                                  : launch_decode_sk<128, false>(p, ctas, min_tiles, st);
+#define B2_SK(DD, FP8)                                                                          \
+  return dtype == B200ATTN_BF16 ? launch_decode_sk<DD, true, FP8>(p, ctas, min_tiles, st)      \
+                                : launch_decode_sk<DD, false, FP8>(p, ctas, min_tiles, st)
+  if (fp8) {
+    if (D == 128) B2_SK(128, true);
+    B2_SK(64, true);
   }
-  return dtype == B200ATTN_BF16 ? launch_decode_sk<64, true>(p, ctas, min_tiles, st)
-                                : launch_decode_sk<64, false>(p, ctas, min_tiles, st);
+  if (D == 128) B2_SK(128, false);
+  B2_SK(64, false);
+#undef B2_SK
+}
+
+extern "C" int b200attn_decode_sk(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache,
+                                  int64_t kv_stride, void* o, int64_t o_stride, float* lse,
+                                  const int32_t* kv_indptr, const int32_t* kv_indices, const int32_t* q_rows,
+                                  const int32_t* req_ids, int32_t B, int32_t Hq, int32_t Hkv, int32_t D,
+                                  int dtype, float sm_scale, int32_t min_chunk, int32_t window_left,
+                                  float logit_cap, const float* sinks, void* workspace,
+                                  int64_t workspace_bytes, void* stream) {
+  return decode_sk_impl(q, q_stride, k_cache, v_cache, kv_stride, o, o_stride, lse, kv_indptr, kv_indices, q_rows,
+                        req_ids, B, Hq, Hkv, D, dtype, sm_scale, min_chunk, window_left, logit_cap, sinks, workspace,
+                        workspace_bytes, stream, false, 1.f, 1.f);
+}
+
+extern "C" int b200attn_decode_sk_fp8kv(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache,
+                                        int64_t kv_stride, void* o, int64_t o_stride, float* lse,
+                                        const int32_t* kv_indptr, const int32_t* kv_indices,
+                                        const int32_t* q_rows, const int32_t* req_ids, int32_t B, int32_t Hq,
+                                        int32_t Hkv, int32_t D, int dtype, float sm_scale, float k_descale,
+                                        float v_descale, int32_t min_chunk, int32_t window_left, float logit_cap,
+                                        const float* sinks, void* workspace, int64_t workspace_bytes,
+                                        void* stream) {
+  return decode_sk_impl(q, q_stride, k_cache, v_cache, kv_stride, o, o_stride, lse, kv_indptr, kv_indices, q_rows,
+                        req_ids, B, Hq, Hkv, D, dtype, sm_scale, min_chunk, window_left, logit_cap, sinks, workspace,
+                        workspace_bytes, stream, true, k_descale, v_descale);
 }

@@ -558,6 +558,16 @@ def decode_attention(
     if kv_indptr.dtype != torch.int32 or kv_indices.dtype != torch.int32:
         raise TypeError("decode_attention: kv_indptr / kv_indices must be int32")
     ws_bytes = 0 if workspace is None else workspace.numel() * workspace.element_size()
+    if fp8 and stream_k:
+        rc = _lib.load().b200attn_decode_sk_fp8kv(
+            q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
+            o.data_ptr(), o.stride(0), _ptr(lse), kv_indptr.data_ptr(), kv_indices.data_ptr(),
+            _ptr(q_rows), _ptr(req_ids), B, Hq, Hkv, D, _fdtype(q), float(sm_scale), float(k_descale),
+            float(v_descale), min_chunk, int(window_left), float(logit_cap), _sinks_ptr(sinks, Hq), _ptr(workspace),
+            ws_bytes, _stream(),
+        )
+        check(rc, "b200attn_decode_sk_fp8kv")
+        return o
     if fp8:
         rc = _lib.load().b200attn_decode_fp8kv(
             q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),

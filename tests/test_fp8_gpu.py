@@ -401,3 +401,29 @@ def test_dequant_gather_unique_shares_rows():
     ops.kv_dequant_gather_unique(k8.to(DEV), v8.to(DEV), idx.to(DEV), 1000, ok, ov, first, out_idx, 1.0, 0.75,
                                  n_dev=torch.tensor([10], dtype=torch.int32, device=DEV))
     assert (out_idx[10:] == -1).all() and (out_idx[:10] >= 0).all()
+
+
+@pytest.mark.parametrize("Hq,Hkv,D,page", [(32, 8, 128, 16), (14, 2, 64, 1), (64, 2, 128, 16)])
+@pytest.mark.parametrize("lens", [[1, 2, 15, 16, 17, 63, 64, 65, 200, 777, 1500], [5000], [300] * 37])
+def test_decode_sk_fp8_matches_oracle(Hq, Hkv, D, page, lens):
+    """Flat tile-stream scheduling over the e4m3 pool (b200attn_decode_sk_fp8kv)."""
+    B = len(lens)
+    sc, k8, v8, kf, vf = _fp8_scenario(lens, [0] * B, Hq, Hkv, D, page, seed=Hq + page + B)
+    q = torch.randn((B, Hq * D), generator=torch.Generator().manual_seed(1)).to(torch.bfloat16)
+    ref, lse_ref = oracle.attention_fp32(q, kf, vf, sc.req_to_token, sc.req_pool_indices, torch.tensor(lens),
+                                         torch.ones(B, dtype=torch.int64), Hq, Hkv, D, sc.scaling, causal=False,
+                                         return_lse=True)
+    d = sc.to(DEV)
+    kv_indptr = torch.zeros(B + 1, dtype=torch.int32, device=DEV)
+    kv_indices = torch.zeros(sum(lens), dtype=torch.int32, device=DEV)
+    ops.build_kv_indices(d.req_to_token, d.req_pool_indices, torch.tensor(lens, device=DEV), kv_indptr, kv_indices)
+    o = torch.full((B, Hq, D), float("nan"), dtype=torch.bfloat16, device=DEV)
+    lse = torch.empty((B, Hq), dtype=torch.float32, device=DEV)
+    ws = torch.zeros(ops.decode_sk_workspace_bytes(B, Hq, Hkv, D), dtype=torch.uint8, device=DEV)
+    for _ in range(2):
+        ops.decode_attention(q.to(DEV).view(B, Hq, D), k8.to(DEV).view(FP8), v8.to(DEV), o, kv_indptr, kv_indices,
+                             sc.scaling, min_chunk=64, workspace=ws, lse=lse, k_descale=0.6, v_descale=0.9,
+                             stream_k=True)
+    torch.cuda.synchronize()
+    assert_close_attn(o.view(B, -1), ref, f"fp8 decode_sk Hq{Hq} D{D} page{page} B{B}")
+    torch.testing.assert_close(lse.cpu(), lse_ref, rtol=2e-3, atol=2e-3)

@@ -37,10 +37,14 @@ for B, ctx in ((1, 8192), (8, 8192), (32, 2048), (64, 4096), (111, 4096), (256, 
     t8 = bench.time_steps(lambda: ops.decode_attention(q, k8, v8, o, kv_indptr, kv_indices, 128 ** -0.5, max_splits=ms8,
                                                        workspace=ws, tail_begin=tb8, k_descale=0.5, v_descale=0.5),
                           20, 5) / 20
+    ws3 = torch.zeros(ops.decode_sk_workspace_bytes(B, 32, 8, 128), dtype=torch.uint8, device=dev)
+    tsk = bench.time_steps(lambda: ops.decode_attention(q, k8, v8, o, kv_indptr, kv_indices, 128 ** -0.5, min_chunk=256,
+                                                        workspace=ws3, k_descale=0.5, v_descale=0.5, stream_k=True),
+                           20, 5) / 20
     t16 = bench.time_steps(lambda: ops.decode_attention(q, kbuf, vbuf, o, kv_indptr, kv_indices, 128 ** -0.5,
                                                         max_splits=ms, workspace=ws), 20, 5) / 20
     kvb = 2 * B * ctx * 8 * 128
-    print(f"B={B} ctx={ctx} splits={ms}/{ms8}: fp8 {t8 * 1e3:.1f} us ({kvb / t8 / 1e6:.0f} GB/s)  bf16 {t16 * 1e3:.1f} us "
+    print(f"B={B} ctx={ctx} splits={ms}/{ms8}: fp8 stream-k {tsk * 1e3:.1f} us ({kvb / tsk / 1e6:.0f} GB/s) | fp8 {t8 * 1e3:.1f} us ({kvb / t8 / 1e6:.0f} GB/s)  bf16 {t16 * 1e3:.1f} us "
           f"({2 * kvb / t16 / 1e6:.0f} GB/s)  speedup {t16 / t8:.2f}x")
     del req_pool, kv_pool, k8, v8, kbuf, vbuf
     torch.cuda.empty_cache()
