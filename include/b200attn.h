@@ -88,6 +88,10 @@ int b200attn_kv_store(const void* k, const void* v, void* k_cache, void* v_cache
  * (`*_dtype`); kv_start and qo_lens/qo_indptr may be null.  kv_indices is int32
  * or int64 (`kv_indices_dtype`); kv_indptr / qo_indptr are int32.
  * `kv_indices_capacity` bounds the writes (entries beyond it are dropped).
+ * `slot_map` (nullable, int32 / int64 `slot_map_dtype`): every slot id is replaced by
+ * slot_map[slot] on the way out (hybrid sliding-window pools: the full -> SWA index
+ * mapping of python/sglang/srt/mem_cache/swa_memory_pool.py:228-231).
+ * One launch for B <= 4096 (each CTA reduces the lengths before its request itself).
  * -------------------------------------------------------------------------- */
 int b200attn_build_kv_indices(const int32_t* req_to_token, int64_t req_to_token_stride,
                               const void* req_pool_indices, int req_pool_dtype,
@@ -97,7 +101,14 @@ int b200attn_build_kv_indices(const int32_t* req_to_token, int64_t req_to_token_
                               int32_t B,
                               int32_t* kv_indptr, void* kv_indices, int kv_indices_dtype,
                               int64_t kv_indices_capacity,
-                              int32_t* qo_indptr, void* stream);
+                              int32_t* qo_indptr, const void* slot_map, int slot_map_dtype,
+                              void* stream);
+
+/* out[i] = slot_map[loc[i]] (int64 out): KVWriteLoc.swa_loc of a hybrid sliding-window pool,
+ *   python/sglang/srt/mem_cache/memory_pool.py:1550-1590, swa_memory_pool.py:228-231,
+ *   triton_backend.py:978-982. */
+int b200attn_translate_slots(const void* loc, int loc_dtype, const void* slot_map,
+                             int slot_map_dtype, int64_t n, int64_t* out, void* stream);
 
 /* Page-table form.  Replaces build_trtllm_mha_page_table
  *   python/sglang/kernels/ops/kvcache/trtllm_mha_page_table.py:40-120
@@ -127,10 +138,14 @@ int b200attn_build_page_table(const int32_t* req_to_token, int64_t req_to_token_
  * if null) — together they let a MIXED batch route its extend_len==1 rows here.
  * `lse` (nullable float[B*Hq], indexed like o rows): natural-log LSE.
  * Workspace: b200attn_decode_workspace_bytes(B, Hq, D, max_splits) bytes, only
- * touched when max_splits > 1: fp32 partials + per-unit arrival counters.  The split
- * partials are merged INSIDE the kernel by the last CTA of a unit to arrive (no
- * second launch).  The workspace must be ZERO-INITIALISED ONCE by the caller before
- * its first use; every launch leaves the counters at zero again.  The split policy is a pure function of
+ * touched when max_splits > 1: a FIXED-SIZE header of per-unit arrival counters
+ * (256 KiB = one int32 per (request, kv head group), at most 65536 units) followed by
+ * the fp32 partials.  The split partials are merged INSIDE the kernel by the last CTA
+ * of a unit to arrive (no second launch).  The workspace must be ZERO-INITIALISED ONCE
+ * by the caller before its first use; every launch leaves the counters at zero again,
+ * and because the header's size and position do not depend on (B, Hq, D, max_splits)
+ * ONE buffer may be reused across launches of any shape (also by b200attn_decode_sk),
+ * as long as launches that share it are stream-ordered.  The split policy is a pure function of
  * (kv length, max_splits, min_chunk) evaluated on the device, so CUDA-graph
  * replay needs no host-side recomputation.
  * `tail_begin` >= 0 restricts splitting to the units (request-major, then kv head
@@ -329,7 +344,8 @@ int b200attn_merge_state(const void* v_a, const float* s_a, const void* v_b,
  *
  * cos_sin_cache: [cache_rows, rot] = (cos | sin) halves per row, fp32 or the element
  * dtype (base.py:173-182).  positions: [T] (pos_axis_stride = 0, mrope_section_host
- * NULL) or [3, T] with `pos_axis_stride` elements between the t/h/w rows and
+ * NULL) or [3, T] with `pos_axis_stride` elements between the t/h/w rows (>= T, or 0
+ * when the three rows alias one [T] vector, i.e. an expanded text-only batch) and
  * mrope_section_host = 3 HOST ints summing to rot/2 (captured by value at launch).
  * Out-of-range positions are clamped to [0, cache_rows).
  *

@@ -15,6 +15,7 @@ from .host import (  # noqa: F401
     MHATokenToKVPool,
     RadixAttention,
     ReqToTokenPool,
+    SWAKVPool,
 )
 from .backend import B200AttnBackend, ForwardMetadata  # noqa: F401
 

@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200attn.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "b200attn.h")
 
-ABI_VERSION = 12  # b200attn_abi_version() of the library this binding matches (api.cu)
+ABI_VERSION = 13  # b200attn_abi_version() of the library this binding matches (api.cu)
 BF16, FP16, FP32 = 0, 1, 2
 I32, I64 = 0, 1
 
@@ -32,8 +32,10 @@ SIGNATURES = {
     ),
     "b200attn_build_kv_indices": (
         C.c_int,
-        [_vp, _i64, _vp, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, C.c_int, _i32, _vp, _vp, C.c_int, _i64, _vp, _vp],
+        [_vp, _i64, _vp, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, C.c_int, _i32, _vp, _vp, C.c_int, _i64, _vp, _vp,
+         C.c_int, _vp],
     ),
+    "b200attn_translate_slots": (C.c_int, [_vp, C.c_int, _vp, C.c_int, _i64, _vp, _vp]),
     "b200attn_build_page_table": (
         C.c_int,
         [_vp, _i64, _vp, C.c_int, _vp, C.c_int, _i32, _i32, _vp, _i64, _i32, _vp],
@@ -131,6 +133,14 @@ def load() -> C.CDLL:
             "There is no CPU / PyTorch fallback for this backend."
         )
     lib = C.CDLL(LIB_PATH)
+    # a stale .so (it is git-ignored and ships out of band) would be called with mismatched argtypes: refuse it
+    # before any signature is typed or any call is made
+    lib.b200attn_abi_version.restype = C.c_int
+    lib.b200attn_abi_version.argtypes = []
+    found = lib.b200attn_abi_version()
+    if found != ABI_VERSION:
+        raise ImportError(f"{LIB_PATH} has ABI version {found}, this binding needs {ABI_VERSION}: rebuild it with "
+                          "`make -C sglang_b200/csrc`")
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing
         fn.restype = res

@@ -69,6 +69,10 @@ class ForwardMetadata:
     # TARGET_VERIFY (speculative decoding): flat tree mask + int32 offsets (triton_backend.py:911-917)
     custom_mask: Optional[torch.Tensor] = None
     mask_indptr: Optional[torch.Tensor] = None
+    # hybrid sliding-window pools (swa_memory_pool.py): the same positions in the SWA pool's index space, used by
+    # the SWA layers for both the read (kv_indices) and the write (KVWriteLoc.swa_loc, memory_pool.py:1550-1590)
+    swa_kv_indices: Optional[torch.Tensor] = None
+    swa_out_cache_loc: Optional[torch.Tensor] = None
 
 
 def _attn_type_value(layer) -> str:
@@ -95,8 +99,12 @@ class B200AttnBackend(_Base):
         self.token_to_kv_pool = model_runner.token_to_kv_pool
         self.req_to_token = self.req_to_token_pool.req_to_token
         self.max_context_len = int(self.req_to_token.shape[1])
-        if getattr(model_runner, "sliding_window_size", None) not in (None, -1):
-            raise NotImplementedError("b200 backend: sliding-window models are not supported")
+        # Sliding-window models (model_runner.sliding_window_size set, load_model_utils.py:135-148): the per-layer
+        # window comes from layer.sliding_window_size.  With a hybrid pool (SWAKVPool: separate, smaller pool for
+        # the SWA layers) those layers address the SWA pool through full_to_swa_index_mapping.
+        self.sliding_window_size = getattr(model_runner, "sliding_window_size", None)
+        self._hybrid_swa = (hasattr(self.token_to_kv_pool, "layers_mapping")
+                            and hasattr(self.token_to_kv_pool, "full_to_swa_index_mapping"))
         self.skip_padding_slot = skip_padding_slot
         self.export_page_table = export_page_table
         self.forward_metadata: Optional[ForwardMetadata] = None
@@ -179,17 +187,43 @@ class B200AttnBackend(_Base):
         kbuf, vbuf = pool.get_kv_buffer(layer.layer_id)
         k = k.view(-1, layer.tp_k_head_num, layer.head_dim)
         v = v.view(-1, layer.tp_v_head_num, layer.v_head_dim)
+        loc = forward_batch.out_cache_loc
+        if self._is_swa_layer(layer):  # KVWriteLoc.swa_loc: translated once per forward (triton_backend.py:978-982)
+            loc = self.forward_metadata.swa_out_cache_loc
         if self._fp8_pool():  # quantising store: div by the scale in the input dtype, then e4m3 (memory_pool.py:2365-2375)
             sc = self._descales(layer)
-            ops.store_cache_fp8(k, v, kbuf, vbuf, forward_batch.out_cache_loc,
+            ops.store_cache_fp8(k, v, kbuf, vbuf, loc,
                                 sc["k_descale"] if getattr(layer, "k_scale", None) is not None else None,
                                 sc["v_descale"] if getattr(layer, "v_scale", None) is not None else None,
                                 reserved_skip_index=0 if self.skip_padding_slot else -1)
             return
         if k.dtype != kbuf.dtype:  # memory_pool.py:2365-2371
             k, v = k.to(kbuf.dtype), v.to(vbuf.dtype)
-        ops.store_cache(k, v, kbuf, vbuf, forward_batch.out_cache_loc,
-                        reserved_skip_index=0 if self.skip_padding_slot else -1)
+        ops.store_cache(k, v, kbuf, vbuf, loc, reserved_skip_index=0 if self.skip_padding_slot else -1)
+
+    def _is_swa_layer(self, layer) -> bool:
+        return bool(self._hybrid_swa and self.token_to_kv_pool.layers_mapping[layer.layer_id][1])
+
+    def _kv_indices(self, layer, md) -> torch.Tensor:
+        return md.swa_kv_indices if self._is_swa_layer(layer) else md.kv_indices
+
+    def _build_swa(self, fb, md, kv_lens, qo_lens=None, out_indices=None, out_loc=None) -> None:
+        """Hybrid pool: the batch's kv positions and write slots in the SWA pool's index space."""
+        if not self._hybrid_swa:
+            return
+        mapping = self.token_to_kv_pool.full_to_swa_index_mapping
+        if mapping is None:
+            raise RuntimeError("b200 backend: hybrid SWA pool without full_to_swa_index_mapping")
+        if out_indices is None:
+            out_indices = torch.empty_like(md.kv_indices)
+        scratch = torch.empty_like(md.kv_indptr)
+        ops.build_kv_indices(self.req_to_token, fb.req_pool_indices, kv_lens, scratch, out_indices,
+                             qo_lens=qo_lens, qo_indptr=torch.empty_like(scratch) if qo_lens is not None else None,
+                             slot_map=mapping)
+        md.swa_kv_indices = out_indices
+        loc = fb.out_cache_loc
+        if loc is not None:
+            md.swa_out_cache_loc = ops.translate_slots(loc, mapping, out=None if out_loc is None else out_loc[:loc.numel()])
 
     # ------------------------------------------------------------------ metadata
     def _build(self, fb, kv_lens, kv_indptr, kv_indices, qo_lens=None, qo_indptr=None) -> None:
@@ -226,6 +260,7 @@ class B200AttnBackend(_Base):
                                  page_table=self._page_table(fb, B), min_chunk=self.MIN_CHUNK)
             cpu = getattr(fb, "seq_lens_cpu", None)
             md._max_kv_len = int(cpu.max()) if cpu is not None else self.max_context_len
+            self._build_swa(fb, md, fb.seq_lens)
             self.forward_metadata = md
             return
         if mode.is_target_verify():
@@ -257,6 +292,7 @@ class B200AttnBackend(_Base):
             md.max_extend_len = max([e for e in ext_cpu if e != 1], default=0)
             pre_cpu = getattr(fb, "extend_prefix_lens_cpu", None)
             md.dec_max_kv_len = (max(pre_cpu[b] for b in reqs) + 1) if pre_cpu is not None else self.max_context_len
+        self._build_swa(fb, md, fb.seq_lens, qo_lens=fb.extend_seq_lens)
         self.forward_metadata = md
 
     def _init_target_verify(self, fb, B: int, kv_indptr: torch.Tensor) -> None:
@@ -264,6 +300,8 @@ class B200AttnBackend(_Base):
         tree mask ``spec_info.custom_mask`` (row-major ``[draft, seq_len + draft]`` blocks, prefix keys always
         visible).  ``seq_lens`` counts the cached tokens only; the draft tokens' K/V are stored by forward_extend at
         ``out_cache_loc`` and appended to ``kv_indices`` here, so the kernels still see one KV source."""
+        if self._hybrid_swa:
+            raise NotImplementedError("b200 backend: TARGET_VERIFY over a hybrid sliding-window pool is not supported")
         spec = fb.spec_info
         nd = int(spec.draft_token_num)
         dev = self.device
@@ -299,6 +337,10 @@ class B200AttnBackend(_Base):
         g.qo_indptr = torch.zeros(max_bs + 1, dtype=torch.int32, device=dev)  # full-graph / breakable-graph extend
         g.max_num_tokens = max_num_tokens
         g.max_splits_cap = max_splits_cap
+        g.swa_kv_indices = g.swa_out_cache_loc = None
+        if self._hybrid_swa:  # triton_backend.py:1100-1108
+            g.swa_kv_indices = torch.zeros_like(g.kv_indices)
+            g.swa_out_cache_loc = torch.zeros(max(max_num_tokens, max_bs), dtype=torch.int64, device=dev)
         g.workspace = None
         if num_q_heads is not None and head_dim is not None:
             nbytes = ops.decode_workspace_bytes(max_bs, num_q_heads, head_dim, max_splits_cap)
@@ -337,15 +379,19 @@ class B200AttnBackend(_Base):
                 cache_seqlens_int32=g.cache_seqlens_int32[:B], max_extend_len=int(g.max_num_tokens),
                 num_extend_tokens=0, min_chunk=self.MIN_CHUNK)
             md._graph = True
+            self._build_swa(fb, md, fb.seq_lens, qo_lens=fb.extend_seq_lens, out_indices=g.swa_kv_indices,
+                            out_loc=g.swa_out_cache_loc)
             self.forward_metadata = md
             return
         self._build(fb, fb.seq_lens, g.kv_indptr, g.kv_indices)
         g.cache_seqlens_int32[:B].copy_(fb.seq_lens[:B])
-        self.forward_metadata = ForwardMetadata(
+        md = ForwardMetadata(
             kv_indptr=g.kv_indptr, kv_indices=g.kv_indices, batch_size=B,
             cache_seqlens_int32=g.cache_seqlens_int32[:B], min_chunk=self.MIN_CHUNK,
             workspace=g.workspace)
-        self.forward_metadata._graph = True
+        md._graph = True
+        self._build_swa(fb, md, fb.seq_lens, out_indices=g.swa_kv_indices, out_loc=g.swa_out_cache_loc)
+        self.forward_metadata = md
 
     def init_forward_metadata_in_graph(self, forward_batch) -> None:
         pass  # nothing is recomputed inside the graph: the kernels read the static buffers
@@ -416,7 +462,8 @@ class B200AttnBackend(_Base):
                         tail_begin = -1
                 else:
                     ms, ws = k, self._workspace(need)
-        ops.decode_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.kv_indptr, md.kv_indices,
+        ops.decode_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.kv_indptr,
+                             self._kv_indices(layer, md),
                              layer.scaling, max_splits=ms, min_chunk=md.min_chunk, workspace=ws, num_items=B,
                              tail_begin=tail_begin, **self._features(layer, kwargs),
                              **(self._descales(layer) if self._fp8_pool() else {}))
@@ -452,11 +499,12 @@ class B200AttnBackend(_Base):
             self._side.wait_stream(cur)
         if md.max_extend_len > 0:
             ws = self._workspace(ops.extend_workspace_bytes(B, q2.shape[0], Hq))
-            ek, ev, eidx, escale = kbuf, vbuf, md.kv_indices, layer.scaling
+            kv_idx = self._kv_indices(layer, md)
+            ek, ev, eidx, escale = kbuf, vbuf, kv_idx, layer.scaling
             if fp8:
                 # the tcgen05 kernel takes 16-bit K/V operands: gather the batch's rows once into a 16-bit scratch
                 # (K exact, k_descale on the score scale; v_descale folded into the V rows), slot ids become 0..n-1
-                n = md.kv_indices.numel()
+                n = kv_idx.numel()
                 Hkv = layer.tp_k_head_num
                 graph = getattr(md, "_graph", False)
                 if self._fp8_scratch is None or self._fp8_scratch.shape[1] < n or self._fp8_scratch.dtype != q2.dtype \
@@ -474,7 +522,7 @@ class B200AttnBackend(_Base):
                 # a slot shared by several requests (radix hit) is converted once; eidx[i] = the scratch row holding
                 # row i's slot.  Graph mode: the launch covers the static kv_indices buffer, the live row count is
                 # kv_indptr[B] on the device
-                ops.kv_dequant_gather_unique(kbuf, vbuf, md.kv_indices, n, ek, ev, self._fp8_first, eidx, 1.0,
+                ops.kv_dequant_gather_unique(kbuf, vbuf, kv_idx, n, ek, ev, self._fp8_first, eidx, 1.0,
                                              dsc["v_descale"], n_dev=md.kv_indptr[B:B + 1] if graph else None)
                 escale = layer.scaling * dsc["k_descale"]
             ops.extend_attention(q2.view(-1, Hq, D), ek, ev, o.view(-1, Hq, D), md.qo_indptr, md.kv_indptr,
@@ -495,7 +543,8 @@ class B200AttnBackend(_Base):
                     ws = self._ws_dec if need > 0 else None
                 else:
                     ws = self._workspace(need)
-                ops.decode_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.kv_indptr, md.kv_indices,
+                ops.decode_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.kv_indptr,
+                                     self._kv_indices(layer, md),
                                      layer.scaling, max_splits=ms, min_chunk=md.min_chunk, workspace=ws,
                                      q_rows=md.dec_q_rows, req_ids=md.dec_req_ids, num_items=md.num_dec,
                                      **self._features(layer, kwargs), **dsc)

@@ -687,7 +687,8 @@ static int launch_decode(const DecodeParams& p, cudaStream_t st) {
 extern "C" int64_t b200attn_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t D,
                                                    int32_t max_splits) {
   if (max_splits <= 1) return 0;
-  return (int64_t)B * Hq * max_splits * (D + 1) * 4 + (int64_t)B * Hq * 4;  // partials + arrival counters
+  // fixed-size counter header (kDecCounterBytes) + fp32 partials and their LSE
+  return b200attn::kDecCounterBytes + (int64_t)B * Hq * max_splits * (D + 1) * 4;
 }
 
 static int decode_impl(const void* q, int64_t q_stride, const void* k_cache,
@@ -720,6 +721,8 @@ static int decode_impl(const void* q, int64_t q_stride, const void* k_cache,
   B2_CHECK_ARG(need == 0 || (workspace && workspace_bytes >= need),
                "decode: workspace too small (%lld < %lld)", (long long)workspace_bytes,
                (long long)need);
+  B2_CHECK_ARG(need == 0 || (int64_t)B * Hkv * ((Hq / Hkv + kDecMaxG - 1) / kDecMaxG) <= kDecMaxUnits,
+               "decode: more than %d units with max_splits > 1", kDecMaxUnits);
   DecodeParams p;
   p.q = q;
   p.k_cache = k_cache;
@@ -730,9 +733,9 @@ static int decode_impl(const void* q, int64_t q_stride, const void* k_cache,
   p.kv_indices = kv_indices;
   p.q_rows = q_rows;
   p.req_ids = req_ids;
-  p.ws_o = reinterpret_cast<float*>(workspace);
+  p.ws_cnt = need > 0 ? reinterpret_cast<int*>(workspace) : nullptr;
+  p.ws_o = need > 0 ? reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + kDecCounterBytes) : nullptr;
   p.ws_lse = p.ws_o ? p.ws_o + (int64_t)B * Hq * max_splits * D : nullptr;
-  p.ws_cnt = p.ws_o ? reinterpret_cast<int*>(p.ws_lse + (int64_t)B * Hq * max_splits) : nullptr;
   p.q_stride = q_stride;
   p.kv_stride = kv_stride;
   p.o_stride = o_stride;

@@ -8,6 +8,11 @@ constexpr int kDecTile = 64;     // keys per pipeline stage
 constexpr int kDecStages = 3;    // cp.async ring depth
 constexpr int kDecThreads = 128; // 4 warps x 16 keys
 constexpr int kDecMaxG = 16;     // q heads per CTA (M of the mma)
+// Split workspaces start with a FIXED-SIZE header of per-unit arrival counters (one int32 per (request, kv head
+// group)), so their address does not depend on the launch shape: a caller may reuse one zero-initialised buffer
+// across launches with different B / max_splits / D without stale partials ever aliasing a counter.
+constexpr int kDecMaxUnits = 1 << 16;
+constexpr int64_t kDecCounterBytes = (int64_t)kDecMaxUnits * 4;
 
 struct DecodeParams {
   const void* q;

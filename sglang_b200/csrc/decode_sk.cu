@@ -483,7 +483,8 @@ extern "C" int64_t b200attn_decode_sk_workspace_bytes(int32_t B, int32_t Hq, int
   if (B <= 0 || Hq <= 0 || Hkv <= 0) return 0;
   const int groups = (Hq / Hkv + kDecMaxG - 1) / kDecMaxG;
   // two partial slots per CTA ([16][D] fp32 + [16] lse) + one arrival counter per unit
-  return (int64_t)sk_ctas_cap() * 2 * kDecMaxG * (D + 1) * 4 + (int64_t)B * Hkv * groups * 4;
+  (void)groups;
+  return kDecCounterBytes + (int64_t)sk_ctas_cap() * 2 * kDecMaxG * (D + 1) * 4;  // fixed counter header first
 }
 
 static int decode_sk_impl(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache,
@@ -522,9 +523,11 @@ static int decode_sk_impl(const void* q, int64_t q_stride, const void* k_cache, 
   p.kv_indices = kv_indices;
   p.q_rows = q_rows;
   p.req_ids = req_ids;
-  p.ws_o = reinterpret_cast<float*>(workspace);
+  B2_CHECK_ARG((int64_t)B * Hkv * ((Hq / Hkv + kDecMaxG - 1) / kDecMaxG) <= kDecMaxUnits,
+               "decode_sk: more than %d units", kDecMaxUnits);
+  p.ws_cnt = reinterpret_cast<int*>(workspace);
+  p.ws_o = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + kDecCounterBytes);
   p.ws_lse = p.ws_o + (int64_t)cap * 2 * kDecMaxG * D;
-  p.ws_cnt = reinterpret_cast<int*>(p.ws_lse + (int64_t)cap * 2 * kDecMaxG);
   p.q_stride = q_stride;
   p.kv_stride = kv_stride;
   p.o_stride = o_stride;

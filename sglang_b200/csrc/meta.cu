@@ -4,10 +4,13 @@
 //   python/sglang/kernels/ops/kvcache/kv_indices.py:8-44
 //   python/sglang/srt/layers/attention/triton_backend.py:438-456
 //   python/sglang/kernels/ops/kvcache/trtllm_mha_page_table.py:40-120
-// Two launches, no host sync, static shapes => CUDA-graph replayable:
-//   1. one CTA scans the per-request lengths into kv_indptr (and qo_indptr);
-//   2. a (chunks, B) grid copies req_to_token rows into the flat index list,
-//      4 indices per thread, coalesced on both sides.
+// ONE launch, no host sync, static shapes => CUDA-graph replayable: a (chunks, B) grid copies
+// req_to_token rows into the flat index list, 4 indices per thread, coalesced on both sides; every
+// CTA derives its request's offset itself (block reduction over the lengths of the requests before
+// it: B loads, far cheaper than a second dependent launch) and the first CTA of a request also
+// publishes kv_indptr / qo_indptr.  Batches above kFusedMaxB keep the scan + gather pair.
+// An optional slot map translates every slot id on the way out (hybrid sliding-window pools:
+// full -> SWA pool index, python/sglang/srt/mem_cache/swa_memory_pool.py:228-231).
 #include "common.cuh"
 
 namespace b200attn {
@@ -77,15 +80,12 @@ constexpr int kGatherPerThread = 4;
 constexpr int kGatherChunk = kGatherThreads * kGatherPerThread;
 
 template <typename OutT>
-__global__ void __launch_bounds__(kGatherThreads)
-    kv_indices_gather_kernel(const int32_t* __restrict__ req_to_token, int64_t stride,
-                             const void* __restrict__ req_pool_indices, int req_dtype,
-                             const void* __restrict__ kv_start, int start_dtype,
-                             const int32_t* __restrict__ kv_indptr,
-                             OutT* __restrict__ kv_indices, int64_t capacity) {
-  const int b = blockIdx.y;
-  const int32_t beg = kv_indptr[b];
-  const int32_t len = kv_indptr[b + 1] - beg;
+__device__ __forceinline__ void gather_row(const int32_t* __restrict__ req_to_token, int64_t stride,
+                                           const void* __restrict__ req_pool_indices, int req_dtype,
+                                           const void* __restrict__ kv_start, int start_dtype, int b,
+                                           int32_t beg, int32_t len, OutT* __restrict__ kv_indices,
+                                           int64_t capacity, const void* __restrict__ slot_map,
+                                           int map_dtype) {
   const int32_t first = blockIdx.x * kGatherChunk;
   if (first >= len) return;
   const int64_t req = load_index(req_pool_indices, req_dtype, b);
@@ -100,8 +100,87 @@ __global__ void __launch_bounds__(kGatherThreads)
 #pragma unroll
   for (int j = 0; j < kGatherPerThread; ++j) {
     const int32_t p = first + j * kGatherThreads + threadIdx.x;
-    if (p < len && (int64_t)beg + p < capacity) kv_indices[(int64_t)beg + p] = (OutT)vals[j];
+    if (p < len && (int64_t)beg + p < capacity) {
+      const int64_t slot = slot_map ? load_index(slot_map, map_dtype, vals[j]) : (int64_t)vals[j];
+      kv_indices[(int64_t)beg + p] = (OutT)slot;
+    }
   }
+}
+
+// out[i] = slot_map[loc[i]] (the SWA translation of out_cache_loc, swa_memory_pool.py:228-231)
+__global__ void __launch_bounds__(256)
+    translate_slots_kernel(const void* __restrict__ loc, int loc_dtype, const void* __restrict__ slot_map,
+                           int map_dtype, int64_t n, int64_t* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (i < n) out[i] = load_index(slot_map, map_dtype, load_index(loc, loc_dtype, i));
+}
+
+template <typename OutT>
+__global__ void __launch_bounds__(kGatherThreads)
+    kv_indices_gather_kernel(const int32_t* __restrict__ req_to_token, int64_t stride,
+                             const void* __restrict__ req_pool_indices, int req_dtype,
+                             const void* __restrict__ kv_start, int start_dtype,
+                             const int32_t* __restrict__ kv_indptr,
+                             OutT* __restrict__ kv_indices, int64_t capacity,
+                             const void* __restrict__ slot_map, int map_dtype) {
+  const int b = blockIdx.y;
+  const int32_t beg = kv_indptr[b];
+  const int32_t len = kv_indptr[b + 1] - beg;
+  gather_row<OutT>(req_to_token, stride, req_pool_indices, req_dtype, kv_start, start_dtype, b, beg, len,
+                   kv_indices, capacity, slot_map, map_dtype);
+}
+
+// Fused variant: offsets by block reduction, indptr published by the request's first CTA.
+constexpr int kFusedMaxB = 4096;
+
+template <typename OutT>
+__global__ void __launch_bounds__(kGatherThreads)
+    kv_meta_fused_kernel(const int32_t* __restrict__ req_to_token, int64_t stride,
+                         const void* __restrict__ req_pool_indices, int req_dtype,
+                         const void* __restrict__ kv_lens, int kv_dtype,
+                         const void* __restrict__ kv_start, int start_dtype,
+                         const void* __restrict__ qo_lens, int qo_dtype,
+                         int32_t* __restrict__ kv_indptr, int32_t* __restrict__ qo_indptr,
+                         OutT* __restrict__ kv_indices, int64_t capacity,
+                         const void* __restrict__ slot_map, int map_dtype) {
+  const int b = blockIdx.y;
+  const int32_t len = (int32_t)load_index(kv_lens, kv_dtype, b);
+  const int32_t first = blockIdx.x * kGatherChunk;
+  if (blockIdx.x > 0 && first >= len) return;  // only a request's first CTA has work besides the gather
+  __shared__ int32_t red[2][kGatherThreads / 32];
+  int32_t s_kv = 0, s_qo = 0;
+  const bool want_qo = blockIdx.x == 0 && qo_lens != nullptr;
+  for (int i = threadIdx.x; i < b; i += kGatherThreads) {
+    s_kv += (int32_t)load_index(kv_lens, kv_dtype, i);
+    if (want_qo) s_qo += (int32_t)load_index(qo_lens, qo_dtype, i);
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    s_kv += __shfl_xor_sync(0xffffffffu, s_kv, off);
+    s_qo += __shfl_xor_sync(0xffffffffu, s_qo, off);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    red[0][threadIdx.x >> 5] = s_kv;
+    red[1][threadIdx.x >> 5] = s_qo;
+  }
+  __syncthreads();
+  int32_t beg = 0, qbeg = 0;
+#pragma unroll
+  for (int w = 0; w < kGatherThreads / 32; ++w) {
+    beg += red[0][w];
+    qbeg += red[1][w];
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    if (b == 0) {
+      kv_indptr[0] = 0;
+      if (qo_indptr) qo_indptr[0] = 0;
+    }
+    kv_indptr[b + 1] = beg + len;
+    if (qo_indptr) qo_indptr[b + 1] = qbeg + (int32_t)load_index(qo_lens, qo_dtype, b);
+  }
+  if (kv_indices == nullptr) return;
+  gather_row<OutT>(req_to_token, stride, req_pool_indices, req_dtype, kv_start, start_dtype, b, beg, len,
+                   kv_indices, capacity, slot_map, map_dtype);
 }
 
 __global__ void __launch_bounds__(256)
@@ -127,7 +206,7 @@ extern "C" int b200attn_build_kv_indices(
     int req_pool_dtype, const void* kv_lens, int kv_lens_dtype, const void* kv_start,
     int kv_start_dtype, const void* qo_lens, int qo_lens_dtype, int32_t B, int32_t* kv_indptr,
     void* kv_indices, int kv_indices_dtype, int64_t kv_indices_capacity, int32_t* qo_indptr,
-    void* stream) {
+    const void* slot_map, int slot_map_dtype, void* stream) {
   using namespace b200attn;
   B2_CHECK_ARG(B >= 0, "build_kv_indices: negative batch");
   B2_CHECK_ARG(kv_indptr != nullptr, "build_kv_indices: kv_indptr is null");
@@ -137,26 +216,57 @@ extern "C" int b200attn_build_kv_indices(
                "build_kv_indices: qo_lens and qo_indptr must be given together");
   B2_CHECK_ARG(kv_indices_dtype == B200ATTN_I32 || kv_indices_dtype == B200ATTN_I64,
                "build_kv_indices: bad kv_indices dtype");
+  B2_CHECK_ARG(slot_map == nullptr || slot_map_dtype == B200ATTN_I32 || slot_map_dtype == B200ATTN_I64,
+               "build_kv_indices: bad slot_map dtype");
   cudaStream_t st = (cudaStream_t)stream;
+  const bool want_indices = kv_indices != nullptr && kv_indices_capacity > 0;
+  // grid.x is sized from the row width (an upper bound on any request's length),
+  // so no device->host read of the lengths is needed.
+  int64_t chunks = want_indices ? (req_to_token_stride + kGatherChunk - 1) / kGatherChunk : 1;
+  if (chunks < 1) chunks = 1;
+  B2_CHECK_ARG(chunks <= 2147483647ll && B <= 65535, "build_kv_indices: grid too large");
+  if (B > 0 && B <= kFusedMaxB) {
+    dim3 grid((unsigned)chunks, (unsigned)B);
+    if (kv_indices_dtype == B200ATTN_I32) {
+      kv_meta_fused_kernel<int32_t><<<grid, kGatherThreads, 0, st>>>(
+          req_to_token, req_to_token_stride, req_pool_indices, req_pool_dtype, kv_lens, kv_lens_dtype,
+          kv_start, kv_start_dtype, qo_lens, qo_lens_dtype, kv_indptr, qo_indptr,
+          want_indices ? (int32_t*)kv_indices : nullptr, kv_indices_capacity, slot_map, slot_map_dtype);
+    } else {
+      kv_meta_fused_kernel<int64_t><<<grid, kGatherThreads, 0, st>>>(
+          req_to_token, req_to_token_stride, req_pool_indices, req_pool_dtype, kv_lens, kv_lens_dtype,
+          kv_start, kv_start_dtype, qo_lens, qo_lens_dtype, kv_indptr, qo_indptr,
+          want_indices ? (int64_t*)kv_indices : nullptr, kv_indices_capacity, slot_map, slot_map_dtype);
+    }
+    B2_LAUNCH_CHECK();
+    return B200ATTN_OK;
+  }
   indptr_scan_kernel<<<1, kScanThreads, 0, st>>>(kv_lens, kv_lens_dtype, qo_lens, qo_lens_dtype,
                                                  B, kv_indptr, qo_indptr);
   B2_LAUNCH_CHECK();
-  if (B == 0 || kv_indices == nullptr || kv_indices_capacity <= 0) return B200ATTN_OK;
-  // grid.x is sized from the row width (an upper bound on any request's length),
-  // so no device->host read of the lengths is needed.
-  int64_t chunks = (req_to_token_stride + kGatherChunk - 1) / kGatherChunk;
-  if (chunks < 1) chunks = 1;
-  B2_CHECK_ARG(chunks <= 2147483647ll && B <= 65535, "build_kv_indices: grid too large");
+  if (B == 0 || !want_indices) return B200ATTN_OK;
   dim3 grid((unsigned)chunks, (unsigned)B);
   if (kv_indices_dtype == B200ATTN_I32) {
     kv_indices_gather_kernel<int32_t><<<grid, kGatherThreads, 0, st>>>(
         req_to_token, req_to_token_stride, req_pool_indices, req_pool_dtype, kv_start,
-        kv_start_dtype, kv_indptr, (int32_t*)kv_indices, kv_indices_capacity);
+        kv_start_dtype, kv_indptr, (int32_t*)kv_indices, kv_indices_capacity, slot_map, slot_map_dtype);
   } else {
     kv_indices_gather_kernel<int64_t><<<grid, kGatherThreads, 0, st>>>(
         req_to_token, req_to_token_stride, req_pool_indices, req_pool_dtype, kv_start,
-        kv_start_dtype, kv_indptr, (int64_t*)kv_indices, kv_indices_capacity);
+        kv_start_dtype, kv_indptr, (int64_t*)kv_indices, kv_indices_capacity, slot_map, slot_map_dtype);
   }
+  B2_LAUNCH_CHECK();
+  return B200ATTN_OK;
+}
+
+extern "C" int b200attn_translate_slots(const void* loc, int loc_dtype, const void* slot_map,
+                                        int slot_map_dtype, int64_t n, int64_t* out, void* stream) {
+  using namespace b200attn;
+  B2_CHECK_ARG(n >= 0, "translate_slots: negative size");
+  if (n == 0) return B200ATTN_OK;
+  B2_CHECK_ARG(loc && slot_map && out, "translate_slots: null pointer");
+  translate_slots_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      loc, loc_dtype, slot_map, slot_map_dtype, n, out);
   B2_LAUNCH_CHECK();
   return B200ATTN_OK;
 }

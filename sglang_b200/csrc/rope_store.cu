@@ -715,7 +715,8 @@ static int rope_store_impl(void* q, void* k, const void* v, void* k_cache, void*
     B2_CHECK_ARG(p.sec0 >= 0 && p.sec1 >= 0 && p.sec2 >= 0 &&
                      p.sec0 + p.sec1 + p.sec2 == rotary_dim / 2,
                  "rope_store: mrope_section must sum to rotary_dim/2");
-    B2_CHECK_ARG(pos_axis_stride >= T, "rope_store: positions[3,T] axis stride < T");
+    // 0 = the three axes alias one row (text-only batches: positions.unsqueeze(0).expand(3, -1))
+    B2_CHECK_ARG(pos_axis_stride >= T || pos_axis_stride == 0, "rope_store: positions[3,T] axis stride < T");
   } else {
     p.sec0 = -1;
     B2_CHECK_ARG(pos_axis_stride == 0, "rope_store: 2-D positions need mrope_section");

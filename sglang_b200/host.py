@@ -13,6 +13,7 @@ backend is duck-type compatible with the real objects:
   ReqToTokenPool         python/sglang/srt/mem_cache/memory_pool.py:256-332
   KVWriteLoc             python/sglang/srt/mem_cache/memory_pool.py:1550-1590
   MHATokenToKVPool       python/sglang/srt/mem_cache/memory_pool.py:1759-2456
+  SWAKVPool              python/sglang/srt/mem_cache/swa_memory_pool.py:20-270
   alloc_extend_naive     python/sglang/srt/mem_cache/allocator/paged.py:44-102
 """
 from __future__ import annotations
@@ -176,6 +177,55 @@ class MHATokenToKVPool:
             cache_k, cache_v, self.get_key_buffer(layer_id), self.get_value_buffer(layer_id), loc,
             reserved_skip_index=0 if self.skip_padding_slot else -1,
         )
+
+
+class SWAKVPool:
+    """Hybrid full / sliding-window cache: two MHA pools, the SWA one smaller and addressed through
+    ``full_to_swa_index_mapping`` (swa_memory_pool.py:20-270).  ``layers_mapping[layer_id] = (index in its pool,
+    is_swa_layer)``.  The attention backend translates slot ids once per forward (``KVWriteLoc.swa_loc``)."""
+
+    def __init__(self, size: int, size_swa: int, page_size: int, dtype: torch.dtype, head_num: int, head_dim: int,
+                 swa_attention_layer_ids: List[int], full_attention_layer_ids: List[int], device: str):
+        self.size, self.size_swa, self.page_size, self.dtype, self.device = size, size_swa, page_size, dtype, device
+        self.head_num, self.head_dim = head_num, head_dim
+        self.full_kv_pool = MHATokenToKVPool(size, page_size, dtype, head_num, head_dim,
+                                             len(full_attention_layer_ids), device)
+        self.swa_kv_pool = MHATokenToKVPool(size_swa, page_size, dtype, head_num, head_dim,
+                                            len(swa_attention_layer_ids), device)
+        self.layers_mapping = {}
+        for i, lid in enumerate(full_attention_layer_ids):
+            self.layers_mapping[lid] = (i, False)
+        for i, lid in enumerate(swa_attention_layer_ids):
+            self.layers_mapping[lid] = (i, True)
+        self.full_to_swa_index_mapping: Optional[torch.Tensor] = None  # int64 [size + page_size + 1], set by the allocator
+        self.start_layer = 0
+        self.layer_transfer_counter = None
+
+    def _pool(self, layer_id: int):
+        idx, is_swa = self.layers_mapping[layer_id]
+        return (self.swa_kv_pool if is_swa else self.full_kv_pool), idx
+
+    def get_key_buffer(self, layer_id: int) -> torch.Tensor:
+        pool, idx = self._pool(layer_id)
+        return pool.get_key_buffer(idx)
+
+    def get_value_buffer(self, layer_id: int) -> torch.Tensor:
+        pool, idx = self._pool(layer_id)
+        return pool.get_value_buffer(idx)
+
+    def get_kv_buffer(self, layer_id: int) -> Tuple[torch.Tensor, torch.Tensor]:
+        return self.get_key_buffer(layer_id), self.get_value_buffer(layer_id)
+
+    def translate_loc_from_full_to_swa(self, kv_indices: torch.Tensor) -> torch.Tensor:
+        return ops.translate_slots(kv_indices, self.full_to_swa_index_mapping)
+
+    def set_kv_buffer(self, layer, loc_info, cache_k, cache_v, k_scale=None, v_scale=None) -> None:
+        pool, idx = self._pool(layer.layer_id)
+        loc = loc_info
+        if hasattr(loc_info, "loc"):
+            loc = loc_info.swa_loc if self.layers_mapping[layer.layer_id][1] else loc_info.loc
+            assert loc is not None, "SWA layers need KVWriteLoc.swa_loc"
+        pool.set_kv_buffer(idx, loc, cache_k, cache_v, k_scale, v_scale)
 
 
 class RadixAttention:

@@ -290,7 +290,11 @@ def apply_rope_with_cos_sin_cache_inplace(
             positions = positions.contiguous()
         if positions.shape[1] != T:
             raise ValueError("rope: positions and q disagree on the number of tokens")
-        pos_axis_stride = max(positions.stride(0), T)
+        # stride(0) == 0 is a valid axis stride (text-only batches: pos.unsqueeze(0).expand(3, -1)); anything
+        # else below T would alias rows, so it is made contiguous
+        if positions.stride(0) != 0 and positions.stride(0) < T:
+            positions = positions.contiguous()
+        pos_axis_stride = positions.stride(0)
         import ctypes as C
         sec = (C.c_int32 * 3)(*[int(x) for x in mrope_section])
     else:
@@ -404,13 +408,16 @@ def build_kv_indices(
     kv_start: Optional[torch.Tensor] = None,
     qo_lens: Optional[torch.Tensor] = None,
     qo_indptr: Optional[torch.Tensor] = None,
+    slot_map: Optional[torch.Tensor] = None,
 ) -> None:
     """Fill ``kv_indptr`` (int32 ``[B+1]``), ``kv_indices`` (flat slot ids) and optionally ``qo_indptr``.
 
     Mirrors ``create_flashinfer_kv_indices_triton`` + the cumsum around it
-    (python/sglang/srt/layers/attention/triton_backend.py:438-456).
+    (python/sglang/srt/layers/attention/triton_backend.py:438-456).  ``slot_map`` translates every slot id
+    (``full_to_swa_index_mapping`` of a hybrid sliding-window pool, swa_memory_pool.py:228-231).
     """
-    _require_cuda(req_to_token, req_pool_indices, kv_lens, kv_indptr, kv_indices, kv_start, qo_lens, qo_indptr)
+    _require_cuda(req_to_token, req_pool_indices, kv_lens, kv_indptr, kv_indices, kv_start, qo_lens, qo_indptr,
+                  slot_map)
     B = kv_lens.numel()
     if req_to_token.dtype != torch.int32 or req_to_token.stride(1) != 1:
         raise TypeError("build_kv_indices: req_to_token must be int32 with contiguous rows")
@@ -426,9 +433,23 @@ def build_kv_indices(
         _ptr(qo_lens), _idtype(qo_lens) if qo_lens is not None else I32,
         B, kv_indptr.data_ptr(), _ptr(kv_indices),
         _idtype(kv_indices) if kv_indices is not None else I32,
-        kv_indices.numel() if kv_indices is not None else 0, _ptr(qo_indptr), _stream(),
+        kv_indices.numel() if kv_indices is not None else 0, _ptr(qo_indptr),
+        _ptr(slot_map), _idtype(slot_map) if slot_map is not None else I32, _stream(),
     )
     check(rc, "b200attn_build_kv_indices")
+
+
+def translate_slots(loc: torch.Tensor, slot_map: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``slot_map[loc]`` as int64: ``KVWriteLoc.swa_loc`` of a hybrid sliding-window pool
+    (``SWAKVPool.translate_loc_from_full_to_swa``, swa_memory_pool.py:228-231)."""
+    _require_cuda(loc, slot_map, out)
+    loc = loc.contiguous()
+    if out is None:
+        out = torch.empty(loc.numel(), dtype=torch.int64, device=loc.device)
+    rc = _lib.load().b200attn_translate_slots(loc.data_ptr(), _idtype(loc), slot_map.data_ptr(), _idtype(slot_map),
+                                              loc.numel(), out.data_ptr(), _stream())
+    check(rc, "b200attn_translate_slots")
+    return out
 
 
 def build_page_table(
