@@ -13,7 +13,24 @@ GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 def golden_files() -> List[str]:
     """Attention-backend fixtures (oracle/gen_golden.py)."""
-    return sorted(p for p in glob.glob(os.path.join(GOLDEN_DIR, "*.pt")) if not os.path.basename(p).startswith(("rope_", "alloc_")))
+    other = ("rope_", "alloc_", "swa_", "verify_", "mrope_", "merge_", "radix_")
+    return sorted(p for p in glob.glob(os.path.join(GOLDEN_DIR, "*.pt")) if not os.path.basename(p).startswith(other))
+
+
+def feature_golden_files() -> List[str]:
+    """Sliding-window and TARGET_VERIFY custom-mask fixtures from the reference kit's own fp32 references
+    (oracle/gen_golden_features.py)."""
+    return sorted(glob.glob(os.path.join(GOLDEN_DIR, "swa_*.pt")) + glob.glob(os.path.join(GOLDEN_DIR, "verify_*.pt")))
+
+
+def feature_pool(g: dict):
+    """Rebuild the (k, v) pool of a feature fixture from its referenced rows (all other slots are zero)."""
+    shape = (g["pool_slots_total"],) + tuple(g["k_pool_rows"].shape[1:])
+    kc = torch.zeros(shape, dtype=g["k_pool_rows"].dtype)
+    vc = torch.zeros(shape, dtype=g["v_pool_rows"].dtype)
+    kc[g["pool_slots"]] = g["k_pool_rows"]
+    vc[g["pool_slots"]] = g["v_pool_rows"]
+    return kc, vc
 
 
 def rope_golden_files() -> List[str]:
