@@ -86,17 +86,66 @@ class MRotaryEmbedding(RotaryEmbedding):
         self.mrope_interleaved = mrope_interleaved
 
 
+def mrope_rope_index(input_ids: torch.Tensor, image_grid_thw: Optional[torch.Tensor], *, image_token_id: int,
+                     vision_start_token_id: int, spatial_merge_size: int = 2) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Per-request M-RoPE positions ``int64[3, L]`` and ``mrope_position_delta`` for a Qwen2-VL / Qwen2.5-VL prompt
+    of text runs and still-image blocks (``get_rope_index``, python/sglang/srt/layers/rotary_embedding/
+    mrope_rope_index.py:46-230, image branch): a text run advances all three axes together from ``max + 1`` of what
+    came before; an image block of grid ``(t, h, w)`` (``h, w`` divided by ``spatial_merge_size``) holds the t axis
+    at its frame index (0 for still images in both model types) and walks the h / w axes over the grid, all offset
+    by the block's start.  ``delta = max position + 1 - L``."""
+    ids = input_ids.tolist()
+    L = len(ids)
+    out, st, img, nxt = [], 0, 0, 0
+    starts = [i for i, t in enumerate(ids) if t == vision_start_token_id and i + 1 < L and ids[i + 1] == image_token_id]
+    for _ in starts:
+        ed = ids.index(image_token_id, st)
+        t, h, w = (int(x) for x in image_grid_thw[img])
+        img += 1
+        gh, gw = h // spatial_merge_size, w // spatial_merge_size
+        text_len = ed - st
+        out.append(torch.arange(text_len, dtype=torch.int64).view(1, -1).expand(3, -1) + nxt)
+        ti = torch.arange(t, dtype=torch.int64).view(-1, 1, 1).expand(t, gh, gw).reshape(-1)
+        if t == 1:
+            ti = torch.zeros_like(ti)
+        hi = torch.arange(gh, dtype=torch.int64).view(1, -1, 1).expand(t, gh, gw).reshape(-1)
+        wi = torch.arange(gw, dtype=torch.int64).view(1, 1, -1).expand(t, gh, gw).reshape(-1)
+        out.append(torch.stack([ti, hi, wi]) + text_len + nxt)
+        nxt = int(out[-1].max()) + 1
+        st = ed + t * gh * gw
+    if st < L:
+        out.append(torch.arange(L - st, dtype=torch.int64).view(1, -1).expand(3, -1) + nxt)
+    pos = torch.cat(out, dim=1) if out else torch.zeros((3, 0), dtype=torch.int64)
+    delta = torch.tensor([[int(pos.max()) + 1 - L if L else 0]], dtype=torch.int64)
+    return pos, delta
+
+
+def _expand_mrope_from_input(mm_positions: Optional[torch.Tensor], delta, seq_len: int) -> torch.Tensor:
+    """ONE position column for a request that is past its precomputed table (forward_batch_info.py:1103-1127)."""
+    if mm_positions is not None and mm_positions.shape[1] >= seq_len:
+        return mm_positions[:, seq_len - 1:seq_len].to(torch.int64)
+    d = torch.as_tensor(delta, dtype=torch.int64).flatten()
+    return (d - 1).unsqueeze(0).repeat(3, 1) + seq_len
+
+
 def mrope_positions_extend(prefix_lens: Sequence[int], extend_lens: Sequence[int],
-                           mm_positions: Sequence[Optional[torch.Tensor]]) -> torch.Tensor:
+                           mm_positions: Sequence[Optional[torch.Tensor]],
+                           deltas: Optional[Sequence] = None) -> torch.Tensor:
     """``int64[3, T]`` for an extend batch: text-only requests get ``arange(prefix, prefix+extend)`` on all
-    three axes, multimodal ones the slice of their precomputed ``mrope_positions``
-    (forward_batch_info.py:1213-1254)."""
+    three axes, multimodal ones the slice of their precomputed ``mrope_positions``; a request whose slice is empty
+    (already past its table) takes the single delta-based column of ``_expand_mrope_from_input``, as the reference
+    does (forward_batch_info.py:1213-1254)."""
     out = []
-    for pre, ext, mm in zip(prefix_lens, extend_lens, mm_positions):
+    for b, (pre, ext, mm) in enumerate(zip(prefix_lens, extend_lens, mm_positions)):
         if mm is None:
             out.append(torch.arange(pre, pre + ext, dtype=torch.int64).unsqueeze(0).repeat(3, 1))
-        else:
-            out.append(mm[:, pre:pre + ext].to(torch.int64))
+            continue
+        sl = mm[:, pre:pre + ext].to(torch.int64)
+        if sl.numel() == 0:
+            if deltas is None:
+                raise ValueError("mrope_positions_extend: a request past its position table needs its delta")
+            sl = _expand_mrope_from_input(mm, deltas[b], pre + ext)
+        out.append(sl)
     return torch.cat(out, dim=1) if out else torch.zeros((3, 0), dtype=torch.int64)
 
 
@@ -104,5 +153,6 @@ def mrope_positions_decode(seq_lens: torch.Tensor, deltas: Optional[Sequence[int
     """``(delta - 1) + seq_len`` on all three axes (forward_batch_info.py:1166-1184)."""
     p = seq_lens.to(torch.int64) - 1
     if deltas is not None:
-        p = p + torch.as_tensor(list(deltas), dtype=torch.int64, device=seq_lens.device)
+        p = p + torch.as_tensor([int(torch.as_tensor(d).flatten()[0]) if d is not None else 0 for d in deltas],
+                                dtype=torch.int64, device=seq_lens.device)
     return p.unsqueeze(0).repeat(3, 1)
