@@ -35,6 +35,9 @@ except Exception:  # standalone: same contract, defined locally
         def init_forward_metadata_in_graph(self, forward_batch):
             pass
 
+        def on_after_cuda_graph_warmup(self):  # base_attn_backend.py:190-197
+            pass
+
         def forward(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, **kwargs):
             mode = forward_batch.forward_mode
             if mode.is_idle():
