@@ -149,6 +149,18 @@ def load() -> C.CDLL:
     return lib
 
 
+def load_variant(path: str) -> C.CDLL:
+    """A second build of the same C ABI (e.g. the checker build libb200attn_serial.so), typed like the product one."""
+    lib = C.CDLL(path)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    if lib.b200attn_abi_version() != ABI_VERSION:
+        raise ImportError(f"{path}: ABI version {lib.b200attn_abi_version()} != {ABI_VERSION}")
+    return lib
+
+
 def check(rc: int, what: str) -> None:
     if rc != 0:
         msg = load().b200attn_last_error().decode("utf-8", "replace")

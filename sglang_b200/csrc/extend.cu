@@ -493,6 +493,12 @@ __global__ void __launch_bounds__(kExtThreads, 1)
                 tc_fence_after();
                 TRACE(2, c, 3 * i + 1);
                 issue_pv(c);
+#ifdef EXT_SERIAL_PVQK
+                // checker build (libb200attn_serial.so, tests/test_extend_determinism_gpu.py): PV_i(c) has COMPLETED
+                // before QK_i(c+2) may overwrite the TMEM columns it reads P from; the product build relies on the
+                // tensor pipe executing one thread's tcgen05.mma in issue order instead
+                if (c + 2 < nc_i) mbar_wait(barb + 8u * (kBarPVDone + i), (g + c) & 1);
+#endif
                 if (c + 2 < nc_i) issue_qk(c + 2);
                 TRACE(2, c, 3 * i + 2);
               }

@@ -100,7 +100,7 @@ def main() -> int:
     n_pass = sum(r[1] == "PASS" for r in results)
     n_fail = sum(r[1] == "FAIL" for r in results)
     n_skip = sum(r[1] == "SKIP" for r in results)
-    lines = [f"reference dense-attention kit vs registered 'b200' backend ({torch.cuda.get_device_name(0)})",
+    lines = [f"reference dense-attention kit vs registered 'b200' backend ({torch.cuda.get_device_name(0) if torch.cuda.is_available() else 'no GPU'})",
              f"reference tree: {root}; torch {torch.__version__}",
              f"{n_pass} passed, {n_fail} failed, {n_skip} skipped of {len(results)}", ""]
     lines += [f"{st:4s} {label}" + (f"   {msg}" if msg else "") for label, st, msg in results]
