@@ -129,3 +129,74 @@ def assert_close_attn(actual: torch.Tensor, expected: torch.Tensor, what: str = 
     bad = err > tol
     assert not bad.any(), (f"{what}: {int(bad.sum())}/{bad.numel()} elements out of tolerance, "
                            f"max abs err {float(err.max()):.4e}")
+
+
+def attention_fp32_blocked(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, req_to_token: torch.Tensor,
+                           req_pool_indices, seq_lens: Sequence[int], extend_lens: Sequence[int], Hq: int, Hkv: int,
+                           D: int, scaling: float, causal: bool, qblock: int = 1024) -> torch.Tensor:
+    """fp32-softmax reference for FULL-SIZE configs on the GPU: the same arithmetic as `oracle.attention_fp32`
+    (the kit's `_dense_attention_reference`, dense_attention.py:802-855), evaluated per (request, kv head, block of
+    query rows) so that an 8192 x 16384 score matrix never exists at once.  Test infrastructure only."""
+    T = q.shape[0]
+    G = Hq // Hkv
+    out = torch.empty((T, Hq, D), dtype=torch.float32, device=q.device)
+    q3 = q.view(T, Hq, D)
+    start = 0
+    for i, (L, E) in enumerate(zip(seq_lens, extend_lens)):
+        L, E = int(L), int(E)
+        tokens = req_to_token[int(req_pool_indices[i]), :L].long()
+        K, V = k_cache[tokens], v_cache[tokens]          # [L, Hkv, D]
+        kpos = torch.arange(L, device=q.device).view(1, 1, L)
+        for h in range(Hkv):
+            Kh, Vh = K[:, h].float(), V[:, h].float()    # [L, D]
+            for r0 in range(0, E, qblock):
+                r1 = min(E, r0 + qblock)
+                qb = q3[start + r0:start + r1, h * G:(h + 1) * G].float()           # [qb, G, D]
+                s = torch.einsum("egd,ld->gel", qb, Kh) * scaling
+                if causal:
+                    qpos = torch.arange(L - E + r0, L - E + r1, device=q.device).view(1, -1, 1)
+                    s = s.masked_fill(kpos > qpos, float("-inf"))
+                p = torch.softmax(s, dim=-1)
+                out[start + r0:start + r1, h * G:(h + 1) * G] = torch.einsum("gel,ld->egd", p, Vh)
+        start += E
+    return out.view(T, Hq * D)
+
+
+def make_scenario_gpu(prefix_lens: Sequence[int], extend_lens: Sequence[int], Hq: int, Hkv: int, D: int,
+                      page_size: int, device: str = "cuda", seed: int = 0, shared_prefix_pages: int = 0,
+                      pool_slack: float = 1.1) -> Scenario:
+    """`make_scenario` for full-size configs: the page permutation is drawn on the CPU (small), the pool and the
+    activations are filled on the device (GBs of N(0,1) values)."""
+    g = torch.Generator().manual_seed(seed)
+    B = len(prefix_lens)
+    seq_lens = [p + e for p, e in zip(prefix_lens, extend_lens)]
+    ctx = -(-max(seq_lens) // page_size) * page_size
+    pages_per_req = [-(-s // page_size) for s in seq_lens]
+    need = sum(pages_per_req) - (B - 1) * shared_prefix_pages if shared_prefix_pages else sum(pages_per_req)
+    num_pages = int(need * pool_slack) + 2
+    perm = torch.randperm(num_pages - 1, generator=g) + 1
+    shared = perm[:shared_prefix_pages]
+    nxt = shared_prefix_pages
+    offs = torch.arange(page_size, dtype=torch.int32)
+    table = torch.zeros((B + 1, ctx), dtype=torch.int32)
+    for b in range(B):
+        own = pages_per_req[b] - shared_prefix_pages
+        pages = torch.cat([shared, perm[nxt:nxt + own]]).to(torch.int32)
+        nxt += own
+        row = (pages[:, None] * page_size + offs[None]).reshape(-1)
+        table[b + 1, :row.numel()] = row
+    loc = torch.cat([table[b + 1, prefix_lens[b]:seq_lens[b]].long() for b in range(B)])
+    gg = torch.Generator(device=device).manual_seed(seed)
+    slots = num_pages * page_size
+    kc = torch.empty((slots, Hkv, D), dtype=torch.bfloat16, device=device).normal_(generator=gg)
+    vc = torch.empty((slots, Hkv, D), dtype=torch.bfloat16, device=device).normal_(generator=gg)
+    kc[:page_size] = 0
+    vc[:page_size] = 0
+    T = sum(extend_lens)
+    q = torch.empty((T, Hq * D), dtype=torch.bfloat16, device=device).normal_(generator=gg)
+    k = torch.empty((T, Hkv, D), dtype=torch.bfloat16, device=device).normal_(generator=gg)
+    v = torch.empty((T, Hkv, D), dtype=torch.bfloat16, device=device).normal_(generator=gg)
+    return Scenario(Hq=Hq, Hkv=Hkv, D=D, page_size=page_size, prefix_lens=list(prefix_lens),
+                    extend_lens=list(extend_lens), seq_lens=seq_lens, req_to_token=table.to(device),
+                    req_pool_indices=torch.arange(1, B + 1, dtype=torch.int64, device=device),
+                    out_cache_loc=loc.to(device), k_cache=kc, v_cache=vc, q=q, k=k, v=v, scaling=D ** -0.5)
