@@ -66,14 +66,18 @@ __global__ void __launch_bounds__(256)
   if (isinf(a) && a > 0) a = -INFINITY;  // merge_attn_states.cu:66-67
   if (isinf(b) && b > 0) b = -INFINITY;
   const float m = fmaxf(a, b);
-  float wa, wb, inv;
-  if (m == -INFINITY) {  // both states empty: output zeros, LSE -inf
-    wa = wb = 0.f;
-    inv = 0.f;
+  // same operations in the same order as the reference kernel (merge_attn_states.cu:71-78,95: expf, two divisions
+  // by the sum, p * p_scale + (s * s_scale)), so that the outputs agree bit for bit with merge_state_v2 on every
+  // row it defines; both states empty (where the reference computes -inf - -inf = NaN): zeros and LSE -inf
+  float wa, wb, ca, cb;
+  if (m == -INFINITY) {
+    wa = wb = ca = cb = 0.f;
   } else {
-    wa = __expf(a - m);
-    wb = __expf(b - m);
-    inv = 1.f / (wa + wb);
+    wa = expf(a - m);
+    wb = expf(b - m);
+    const float tot = wa + wb;
+    ca = wa / tot;
+    cb = wb / tot;
   }
   const int64_t off = row * (int64_t)packs_per_row * N + (int64_t)pk * N;
   const uint4 pa = *reinterpret_cast<const uint4*>(va + off);
@@ -82,11 +86,10 @@ __global__ void __launch_bounds__(256)
   const T* ea = reinterpret_cast<const T*>(&pa);
   const T* eb = reinterpret_cast<const T*>(&pb);
   T* eo = reinterpret_cast<T*>(&po);
-  const float ca = wa * inv, cb = wb * inv;
 #pragma unroll
-  for (int i = 0; i < N; ++i) eo[i] = from_f<T>(to_f(ea[i]) * ca + to_f(eb[i]) * cb);
+  for (int i = 0; i < N; ++i) eo[i] = from_f<T>(to_f(ea[i]) * ca + (to_f(eb[i]) * cb));
   *reinterpret_cast<uint4*>(vo + off) = po;
-  if (so != nullptr && pk == 0) so[row] = (m == -INFINITY) ? -INFINITY : __logf(wa + wb) + m;
+  if (so != nullptr && pk == 0) so[row] = (m == -INFINITY) ? -INFINITY : logf(wa + wb) + m;
 }
 
 template <typename T>
