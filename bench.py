@@ -38,6 +38,8 @@ sys.path.insert(0, ROOT)
 CFG2 = dict(B=64, ctx=4096, Hq=32, Hkv=8, D=128, page=16, layers=32)
 CFG3 = dict(B=32, prefix=2048, ext=512, Hq=32, Hkv=8, D=128, page=16)
 SEED = 20261104
+WORKLOAD = ("llama-3.1-8b decode attention layer-call (KV store + paged GQA split-KV decode + merge): "
+            "batch 64 x 4096 ctx, GQA 32q/8kv, head_dim 128, page_size 16 (BASELINE configs[1])")
 
 
 def measured_peaks():
@@ -120,6 +122,39 @@ class ClockSampler:
                     reasons=reasons, samples=len(sm))
 
 
+def sampled_check(q, o, kc, vc, table, req_rows, seq_lens, ext_lens, Hq, Hkv, D, causal, k_mul=1.0, v_mul=1.0,
+                  max_reqs=3, max_rows=48):
+    """Checker for the side legs (never timed): a torch fp32-softmax reference on the GPU for a SAMPLE of the batch
+    (first / middle / last request, the first and last `max_rows / 2` query rows of each), compared with the kernel
+    output at BASELINE's tolerance (1e-2 relative / 2e-2 absolute).  Returns dict(max_abs_err, within_tolerance, rows)."""
+    G = Hq // Hkv
+    B = len(seq_lens)
+    picks = sorted({0, B // 2, B - 1})[:max_reqs]
+    starts = [0]
+    for e in ext_lens:
+        starts.append(starts[-1] + int(e))
+    worst, ok, nrows = 0.0, True, 0
+    for b in picks:
+        L, E = int(seq_lens[b]), int(ext_lens[b])
+        rows = sorted(set(list(range(min(E, max_rows // 2))) + list(range(max(0, E - max_rows // 2), E))))
+        tok = table[int(req_rows[b]), :L].long()
+        K = kc[tok].float().mul_(k_mul).repeat_interleave(G, dim=1)   # [L, Hq, D]
+        V = vc[tok].float().mul_(v_mul).repeat_interleave(G, dim=1)
+        r = torch.tensor(rows, device=q.device)
+        qq = q.view(-1, Hq, D)[starts[b] + r].float()
+        sc = torch.einsum("ehd,lhd->hel", qq, K) * (D ** -0.5)
+        if causal:
+            qpos = (L - E + r).view(1, -1, 1)
+            sc = sc.masked_fill(torch.arange(L, device=q.device).view(1, 1, L) > qpos, float("-inf"))
+        ref = torch.einsum("hel,lhd->ehd", torch.softmax(sc, dim=-1), V)
+        got = o.view(-1, Hq, D)[starts[b] + r].float()
+        err = (got - ref).abs()
+        worst = max(worst, float(err.max()))
+        ok = ok and bool((err <= 2e-2 + 1e-2 * ref.abs()).all()) and bool(torch.isfinite(got).all())
+        nrows += len(rows)
+    return dict(max_abs_err=worst, within_tolerance=ok, rows_checked=nrows, requests_checked=picks)
+
+
 # ---- synthetic state ------------------------------------------------------------
 def build_decode_state(c, device, gen):
     """Pool, req_to_token (random pages per request, page 0 reserved) and one step's inputs."""
@@ -152,6 +187,19 @@ class Runner:
         self.device, self.page_size = device, page
         self.req_to_token_pool, self.token_to_kv_pool = req_pool, kv_pool
         self.sliding_window_size = None
+
+
+SIDE_STEPS, SIDE_WARMUP = 20, 5  # every side leg: >= 20 timed launches after >= 5 warm-ups
+
+
+def max_over_ranks(ms, dev):
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized()):
+        return ms
+    t = torch.tensor([ms], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t)
 
 
 def time_steps(fn, steps, warmup, barrier=None):
@@ -224,9 +272,7 @@ def run_reference(args, rank, world):
         impl="reference", metric="decode_attn_hbm_gbs", value=gbs, unit="GB/s", n_gpus=args.gpus, steps=args.steps,
         warmup=args.warmup, ms_per_step=sec * 1e3, higher_is_better=True, scaling="weak", vs_baseline=None,
         dtype="bf16", data="synthetic",
-        config=dict(workload="llama-3.1-8b decode attention layer-call: batch 64 x 4096 ctx, GQA 32q/8kv, "
-                             "head_dim 128, page_size 16 (BASELINE configs[1])",
-                    sample=f"{sample_B} of 64 requests per step, full 4096-key contexts (the whole workload)"),
+        config=dict(workload=WORKLOAD),
         cpu_baseline=dict(value=gbs, unit="GB/s", cores=threads, kind="port",
                           sample=f"{sample_B} of 64 requests x 4096 ctx per call, median of {max(args.steps, 1)}"),
         e2e=dict(value=gbs, unit="GB/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
@@ -283,14 +329,35 @@ def run_b200(args, rank, world, local_rank):
     md = backend.forward_metadata
     kbuf, vbuf = kv_pool.get_kv_buffer(0)
     max_splits = ops.pick_max_splits(B, Hkv, Hq // Hkv, c["ctx"], md.min_chunk)
-    launches_per_step = 2 + (1 if max_splits > 1 else 0)
+    launches_per_step = 2  # kv_store_kernel + decode_kernel (split partials are merged inside the decode kernel)
 
-    # (1) the step: store + decode attention (+ merge), inputs resident in HBM
+    # (1) the step: store + decode attention (+ in-kernel merge), inputs resident in HBM.  The layer-call is captured
+    #     ONCE into a CUDA graph and replayed per step - the way SGLang's decode runner drives a backend
+    #     (decode_cuda_graph_runner.py:1148-1363) - so the host launch gap between the store and the decode kernel
+    #     (two eager ctypes launches from Python) is not part of the number.  `eager_ms_per_step` keeps the eager loop.
     def step():
         return layer(devt["q"], devt["k"], devt["v"], fb)
 
+    o_eager = step().clone()
+    side0 = torch.cuda.Stream()
+    side0.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side0):
+        step()
+        torch.cuda.synchronize()
+        step_graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(step_graph, stream=side0):
+            o_graph = step()
+    torch.cuda.current_stream().wait_stream(side0)
+    step_graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(o_graph, o_eager), "captured layer-call disagrees with the eager one"
+    head_check = sampled_check(devt["q"], o_graph, kbuf, vbuf, req_pool.req_to_token, host["req_pool_indices"],
+                               [c["ctx"]] * B, [1] * B, Hq, Hkv, D, causal=False)
+    assert head_check["within_tolerance"], f"cfg2 decode output out of tolerance: {head_check}"
+
     clk = ClockSampler(local_rank).__enter__()
-    total_ms = time_steps(step, args.steps, args.warmup, barrier)
+    eager_ms = time_steps(step, args.steps, args.warmup, barrier) / args.steps
+    total_ms = time_steps(step_graph.replay, args.steps, args.warmup, barrier)
     if world > 1:
         t = torch.tensor([total_ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -325,20 +392,22 @@ def run_b200(args, rank, world, local_rank):
         backend.init_forward_metadata(fb)
         o_host.copy_(layer(devt["q"], devt["k"], devt["v"], fb), non_blocking=True)
 
-    def best_of(fn, reps=3):
-        """K timed steps, max over ranks, repeated `reps` times; the fastest repetition counts (the region is ~10 ms of
-        host<->device traffic: one host hiccup moves it by 10-20 %, measured 225 / 247 / 240 us on the same box)."""
-        best = None
+    E2E_REPS = 5
+
+    def median_of(fn, reps=E2E_REPS):
+        """K timed steps (max over ranks), repeated `reps` times; returns (median, min, max) ms per step.  The MEDIAN
+        repetition is what is reported."""
+        out = []
         for _ in range(reps):
             ms = time_steps(fn, args.steps, args.warmup, barrier)
             if world > 1:
                 t = torch.tensor([ms], device=dev)
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
                 ms = float(t)
-            best = ms if best is None else min(best, ms)
-        return best / args.steps
+            out.append(ms / args.steps)
+        return statistics.median(out), min(out), max(out)
 
-    e2e_ms = best_of(e2e_step)
+    e2e_ms, e2e_lo, e2e_hi = median_of(e2e_step)
     e2e_val = world * nbytes / (e2e_ms * 1e-3) / 1e9
 
     # (3b) the same step the way SGLang's decode runner drives a backend (decode_cuda_graph_runner.py:1148-1363):
@@ -397,28 +466,26 @@ def run_b200(args, rank, world, local_rank):
             with torch.cuda.graph(g_, stream=side):
                 graph_body(fused)
         torch.cuda.current_stream().wait_stream(side)
-        return best_of(g_.replay), g_
+        return median_of(g_.replay), g_
 
-    e2e_sep_ms, graph = time_graph(False)
+    (e2e_sep_ms, sep_lo, sep_hi), graph = time_graph(False)
     o_sep = o_host.clone()
-    # the fused-layout graph is bimodal ACROSS captures on the same box (225 vs 275-290 us per step; the separate
-    # graph and the eager loop are not): capture it up to three times and keep the fastest instance
-    e2e_graph_ms, graph2, captures = None, None, 0
-    while captures < 3:
-        ms_, g_ = time_graph(True)
-        captures += 1
-        if e2e_graph_ms is None or ms_ < e2e_graph_ms:
-            e2e_graph_ms, graph2 = ms_, g_
-        if world > 1 or e2e_graph_ms < 0.97 * min(e2e_sep_ms, e2e_ms):
-            break  # multi-rank: every rank must take the same number of captures
+    # HEADLINE e2e driver, fixed a priori: ONE captured graph per step over the model's fused-qkv layout (the path
+    # SGLang's decode runner takes), ONE capture, median of E2E_REPS repetitions.  The other two drivers (six-tensor
+    # graph, eager loop) are side keys.  Round 1 saw this graph come out bimodal ACROSS captures (225 vs 275-290 us);
+    # that is reported, not selected away: two further captures are timed and listed in `capture_spread_ms` (N = 1).
+    (e2e_graph_ms, fused_lo, fused_hi), graph2 = time_graph(True)
     torch.cuda.synchronize()
     assert torch.equal(o_sep, o_host), "fused-layout e2e step disagrees with the separate-tensor step"
+    capture_spread = [e2e_graph_ms]
+    if world == 1:
+        for _ in range(2):
+            (ms_, _, _), g_ = time_graph(True)
+            capture_spread.append(ms_)
+            del g_
     e2e_sep_val = world * nbytes / (e2e_sep_ms * 1e-3) / 1e9
     fused_ms = e2e_graph_ms
-    # headline e2e = the fastest of the three drivers of the SAME public API on the same bytes; all three are reported
-    variants = {"graph_fused_layout": e2e_graph_ms, "graph_separate_tensors": e2e_sep_ms, "eager": e2e_ms}
-    e2e_driver = min(variants, key=variants.get)
-    e2e_graph_ms = variants[e2e_driver]
+    e2e_driver = "graph_fused_layout"
     e2e_graph_val = world * nbytes / (e2e_graph_ms * 1e-3) / 1e9
 
     # (4) extend leg (configs[2]): 32 requests sharing a 2048-token prefix + 512 new tokens, causal
@@ -449,12 +516,34 @@ def run_b200(args, rank, world, local_rank):
             [2048] * 32, [512] * 32, 32, 8, 128, 16, True, "EXTEND", shared_prefix=2048, fp8_kv=True)
         torch.cuda.empty_cache()
         # configs[4]: Llama-3.1-70B attention shape, this rank's KV-head shard
-        extra["cfg5_decode"] = run_cfg5_decode(dev, gen, peaks, world)
+        # STRONG scaling (the partitioning north_star names): the SAME total work - 8 kv heads / 64 q heads - cut into
+        # Hkv = 8 / N per rank; every leg barrier-to-barrier, max over ranks.  t1 (the unsharded shape) is measured
+        # in the same run on every rank, so efficiency = t1 / (N * tN) needs no second invocation.
+        extra["cfg5_decode"] = run_cfg5_decode(dev, gen, peaks, world, barrier=barrier)
         torch.cuda.empty_cache()
         extra["cfg5_chunked_prefill"] = run_backend_case(
             dev, gen, peaks, f"llama-3.1-70b chunked prefill shard: prefix 8192 + 8192 new, causal, Hq {64 // world} "
             f"/ Hkv {max(1, 8 // world)} per GPU of {world} (BASELINE configs[4])", [8192], [8192], 64 // world,
-            max(1, 8 // world), 128, 16, True, "EXTEND")
+            max(1, 8 // world), 128, 16, True, "EXTEND", barrier=barrier)
+        torch.cuda.empty_cache()
+        if world > 1:
+            full_dec = run_cfg5_decode(dev, gen, peaks, 1, barrier=barrier)
+            torch.cuda.empty_cache()
+            full_pre = run_backend_case(dev, gen, peaks, "llama-3.1-70b chunked prefill, unsharded (Hq 64 / Hkv 8)",
+                                        [8192], [8192], 64, 8, 128, 16, True, "EXTEND", barrier=barrier)
+            torch.cuda.empty_cache()
+        else:
+            full_dec, full_pre = extra["cfg5_decode"], extra["cfg5_chunked_prefill"]
+        extra["scaling_strong"] = dict(
+            workload="llama-3.1-70b attention (BASELINE configs[4]) head-sharded over N GPUs: decode 256 x 8192 ctx + "
+                     "8192-token chunked prefill over an 8192-token prefix; total work fixed (8 kv heads)",
+            n_gpus=world, timing="barrier-to-barrier, max over ranks; t1 = the unsharded shape timed in this same run",
+            decode=dict(t1_ms=full_dec["kernel_ms"], tN_ms=extra["cfg5_decode"]["kernel_ms"],
+                        efficiency=full_dec["kernel_ms"] / (world * extra["cfg5_decode"]["kernel_ms"]),
+                        aggregate_gbs=world * extra["cfg5_decode"]["gbs"]),
+            chunked_prefill=dict(t1_ms=full_pre["ms_per_step"], tN_ms=extra["cfg5_chunked_prefill"]["ms_per_step"],
+                                 efficiency=full_pre["ms_per_step"] / (world * extra["cfg5_chunked_prefill"]["ms_per_step"]),
+                                 aggregate_tflops=world * extra["cfg5_chunked_prefill"]["tflops"]))
     clk.__exit__()
     clocks = clk.summary()
 
@@ -472,35 +561,35 @@ def run_b200(args, rank, world, local_rank):
     line = dict(
         metric="decode_attn_hbm_gbs", value=value, unit="GB/s", n_gpus=world, steps=args.steps, warmup=args.warmup,
         ms_per_step=ms_step, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="bf16", data="synthetic",
-        config=dict(workload="llama-3.1-8b decode attention layer-call (KV store + paged GQA split-KV decode + merge): "
-                             "batch 64 x 4096 ctx, GQA 32q/8kv, head_dim 128, page_size 16 (BASELINE configs[1])",
+        config=dict(workload=WORKLOAD,
                     parallelism=f"kv-head sharded x{world} (8 kv heads per GPU), no collective",
-                    l2="inputs larger than L2 (1.07 GB KV per call vs 126 MB)", max_splits=max_splits),
+                    l2="inputs larger than L2 (1.07 GB KV per call vs 126 MB)", max_splits=max_splits,
+                    step_driver="one CUDA graph replay per step (store + decode captured once)"),
+        eager_ms_per_step=eager_ms, output_check=head_check,
         roofline=dict(bound="hbm", achieved=achieved, peak=peaks["hbm"], unit="GB/s", frac=achieved / peaks["hbm"],
                       traffic=ncu_traffic("decode_kernel<128,bf16> cfg2") if world == 1 else None,
                       kernel="decode_kernel<128,bf16> (+merge)", kernel_ms=kern_ms,
                       peak_source=peaks["src"], frac_of_8tbs=achieved / 8000.0),
         cpu_baseline=cpu,
         e2e=dict(value=e2e_graph_val, unit="GB/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h,
-                 ms_per_step=e2e_graph_ms, host_placement=numa_note, driver=e2e_driver,
-                 graph_fused_layout=dict(ms_per_step=fused_ms, captures=captures,
-                                         value=world * nbytes / (fused_ms * 1e-3) / 1e9),
+                 ms_per_step=e2e_graph_ms, ms_min=fused_lo, ms_max=fused_hi, repetitions=E2E_REPS,
+                 host_placement=numa_note, driver=e2e_driver, capture_spread_ms=capture_spread,
                  mode="B200AttnBackend behind one CUDA graph per step (pinned-host H2D copies, metadata refill, "
                       "store + decode, D2H read all captured; SGLang's decode-runner path); inputs in the model's "
                       "layout: one fused [B, (Hq+2Hkv)*D] qkv activation + one int64 [3, B] index block = 2 H2D copies; "
-                      "fastest of 3 repetitions of K steps (every e2e variant here is timed that way); `driver` names which "
-                      "of the three variants (this graph, the six-tensor graph, the eager loop) was fastest and is "
-                      "reported as `value`",
-                 separate_tensors=dict(value=e2e_sep_val, ms_per_step=e2e_sep_ms,
+                      "ONE capture, value = MEDIAN of 5 repetitions of K steps (min / max beside it); "
+                      "`capture_spread_ms` = the medians of this capture and two more captures of the same graph",
+                 separate_tensors=dict(value=e2e_sep_val, ms_per_step=e2e_sep_ms, ms_min=sep_lo, ms_max=sep_hi,
                                        mode="same graph with q, k, v and the three index vectors as six host "
                                             "tensors = 6 H2D copies"),
-                 eager=dict(value=e2e_val, ms_per_step=e2e_ms,
+                 eager=dict(value=e2e_val, ms_per_step=e2e_ms, ms_min=e2e_lo, ms_max=e2e_hi,
                             mode="same step launched eagerly from Python (CPU-launch-bound)")),
         gpu_launches=launches_per_step * args.steps,
         clocks=clocks,
         extend=ext,
         other_configs=extra,
-        tokens_per_s_attention_only=world * B / (c["layers"] * ms_step * 1e-3),
+        # weak scaling of a head-sharded model N times as wide: every rank serves the SAME B tokens
+        tokens_per_s_attention_only=B / (c["layers"] * ms_step * 1e-3),
     )
     print(json.dumps(line), flush=True)
 
@@ -547,20 +636,23 @@ def run_extend_leg(args, dev, gen, peaks):
         ops.extend_attention(q, kc, vc, o, qo_indptr, kv_indptr, kv_indices, D ** -0.5, causal=True,
                              page_size=page, max_qo_len=E)
 
-    steps = max(args.steps // 4, 3)
-    ms = time_steps(step, steps, args.warmup) / steps
-    kms = time_steps(kern, steps, args.warmup) / steps
+    steps = max(args.steps, SIDE_STEPS)
+    ms = time_steps(step, steps, max(args.warmup, SIDE_WARMUP)) / steps
+    kms = time_steps(kern, steps, max(args.warmup, SIDE_WARMUP)) / steps
     fl = extend_flops(c)
     tf = fl / (kms * 1e-3) / 1e12
+    check = sampled_check(q, o, kc, vc, table, list(range(1, B + 1)), [P + E] * B, [E] * B, Hq, Hkv, D, causal=True)
+    assert check["within_tolerance"], f"cfg3 extend output out of tolerance: {check}"
     return dict(workload="llama-3.1-8b extend: 32 req x (2048 shared prefix + 512 new), causal (BASELINE configs[2])",
                 ms_per_step=ms, kernel_ms=kms, tflops=tf, flops=fl, tokens_per_s_attention_only=T / (32 * ms * 1e-3),
+                timed_launches=steps, output_check=check,
                 roofline=dict(bound="tensor", achieved=tf, peak=peaks["tf_burst"], unit="TFLOP/s",
                               frac=tf / peaks["tf_burst"], frac_of_2250=tf / 2250.0, peak_source=peaks["src"],
                               traffic=ncu_traffic("extend_kernel<128,bf16> cfg3")))
 
 
 def run_backend_case(dev, gen, peaks, label, prefix_lens, ext_lens, Hq, Hkv, D, page, causal, mode_name,
-                     shared_prefix=0, steps=6, warmup=3, fp8_kv=False):
+                     shared_prefix=0, steps=SIDE_STEPS, warmup=SIDE_WARMUP, fp8_kv=False, barrier=None):
     """One ragged extend / MIXED layer-call through B200AttnBackend (store + attention), inputs resident in
     HBM.  `shared_prefix` leading tokens of every request map to the SAME physical pages (radix hit).
     FLOPs are algorithmic: 4*D per (q head, query, visible key); rows with extend_len 1 count as bytes."""
@@ -608,7 +700,14 @@ def run_backend_case(dev, gen, peaks, label, prefix_lens, ext_lens, Hq, Hkv, D, 
                       extend_seq_lens_cpu=list(ext_lens), extend_prefix_lens_cpu=list(prefix_lens),
                       attn_backend=backend)
     backend.init_forward_metadata(fb)
-    ms = time_steps(lambda: layer(q, k, v, fb), steps, warmup) / steps
+    o = layer(q, k, v, fb)
+    kb, vb = kv_pool.get_kv_buffer(0)
+    check = sampled_check(q, o, kb, vb, req_pool.req_to_token, list(range(1, B + 1)), seq, ext_lens, Hq, Hkv, D,
+                          causal=causal, k_mul=0.5 if fp8_kv else 1.0, v_mul=0.5 if fp8_kv else 1.0)
+    assert check["within_tolerance"], f"{label}: output out of tolerance: {check}"
+    ms = time_steps(lambda: layer(q, k, v, fb), steps, warmup, barrier) / steps
+    if barrier is not None:
+        ms = max_over_ranks(ms, dev)
     pairs = 0
     dec_bytes = 0
     for p_, e in zip(prefix_lens, ext_lens):
@@ -619,7 +718,8 @@ def run_backend_case(dev, gen, peaks, label, prefix_lens, ext_lens, Hq, Hkv, D, 
     fl = 4 * D * Hq * pairs
     tf = fl / (ms * 1e-3) / 1e12
     return dict(workload=label, ms_per_step=ms, flops=fl, tflops=tf, decode_row_kv_bytes=dec_bytes, tokens=T,
-                frac_of_measured_bf16=tf / peaks["tf_burst"], frac_of_2250=tf / 2250.0)
+                frac_of_measured_bf16=tf / peaks["tf_burst"], frac_of_2250=tf / 2250.0, timed_launches=steps,
+                output_check=check)
 
 
 def run_cfg1(dev, gen, steps=50, warmup=5):
@@ -670,7 +770,7 @@ def run_cfg1(dev, gen, steps=50, warmup=5):
                 max_abs_err=float(err.max()), within_tolerance=ok)
 
 
-def run_cfg2_decode_fp8(dev, gen, peaks, steps=20, warmup=5):
+def run_cfg2_decode_fp8(dev, gen, peaks, steps=SIDE_STEPS, warmup=SIDE_WARMUP):
     """BASELINE configs[1] shape with an e4m3 KV pool (k/v descale 0.5): decode_fp8_kernel alone, CUDA events."""
     from sglang_b200 import ops
 
@@ -690,18 +790,23 @@ def run_cfg2_decode_fp8(dev, gen, peaks, steps=20, warmup=5):
     ws = torch.zeros(max(ops.decode_workspace_bytes(B, Hq, D, ms_), 16), dtype=torch.uint8, device=dev)
     f = lambda: ops.decode_attention(q, k8, v8, o, kv_indptr, kv_indices, D ** -0.5, max_splits=ms_, min_chunk=256,
                                      workspace=ws, tail_begin=tail_begin, k_descale=0.5, v_descale=0.5)
+    f()
+    check = sampled_check(q, o, k8, v8, req_pool.req_to_token, list(range(1, B + 1)), [c["ctx"]] * B, [1] * B, Hq, Hkv, D,
+                          causal=False, k_mul=0.5, v_mul=0.5)
+    assert check["within_tolerance"], f"cfg2 fp8 decode output out of tolerance: {check}"
     t = time_steps(f, steps, warmup) / steps
     nbytes = 2 * B * c["ctx"] * Hkv * D + 2 * B * Hq * D * 2 + 4 * B * c["ctx"]
     gbs = nbytes / (t * 1e-3) / 1e9
     return dict(workload="llama-3.1-8b decode over a float8_e4m3fn KV pool: batch 64 x 4096 ctx, GQA 32q/8kv, "
                          "head_dim 128, page_size 16", kernel="decode_fp8_kernel<128,bf16>", kernel_ms=t, bytes=nbytes,
                 tail_split=[tail_begin, ms_],
-                gbs=gbs, frac_of_measured_hbm=gbs / peaks["hbm"], frac_of_8tbs=gbs / 8000.0,
-                bf16_pool_equivalent_gbs=(nbytes + 2 * B * c["ctx"] * Hkv * D) / (t * 1e-3) / 1e9)
+                gbs=gbs, frac_of_measured_hbm=gbs / peaks["hbm"], frac_of_8tbs=gbs / 8000.0, timed_launches=steps,
+                output_check=check, bf16_pool_equivalent_gbs=(nbytes + 2 * B * c["ctx"] * Hkv * D) / (t * 1e-3) / 1e9)
 
 
-def run_cfg5_decode(dev, gen, peaks, world, steps=10, warmup=3):
-    """BASELINE configs[4](i): Llama-3.1-70B decode, batch 256 x 8192 ctx, this rank's KV-head shard (Hkv 8/N)."""
+def run_cfg5_decode(dev, gen, peaks, world, steps=SIDE_STEPS, warmup=SIDE_WARMUP, barrier=None):
+    """BASELINE configs[4](i): Llama-3.1-70B decode, batch 256 x 8192 ctx, this rank's KV-head shard (Hkv 8/N).
+    With `barrier`: barrier-to-barrier, max over ranks."""
     from sglang_b200 import ops
 
     c = dict(B=256, ctx=8192, Hq=64 // world, Hkv=max(1, 8 // world), D=128, page=16, layers=80)
@@ -718,11 +823,18 @@ def run_cfg5_decode(dev, gen, peaks, world, steps=10, warmup=3):
     ws = torch.zeros(max(ops.decode_workspace_bytes(B, Hq, D, ms_), 16), dtype=torch.uint8, device=dev)
     f = lambda: ops.decode_attention(q, kbuf, vbuf, o, kv_indptr, kv_indices, D ** -0.5, max_splits=ms_,
                                      min_chunk=256, workspace=ws)
-    t = time_steps(f, steps, warmup) / steps
+    f()
+    check = sampled_check(q, o, kbuf, vbuf, req_pool.req_to_token, list(range(1, B + 1)), [c["ctx"]] * B, [1] * B,
+                          Hq, Hkv, D, causal=False)
+    assert check["within_tolerance"], f"cfg5 decode output out of tolerance: {check}"
+    t = time_steps(f, steps, warmup, barrier) / steps
+    if barrier is not None:
+        t = max_over_ranks(t, dev)
     nbytes = decode_bytes(c) - 2 * 2 * B * Hkv * D * 2
     gbs = nbytes / (t * 1e-3) / 1e9
     return dict(workload=f"llama-3.1-70b decode shard: batch 256 x 8192 ctx, Hq {Hq} / Hkv {Hkv} per GPU of {world} "
                          "(BASELINE configs[4])", kernel_ms=t, bytes=nbytes, gbs=gbs, max_splits=ms_,
+                timed_launches=steps, output_check=check,
                 frac_of_measured_hbm=gbs / peaks["hbm"], frac_of_8tbs=gbs / 8000.0)
 
 
