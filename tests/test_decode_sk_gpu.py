@@ -31,7 +31,7 @@ def _run(sc, lens, q, min_chunk=64, lse=False, dtype=torch.bfloat16, **kw):
         ops.decode_attention(q.to(DEV).view(B, sc.Hq, sc.D), d.k_cache, d.v_cache, o, kv_indptr, kv_indices,
                              sc.scaling, min_chunk=min_chunk, workspace=ws, lse=lse_t, stream_k=True, **kw)
     torch.cuda.synchronize()
-    assert int(ws[-4 * B * sc.Hkv * (-(-(sc.Hq // sc.Hkv) // 16)):].view(torch.int32).abs().sum()) == 0
+    assert int(ws[:4 * 65536].view(torch.int32).abs().sum()) == 0  # the fixed-size counter header is clean again
     return o.view(B, -1), lse_t
 
 
