@@ -54,23 +54,47 @@ def install() -> str:
             ipd.HTML = object
             ipd.display = lambda *a, **k: None
             sys.modules["IPython.display"] = ipd
+    import torch
+
+    if torch.cuda.is_available():
+        # with a CUDA device the reference imports its AOT wheel at module scope throughout srt/ (guarded by
+        # `_is_cuda`); without one it never does, so the stand-in is only installed here
+        try:
+            import sgl_kernel  # noqa: F401
+        except ImportError:
+            if not any(isinstance(f, _MissingFinder) for f in sys.meta_path):
+                sys.meta_path.append(_MissingFinder("sgl_kernel"))
     return root
 
 
-class _Missing(types.ModuleType):
-    """Stand-in for a compiled third-party package the reference imports at module scope but that this image
-    lacks (sgl_kernel: the reference's own AOT wheel, not built here).  Any attribute is a callable that
-    raises when CALLED, so importing the test kits works and only the kernels that are really absent fail."""
+class _Absent:
+    """Placeholder for any object of a package that is not installed: attribute access yields another placeholder
+    (module-scope constant tables such as `scalar_types.uint4b8` import fine), CALLING it raises."""
+
+    def __init__(self, name):
+        self.__dict__["_name"] = name
 
     def __getattr__(self, name):
         if name.startswith("__"):
             raise AttributeError(name)
+        return _Absent(f"{self._name}.{name}")
 
-        def _absent(*a, **k):
-            raise NotImplementedError(f"{self.__name__}.{name} is not available in this image")
+    def __call__(self, *a, **k):
+        raise NotImplementedError(f"{self._name} is not available in this image")
 
-        _absent.__name__ = name
-        return _absent
+    def __repr__(self):
+        return f"<absent {self._name}>"
+
+
+class _Missing(types.ModuleType):
+    """Stand-in for a compiled package the reference imports at module scope but that this image lacks
+    (sgl_kernel: the reference's own AOT wheel, not built here).  Every attribute is an `_Absent` placeholder, so
+    importing the reference works and only kernels that are really absent fail, loudly, when CALLED."""
+
+    def __getattr__(self, name):
+        if name.startswith("__"):
+            raise AttributeError(name)
+        return _Absent(f"{self.__name__}.{name}")
 
 
 class _MissingFinder:
@@ -107,8 +131,9 @@ def import_runner_modes():
     try:
         import sgl_kernel  # noqa: F401
     except ImportError:
-        finder = _MissingFinder("sgl_kernel")
-        sys.meta_path.append(finder)
+        if not any(isinstance(f, _MissingFinder) for f in sys.meta_path):
+            finder = _MissingFinder("sgl_kernel")
+            sys.meta_path.append(finder)
     try:
         dec = importlib.import_module("sglang.test.kits.attention_unittest.runner_modes.cuda_graph_decode_runner")
         tv = importlib.import_module("sglang.test.kits.attention_unittest.runner_modes.speculative_target_verify_runner")
