@@ -1,0 +1,637 @@
+// (a4) Paged GQA decode, warp-specialised persistent kernel fed by TMA (sm_100a).
+//
+// Same arithmetic as decode_kernel (decode.cu: G x D query block padded to the M = 16 of mma.sync.m16n8k16, each
+// of four consumer warps takes 16 keys of a 64-key tile, fp32 online softmax) and the same flat tile-stream work
+// partition as decode_sk_kernel (decode_sk.cu: the batch is ONE unit-major stream of 64-key tiles, CTA c of N owns
+// the contiguous range [c*T/N, (c+1)*T/N), units cut across CTAs are merged by the last piece to arrive).  What
+// changes is how bytes reach shared memory and who waits for them:
+//
+//   warp 4      PRODUCER.  Walks the CTA's tile range and keeps a 3-stage ring (32 KB per stage: K + V of 64
+//               keys) full through the copy engine: per tile the warp reads the 64 slot ids and, when every aligned
+//               16-key group sits in 16 consecutive pool slots (true under the paged allocator for page_size >= 16),
+//               issues 16-row tiled TMA boxes (one instruction per 4 KB); otherwise - page_size 1, fragmented or
+//               ragged last tiles - tile::gather4 (4 arbitrary pool rows per instruction, rows past the end
+//               zero-filled).  It also brings each segment's G x D query block in with one bulk copy, and with
+//               `new_k / new_v` it writes the step's new K/V row into the pool itself right before the tile that
+//               reads it (the separate kv_store launch disappears).  The producer runs AHEAD ACROSS segment
+//               boundaries: while the consumers merge and write a finished unit, the next unit's first tiles and
+//               query block are already landing, so the three dependent DRAM latencies (kv_indptr -> slot ids ->
+//               first K row) that every CTA of decode_kernel pays per unit are paid once per CTA.
+//   warps 0-3   CONSUMERS.  mbarrier-wait on a stage, S = Q K^T and O += P V straight out of the 128B-swizzled
+//               tiles (ldmatrix / .trans), release the stage.  At the end of a segment the four warps merge through
+//               the LAST tile's stage (its 32 KB are exactly the [4][16][D] fp32 scratch the merge needs) before
+//               releasing it, so no shared memory is reserved for the epilogue.
+//
+// Algorithmic bytes per (request, kv head): 2 * L * D * 2 (K and V rows) + 4 * L (slot ids).
+#include "decode.cuh"
+#include "sm100.cuh"
+
+namespace b200attn {
+
+constexpr int kWsThreads = 160;  // 4 consumer warps + 1 producer warp
+constexpr int kWsConsumers = 128;
+constexpr int kWsStages = 3;
+
+struct WsItem {
+  int kv_beg, L, tiles;
+};
+
+__device__ __forceinline__ WsItem ws_item(const DecodeParams& p, int item) {
+  const int req = p.req_ids ? p.req_ids[item] : item;
+  int kv_beg = p.kv_indptr[req];
+  int L = p.kv_indptr[req + 1] - kv_beg;
+  const int lo = window_lo(L, p.window_left);
+  WsItem it;
+  it.kv_beg = kv_beg + lo;
+  it.L = L - lo;
+  it.tiles = max(1, (it.L + kDecTile - 1) / kDecTile);  // an empty request still owns one (fully masked) tile
+  return it;
+}
+
+// CTA that owns global tile g under the partition start(c) = floor(c * T / N)
+__device__ __forceinline__ int ws_owner(int64_t g, int64_t T, int N) {
+  return (int)(((g + 1) * N - 1) / T);
+}
+
+template <int D>
+struct WsSmem {
+  static constexpr int kHalves = D / 64;                    // 64-column (128-byte) halves of a row
+  static constexpr int kHalfBytes = kDecTile * 128;         // 64 rows x 128 B
+  static constexpr int kTileBytes = kHalves * kHalfBytes;   // one operand, one stage
+  static constexpr int kStageBytes = 2 * kTileBytes;        // K + V
+  static constexpr int kRing = 0;
+  static constexpr int kQBytes = kDecMaxG * D * 2;          // one segment's query block
+  static constexpr int kQ = kRing + kWsStages * kStageBytes;
+  static constexpr int kML = kQ + 2 * kQBytes;              // float m[4][16], l[4][16]
+  static constexpr int kBar = kML + 512;
+  static constexpr int kTotal = kBar + 128;
+};
+
+enum WsBar { kWsFull = 0, kWsEmpty = kWsStages, kWsQFull = 2 * kWsStages, kWsQEmpty = 2 * kWsStages + 2, kWsBarCount = 2 * kWsStages + 4 };
+
+// byte offset of 16-byte chunk `chunk` of row `row` inside one operand tile laid out by TMA with SWIZZLE_128B:
+// [half][row][128 B], chunk index XOR (row & 7) inside each 128-byte line (tile base 1024-byte aligned)
+template <int D>
+__device__ __forceinline__ uint32_t ws_off(int row, int chunk) {
+  return (uint32_t)((chunk >> 3) * (kDecTile * 128) + row * 128 + (((chunk & 7) ^ (row & 7)) << 4));
+}
+
+__device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, 128;\n" ::: "memory"); }
+
+struct WsFused {  // the step's new K/V rows, written into the pool by the producer (nullptr: the caller stored them)
+  const void* new_k;
+  const void* new_v;
+  int64_t new_stride;  // elements between token rows of new_k / new_v
+  int skip_slot;       // rows whose slot equals this are not written (the reserved padding slot); -1: write all
+};
+
+template <int D, bool kBf16>
+__global__ void __launch_bounds__(kWsThreads, 2)
+    decode_ws_kernel(const __grid_constant__ CUtensorMap tm_kg, const __grid_constant__ CUtensorMap tm_vg,
+                     const __grid_constant__ CUtensorMap tm_kb, const __grid_constant__ CUtensorMap tm_vb,
+                     const DecodeParams p, const WsFused fused, const int min_tiles, const int num_slots) {
+  using namespace sm100;
+  using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
+  using S = WsSmem<D>;
+  constexpr int kHalves = S::kHalves;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ int64_t s_red[kWsThreads / 32];
+  __shared__ int s_i0;
+  __shared__ int64_t s_pre0;
+  __shared__ int s_last;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int HG = p.Hkv * p.groups_per_kvh;
+
+  // ---- partition: total tiles, this CTA's range, the request its range starts in (decode_sk.cu) ---------------
+  int64_t mine = 0;
+  for (int i = tid; i < p.B; i += kWsThreads) mine += ws_item(p, i).tiles;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+  if (lane == 0) s_red[warp] = mine;
+  __syncthreads();
+  int64_t total = 0;
+#pragma unroll
+  for (int w = 0; w < kWsThreads / 32; ++w) total += s_red[w];
+  total *= HG;
+  const int N = (int)max((int64_t)1, min((int64_t)gridDim.x, total / min_tiles));
+  const int c = blockIdx.x;
+  if (c >= N) return;
+  const int64_t g0 = (int64_t)c * total / N;
+  const int64_t g1 = (int64_t)(c + 1) * total / N;
+  if (g0 >= g1) return;
+  {
+    int64_t base = 0;  // tiles of the requests before this chunk (same value in every thread)
+    for (int i0 = 0; i0 < p.B; i0 += kWsThreads) {
+      const int i = i0 + tid;
+      const int64_t t = i < p.B ? ws_item(p, i).tiles : 0;
+      int64_t incl = t;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int64_t y = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += y;
+      }
+      __syncthreads();  // s_red reuse
+      if (lane == 31) s_red[warp] = incl;
+      __syncthreads();
+      int64_t woff = 0, chunk_total = 0;
+#pragma unroll
+      for (int w = 0; w < kWsThreads / 32; ++w) {
+        if (w < warp) woff += s_red[w];
+        chunk_total += s_red[w];
+      }
+      const int64_t excl = base + woff + incl - t;
+      if (i < p.B && excl * HG <= g0 && g0 < (excl + t) * HG) {
+        s_i0 = i;
+        s_pre0 = excl;
+      }
+      base += chunk_total;
+      if (base * HG > g0) break;  // uniform: found in this chunk
+    }
+  }
+  const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (smem0 - smem_u32(smem_raw));
+  const uint32_t bar0 = smem0 + S::kBar;
+  auto bar = [&](int i) { return bar0 + 8u * i; };
+  if (tid == 0) {
+    for (int s = 0; s < kWsStages; ++s) {
+      mbar_init(bar(kWsFull + s), 1);
+      mbar_init(bar(kWsEmpty + s), 4);  // one release per consumer warp
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar(kWsQFull + s), 1);
+      mbar_init(bar(kWsQEmpty + s), 4);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  // ---- segment walk, identical in both roles --------------------------------------------------------------------
+  int item = s_i0;
+  int64_t pre = s_pre0;  // tiles of the requests before `item`
+  WsItem it = ws_item(p, item);
+  int64_t cur = g0;
+  int n = 0;     // tiles produced / consumed so far (ring position)
+  int nseg = 0;  // segments so far (query-block buffer parity)
+
+  if (warp == 4) {
+    // ================================ producer ================================
+    if (lane == 0) {
+      tma_prefetch_desc(&tm_kg);
+      tma_prefetch_desc(&tm_vg);
+      tma_prefetch_desc(&tm_kb);
+      tma_prefetch_desc(&tm_vb);
+    }
+    while (cur < g1) {
+      const int64_t ubase = pre * HG;
+      const int hg = (int)((cur - ubase) / it.tiles);
+      const int64_t us = ubase + (int64_t)hg * it.tiles;
+      const int64_t ue = us + it.tiles;
+      const int t_lo = (int)(cur - us);
+      const int64_t seg_end = min(g1, ue);
+      const int t_hi = t_lo + (int)(seg_end - cur);
+      const int kvh = hg / p.groups_per_kvh;
+      const int grp = hg - kvh * p.groups_per_kvh;
+      const int qrow = p.q_rows ? p.q_rows[item] : item;
+      const int h0 = kvh * p.G + grp * kDecMaxG;
+      const int gcount = min(kDecMaxG, p.G - grp * kDecMaxG);
+      const int k_hi = min(it.L, t_hi * kDecTile);
+      // query block of this segment
+      const int qs = nseg & 1;
+      if (nseg >= 2) mbar_wait(bar(kWsQEmpty + qs), ((nseg >> 1) + 1) & 1);
+      if (lane == 0) {
+        const uint32_t qbytes = (uint32_t)(gcount * D * 2);
+        mbar_arrive_expect_tx(bar(kWsQFull + qs), qbytes);
+        bulk_load_1d(smem0 + S::kQ + qs * S::kQBytes,
+                     reinterpret_cast<const T*>(p.q) + (int64_t)qrow * p.q_stride + (int64_t)h0 * D, qbytes,
+                     bar(kWsQFull + qs));
+      }
+      const int32_t* idx = p.kv_indices + it.kv_beg;
+      const int col = kvh * D;
+      for (int t = t_lo; t < t_hi; ++t, ++n) {
+        const int key0 = t * kDecTile;
+        int r[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int key = key0 + (lane & 15) * 4 + i;
+          r[i] = key < k_hi ? __ldg(idx + key) : num_slots;  // row past the pool -> zero-filled by the copy engine
+        }
+        // new-token row of this unit: written right before the tile that contains it is fetched
+        if (fused.new_k != nullptr && t == it.tiles - 1 && it.L > 0) {
+          const int slot = __ldg(idx + it.L - 1);
+          if (slot != fused.skip_slot && slot >= 0 && slot < num_slots) {
+            constexpr int kVecs = D * 2 / 16;  // 16-byte pieces of one (token, kv head) row
+            const bool isv = lane >= 16;
+            const uint8_t* src = reinterpret_cast<const uint8_t*>(isv ? fused.new_v : fused.new_k) +
+                                 ((int64_t)item * fused.new_stride + (int64_t)kvh * D) * 2;
+            uint8_t* dst = reinterpret_cast<uint8_t*>(const_cast<void*>(isv ? p.v_cache : p.k_cache)) +
+                           ((int64_t)slot * p.kv_stride + (int64_t)kvh * D) * 2;
+            for (int v = lane & 15; v < kVecs; v += 16)
+              *reinterpret_cast<uint4*>(dst + v * 16) = *reinterpret_cast<const uint4*>(src + v * 16);
+          }
+          // generic-proxy global writes -> ordered before the async-proxy (TMA) reads issued after the __syncwarp below
+          asm volatile("fence.proxy.async.global;\n" ::: "memory");
+        }
+        const int g0s = __shfl_sync(0xffffffffu, r[0], lane & ~3);
+        bool contig = (r[1] == r[0] + 1) && (r[2] == r[0] + 2) && (r[3] == r[0] + 3) &&
+                      (r[0] == g0s + 4 * (lane & 3));
+        contig = __all_sync(0xffffffffu, contig) && (key0 + kDecTile <= k_hi);
+        const int st = n % kWsStages;
+        if (n >= kWsStages) mbar_wait(bar(kWsEmpty + st), ((n / kWsStages) + 1) & 1);
+        if (lane == 0) mbar_arrive_expect_tx(bar(kWsFull + st), S::kStageBytes);
+        __syncwarp();
+        const uint32_t dst = smem0 + S::kRing + st * S::kStageBytes;
+        if (contig) {
+          // 4 pages x halves x {K, V}: one 16-row box each, spread over the first lanes
+          const int job = lane;                       // job = op * 4 * kHalves + page * kHalves + hf
+          const int op = job / (4 * kHalves), pg = (job / kHalves) & 3, hf = job % kHalves;
+          const int row = __shfl_sync(0xffffffffu, r[0], pg * 4);
+          if (job < 8 * kHalves)
+            tma_load_2d(dst + op * S::kTileBytes + hf * S::kHalfBytes + pg * 16 * 128, op ? &tm_vb : &tm_kb,
+                        bar(kWsFull + st), col + hf * 64, row);
+        } else {
+          const int op = lane >> 4;
+#pragma unroll
+          for (int hf = 0; hf < kHalves; ++hf)
+            tma_gather4(dst + op * S::kTileBytes + hf * S::kHalfBytes + (lane & 15) * 4 * 128, op ? &tm_vg : &tm_kg,
+                        bar(kWsFull + st), col + hf * 64, r[0], r[1], r[2], r[3]);
+        }
+      }
+      ++nseg;
+      cur = seg_end;
+      if (cur == ue && hg == HG - 1 && cur < g1) {
+        pre += it.tiles;
+        ++item;
+        it = ws_item(p, item);
+      }
+    }
+    return;
+  }
+
+  // ================================ consumers ================================
+  const int lm = lane >> 3, lr = lane & 7;
+  float* sm_m = reinterpret_cast<float*>(smem + S::kML);  // [4][16]
+  float* sm_l = sm_m + 64;                                // [4][16]
+  while (cur < g1) {
+    const int64_t ubase = pre * HG;
+    const int hg = (int)((cur - ubase) / it.tiles);
+    const int64_t us = ubase + (int64_t)hg * it.tiles;
+    const int64_t ue = us + it.tiles;
+    const int t_lo = (int)(cur - us);
+    const int64_t seg_end = min(g1, ue);
+    const int t_hi = t_lo + (int)(seg_end - cur);
+    const bool whole = (t_lo == 0 && t_hi == it.tiles);
+    const int kvh = hg / p.groups_per_kvh;
+    const int grp = hg - kvh * p.groups_per_kvh;
+    const int qrow = p.q_rows ? p.q_rows[item] : item;
+    const int h0 = kvh * p.G + grp * kDecMaxG;
+    const int gcount = min(kDecMaxG, p.G - grp * kDecMaxG);
+    const int k_lo = t_lo * kDecTile;
+    const int k_hi = min(it.L, t_hi * kDecTile);
+
+    // ---- Q fragments (A operand, 16 x D) from the producer's bulk copy; rows >= gcount are zero ----------
+    uint32_t qf[D / 16][4];
+    {
+      const int qs = nseg & 1;
+      mbar_wait(bar(kWsQFull + qs), (nseg >> 1) & 1);
+      const uint8_t* qb = smem + S::kQ + qs * S::kQBytes;
+      const int r0 = lane >> 2, c0 = (lane & 3) * 2;
+#pragma unroll
+      for (int ks = 0; ks < D / 16; ++ks) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int r = r0 + (j & 1) * 8;
+          const int cc = ks * 16 + c0 + (j >> 1) * 8;
+          qf[ks][j] = (r < gcount) ? *reinterpret_cast<const uint32_t*>(qb + (r * D + cc) * 2) : 0u;
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(kWsQEmpty + qs));
+    }
+
+    float o_acc[D / 8][4];
+#pragma unroll
+    for (int i = 0; i < D / 8; ++i) o_acc[i][0] = o_acc[i][1] = o_acc[i][2] = o_acc[i][3] = 0.f;
+    float m_run[2] = {-INFINITY, -INFINITY};
+    float l_run[2] = {0.f, 0.f};
+    int st = 0;
+    for (int t = t_lo; t < t_hi; ++t, ++n) {
+      st = n % kWsStages;
+      mbar_wait(bar(kWsFull + st), (n / kWsStages) & 1);
+      const uint32_t ks = smem0 + S::kRing + st * S::kStageBytes;
+      const uint32_t vs = ks + S::kTileBytes;
+      const int key0 = t * kDecTile + warp * 16;  // first key of this warp
+      if (key0 < k_hi) {                          // warp-uniform
+        float s[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+        {
+          const int krow = warp * 16 + (lm >> 1) * 8 + lr;
+#pragma unroll
+          for (int ksp = 0; ksp < D / 16; ++ksp) {
+            uint32_t b0, b1, b2, b3;
+            ldmatrix_x4(b0, b1, b2, b3, ks + ws_off<D>(krow, 2 * ksp + (lm & 1)));
+            mma_16816<kBf16>(s[0], qf[ksp], b0, b1);
+            mma_16816<kBf16>(s[1], qf[ksp], b2, b3);
+          }
+        }
+        const int kcol = key0 + (lane & 3) * 2;
+        float tmax[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+        for (int nb = 0; nb < 2; ++nb) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int key = kcol + nb * 8 + (j & 1);
+            float x = p.cap_post > 0.f ? p.cap_post * tanh_approx(s[nb][j] * p.cap_pre) : s[nb][j] * p.scale_log2;
+            x = (key < k_hi) ? x : -INFINITY;
+            s[nb][j] = x;
+            tmax[j >> 1] = fmaxf(tmax[j >> 1], x);
+          }
+        }
+        float alpha[2];
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          tmax[r] = fmaxf(tmax[r], __shfl_xor_sync(0xffffffffu, tmax[r], 1));
+          tmax[r] = fmaxf(tmax[r], __shfl_xor_sync(0xffffffffu, tmax[r], 2));
+          const float m_new = fmaxf(m_run[r], tmax[r]);  // finite: key0 < k_hi => >= 1 valid key
+          alpha[r] = fast_exp2(m_run[r] - m_new);
+          m_run[r] = m_new;
+          l_run[r] *= alpha[r];
+        }
+        uint32_t pf[4];
+#pragma unroll
+        for (int nb = 0; nb < 2; ++nb) {
+          const float p0 = fast_exp2(s[nb][0] - m_run[0]);
+          const float p1 = fast_exp2(s[nb][1] - m_run[0]);
+          const float p2 = fast_exp2(s[nb][2] - m_run[1]);
+          const float p3 = fast_exp2(s[nb][3] - m_run[1]);
+          l_run[0] += p0 + p1;
+          l_run[1] += p2 + p3;
+          pf[nb * 2 + 0] = pack2<kBf16>(p0, p1);
+          pf[nb * 2 + 1] = pack2<kBf16>(p2, p3);
+        }
+        const int vrow = warp * 16 + (lm & 1) * 8 + lr;
+        const bool rescale = __any_sync(0xffffffffu, alpha[0] != 1.f || alpha[1] != 1.f);
+#pragma unroll
+        for (int np = 0; np < D / 16; ++np) {
+          uint32_t b0, b1, b2, b3;
+          ldmatrix_x4_trans(b0, b1, b2, b3, vs + ws_off<D>(vrow, 2 * np + (lm >> 1)));
+          if (rescale) {  // warp-uniform: the running max moved in this tile
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              float(&acc)[4] = o_acc[2 * np + h];
+              acc[0] *= alpha[0];
+              acc[1] *= alpha[0];
+              acc[2] *= alpha[1];
+              acc[3] *= alpha[1];
+            }
+          }
+          mma_16816<kBf16>(o_acc[2 * np], pf, b0, b1);
+          mma_16816<kBf16>(o_acc[2 * np + 1], pf, b2, b3);
+        }
+      }
+      if (t + 1 < t_hi) {  // the segment's last stage is released after the merge below
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(kWsEmpty + st));
+      }
+    }
+
+    // ---- merge the four warps through the last tile's stage (fp32 [4][16][D] == one stage) ------------------
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 1);
+      l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
+    }
+    float* sm_o = reinterpret_cast<float*>(smem + S::kRing + st * S::kStageBytes);
+    consumer_sync();  // every warp has finished reading the stage
+    {
+      const int r0 = lane >> 2, c0 = (lane & 3) * 2;
+#pragma unroll
+      for (int i = 0; i < D / 8; ++i) {
+        float* dst = sm_o + (warp * 16 + r0) * D + i * 8 + c0;
+        *reinterpret_cast<float2*>(dst) = make_float2(o_acc[i][0], o_acc[i][1]);
+        *reinterpret_cast<float2*>(dst + 8 * D) = make_float2(o_acc[i][2], o_acc[i][3]);
+      }
+      if ((lane & 3) == 0) {
+        sm_m[warp * 16 + r0] = m_run[0];
+        sm_m[warp * 16 + r0 + 8] = m_run[1];
+        sm_l[warp * 16 + r0] = l_run[0];
+        sm_l[warp * 16 + r0 + 8] = l_run[1];
+      }
+    }
+    consumer_sync();
+    const int wslot = c * 2 + (t_lo == 0 ? 1 : 0);  // partial pieces only
+    for (int e = tid; e < gcount * (D / 4); e += kWsConsumers) {
+      const int r = e / (D / 4), cc = (e - r * (D / 4)) * 4;
+      float m = -INFINITY;
+#pragma unroll
+      for (int w = 0; w < 4; ++w) m = fmaxf(m, sm_m[w * 16 + r]);
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      float l = 0.f;
+#pragma unroll
+      for (int w = 0; w < 4; ++w) {
+        const float mw = sm_m[w * 16 + r];
+        const float f = (mw == -INFINITY) ? 0.f : fast_exp2(mw - m);
+        const float4 x = *reinterpret_cast<const float4*>(sm_o + (w * 16 + r) * D + cc);
+        acc.x += f * x.x;
+        acc.y += f * x.y;
+        acc.z += f * x.z;
+        acc.w += f * x.w;
+        l += f * sm_l[w * 16 + r];
+      }
+      if (whole && p.sinks != nullptr && l > 0.f) l += fast_exp2(__ldg(p.sinks + h0 + r) * kLog2e - m);
+      const float inv = (l > 0.f) ? 1.f / l : 0.f;
+      acc.x *= inv;
+      acc.y *= inv;
+      acc.z *= inv;
+      acc.w *= inv;
+      const float lse2 = (l > 0.f) ? m + log2f(l) : -INFINITY;
+      const int h = h0 + r;
+      if (whole) {
+        T* dst = reinterpret_cast<T*>(p.o) + (int64_t)qrow * p.o_stride + (int64_t)h * D + cc;
+        uint2 pk;
+        pk.x = pack2<kBf16>(acc.x, acc.y);
+        pk.y = pack2<kBf16>(acc.z, acc.w);
+        *reinterpret_cast<uint2*>(dst) = pk;
+        if (p.lse != nullptr && cc == 0) p.lse[(int64_t)qrow * p.Hq + h] = lse2 * kLn2;
+      } else {
+        const int64_t w = (int64_t)wslot * kDecMaxG + r;
+        *reinterpret_cast<float4*>(p.ws_o + w * D + cc) = acc;
+        if (cc == 0) p.ws_lse[w] = lse2;
+      }
+    }
+    if (!whole) {
+      // ---- arrival ticket; the last piece of the unit to arrive merges all of them -------------------------
+      const int c_first = ws_owner(us, total, N);
+      const int c_last = ws_owner(ue - 1, total, N);
+      __threadfence();
+      consumer_sync();
+      if (tid == 0) {
+        int* cnt = p.ws_cnt + (int64_t)item * HG + hg;
+        const int ticket = atomicAdd(cnt, 1);
+        s_last = (ticket == c_last - c_first);
+        if (s_last) *cnt = 0;  // self-cleaning
+      }
+      consumer_sync();
+      if (s_last) {
+        __threadfence();
+        for (int e = tid; e < gcount * (D / 4); e += kWsConsumers) {
+          const int r = e / (D / 4), cc = (e - r * (D / 4)) * 4;
+          const int h = h0 + r;
+          float m = -INFINITY;
+          for (int pc = c_first; pc <= c_last; ++pc) {
+            const int64_t w = (int64_t)(pc * 2 + (pc == c_first ? 1 : 0)) * kDecMaxG + r;
+            m = fmaxf(m, __ldcg(p.ws_lse + w));
+          }
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+          float l = 0.f;
+          for (int pc = c_first; pc <= c_last; ++pc) {
+            const int64_t w = (int64_t)(pc * 2 + (pc == c_first ? 1 : 0)) * kDecMaxG + r;
+            const float ls = __ldcg(p.ws_lse + w);
+            const float f = (ls == -INFINITY) ? 0.f : fast_exp2(ls - m);
+            const float4 x = __ldcg(reinterpret_cast<const float4*>(p.ws_o + w * D + cc));
+            acc.x += f * x.x;
+            acc.y += f * x.y;
+            acc.z += f * x.z;
+            acc.w += f * x.w;
+            l += f;
+          }
+          if (p.sinks != nullptr && l > 0.f) l += fast_exp2(__ldg(p.sinks + h) * kLog2e - m);
+          const float inv = (l > 0.f) ? 1.f / l : 0.f;
+          T* dst = reinterpret_cast<T*>(p.o) + (int64_t)qrow * p.o_stride + (int64_t)h * D + cc;
+          uint2 pk;
+          pk.x = pack2<kBf16>(acc.x * inv, acc.y * inv);
+          pk.y = pack2<kBf16>(acc.z * inv, acc.w * inv);
+          *reinterpret_cast<uint2*>(dst) = pk;
+          if (p.lse != nullptr && cc == 0)
+            p.lse[(int64_t)qrow * p.Hq + h] = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
+        }
+      }
+    }
+    consumer_sync();  // scratch (the stage), sm_m / sm_l and s_last are free again
+    fence_proxy_async_smem();  // generic-proxy scratch writes before the copy engine refills the stage
+    if (lane == 0) mbar_arrive(bar(kWsEmpty + st));
+    ++nseg;
+    cur = seg_end;
+    if (cur == ue && hg == HG - 1 && cur < g1) {
+      pre += it.tiles;
+      ++item;
+      it = ws_item(p, item);
+    }
+  }
+}
+
+int ws_ctas() { return 2 * sm_count(); }
+
+template <int D, bool kBf16>
+static int launch_decode_ws(const CUtensorMap& kg, const CUtensorMap& vg, const CUtensorMap& kb, const CUtensorMap& vb,
+                            const DecodeParams& p, const WsFused& fused, int min_tiles, int num_slots,
+                            cudaStream_t st) {
+  constexpr int kSmem = WsSmem<D>::kTotal + 1024;  // + alignment slack
+  static bool configured = false;
+  if (!configured) {
+    B2_CUDA(cudaFuncSetAttribute(decode_ws_kernel<D, kBf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+    B2_CUDA(cudaFuncSetAttribute(decode_ws_kernel<D, kBf16>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    configured = true;
+  }
+  decode_ws_kernel<D, kBf16><<<ws_ctas(), kWsThreads, kSmem, st>>>(kg, vg, kb, vb, p, fused, min_tiles, num_slots);
+  B2_LAUNCH_CHECK();
+  return B200ATTN_OK;
+}
+
+}  // namespace b200attn
+
+extern "C" int64_t b200attn_decode_ws_workspace_bytes(int32_t D) {
+  using namespace b200attn;
+  // fixed counter header + two partial slots per CTA ([16][D] fp32 + [16] lse)
+  return kDecCounterBytes + (int64_t)ws_ctas() * 2 * kDecMaxG * (D + 1) * 4;
+}
+
+extern "C" int b200attn_decode_ws(const void* q, int64_t q_stride, void* k_cache, void* v_cache, int64_t kv_stride,
+                                  int64_t num_slots, void* o, int64_t o_stride, float* lse,
+                                  const int32_t* kv_indptr, const int32_t* kv_indices, const int32_t* q_rows,
+                                  const int32_t* req_ids, int32_t B, int32_t Hq, int32_t Hkv, int32_t D, int dtype,
+                                  float sm_scale, int32_t min_chunk, int32_t window_left, float logit_cap,
+                                  const float* sinks, const void* new_k, const void* new_v, int64_t new_kv_stride,
+                                  int64_t skip_slot, void* workspace, int64_t workspace_bytes, void* stream) {
+  using namespace b200attn;
+  B2_CHECK_ARG(B >= 0, "decode_ws: negative batch");
+  B2_CHECK_ARG(logit_cap >= 0.f, "decode_ws: negative logit_cap");
+  if (B == 0) return B200ATTN_OK;
+  B2_CHECK_ARG(q && k_cache && v_cache && o && kv_indptr && kv_indices, "decode_ws: null pointer");
+  B2_CHECK_ARG(Hq > 0 && Hkv > 0 && Hq % Hkv == 0, "decode_ws: Hq=%d must be a multiple of Hkv=%d", Hq, Hkv);
+  B2_CHECK_ARG(min_chunk >= 1, "decode_ws: bad min_chunk");
+  B2_CHECK_ARG(num_slots > 0 && num_slots < (1ll << 31), "decode_ws: bad num_slots");
+  B2_CHECK_ARG(q_stride % 8 == 0 && kv_stride % 8 == 0 && o_stride % 4 == 0,
+               "decode_ws: strides must keep rows 16-byte aligned");
+  B2_CHECK_ARG((((uintptr_t)q | (uintptr_t)k_cache | (uintptr_t)v_cache | (uintptr_t)o) & 15) == 0,
+               "decode_ws: tensors must be 16-byte aligned");
+  B2_CHECK_ARG((new_k == nullptr) == (new_v == nullptr), "decode_ws: new_k and new_v must be given together");
+  B2_CHECK_ARG(new_k == nullptr || (q_rows == nullptr && req_ids == nullptr && new_kv_stride % 8 == 0 &&
+                                    (((uintptr_t)new_k | (uintptr_t)new_v) & 15) == 0),
+               "decode_ws: the fused store needs identity row maps and 16-byte aligned new_k / new_v rows");
+  if (dtype != B200ATTN_BF16 && dtype != B200ATTN_FP16) B2_UNSUPPORTED("decode_ws: dtype %d", dtype);
+  if (D != 64 && D != 128) B2_UNSUPPORTED("decode_ws: head_dim %d (supported: 64, 128)", D);
+  const int64_t need = b200attn_decode_ws_workspace_bytes(D);
+  B2_CHECK_ARG(workspace && workspace_bytes >= need, "decode_ws: workspace too small (%lld < %lld)",
+               (long long)workspace_bytes, (long long)need);
+  B2_CHECK_ARG((int64_t)B * Hkv * ((Hq / Hkv + kDecMaxG - 1) / kDecMaxG) <= kDecMaxUnits,
+               "decode_ws: more than %d units", kDecMaxUnits);
+  const CUtensorMap *kg, *vg, *kb, *vb;
+  int rc = tensor_map_cached(&kg, k_cache, (uint64_t)num_slots, (uint64_t)Hkv * D, (uint64_t)kv_stride * 2, 64, 1);
+  if (rc) return rc;
+  rc = tensor_map_cached(&vg, v_cache, (uint64_t)num_slots, (uint64_t)Hkv * D, (uint64_t)kv_stride * 2, 64, 1);
+  if (rc) return rc;
+  rc = tensor_map_cached(&kb, k_cache, (uint64_t)num_slots, (uint64_t)Hkv * D, (uint64_t)kv_stride * 2, 64, 16);
+  if (rc) return rc;
+  rc = tensor_map_cached(&vb, v_cache, (uint64_t)num_slots, (uint64_t)Hkv * D, (uint64_t)kv_stride * 2, 64, 16);
+  if (rc) return rc;
+  const int cap = ws_ctas();
+  DecodeParams p;
+  p.q = q;
+  p.k_cache = k_cache;
+  p.v_cache = v_cache;
+  p.o = o;
+  p.lse = lse;
+  p.kv_indptr = kv_indptr;
+  p.kv_indices = kv_indices;
+  p.q_rows = q_rows;
+  p.req_ids = req_ids;
+  p.ws_cnt = reinterpret_cast<int*>(workspace);
+  p.ws_o = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + kDecCounterBytes);
+  p.ws_lse = p.ws_o + (int64_t)cap * 2 * kDecMaxG * D;
+  p.q_stride = q_stride;
+  p.kv_stride = kv_stride;
+  p.o_stride = o_stride;
+  p.B = B;
+  p.Hq = Hq;
+  p.Hkv = Hkv;
+  p.G = Hq / Hkv;
+  p.groups_per_kvh = (p.G + kDecMaxG - 1) / kDecMaxG;
+  p.max_splits = 1;
+  p.min_chunk = min_chunk;
+  p.scale_log2 = sm_scale * kLog2e;
+  p.window_left = window_left;
+  p.cap_pre = logit_cap > 0.f ? sm_scale / logit_cap : 0.f;
+  p.cap_post = logit_cap > 0.f ? logit_cap * kLog2e : 0.f;
+  p.sinks = sinks;
+  p.tail_begin = -1;
+  p.out_scale = 1.f;
+  WsFused fused;
+  fused.new_k = new_k;
+  fused.new_v = new_v;
+  fused.new_stride = new_kv_stride;
+  fused.skip_slot = (int)skip_slot;
+  const int min_tiles = (min_chunk + kDecTile - 1) / kDecTile;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (D == 128)
+    return dtype == B200ATTN_BF16
+               ? launch_decode_ws<128, true>(*kg, *vg, *kb, *vb, p, fused, min_tiles, (int)num_slots, st)
+               : launch_decode_ws<128, false>(*kg, *vg, *kb, *vb, p, fused, min_tiles, (int)num_slots, st);
+  return dtype == B200ATTN_BF16
+             ? launch_decode_ws<64, true>(*kg, *vg, *kb, *vb, p, fused, min_tiles, (int)num_slots, st)
+             : launch_decode_ws<64, false>(*kg, *vg, *kb, *vb, p, fused, min_tiles, (int)num_slots, st);
+}

@@ -38,6 +38,8 @@
 // Algorithmic FLOPs per (request, q head): 4 * D * sum_j (#visible keys of row j).
 #include "sm100.cuh"
 
+#include <mutex>
+
 namespace b200attn {
 
 constexpr int kExtM = 128;        // query rows per tile (two tiles per CTA)
@@ -821,6 +823,45 @@ int make_tensor_map_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64
   return B200ATTN_OK;
 }
 
+// Tensor maps of long-lived buffers (the KV pool) depend only on (base, shape, stride, box): they are encoded once
+// and kept - the encode is a driver call of a few microseconds, paid per layer-call otherwise.  Small FIFO cache,
+// mutex-protected; entries are returned by pointer and stay valid for the life of the process.
+int tensor_map_cached(const CUtensorMap** out, const void* base, uint64_t rows, uint64_t cols,
+                      uint64_t row_stride_bytes, uint32_t box_cols, uint32_t box_rows, CUtensorMapSwizzle swizzle) {
+  struct Entry {
+    const void* base;
+    uint64_t rows, cols, stride;
+    uint32_t bc, br;
+    int sw;
+    CUtensorMap map;
+  };
+  constexpr int kCap = 256;
+  static Entry* entries = new Entry[kCap];
+  static int count = 0, next = 0;
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  for (int i = 0; i < count; ++i) {
+    const Entry& e = entries[i];
+    if (e.base == base && e.rows == rows && e.cols == cols && e.stride == row_stride_bytes && e.bc == box_cols &&
+        e.br == box_rows && e.sw == (int)swizzle) {
+      *out = &e.map;
+      return B200ATTN_OK;
+    }
+  }
+  Entry fresh;
+  int rc = make_tensor_map_2d(&fresh.map, base, rows, cols, row_stride_bytes, box_cols, box_rows, swizzle);
+  if (rc) return rc;
+  fresh.base = base; fresh.rows = rows; fresh.cols = cols; fresh.stride = row_stride_bytes;
+  fresh.bc = box_cols; fresh.br = box_rows; fresh.sw = (int)swizzle;
+  // entries handed out earlier must stay valid: once the table is full the oldest slot is overwritten IN PLACE only
+  // when no launch can still be reading it - tensor maps are passed to kernels BY VALUE (__grid_constant__), so a
+  // returned pointer is dereferenced on the host before the launcher returns, under this same call
+  const int slot = count < kCap ? count++ : (next++ % kCap);
+  entries[slot] = fresh;
+  *out = &entries[slot].map;
+  return B200ATTN_OK;
+}
+
 template <int D, bool kBf16>
 static int launch_extend(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
                          const CUtensorMap& tkb, const CUtensorMap& tvb, const CUtensorMap& to,
@@ -886,22 +927,23 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
                "extend: tensors must be 16-byte aligned");
   if (dtype != B200ATTN_BF16 && dtype != B200ATTN_FP16) B2_UNSUPPORTED("extend: dtype %d", dtype);
   if (D != 64 && D != 128) B2_UNSUPPORTED("extend: head_dim %d (supported: 64, 128)", D);
-  CUtensorMap tq, tk, tv, tkb, tvb, to;
+  // q / o are activations (a new address every call): encoded per call; the four pool maps are cached
+  CUtensorMap tq, to;
+  const CUtensorMap *ptk, *ptv, *ptkb, *ptvb;
   int rc = make_tensor_map_2d(&tq, q, (uint64_t)total_q_host, (uint64_t)Hq * D,
                               (uint64_t)q_stride * 2, 64, kExtM);
   if (rc) return rc;
-  rc = make_tensor_map_2d(&tk, k_cache, (uint64_t)num_slots, (uint64_t)Hkv * D,
-                          (uint64_t)kv_stride * 2, 64, 1);
+  rc = tensor_map_cached(&ptk, k_cache, (uint64_t)num_slots, (uint64_t)Hkv * D, (uint64_t)kv_stride * 2, 64, 1);
   if (rc) return rc;
-  rc = make_tensor_map_2d(&tv, v_cache, (uint64_t)num_slots, (uint64_t)Hkv * D,
-                          (uint64_t)kv_stride * 2, 64, 1);
+  rc = tensor_map_cached(&ptv, v_cache, (uint64_t)num_slots, (uint64_t)Hkv * D, (uint64_t)kv_stride * 2, 64, 1);
   if (rc) return rc;
-  rc = make_tensor_map_2d(&tkb, k_cache, (uint64_t)num_slots, (uint64_t)Hkv * D,
-                          (uint64_t)kv_stride * 2, 64, kExtBoxRows);
+  rc = tensor_map_cached(&ptkb, k_cache, (uint64_t)num_slots, (uint64_t)Hkv * D, (uint64_t)kv_stride * 2, 64,
+                         kExtBoxRows);
   if (rc) return rc;
-  rc = make_tensor_map_2d(&tvb, v_cache, (uint64_t)num_slots, (uint64_t)Hkv * D,
-                          (uint64_t)kv_stride * 2, 64, kExtBoxRows);
+  rc = tensor_map_cached(&ptvb, v_cache, (uint64_t)num_slots, (uint64_t)Hkv * D, (uint64_t)kv_stride * 2, 64,
+                         kExtBoxRows);
   if (rc) return rc;
+  const CUtensorMap &tk = *ptk, &tv = *ptv, &tkb = *ptkb, &tvb = *ptvb;
   rc = make_tensor_map_2d(&to, o, (uint64_t)total_q_host, (uint64_t)Hq * D, (uint64_t)o_stride * 2,
                           kExtOSlabCols, kExtM, CU_TENSOR_MAP_SWIZZLE_64B);
   if (rc) return rc;

@@ -184,4 +184,9 @@ int make_tensor_map_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64
                        uint64_t row_stride_bytes, uint32_t box_cols, uint32_t box_rows,
                        CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B);
 
+// Same, encoded once per distinct (base, shape, stride, box, swizzle) and kept (extend.cu): for long-lived buffers.
+int tensor_map_cached(const CUtensorMap** out, const void* base, uint64_t rows, uint64_t cols,
+                      uint64_t row_stride_bytes, uint32_t box_cols, uint32_t box_rows,
+                      CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B);
+
 }  // namespace b200attn
