@@ -194,6 +194,34 @@ int b200attn_decode_sk(const void* q, int64_t q_stride, const void* k_cache, con
                        float logit_cap, const float* sinks, void* workspace,
                        int64_t workspace_bytes, void* stream);
 
+/* --------------------------------------------------------------------------
+ * (a4) Decode, warp-specialised persistent kernel fed by TMA (16-bit pools; the
+ * default decode path of B200AttnBackend).  Same contract, arithmetic and flat
+ * tile-stream partition as b200attn_decode_sk; one producer warp per CTA keeps a
+ * 3-stage ring full through the copy engine (16-row tiled boxes when every aligned
+ * 16-key group sits in 16 consecutive pool slots, tile::gather4 otherwise) and runs
+ * ahead across unit boundaries, four consumer warps do the mma.sync math.
+ * `num_slots` = rows of the pool (gather rows past it are zero-filled).
+ * `new_k` / `new_v` (nullable, [B, Hkv, D] with token stride `new_kv_stride`
+ * elements): the step's new K/V rows; the kernel writes row b into slot
+ * kv_indices[kv_indptr[b+1] - 1] of the pool before reading it, replacing the
+ * separate b200attn_kv_store launch of a decode layer-call (memory_pool.py:2331-2456:
+ * store before read).  Rows whose slot == skip_slot are not written (-1: write all).
+ * Needs identity q_rows / req_ids.  k_cache / v_cache are written only in that case.
+ * Workspace: b200attn_decode_ws_workspace_bytes(D) bytes, zero-initialised once
+ * (fixed-size counter header first, like b200attn_decode).
+ * -------------------------------------------------------------------------- */
+int64_t b200attn_decode_ws_workspace_bytes(int32_t D);
+
+int b200attn_decode_ws(const void* q, int64_t q_stride, void* k_cache, void* v_cache,
+                       int64_t kv_stride, int64_t num_slots, void* o, int64_t o_stride, float* lse,
+                       const int32_t* kv_indptr, const int32_t* kv_indices, const int32_t* q_rows,
+                       const int32_t* req_ids, int32_t B, int32_t Hq, int32_t Hkv, int32_t D,
+                       int dtype, float sm_scale, int32_t min_chunk, int32_t window_left,
+                       float logit_cap, const float* sinks, const void* new_k, const void* new_v,
+                       int64_t new_kv_stride, int64_t skip_slot, void* workspace,
+                       int64_t workspace_bytes, void* stream);
+
 /* b200attn_decode_sk over an e4m3 byte pool (the byte path of b200attn_decode_fp8kv, 3 CTAs per SM). */
 int b200attn_decode_sk_fp8kv(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache,
                              int64_t kv_stride, void* o, int64_t o_stride, float* lse,

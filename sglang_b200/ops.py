@@ -485,6 +485,10 @@ def decode_sk_workspace_bytes(B: int, Hq: int, Hkv: int, D: int) -> int:
     return int(_lib.load().b200attn_decode_sk_workspace_bytes(B, Hq, Hkv, D))
 
 
+def decode_ws_workspace_bytes(D: int) -> int:
+    return int(_lib.load().b200attn_decode_ws_workspace_bytes(D))
+
+
 def decode_ctas_per_sm(fp8_kv: bool = False) -> int:
     """Resident CTAs per SM of the decode kernels (their __launch_bounds__): 2 x 96 KB rings for 16-bit pools,
     3 x 64 KB for e4m3 pools (csrc/decode.cu); the wave arithmetic of the two split heuristics below needs it."""
@@ -550,6 +554,10 @@ def decode_attention(
     k_descale: float = 1.0,
     v_descale: float = 1.0,
     stream_k: bool = False,
+    ws_kernel: bool = False,
+    new_k: Optional[torch.Tensor] = None,
+    new_v: Optional[torch.Tensor] = None,
+    skip_slot: int = 0,
 ) -> torch.Tensor:
     """Paged GQA decode: ``q [B,Hq,D]``, caches ``[slots,Hkv,D]`` -> ``o [B,Hq,D]``.
 
@@ -579,6 +587,30 @@ def decode_attention(
     if kv_indptr.dtype != torch.int32 or kv_indices.dtype != torch.int32:
         raise TypeError("decode_attention: kv_indptr / kv_indices must be int32")
     ws_bytes = 0 if workspace is None else workspace.numel() * workspace.element_size()
+    if ws_kernel:
+        # warp-specialised persistent TMA kernel (b200attn_decode_ws); with new_k / new_v it also performs the
+        # step's KV store (row b -> the slot of request b's last key) before reading the pool
+        if fp8:
+            raise NotImplementedError("decode_attention: ws_kernel takes 16-bit pools")
+        nk = nv = None
+        nstride = 0
+        if new_k is not None:
+            _require_cuda(new_k, new_v)
+            nk, nv = new_k.reshape(new_k.shape[0], -1), new_v.reshape(new_v.shape[0], -1)
+            if nk.dtype != k_cache.dtype or nv.dtype != v_cache.dtype or nk.stride(1) != 1 or nv.stride(1) != 1 \
+                    or nk.stride(0) != nv.stride(0) or nk.shape[1] != Hkv * D or nv.shape[1] != Hkv * D:
+                raise ValueError("decode_attention: new_k / new_v must be [B, Hkv*D] rows of the pool dtype "
+                                 "with one common token stride")
+            nstride = nk.stride(0)
+        rc = _lib.load().b200attn_decode_ws(
+            q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
+            min(k_cache.shape[0], v_cache.shape[0]), o.data_ptr(), o.stride(0), _ptr(lse), kv_indptr.data_ptr(),
+            kv_indices.data_ptr(), _ptr(q_rows), _ptr(req_ids), B, Hq, Hkv, D, _fdtype(q), float(sm_scale),
+            min_chunk, int(window_left), float(logit_cap), _sinks_ptr(sinks, Hq), _ptr(nk), _ptr(nv), nstride,
+            int(skip_slot), _ptr(workspace), ws_bytes, _stream(),
+        )
+        check(rc, "b200attn_decode_ws")
+        return o
     if fp8 and stream_k:
         rc = _lib.load().b200attn_decode_sk_fp8kv(
             q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
