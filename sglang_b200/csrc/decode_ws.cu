@@ -187,88 +187,126 @@ __global__ void __launch_bounds__(kWsThreads, 2)
       tma_prefetch_desc(&tm_kb);
       tma_prefetch_desc(&tm_vb);
     }
-    while (cur < g1) {
-      const int64_t ubase = pre * HG;
-      const int hg = (int)((cur - ubase) / it.tiles);
-      const int64_t us = ubase + (int64_t)hg * it.tiles;
-      const int64_t ue = us + it.tiles;
-      const int t_lo = (int)(cur - us);
-      const int64_t seg_end = min(g1, ue);
-      const int t_hi = t_lo + (int)(seg_end - cur);
-      const int kvh = hg / p.groups_per_kvh;
-      const int grp = hg - kvh * p.groups_per_kvh;
-      const int qrow = p.q_rows ? p.q_rows[item] : item;
-      const int h0 = kvh * p.G + grp * kDecMaxG;
-      const int gcount = min(kDecMaxG, p.G - grp * kDecMaxG);
-      const int k_hi = min(it.L, t_hi * kDecTile);
-      // query block of this segment
-      const int qs = nseg & 1;
-      if (nseg >= 2) mbar_wait(bar(kWsQEmpty + qs), ((nseg >> 1) + 1) & 1);
-      if (lane == 0) {
-        const uint32_t qbytes = (uint32_t)(gcount * D * 2);
-        mbar_arrive_expect_tx(bar(kWsQFull + qs), qbytes);
-        bulk_load_1d(smem0 + S::kQ + qs * S::kQBytes,
-                     reinterpret_cast<const T*>(p.q) + (int64_t)qrow * p.q_stride + (int64_t)h0 * D, qbytes,
-                     bar(kWsQFull + qs));
-      }
-      const int32_t* idx = p.kv_indices + it.kv_beg;
-      const int col = kvh * D;
-      for (int t = t_lo; t < t_hi; ++t, ++n) {
-        const int key0 = t * kDecTile;
-        int r[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int key = key0 + (lane & 15) * 4 + i;
-          r[i] = key < k_hi ? __ldg(idx + key) : num_slots;  // row past the pool -> zero-filled by the copy engine
-        }
-        // new-token row of this unit: written right before the tile that contains it is fetched
-        if (fused.new_k != nullptr && t == it.tiles - 1 && it.L > 0) {
-          const int slot = __ldg(idx + it.L - 1);
-          if (slot != fused.skip_slot && slot >= 0 && slot < num_slots) {
-            constexpr int kVecs = D * 2 / 16;  // 16-byte pieces of one (token, kv head) row
-            const bool isv = lane >= 16;
-            const uint8_t* src = reinterpret_cast<const uint8_t*>(isv ? fused.new_v : fused.new_k) +
-                                 ((int64_t)item * fused.new_stride + (int64_t)kvh * D) * 2;
-            uint8_t* dst = reinterpret_cast<uint8_t*>(const_cast<void*>(isv ? p.v_cache : p.k_cache)) +
-                           ((int64_t)slot * p.kv_stride + (int64_t)kvh * D) * 2;
-            for (int v = lane & 15; v < kVecs; v += 16)
-              *reinterpret_cast<uint4*>(dst + v * 16) = *reinterpret_cast<const uint4*>(src + v * 16);
+    // Flat, software-pipelined walk over the CTA's tiles: the slot ids (and the new-token slot) of tile n + 1 are
+    // requested BEFORE tile n is issued, across segment and request boundaries, so the producer never sits on a
+    // dependent index load between two TMA issues.
+    struct Tile {
+      const int32_t* idx;
+      int key0, k_hi, col, kvh, item, L;
+      bool last_of_unit;
+    };
+    int t = 0, t_hi = 0, hg = 0;
+    int64_t ue = 0, seg_end = 0;
+    Tile cur_t, nxt_t;
+    int r[4], rn[4];
+    int last_slot = -1, last_slot_n = -1;
+    // describes the next tile into `nxt_t` (setting up its segment, and issuing the segment's query-block copy, when
+    // it is the segment's first); returns false at the end of the range
+    auto next_tile = [&]() -> bool {
+      if (t == t_hi) {  // segment exhausted (or first call)
+        if (t_hi != 0) {
+          cur = seg_end;
+          if (cur == ue && hg == HG - 1 && cur < g1) {
+            pre += it.tiles;
+            ++item;
+            it = ws_item(p, item);
           }
-          // generic-proxy global writes -> ordered before the async-proxy (TMA) reads issued after the __syncwarp below
-          asm volatile("fence.proxy.async.global;\n" ::: "memory");
         }
-        const int g0s = __shfl_sync(0xffffffffu, r[0], lane & ~3);
-        bool contig = (r[1] == r[0] + 1) && (r[2] == r[0] + 2) && (r[3] == r[0] + 3) &&
-                      (r[0] == g0s + 4 * (lane & 3));
-        contig = __all_sync(0xffffffffu, contig) && (key0 + kDecTile <= k_hi);
-        const int st = n % kWsStages;
-        if (n >= kWsStages) mbar_wait(bar(kWsEmpty + st), ((n / kWsStages) + 1) & 1);
-        if (lane == 0) mbar_arrive_expect_tx(bar(kWsFull + st), S::kStageBytes);
-        __syncwarp();
-        const uint32_t dst = smem0 + S::kRing + st * S::kStageBytes;
-        if (contig) {
-          // 4 pages x halves x {K, V}: one 16-row box each, spread over the first lanes
-          const int job = lane;                       // job = op * 4 * kHalves + page * kHalves + hf
-          const int op = job / (4 * kHalves), pg = (job / kHalves) & 3, hf = job % kHalves;
-          const int row = __shfl_sync(0xffffffffu, r[0], pg * 4);
-          if (job < 8 * kHalves)
-            tma_load_2d(dst + op * S::kTileBytes + hf * S::kHalfBytes + pg * 16 * 128, op ? &tm_vb : &tm_kb,
-                        bar(kWsFull + st), col + hf * 64, row);
-        } else {
-          const int op = lane >> 4;
+        if (cur >= g1) return false;
+        const int64_t ubase = pre * HG;
+        hg = (int)((cur - ubase) / it.tiles);
+        const int64_t us = ubase + (int64_t)hg * it.tiles;
+        ue = us + it.tiles;
+        t = (int)(cur - us);
+        seg_end = min(g1, ue);
+        t_hi = t + (int)(seg_end - cur);
+        const int kvh = hg / p.groups_per_kvh;
+        const int grp = hg - kvh * p.groups_per_kvh;
+        const int qrow = p.q_rows ? p.q_rows[item] : item;
+        const int h0 = kvh * p.G + grp * kDecMaxG;
+        const int gcount = min(kDecMaxG, p.G - grp * kDecMaxG);
+        const int qs = nseg & 1;
+        if (nseg >= 2) mbar_wait(bar(kWsQEmpty + qs), ((nseg >> 1) + 1) & 1);
+        if (lane == 0) {
+          const uint32_t qbytes = (uint32_t)(gcount * D * 2);
+          mbar_arrive_expect_tx(bar(kWsQFull + qs), qbytes);
+          bulk_load_1d(smem0 + S::kQ + qs * S::kQBytes,
+                       reinterpret_cast<const T*>(p.q) + (int64_t)qrow * p.q_stride + (int64_t)h0 * D, qbytes,
+                       bar(kWsQFull + qs));
+        }
+        ++nseg;
+        nxt_t.idx = p.kv_indices + it.kv_beg;
+        nxt_t.k_hi = min(it.L, t_hi * kDecTile);
+        nxt_t.col = kvh * D;
+        nxt_t.kvh = kvh;
+        nxt_t.item = item;
+        nxt_t.L = it.L;
+      }
+      nxt_t.key0 = t * kDecTile;
+      nxt_t.last_of_unit = (t == it.tiles - 1);
+      ++t;
+      return true;
+    };
+    auto fetch_ids = [&](const Tile& td, int (&out)[4], int& lslot) {
 #pragma unroll
-          for (int hf = 0; hf < kHalves; ++hf)
-            tma_gather4(dst + op * S::kTileBytes + hf * S::kHalfBytes + (lane & 15) * 4 * 128, op ? &tm_vg : &tm_kg,
-                        bar(kWsFull + st), col + hf * 64, r[0], r[1], r[2], r[3]);
-        }
+      for (int i = 0; i < 4; ++i) {
+        const int key = td.key0 + (lane & 15) * 4 + i;
+        out[i] = key < td.k_hi ? __ldg(td.idx + key) : num_slots;  // row past the pool -> zero-filled by the copy engine
       }
-      ++nseg;
-      cur = seg_end;
-      if (cur == ue && hg == HG - 1 && cur < g1) {
-        pre += it.tiles;
-        ++item;
-        it = ws_item(p, item);
+      lslot = (fused.new_k != nullptr && td.last_of_unit && td.L > 0) ? __ldg(td.idx + td.L - 1) : -1;
+    };
+    bool have = next_tile();
+    if (have) {
+      cur_t = nxt_t;
+      fetch_ids(cur_t, r, last_slot);
+    }
+    while (have) {
+      const bool have_next = next_tile();
+      if (have_next) fetch_ids(nxt_t, rn, last_slot_n);
+      // ---- issue the current tile ----
+      if (last_slot >= 0 && last_slot != fused.skip_slot && last_slot < num_slots) {
+        // new-token row of this unit: written right before the tile that contains it is fetched
+        constexpr int kVecs = D * 2 / 16;  // 16-byte pieces of one (token, kv head) row
+        const bool isv = lane >= 16;
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(isv ? fused.new_v : fused.new_k) +
+                             ((int64_t)cur_t.item * fused.new_stride + (int64_t)cur_t.kvh * D) * 2;
+        uint8_t* dstg = reinterpret_cast<uint8_t*>(const_cast<void*>(isv ? p.v_cache : p.k_cache)) +
+                        ((int64_t)last_slot * p.kv_stride + (int64_t)cur_t.kvh * D) * 2;
+        for (int v = lane & 15; v < kVecs; v += 16)
+          *reinterpret_cast<uint4*>(dstg + v * 16) = *reinterpret_cast<const uint4*>(src + v * 16);
+        // generic-proxy global writes -> ordered before the async-proxy (TMA) reads issued after the __syncwarp below
+        asm volatile("fence.proxy.async.global;\n" ::: "memory");
       }
+      const int g0s = __shfl_sync(0xffffffffu, r[0], lane & ~3);
+      bool contig = (r[1] == r[0] + 1) && (r[2] == r[0] + 2) && (r[3] == r[0] + 3) &&
+                    (r[0] == g0s + 4 * (lane & 3));
+      contig = __all_sync(0xffffffffu, contig) && (cur_t.key0 + kDecTile <= cur_t.k_hi);
+      const int st = n % kWsStages;
+      if (n >= kWsStages) mbar_wait(bar(kWsEmpty + st), ((n / kWsStages) + 1) & 1);
+      if (lane == 0) mbar_arrive_expect_tx(bar(kWsFull + st), S::kStageBytes);
+      __syncwarp();
+      const uint32_t dst = smem0 + S::kRing + st * S::kStageBytes;
+      if (contig) {
+        // 4 pages x halves x {K, V}: one 16-row box each, spread over the first lanes
+        const int job = lane;  // job = op * 4 * kHalves + page * kHalves + hf
+        const int op = job / (4 * kHalves), pg = (job / kHalves) & 3, hf = job % kHalves;
+        const int row = __shfl_sync(0xffffffffu, r[0], pg * 4);
+        if (job < 8 * kHalves)
+          tma_load_2d(dst + op * S::kTileBytes + hf * S::kHalfBytes + pg * 16 * 128, op ? &tm_vb : &tm_kb,
+                      bar(kWsFull + st), cur_t.col + hf * 64, row);
+      } else {
+        const int op = lane >> 4;
+#pragma unroll
+        for (int hf = 0; hf < kHalves; ++hf)
+          tma_gather4(dst + op * S::kTileBytes + hf * S::kHalfBytes + (lane & 15) * 4 * 128, op ? &tm_vg : &tm_kg,
+                      bar(kWsFull + st), cur_t.col + hf * 64, r[0], r[1], r[2], r[3]);
+      }
+      ++n;
+      have = have_next;
+      cur_t = nxt_t;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) r[i] = rn[i];
+      last_slot = last_slot_n;
     }
     return;
   }
