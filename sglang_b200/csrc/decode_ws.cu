@@ -83,6 +83,18 @@ __device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint
 }
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, 128;\n" ::: "memory"); }
 
+// dev-only timeline (make trace: -DWS_TRACE): p.lse is taken over as int64 [CTAs][8] of %globaltimer stamps
+#ifdef WS_TRACE
+__device__ __forceinline__ void ws_stamp(const DecodeParams& p, int slot) {
+  long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  reinterpret_cast<long long*>(p.lse)[(int64_t)blockIdx.x * 8 + slot] = t;
+}
+#define WS_STAMP(cond, slot) if (cond) ws_stamp(p, slot)
+#else
+#define WS_STAMP(cond, slot)
+#endif
+
 struct WsFused {  // the step's new K/V rows, written into the pool by the producer (nullptr: the caller stored them)
   const void* new_k;
   const void* new_v;
@@ -107,6 +119,12 @@ __global__ void __launch_bounds__(kWsThreads, 2)
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int HG = p.Hkv * p.groups_per_kvh;
+  WS_STAMP(tid == 0, 0);
+  // programmatic dependent launch: everything above ran while the previous kernel in the stream drained; global
+  // memory written by it (the pool, kv_indptr / kv_indices) is only read after this wait.  No-op when the kernel
+  // was launched without the attribute.
+  asm volatile("griddepcontrol.wait;\n" ::: "memory");
+  WS_STAMP(tid == 0, 1);
 
   // ---- partition: total tiles, this CTA's range, the request its range starts in (decode_sk.cu) ---------------
   int64_t mine = 0;
@@ -170,6 +188,8 @@ __global__ void __launch_bounds__(kWsThreads, 2)
     mbar_fence_init();
   }
   __syncthreads();
+  asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
+  WS_STAMP(tid == 0, 2);
 
   // ---- segment walk, identical in both roles --------------------------------------------------------------------
   int item = s_i0;
@@ -301,6 +321,7 @@ __global__ void __launch_bounds__(kWsThreads, 2)
           tma_gather4(dst + op * S::kTileBytes + hf * S::kHalfBytes + (lane & 15) * 4 * 128, op ? &tm_vg : &tm_kg,
                       bar(kWsFull + st), cur_t.col + hf * 64, r[0], r[1], r[2], r[3]);
       }
+      WS_STAMP(n == 0 && lane == 0, 3);
       ++n;
       have = have_next;
       cur_t = nxt_t;
@@ -361,6 +382,7 @@ __global__ void __launch_bounds__(kWsThreads, 2)
     for (int t = t_lo; t < t_hi; ++t, ++n) {
       st = n % kWsStages;
       mbar_wait(bar(kWsFull + st), (n / kWsStages) & 1);
+      WS_STAMP(n == 0 && tid == 0, 4);
       const uint32_t ks = smem0 + S::kRing + st * S::kStageBytes;
       const uint32_t vs = ks + S::kTileBytes;
       const int key0 = t * kDecTile + warp * 16;  // first key of this warp
@@ -437,6 +459,7 @@ __global__ void __launch_bounds__(kWsThreads, 2)
       }
     }
 
+    WS_STAMP(seg_end == g1 && tid == 0, 5);
     // ---- merge the four warps through the last tile's stage (fp32 [4][16][D] == one stage) ------------------
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
@@ -560,6 +583,7 @@ __global__ void __launch_bounds__(kWsThreads, 2)
       it = ws_item(p, item);
     }
   }
+  WS_STAMP(tid == 0, 6);
 }
 
 int ws_ctas() { return 2 * sm_count(); }
@@ -574,6 +598,23 @@ static int launch_decode_ws(const CUtensorMap& kg, const CUtensorMap& vg, const 
     B2_CUDA(cudaFuncSetAttribute(decode_ws_kernel<D, kBf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     B2_CUDA(cudaFuncSetAttribute(decode_ws_kernel<D, kBf16>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     configured = true;
+  }
+  // B200ATTN_PDL=1: programmatic stream serialization - the grid may start while the previous kernel of the stream
+  // drains; the kernel orders itself with griddepcontrol.wait (dev switch, measured in profiles/)
+  static const bool pdl = [] { const char* e = getenv("B200ATTN_PDL"); return e != nullptr && atoi(e) != 0; }();
+  if (pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)ws_ctas());
+    cfg.blockDim = dim3(kWsThreads);
+    cfg.dynamicSmemBytes = kSmem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    B2_CUDA(cudaLaunchKernelEx(&cfg, decode_ws_kernel<D, kBf16>, kg, vg, kb, vb, p, fused, min_tiles, num_slots));
+    return B200ATTN_OK;
   }
   decode_ws_kernel<D, kBf16><<<ws_ctas(), kWsThreads, kSmem, st>>>(kg, vg, kb, vb, p, fused, min_tiles, num_slots);
   B2_LAUNCH_CHECK();
