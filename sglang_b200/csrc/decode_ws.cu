@@ -91,8 +91,10 @@ __device__ __forceinline__ void ws_stamp(const DecodeParams& p, int slot) {
   reinterpret_cast<long long*>(p.lse)[(int64_t)blockIdx.x * 8 + slot] = t;
 }
 #define WS_STAMP(cond, slot) if (cond) ws_stamp(p, slot)
+#define WS_LSE_ON false
 #else
 #define WS_STAMP(cond, slot)
+#define WS_LSE_ON (p.lse != nullptr)
 #endif
 
 struct WsFused {  // the step's new K/V rows, written into the pool by the producer (nullptr: the caller stored them)
@@ -517,7 +519,7 @@ __global__ void __launch_bounds__(kWsThreads, 2)
         pk.x = pack2<kBf16>(acc.x, acc.y);
         pk.y = pack2<kBf16>(acc.z, acc.w);
         *reinterpret_cast<uint2*>(dst) = pk;
-        if (p.lse != nullptr && cc == 0) p.lse[(int64_t)qrow * p.Hq + h] = lse2 * kLn2;
+        if (WS_LSE_ON && cc == 0) p.lse[(int64_t)qrow * p.Hq + h] = lse2 * kLn2;
       } else {
         const int64_t w = (int64_t)wslot * kDecMaxG + r;
         *reinterpret_cast<float4*>(p.ws_o + w * D + cc) = acc;
@@ -567,7 +569,7 @@ __global__ void __launch_bounds__(kWsThreads, 2)
           pk.x = pack2<kBf16>(acc.x * inv, acc.y * inv);
           pk.y = pack2<kBf16>(acc.z * inv, acc.w * inv);
           *reinterpret_cast<uint2*>(dst) = pk;
-          if (p.lse != nullptr && cc == 0)
+          if (WS_LSE_ON && cc == 0)
             p.lse[(int64_t)qrow * p.Hq + h] = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
         }
       }

@@ -16,7 +16,7 @@ Hq, Hkv, D, page = 32, 8, 128, 16
 def main():
     _lib.load()
     _lib._lib = _lib.load_variant(os.path.join(os.path.dirname(_lib.LIB_PATH), "libb200attn_trace.so"))
-    for B, ctx in [(64, 4096), (16, 4096), (4, 8192), (256, 8192)]:
+    for B, ctx in [(64, 4096), (16, 4096), (256, 8192)]:
         n_pages = B * ctx // page + 8
         perm = torch.randperm(n_pages - 1) + 1
         table = perm[: B * ctx // page].view(B, ctx // page).int().to(DEV)
@@ -46,7 +46,12 @@ def main():
         print(f"B={B} ctx={ctx}: event time {ev0.elapsed_time(ev1) * 1e3:.1f} us, {int(live.sum())} CTAs")
         for j, nm in enumerate(names):
             col = rel[:, j]
-            print(f"   {nm:14s} min {col.min():8.2f}  median {col.median():8.2f}  max {col.max():8.2f} us")
+            qs = torch.quantile(col, torch.tensor([0.0, 0.1, 0.25, 0.5, 0.75, 0.9, 1.0], dtype=torch.float64))
+            print(f"   {nm:14s} " + "  ".join(f"{float(x):8.2f}" for x in qs) + f"   mean {float(col.mean()):8.2f}")
+        fin = rel[:, 5]
+        print("   last_computed by CTA index (first 40):", [round(float(x)) for x in fin[:40]])
+        print("   last_computed, CTA c vs c+148 (same SM?) corr:",
+              float(torch.corrcoef(torch.stack([fin[:148], fin[148:296]]))[0, 1]) if fin.numel() == 296 else None)
         del kc, vc
 
 
