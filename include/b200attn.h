@@ -196,8 +196,10 @@ int b200attn_decode_sk(const void* q, int64_t q_stride, const void* k_cache, con
 
 /* --------------------------------------------------------------------------
  * (a4) Decode, warp-specialised persistent kernel fed by TMA (16-bit pools; the
- * default decode path of B200AttnBackend).  Same contract, arithmetic and flat
- * tile-stream partition as b200attn_decode_sk; one producer warp per CTA keeps a
+ * default decode path of B200AttnBackend).  Same contract and arithmetic as
+ * b200attn_decode_sk; the tile stream is cut by a guided schedule (one static chunk
+ * of half the fair share per CTA, then ever smaller chunks drawn from a global
+ * ticket, so CTAs that stream faster take more); one producer warp per CTA keeps a
  * 3-stage ring full through the copy engine (16-row tiled boxes when every aligned
  * 16-key group sits in 16 consecutive pool slots, tile::gather4 otherwise) and runs
  * ahead across unit boundaries, four consumer warps do the mma.sync math.
@@ -208,10 +210,10 @@ int b200attn_decode_sk(const void* q, int64_t q_stride, const void* k_cache, con
  * separate b200attn_kv_store launch of a decode layer-call (memory_pool.py:2331-2456:
  * store before read).  Rows whose slot == skip_slot are not written (-1: write all).
  * Needs identity q_rows / req_ids.  k_cache / v_cache are written only in that case.
- * Workspace: b200attn_decode_ws_workspace_bytes(D) bytes, zero-initialised once
+ * Workspace: b200attn_decode_ws_workspace_bytes(Hq, Hkv, D) bytes, zero-initialised once
  * (fixed-size counter header first, like b200attn_decode).
  * -------------------------------------------------------------------------- */
-int64_t b200attn_decode_ws_workspace_bytes(int32_t D);
+int64_t b200attn_decode_ws_workspace_bytes(int32_t Hq, int32_t Hkv, int32_t D);
 
 int b200attn_decode_ws(const void* q, int64_t q_stride, void* k_cache, void* v_cache,
                        int64_t kv_stride, int64_t num_slots, void* o, int64_t o_stride, float* lse,

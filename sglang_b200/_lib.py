@@ -52,7 +52,7 @@ SIGNATURES = {
         [_vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, C.c_int,
          _f32, _i32, _i32, _f32, _vp, _vp, _i64, _vp],
     ),
-    "b200attn_decode_ws_workspace_bytes": (_i64, [_i32]),
+    "b200attn_decode_ws_workspace_bytes": (_i64, [_i32, _i32, _i32]),
     "b200attn_decode_ws": (
         C.c_int,
         [_vp, _i64, _vp, _vp, _i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, C.c_int,

@@ -31,6 +31,13 @@ namespace b200attn {
 constexpr int kWsThreads = 160;  // 4 consumer warps + 1 producer warp
 constexpr int kWsConsumers = 128;
 constexpr int kWsStages = 3;
+constexpr int kWsMinChunk = 2;    // smallest chunk of the guided schedule (tiles)
+constexpr int kWsMaxLevels = 12;  // schedule levels; chunks <= (kWsMaxLevels + 1) * CTAs
+
+struct WsMsg {  // chunk index (-1: no more work), the request its first tile lies in, tiles of the requests before it
+  int k, item;
+  int64_t pre;
+};
 
 struct WsItem {
   int kv_beg, L, tiles;
@@ -108,15 +115,19 @@ template <int D, bool kBf16>
 __global__ void __launch_bounds__(kWsThreads, 2)
     decode_ws_kernel(const __grid_constant__ CUtensorMap tm_kg, const __grid_constant__ CUtensorMap tm_vg,
                      const __grid_constant__ CUtensorMap tm_kb, const __grid_constant__ CUtensorMap tm_vb,
-                     const DecodeParams p, const WsFused fused, const int min_tiles, const int num_slots) {
+                     const DecodeParams p, const WsFused fused, const int min_tiles, const int num_slots,
+                     const int ws_rows) {
   using namespace sm100;
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
   using S = WsSmem<D>;
   constexpr int kHalves = S::kHalves;
   extern __shared__ uint8_t smem_raw[];
   __shared__ int64_t s_red[kWsThreads / 32];
-  __shared__ int s_i0;
-  __shared__ int64_t s_pre0;
+  __shared__ int64_t s_loff[kWsMaxLevels + 1];  // first tile of every schedule level (+ total)
+  __shared__ int s_lfirst[kWsMaxLevels + 1];    // first chunk index of every level (+ number of chunks)
+  __shared__ int s_lsize[kWsMaxLevels];         // chunk size (tiles) of every level
+  __shared__ int s_nlev;
+  __shared__ WsMsg s_msg[2];                    // producer -> consumers: the chunk a segment opens
   __shared__ int s_last;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -128,7 +139,14 @@ __global__ void __launch_bounds__(kWsThreads, 2)
   asm volatile("griddepcontrol.wait;\n" ::: "memory");
   WS_STAMP(tid == 0, 1);
 
-  // ---- partition: total tiles, this CTA's range, the request its range starts in (decode_sk.cu) ---------------
+  // ---- work list: the batch is ONE unit-major stream of 64-key tiles,
+  //     g = HG * (tiles of the requests before i) + hg * tiles_i + t        (unit = (request i, kv head group hg)),
+  // cut into CHUNKS by a guided schedule that every CTA derives for itself: level 0 hands each of the N CTAs one
+  // chunk of ~ half its fair share (static: chunk = blockIdx.x, no atomic), every further level halves the chunk
+  // size over what is left, down to kWsMinChunk tiles; chunks beyond level 0 are drawn from a global ticket by
+  // whichever CTA runs dry first.  SMs do not stream at the same rate (measured: equal static ranges finish
+  // between 144 and 177 us on cfg2), so equal ranges leave a ~7 % tail; with tickets the tail is one small chunk.
+  // Chunk boundaries are a pure function of (total, N): pieces of a unit are found arithmetically for the merge.
   int64_t mine = 0;
   for (int i = tid; i < p.B; i += kWsThreads) mine += ws_item(p, i).tiles;
 #pragma unroll
@@ -139,40 +157,27 @@ __global__ void __launch_bounds__(kWsThreads, 2)
 #pragma unroll
   for (int w = 0; w < kWsThreads / 32; ++w) total += s_red[w];
   total *= HG;
-  const int N = (int)max((int64_t)1, min((int64_t)gridDim.x, total / min_tiles));
-  const int c = blockIdx.x;
-  if (c >= N) return;
-  const int64_t g0 = (int64_t)c * total / N;
-  const int64_t g1 = (int64_t)(c + 1) * total / N;
-  if (g0 >= g1) return;
-  {
-    int64_t base = 0;  // tiles of the requests before this chunk (same value in every thread)
-    for (int i0 = 0; i0 < p.B; i0 += kWsThreads) {
-      const int i = i0 + tid;
-      const int64_t t = i < p.B ? ws_item(p, i).tiles : 0;
-      int64_t incl = t;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int64_t y = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += y;
-      }
-      __syncthreads();  // s_red reuse
-      if (lane == 31) s_red[warp] = incl;
-      __syncthreads();
-      int64_t woff = 0, chunk_total = 0;
-#pragma unroll
-      for (int w = 0; w < kWsThreads / 32; ++w) {
-        if (w < warp) woff += s_red[w];
-        chunk_total += s_red[w];
-      }
-      const int64_t excl = base + woff + incl - t;
-      if (i < p.B && excl * HG <= g0 && g0 < (excl + t) * HG) {
-        s_i0 = i;
-        s_pre0 = excl;
-      }
-      base += chunk_total;
-      if (base * HG > g0) break;  // uniform: found in this chunk
+  const int N = (int)gridDim.x;
+  if (tid == 0) {
+    const int64_t cmin = max(kWsMinChunk, min_tiles);
+    int64_t off = 0, first = 0;
+    int nl = 0;
+    while (off < total) {
+      const int64_t R = total - off;
+      const bool last = (nl == kWsMaxLevels - 1);
+      const int64_t S = max(cmin, (R + 2 * N - 1) / (2 * N));
+      const int64_t all = (R + S - 1) / S;
+      const int64_t cnt = (S == cmin || last) ? all : min((int64_t)N, all);
+      s_loff[nl] = off;
+      s_lfirst[nl] = (int)first;
+      s_lsize[nl] = (int)S;
+      off = min(total, off + cnt * S);
+      first += cnt;
+      ++nl;
     }
+    s_loff[nl] = total;
+    s_lfirst[nl] = (int)first;
+    s_nlev = nl;
   }
   const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (smem0 - smem_u32(smem_raw));
@@ -193,11 +198,29 @@ __global__ void __launch_bounds__(kWsThreads, 2)
   asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
   WS_STAMP(tid == 0, 2);
 
-  // ---- segment walk, identical in both roles --------------------------------------------------------------------
-  int item = s_i0;
-  int64_t pre = s_pre0;  // tiles of the requests before `item`
-  WsItem it = ws_item(p, item);
-  int64_t cur = g0;
+  // ---- schedule arithmetic (shared memory tables, read-only from here on) ----------------------------------------
+  const int nlev = s_nlev;
+  const int num_chunks = s_lfirst[nlev];
+  auto chunk_bounds = [&](int k, int64_t& b, int64_t& e) {
+    int L = 0;
+    while (k >= s_lfirst[L + 1]) ++L;
+    b = s_loff[L] + (int64_t)(k - s_lfirst[L]) * s_lsize[L];
+    e = min(b + s_lsize[L], s_loff[L + 1]);
+  };
+  auto chunk_of = [&](int64_t g) -> int {  // chunk that holds global tile g
+    int L = 0;
+    while (g >= s_loff[L + 1]) ++L;
+    return s_lfirst[L] + (int)((g - s_loff[L]) / s_lsize[L]);
+  };
+  int* sched_next = p.ws_cnt + kDecMaxUnits - 2;  // ticket of the dynamically drawn chunks
+  int* sched_done = p.ws_cnt + kDecMaxUnits - 1;  // CTAs that have drawn their last ticket
+  const int num_static = s_lfirst[nlev > 0 ? 1 : 0];  // level 0: chunk = blockIdx.x
+
+  // ---- segment walk state (both roles) --------------------------------------------------------------------------
+  int item = 0;
+  int64_t pre = 0;  // tiles of the requests before `item`
+  WsItem it;
+  int64_t cur = 0, g1 = 0;  // position in / end of the current chunk
   int n = 0;     // tiles produced / consumed so far (ring position)
   int nseg = 0;  // segments so far (query-block buffer parity)
 
@@ -219,6 +242,11 @@ __global__ void __launch_bounds__(kWsThreads, 2)
     };
     int t = 0, t_hi = 0, hg = 0;
     int64_t ue = 0, seg_end = 0;
+    int chunk = (int)blockIdx.x < num_static ? (int)blockIdx.x : -1;  // -1: draw a ticket
+    bool chunk_open = false;   // `chunk` has been entered (its first segment was set up)
+    bool finished = false;
+    int scan_item = 0;         // forward scan over the requests (chunk starts only move forward)
+    int64_t scan_pre = 0;
     Tile cur_t, nxt_t;
     int r[4], rn[4];
     int last_slot = -1, last_slot_n = -1;
@@ -226,6 +254,7 @@ __global__ void __launch_bounds__(kWsThreads, 2)
     // it is the segment's first); returns false at the end of the range
     auto next_tile = [&]() -> bool {
       if (t == t_hi) {  // segment exhausted (or first call)
+        if (finished) return false;
         if (t_hi != 0) {
           cur = seg_end;
           if (cur == ue && hg == HG - 1 && cur < g1) {
@@ -234,7 +263,58 @@ __global__ void __launch_bounds__(kWsThreads, 2)
             it = ws_item(p, item);
           }
         }
-        if (cur >= g1) return false;
+        bool first_of_chunk = false;
+        if (!chunk_open || cur >= g1) {
+          // ---- next chunk: the static one first, then tickets ----
+          if (chunk_open || chunk < 0) {
+            int tk = 0;
+            if (lane == 0) tk = num_static + atomicAdd(sched_next, 1);
+            chunk = __shfl_sync(0xffffffffu, tk, 0);
+          }
+          chunk_open = true;
+          const int qs = nseg & 1;
+          if (nseg >= 2) mbar_wait(bar(kWsQEmpty + qs), ((nseg >> 1) + 1) & 1);
+          if (chunk >= num_chunks) {
+            // no more work: tell the consumers, and let the last CTA to get here reset the scheduler
+            if (lane == 0) {
+              s_msg[qs].k = -1;
+              mbar_arrive(bar(kWsQFull + qs));
+              if (atomicAdd(sched_done, 1) == (int)gridDim.x - 1) {
+                *sched_next = 0;
+                *sched_done = 0;
+              }
+            }
+            finished = true;
+            return false;
+          }
+          chunk_bounds(chunk, cur, g1);
+          // request holding tile `cur`: warp-parallel forward scan from where the previous chunk's search ended
+          while (true) {
+            const int i = scan_item + lane;
+            const int ti = i < p.B ? ws_item(p, i).tiles : 0;
+            int64_t incl = ti;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+              const int64_t y = __shfl_up_sync(0xffffffffu, incl, o);
+              if (lane >= o) incl += y;
+            }
+            const unsigned hit = __ballot_sync(0xffffffffu, i < p.B && (scan_pre + incl) * HG > cur);
+            if (hit != 0u) {
+              const int l = __ffs(hit) - 1;
+              const int64_t incl_l = __shfl_sync(0xffffffffu, incl, l);
+              const int ti_l = __shfl_sync(0xffffffffu, ti, l);
+              scan_item += l;
+              scan_pre += incl_l - ti_l;
+              break;
+            }
+            scan_pre += __shfl_sync(0xffffffffu, incl, 31);
+            scan_item += 32;
+          }
+          item = scan_item;
+          pre = scan_pre;
+          it = ws_item(p, item);
+          first_of_chunk = true;
+        }
         const int64_t ubase = pre * HG;
         hg = (int)((cur - ubase) / it.tiles);
         const int64_t us = ubase + (int64_t)hg * it.tiles;
@@ -248,8 +328,13 @@ __global__ void __launch_bounds__(kWsThreads, 2)
         const int h0 = kvh * p.G + grp * kDecMaxG;
         const int gcount = min(kDecMaxG, p.G - grp * kDecMaxG);
         const int qs = nseg & 1;
-        if (nseg >= 2) mbar_wait(bar(kWsQEmpty + qs), ((nseg >> 1) + 1) & 1);
+        if (!first_of_chunk && nseg >= 2) mbar_wait(bar(kWsQEmpty + qs), ((nseg >> 1) + 1) & 1);
         if (lane == 0) {
+          if (first_of_chunk) {  // published with the segment's query block (the arrive below releases these writes)
+            s_msg[qs].k = chunk;
+            s_msg[qs].item = item;
+            s_msg[qs].pre = pre;
+          }
           const uint32_t qbytes = (uint32_t)(gcount * D * 2);
           mbar_arrive_expect_tx(bar(kWsQFull + qs), qbytes);
           bulk_load_1d(smem0 + S::kQ + qs * S::kQBytes,
@@ -338,7 +423,22 @@ __global__ void __launch_bounds__(kWsThreads, 2)
   const int lm = lane >> 3, lr = lane & 7;
   float* sm_m = reinterpret_cast<float*>(smem + S::kML);  // [4][16]
   float* sm_l = sm_m + 64;                                // [4][16]
-  while (cur < g1) {
+  int chunk = -1;
+  while (true) {
+    // every segment starts with the producer's query block; the first segment of a chunk also carries the chunk
+    {
+      const int qs = nseg & 1;
+      mbar_wait(bar(kWsQFull + qs), (nseg >> 1) & 1);
+      if (cur >= g1) {
+        const WsMsg msg = s_msg[qs];
+        if (msg.k < 0) break;
+        chunk = msg.k;
+        item = msg.item;
+        pre = msg.pre;
+        chunk_bounds(chunk, cur, g1);
+        it = ws_item(p, item);
+      }
+    }
     const int64_t ubase = pre * HG;
     const int hg = (int)((cur - ubase) / it.tiles);
     const int64_t us = ubase + (int64_t)hg * it.tiles;
@@ -359,7 +459,6 @@ __global__ void __launch_bounds__(kWsThreads, 2)
     uint32_t qf[D / 16][4];
     {
       const int qs = nseg & 1;
-      mbar_wait(bar(kWsQFull + qs), (nseg >> 1) & 1);
       const uint8_t* qb = smem + S::kQ + qs * S::kQBytes;
       const int r0 = lane >> 2, c0 = (lane & 3) * 2;
 #pragma unroll
@@ -461,7 +560,7 @@ __global__ void __launch_bounds__(kWsThreads, 2)
       }
     }
 
-    WS_STAMP(seg_end == g1 && tid == 0, 5);
+    WS_STAMP(tid == 0, 5);
     // ---- merge the four warps through the last tile's stage (fp32 [4][16][D] == one stage) ------------------
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
@@ -486,7 +585,7 @@ __global__ void __launch_bounds__(kWsThreads, 2)
       }
     }
     consumer_sync();
-    const int wslot = c * 2 + (t_lo == 0 ? 1 : 0);  // partial pieces only
+    const int wslot = chunk * 2 + (t_lo == 0 ? 1 : 0);  // partial pieces only
     for (int e = tid; e < gcount * (D / 4); e += kWsConsumers) {
       const int r = e / (D / 4), cc = (e - r * (D / 4)) * 4;
       float m = -INFINITY;
@@ -521,15 +620,15 @@ __global__ void __launch_bounds__(kWsThreads, 2)
         *reinterpret_cast<uint2*>(dst) = pk;
         if (WS_LSE_ON && cc == 0) p.lse[(int64_t)qrow * p.Hq + h] = lse2 * kLn2;
       } else {
-        const int64_t w = (int64_t)wslot * kDecMaxG + r;
+        const int64_t w = (int64_t)wslot * ws_rows + r;
         *reinterpret_cast<float4*>(p.ws_o + w * D + cc) = acc;
         if (cc == 0) p.ws_lse[w] = lse2;
       }
     }
     if (!whole) {
       // ---- arrival ticket; the last piece of the unit to arrive merges all of them -------------------------
-      const int c_first = ws_owner(us, total, N);
-      const int c_last = ws_owner(ue - 1, total, N);
+      const int c_first = chunk_of(us);
+      const int c_last = chunk_of(ue - 1);
       __threadfence();
       consumer_sync();
       if (tid == 0) {
@@ -546,13 +645,13 @@ __global__ void __launch_bounds__(kWsThreads, 2)
           const int h = h0 + r;
           float m = -INFINITY;
           for (int pc = c_first; pc <= c_last; ++pc) {
-            const int64_t w = (int64_t)(pc * 2 + (pc == c_first ? 1 : 0)) * kDecMaxG + r;
+            const int64_t w = (int64_t)(pc * 2 + (pc == c_first ? 1 : 0)) * ws_rows + r;
             m = fmaxf(m, __ldcg(p.ws_lse + w));
           }
           float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
           float l = 0.f;
           for (int pc = c_first; pc <= c_last; ++pc) {
-            const int64_t w = (int64_t)(pc * 2 + (pc == c_first ? 1 : 0)) * kDecMaxG + r;
+            const int64_t w = (int64_t)(pc * 2 + (pc == c_first ? 1 : 0)) * ws_rows + r;
             const float ls = __ldcg(p.ws_lse + w);
             const float f = (ls == -INFINITY) ? 0.f : fast_exp2(ls - m);
             const float4 x = __ldcg(reinterpret_cast<const float4*>(p.ws_o + w * D + cc));
@@ -592,7 +691,7 @@ int ws_ctas() { return 2 * sm_count(); }
 
 template <int D, bool kBf16>
 static int launch_decode_ws(const CUtensorMap& kg, const CUtensorMap& vg, const CUtensorMap& kb, const CUtensorMap& vb,
-                            const DecodeParams& p, const WsFused& fused, int min_tiles, int num_slots,
+                            const DecodeParams& p, const WsFused& fused, int min_tiles, int num_slots, int ws_rows,
                             cudaStream_t st) {
   constexpr int kSmem = WsSmem<D>::kTotal + 1024;  // + alignment slack
   static bool configured = false;
@@ -615,20 +714,26 @@ static int launch_decode_ws(const CUtensorMap& kg, const CUtensorMap& vg, const 
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    B2_CUDA(cudaLaunchKernelEx(&cfg, decode_ws_kernel<D, kBf16>, kg, vg, kb, vb, p, fused, min_tiles, num_slots));
+    B2_CUDA(cudaLaunchKernelEx(&cfg, decode_ws_kernel<D, kBf16>, kg, vg, kb, vb, p, fused, min_tiles, num_slots, ws_rows));
     return B200ATTN_OK;
   }
-  decode_ws_kernel<D, kBf16><<<ws_ctas(), kWsThreads, kSmem, st>>>(kg, vg, kb, vb, p, fused, min_tiles, num_slots);
+  decode_ws_kernel<D, kBf16><<<ws_ctas(), kWsThreads, kSmem, st>>>(kg, vg, kb, vb, p, fused, min_tiles, num_slots, ws_rows);
   B2_LAUNCH_CHECK();
   return B200ATTN_OK;
 }
 
 }  // namespace b200attn
 
-extern "C" int64_t b200attn_decode_ws_workspace_bytes(int32_t D) {
+namespace b200attn {
+static int ws_rows_for(int Hq, int Hkv) { return Hq / Hkv < kDecMaxG ? Hq / Hkv : kDecMaxG; }
+static int64_t ws_max_chunks() { return (int64_t)(kWsMaxLevels + 1) * ws_ctas(); }
+}  // namespace b200attn
+
+extern "C" int64_t b200attn_decode_ws_workspace_bytes(int32_t Hq, int32_t Hkv, int32_t D) {
   using namespace b200attn;
-  // fixed counter header + two partial slots per CTA ([16][D] fp32 + [16] lse)
-  return kDecCounterBytes + (int64_t)ws_ctas() * 2 * kDecMaxG * (D + 1) * 4;
+  if (Hq <= 0 || Hkv <= 0 || D <= 0) return 0;
+  // fixed counter header + two partial slots per chunk of the guided schedule ([min(G,16)][D] fp32 + lse)
+  return kDecCounterBytes + ws_max_chunks() * 2 * ws_rows_for(Hq, Hkv) * (D + 1) * 4;
 }
 
 extern "C" int b200attn_decode_ws(const void* q, int64_t q_stride, void* k_cache, void* v_cache, int64_t kv_stride,
@@ -656,11 +761,11 @@ extern "C" int b200attn_decode_ws(const void* q, int64_t q_stride, void* k_cache
                "decode_ws: the fused store needs identity row maps and 16-byte aligned new_k / new_v rows");
   if (dtype != B200ATTN_BF16 && dtype != B200ATTN_FP16) B2_UNSUPPORTED("decode_ws: dtype %d", dtype);
   if (D != 64 && D != 128) B2_UNSUPPORTED("decode_ws: head_dim %d (supported: 64, 128)", D);
-  const int64_t need = b200attn_decode_ws_workspace_bytes(D);
+  const int64_t need = b200attn_decode_ws_workspace_bytes(Hq, Hkv, D);
   B2_CHECK_ARG(workspace && workspace_bytes >= need, "decode_ws: workspace too small (%lld < %lld)",
                (long long)workspace_bytes, (long long)need);
-  B2_CHECK_ARG((int64_t)B * Hkv * ((Hq / Hkv + kDecMaxG - 1) / kDecMaxG) <= kDecMaxUnits,
-               "decode_ws: more than %d units", kDecMaxUnits);
+  B2_CHECK_ARG((int64_t)B * Hkv * ((Hq / Hkv + kDecMaxG - 1) / kDecMaxG) <= kDecMaxUnits - 2,
+               "decode_ws: more than %d units", kDecMaxUnits - 2);  // the last two counters drive the chunk tickets
   const CUtensorMap *kg, *vg, *kb, *vb;
   int rc = tensor_map_cached(&kg, k_cache, (uint64_t)num_slots, (uint64_t)Hkv * D, (uint64_t)kv_stride * 2, 64, 1);
   if (rc) return rc;
@@ -670,7 +775,7 @@ extern "C" int b200attn_decode_ws(const void* q, int64_t q_stride, void* k_cache
   if (rc) return rc;
   rc = tensor_map_cached(&vb, v_cache, (uint64_t)num_slots, (uint64_t)Hkv * D, (uint64_t)kv_stride * 2, 64, 16);
   if (rc) return rc;
-  const int cap = ws_ctas();
+  const int rows = ws_rows_for(Hq, Hkv);
   DecodeParams p;
   p.q = q;
   p.k_cache = k_cache;
@@ -683,7 +788,7 @@ extern "C" int b200attn_decode_ws(const void* q, int64_t q_stride, void* k_cache
   p.req_ids = req_ids;
   p.ws_cnt = reinterpret_cast<int*>(workspace);
   p.ws_o = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + kDecCounterBytes);
-  p.ws_lse = p.ws_o + (int64_t)cap * 2 * kDecMaxG * D;
+  p.ws_lse = p.ws_o + ws_max_chunks() * 2 * rows * D;
   p.q_stride = q_stride;
   p.kv_stride = kv_stride;
   p.o_stride = o_stride;
@@ -710,9 +815,9 @@ extern "C" int b200attn_decode_ws(const void* q, int64_t q_stride, void* k_cache
   cudaStream_t st = (cudaStream_t)stream;
   if (D == 128)
     return dtype == B200ATTN_BF16
-               ? launch_decode_ws<128, true>(*kg, *vg, *kb, *vb, p, fused, min_tiles, (int)num_slots, st)
-               : launch_decode_ws<128, false>(*kg, *vg, *kb, *vb, p, fused, min_tiles, (int)num_slots, st);
+               ? launch_decode_ws<128, true>(*kg, *vg, *kb, *vb, p, fused, min_tiles, (int)num_slots, rows, st)
+               : launch_decode_ws<128, false>(*kg, *vg, *kb, *vb, p, fused, min_tiles, (int)num_slots, rows, st);
   return dtype == B200ATTN_BF16
-             ? launch_decode_ws<64, true>(*kg, *vg, *kb, *vb, p, fused, min_tiles, (int)num_slots, st)
-             : launch_decode_ws<64, false>(*kg, *vg, *kb, *vb, p, fused, min_tiles, (int)num_slots, st);
+             ? launch_decode_ws<64, true>(*kg, *vg, *kb, *vb, p, fused, min_tiles, (int)num_slots, rows, st)
+             : launch_decode_ws<64, false>(*kg, *vg, *kb, *vb, p, fused, min_tiles, (int)num_slots, rows, st);
 }

@@ -485,8 +485,8 @@ def decode_sk_workspace_bytes(B: int, Hq: int, Hkv: int, D: int) -> int:
     return int(_lib.load().b200attn_decode_sk_workspace_bytes(B, Hq, Hkv, D))
 
 
-def decode_ws_workspace_bytes(D: int) -> int:
-    return int(_lib.load().b200attn_decode_ws_workspace_bytes(D))
+def decode_ws_workspace_bytes(Hq: int, Hkv: int, D: int) -> int:
+    return int(_lib.load().b200attn_decode_ws_workspace_bytes(Hq, Hkv, D))
 
 
 def decode_ctas_per_sm(fp8_kv: bool = False) -> int:

@@ -28,7 +28,7 @@ def _run(sc, lens, q, min_chunk=64, lse=False, dtype=torch.bfloat16, d=None, **k
         d, kv_indptr, kv_indices = d
     B = len(lens)
     o = torch.full((B, sc.Hq, sc.D), float("nan"), dtype=dtype, device=DEV)
-    ws = torch.zeros(ops.decode_ws_workspace_bytes(sc.D), dtype=torch.uint8, device=DEV)
+    ws = torch.zeros(ops.decode_ws_workspace_bytes(sc.Hq, sc.Hkv, sc.D), dtype=torch.uint8, device=DEV)
     lse_t = torch.empty((B, sc.Hq), dtype=torch.float32, device=DEV) if lse else None
     for _ in range(2):  # the second launch must find the arrival counters at zero again
         o.fill_(float("nan"))
@@ -82,7 +82,7 @@ def test_decode_ws_features_fp16_and_row_maps():
         assert_close_attn(o, ref, f"decode_ws fp16 {kw}")
     d, kv_indptr, kv_indices = _meta(sc, lens)
     o = torch.zeros((4, Hq, D), dtype=torch.float16, device=DEV)
-    ws = torch.zeros(ops.decode_ws_workspace_bytes(D), dtype=torch.uint8, device=DEV)
+    ws = torch.zeros(ops.decode_ws_workspace_bytes(Hq, Hkv, D), dtype=torch.uint8, device=DEV)
     qg = q.to(DEV).view(4, Hq, D)
     ops.decode_attention(qg, d.k_cache, d.v_cache, o, kv_indptr, kv_indices, sc.scaling, workspace=ws,
                          q_rows=torch.tensor([2, 0], dtype=torch.int32, device=DEV),

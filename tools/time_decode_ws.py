@@ -37,7 +37,7 @@ def main():
         t = timed(lambda: ops.decode_attention(q, kc, vc, o, kv_indptr, kv_indices, D ** -0.5, max_splits=ms,
                                                min_chunk=256, workspace=ws))
         res["split_us"] = round(t * 1e3, 1)
-        ws2 = torch.zeros(ops.decode_ws_workspace_bytes(D), dtype=torch.uint8, device=DEV)
+        ws2 = torch.zeros(ops.decode_ws_workspace_bytes(Hq, Hkv, D), dtype=torch.uint8, device=DEV)
         for mc in (64, 256, 512):
             t = timed(lambda: ops.decode_attention(q, kc, vc, o2, kv_indptr, kv_indices, D ** -0.5, min_chunk=mc,
                                                    workspace=ws2, ws_kernel=True))

@@ -26,7 +26,7 @@ def main():
         vc = torch.randn((n_pages * page, Hkv, D), device=DEV).bfloat16()
         q = torch.randn((B, Hq, D), device=DEV).bfloat16()
         o = torch.empty_like(q)
-        ws = torch.zeros(ops.decode_ws_workspace_bytes(D), dtype=torch.uint8, device=DEV)
+        ws = torch.zeros(ops.decode_ws_workspace_bytes(Hq, Hkv, D), dtype=torch.uint8, device=DEV)
         ctas = 2 * ops.sm_count()
         trace = torch.zeros((max(ctas * 8, B * Hq) * 2,), dtype=torch.float32, device=DEV)  # viewed as int64 [ctas][8]
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
