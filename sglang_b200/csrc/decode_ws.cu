@@ -28,7 +28,8 @@
 
 namespace b200attn {
 
-constexpr int kWsThreads = 160;  // 4 consumer warps + 1 producer warp
+constexpr int kWsThreads = 192;  // 4 consumer warps + 1 producer warp + 1 merger warp
+constexpr int kWsMq = 4;         // consumer -> merger hand-off ring
 constexpr int kWsConsumers = 128;
 constexpr int kWsStages = 3;
 constexpr int kWsMinChunk = 2;    // smallest chunk of the guided schedule (tiles)
@@ -71,10 +72,21 @@ struct WsSmem {
   static constexpr int kQ = kRing + kWsStages * kStageBytes;
   static constexpr int kML = kQ + 2 * kQBytes;              // float m[4][16], l[4][16]
   static constexpr int kBar = kML + 512;
-  static constexpr int kTotal = kBar + 128;
+  static constexpr int kTotal = kBar + 8 * 24;
 };
 
-enum WsBar { kWsFull = 0, kWsEmpty = kWsStages, kWsQFull = 2 * kWsStages, kWsQEmpty = 2 * kWsStages + 2, kWsBarCount = 2 * kWsStages + 4 };
+enum WsBar {
+  kWsFull = 0,
+  kWsEmpty = kWsStages,
+  kWsQFull = 2 * kWsStages,
+  kWsQEmpty = 2 * kWsStages + 2,
+  kWsMqFull = 2 * kWsStages + 4,
+  kWsMqEmpty = kWsMqFull + kWsMq,
+  kWsBarCount = kWsMqEmpty + kWsMq
+};
+struct WsMerge {  // one partial piece of a unit, handed from the consumers to the merger warp
+  int unit, qrow, h0, gcount, c_first, c_last;
+};
 
 // byte offset of 16-byte chunk `chunk` of row `row` inside one operand tile laid out by TMA with SWIZZLE_128B:
 // [half][row][128 B], chunk index XOR (row & 7) inside each 128-byte line (tile base 1024-byte aligned)
@@ -128,7 +140,7 @@ __global__ void __launch_bounds__(kWsThreads, 2)
   __shared__ int s_lsize[kWsMaxLevels];         // chunk size (tiles) of every level
   __shared__ int s_nlev;
   __shared__ WsMsg s_msg[2];                    // producer -> consumers: the chunk a segment opens
-  __shared__ int s_last;
+  __shared__ WsMerge s_mq[kWsMq];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int HG = p.Hkv * p.groups_per_kvh;
@@ -192,6 +204,10 @@ __global__ void __launch_bounds__(kWsThreads, 2)
       mbar_init(bar(kWsQFull + s), 1);
       mbar_init(bar(kWsQEmpty + s), 4);
     }
+    for (int s = 0; s < kWsMq; ++s) {
+      mbar_init(bar(kWsMqFull + s), 1);
+      mbar_init(bar(kWsMqEmpty + s), 1);
+    }
     mbar_fence_init();
   }
   __syncthreads();
@@ -214,7 +230,7 @@ __global__ void __launch_bounds__(kWsThreads, 2)
   };
   int* sched_next = p.ws_cnt + kDecMaxUnits - 2;  // ticket of the dynamically drawn chunks
   int* sched_done = p.ws_cnt + kDecMaxUnits - 1;  // CTAs that have drawn their last ticket
-  const int num_static = s_lfirst[nlev > 0 ? 1 : 0];  // level 0: chunk = blockIdx.x
+  const int num_static = min((int)gridDim.x, s_lfirst[nlev > 0 ? 1 : 0]);  // level 0: chunk = blockIdx.x
 
   // ---- segment walk state (both roles) --------------------------------------------------------------------------
   int item = 0;
@@ -419,7 +435,65 @@ __global__ void __launch_bounds__(kWsThreads, 2)
     return;
   }
 
+  if (warp == 5) {
+    // ================================ merger ================================
+    for (int mseq = 0;; ++mseq) {
+      const int ms = mseq % kWsMq;
+      mbar_wait(bar(kWsMqFull + ms), (mseq / kWsMq) & 1);
+      const WsMerge d = s_mq[ms];
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(kWsMqEmpty + ms));
+      if (d.unit < 0) break;
+      // the piece's partial rows (written by the consumer warps, ordered before the hand-off) become visible
+      // device-wide before the ticket is drawn
+      __threadfence();
+      int last = 0;
+      if (lane == 0) {
+        int* cnt = p.ws_cnt + d.unit;
+        const int ticket = atomicAdd(cnt, 1);
+        last = (ticket == d.c_last - d.c_first);
+        if (last) *cnt = 0;  // self-cleaning
+      }
+      last = __shfl_sync(0xffffffffu, last, 0);
+      if (!last) continue;
+      __threadfence();
+      for (int e = lane; e < d.gcount * (D / 4); e += 32) {
+        const int r = e / (D / 4), cc = (e - r * (D / 4)) * 4;
+        const int h = d.h0 + r;
+        float m = -INFINITY;
+        for (int pc = d.c_first; pc <= d.c_last; ++pc) {
+          const int64_t w = (int64_t)(pc * 2 + (pc == d.c_first ? 1 : 0)) * ws_rows + r;
+          m = fmaxf(m, __ldcg(p.ws_lse + w));
+        }
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        float l = 0.f;
+        for (int pc = d.c_first; pc <= d.c_last; ++pc) {
+          const int64_t w = (int64_t)(pc * 2 + (pc == d.c_first ? 1 : 0)) * ws_rows + r;
+          const float ls = __ldcg(p.ws_lse + w);
+          const float f = (ls == -INFINITY) ? 0.f : fast_exp2(ls - m);
+          const float4 x = __ldcg(reinterpret_cast<const float4*>(p.ws_o + w * D + cc));
+          acc.x += f * x.x;
+          acc.y += f * x.y;
+          acc.z += f * x.z;
+          acc.w += f * x.w;
+          l += f;
+        }
+        if (p.sinks != nullptr && l > 0.f) l += fast_exp2(__ldg(p.sinks + h) * kLog2e - m);
+        const float inv = (l > 0.f) ? 1.f / l : 0.f;
+        T* dst = reinterpret_cast<T*>(p.o) + (int64_t)d.qrow * p.o_stride + (int64_t)h * D + cc;
+        uint2 pk;
+        pk.x = pack2<kBf16>(acc.x * inv, acc.y * inv);
+        pk.y = pack2<kBf16>(acc.z * inv, acc.w * inv);
+        *reinterpret_cast<uint2*>(dst) = pk;
+        if (WS_LSE_ON && cc == 0)
+          p.lse[(int64_t)d.qrow * p.Hq + h] = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
+      }
+    }
+    return;
+  }
+
   // ================================ consumers ================================
+  int mseq = 0;  // pieces handed to the merger warp so far
   const int lm = lane >> 3, lr = lane & 7;
   float* sm_m = reinterpret_cast<float*>(smem + S::kML);  // [4][16]
   float* sm_l = sm_m + 64;                                // [4][16]
@@ -626,52 +700,22 @@ __global__ void __launch_bounds__(kWsThreads, 2)
       }
     }
     if (!whole) {
-      // ---- arrival ticket; the last piece of the unit to arrive merges all of them -------------------------
-      const int c_first = chunk_of(us);
-      const int c_last = chunk_of(ue - 1);
-      __threadfence();
-      consumer_sync();
+      // ---- hand the piece to the merger warp: it takes the unit's arrival ticket and, if this was the last piece,
+      //      merges them - a fence, an atomic round trip and an L2 read that the streaming warps do not wait for ----
+      consumer_sync();  // every partial row of this piece has been written (by all four warps)
       if (tid == 0) {
-        int* cnt = p.ws_cnt + (int64_t)item * HG + hg;
-        const int ticket = atomicAdd(cnt, 1);
-        s_last = (ticket == c_last - c_first);
-        if (s_last) *cnt = 0;  // self-cleaning
+        const int ms = mseq % kWsMq;
+        if (mseq >= kWsMq) mbar_wait(bar(kWsMqEmpty + ms), ((mseq / kWsMq) + 1) & 1);
+        WsMerge& d = s_mq[ms];
+        d.unit = item * HG + hg;
+        d.qrow = qrow;
+        d.h0 = h0;
+        d.gcount = gcount;
+        d.c_first = chunk_of(us);
+        d.c_last = chunk_of(ue - 1);
+        mbar_arrive(bar(kWsMqFull + ms));
       }
-      consumer_sync();
-      if (s_last) {
-        __threadfence();
-        for (int e = tid; e < gcount * (D / 4); e += kWsConsumers) {
-          const int r = e / (D / 4), cc = (e - r * (D / 4)) * 4;
-          const int h = h0 + r;
-          float m = -INFINITY;
-          for (int pc = c_first; pc <= c_last; ++pc) {
-            const int64_t w = (int64_t)(pc * 2 + (pc == c_first ? 1 : 0)) * ws_rows + r;
-            m = fmaxf(m, __ldcg(p.ws_lse + w));
-          }
-          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-          float l = 0.f;
-          for (int pc = c_first; pc <= c_last; ++pc) {
-            const int64_t w = (int64_t)(pc * 2 + (pc == c_first ? 1 : 0)) * ws_rows + r;
-            const float ls = __ldcg(p.ws_lse + w);
-            const float f = (ls == -INFINITY) ? 0.f : fast_exp2(ls - m);
-            const float4 x = __ldcg(reinterpret_cast<const float4*>(p.ws_o + w * D + cc));
-            acc.x += f * x.x;
-            acc.y += f * x.y;
-            acc.z += f * x.z;
-            acc.w += f * x.w;
-            l += f;
-          }
-          if (p.sinks != nullptr && l > 0.f) l += fast_exp2(__ldg(p.sinks + h) * kLog2e - m);
-          const float inv = (l > 0.f) ? 1.f / l : 0.f;
-          T* dst = reinterpret_cast<T*>(p.o) + (int64_t)qrow * p.o_stride + (int64_t)h * D + cc;
-          uint2 pk;
-          pk.x = pack2<kBf16>(acc.x * inv, acc.y * inv);
-          pk.y = pack2<kBf16>(acc.z * inv, acc.w * inv);
-          *reinterpret_cast<uint2*>(dst) = pk;
-          if (WS_LSE_ON && cc == 0)
-            p.lse[(int64_t)qrow * p.Hq + h] = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
-        }
-      }
+      ++mseq;
     }
     consumer_sync();  // scratch (the stage), sm_m / sm_l and s_last are free again
     fence_proxy_async_smem();  // generic-proxy scratch writes before the copy engine refills the stage
@@ -683,6 +727,12 @@ __global__ void __launch_bounds__(kWsThreads, 2)
       ++item;
       it = ws_item(p, item);
     }
+  }
+  if (tid == 0) {  // tell the merger warp that no more pieces will come
+    const int ms = mseq % kWsMq;
+    if (mseq >= kWsMq) mbar_wait(bar(kWsMqEmpty + ms), ((mseq / kWsMq) + 1) & 1);
+    s_mq[ms].unit = -1;
+    mbar_arrive(bar(kWsMqFull + ms));
   }
   WS_STAMP(tid == 0, 6);
 }
