@@ -150,7 +150,7 @@ int b200attn_build_page_table(const int32_t* req_to_token, int64_t req_to_token_
  * replay needs no host-side recomputation.
  * `tail_begin` >= 0 restricts splitting to the units (request-major, then kv head
  * group) of rank >= tail_begin: the caller passes the number of units that fill whole
- * waves of resident CTAs (2 per SM), so that only the last, partial wave is split
+ * waves of resident CTAs (b200attn_decode_ctas_per_sm per SM), so that only the last, partial wave is split
  * `max_splits` ways and no SM idles for a whole unit (a function of B and the head
  * counts only => graph-safe).  -1: every unit uses the length-based policy.
  *
@@ -164,6 +164,10 @@ int b200attn_build_page_table(const int32_t* req_to_token, int64_t req_to_token_
  *                      denominator of q head h (attention sinks).
  * -------------------------------------------------------------------------- */
 int64_t b200attn_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t D, int32_t max_splits);
+
+/* Resident CTAs per SM of the kernel b200attn_decode (kv_fp8 = 0: four 64-thread CTAs with 32-key tiles) or
+ * b200attn_decode_fp8kv (kv_fp8 = 1) launches: the caller's split / tail-split wave arithmetic needs it. */
+int b200attn_decode_ctas_per_sm(int kv_fp8);
 
 int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
                     const void* v_cache, int64_t kv_stride, void* o, int64_t o_stride,

@@ -41,6 +41,7 @@ SIGNATURES = {
         [_vp, _i64, _vp, C.c_int, _vp, C.c_int, _i32, _i32, _vp, _i64, _i32, _vp],
     ),
     "b200attn_decode_workspace_bytes": (_i64, [_i32, _i32, _i32, _i32]),
+    "b200attn_decode_ctas_per_sm": (C.c_int, [C.c_int]),
     "b200attn_decode": (
         C.c_int,
         [_vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, C.c_int,

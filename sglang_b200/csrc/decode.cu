@@ -23,8 +23,15 @@
 
 namespace b200attn {
 
-template <int D, bool kBf16>
-__global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodeParams p) {
+// NW = warps per CTA (16 keys per warp and tile).  NW = 4: 64-key tiles, 3 x 32 KB ring, 2 CTAs per SM (the original
+// shape).  NW = 2: 64-thread CTAs, 32-key tiles, 3 x 16 KB ring, FOUR CTAs per SM: the same 128 KB of loads in
+// flight per SM, but 592 resident slots instead of 296 - cfg2's 512 units become ONE wave (no 73 %-full second
+// wave, every CTA streams at the same rate from start to end) and small batches can be split twice as finely
+// before a second wave forms.
+template <int D, bool kBf16, int NW>
+__global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const DecodeParams p) {
+  constexpr int kDecTile = 16 * NW;     // shadows the 4-warp constants of decode.cuh
+  constexpr int kDecThreads = 32 * NW;
   using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
   constexpr int kChunks = D / 8;                   // 16-byte chunks per row
   constexpr int kTileBytes = kDecTile * D * 2;     // one operand, one stage
@@ -212,9 +219,9 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodePara
     l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 1);
     l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
   }
-  float* sm_o = reinterpret_cast<float*>(smem);           // [4][16][D]
-  float* sm_m = sm_o + 4 * 16 * D;                        // [4][16]
-  float* sm_l = sm_m + 64;                                // [4][16]
+  float* sm_o = reinterpret_cast<float*>(smem);           // [NW][16][D]
+  float* sm_m = sm_o + NW * 16 * D;                       // [NW][16]
+  float* sm_l = sm_m + NW * 16;                           // [NW][16]
   {
     const int r0 = lane >> 2, c0 = (lane & 3) * 2;
 #pragma unroll
@@ -236,11 +243,11 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_kernel(const DecodePara
     const int r = e / (D / 4), c = (e - r * (D / 4)) * 4;
     float m = -INFINITY;
 #pragma unroll
-    for (int w = 0; w < 4; ++w) m = fmaxf(m, sm_m[w * 16 + r]);
+    for (int w = 0; w < NW; ++w) m = fmaxf(m, sm_m[w * 16 + r]);
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     float l = 0.f;
 #pragma unroll
-    for (int w = 0; w < 4; ++w) {
+    for (int w = 0; w < NW; ++w) {
       const float mw = sm_m[w * 16 + r];
       const float f = (mw == -INFINITY) ? 0.f : fast_exp2(mw - m);
       const float4 x = *reinterpret_cast<const float4*>(sm_o + (w * 16 + r) * D + c);
@@ -663,26 +670,46 @@ static int launch_decode_fp8(const DecodeParams& p, cudaStream_t st) {
   return B200ATTN_OK;
 }
 
-template <int D, bool kBf16>
-static int launch_decode(const DecodeParams& p, cudaStream_t st) {
-  constexpr int kRing = kDecStages * 2 * kDecTile * D * 2;
-  constexpr int kMerge = (4 * 16 * D + 128) * 4;
+template <int D, bool kBf16, int NW>
+static int launch_decode_nw(const DecodeParams& p, cudaStream_t st) {
+  constexpr int kRing = kDecStages * 2 * (16 * NW) * D * 2;
+  constexpr int kMerge = (NW * 16 * D + 2 * NW * 16) * 4;
   constexpr int kSmem = kRing > kMerge ? kRing : kMerge;
   static bool configured = false;  // idempotent attribute; races are benign
   if (!configured) {
-    B2_CUDA(cudaFuncSetAttribute(decode_kernel<D, kBf16>,
+    B2_CUDA(cudaFuncSetAttribute(decode_kernel<D, kBf16, NW>,
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-    B2_CUDA(cudaFuncSetAttribute(decode_kernel<D, kBf16>,
+    B2_CUDA(cudaFuncSetAttribute(decode_kernel<D, kBf16, NW>,
                                  cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     configured = true;
   }
   dim3 grid((unsigned)p.max_splits, (unsigned)(p.Hkv * p.groups_per_kvh), (unsigned)p.B);
-  decode_kernel<D, kBf16><<<grid, kDecThreads, kSmem, st>>>(p);
+  decode_kernel<D, kBf16, NW><<<grid, 32 * NW, kSmem, st>>>(p);
   B2_LAUNCH_CHECK();
   return B200ATTN_OK;
 }
 
+// warps per CTA of the 16-bit kernel: 2 (four 64-thread CTAs per SM) unless B200ATTN_DECODE_WARPS=4
+int decode_warps() {
+  static const int nw = [] {
+    const char* e = getenv("B200ATTN_DECODE_WARPS");
+    return (e != nullptr && atoi(e) == 4) ? 4 : 2;
+  }();
+  return nw;
+}
+
+template <int D, bool kBf16>
+static int launch_decode(const DecodeParams& p, cudaStream_t st) {
+  return decode_warps() == 2 ? launch_decode_nw<D, kBf16, 2>(p, st) : launch_decode_nw<D, kBf16, 4>(p, st);
+}
+
 }  // namespace b200attn
+
+// resident CTAs per SM of the kernel b200attn_decode / b200attn_decode_fp8kv will launch (the wave arithmetic of the
+// host-side split heuristics needs it)
+extern "C" int b200attn_decode_ctas_per_sm(int kv_fp8) {
+  return kv_fp8 ? B200ATTN_FP8_CTAS : (b200attn::decode_warps() == 2 ? 4 : 2);
+}
 
 extern "C" int64_t b200attn_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t D,
                                                    int32_t max_splits) {

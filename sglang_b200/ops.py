@@ -490,13 +490,14 @@ def decode_ws_workspace_bytes(Hq: int, Hkv: int, D: int) -> int:
 
 
 def decode_ctas_per_sm(fp8_kv: bool = False) -> int:
-    """Resident CTAs per SM of the decode kernels (their __launch_bounds__): 2 x 96 KB rings for 16-bit pools,
-    3 x 64 KB for e4m3 pools (csrc/decode.cu); the wave arithmetic of the two split heuristics below needs it."""
-    return 3 if fp8_kv else 2
+    """Resident CTAs per SM of the decode kernel that will run (its __launch_bounds__): 4 x 48 KB rings of 64-thread
+    CTAs for 16-bit pools, 3 x 64 KB for e4m3 pools (csrc/decode.cu); the wave arithmetic of the two split heuristics
+    below needs it."""
+    return int(_lib.load().b200attn_decode_ctas_per_sm(1 if fp8_kv else 0))
 
 
 def pick_max_splits(B: int, Hkv: int, G: int, max_kv_len: int, min_chunk: int = 256,
-                    ctas_per_sm: int = 2, num_sms: Optional[int] = None) -> int:
+                    ctas_per_sm: Optional[int] = None, num_sms: Optional[int] = None) -> int:
     """Host-side choice of the split cap.  The decode grid is (splits x kv-head groups x batch) CTAs over
     ``W = ctas_per_sm * num_sms`` resident slots.  Measured on B200 (tools/compare_small_decode.py, 8 kv heads,
     W = 296): the best cap is the LARGEST one that keeps every CTA in the first wave, ``floor(W / units)`` —
@@ -506,6 +507,8 @@ def pick_max_splits(B: int, Hkv: int, G: int, max_kv_len: int, min_chunk: int = 
     empty LAST wave is handled by pick_tail_split."""
     if num_sms is None:
         num_sms = sm_count()
+    if ctas_per_sm is None:
+        ctas_per_sm = decode_ctas_per_sm(False)
     groups = (G + 15) // 16
     items = max(1, B * Hkv * groups)
     slots = ctas_per_sm * num_sms
@@ -513,7 +516,7 @@ def pick_max_splits(B: int, Hkv: int, G: int, max_kv_len: int, min_chunk: int = 
     return int(max(1, min(cap, slots // items)))
 
 
-def pick_tail_split(B: int, Hkv: int, G: int, num_sms: Optional[int] = None, ctas_per_sm: int = 2,
+def pick_tail_split(B: int, Hkv: int, G: int, num_sms: Optional[int] = None, ctas_per_sm: Optional[int] = None,
                     max_k: int = 8) -> Tuple[int, int]:
     """Tail splitting for batches whose units do not fill whole waves of resident CTAs.
 
@@ -522,7 +525,7 @@ def pick_tail_split(B: int, Hkv: int, G: int, num_sms: Optional[int] = None, cta
     the split tail is one wave).  Measured on B200 (tools/decode_waves.py, ctx 4096): R/W = 0.08 -> 158.5 us ->
     117.0 us; R/W = 0.73 -> 171 us -> 177 us (the shorter CTAs and the merge launch cost more than the idle
     slots), hence the R <= W/2 gate.  Returns ``(tail_begin, k)``; ``(-1, 1)`` when nothing is gained."""
-    W = ctas_per_sm * (num_sms or sm_count())
+    W = (ctas_per_sm or decode_ctas_per_sm(False)) * (num_sms or sm_count())
     U = B * Hkv * (-(-G // 16))
     F, R = divmod(U, W)
     if F == 0 or R == 0 or 2 * R > W:
