@@ -328,7 +328,7 @@ def run_b200(args, rank, world, local_rank):
     backend.init_forward_metadata(fb)
     md = backend.forward_metadata
     kbuf, vbuf = kv_pool.get_kv_buffer(0)
-    max_splits = ops.pick_max_splits(B, Hkv, Hq // Hkv, c["ctx"], md.min_chunk)
+    warps, max_splits, tail_begin = ops.plan_decode(B, Hkv, Hq // Hkv, c["ctx"], md.min_chunk)
     launches_per_step = 2  # kv_store_kernel + decode_kernel (split partials are merged inside the decode kernel)
 
     # (1) the step: store + decode attention (+ in-kernel merge), inputs resident in HBM.  The layer-call is captured
@@ -373,7 +373,7 @@ def run_b200(args, rank, world, local_rank):
 
     def kern():
         ops.decode_attention(q3, kbuf, vbuf, o3, md.kv_indptr, md.kv_indices, layer.scaling, max_splits=max_splits,
-                             min_chunk=md.min_chunk, workspace=ws)
+                             min_chunk=md.min_chunk, workspace=ws, warps=warps, tail_begin=tail_begin)
 
     kern_ms = time_steps(kern, args.steps, args.warmup) / args.steps
     kern_bytes = nbytes - 2 * 2 * B * Hkv * D * 2  # without the store's read+write
@@ -564,6 +564,7 @@ def run_b200(args, rank, world, local_rank):
         config=dict(workload=WORKLOAD,
                     parallelism=f"kv-head sharded x{world} (8 kv heads per GPU), no collective",
                     l2="inputs larger than L2 (1.07 GB KV per call vs 126 MB)", max_splits=max_splits,
+                    decode_warps_per_cta=warps,
                     step_driver="one CUDA graph replay per step (store + decode captured once)"),
         eager_ms_per_step=eager_ms, output_check=head_check,
         roofline=dict(bound="hbm", achieved=achieved, peak=peaks["hbm"], unit="GB/s", frac=achieved / peaks["hbm"],
@@ -819,10 +820,10 @@ def run_cfg5_decode(dev, gen, peaks, world, steps=SIDE_STEPS, warmup=SIDE_WARMUP
     q = host["q"].to(dev).view(B, Hq, D)
     o = torch.empty_like(q)
     kbuf, vbuf = kv_pool.get_kv_buffer(0)
-    ms_ = ops.pick_max_splits(B, Hkv, Hq // Hkv, c["ctx"], 256)
+    warps, ms_, tb_ = ops.plan_decode(B, Hkv, Hq // Hkv, c["ctx"], 256)
     ws = torch.zeros(max(ops.decode_workspace_bytes(B, Hq, D, ms_), 16), dtype=torch.uint8, device=dev)
     f = lambda: ops.decode_attention(q, kbuf, vbuf, o, kv_indptr, kv_indices, D ** -0.5, max_splits=ms_,
-                                     min_chunk=256, workspace=ws)
+                                     min_chunk=256, workspace=ws, warps=warps, tail_begin=tb_)
     f()
     check = sampled_check(q, o, kbuf, vbuf, req_pool.req_to_token, list(range(1, B + 1)), [c["ctx"]] * B, [1] * B,
                           Hq, Hkv, D, causal=False)

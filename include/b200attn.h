@@ -153,6 +153,9 @@ int b200attn_build_page_table(const int32_t* req_to_token, int64_t req_to_token_
  * waves of resident CTAs (b200attn_decode_ctas_per_sm per SM), so that only the last, partial wave is split
  * `max_splits` ways and no SM idles for a whole unit (a function of B and the head
  * counts only => graph-safe).  -1: every unit uses the length-based policy.
+ * `warps` = 4 or 2 warps per CTA (16 keys per warp and tile): 4 streams fastest per CTA (steady state,
+ * small batches); 2 puts four CTAs on an SM, which turns a batch of 297..592 units (cfg2: 512) into ONE
+ * wave of equally fast CTAs instead of a full wave plus a partial one.
  *
  * Feature flags shared with b200attn_extend (triton_backend.py:1405-1416,
  * decode_attention.py:986-988, extend_attention.py:480-486,546-547,721-723):
@@ -165,16 +168,17 @@ int b200attn_build_page_table(const int32_t* req_to_token, int64_t req_to_token_
  * -------------------------------------------------------------------------- */
 int64_t b200attn_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t D, int32_t max_splits);
 
-/* Resident CTAs per SM of the kernel b200attn_decode (kv_fp8 = 0: four 64-thread CTAs with 32-key tiles) or
- * b200attn_decode_fp8kv (kv_fp8 = 1) launches: the caller's split / tail-split wave arithmetic needs it. */
-int b200attn_decode_ctas_per_sm(int kv_fp8);
+/* Resident CTAs per SM of the kernel b200attn_decode launches with `warps` warps per CTA (4: 64-key tiles, 2 CTAs
+ * per SM; 2: 64-thread CTAs with 32-key tiles, FOUR per SM = 592 resident slots on B200) or of
+ * b200attn_decode_fp8kv (kv_fp8 = 1): the caller's split / tail-split wave arithmetic needs it. */
+int b200attn_decode_ctas_per_sm(int kv_fp8, int warps);
 
 int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
                     const void* v_cache, int64_t kv_stride, void* o, int64_t o_stride,
                     float* lse, const int32_t* kv_indptr, const int32_t* kv_indices,
                     const int32_t* q_rows, const int32_t* req_ids, int32_t B,
                     int32_t Hq, int32_t Hkv, int32_t D, int dtype, float sm_scale,
-                    int32_t max_splits, int32_t min_chunk, int32_t tail_begin,
+                    int32_t max_splits, int32_t min_chunk, int32_t tail_begin, int32_t warps,
                     int32_t window_left, float logit_cap, const float* sinks, void* workspace,
                     int64_t workspace_bytes, void* stream);
 

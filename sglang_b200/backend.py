@@ -114,7 +114,7 @@ class B200AttnBackend(_Base):
         self.num_sms = ops.sm_count()
         # CUDA-graph state (init_cuda_graph_state)
         self._graph: Optional[SimpleNamespace] = None
-        self._graph_splits: Dict[int, int] = {}
+        self._graph_splits: Dict[object, object] = {}
         # eager-mode scratch that survives across forwards (grown on demand)
         self._ws: Optional[torch.Tensor] = None
         self._fp8_scratch: Optional[torch.Tensor] = None  # [2, n, Hkv, D] 16-bit K/V operands of extend over an fp8 pool
@@ -432,16 +432,39 @@ class B200AttnBackend(_Base):
         kbuf, vbuf = self.token_to_kv_pool.get_kv_buffer(layer.layer_id)
         B = md.batch_size
         G = Hq // Hkv
-        cps = ops.decode_ctas_per_sm(self._fp8_pool())  # resident CTAs per SM of the kernel that will run
-        if getattr(md, "_graph", False):
-            # the split cap is baked into the captured grid: fix it per batch size
-            ms = self._graph_splits.get(B)
-            if ms is None:
-                ms = min(self._graph.max_splits_cap,
-                         ops.pick_max_splits(B, Hkv, G, self.max_context_len, md.min_chunk, num_sms=self.num_sms, ctas_per_sm=cps))
-                self._graph_splits[B] = ms
+        fp8 = self._fp8_pool()
+        graph = getattr(md, "_graph", False)
+        warps, tail_begin = 4, -1
+        if fp8:
+            cps = ops.decode_ctas_per_sm(True)
+            if graph:  # the split cap is baked into the captured grid: fix it per batch size
+                ms = self._graph_splits.get(B)
+                if ms is None:
+                    ms = min(self._graph.max_splits_cap, ops.pick_max_splits(
+                        B, Hkv, G, self.max_context_len, md.min_chunk, num_sms=self.num_sms, ctas_per_sm=cps))
+                    self._graph_splits[B] = ms
+            else:
+                ms = ops.pick_max_splits(B, Hkv, G, getattr(md, "_max_kv_len", self.max_context_len), md.min_chunk,
+                                         num_sms=self.num_sms, ctas_per_sm=cps)
+            if ms == 1:  # whole waves stay unsplit; a nearly empty last wave is split (ops.pick_tail_split)
+                tail_begin, k = ops.pick_tail_split(B, Hkv, G, num_sms=self.num_sms, ctas_per_sm=cps)
+                ms, tail_begin = (k, tail_begin) if k > 1 else (1, -1)
+        else:
+            # 16-bit pools: (warps per CTA, split cap, tail split) from the batch shape (ops.plan_decode); under a
+            # graph the plan is a function of the bucket size only (kv lengths bounded by the context length)
+            key = ("plan", B, Hkv, G)
+            plan = self._graph_splits.get(key) if graph else None
+            if plan is None:
+                plan = ops.plan_decode(B, Hkv, G, self.max_context_len if graph else
+                                       getattr(md, "_max_kv_len", self.max_context_len), md.min_chunk,
+                                       num_sms=self.num_sms)
+                if graph:
+                    plan = (plan[0], min(plan[1], self._graph.max_splits_cap), plan[2])
+                    self._graph_splits[key] = plan
+            warps, ms, tail_begin = plan
+        need = ops.decode_workspace_bytes(B, Hq, D, ms)
+        if graph:
             ws = md.workspace
-            need = ops.decode_workspace_bytes(B, Hq, D, ms)
             if need > 0 and (ws is None or ws.numel() < need):
                 if torch.cuda.is_current_stream_capturing():
                     raise RuntimeError("b200 backend: pass num_q_heads/head_dim to init_cuda_graph_state")
@@ -450,26 +473,12 @@ class B200AttnBackend(_Base):
                     dtype=torch.uint8, device=self.device)
                 md.workspace = ws
         else:
-            ms = ops.pick_max_splits(B, Hkv, G, getattr(md, "_max_kv_len", self.max_context_len),
-                                     md.min_chunk, num_sms=self.num_sms, ctas_per_sm=cps)
-            ws = self._workspace(ops.decode_workspace_bytes(B, Hq, D, ms))
-        tail_begin = -1
-        if ms == 1:  # whole waves stay unsplit; a nearly empty last wave is split (ops.pick_tail_split)
-            tail_begin, k = ops.pick_tail_split(B, Hkv, G, num_sms=self.num_sms, ctas_per_sm=cps)
-            if k > 1:
-                need = ops.decode_workspace_bytes(B, Hq, D, k)
-                if getattr(md, "_graph", False):
-                    if ws is not None and ws.numel() >= need:
-                        ms = k
-                    else:
-                        tail_begin = -1
-                else:
-                    ms, ws = k, self._workspace(need)
+            ws = self._workspace(need)
         ops.decode_attention(q2.view(-1, Hq, D), kbuf, vbuf, o.view(-1, Hq, D), md.kv_indptr,
                              self._kv_indices(layer, md),
                              layer.scaling, max_splits=ms, min_chunk=md.min_chunk, workspace=ws, num_items=B,
-                             tail_begin=tail_begin, **self._features(layer, kwargs),
-                             **(self._descales(layer) if self._fp8_pool() else {}))
+                             tail_begin=tail_begin, warps=warps, **self._features(layer, kwargs),
+                             **(self._descales(layer) if fp8 else {}))
         return o
 
     def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, **kwargs):
@@ -536,8 +545,13 @@ class B200AttnBackend(_Base):
                                  skip_single_rows=md.num_dec > 0, **mask_kw, **self._features(layer, kwargs))
         if md.num_dec > 0:  # a single query row sees all of its keys, causal or not
             Hkv = layer.tp_k_head_num
-            ms = ops.pick_max_splits(md.num_dec, Hkv, Hq // Hkv, md.dec_max_kv_len, md.min_chunk,
-                                     num_sms=self.num_sms, ctas_per_sm=ops.decode_ctas_per_sm(fp8))
+            dwarps, dtail = 4, -1
+            if fp8:
+                ms = ops.pick_max_splits(md.num_dec, Hkv, Hq // Hkv, md.dec_max_kv_len, md.min_chunk,
+                                         num_sms=self.num_sms, ctas_per_sm=ops.decode_ctas_per_sm(True))
+            else:
+                dwarps, ms, dtail = ops.plan_decode(md.num_dec, Hkv, Hq // Hkv, md.dec_max_kv_len, md.min_chunk,
+                                                    num_sms=self.num_sms)
             need = ops.decode_workspace_bytes(md.num_dec, Hq, D, ms)
             with (torch.cuda.stream(self._side) if overlap else contextlib.nullcontext()):
                 if overlap:  # its own workspace: the extend kernel is using self._ws concurrently
@@ -550,7 +564,7 @@ class B200AttnBackend(_Base):
                                      self._kv_indices(layer, md),
                                      layer.scaling, max_splits=ms, min_chunk=md.min_chunk, workspace=ws,
                                      q_rows=md.dec_q_rows, req_ids=md.dec_req_ids, num_items=md.num_dec,
-                                     **self._features(layer, kwargs), **dsc)
+                                     warps=dwarps, tail_begin=dtail, **self._features(layer, kwargs), **dsc)
             if overlap:
                 cur.wait_stream(self._side)
         return o

@@ -689,26 +689,17 @@ static int launch_decode_nw(const DecodeParams& p, cudaStream_t st) {
   return B200ATTN_OK;
 }
 
-// warps per CTA of the 16-bit kernel: 2 (four 64-thread CTAs per SM) unless B200ATTN_DECODE_WARPS=4
-int decode_warps() {
-  static const int nw = [] {
-    const char* e = getenv("B200ATTN_DECODE_WARPS");
-    return (e != nullptr && atoi(e) == 4) ? 4 : 2;
-  }();
-  return nw;
-}
-
 template <int D, bool kBf16>
-static int launch_decode(const DecodeParams& p, cudaStream_t st) {
-  return decode_warps() == 2 ? launch_decode_nw<D, kBf16, 2>(p, st) : launch_decode_nw<D, kBf16, 4>(p, st);
+static int launch_decode(const DecodeParams& p, int warps, cudaStream_t st) {
+  return warps == 2 ? launch_decode_nw<D, kBf16, 2>(p, st) : launch_decode_nw<D, kBf16, 4>(p, st);
 }
 
 }  // namespace b200attn
 
 // resident CTAs per SM of the kernel b200attn_decode / b200attn_decode_fp8kv will launch (the wave arithmetic of the
 // host-side split heuristics needs it)
-extern "C" int b200attn_decode_ctas_per_sm(int kv_fp8) {
-  return kv_fp8 ? B200ATTN_FP8_CTAS : (b200attn::decode_warps() == 2 ? 4 : 2);
+extern "C" int b200attn_decode_ctas_per_sm(int kv_fp8, int warps) {
+  return kv_fp8 ? B200ATTN_FP8_CTAS : (warps == 2 ? 4 : 2);
 }
 
 extern "C" int64_t b200attn_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t D,
@@ -727,7 +718,7 @@ static int decode_impl(const void* q, int64_t q_stride, const void* k_cache,
                        int32_t window_left,
                        float logit_cap, const float* sinks, void* workspace,
                        int64_t workspace_bytes, void* stream, bool kv_fp8, float k_descale,
-                       float v_descale) {
+                       float v_descale, int32_t warps = 4) {
   using namespace b200attn;
   B2_CHECK_ARG(B >= 0, "decode: negative batch");
   B2_CHECK_ARG(logit_cap >= 0.f, "decode: negative logit_cap");
@@ -737,6 +728,7 @@ static int decode_impl(const void* q, int64_t q_stride, const void* k_cache,
                Hq, Hkv);
   B2_CHECK_ARG(B <= 65535 && Hq <= 65535, "decode: grid too large");
   B2_CHECK_ARG(max_splits >= 1 && max_splits <= 1024 && min_chunk >= 1, "decode: bad split policy");
+  B2_CHECK_ARG(warps == 2 || warps == 4, "decode: warps must be 2 or 4");
   B2_CHECK_ARG(q_stride % 8 == 0 && kv_stride % (kv_fp8 ? 16 : 8) == 0 && o_stride % 4 == 0,
                "decode: strides must keep rows 16-byte aligned");
   B2_CHECK_ARG(!kv_fp8 || (k_descale > 0.f && v_descale > 0.f), "decode: fp8 descales must be positive");
@@ -790,9 +782,9 @@ static int decode_impl(const void* q, int64_t q_stride, const void* k_cache,
     return dtype == B200ATTN_BF16 ? launch_decode_fp8<64, true>(p, st) : launch_decode_fp8<64, false>(p, st);
   }
   if (D == 128) {
-    return dtype == B200ATTN_BF16 ? launch_decode<128, true>(p, st) : launch_decode<128, false>(p, st);
+    return dtype == B200ATTN_BF16 ? launch_decode<128, true>(p, warps, st) : launch_decode<128, false>(p, warps, st);
   }
-  return dtype == B200ATTN_BF16 ? launch_decode<64, true>(p, st) : launch_decode<64, false>(p, st);
+  return dtype == B200ATTN_BF16 ? launch_decode<64, true>(p, warps, st) : launch_decode<64, false>(p, warps, st);
 }
 
 extern "C" int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
@@ -800,13 +792,13 @@ extern "C" int b200attn_decode(const void* q, int64_t q_stride, const void* k_ca
                                float* lse, const int32_t* kv_indptr, const int32_t* kv_indices,
                                const int32_t* q_rows, const int32_t* req_ids, int32_t B,
                                int32_t Hq, int32_t Hkv, int32_t D, int dtype, float sm_scale,
-                               int32_t max_splits, int32_t min_chunk, int32_t tail_begin,
+                               int32_t max_splits, int32_t min_chunk, int32_t tail_begin, int32_t warps,
                                int32_t window_left,
                                float logit_cap, const float* sinks, void* workspace,
                                int64_t workspace_bytes, void* stream) {
   return decode_impl(q, q_stride, k_cache, v_cache, kv_stride, o, o_stride, lse, kv_indptr, kv_indices,
                      q_rows, req_ids, B, Hq, Hkv, D, dtype, sm_scale, max_splits, min_chunk, tail_begin,
-                     window_left, logit_cap, sinks, workspace, workspace_bytes, stream, false, 1.f, 1.f);
+                     window_left, logit_cap, sinks, workspace, workspace_bytes, stream, false, 1.f, 1.f, warps);
 }
 
 extern "C" int b200attn_decode_fp8kv(const void* q, int64_t q_stride, const void* k_cache,

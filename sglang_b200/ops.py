@@ -489,15 +489,40 @@ def decode_ws_workspace_bytes(Hq: int, Hkv: int, D: int) -> int:
     return int(_lib.load().b200attn_decode_ws_workspace_bytes(Hq, Hkv, D))
 
 
-def decode_ctas_per_sm(fp8_kv: bool = False) -> int:
-    """Resident CTAs per SM of the decode kernel that will run (its __launch_bounds__): 4 x 48 KB rings of 64-thread
-    CTAs for 16-bit pools, 3 x 64 KB for e4m3 pools (csrc/decode.cu); the wave arithmetic of the two split heuristics
-    below needs it."""
-    return int(_lib.load().b200attn_decode_ctas_per_sm(1 if fp8_kv else 0))
+def decode_ctas_per_sm(fp8_kv: bool = False, warps: int = 4) -> int:
+    """Resident CTAs per SM of the decode kernel that will run (its __launch_bounds__): 2 x 96 KB rings (4 warps) or
+    4 x 48 KB rings of 64-thread CTAs (2 warps) for 16-bit pools, 3 x 64 KB for e4m3 pools (csrc/decode.cu); the wave
+    arithmetic of the split heuristics below needs it."""
+    return int(_lib.load().b200attn_decode_ctas_per_sm(1 if fp8_kv else 0, warps))
+
+
+def plan_decode(B: int, Hkv: int, G: int, max_kv_len: int, min_chunk: int = 256,
+                num_sms: Optional[int] = None) -> Tuple[int, int, int]:
+    """(warps, max_splits, tail_begin) of a 16-bit decode launch.  A pure function of the batch SHAPE (graph-safe).
+
+    Units = B * Hkv * ceil(G / 16) equal-priority CTAs.  Measured on B200 (profiles/r02_decode_warps.txt): a 4-warp
+    CTA streams twice as fast as a 2-warp one and the 4-warp grid is 3.5 % faster in steady state (cfg5: 1248 vs
+    1291 us), but only 2 fit on an SM; with 2 warps four do, and a batch of 297..592 units (cfg2: 512) runs as ONE
+    wave in which every CTA streams at the same rate to the end (171 -> 165 us) instead of a full wave plus a
+    partial one.  Everything else keeps 4 warps with the split cap / tail split of pick_max_splits / pick_tail_split."""
+    if num_sms is None:
+        num_sms = sm_count()
+    units = B * Hkv * (-(-G // 16))
+    if 2 * num_sms < units <= 4 * num_sms:
+        return 2, 1, -1
+    ms = pick_max_splits(B, Hkv, G, max_kv_len, min_chunk, ctas_per_sm=2, num_sms=num_sms)
+    tail_begin = -1
+    if ms == 1:
+        tail_begin, k = pick_tail_split(B, Hkv, G, num_sms=num_sms, ctas_per_sm=2)
+        if k > 1:
+            ms = k
+        else:
+            tail_begin = -1
+    return 4, ms, tail_begin
 
 
 def pick_max_splits(B: int, Hkv: int, G: int, max_kv_len: int, min_chunk: int = 256,
-                    ctas_per_sm: Optional[int] = None, num_sms: Optional[int] = None) -> int:
+                    ctas_per_sm: int = 2, num_sms: Optional[int] = None) -> int:
     """Host-side choice of the split cap.  The decode grid is (splits x kv-head groups x batch) CTAs over
     ``W = ctas_per_sm * num_sms`` resident slots.  Measured on B200 (tools/compare_small_decode.py, 8 kv heads,
     W = 296): the best cap is the LARGEST one that keeps every CTA in the first wave, ``floor(W / units)`` —
@@ -507,8 +532,6 @@ def pick_max_splits(B: int, Hkv: int, G: int, max_kv_len: int, min_chunk: int = 
     empty LAST wave is handled by pick_tail_split."""
     if num_sms is None:
         num_sms = sm_count()
-    if ctas_per_sm is None:
-        ctas_per_sm = decode_ctas_per_sm(False)
     groups = (G + 15) // 16
     items = max(1, B * Hkv * groups)
     slots = ctas_per_sm * num_sms
@@ -516,7 +539,7 @@ def pick_max_splits(B: int, Hkv: int, G: int, max_kv_len: int, min_chunk: int = 
     return int(max(1, min(cap, slots // items)))
 
 
-def pick_tail_split(B: int, Hkv: int, G: int, num_sms: Optional[int] = None, ctas_per_sm: Optional[int] = None,
+def pick_tail_split(B: int, Hkv: int, G: int, num_sms: Optional[int] = None, ctas_per_sm: int = 2,
                     max_k: int = 8) -> Tuple[int, int]:
     """Tail splitting for batches whose units do not fill whole waves of resident CTAs.
 
@@ -525,7 +548,7 @@ def pick_tail_split(B: int, Hkv: int, G: int, num_sms: Optional[int] = None, cta
     the split tail is one wave).  Measured on B200 (tools/decode_waves.py, ctx 4096): R/W = 0.08 -> 158.5 us ->
     117.0 us; R/W = 0.73 -> 171 us -> 177 us (the shorter CTAs and the merge launch cost more than the idle
     slots), hence the R <= W/2 gate.  Returns ``(tail_begin, k)``; ``(-1, 1)`` when nothing is gained."""
-    W = (ctas_per_sm or decode_ctas_per_sm(False)) * (num_sms or sm_count())
+    W = ctas_per_sm * (num_sms or sm_count())
     U = B * Hkv * (-(-G // 16))
     F, R = divmod(U, W)
     if F == 0 or R == 0 or 2 * R > W:
@@ -558,6 +581,7 @@ def decode_attention(
     v_descale: float = 1.0,
     stream_k: bool = False,
     ws_kernel: bool = False,
+    warps: int = 4,
     new_k: Optional[torch.Tensor] = None,
     new_v: Optional[torch.Tensor] = None,
     skip_slot: int = 0,
@@ -647,8 +671,8 @@ def decode_attention(
         q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
         o.data_ptr(), o.stride(0), _ptr(lse), kv_indptr.data_ptr(), kv_indices.data_ptr(),
         _ptr(q_rows), _ptr(req_ids), B, Hq, Hkv, D, _fdtype(q), float(sm_scale), max_splits,
-        min_chunk, int(tail_begin), int(window_left), float(logit_cap), _sinks_ptr(sinks, Hq), _ptr(workspace),
-        ws_bytes, _stream(),
+        min_chunk, int(tail_begin), int(warps), int(window_left), float(logit_cap), _sinks_ptr(sinks, Hq),
+        _ptr(workspace), ws_bytes, _stream(),
     )
     check(rc, "b200attn_decode")
     return o

@@ -32,11 +32,12 @@ def main():
         o, o2 = torch.empty_like(q), torch.empty_like(q)
         nbytes = B * ctx * Hkv * D * 4
         res = dict(B=B, ctx=ctx)
-        ms = ops.pick_max_splits(B, Hkv, Hq // Hkv, ctx, 256)
+        warps, ms, tb = ops.plan_decode(B, Hkv, Hq // Hkv, ctx, 256)
         ws = torch.zeros(max(ops.decode_workspace_bytes(B, Hq, D, ms), 16), dtype=torch.uint8, device=DEV)
         t = timed(lambda: ops.decode_attention(q, kc, vc, o, kv_indptr, kv_indices, D ** -0.5, max_splits=ms,
-                                               min_chunk=256, workspace=ws))
+                                               min_chunk=256, workspace=ws, warps=warps, tail_begin=tb))
         res["split_us"] = round(t * 1e3, 1)
+        res["plan"] = [warps, ms, tb]
         ws2 = torch.zeros(ops.decode_ws_workspace_bytes(Hq, Hkv, D), dtype=torch.uint8, device=DEV)
         for mc in (64, 256, 512):
             t = timed(lambda: ops.decode_attention(q, kc, vc, o2, kv_indptr, kv_indices, D ** -0.5, min_chunk=mc,
