@@ -500,15 +500,17 @@ def plan_decode(B: int, Hkv: int, G: int, max_kv_len: int, min_chunk: int = 256,
                 num_sms: Optional[int] = None) -> Tuple[int, int, int]:
     """(warps, max_splits, tail_begin) of a 16-bit decode launch.  A pure function of the batch SHAPE (graph-safe).
 
-    Units = B * Hkv * ceil(G / 16) equal-priority CTAs.  Measured on B200 (profiles/r02_decode_warps.txt): a 4-warp
+    Units = B * Hkv * ceil(G / 16) equal-priority CTAs.  Measured on B200 (profiles/r02_decode_warps.jsonl): a 4-warp
     CTA streams twice as fast as a 2-warp one and the 4-warp grid is 3.5 % faster in steady state (cfg5: 1248 vs
-    1291 us), but only 2 fit on an SM; with 2 warps four do, and a batch of 297..592 units (cfg2: 512) runs as ONE
-    wave in which every CTA streams at the same rate to the end (171 -> 165 us) instead of a full wave plus a
+    1291 us), but only 2 fit on an SM; with 2 warps four do, and a batch of ~415..592 units (cfg2: 512) runs as ONE
+    wave in which every CTA streams at the same rate to the end (170.5 -> 166.5 us) instead of a full wave plus a
     partial one.  Everything else keeps 4 warps with the split cap / tail split of pick_max_splits / pick_tail_split."""
     if num_sms is None:
         num_sms = sm_count()
     units = B * Hkv * (-(-G // 16))
-    if 2 * num_sms < units <= 4 * num_sms:
+    # measured crossover (tools/sweep_decode_warps.py, ctx 4096): 384 units 140.9 (2 warps) vs 130.1 us (4 warps +
+    # tail split), 448 units 152.5 vs 160.6, 512 units 166.5 vs 170.5, 592 units 187.0 vs 189.2
+    if 2.8 * num_sms < units <= 4 * num_sms:
         return 2, 1, -1
     ms = pick_max_splits(B, Hkv, G, max_kv_len, min_chunk, ctas_per_sm=2, num_sms=num_sms)
     tail_begin = -1
