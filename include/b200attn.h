@@ -349,6 +349,43 @@ int b200attn_extend(const void* q, int64_t q_stride, const void* k_cache,
                     void* stream);
 
 /* --------------------------------------------------------------------------
+ * (f3) Radix prefix match on the device.  Replaces, for the attention path, the lookup side of
+ *   python/sglang/srt/mem_cache/radix_cache.py: RadixCache.match_prefix (:377-423), insert (:425-445) and the
+ *   slot release of evict (:593-621; which leaves to evict stays the scheduler's LRU policy).
+ * The cache is a page trie in a caller-owned hash table (all device memory, zero-initialised once except
+ * `rev` = -1 and ctrs[0] = 1): entry e > 0 = one cached page; entry 0 = the root.
+ *   match : per request b, tokens[indptr[b] : indptr[b+1]) truncated to whole pages ->
+ *           out_indices[b * out_stride + i] (int64 KV slots of the longest cached prefix), out_len[b] tokens.
+ *           One warp per request, all pages of a request probed in parallel; bit-exact vs match_prefix.
+ *   insert: request after request; pages already cached keep their slots, the rest are appended with
+ *           values[indptr[b] + i]; out_prefix_len[b] = tokens that were already cached (InsertResult.prefix_len).
+ *           ctrs[3] becomes 1 when `cap` entries do not suffice.
+ *   erase_slots: KV slots handed back by the allocator (values of evicted leaves) -> their entries are unlinked.
+ * tokens / slots are int32 or int64 (`*_dtype`).
+ * -------------------------------------------------------------------------- */
+typedef struct {
+  int32_t* parent;    /* [cap]          parent entry (0 = root, -2 = dead)                      */
+  int32_t* tokens;    /* [cap * page]   token ids of the entry's page                            */
+  int64_t* values;    /* [cap * page]   KV slots of the entry's page                             */
+  uint64_t* ehash;    /* [cap]          hash of the token prefix that ends with this page        */
+  uint64_t* tkeys;    /* [tcap]         open addressing: 0 empty, 1 tombstone, else the hash     */
+  int32_t* tvals;     /* [tcap]         entry id                                                 */
+  int32_t* rev;       /* [num_pages]    KV page -> entry that holds it, -1 none                  */
+  int32_t* freelist;  /* [cap]          recycled entry ids                                       */
+  int32_t* ctrs;      /* [4]            next fresh id (init 1), free-list top, live entries, overflow flag */
+  int32_t cap, tcap, page, num_pages;
+} b200attn_radix_t;
+
+int b200attn_radix_match(const b200attn_radix_t* table, const void* tokens, int tokens_dtype,
+                         const int64_t* indptr, int32_t B, int64_t* out_indices, int64_t out_stride,
+                         int32_t* out_len, void* stream);
+int b200attn_radix_insert(const b200attn_radix_t* table, const void* tokens, int tokens_dtype,
+                          const int64_t* indptr, const int64_t* values, int32_t B,
+                          int32_t* out_prefix_len, void* stream);
+int b200attn_radix_erase_slots(const b200attn_radix_t* table, const void* slots, int slots_dtype,
+                               int64_t n, void* stream);
+
+/* --------------------------------------------------------------------------
  * (a6) merge_state.  Replaces merge_state / merge_state_v2
  *   python/sglang/srt/layers/attention/merge_state.py:26-46
  *   python/sglang/kernels/aot/csrc/attention/merge_attn_states.cu:31-206

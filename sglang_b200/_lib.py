@@ -15,11 +15,19 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200attn.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "b200attn.h")
 
-ABI_VERSION = 15  # b200attn_abi_version() of the library this binding matches (api.cu)
+ABI_VERSION = 16  # b200attn_abi_version() of the library this binding matches (api.cu)
 BF16, FP16, FP32 = 0, 1, 2
 I32, I64 = 0, 1
 
 _vp, _i32, _i64, _f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
+
+class RadixTable(C.Structure):
+    """b200attn_radix_t (include/b200attn.h): device pointers + sizes of the page-trie hash table."""
+
+    _fields_ = [("parent", _vp), ("tokens", _vp), ("values", _vp), ("ehash", _vp), ("tkeys", _vp), ("tvals", _vp),
+                ("rev", _vp), ("freelist", _vp), ("ctrs", _vp), ("cap", _i32), ("tcap", _i32), ("page", _i32),
+                ("num_pages", _i32)]
+
 
 # name -> (restype, argtypes); must match include/b200attn.h
 SIGNATURES = {
@@ -92,6 +100,9 @@ SIGNATURES = {
         C.c_int,
         [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, C.c_int, _vp],
     ),
+    "b200attn_radix_match": (C.c_int, [C.POINTER(RadixTable), _vp, C.c_int, _vp, _i32, _vp, _i64, _vp, _vp]),
+    "b200attn_radix_insert": (C.c_int, [C.POINTER(RadixTable), _vp, C.c_int, _vp, _vp, _i32, _vp, _vp]),
+    "b200attn_radix_erase_slots": (C.c_int, [C.POINTER(RadixTable), _vp, C.c_int, _i64, _vp]),
     "b200attn_alloc_extend": (
         C.c_int, [_vp, _vp, _vp, C.c_int, _vp, C.c_int, _i64, _vp, C.c_int, _i32, _i32, _vp, _vp],
     ),
