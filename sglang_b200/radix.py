@@ -36,7 +36,7 @@ def _flatten(keys: Sequence[torch.Tensor], device) -> Tuple[torch.Tensor, torch.
     indptr = torch.zeros(len(keys) + 1, dtype=torch.int64)
     if lens:
         indptr[1:] = torch.cumsum(torch.tensor(lens, dtype=torch.int64), 0)
-    flat = torch.cat([k.reshape(-1).to(torch.int64) for k in keys]) if lens else torch.zeros(0, dtype=torch.int64)
+    flat = torch.cat([k.reshape(-1).to(torch.int64) for k in keys] + [torch.zeros(1, dtype=torch.int64)])  # never empty
     return flat.to(device, non_blocking=True), indptr.to(device, non_blocking=True)
 
 
