@@ -600,18 +600,33 @@ def run_extend_leg(args, dev, gen, peaks):
 
     c = CFG3
     B, P, E, Hq, Hkv, D, page = c["B"], c["prefix"], c["ext"], c["Hq"], c["Hkv"], c["D"], c["page"]
+    # The batch's KV layout is produced the way production produces it: the shared prefix is a
+    # radix-cache HIT - one earlier request left its 2048 tokens in the (device-side) radix cache, every request of
+    # this batch matches them and so maps its first 128 logical pages to the SAME physical pages - and the new
+    # tokens' slots come from the paged allocator's alloc_extend (fragmented free list: shuffled page order).
+    from sglang_b200.allocator import PagedTokenToKVPoolAllocator
+    from sglang_b200.radix import DeviceRadixCache
+
     shared = P // page
     own = E // page
     num_pages = shared + B * own + 8
-    perm = torch.randperm(num_pages - 1, generator=gen) + 1
-    table = torch.zeros((B + 1, P + E), dtype=torch.int32)
-    offs = torch.arange(page)
-    pre = (perm[:shared, None] * page + offs[None]).reshape(-1)
-    for b in range(B):
-        mine = perm[shared + b * own: shared + (b + 1) * own]
-        table[b + 1, :P] = pre
-        table[b + 1, P:] = (mine[:, None] * page + offs[None]).reshape(-1)
-    table = table.to(dev)
+    alloc = PagedTokenToKVPoolAllocator(num_pages * page, page, dev)
+    alloc.free_pages = alloc.free_pages[torch.randperm(alloc.free_pages.numel(), generator=gen).to(dev)]
+    radix = DeviceRadixCache(page, max_cached_pages=num_pages, num_kv_pages=num_pages + 1, device=dev)
+    prefix_tokens = torch.randint(0, 128000, (P,), generator=gen)
+    prefix_slots = alloc.alloc(P)
+    assert radix.insert([prefix_tokens], [prefix_slots]) == [0]
+    keys = [torch.cat([prefix_tokens, torch.randint(0, 128000, (E,), generator=gen)]) for _ in range(B)]
+    hits = radix.match_prefix(keys)
+    assert all(h.numel() == P and torch.equal(h, prefix_slots) for h in hits), "radix match must return the shared prefix"
+    pre_cpu, seq_cpu = torch.full((B,), P, dtype=torch.int64), torch.full((B,), P + E, dtype=torch.int64)
+    last_loc = torch.stack([h[-1] for h in hits])
+    new_slots = alloc.alloc_extend(pre_cpu.to(dev), pre_cpu, seq_cpu.to(dev), seq_cpu, last_loc, B * E)
+    assert new_slots is not None and int(alloc.status) == 0
+    table = torch.zeros((B + 1, P + E), dtype=torch.int32, device=dev)
+    table[1:, :P] = torch.stack(hits).to(torch.int32)
+    table[1:, P:] = new_slots.view(B, E).to(torch.int32)
+    num_pages += 1  # slots of the pool: page 0 is the padding page
     kc = torch.randn((num_pages * page, Hkv, D), device=dev).to(torch.bfloat16)
     vc = torch.randn((num_pages * page, Hkv, D), device=dev).to(torch.bfloat16)
     T = B * E
@@ -619,7 +634,7 @@ def run_extend_leg(args, dev, gen, peaks):
     k = torch.randn((T, Hkv, D), device=dev).to(torch.bfloat16)
     v = torch.randn((T, Hkv, D), device=dev).to(torch.bfloat16)
     o = torch.empty_like(q)
-    loc = table[1:, P:].reshape(-1).long()
+    loc = new_slots
     req = torch.arange(1, B + 1, device=dev)
     seq = torch.full((B,), P + E, device=dev)
     extl = torch.full((B,), E, dtype=torch.int32, device=dev)
