@@ -48,7 +48,10 @@ constexpr int kExtC = 64;         // keys per softmax / MMA chunk (S/P double-bu
 constexpr int kExtStages = 2;     // K and V ring depth
 constexpr int kExtThreads = 384;  // 2 softmax warpgroups + {K producer, V producer, MMA, idle}
 constexpr int kExtBoxRows = 16;   // rows of one tiled K/V TMA box
-constexpr float kRescaleThreshold = 8.f;  // log2 domain
+#ifndef EXT_RESCALE_THRESHOLD
+#define EXT_RESCALE_THRESHOLD 8.f
+#endif
+constexpr float kRescaleThreshold = EXT_RESCALE_THRESHOLD;  // log2 domain
 constexpr int kRegsSoftmax = 208, kRegsOther = 80;
 constexpr int kExtMaxItems = 32;  // work items described per round
 constexpr int kExtOSlabCols = 32; // epilogue: O leaves through shared memory in 128 x 32 slabs (TMA store)
@@ -179,7 +182,13 @@ __device__ __forceinline__ float ex2_approx(float x) {
 // f in [-0.5, 0.5], degree-3 minimax polynomial for 2^f (max relative error 7.5e-5, far below the
 // bf16 rounding of P), then j is added into the exponent field.  x is clamped at -125 so that
 // masked (-inf) and far-below-max scores give ~1e-38 instead of wrapping the exponent.
-constexpr int kEmuPeriod = 5, kEmuCount = 2;  // pairs q with q % 5 < 2 are emulated (40 %)
+#ifndef EXT_EMU_PERIOD
+#define EXT_EMU_PERIOD 5
+#endif
+#ifndef EXT_EMU_COUNT
+#define EXT_EMU_COUNT 2
+#endif
+constexpr int kEmuPeriod = EXT_EMU_PERIOD, kEmuCount = EXT_EMU_COUNT;  // pairs q with q % 5 < 2 are emulated (40 %)
 __device__ __forceinline__ void exp2_emu2(float x0, float x1, float& p0, float& p1) {
   constexpr float kMagic = 12582912.f;  // 1.5 * 2^23: low mantissa bits of (x + kMagic) = round(x)
   x0 = fmaxf(x0, -125.f);
