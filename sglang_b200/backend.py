@@ -89,7 +89,12 @@ class B200AttnBackend(_Base):
     # decode kv splits never finer than this many keys
     MIN_CHUNK = 256
 
-    def __init__(self, model_runner, skip_padding_slot: bool = True, export_page_table: bool = False):
+    # deterministic (batch-invariant) mode: decode splits are fixed 256-key tiles, a function of the request's own
+    # length only (triton_backend.py:286-304,377-386: SGLANG_TRITON_DECODE_SPLIT_TILE_SIZE = 256)
+    DETERMINISTIC_SPLIT_TILE = 256
+
+    def __init__(self, model_runner, skip_padding_slot: bool = True, export_page_table: bool = False,
+                 deterministic: Optional[bool] = None):
         super().__init__()
         if not torch.cuda.is_available():
             raise AssertionError("B200AttnBackend needs a CUDA device (sm_100a); no CPU fallback")
@@ -110,6 +115,14 @@ class B200AttnBackend(_Base):
                             and hasattr(self.token_to_kv_pool, "full_to_swa_index_mapping"))
         self.skip_padding_slot = skip_padding_slot
         self.export_page_table = export_page_table
+        # --enable-deterministic-inference (server_args): outputs must not depend on what else is in the batch.  The
+        # extend kernel is batch-invariant by construction (one pass over a row's keys in order, per-row lazy
+        # rescale); decode becomes so by splitting every request into fixed 256-key tiles merged in index order,
+        # instead of a split cap chosen from the batch shape.
+        if deterministic is None:
+            deterministic = bool(getattr(getattr(model_runner, "server_args", None),
+                                         "enable_deterministic_inference", False))
+        self.deterministic = bool(deterministic)
         self.forward_metadata: Optional[ForwardMetadata] = None
         self.num_sms = ops.sm_count()
         # CUDA-graph state (init_cuda_graph_state)
@@ -203,6 +216,11 @@ class B200AttnBackend(_Base):
         if k.dtype != kbuf.dtype:  # memory_pool.py:2365-2371
             k, v = k.to(kbuf.dtype), v.to(vbuf.dtype)
         ops.store_cache(k, v, kbuf, vbuf, loc, reserved_skip_index=0 if self.skip_padding_slot else -1)
+
+    def _deterministic_splits(self) -> int:
+        """Split cap of the deterministic mode: with min_chunk = 256 the device-side policy then cuts a request of L
+        keys into ceil(L / 256) pieces whatever the batch (csrc/common.cuh split_policy)."""
+        return max(1, min(1024, -(-self.max_context_len // self.DETERMINISTIC_SPLIT_TILE)))
 
     def _is_swa_layer(self, layer) -> bool:
         return bool(self._hybrid_swa and self.token_to_kv_pool.layers_mapping[layer.layer_id][1])
@@ -332,6 +350,8 @@ class B200AttnBackend(_Base):
     def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int, *, num_q_heads: Optional[int] = None,
                               head_dim: Optional[int] = None, max_splits_cap: int = 16) -> None:
         dev = self.device
+        if self.deterministic:
+            max_splits_cap = max(max_splits_cap, self._deterministic_splits())
         g = SimpleNamespace()
         g.max_bs = max_bs
         g.kv_indptr = torch.zeros(max_bs + 1, dtype=torch.int32, device=dev)
@@ -435,7 +455,9 @@ class B200AttnBackend(_Base):
         fp8 = self._fp8_pool()
         graph = getattr(md, "_graph", False)
         warps, tail_begin = 4, -1
-        if fp8:
+        if self.deterministic:
+            ms = self._deterministic_splits()
+        elif fp8:
             cps = ops.decode_ctas_per_sm(True)
             if graph:  # the split cap is baked into the captured grid: fix it per batch size
                 ms = self._graph_splits.get(B)
@@ -546,7 +568,9 @@ class B200AttnBackend(_Base):
         if md.num_dec > 0:  # a single query row sees all of its keys, causal or not
             Hkv = layer.tp_k_head_num
             dwarps, dtail = 4, -1
-            if fp8:
+            if self.deterministic:
+                ms = self._deterministic_splits()
+            elif fp8:
                 ms = ops.pick_max_splits(md.num_dec, Hkv, Hq // Hkv, md.dec_max_kv_len, md.min_chunk,
                                          num_sms=self.num_sms, ctas_per_sm=ops.decode_ctas_per_sm(True))
             else:
