@@ -110,6 +110,13 @@ int b200attn_build_kv_indices(const int32_t* req_to_token, int64_t req_to_token_
 int b200attn_translate_slots(const void* loc, int loc_dtype, const void* slot_map,
                              int slot_map_dtype, int64_t n, int64_t* out, void* stream);
 
+/* One decode ITEM per query token of an extend batch: req_ids[t] = the request of token t, item_lens[t] = the
+ * number of leading keys it sees (causal: prefix + j + 1, else the request's full length; 0 for tokens past
+ * qo_indptr[B]).  Feeds b200attn_decode (`req_ids`, `item_lens`) for head dims the tcgen05 extend kernel does not
+ * take (torch_native_backend.py:61-174 semantics, one query row at a time). */
+int b200attn_build_token_items(const int32_t* qo_indptr, const int32_t* kv_indptr, int32_t B, int64_t T,
+                               int causal, int32_t* req_ids, int32_t* item_lens, void* stream);
+
 /* Page-table form.  Replaces build_trtllm_mha_page_table
  *   python/sglang/kernels/ops/kvcache/trtllm_mha_page_table.py:40-120
  *   page_table[b, j] = req_to_token[req_pool_indices[b], j*page_size] / page_size
@@ -153,6 +160,9 @@ int b200attn_build_page_table(const int32_t* req_to_token, int64_t req_to_token_
  * waves of resident CTAs (b200attn_decode_ctas_per_sm per SM), so that only the last, partial wave is split
  * `max_splits` ways and no SM idles for a whole unit (a function of B and the head
  * counts only => graph-safe).  -1: every unit uses the length-based policy.
+ * Head dims: any multiple of 8 up to 128 (rows are D wide; the kernel pads to 64 / 128 on the way into shared
+ * memory).  `item_lens` (nullable int32[B]): item r sees only the first item_lens[r] keys of its request
+ * (see b200attn_build_token_items).
  * `warps` = 4 or 2 warps per CTA (16 keys per warp and tile): 4 streams fastest per CTA (steady state,
  * small batches); 2 puts four CTAs on an SM, which turns a batch of 297..592 units (cfg2: 512) into ONE
  * wave of equally fast CTAs instead of a full wave plus a partial one.
@@ -179,8 +189,8 @@ int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
                     const int32_t* q_rows, const int32_t* req_ids, int32_t B,
                     int32_t Hq, int32_t Hkv, int32_t D, int dtype, float sm_scale,
                     int32_t max_splits, int32_t min_chunk, int32_t tail_begin, int32_t warps,
-                    int32_t window_left, float logit_cap, const float* sinks, void* workspace,
-                    int64_t workspace_bytes, void* stream);
+                    int32_t window_left, float logit_cap, const float* sinks,
+                    const int32_t* item_lens, void* workspace, int64_t workspace_bytes, void* stream);
 
 /* --------------------------------------------------------------------------
  * (a4) Decode, flat tile-stream scheduling.  Same contract and arithmetic as

@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200attn.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "b200attn.h")
 
-ABI_VERSION = 16  # b200attn_abi_version() of the library this binding matches (api.cu)
+ABI_VERSION = 17  # b200attn_abi_version() of the library this binding matches (api.cu)
 BF16, FP16, FP32 = 0, 1, 2
 I32, I64 = 0, 1
 
@@ -53,8 +53,9 @@ SIGNATURES = {
     "b200attn_decode": (
         C.c_int,
         [_vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, C.c_int,
-         _f32, _i32, _i32, _i32, _i32, _i32, _f32, _vp, _vp, _i64, _vp],
+         _f32, _i32, _i32, _i32, _i32, _i32, _f32, _vp, _vp, _vp, _i64, _vp],
     ),
+    "b200attn_build_token_items": (C.c_int, [_vp, _vp, _i32, _i64, C.c_int, _vp, _vp, _vp]),
     "b200attn_decode_sk_workspace_bytes": (_i64, [_i32, _i32, _i32, _i32]),
     "b200attn_decode_sk": (
         C.c_int,

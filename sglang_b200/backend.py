@@ -217,6 +217,33 @@ class B200AttnBackend(_Base):
             k, v = k.to(kbuf.dtype), v.to(vbuf.dtype)
         ops.store_cache(k, v, kbuf, vbuf, loc, reserved_skip_index=0 if self.skip_padding_slot else -1)
 
+    def _forward_extend_generic_head_dim(self, q2, o, layer, md, kbuf, vbuf, causal, fp8, kwargs):
+        """Head dims the tcgen05 extend kernel is not instantiated for (it takes 64 and 128; the reference's kernel
+        tests also sweep 96, 80, ... - test_triton_attention_kernels.py:169-322): every query TOKEN becomes one item
+        of the mma.sync decode kernel (any head dim that is a multiple of 8 up to 128) and sees its first
+        prefix + j + 1 keys (all keys when not causal).  Same semantics (torch_native_backend.py:61-174), HBM-bound
+        instead of tensor-core tiled: a compatibility path, not the fast one."""
+        if fp8 or md.custom_mask is not None:
+            raise NotImplementedError("b200 backend: head_dim not in (64, 128) with an fp8 pool / custom mask")
+        Hq, Hkv, D = layer.tp_q_head_num, layer.tp_k_head_num, layer.head_dim
+        T = q2.shape[0]
+        if T == 0:
+            return o
+        req_ids, item_lens = ops.build_token_items(md.qo_indptr, md.kv_indptr, md.batch_size, T, causal)
+        kv_idx = self._kv_indices(layer, md)
+        q3, o3 = q2.view(-1, Hq, D), o.view(-1, Hq, D)
+        step = 32768  # grid.z limit of the decode launch
+        for t0 in range(0, T, step):
+            n = min(step, T - t0)
+            warps, ms, tail = ops.plan_decode(n, Hkv, Hq // Hkv, self.max_context_len, md.min_chunk,
+                                              num_sms=self.num_sms)
+            ws = self._workspace(ops.decode_workspace_bytes(n, Hq, D, ms))
+            ops.decode_attention(q3[t0:t0 + n], kbuf, vbuf, o3[t0:t0 + n], md.kv_indptr, kv_idx, layer.scaling,
+                                 max_splits=ms, min_chunk=md.min_chunk, workspace=ws, num_items=n,
+                                 req_ids=req_ids[t0:t0 + n], item_lens=item_lens[t0:t0 + n], warps=warps,
+                                 tail_begin=tail, **self._features(layer, kwargs))
+        return o
+
     def _deterministic_splits(self) -> int:
         """Split cap of the deterministic mode: with min_chunk = 256 the device-side policy then cuts a request of L
         keys into ceil(L / 256) pieces whatever the batch (csrc/common.cuh split_policy)."""
@@ -523,6 +550,8 @@ class B200AttnBackend(_Base):
         B = md.batch_size
         fp8 = self._fp8_pool()
         dsc = self._descales(layer) if fp8 else {}
+        if D not in (64, 128):
+            return self._forward_extend_generic_head_dim(q2, o, layer, md, kbuf, vbuf, causal, fp8, kwargs)
         overlap = md.max_extend_len > 0 and md.num_dec > 0 and os.environ.get("B200ATTN_MIXED_OVERLAP", "1") != "0"
         if overlap:
             # fork AFTER the store and BEFORE the extend launch: the extend kernel's 148 persistent CTAs take the SMs

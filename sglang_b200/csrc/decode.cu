@@ -49,6 +49,8 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
   const int qrow = p.q_rows ? p.q_rows[item] : item;
   int kv_beg = p.kv_indptr[req];
   int L = p.kv_indptr[req + 1] - kv_beg;
+  if (p.item_lens != nullptr) L = min(L, max(0, p.item_lens[item]));
+  const int Dv = p.Dv;
   {
     const int lo = window_lo(L, p.window_left);  // sliding window: drop the keys before it
     kv_beg += lo;
@@ -68,7 +70,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
   // ---- Q fragments (A operand, 16 x D), rows >= gcount are zero -----------
   uint32_t qf[D / 16][4];
   {
-    const T* qbase = reinterpret_cast<const T*>(p.q) + (int64_t)qrow * p.q_stride + (int64_t)h0 * D;
+    const T* qbase = reinterpret_cast<const T*>(p.q) + (int64_t)qrow * p.q_stride + (int64_t)h0 * Dv;
     const int r0 = lane >> 2, c0 = (lane & 3) * 2;
 #pragma unroll
     for (int ks = 0; ks < D / 16; ++ks) {
@@ -76,7 +78,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
       for (int j = 0; j < 4; ++j) {
         const int r = r0 + (j & 1) * 8;
         const int c = ks * 16 + c0 + (j >> 1) * 8;
-        qf[ks][j] = (r < gcount) ? *reinterpret_cast<const uint32_t*>(qbase + (int64_t)r * D + c) : 0u;
+        qf[ks][j] = (r < gcount && c < Dv) ? *reinterpret_cast<const uint32_t*>(qbase + (int64_t)r * Dv + c) : 0u;
       }
     }
   }
@@ -84,8 +86,9 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
   // ---- producer state -------------------------------------------------------
   const int ld_chunk = tid % kChunks;
   const int ld_row0 = tid / kChunks;
-  const uint8_t* kc = reinterpret_cast<const uint8_t*>(p.k_cache) + (int64_t)kvh * D * 2 + ld_chunk * 16;
-  const uint8_t* vc = reinterpret_cast<const uint8_t*>(p.v_cache) + (int64_t)kvh * D * 2 + ld_chunk * 16;
+  const bool ld_col_ok = ld_chunk * 8 < Dv;  // chunks past the real head dim are zero-filled
+  const uint8_t* kc = reinterpret_cast<const uint8_t*>(p.k_cache) + (int64_t)kvh * Dv * 2 + (ld_col_ok ? ld_chunk * 16 : 0);
+  const uint8_t* vc = reinterpret_cast<const uint8_t*>(p.v_cache) + (int64_t)kvh * Dv * 2 + (ld_col_ok ? ld_chunk * 16 : 0);
   const int64_t row_bytes = p.kv_stride * 2;
   const int32_t* idx = p.kv_indices + kv_beg;
   const uint32_t smem_base = smem_u32(smem);
@@ -106,9 +109,9 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
     for (int i = 0; i < kLoadsPerThread; ++i) {
       const int row = ld_row0 + i * kRowsPerPass;
       const uint32_t off = swz_off<D>(row, ld_chunk);
-      const bool ok = slots[i] >= 0;
+      const bool ok = slots[i] >= 0 && ld_col_ok;
       const int64_t g = ok ? (int64_t)slots[i] * row_bytes : 0;
-      cp_async16(ks + off, kc + g, ok ? 16 : 0);  // invalid rows are zero-filled
+      cp_async16(ks + off, kc + g, ok ? 16 : 0);  // invalid rows / columns are zero-filled
       cp_async16(vs + off, vc + g, ok ? 16 : 0);
     }
   };
@@ -266,11 +269,11 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
     const float lse2 = (l > 0.f) ? m + log2f(l) : -INFINITY;
     const int h = h0 + r;
     if (direct) {
-      T* dst = reinterpret_cast<T*>(p.o) + (int64_t)qrow * p.o_stride + (int64_t)h * D + c;
+      T* dst = reinterpret_cast<T*>(p.o) + (int64_t)qrow * p.o_stride + (int64_t)h * Dv + c;
       uint2 pk;
       pk.x = pack2<kBf16>(acc.x, acc.y);
       pk.y = pack2<kBf16>(acc.z, acc.w);
-      *reinterpret_cast<uint2*>(dst) = pk;
+      if (c < Dv) *reinterpret_cast<uint2*>(dst) = pk;
       if (p.lse != nullptr && c == 0) p.lse[(int64_t)qrow * p.Hq + h] = lse2 * kLn2;
     } else {
       const int64_t w = ((int64_t)item * p.Hq + h) * p.max_splits + split;
@@ -314,11 +317,11 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
     }
     if (p.sinks != nullptr && l > 0.f) l += fast_exp2(__ldg(p.sinks + h) * kLog2e - m);
     const float inv = (l > 0.f) ? 1.f / l : 0.f;
-    T* dst = reinterpret_cast<T*>(p.o) + (int64_t)qrow * p.o_stride + (int64_t)h * D + c;
+    T* dst = reinterpret_cast<T*>(p.o) + (int64_t)qrow * p.o_stride + (int64_t)h * Dv + c;
     uint2 pk;
     pk.x = pack2<kBf16>(acc.x * inv, acc.y * inv);
     pk.y = pack2<kBf16>(acc.z * inv, acc.w * inv);
-    *reinterpret_cast<uint2*>(dst) = pk;
+    if (c < Dv) *reinterpret_cast<uint2*>(dst) = pk;
     if (p.lse != nullptr && c == 0)
       p.lse[(int64_t)qrow * p.Hq + h] = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
   }
@@ -705,6 +708,7 @@ extern "C" int b200attn_decode_ctas_per_sm(int kv_fp8, int warps) {
 extern "C" int64_t b200attn_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t D,
                                                    int32_t max_splits) {
   if (max_splits <= 1) return 0;
+  D = D <= 64 ? 64 : 128;  // the kernels run on the padded head dim
   // fixed-size counter header (kDecCounterBytes) + fp32 partials and their LSE
   return b200attn::kDecCounterBytes + (int64_t)B * Hq * max_splits * (D + 1) * 4;
 }
@@ -718,7 +722,7 @@ static int decode_impl(const void* q, int64_t q_stride, const void* k_cache,
                        int32_t window_left,
                        float logit_cap, const float* sinks, void* workspace,
                        int64_t workspace_bytes, void* stream, bool kv_fp8, float k_descale,
-                       float v_descale, int32_t warps = 4) {
+                       float v_descale, int32_t warps = 4, const int32_t* item_lens = nullptr) {
   using namespace b200attn;
   B2_CHECK_ARG(B >= 0, "decode: negative batch");
   B2_CHECK_ARG(logit_cap >= 0.f, "decode: negative logit_cap");
@@ -735,7 +739,12 @@ static int decode_impl(const void* q, int64_t q_stride, const void* k_cache,
   B2_CHECK_ARG((((uintptr_t)q | (uintptr_t)k_cache | (uintptr_t)v_cache | (uintptr_t)o) & 15) == 0,
                "decode: tensors must be 16-byte aligned");
   if (dtype != B200ATTN_BF16 && dtype != B200ATTN_FP16) B2_UNSUPPORTED("decode: dtype %d", dtype);
-  if (D != 64 && D != 128) B2_UNSUPPORTED("decode: head_dim %d (supported: 64, 128)", D);
+  // 16-bit pools: any head dim that is a multiple of 8 up to 128 runs on the padded 64 / 128 instantiation
+  const int Dv = D;
+  if (kv_fp8 ? (D != 64 && D != 128) : (D < 8 || D > 128 || D % 8 != 0))
+    B2_UNSUPPORTED("decode: head_dim %d (supported: multiples of 8 up to 128; e4m3 pools: 64, 128)", D);
+  B2_CHECK_ARG(!kv_fp8 || item_lens == nullptr, "decode: item_lens is not supported over e4m3 pools");
+  D = D <= 64 ? 64 : 128;
   const int64_t need = b200attn_decode_workspace_bytes(B, Hq, D, max_splits);
   B2_CHECK_ARG(need == 0 || (workspace && workspace_bytes >= need),
                "decode: workspace too small (%lld < %lld)", (long long)workspace_bytes,
@@ -774,6 +783,8 @@ static int decode_impl(const void* q, int64_t q_stride, const void* k_cache,
   p.cap_post = logit_cap > 0.f ? logit_cap * kLog2e : 0.f;
   p.sinks = sinks;
   p.tail_begin = max_splits > 1 ? tail_begin : -1;
+  p.Dv = Dv;
+  p.item_lens = item_lens;
   cudaStream_t st = (cudaStream_t)stream;
   if (kv_fp8) {
     if (D == 128) {
@@ -794,11 +805,12 @@ extern "C" int b200attn_decode(const void* q, int64_t q_stride, const void* k_ca
                                int32_t Hq, int32_t Hkv, int32_t D, int dtype, float sm_scale,
                                int32_t max_splits, int32_t min_chunk, int32_t tail_begin, int32_t warps,
                                int32_t window_left,
-                               float logit_cap, const float* sinks, void* workspace,
+                               float logit_cap, const float* sinks, const int32_t* item_lens, void* workspace,
                                int64_t workspace_bytes, void* stream) {
   return decode_impl(q, q_stride, k_cache, v_cache, kv_stride, o, o_stride, lse, kv_indptr, kv_indices,
                      q_rows, req_ids, B, Hq, Hkv, D, dtype, sm_scale, max_splits, min_chunk, tail_begin,
-                     window_left, logit_cap, sinks, workspace, workspace_bytes, stream, false, 1.f, 1.f, warps);
+                     window_left, logit_cap, sinks, workspace, workspace_bytes, stream, false, 1.f, 1.f, warps,
+                     item_lens);
 }
 
 extern "C" int b200attn_decode_fp8kv(const void* q, int64_t q_stride, const void* k_cache,

@@ -41,6 +41,13 @@ struct DecodeParams {
   // THOSE units are split `max_splits` ways.  tail_begin < 0: every unit uses the length-based policy.
   int tail_begin;
   float out_scale;  // fp8 KV only: v_descale * 2^8 applied to the normalised output (decode_fp8_kernel)
+  // 16-bit split kernel only.  Dv: the REAL head dim (multiple of 8, <= the kernel's padded template D): rows of q /
+  // k / v / o are Dv wide, columns >= Dv are zero-filled on the way into shared memory / registers and never
+  // stored (head dims 80, 96, ... run on the D = 128 instantiation, 16, 32, ... on D = 64).
+  int Dv;
+  // item_lens (nullable int32[B]): number of leading keys of request req_ids[item] that item sees, instead of all
+  // of them - one item per QUERY TOKEN of an extend batch (causal: prefix + j + 1), the generic-head-dim extend path
+  const int32_t* item_lens;
 };
 
 // split cap of one unit (shared by the attention and the merge kernel)

@@ -199,7 +199,42 @@ __global__ void __launch_bounds__(256)
   page_table[b * pt_stride + j] = slot / page_size;
 }
 
+// one item per QUERY TOKEN of an extend batch (the generic-head-dim extend path runs them through the decode
+// kernel): the request the token belongs to and the number of leading keys it sees
+__global__ void __launch_bounds__(256)
+    token_items_kernel(const int32_t* __restrict__ qo_indptr, const int32_t* __restrict__ kv_indptr, int B, int64_t T,
+                       int causal, int32_t* __restrict__ req_ids, int32_t* __restrict__ item_lens) {
+  const int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (t >= T) return;
+  if (t >= qo_indptr[B]) {  // padded token of a static buffer
+    req_ids[t] = 0;
+    item_lens[t] = 0;
+    return;
+  }
+  int lo = 0, hi = B;  // largest b with qo_indptr[b] <= t
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (qo_indptr[mid] <= t) lo = mid; else hi = mid;
+  }
+  const int q0 = qo_indptr[lo], E = qo_indptr[lo + 1] - q0;
+  const int L = kv_indptr[lo + 1] - kv_indptr[lo];
+  req_ids[t] = lo;
+  item_lens[t] = causal ? L - E + (int)(t - q0) + 1 : L;
+}
+
 }  // namespace b200attn
+
+extern "C" int b200attn_build_token_items(const int32_t* qo_indptr, const int32_t* kv_indptr, int32_t B, int64_t T,
+                                          int causal, int32_t* req_ids, int32_t* item_lens, void* stream) {
+  using namespace b200attn;
+  B2_CHECK_ARG(B >= 0 && T >= 0, "build_token_items: negative size");
+  if (T == 0 || B == 0) return B200ATTN_OK;
+  B2_CHECK_ARG(qo_indptr && kv_indptr && req_ids && item_lens, "build_token_items: null pointer");
+  token_items_kernel<<<(unsigned)((T + 255) / 256), 256, 0, (cudaStream_t)stream>>>(qo_indptr, kv_indptr, B, T,
+                                                                                    causal, req_ids, item_lens);
+  B2_LAUNCH_CHECK();
+  return B200ATTN_OK;
+}
 
 extern "C" int b200attn_build_kv_indices(
     const int32_t* req_to_token, int64_t req_to_token_stride, const void* req_pool_indices,

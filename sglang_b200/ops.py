@@ -476,6 +476,22 @@ def build_page_table(
     check(rc, "b200attn_build_page_table")
 
 
+def build_token_items(qo_indptr: torch.Tensor, kv_indptr: torch.Tensor, B: int, T: int, causal: bool,
+                      req_ids: Optional[torch.Tensor] = None, item_lens: Optional[torch.Tensor] = None
+                      ) -> Tuple[torch.Tensor, torch.Tensor]:
+    """One decode item per query token of an extend batch (b200attn_build_token_items): ``(req_ids, item_lens)``
+    int32 [T] for ``decode_attention(..., req_ids=, item_lens=)`` - the generic-head-dim extend path."""
+    _require_cuda(qo_indptr, kv_indptr, req_ids, item_lens)
+    if req_ids is None:
+        req_ids = torch.empty(max(T, 1), dtype=torch.int32, device=qo_indptr.device)
+    if item_lens is None:
+        item_lens = torch.empty(max(T, 1), dtype=torch.int32, device=qo_indptr.device)
+    rc = _lib.load().b200attn_build_token_items(qo_indptr.data_ptr(), kv_indptr.data_ptr(), B, T, int(bool(causal)),
+                                                req_ids.data_ptr(), item_lens.data_ptr(), _stream())
+    check(rc, "b200attn_build_token_items")
+    return req_ids, item_lens
+
+
 # -------------------------------------------------------------------------- decode
 def decode_workspace_bytes(B: int, Hq: int, D: int, max_splits: int) -> int:
     return _lib.load().b200attn_decode_workspace_bytes(B, Hq, D, max_splits)
@@ -584,6 +600,7 @@ def decode_attention(
     stream_k: bool = False,
     ws_kernel: bool = False,
     warps: int = 4,
+    item_lens: Optional[torch.Tensor] = None,
     new_k: Optional[torch.Tensor] = None,
     new_v: Optional[torch.Tensor] = None,
     skip_slot: int = 0,
@@ -674,7 +691,7 @@ def decode_attention(
         o.data_ptr(), o.stride(0), _ptr(lse), kv_indptr.data_ptr(), kv_indices.data_ptr(),
         _ptr(q_rows), _ptr(req_ids), B, Hq, Hkv, D, _fdtype(q), float(sm_scale), max_splits,
         min_chunk, int(tail_begin), int(warps), int(window_left), float(logit_cap), _sinks_ptr(sinks, Hq),
-        _ptr(workspace), ws_bytes, _stream(),
+        _ptr(item_lens), _ptr(workspace), ws_bytes, _stream(),
     )
     check(rc, "b200attn_decode")
     return o
