@@ -14,4 +14,6 @@ timeout 600 ncu --set full --clock-control none --import-source on -k regex:deco
     -f -o $OUT/${TAG}_decode_full $CMD > $OUT/${TAG}_ncu_decode.log 2>&1
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:extend_kernel -s 4 -c 2 \
     -f -o $OUT/${TAG}_extend_full $CMD > $OUT/${TAG}_ncu_extend.log 2>&1
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:extend_kernel -s 2 -c 1 \
+    -f -o $OUT/${TAG}_extend_cfg4_full python tools/prof_cfg4.py > $OUT/${TAG}_ncu_extend_cfg4.log 2>&1
 ls -la $OUT | tail -12
