@@ -36,8 +36,9 @@ def _flatten(keys: Sequence[torch.Tensor], device) -> Tuple[torch.Tensor, torch.
     indptr = torch.zeros(len(keys) + 1, dtype=torch.int64)
     if lens:
         indptr[1:] = torch.cumsum(torch.tensor(lens, dtype=torch.int64), 0)
-    flat = torch.cat([k.reshape(-1).to(torch.int64) for k in keys] + [torch.zeros(1, dtype=torch.int64)])  # never empty
-    return flat.to(device, non_blocking=True), indptr.to(device, non_blocking=True)
+    parts = [k.reshape(-1).to(device=device, dtype=torch.int64, non_blocking=True) for k in keys]
+    flat = torch.cat(parts + [torch.zeros(1, dtype=torch.int64, device=device)])  # never empty
+    return flat, indptr.to(device, non_blocking=True)
 
 
 class DeviceRadixCache:
