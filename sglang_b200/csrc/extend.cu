@@ -331,20 +331,17 @@ __global__ void __launch_bounds__(kExtThreads, 1)
   // (cfg4, G = 7, causal: per-CTA max/mean work 1.27 -> 1.03).  rank_cnt[r] = Hkv * #{requests with > r pairs}.
   const bool ranked = p.rank_cum != nullptr;
   if (ranked) {
-    // every CTA writes the SAME values; counts and prefix sums live in separate halves so that a CTA still counting
-    // never overwrites a prefix sum another CTA is already reading
-    int32_t* rank_cnt = p.rank_cum + p.max_rank + 2;
     for (int r = threadIdx.x; r < p.max_rank; r += kExtThreads) {
       int c = 0;
       for (int b = 0; b < p.B; ++b) c += (cum[b + 1] - cum[b] > r) ? 1 : 0;
-      rank_cnt[r] = c * p.Hkv;
+      p.rank_cum[r + 1] = c * p.Hkv;
     }
     if (threadIdx.x == 0) p.rank_cum[0] = 0;
     __syncthreads();
-    if (warp == 0) {  // inclusive scan of the counts into rank_cum[1 ..]
+    if (warp == 0) {  // inclusive scan of rank_cum[1 ..] in place
       int carry = 0;
       for (int base = 0; base < p.max_rank; base += 32) {
-        int v = (base + lane < p.max_rank) ? rank_cnt[base + lane] : 0;
+        int v = (base + lane < p.max_rank) ? p.rank_cum[base + lane + 1] : 0;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
           const int u = __shfl_up_sync(0xffffffffu, v, o);
@@ -968,7 +965,7 @@ static int launch_extend(const CUtensorMap& tq, const CUtensorMap& tk, const CUt
 extern "C" int64_t b200attn_extend_workspace_bytes(int32_t B, int64_t total_q, int32_t Hq) {
   if (B <= 0 || total_q <= 0 || Hq <= 0) return 0;
   const int64_t max_qtiles = (total_q + b200attn::kExtM - 1) / b200attn::kExtM;
-  return ((max_qtiles * Hq + 1) / 2 + 2) * 2 * 4;  // prefix sums + counts
+  return ((max_qtiles * Hq + 1) / 2 + 2) * 4;
 }
 
 extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_cache,
@@ -1050,7 +1047,7 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
   p.max_rank = (max_qtiles * p.G + 1) / 2;
   p.rank_cum = nullptr;
 #ifndef EXT_TRACE
-  if (workspace != nullptr && workspace_bytes >= (int64_t)(p.max_rank + 2) * 2 * 4 && B <= ExtSmem<128>::kMaxB)
+  if (workspace != nullptr && workspace_bytes >= (int64_t)(p.max_rank + 2) * 4 && B <= ExtSmem<128>::kMaxB)
     p.rank_cum = reinterpret_cast<int32_t*>(workspace);
 #endif
   cudaStream_t st = (cudaStream_t)stream;
