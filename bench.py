@@ -643,16 +643,14 @@ def run_extend_leg(args, dev, gen, peaks):
     kv_indices = torch.zeros(B * (P + E), dtype=torch.int32, device=dev)
     ops.build_kv_indices(table, req, seq, kv_indptr, kv_indices, qo_lens=extl, qo_indptr=qo_indptr)
 
-    ews = torch.empty(max(ops.extend_workspace_bytes(B, T, Hq), 16), dtype=torch.uint8, device=dev)
-
     def step():
         ops.store_cache(k, v, kc, vc, loc, reserved_skip_index=0)
         ops.extend_attention(q, kc, vc, o, qo_indptr, kv_indptr, kv_indices, D ** -0.5, causal=True,
-                             page_size=page, max_qo_len=E, workspace=ews)
+                             page_size=page, max_qo_len=E)
 
     def kern():
         ops.extend_attention(q, kc, vc, o, qo_indptr, kv_indptr, kv_indices, D ** -0.5, causal=True,
-                             page_size=page, max_qo_len=E, workspace=ews)
+                             page_size=page, max_qo_len=E)
 
     steps = max(args.steps, SIDE_STEPS)
     ms = time_steps(step, steps, max(args.warmup, SIDE_WARMUP)) / steps

@@ -136,7 +136,6 @@ class B200AttnBackend(_Base):
         # MIXED batches: the decode rows run on a side stream so that they fill the tail of the persistent extend kernel
         self._side: Optional[torch.cuda.Stream] = None
         self._ws_dec: Optional[torch.Tensor] = None
-        self._ws_ext: Optional[torch.Tensor] = None  # extend kernel: rank table of the heavy-first item order
 
     # ------------------------------------------------------------------ helpers
     def support_triton(self) -> bool:  # base_attn_backend.py:298
@@ -562,13 +561,7 @@ class B200AttnBackend(_Base):
                 self._side = torch.cuda.Stream()
             self._side.wait_stream(cur)
         if md.max_extend_len > 0:
-            # its own buffer: the decode workspace starts with zero-initialised arrival counters
-            need_ext = ops.extend_workspace_bytes(B, q2.shape[0], Hq)
-            if self._ws_ext is None or self._ws_ext.numel() < need_ext:
-                if torch.cuda.is_current_stream_capturing():
-                    raise RuntimeError("b200 backend: run one eager extend before capturing (workspace)")
-                self._ws_ext = torch.empty(max(need_ext, 16), dtype=torch.uint8, device=self.device)
-            ws = self._ws_ext
+            ws = self._workspace(ops.extend_workspace_bytes(B, q2.shape[0], Hq))
             kv_idx = self._kv_indices(layer, md)
             ek, ev, eidx, escale = kbuf, vbuf, kv_idx, layer.scaling
             if fp8:

@@ -78,11 +78,6 @@ struct ExtendParams {
   const uint8_t* custom_mask;
   const int32_t* mask_indptr;
   int mask_skip_prefix;
-  // Global heavy-first item order (workspace, nullable): rank_cum[r] = items of rank < r, where the rank of an item
-  // is its distance from the heaviest (last) tile pair of its (request, kv head).  int32 [max_rank + 2], written
-  // identically by every CTA in its prologue.  Null: the per-unit order of round 1.
-  int32_t* rank_cum;
-  int max_rank;
 #ifdef EXT_TRACE
   long long* trace;  // dev-only timeline of CTA (0,0,0): [role 0..2][step 0..31][8]
 #endif
@@ -326,33 +321,6 @@ __global__ void __launch_bounds__(kExtThreads, 1)
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const int total_items = cum[p.B] * p.Hkv;
-  // ---- rank table: items are dealt in GLOBAL heavy-first order - all units' heaviest pairs, then all second
-  // heaviest, ... - so that the boustrophedon deal below is an LPT over the whole list and not just within a unit
-  // (cfg4, G = 7, causal: per-CTA max/mean work 1.27 -> 1.03).  rank_cnt[r] = Hkv * #{requests with > r pairs}.
-  const bool ranked = p.rank_cum != nullptr;
-  if (ranked) {
-    for (int r = threadIdx.x; r < p.max_rank; r += kExtThreads) {
-      int c = 0;
-      for (int b = 0; b < p.B; ++b) c += (cum[b + 1] - cum[b] > r) ? 1 : 0;
-      p.rank_cum[r + 1] = c * p.Hkv;
-    }
-    if (threadIdx.x == 0) p.rank_cum[0] = 0;
-    __syncthreads();
-    if (warp == 0) {  // inclusive scan of rank_cum[1 ..] in place
-      int carry = 0;
-      for (int base = 0; base < p.max_rank; base += 32) {
-        int v = (base + lane < p.max_rank) ? p.rank_cum[base + lane + 1] : 0;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const int u = __shfl_up_sync(0xffffffffu, v, o);
-          if (lane >= o) v += u;
-        }
-        if (base + lane < p.max_rank) p.rank_cum[base + lane + 1] = v + carry;
-        carry += __shfl_sync(0xffffffffu, v, 31);
-      }
-    }
-    __syncthreads();
-  }
   // Boustrophedon assignment: round k hands item k*G + x to CTA x when k is even and to CTA G-1-x when k is odd.
   // Items are ordered heavy-first within a (request, kv head), so a CTA that drew a heavy item in one round draws a
   // light one in the next (static LPT): 8.2 K + 8.2 K chunked prefill on one kv head, 256 items on 148 CTAs:
@@ -566,39 +534,14 @@ __global__ void __launch_bounds__(kExtThreads, 1)
       if ((int)threadIdx.x < n_round) {
         const int rk = r0 + (int)threadIdx.x;  // round index of this item
         const int id = rk * (int)gridDim.x + ((rk & 1) ? (int)gridDim.x - 1 - (int)blockIdx.x : (int)blockIdx.x);
-        int b, np, rem;
-        if (ranked) {
-          int lo = 0, hi = p.max_rank;  // largest r with rank_cum[r] <= id
-          while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (p.rank_cum[mid] <= id) lo = mid; else hi = mid;
-          }
-          const int r = lo;
-          const int within = id - p.rank_cum[r];
-          const int u = within / p.Hkv;  // the u-th request that has more than r pairs
-          int seen = 0;
-          b = 0;
-          for (int bb = 0; bb < p.B; ++bb) {
-            if (cum[bb + 1] - cum[bb] > r) {
-              if (seen == u) {
-                b = bb;
-                break;
-              }
-              ++seen;
-            }
-          }
-          np = cum[b + 1] - cum[b];
-          rem = (within - u * p.Hkv) * np + r;  // kvh = rem / np, pair = np - 1 - r (heaviest first)
-        } else {
-          int lo = 0, hi = p.B;  // largest b with cum[b] * Hkv <= id
-          while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (cum[mid] * p.Hkv <= id) lo = mid; else hi = mid;
-          }
-          b = lo;
-          np = cum[b + 1] - cum[b];
-          rem = id - cum[b] * p.Hkv;
+        int lo = 0, hi = p.B;  // largest b with cum[b] * Hkv <= id
+        while (hi - lo > 1) {
+          const int mid = (lo + hi) >> 1;
+          if (cum[mid] * p.Hkv <= id) lo = mid; else hi = mid;
         }
+        const int b = lo;
+        const int np = cum[b + 1] - cum[b];
+        const int rem = id - cum[b] * p.Hkv;
         ItemDesc d;
         d.q_beg = p.qo_indptr[b];
         d.E = p.qo_indptr[b + 1] - d.q_beg;
@@ -960,13 +903,7 @@ static int launch_extend(const CUtensorMap& tq, const CUtensorMap& tk, const CUt
 
 }  // namespace b200attn
 
-// workspace = the rank table of the global heavy-first item order: int32 [max tile pairs of a (request, kv head) + 2],
-// bounded through the longest request a launch can see (total_q rows, at most Hq heads per kv head)
-extern "C" int64_t b200attn_extend_workspace_bytes(int32_t B, int64_t total_q, int32_t Hq) {
-  if (B <= 0 || total_q <= 0 || Hq <= 0) return 0;
-  const int64_t max_qtiles = (total_q + b200attn::kExtM - 1) / b200attn::kExtM;
-  return ((max_qtiles * Hq + 1) / 2 + 2) * 4;
-}
+extern "C" int64_t b200attn_extend_workspace_bytes(int32_t, int64_t, int32_t) { return 0; }
 
 extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_cache,
                                const void* v_cache, int64_t kv_stride, int64_t num_slots, void* o,
@@ -980,7 +917,10 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
                                int64_t workspace_bytes, void* stream) {
   using namespace b200attn;
   B2_CHECK_ARG(logit_cap >= 0.f, "extend: negative logit_cap");
-
+#ifndef EXT_TRACE
+  (void)workspace;
+  (void)workspace_bytes;
+#endif
   (void)page_size;  // rows are gathered token-granular: any page size, no contiguity assumption
   B2_CHECK_ARG(B >= 0 && total_q_host >= 0 && max_qo_len_host >= 0, "extend: negative size");
   if (B == 0 || total_q_host == 0 || max_qo_len_host == 0) return B200ATTN_OK;
@@ -1044,12 +984,6 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
   p.trace = workspace_bytes >= 6 * 32 * 8 * 8 ? (long long*)workspace : nullptr;
 #endif
   const int max_qtiles = (max_qo_len_host + kExtM - 1) / kExtM;
-  p.max_rank = (max_qtiles * p.G + 1) / 2;
-  p.rank_cum = nullptr;
-#ifndef EXT_TRACE
-  if (workspace != nullptr && workspace_bytes >= (int64_t)(p.max_rank + 2) * 4 && B <= ExtSmem<128>::kMaxB)
-    p.rank_cum = reinterpret_cast<int32_t*>(workspace);
-#endif
   cudaStream_t st = (cudaStream_t)stream;
   if (D == 128)
     return dtype == B200ATTN_BF16 ? launch_extend<128, true>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st)
