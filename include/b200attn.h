@@ -331,9 +331,12 @@ int b200attn_kv_dequant_gather_unique(const void* k_cache, const void* v_cache, 
  * caller sends through b200attn_decode (q_rows / req_ids) instead.
  *
  * The QK^T and PV contractions run on tcgen05 tensor cores with TMEM
- * accumulators; `page_size` > 1 promises the paged-allocator invariant
- * (python/sglang/srt/mem_cache/allocator/paged.py:163-166: a logical page lies
- * in one physical page) and enables TMA page boxes; page_size == 1 gathers rows.
+ * accumulators; K/V tiles are fetched by TMA.  `page_size` is accepted for interface
+ * parity and IGNORED: the kernel gathers token-granular slots and discovers per tile
+ * whether every aligned 16-key group sits in 16 consecutive pool slots (true under the
+ * paged allocator for page_size >= 16, paged.py:163-166) -> 16-row tiled TMA boxes;
+ * otherwise (page_size 1, fragmented or ragged tiles) tile::gather4 rows.
+ * `workspace` is unused (b200attn_extend_workspace_bytes returns 0; kept for ABI symmetry).
  * `lse` nullable float[T*Hq] natural log.  `max_qo_len_host` / `total_q_host`
  * are host-side upper bounds used only to size the grid (graph-safe).
  * `custom_mask` (nullable uint8, nonzero = visible) with `mask_indptr` int32[B+1]:
