@@ -18,10 +18,13 @@ def test_library_exports_every_symbol():
 
 def test_abi_version_and_error_string():
     lib = _lib.load()
-    assert lib.b200attn_abi_version() == _lib.ABI_VERSION == 12
+    assert lib.b200attn_abi_version() == _lib.ABI_VERSION == 17
     assert isinstance(lib.b200attn_last_error(), bytes)
     assert lib.b200attn_decode_workspace_bytes(4, 32, 128, 1) == 0
-    assert lib.b200attn_decode_workspace_bytes(4, 32, 128, 3) == 4 * 32 * 3 * 129 * 4 + 4 * 32 * 4
+    # fixed-size arrival-counter header (65536 int32) + fp32 partials and their LSE
+    assert lib.b200attn_decode_workspace_bytes(4, 32, 128, 3) == 65536 * 4 + 4 * 32 * 3 * 129 * 4
+    assert lib.b200attn_decode_workspace_bytes(4, 32, 80, 3) == lib.b200attn_decode_workspace_bytes(4, 32, 128, 3)
+    assert lib.b200attn_decode_ctas_per_sm(0, 2) == 4 and lib.b200attn_decode_ctas_per_sm(0, 4) == 2
 
 
 def test_argument_validation_without_gpu():

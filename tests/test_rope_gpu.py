@@ -119,6 +119,13 @@ def test_rope_then_store_equals_fused_and_matches_layer_classes():
     m(pos.unsqueeze(0).repeat(3, 1), q3, k3)   # t == h == w  ==> identical to 1-D rope with the same base
     m(pos, q4, k4)
     assert torch.equal(q3, q4) and torch.equal(k3, k4)
+    # text-only batches hand the three axes as ONE expanded row (stride 0 between axes): no out-of-bounds reads,
+    # same result as the materialised [3, T] positions
+    q5, k5 = q.clone(), k.clone()
+    expanded = pos.unsqueeze(0).expand(3, -1)
+    assert expanded.stride(0) == 0
+    m(expanded, q5, k5)
+    assert torch.equal(q3, q5) and torch.equal(k3, k5)
     with pytest.raises(AssertionError):
         rope(pos.unsqueeze(0).repeat(3, 1), q3, k3)
 
