@@ -13,7 +13,7 @@ GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 def golden_files() -> List[str]:
     """Attention-backend fixtures (oracle/gen_golden.py)."""
-    other = ("rope_", "alloc_", "swa_", "verify_", "mrope_", "merge_", "radix_")
+    other = ("rope_", "alloc_", "swa_", "verify_", "mrope_", "merge_", "radix_", "triton_")
     return sorted(p for p in glob.glob(os.path.join(GOLDEN_DIR, "*.pt")) if not os.path.basename(p).startswith(other))
 
 
