@@ -265,6 +265,11 @@ __global__ void __launch_bounds__(kExtThreads, 1)
     p.trace[(3 * 32 + 0) * 8 + 0] = clk();
     p.trace[(3 * 32 + 0) * 8 + 1] = gt;
   }
+  if (p.trace != nullptr && threadIdx.x == 0) {  // every CTA: start / end wall time (tools/trace_extend_ctas.py)
+    long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    p.trace[6 * 32 * 8 + blockIdx.x * 2] = gt;
+  }
 #endif
   if (threadIdx.x == 0) {
     for (int s = 0; s < kExtStages; ++s) {
@@ -778,6 +783,11 @@ __global__ void __launch_bounds__(kExtThreads, 1)
     p.trace[(3 * 32 + 0) * 8 + 2] = clk();
     p.trace[(3 * 32 + 0) * 8 + 3] = gt;
   }
+  if (p.trace != nullptr && threadIdx.x == 0) {
+    long long gt;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+    p.trace[6 * 32 * 8 + blockIdx.x * 2 + 1] = gt;
+  }
 #endif
   if (warp == 10) {
     tc_fence_after();
@@ -981,7 +991,7 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
   p.mask_indptr = mask_indptr;
   p.mask_skip_prefix = mask_skip_prefix;
 #ifdef EXT_TRACE
-  p.trace = workspace_bytes >= 6 * 32 * 8 * 8 ? (long long*)workspace : nullptr;
+  p.trace = workspace_bytes >= (6 * 32 * 8 + 2 * 160) * 8 ? (long long*)workspace : nullptr;
 #endif
   const int max_qtiles = (max_qo_len_host + kExtM - 1) / kExtM;
   cudaStream_t st = (cudaStream_t)stream;

@@ -39,12 +39,12 @@ kv_indptr = torch.zeros(B + 1, dtype=torch.int32, device=dev)
 qo_indptr = torch.zeros(B + 1, dtype=torch.int32, device=dev)
 kv_indices = torch.zeros(B * (P + E), dtype=torch.int32, device=dev)
 ops.build_kv_indices(table, req, seq, kv_indptr, kv_indices, qo_lens=extl, qo_indptr=qo_indptr)
-ws = torch.zeros(6 * 32 * 8, dtype=torch.int64, device=dev)
+ws = torch.zeros(6 * 32 * 8 + 2 * 160, dtype=torch.int64, device=dev)
 for _ in range(30):
     ops.extend_attention(q, kc, vc, o, qo_indptr, kv_indptr, kv_indices, D ** -0.5, causal=True, page_size=page,
                          max_qo_len=E, workspace=ws)
 torch.cuda.synchronize()
-t = ws.cpu().view(6, 32, 8)
+t = ws.cpu()[:6 * 32 * 8].view(6, 32, 8)
 t0 = int(t[2, 0, 0])
 print("softmax WG i: [wait_start, S_seen, ld_done, max_done, exp_done, arrived]; "
       "MMA: [w0, P0_seen, issued0, w1, P1_seen, issued1]")

@@ -27,12 +27,12 @@ kc = torch.randn((n_pages * page, Hkv, D), device=dev).bfloat16()
 vc = torch.randn((n_pages * page, Hkv, D), device=dev).bfloat16()
 q = torch.randn((B * E, Hq, D), device=dev).bfloat16()
 o = torch.empty_like(q)
-ws = torch.zeros(6 * 32 * 8, dtype=torch.int64, device=dev)
+ws = torch.zeros(6 * 32 * 8 + 2 * 160, dtype=torch.int64, device=dev)
 for _ in range(10):
     ops.extend_attention(q, kc, vc, o, qo_indptr, kv_indptr, kv_indices, D ** -0.5, causal=True, page_size=page,
                          max_qo_len=E, workspace=ws)
 torch.cuda.synchronize()
-t = ws.cpu().view(6, 32, 8)
+t = ws.cpu()[:6 * 32 * 8].view(6, 32, 8)
 c0, g0, c1, g1 = (int(t[3, 0, k]) for k in range(4))
 t0 = c0
 print(f"B={B} P={P} E={E}: CTA 0 lifetime {c1 - c0} cycles, {g1 - g0} ns, clock {(c1 - c0) / max(g1 - g0, 1) * 1e3:.0f} MHz")
