@@ -19,8 +19,8 @@
 //                                      in TMEM when the row max grew by > 2^8), P written back as bf16
 //                                      INTO its S half (tcgen05.st), so the second GEMM reads its A
 //                                      operand from TMEM; epilogue O / l.
-// The kernel is persistent: one CTA per SM walks a static round-robin slice of the item list (item =
-// (request, kv head, tile pair), heavy causal pairs first), and every role keeps its pipeline state
+// The kernel is persistent: one CTA per SM draws work items from the item list (item = (request, kv head,
+// tile pair), heavy causal pairs first; two static items, then tickets), and every role keeps its pipeline state
 // (K/V ring position, S/P half parity, Q/O phases) across items, so the TMA producers run ahead
 // into the next item while the softmax warps still finish the current one.
 //
@@ -38,6 +38,7 @@
 // Algorithmic FLOPs per (request, q head): 4 * D * sum_j (#visible keys of row j).
 #include "sm100.cuh"
 
+#include <atomic>
 #include <mutex>
 
 namespace b200attn {
@@ -53,7 +54,8 @@ constexpr int kExtBoxRows = 16;   // rows of one tiled K/V TMA box
 #endif
 constexpr float kRescaleThreshold = EXT_RESCALE_THRESHOLD;  // log2 domain
 constexpr int kRegsSoftmax = 208, kRegsOther = 80;
-constexpr int kExtMaxItems = 32;  // work items described per round
+constexpr int kExtRing = 8;        // work-item descriptor ring (scheduler -> every role)
+constexpr int kExtSchedSlots = 1024;  // launches in flight that may hold a ticket counter pair at the same time
 constexpr int kExtOSlabCols = 32; // epilogue: O leaves through shared memory in 128 x 32 slabs (TMA store)
 
 struct ExtendParams {
@@ -78,6 +80,7 @@ struct ExtendParams {
   const uint8_t* custom_mask;
   const int32_t* mask_indptr;
   int mask_skip_prefix;
+  int sched_slot;  // this launch's {ticket, CTAs done} pair in g_ext_sched
 #ifdef EXT_TRACE
   long long* trace;  // dev-only timeline of CTA (0,0,0): [role 0..2][step 0..31][8]
 #endif
@@ -94,14 +97,14 @@ struct ExtSmem {
   static constexpr int kOSlab = kExtM * kExtOSlabCols * 2;                 // one 128 x 32 output slab (8 KB)
   static constexpr int kO = kV + kExtStages * kTile;                       // [2 tiles][2 buffers] output slabs
   static constexpr int kBar = kO + 4 * kOSlab;
-  static constexpr int kItems = kBar + 256;                                // ItemDesc[kExtMaxItems]
-  static constexpr int kCum = kItems + kExtMaxItems * 32;                  // int[kMaxB + 1] pair prefix sums
+  static constexpr int kItems = kBar + 512;                                // ItemDesc[kExtRing]
+  static constexpr int kCum = kItems + kExtRing * 32;                      // int[kMaxB + 1] pair prefix sums
   // requests per launch (the host slices larger batches); D = 128 leaves room for 128 (227 KB shared memory)
   static constexpr int kMaxB = D == 128 ? 128 : 2048;
   static constexpr int kTotal = kCum + (kMaxB + 1) * 4 + 12;
 };
 
-// One work item = two query tiles of one (request, kv head); built per round into shared memory.
+// One work item = two query tiles of one (request, kv head); E < 0 = no more work for this CTA.
 struct ItemDesc {
   int q_beg, E, kv_beg, L, kvh, pair, pad0, pad1;
 };
@@ -124,8 +127,15 @@ enum ExtBar {
   kBarPVDone = kBarPFull + 4,           // [2]  MMA -> softmax_i : PV_i(c) done (only waited on before a rescale)
   kBarOFinal = kBarPVDone + 2,          // [2]  MMA -> softmax_i : last PV_i of the item done
   kBarQEmpty = kBarOFinal + 2,          // [2]  MMA -> producer : last QK_i of the item done, Q_i tile is free
-  kBarCount = kBarQEmpty + 2
+  kBarItemFull = kBarQEmpty + 2,        // [ring]  scheduler (K producer warp) -> every role : descriptor n is written
+  kBarItemEmpty = kBarItemFull + kExtRing,  // [ring]  every other role -> scheduler : descriptor n has been read
+  kBarCount = kBarItemEmpty + kExtRing
 };
+static_assert(kBarCount * 8 <= 512, "barrier block");
+
+// {next ticket, CTAs that drew their last ticket} per launch slot.  Zero at module load; the last CTA of a launch
+// to run out of work re-arms its pair, so a replayed CUDA graph finds it zero again.
+__device__ int g_ext_sched[kExtSchedSlots * 2];
 
 // ---- packed fp32x2 helpers (FFMA2 / FADD2 / FMNMX3 on sm_100) ----
 __device__ __forceinline__ uint64_t f2_pack(float lo, float hi) {
@@ -288,6 +298,10 @@ __global__ void __launch_bounds__(kExtThreads, 1)
       mbar_init(bar(kBarOFinal + i), 1);
       mbar_init(bar(kBarQEmpty + i), 1);
     }
+    for (int s = 0; s < kExtRing; ++s) {
+      mbar_init(bar(kBarItemFull + s), 1);
+      mbar_init(bar(kBarItemEmpty + s), 11);  // V producer, two MMA issuers, eight softmax warps
+    }
     mbar_fence_init();
   }
   if (warp == 10) tmem_alloc<kTmemCols>(smem_u32(tmem_slot));
@@ -326,14 +340,55 @@ __global__ void __launch_bounds__(kExtThreads, 1)
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const int total_items = cum[p.B] * p.Hkv;
-  // Boustrophedon assignment: round k hands item k*G + x to CTA x when k is even and to CTA G-1-x when k is odd.
-  // Items are ordered heavy-first within a (request, kv head), so a CTA that drew a heavy item in one round draws a
-  // light one in the next (static LPT): 8.2 K + 8.2 K chunked prefill on one kv head, 256 items on 148 CTAs:
-  // max/mean per-CTA work 1.31 -> 1.09.
-  const int grid_n = (int)gridDim.x;
-  const int full_rounds = total_items / grid_n, last_round = total_items - full_rounds * grid_n;
-  const int pos_last = (full_rounds & 1) ? grid_n - 1 - (int)blockIdx.x : (int)blockIdx.x;
-  const int n_my = full_rounds + (pos_last < last_round ? 1 : 0);
+  // Dynamic schedule: CTA x starts on items x and 2 * grid - 1 - x, every further item is a ticket drawn from a
+  // device counter, in list order (request, kv head, heavy pairs first: neighbours in time share a kv head's K/V
+  // tiles in L2, and the last tickets are the light pairs).  A static split left the CTAs finishing 4 % (32 x 2.5 K prefill) to 16 %
+  // (16 x 1280, 28/4 heads) apart: per-item cost is not proportional to its keys and SMs do not stream at one rate.
+  // The K producer warp is the scheduler: it draws the ticket of item n+2 when it starts item n (the atomic's latency
+  // hides behind the item's K loads) and publishes that descriptor when the loads are issued, one whole item before
+  // any role needs it (published one item ahead only, Q(n+1) landed ~1.4 us late: 1131 -> 1092 TFLOP/s on cfg3).
+  int* const sched = g_ext_sched + 2 * p.sched_slot;
+  auto describe = [&](int id) {  // id -> (request, kv head, pair)
+    ItemDesc d;
+    d.q_beg = d.kv_beg = d.L = d.kvh = d.pair = d.pad0 = d.pad1 = 0;
+    d.E = -1;
+    if (id >= total_items) return d;
+    int lo = 0, hi = p.B;  // largest b with cum[b] * Hkv <= id
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (cum[mid] * p.Hkv <= id) lo = mid; else hi = mid;
+    }
+    const int b = lo;
+    const int np = cum[b + 1] - cum[b];
+    const int rem = id - cum[b] * p.Hkv;
+    d.q_beg = p.qo_indptr[b];
+    d.E = p.qo_indptr[b + 1] - d.q_beg;
+    d.kv_beg = p.kv_indptr[b];
+    d.L = p.kv_indptr[b + 1] - d.kv_beg;
+    d.kvh = rem / np;
+    d.pair = np - 1 - rem % np;
+    d.pad0 = p.custom_mask != nullptr ? p.mask_indptr[b] : 0;  // offset of this request's mask block
+    return d;
+  };
+  // scheduler side: wait until every role has read the descriptor that lived in this ring slot, then overwrite it
+  auto publish = [&](int n, const ItemDesc& d) {
+    const int slot = n % kExtRing;
+    if (n >= kExtRing) mbar_wait(bar(kBarItemEmpty + slot), ((n / kExtRing) + 1) & 1);
+    if (lane == 0) {
+      items[slot] = d;
+      mbar_arrive(bar(kBarItemFull + slot));  // release: the descriptor is visible to whoever sees the phase flip
+    }
+    __syncwarp();
+  };
+  // reader side (whole warps): descriptor n, acknowledged as soon as it sits in registers
+  auto acquire = [&](int n) {
+    const int slot = n % kExtRing;
+    mbar_wait(bar(kBarItemFull + slot), (n / kExtRing) & 1);
+    const ItemDesc d = items[slot];
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar(kBarItemEmpty + slot));
+    return d;
+  };
 
   // ---- per-role pipeline state, carried across items and rounds ----
   int kt = 0;              // K/V tiles consumed / produced so far (ring position)
@@ -345,9 +400,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
   // round loop and meet at the two barriers of every round.
   if (warp >= 8) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" ::"n"(kRegsOther));
-    for (int r0 = 0; r0 < n_my; r0 += kExtMaxItems) {
-      const int n_round = min(kExtMaxItems, n_my - r0);
-      __syncthreads();  // this round's descriptors are in shared memory
+    {
       if (warp == 8 || warp == 9) {
         // ===================== TMA producers (warp 8: Q + K, warp 9: V) =====================
         const bool is_k = (warp == 8);
@@ -355,8 +408,21 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         const CUtensorMap* tm_b = is_k ? &tm_kbox : &tm_vbox;
         const uint32_t tile0 = smem0 + (is_k ? S::kK : S::kV);
         const int bar_full = is_k ? kBarKFull : kBarVFull, bar_empty = is_k ? kBarKEmpty : kBarVEmpty;
-        for (int it = 0; it < n_round; ++it) {
-          const ItemDesc d = items[it];
+        ItemDesc d;
+        int ticket = 0;
+        if (is_k) {
+          publish(0, describe((int)blockIdx.x));
+          publish(1, describe(2 * (int)gridDim.x - 1 - (int)blockIdx.x));
+        }
+        for (int n = 0;; ++n) {
+          if (is_k) {
+            d = items[n % kExtRing];  // written by this warp's lane 0 (program order + __syncwarp)
+            if (d.E < 0) break;
+            if (lane == 0) ticket = atomicAdd(sched, 1);  // item n + 2; needed only after this item's loads are issued
+          } else {
+            d = acquire(n);
+            if (d.E < 0) break;
+          }
           ItemTiles t;
           derive_tiles(d, p, t);
           // The Q tiles are loaded by the V producer: the K producer must NOT wait for the previous item's last
@@ -421,6 +487,12 @@ __global__ void __launch_bounds__(kExtThreads, 1)
             }
             load_slots(j + 1);
           }
+          if (is_k) publish(n + 2, describe(2 * (int)gridDim.x + __shfl_sync(0xffffffffu, ticket, 0)));
+        }
+        // out of work: the last CTA of the launch to get here re-arms the counter pair
+        if (is_k && lane == 0 && atomicAdd(sched + 1, 1) == (int)gridDim.x - 1) {
+          sched[0] = 0;
+          sched[1] = 0;
         }
       } else {
         // ===================== MMA issuers (warp 10: tile 0, warp 11: tile 1) =====================
@@ -440,8 +512,11 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         auto desc = [](uint64_t hi, uint32_t addr) { return hi | (uint64_t)((addr & 0x3FFFF) >> 4); };
         const uint32_t qa = smem_u + S::kQ + i * S::kTile;
         const uint32_t ts = tmem_u + kColS + i * 128, to = tmem_u + kColO + i * 128;
-        for (int it = 0; it < n_round; ++it) {
-          const ItemDesc d = items[it];
+        for (int n = 0;; ++n) {
+          const ItemDesc d = acquire(n);
+          if (d.E < 0) break;
+          const int it = n & 31;
+          (void)it;
           ItemTiles t;
           derive_tiles(d, p, t);
           const int nc_i = __shfl_sync(0xffffffffu, i == 0 ? t.nc[0] : t.nc[1], 0);
@@ -529,36 +604,10 @@ __global__ void __launch_bounds__(kExtThreads, 1)
           nq_my += nc_i > 0 ? 1 : 0;
         }
       }
-      __syncthreads();  // every role is done with this round's descriptors
     }
   } else {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(kRegsSoftmax));
-    for (int r0 = 0; r0 < n_my; r0 += kExtMaxItems) {
-      const int n_round = min(kExtMaxItems, n_my - r0);
-      // ---- describe this round's items: id -> (request, kv head, pair), heavy pairs first ----
-      if ((int)threadIdx.x < n_round) {
-        const int rk = r0 + (int)threadIdx.x;  // round index of this item
-        const int id = rk * (int)gridDim.x + ((rk & 1) ? (int)gridDim.x - 1 - (int)blockIdx.x : (int)blockIdx.x);
-        int lo = 0, hi = p.B;  // largest b with cum[b] * Hkv <= id
-        while (hi - lo > 1) {
-          const int mid = (lo + hi) >> 1;
-          if (cum[mid] * p.Hkv <= id) lo = mid; else hi = mid;
-        }
-        const int b = lo;
-        const int np = cum[b + 1] - cum[b];
-        const int rem = id - cum[b] * p.Hkv;
-        ItemDesc d;
-        d.q_beg = p.qo_indptr[b];
-        d.E = p.qo_indptr[b + 1] - d.q_beg;
-        d.kv_beg = p.kv_indptr[b];
-        d.L = p.kv_indptr[b + 1] - d.kv_beg;
-        d.kvh = rem / np;
-        d.pair = np - 1 - rem % np;
-        d.pad0 = p.custom_mask != nullptr ? p.mask_indptr[b] : 0;  // offset of this request's mask block
-        d.pad1 = 0;
-        items[threadIdx.x] = d;
-      }
-      __syncthreads();
+    {
       // ===================== softmax + epilogue (thread = query row of tile i) =====================
       using T = typename std::conditional<kBf16, __nv_bfloat16, __half>::type;
       const int i = warp >> 2;            // tile of this warpgroup
@@ -566,8 +615,11 @@ __global__ void __launch_bounds__(kExtThreads, 1)
       const uint32_t lane_addr = tmem + ((uint32_t)((warp & 3) * 32) << 16);
       const uint32_t col_s = lane_addr + kColS + i * 128, col_o = lane_addr + kColO + i * 128;
       const uint64_t scale2 = f2_pack(p.scale_log2, p.scale_log2);
-      for (int it = 0; it < n_round; ++it) {
-        const ItemDesc d = items[it];
+      for (int n = 0;; ++n) {
+        const ItemDesc d = acquire(n);
+        if (d.E < 0) break;
+        const int it = n & 31;
+        (void)it;
         ItemTiles t;
         derive_tiles(d, p, t);
         const int nc_i = i == 0 ? t.nc[0] : t.nc[1];
@@ -769,7 +821,6 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         g_my += nc_i;
         ++nq_my;
       }
-      __syncthreads();  // every role is done with this round's descriptors
     }
     // the staged output slabs must have left shared memory (and be globally visible) before the CTA retires
     if ((threadIdx.x & 127) == 0) asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory");
@@ -799,6 +850,8 @@ __global__ void __launch_bounds__(kExtThreads, 1)
 
 // ------------------------------------------------------------------ host side
 namespace b200attn {
+
+static std::atomic<unsigned> g_sched_next{0};
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -892,9 +945,11 @@ static int launch_extend(const CUtensorMap& tq, const CUtensorMap& tk, const CUt
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     configured = true;
   }
-  // Persistent: one CTA per SM, static round-robin over the item list (request, kv head, tile pair);
-  // consecutive items share a kv head's K/V tiles, run at the same time on neighbouring SMs and hit
-  // them in L2.  The host only knows an upper bound of the item count (sizes the grid, graph-safe).
+  // Persistent: one CTA per SM, items (request, kv head, tile pair) drawn in list order; consecutive items
+  // share a kv head's K/V tiles, run at the same time on neighbouring SMs and hit them in L2.  The host only
+  // knows an upper bound of the item count (sizes the grid, graph-safe).  Each launch gets its own ticket counter
+  // pair: launches that overlap in time (other streams) are independent as long as fewer than kExtSchedSlots
+  // launches separate them.
   const long long upper = (long long)((max_qtiles * p.G + 1) / 2) * p.Hkv;
   const int sms = sm_count();
   constexpr int kExtMaxB = ExtSmem<D>::kMaxB;
@@ -905,6 +960,7 @@ static int launch_extend(const CUtensorMap& tq, const CUtensorMap& tk, const CUt
     ps.kv_indptr = p.kv_indptr + b0;
     const long long items = upper * ps.B;
     dim3 grid((unsigned)(items < sms ? items : sms));
+    ps.sched_slot = (int)(g_sched_next.fetch_add(1u) % (unsigned)kExtSchedSlots);
     extend_kernel<D, kBf16><<<grid, kExtThreads, kSmem, st>>>(tq, tk, tv, tkb, tvb, to, ps);
     B2_LAUNCH_CHECK();
   }
