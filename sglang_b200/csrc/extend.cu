@@ -40,6 +40,7 @@
 
 #include <atomic>
 #include <mutex>
+#include <type_traits>
 
 namespace b200attn {
 
@@ -136,6 +137,22 @@ static_assert(kBarCount * 8 <= 512, "barrier block");
 // {next ticket, CTAs that drew their last ticket} per launch slot.  Zero at module load; the last CTA of a launch
 // to run out of work re-arms its pair, so a replayed CUDA graph finds it zero again.
 __device__ int g_ext_sched[kExtSchedSlots * 2];
+
+// O_i *= alpha (this thread's row; D fp32 columns of TMEM).  Rare (row max grew by more than the lazy-rescale
+// threshold) and deliberately NOT inlined: the softmax chunk loop stays short.
+template <int D>
+__device__ __noinline__ void rescale_o(uint32_t col_o, float alpha) {
+  using namespace sm100;
+#pragma unroll
+  for (int q = 0; q < D / 32; ++q) {
+    uint32_t v[32];
+    tmem_ld32(col_o + q * 32, v);
+    tmem_wait_ld();
+#pragma unroll
+    for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(__uint_as_float(v[e]) * alpha);
+    tmem_st32(col_o + q * 32, v);
+  }
+}
 
 // ---- packed fp32x2 helpers (FFMA2 / FADD2 / FMNMX3 on sm_100) ----
 __device__ __forceinline__ uint64_t f2_pack(float lo, float hi) {
@@ -634,7 +651,13 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         const int lower = p.window_left >= 0 ? min(limit - 1, max(0, t.prefix + m0 + row - p.window_left)) : 0;
         float m_used = -INFINITY;  // reference max (log2 domain) the running sums are expressed in
         float l_run = 0.f;
-        for (int c = 0; c < nc_i; ++c) {
+        // One 64-key chunk.  Two copies of this body exist: kEdge = false is the straight-line interior chunk (no
+        // mask, cap or window code at all: ~400 instructions, fits the instruction cache of a sub-partition);
+        // kEdge = true carries every masking block.  With one copy, an interior chunk branched over four fully
+        // unrolled 64-element mask blocks and paid an instruction-fetch stall after each jump (ncu: ~15 % of the
+        // softmax warps' samples were no_inst / branch_resolving on those BSSY / BSYNC / BRA).
+        auto chunk = [&](auto edge_tag, const int c) {
+          constexpr bool kEdge = decltype(edge_tag)::value;
           const int gc = g_my + c;                          // chunk count of this tile since kernel start
           const uint32_t col_c = col_s + (gc & 1) * kExtC;  // S/P half of this chunk
           TRACE(i, c, 0);
@@ -653,6 +676,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
           tmem_wait_ld();
           TRACE(i, c, 2);
           const int n0 = t.kbase + c * kExtC;
+          if constexpr (kEdge) {
           if (p.cap_pre > 0.f) {  // logit cap (uniform branch): s <- c/sm_scale * tanh(s * sm_scale / c)
             const float inv_pre = 1.f / p.cap_pre;
 #pragma unroll
@@ -677,6 +701,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
               if (key >= first && key < limit && __ldg(mrow + key) == 0) s[e] = -INFINITY;
             }
           }
+          }  // kEdge
           float mx4[4] = {s[0], s[1], s[2], s[3]};
 #pragma unroll
           for (int e = 4; e < kExtC; e += 8) {
@@ -702,15 +727,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
             mbar_wait(bar(kBarPVDone + i), (gc - 1) & 1);
             tc_fence_after();
             l_run *= alpha;
-#pragma unroll
-            for (int q = 0; q < D / 32; ++q) {
-              uint32_t v[32];
-              tmem_ld32(col_o + q * 32, v);
-              tmem_wait_ld();
-#pragma unroll
-              for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(__uint_as_float(v[e]) * alpha);
-              tmem_st32(col_o + q * 32, v);
-            }
+            rescale_o<D>(col_o, alpha);  // out of line: keeps the hot loop compact
           }
           TRACE(i, c, 3);
           // p = exp2(s * scale - m); packed bf16 pairs go back into the first 32 columns of this S half
@@ -746,6 +763,23 @@ __global__ void __launch_bounds__(kExtThreads, 1)
           tc_fence_before();
           mbar_arrive(bar(kBarPFull + i * 2 + (gc & 1)));
           TRACE(i, c, 5);
+        };
+        const bool any_feature = p.cap_pre > 0.f || p.custom_mask != nullptr;
+        // warp-uniform: no row of this warp needs a mask in chunk c
+        auto interior = [&](int c) {
+          const int n0 = t.kbase + c * kExtC;
+          return __all_sync(0xffffffffu, n0 + kExtC <= limit && n0 >= lower) && !any_feature;
+        };
+        for (int c = 0; c < nc_i;) {
+          if (interior(c)) {
+            do {  // runs of interior chunks stay inside this short loop (one near back edge)
+              chunk(std::false_type{}, c);
+              ++c;
+            } while (c < nc_i && interior(c));
+          } else {
+            chunk(std::true_type{}, c);
+            ++c;
+          }
         }
         // ---- epilogue of this item (the issuer already runs QK of the next one) ----
         if (i == 0) { TRACE(4, it, 2); }
