@@ -183,6 +183,10 @@ int64_t b200attn_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t D, int32_
  * b200attn_decode_fp8kv (kv_fp8 = 1): the caller's split / tail-split wave arithmetic needs it. */
 int b200attn_decode_ctas_per_sm(int kv_fp8, int warps);
 
+/* b200attn_decode / b200attn_decode_fp8kv are launched with programmatic stream serialization: the grid may be
+ * scheduled while the previous kernel of the stream drains and orders itself with griddepcontrol.wait before its
+ * first global access.  Environment B200ATTN_PDL=0 restores plain stream order. */
+
 int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
                     const void* v_cache, int64_t kv_stride, void* o, int64_t o_stride,
                     float* lse, const int32_t* kv_indptr, const int32_t* kv_indices,

@@ -8,6 +8,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 
 #include "../../include/b200attn.h"
 
@@ -174,3 +175,34 @@ __host__ __device__ __forceinline__ void split_policy(int L, int max_splits, int
 }
 
 }  // namespace b200attn
+
+// Programmatic dependent launch (PDL).  A kernel launched through launch_pdl() may be scheduled while the previous
+// kernel of the stream is still draining (as soon as all of that kernel's CTAs have executed pdl_trigger() or
+// exited); it must execute pdl_wait() before its first global-memory access: the wait returns when the previous
+// grid has completed and its writes are visible.  What overlaps is launch latency and CTA start-up, nothing else.
+// B200ATTN_PDL=0 falls back to plain stream order.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;\n" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory"); }
+
+inline bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("B200ATTN_PDL"); return e == nullptr || atoi(e) != 0; }();
+  return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+#endif
+

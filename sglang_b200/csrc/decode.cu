@@ -45,6 +45,8 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
   const int item = blockIdx.z;
   const int kvh = hg / p.groups_per_kvh;
   const int grp = hg - kvh * p.groups_per_kvh;
+  pdl_wait();     // everything below reads what earlier kernels of the stream wrote (indices, the new K/V rows)
+  pdl_trigger();  // the next kernel may be scheduled into SMs as CTAs of this grid retire
   const int req = p.req_ids ? p.req_ids[item] : item;
   const int qrow = p.q_rows ? p.q_rows[item] : item;
   int kv_beg = p.kv_indptr[req];
@@ -357,6 +359,8 @@ __global__ void __launch_bounds__(kDecThreads, B200ATTN_FP8_CTAS) decode_fp8_ker
   const int item = blockIdx.z;
   const int kvh = hg / p.groups_per_kvh;
   const int grp = hg - kvh * p.groups_per_kvh;
+  pdl_wait();     // everything below reads what earlier kernels of the stream wrote (indices, the new K/V rows)
+  pdl_trigger();  // the next kernel may be scheduled into SMs as CTAs of this grid retire
   const int req = p.req_ids ? p.req_ids[item] : item;
   const int qrow = p.q_rows ? p.q_rows[item] : item;
   int kv_beg = p.kv_indptr[req];
@@ -668,8 +672,7 @@ static int launch_decode_fp8(const DecodeParams& p, cudaStream_t st) {
     configured = true;
   }
   dim3 grid((unsigned)p.max_splits, (unsigned)(p.Hkv * p.groups_per_kvh), (unsigned)p.B);
-  decode_fp8_kernel<D, kBf16><<<grid, kDecThreads, kSmem, st>>>(p);
-  B2_LAUNCH_CHECK();
+  B2_CUDA(launch_pdl(decode_fp8_kernel<D, kBf16>, grid, dim3(kDecThreads), kSmem, st, p));
   return B200ATTN_OK;
 }
 
@@ -687,8 +690,7 @@ static int launch_decode_nw(const DecodeParams& p, cudaStream_t st) {
     configured = true;
   }
   dim3 grid((unsigned)p.max_splits, (unsigned)(p.Hkv * p.groups_per_kvh), (unsigned)p.B);
-  decode_kernel<D, kBf16, NW><<<grid, 32 * NW, kSmem, st>>>(p);
-  B2_LAUNCH_CHECK();
+  B2_CUDA(launch_pdl(decode_kernel<D, kBf16, NW>, grid, dim3(32 * NW), kSmem, st, p));
   return B200ATTN_OK;
 }
 
