@@ -28,6 +28,20 @@ namespace b200attn {
 // flight per SM, but 592 resident slots instead of 296 - cfg2's 512 units become ONE wave (no 73 %-full second
 // wave, every CTA streams at the same rate from start to end) and small batches can be split twice as finely
 // before a second wave forms.
+#ifdef DEC_TRACE
+// dev-only (libb200attn_trace.so, tools/trace_decode.py): per-CTA wall-clock stamps of decode_kernel
+__device__ long long g_dec_trace[8 * 16384];
+#define DTRACE(slot)                                                                                       \
+  if (threadIdx.x == 0) {                                                                                  \
+    const int cta_ = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);                       \
+    long long gt_;                                                                                         \
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_));                                                \
+    if (cta_ < 16384) g_dec_trace[cta_ * 8 + (slot)] = gt_;                                                \
+  }
+#else
+#define DTRACE(slot)
+#endif
+
 template <int D, bool kBf16, int NW>
 __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const DecodeParams p) {
   constexpr int kDecTile = 16 * NW;     // shadows the 4-warp constants of decode.cuh
@@ -45,8 +59,10 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
   const int item = blockIdx.z;
   const int kvh = hg / p.groups_per_kvh;
   const int grp = hg - kvh * p.groups_per_kvh;
+  DTRACE(0);
   pdl_wait();     // everything below reads what earlier kernels of the stream wrote (indices, the new K/V rows)
   pdl_trigger();  // the next kernel may be scheduled into SMs as CTAs of this grid retire
+  DTRACE(1);
   const int req = p.req_ids ? p.req_ids[item] : item;
   const int qrow = p.q_rows ? p.q_rows[item] : item;
   int kv_beg = p.kv_indptr[req];
@@ -69,22 +85,6 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
   const int h0 = kvh * p.G + grp * kDecMaxG;             // first q head of this CTA
   const int gcount = min(kDecMaxG, p.G - grp * kDecMaxG); // valid q heads (rows of M)
 
-  // ---- Q fragments (A operand, 16 x D), rows >= gcount are zero -----------
-  uint32_t qf[D / 16][4];
-  {
-    const T* qbase = reinterpret_cast<const T*>(p.q) + (int64_t)qrow * p.q_stride + (int64_t)h0 * Dv;
-    const int r0 = lane >> 2, c0 = (lane & 3) * 2;
-#pragma unroll
-    for (int ks = 0; ks < D / 16; ++ks) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int r = r0 + (j & 1) * 8;
-        const int c = ks * 16 + c0 + (j >> 1) * 8;
-        qf[ks][j] = (r < gcount && c < Dv) ? *reinterpret_cast<const uint32_t*>(qbase + (int64_t)r * Dv + c) : 0u;
-      }
-    }
-  }
-
   // ---- producer state -------------------------------------------------------
   const int ld_chunk = tid % kChunks;
   const int ld_row0 = tid / kChunks;
@@ -104,26 +104,53 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
       slots[i] = (tile < ntiles && key < k_hi) ? __ldg(idx + key) : -1;
     }
   };
-  auto issue_tile = [&](int stage) {
+  auto issue_tile_from = [&](const int32_t (&sl)[kLoadsPerThread], int stage) {
     const uint32_t ks = smem_base + stage * kStageBytes;
     const uint32_t vs = ks + kTileBytes;
 #pragma unroll
     for (int i = 0; i < kLoadsPerThread; ++i) {
       const int row = ld_row0 + i * kRowsPerPass;
       const uint32_t off = swz_off<D>(row, ld_chunk);
-      const bool ok = slots[i] >= 0 && ld_col_ok;
-      const int64_t g = ok ? (int64_t)slots[i] * row_bytes : 0;
+      const bool ok = sl[i] >= 0 && ld_col_ok;
+      const int64_t g = ok ? (int64_t)sl[i] * row_bytes : 0;
       cp_async16(ks + off, kc + g, ok ? 16 : 0);  // invalid rows / columns are zero-filled
       cp_async16(vs + off, vc + g, ok ? 16 : 0);
     }
   };
+  auto issue_tile = [&](int stage) { issue_tile_from(slots, stage); };
 
-  fetch_slots(0);
+  // Prologue, ordered for memory-level parallelism (a warp issues in order: one dependent use stalls every load
+  // behind it).  The slot ids of ALL prologue tiles and of the first steady-state tile go out first, then the Q
+  // fragment loads, and only then the first instruction that needs a slot id.  (Fetching tile s+1's ids after
+  // issuing tile s serialised two L2 round trips: 4.1 us from CTA start to the first tile, tools/trace_decode.py.)
+  int32_t pslots[kDecStages - 1][kLoadsPerThread];
 #pragma unroll
   for (int s = 0; s < kDecStages - 1; ++s) {
-    if (s < ntiles) issue_tile(s);
+    fetch_slots(s);
+#pragma unroll
+    for (int i = 0; i < kLoadsPerThread; ++i) pslots[s][i] = slots[i];
+  }
+  fetch_slots(kDecStages - 1);
+  // ---- Q fragments (A operand, 16 x D), rows >= gcount are zero -----------
+  uint32_t qf[D / 16][4];
+  {
+    const T* qbase = reinterpret_cast<const T*>(p.q) + (int64_t)qrow * p.q_stride + (int64_t)h0 * Dv;
+    const int r0 = lane >> 2, c0 = (lane & 3) * 2;
+#pragma unroll
+    for (int ks = 0; ks < D / 16; ++ks) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int r = r0 + (j & 1) * 8;
+        const int c = ks * 16 + c0 + (j >> 1) * 8;
+        qf[ks][j] = (r < gcount && c < Dv) ? *reinterpret_cast<const uint32_t*>(qbase + (int64_t)r * Dv + c) : 0u;
+      }
+    }
+  }
+
+#pragma unroll
+  for (int s = 0; s < kDecStages - 1; ++s) {
+    if (s < ntiles) issue_tile_from(pslots[s], s);
     cp_async_commit();
-    fetch_slots(s + 1);
   }
 
   // ---- per-warp online-softmax state ---------------------------------------
@@ -135,9 +162,11 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
 
   const int lm = lane >> 3, lr = lane & 7;  // ldmatrix: matrix id / row in matrix
 
+  DTRACE(2);
   for (int t = 0; t < ntiles; ++t) {
     cp_async_wait<kDecStages - 2>();
     __syncthreads();
+    if (t == 0) { DTRACE(3); }
     {
       const int nt = t + kDecStages - 1;
       if (nt < ntiles) issue_tile(nt % kDecStages);
@@ -217,6 +246,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
   }
   cp_async_wait<0>();
   __syncthreads();  // ring is dead; reuse it for the cross-warp merge
+  DTRACE(4);
 
   // ---- merge the four warps (fp32, shared memory) ---------------------------
 #pragma unroll
@@ -230,10 +260,17 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
   {
     const int r0 = lane >> 2, c0 = (lane & 3) * 2;
 #pragma unroll
-    for (int n = 0; n < D / 8; ++n) {
-      float* dst = sm_o + (warp * 16 + r0) * D + n * 8 + c0;
-      *reinterpret_cast<float2*>(dst) = make_float2(o_acc[n][0], o_acc[n][1]);
-      *reinterpret_cast<float2*>(dst + 8 * D) = make_float2(o_acc[n][2], o_acc[n][3]);
+    // only the gcount (<= 16) real q heads are written and read back: with G = 4 that is a quarter of the tile
+    if (r0 < gcount) {
+#pragma unroll
+      for (int n = 0; n < D / 8; ++n)
+        *reinterpret_cast<float2*>(sm_o + (warp * 16 + r0) * D + n * 8 + c0) = make_float2(o_acc[n][0], o_acc[n][1]);
+    }
+    if (r0 + 8 < gcount) {
+#pragma unroll
+      for (int n = 0; n < D / 8; ++n)
+        *reinterpret_cast<float2*>(sm_o + (warp * 16 + r0 + 8) * D + n * 8 + c0) =
+            make_float2(o_acc[n][2], o_acc[n][3]);
     }
     if ((lane & 3) == 0) {
       sm_m[warp * 16 + r0] = m_run[0];
@@ -283,39 +320,64 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
       if (c == 0) p.ws_lse[w] = lse2;
     }
   }
+  DTRACE(5);
   if (direct) return;
   // ---- split merge by the LAST CTA of the unit to arrive (no second launch) ----
   // writers: partials -> fence -> barrier -> one relaxed atomic ticket; the CTA that draws the last ticket sees
   // every partial (fence after the ticket) and reads them through L2 (ld.global.cg, never the read-only path).
   __shared__ int s_last;
-  __threadfence();
-  __syncthreads();
+  __syncthreads();  // every thread's partial stores happen-before thread 0's fence (cumulativity carries them)
   if (tid == 0) {
     int* cnt = p.ws_cnt + (int64_t)item * (p.Hkv * p.groups_per_kvh) + hg;
+    __threadfence();
     const int ticket = atomicAdd(cnt, 1);
     s_last = (ticket == nsplit - 1);
-    if (s_last) *cnt = 0;  // self-cleaning: the next launch finds zeros again
+    if (s_last) {
+      *cnt = 0;          // self-cleaning: the next launch finds zeros again
+      __threadfence();   // acquire side: the other CTAs' partials, ordered before their tickets, are visible below
+    }
   }
   __syncthreads();
+  DTRACE(6);
   if (!s_last) return;
-  __threadfence();
   for (int e = tid; e < gcount * (D / 4); e += kDecThreads) {
     const int r = e / (D / 4), c = (e - r * (D / 4)) * 4;
     const int h = h0 + r;
     const int64_t w0 = ((int64_t)item * p.Hq + h) * p.max_splits;
+    // one pass, four partials in flight at a time (all loads of a group are issued before the first use), running
+    // max carried across groups: a 2..4-way split costs ONE L2 round trip here instead of two dependent passes
     float m = -INFINITY;
-    for (int sp = 0; sp < nsplit; ++sp) m = fmaxf(m, __ldcg(p.ws_lse + w0 + sp));
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     float l = 0.f;
-    for (int sp = 0; sp < nsplit; ++sp) {
-      const float ls = __ldcg(p.ws_lse + w0 + sp);
-      const float f = (ls == -INFINITY) ? 0.f : fast_exp2(ls - m);
-      const float4 x = __ldcg(reinterpret_cast<const float4*>(p.ws_o + (w0 + sp) * D + c));
-      acc.x += f * x.x;
-      acc.y += f * x.y;
-      acc.z += f * x.z;
-      acc.w += f * x.w;
-      l += f;
+    for (int sp0 = 0; sp0 < nsplit; sp0 += 4) {
+      float ls[4];
+      float4 x[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const bool ok = sp0 + u < nsplit;
+        ls[u] = ok ? __ldcg(p.ws_lse + w0 + sp0 + u) : -INFINITY;
+        x[u] = ok ? __ldcg(reinterpret_cast<const float4*>(p.ws_o + (w0 + sp0 + u) * D + c))
+                  : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      const float mg = fmaxf(fmaxf(ls[0], ls[1]), fmaxf(ls[2], ls[3]));
+      if (mg > m) {  // rescale what has been accumulated so far
+        const float f0 = (m == -INFINITY) ? 0.f : fast_exp2(m - mg);
+        acc.x *= f0;
+        acc.y *= f0;
+        acc.z *= f0;
+        acc.w *= f0;
+        l *= f0;
+        m = mg;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float f = (ls[u] == -INFINITY) ? 0.f : fast_exp2(ls[u] - m);
+        acc.x += f * x[u].x;
+        acc.y += f * x[u].y;
+        acc.z += f * x[u].z;
+        acc.w += f * x[u].w;
+        l += f;
+      }
     }
     if (p.sinks != nullptr && l > 0.f) l += fast_exp2(__ldg(p.sinks + h) * kLog2e - m);
     const float inv = (l > 0.f) ? 1.f / l : 0.f;
@@ -327,6 +389,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
     if (p.lse != nullptr && c == 0)
       p.lse[(int64_t)qrow * p.Hq + h] = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
   }
+  DTRACE(7);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -830,3 +893,9 @@ extern "C" int b200attn_decode_fp8kv(const void* q, int64_t q_stride, const void
                      window_left, logit_cap, sinks, workspace, workspace_bytes, stream, true, k_descale,
                      v_descale);
 }
+
+#ifdef DEC_TRACE
+extern "C" int b200attn_decode_trace_read(void* dst_host, int64_t bytes) {
+  return cudaMemcpyFromSymbol(dst_host, b200attn::g_dec_trace, (size_t)bytes) == cudaSuccess ? 0 : 1;
+}
+#endif
