@@ -444,6 +444,47 @@ __global__ void __launch_bounds__(kDecThreads, B200ATTN_FP8_CTAS) decode_fp8_ker
   const int h0 = kvh * p.G + grp * kDecMaxG;
   const int gcount = min(kDecMaxG, p.G - grp * kDecMaxG);
 
+  const int ld_chunk = tid % kChunks;
+  const int ld_row0 = tid / kChunks;
+  const uint8_t* kc8 = reinterpret_cast<const uint8_t*>(p.k_cache) + (int64_t)kvh * D + ld_chunk * 16;
+  const uint8_t* vc8 = reinterpret_cast<const uint8_t*>(p.v_cache) + (int64_t)kvh * D + ld_chunk * 16;
+  const int64_t row_bytes = p.kv_stride;
+  const int32_t* idx = p.kv_indices + kv_beg;
+  const uint32_t smem_base = smem_u32(smem);
+
+  int32_t slots[kLoadsPerThread];
+  auto fetch_slots = [&](int tile) {
+    const int base = k_lo + tile * kDecTile + ld_row0;
+#pragma unroll
+    for (int i = 0; i < kLoadsPerThread; ++i) {
+      const int key = base + i * kRowsPerPass;
+      slots[i] = (tile < ntiles && key < k_hi) ? __ldg(idx + key) : -1;
+    }
+  };
+  auto issue_tile_from = [&](const int32_t (&sl)[kLoadsPerThread], int stage) {
+    const uint32_t ks = smem_base + stage * kStageBytes;
+    const uint32_t vs = ks + kTileBytes;
+#pragma unroll
+    for (int i = 0; i < kLoadsPerThread; ++i) {
+      const int row = ld_row0 + i * kRowsPerPass;
+      const uint32_t off = swz8_off<D>(row, ld_chunk);
+      const bool ok = sl[i] >= 0;
+      const int64_t g = ok ? (int64_t)sl[i] * row_bytes : 0;
+      cp_async16(ks + off, kc8 + g, ok ? 16 : 0);
+      cp_async16(vs + off, vc8 + g, ok ? 16 : 0);
+    }
+  };
+  auto issue_tile = [&](int stage) { issue_tile_from(slots, stage); };
+
+  // prologue ordered for memory-level parallelism, as in decode_kernel: every slot-id load first, then Q, then uses
+  int32_t pslots[kDec8Stages - 1][kLoadsPerThread];
+#pragma unroll
+  for (int s = 0; s < kDec8Stages - 1; ++s) {
+    fetch_slots(s);
+#pragma unroll
+    for (int i = 0; i < kLoadsPerThread; ++i) pslots[s][i] = slots[i];
+  }
+  fetch_slots(kDec8Stages - 1);
   // ---- Q fragments in f16, contraction index permuted: chunk kc, lane quad slot t holds d = 16kc + 4t + {0,1}
   // (k-slots 2t,2t+1) and d = 16kc + 4t + {2,3} (k-slots 2t+8, 2t+9) -----------------------------------------
   uint32_t qf[D / 16][4];
@@ -466,43 +507,10 @@ __global__ void __launch_bounds__(kDecThreads, B200ATTN_FP8_CTAS) decode_fp8_ker
     }
   }
 
-  const int ld_chunk = tid % kChunks;
-  const int ld_row0 = tid / kChunks;
-  const uint8_t* kc8 = reinterpret_cast<const uint8_t*>(p.k_cache) + (int64_t)kvh * D + ld_chunk * 16;
-  const uint8_t* vc8 = reinterpret_cast<const uint8_t*>(p.v_cache) + (int64_t)kvh * D + ld_chunk * 16;
-  const int64_t row_bytes = p.kv_stride;
-  const int32_t* idx = p.kv_indices + kv_beg;
-  const uint32_t smem_base = smem_u32(smem);
-
-  int32_t slots[kLoadsPerThread];
-  auto fetch_slots = [&](int tile) {
-    const int base = k_lo + tile * kDecTile + ld_row0;
-#pragma unroll
-    for (int i = 0; i < kLoadsPerThread; ++i) {
-      const int key = base + i * kRowsPerPass;
-      slots[i] = (tile < ntiles && key < k_hi) ? __ldg(idx + key) : -1;
-    }
-  };
-  auto issue_tile = [&](int stage) {
-    const uint32_t ks = smem_base + stage * kStageBytes;
-    const uint32_t vs = ks + kTileBytes;
-#pragma unroll
-    for (int i = 0; i < kLoadsPerThread; ++i) {
-      const int row = ld_row0 + i * kRowsPerPass;
-      const uint32_t off = swz8_off<D>(row, ld_chunk);
-      const bool ok = slots[i] >= 0;
-      const int64_t g = ok ? (int64_t)slots[i] * row_bytes : 0;
-      cp_async16(ks + off, kc8 + g, ok ? 16 : 0);
-      cp_async16(vs + off, vc8 + g, ok ? 16 : 0);
-    }
-  };
-
-  fetch_slots(0);
 #pragma unroll
   for (int s = 0; s < kDec8Stages - 1; ++s) {
-    if (s < ntiles) issue_tile(s);
+    if (s < ntiles) issue_tile_from(pslots[s], s);
     cp_async_commit();
-    fetch_slots(s + 1);
   }
 
   // o_acc[2c + e]: chunk c (16 output dims), e = 0: dims 16c + 4t + {0,2}, e = 1: dims 16c + 4t + {1,3}
@@ -623,12 +631,14 @@ __global__ void __launch_bounds__(kDecThreads, B200ATTN_FP8_CTAS) decode_fp8_ker
   {
     const int r0 = lane >> 2, c0 = (lane & 3) * 4;
 #pragma unroll
-    for (int c = 0; c < D / 16; ++c) {
+    for (int c = 0; c < D / 16; ++c) {  // only the gcount real q-head rows are read back
       float* dst = sm_o + (warp * 16 + r0) * D + c * 16 + c0;
-      *reinterpret_cast<float4*>(dst) =
-          make_float4(o_acc[2 * c][0], o_acc[2 * c + 1][0], o_acc[2 * c][1], o_acc[2 * c + 1][1]);
-      *reinterpret_cast<float4*>(dst + 8 * D) =
-          make_float4(o_acc[2 * c][2], o_acc[2 * c + 1][2], o_acc[2 * c][3], o_acc[2 * c + 1][3]);
+      if (r0 < gcount)
+        *reinterpret_cast<float4*>(dst) =
+            make_float4(o_acc[2 * c][0], o_acc[2 * c + 1][0], o_acc[2 * c][1], o_acc[2 * c + 1][1]);
+      if (r0 + 8 < gcount)
+        *reinterpret_cast<float4*>(dst + 8 * D) =
+            make_float4(o_acc[2 * c][2], o_acc[2 * c + 1][2], o_acc[2 * c][3], o_acc[2 * c + 1][3]);
     }
     if ((lane & 3) == 0) {
       sm_m[warp * 16 + r0] = m_run[0];
@@ -680,34 +690,55 @@ __global__ void __launch_bounds__(kDecThreads, B200ATTN_FP8_CTAS) decode_fp8_ker
   }
   if (direct) return;
   __shared__ int s_last;
-  __threadfence();
-  __syncthreads();
+  __syncthreads();  // as in decode_kernel: one thread fences on either side of the ticket
   if (tid == 0) {
     int* cnt = p.ws_cnt + (int64_t)item * (p.Hkv * p.groups_per_kvh) + hg;
+    __threadfence();
     const int ticket = atomicAdd(cnt, 1);
     s_last = (ticket == nsplit - 1);
-    if (s_last) *cnt = 0;
+    if (s_last) {
+      *cnt = 0;
+      __threadfence();
+    }
   }
   __syncthreads();
   if (!s_last) return;
-  __threadfence();
   for (int e = tid; e < gcount * (D / 4); e += kDecThreads) {
     const int r = e / (D / 4), c = (e - r * (D / 4)) * 4;
     const int h = h0 + r;
     const int64_t w0 = ((int64_t)item * p.Hq + h) * p.max_splits;
-    float m = -INFINITY;
-    for (int sp = 0; sp < nsplit; ++sp) m = fmaxf(m, __ldcg(p.ws_lse + w0 + sp));
+    float m = -INFINITY;  // one pass, four partials per L2 round trip (see decode_kernel)
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     float l = 0.f;
-    for (int sp = 0; sp < nsplit; ++sp) {
-      const float ls = __ldcg(p.ws_lse + w0 + sp);
-      const float f = (ls == -INFINITY) ? 0.f : fast_exp2(ls - m);
-      const float4 x = __ldcg(reinterpret_cast<const float4*>(p.ws_o + (w0 + sp) * D + c));
-      acc.x += f * x.x;
-      acc.y += f * x.y;
-      acc.z += f * x.z;
-      acc.w += f * x.w;
-      l += f;
+    for (int sp0 = 0; sp0 < nsplit; sp0 += 4) {
+      float ls[4];
+      float4 x[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const bool ok = sp0 + u < nsplit;
+        ls[u] = ok ? __ldcg(p.ws_lse + w0 + sp0 + u) : -INFINITY;
+        x[u] = ok ? __ldcg(reinterpret_cast<const float4*>(p.ws_o + (w0 + sp0 + u) * D + c))
+                  : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      const float mg = fmaxf(fmaxf(ls[0], ls[1]), fmaxf(ls[2], ls[3]));
+      if (mg > m) {
+        const float f0 = (m == -INFINITY) ? 0.f : fast_exp2(m - mg);
+        acc.x *= f0;
+        acc.y *= f0;
+        acc.z *= f0;
+        acc.w *= f0;
+        l *= f0;
+        m = mg;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float f = (ls[u] == -INFINITY) ? 0.f : fast_exp2(ls[u] - m);
+        acc.x += f * x[u].x;
+        acc.y += f * x[u].y;
+        acc.z += f * x[u].z;
+        acc.w += f * x[u].w;
+        l += f;
+      }
     }
     if (p.sinks != nullptr && l > 0.f) l += fast_exp2(__ldg(p.sinks + h) * kLog2e - m);
     const float inv = (l > 0.f) ? 1.f / l : 0.f;  // the partials already carry out_scale
