@@ -160,7 +160,7 @@ int b200attn_build_page_table(const int32_t* req_to_token, int64_t req_to_token_
  * waves of resident CTAs (b200attn_decode_ctas_per_sm per SM), so that only the last, partial wave is split
  * `max_splits` ways and no SM idles for a whole unit (a function of B and the head
  * counts only => graph-safe).  -1: every unit uses the length-based policy.
- * Head dims: any multiple of 8 up to 128 (rows are D wide; the kernel pads to 64 / 128 on the way into shared
+ * Head dims: any multiple of 8 up to 256 (rows are D wide; the kernel pads to 64 / 128 / 256 on the way into shared
  * memory).  `item_lens` (nullable int32[B]): item r sees only the first item_lens[r] keys of its request
  * (see b200attn_build_token_items).
  * `warps` = 4 or 2 warps per CTA (16 keys per warp and tile): 4 streams fastest per CTA (steady state,

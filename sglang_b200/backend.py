@@ -220,7 +220,7 @@ class B200AttnBackend(_Base):
     def _forward_extend_generic_head_dim(self, q2, o, layer, md, kbuf, vbuf, causal, fp8, kwargs):
         """Head dims the tcgen05 extend kernel is not instantiated for (it takes 64 and 128; the reference's kernel
         tests also sweep 96, 80, ... - test_triton_attention_kernels.py:169-322): every query TOKEN becomes one item
-        of the mma.sync decode kernel (any head dim that is a multiple of 8 up to 128) and sees its first
+        of the mma.sync decode kernel (any head dim that is a multiple of 8 up to 256) and sees its first
         prefix + j + 1 keys (all keys when not causal).  Same semantics (torch_native_backend.py:61-174), HBM-bound
         instead of tensor-core tiled: a compatibility path, not the fast one."""
         if fp8 or md.custom_mask is not None:

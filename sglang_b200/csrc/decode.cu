@@ -798,13 +798,13 @@ static int launch_decode(const DecodeParams& p, int warps, cudaStream_t st) {
 // resident CTAs per SM of the kernel b200attn_decode / b200attn_decode_fp8kv will launch (the wave arithmetic of the
 // host-side split heuristics needs it)
 extern "C" int b200attn_decode_ctas_per_sm(int kv_fp8, int warps) {
-  return kv_fp8 ? B200ATTN_FP8_CTAS : (warps == 2 ? 4 : 2);
+  return kv_fp8 ? B200ATTN_FP8_CTAS : (warps == 2 ? 4 : 2);  // head dims above 128: two (always the 2-warp kernel)
 }
 
 extern "C" int64_t b200attn_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t D,
                                                    int32_t max_splits) {
   if (max_splits <= 1) return 0;
-  D = D <= 64 ? 64 : 128;  // the kernels run on the padded head dim
+  D = D <= 64 ? 64 : (D <= 128 ? 128 : 256);  // the kernels run on the padded head dim
   // fixed-size counter header (kDecCounterBytes) + fp32 partials and their LSE
   return b200attn::kDecCounterBytes + (int64_t)B * Hq * max_splits * (D + 1) * 4;
 }
@@ -835,12 +835,13 @@ static int decode_impl(const void* q, int64_t q_stride, const void* k_cache,
   B2_CHECK_ARG((((uintptr_t)q | (uintptr_t)k_cache | (uintptr_t)v_cache | (uintptr_t)o) & 15) == 0,
                "decode: tensors must be 16-byte aligned");
   if (dtype != B200ATTN_BF16 && dtype != B200ATTN_FP16) B2_UNSUPPORTED("decode: dtype %d", dtype);
-  // 16-bit pools: any head dim that is a multiple of 8 up to 128 runs on the padded 64 / 128 instantiation
+  // 16-bit pools: any head dim that is a multiple of 8 up to 256 runs on the padded 64 / 128 / 256 instantiation
+  // (256: Gemma-style heads; 64-thread CTAs with 32-key tiles only, two per SM - the 96 KB ring sets that)
   const int Dv = D;
-  if (kv_fp8 ? (D != 64 && D != 128) : (D < 8 || D > 128 || D % 8 != 0))
-    B2_UNSUPPORTED("decode: head_dim %d (supported: multiples of 8 up to 128; e4m3 pools: 64, 128)", D);
+  if (kv_fp8 ? (D != 64 && D != 128) : (D < 8 || D > 256 || D % 8 != 0))
+    B2_UNSUPPORTED("decode: head_dim %d (supported: multiples of 8 up to 256; e4m3 pools: 64, 128)", D);
   B2_CHECK_ARG(!kv_fp8 || item_lens == nullptr, "decode: item_lens is not supported over e4m3 pools");
-  D = D <= 64 ? 64 : 128;
+  D = D <= 64 ? 64 : (D <= 128 ? 128 : 256);
   const int64_t need = b200attn_decode_workspace_bytes(B, Hq, D, max_splits);
   B2_CHECK_ARG(need == 0 || (workspace && workspace_bytes >= need),
                "decode: workspace too small (%lld < %lld)", (long long)workspace_bytes,
@@ -887,6 +888,9 @@ static int decode_impl(const void* q, int64_t q_stride, const void* k_cache,
       return dtype == B200ATTN_BF16 ? launch_decode_fp8<128, true>(p, st) : launch_decode_fp8<128, false>(p, st);
     }
     return dtype == B200ATTN_BF16 ? launch_decode_fp8<64, true>(p, st) : launch_decode_fp8<64, false>(p, st);
+  }
+  if (D == 256) {
+    return dtype == B200ATTN_BF16 ? launch_decode_nw<256, true, 2>(p, st) : launch_decode_nw<256, false, 2>(p, st);
   }
   if (D == 128) {
     return dtype == B200ATTN_BF16 ? launch_decode<128, true>(p, warps, st) : launch_decode<128, false>(p, warps, st);

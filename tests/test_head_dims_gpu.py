@@ -1,6 +1,6 @@
 """Head dims other than 64 / 128 (the reference's kernel tests sweep 256, 128, 96, 80, 13:
-test/registered/attention/test_triton_attention_kernels.py:169-322): every multiple of 8 up to 128 runs - decode on
-the padded mma.sync kernel, extend token-by-token through the same kernel (B200AttnBackend.
+test/registered/attention/test_triton_attention_kernels.py:169-322): every multiple of 8 up to 256 runs - decode on
+the padded mma.sync kernel (64 / 128 / 256 instantiations), extend token-by-token through the same kernel (B200AttnBackend.
 _forward_extend_generic_head_dim).  Parity vs the fp32 oracle at BASELINE's tolerance; the store stays bit-exact."""
 import types
 
@@ -27,7 +27,7 @@ def _backend(sc):
     return B200AttnBackend(runner, skip_padding_slot=False), kv_pool
 
 
-@pytest.mark.parametrize("D", [16, 32, 80, 96, 112])
+@pytest.mark.parametrize("D", [16, 32, 80, 96, 112, 192, 256])
 @pytest.mark.parametrize("Hq,Hkv,page", [(8, 2, 16), (14, 2, 1)])
 def test_decode_generic_head_dim(D, Hq, Hkv, page):
     lens = [1, 17, 64, 65, 300, 1500, 4096]
@@ -59,7 +59,7 @@ def test_decode_generic_head_dim(D, Hq, Hkv, page):
         assert_close_attn(o2.view(B, -1), ref, f"decode D={D} 8 splits warps={warps}")
 
 
-@pytest.mark.parametrize("D", [80, 96, 32])
+@pytest.mark.parametrize("D", [80, 96, 32, 256])
 @pytest.mark.parametrize("causal", [True, False])
 def test_extend_generic_head_dim(D, causal):
     prefix, ext = [0, 130, 33, 500], [70, 129, 1, 300]

@@ -9,7 +9,7 @@ ForwardContext, q/k/v from real nn.Linear projections, expected output from the 
 entry point INTEGRATION.md describes — and runs
 
   * make_dense_cases("b200") x {contiguous, shuffled_pages, interleaved_pages, non_monotonic_extend}
-    at head_dim 128, 64 and the kit's own default 16;
+    at head_dim 128, 64, 256 and the kit's own default 16;
   * the kit's sliding-window cases (dense_attention.py:212-260) — plain pool, layer.sliding_window_size;
   * the CUDA-graph decode runner mode (runner_modes/cuda_graph_decode_runner.py: capture-bucket 4, padded replay,
     metadata invariants) and the EAGLE TARGET_VERIFY mode (speculative_target_verify_runner.py, chain + tree masks).
@@ -90,7 +90,7 @@ def main() -> int:
             traceback.print_exc()
 
     layouts = ("contiguous", "shuffled_pages", "interleaved_pages", "non_monotonic_extend")
-    for hd in (128, 64, 16):  # 16 = the kit's own DEFAULT_HEAD_DIM (generic-head-dim path of the backend)
+    for hd in (128, 64, 16, 256):  # 256 = Gemma-style heads; 16 = the kit's own DEFAULT_HEAD_DIM (generic-head-dim path of the backend)
         kw = dict(head_dim=hd, hidden_size=64, device="cuda", dtype=torch.float16)
         for case in da.make_dense_cases("b200"):
             for layout in layouts:
@@ -112,8 +112,8 @@ def main() -> int:
             case = da.DenseAttentionCase(name=name, backend="b200", forward_mode=ForwardMode.DECODE, num_heads=heads,
                                          num_kv_heads=kvh, page_size=16, prefix_lens=pre)
             run(f"cuda_graph_decode/{name}/d{hd}", lambda c=case: dec.run_dense_cuda_graph_decode_case(tc, c, **kw))
-        if hd == 16:
-            continue  # tree masks are not built on the generic-head-dim path
+        if hd not in (64, 128):
+            continue  # tree masks need the tcgen05 extend kernel (64 / 128): the generic-head-dim path raises
         for name, topk, nd, pre in (("verify_chain", 1, 4, (4, 7, 30)), ("verify_tree", 2, 3, (4, 7))):
             case = da.DenseAttentionCase(name=name, backend="b200", forward_mode=ForwardMode.TARGET_VERIFY,
                                          num_heads=4, num_kv_heads=4, page_size=16, prefix_lens=pre,
