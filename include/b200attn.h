@@ -104,6 +104,14 @@ int b200attn_build_kv_indices(const int32_t* req_to_token, int64_t req_to_token_
                               int32_t* qo_indptr, const void* slot_map, int slot_map_dtype,
                               void* stream);
 
+/* Host <-> device staging by a kernel: dst0[0:bytes0] = src0, dst1[0:bytes1] = src1 in ONE launch (either segment
+ * may be empty).  Either side of a segment may be PINNED HOST memory (mapped under UVA): this is how a step driven
+ * from host buffers inside a CUDA graph refills its static device buffers and returns its result without memcpy
+ * nodes - the role of the buffer refills in python/sglang/srt/model_executor/cuda_graph_runner.py (replay_prepare)
+ * and runner_utils/buffers.py.  16-byte aligned buffers, sizes multiples of 16. */
+int b200attn_stage_copy(void* dst0, const void* src0, int64_t bytes0, void* dst1, const void* src1,
+                        int64_t bytes1, void* stream);
+
 /* out[i] = slot_map[loc[i]] (int64 out): KVWriteLoc.swa_loc of a hybrid sliding-window pool,
  *   python/sglang/srt/mem_cache/memory_pool.py:1550-1590, swa_memory_pool.py:228-231,
  *   triton_backend.py:978-982. */

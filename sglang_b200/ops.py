@@ -439,6 +439,30 @@ def build_kv_indices(
     check(rc, "b200attn_build_kv_indices")
 
 
+def stage_copy(dst: torch.Tensor, src: torch.Tensor, dst1: Optional[torch.Tensor] = None,
+               src1: Optional[torch.Tensor] = None) -> None:
+    """``dst[...] = src`` (and ``dst1[...] = src1``) by ONE kernel launch on the current stream.  Each tensor is a
+    contiguous CUDA tensor or a contiguous PINNED host tensor (mapped into the device address space): the kernel
+    reads / writes host memory itself, so a CUDA graph of a host-driven step holds no memcpy nodes
+    (csrc/stage.cu; the buffer refills of cuda_graph_runner.py replay_prepare)."""
+    segs = []
+    for d, s_ in ((dst, src), (dst1, src1)):
+        if d is None:
+            segs += [0, 0, 0]
+            continue
+        for t in (d, s_):
+            if not (t.is_cuda or t.is_pinned()):
+                raise RuntimeError("b200attn.stage_copy: tensors must be CUDA or pinned host tensors (no CPU fallback)")
+            if not t.is_contiguous():
+                raise RuntimeError("b200attn.stage_copy: tensors must be contiguous")
+        nb = d.numel() * d.element_size()
+        if nb != s_.numel() * s_.element_size():
+            raise RuntimeError("b200attn.stage_copy: size mismatch")
+        segs += [d.data_ptr(), s_.data_ptr(), nb]
+    rc = _lib.load().b200attn_stage_copy(*segs, _stream())
+    check(rc, "b200attn_stage_copy")
+
+
 def translate_slots(loc: torch.Tensor, slot_map: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``slot_map[loc]`` as int64: ``KVWriteLoc.swa_loc`` of a hybrid sliding-window pool
     (``SWAKVPool.translate_loc_from_full_to_swa``, swa_memory_pool.py:228-231)."""
