@@ -112,6 +112,27 @@ int b200attn_build_kv_indices(const int32_t* req_to_token, int64_t req_to_token_
 int b200attn_stage_copy(void* dst0, const void* src0, int64_t bytes0, void* dst1, const void* src1,
                         int64_t bytes1, void* stream);
 
+/* --------------------------------------------------------------------------
+ * (f4) The collective after attention: sum all-reduce of the o_proj output over NVLS (in-switch reduction), one
+ * launch per rank.  Replaces GroupCoordinator.all_reduce for this message
+ * (python/sglang/srt/distributed/parallel_state.py:648-757) the way the reference's symmetric-memory communicator
+ * does (device_communicators/torch_symm_mem.py:34-200: copy in, torch's multimem op, copy out = three launches).
+ *   local_payload / mc_payload: this rank's instance and the MULTICAST address of the same symmetric allocation
+ *   (torch.distributed._symmetric_memory: buffer_ptrs[rank] / multicast_ptr, plus the payload offset);
+ *   flag_ptrs: HOST array of `world` device pointers, flag_ptrs[r] = rank r's flag block as mapped on THIS rank
+ *   (b200attn_allreduce_flag_bytes() bytes each, zeroed once; self-resetting);
+ *   in / out: local tensors staged into / out of the payload by the same kernel; either may be null (the producer
+ *   wrote the payload itself / the consumer reads it).  bytes % 16 == 0, dtype BF16 / FP16 / FP32.
+ *   local_small / mc_small (nullable): a second region of b200attn_allreduce_small_bytes() bytes in the same
+ *   symmetric allocation; with it, messages up to 1 MB (and bytes * world <= 4 MB) with both `in` and `out` take the
+ *   one-shot form: stage-in, ONE barrier, every rank reduces the whole message through the switch into `out`.
+ * Every rank of the group must launch it with the same arguments' shape; at most 128 CTAs, all co-resident. */
+int64_t b200attn_allreduce_flag_bytes(void);
+int64_t b200attn_allreduce_small_bytes(void);
+int b200attn_allreduce_nvls(const void* in, void* out, void* local_payload, void* mc_payload, void* local_small,
+                            void* mc_small, void* const* flag_ptrs, int32_t rank, int32_t world, int64_t bytes,
+                            int dtype, void* stream);
+
 /* out[i] = slot_map[loc[i]] (int64 out): KVWriteLoc.swa_loc of a hybrid sliding-window pool,
  *   python/sglang/srt/mem_cache/memory_pool.py:1550-1590, swa_memory_pool.py:228-231,
  *   triton_backend.py:978-982. */

@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200attn.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "b200attn.h")
 
-ABI_VERSION = 18  # b200attn_abi_version() of the library this binding matches (api.cu)
+ABI_VERSION = 19  # b200attn_abi_version() of the library this binding matches (api.cu)
 BF16, FP16, FP32 = 0, 1, 2
 I32, I64 = 0, 1
 
@@ -45,6 +45,9 @@ SIGNATURES = {
     ),
     "b200attn_translate_slots": (C.c_int, [_vp, C.c_int, _vp, C.c_int, _i64, _vp, _vp]),
     "b200attn_stage_copy": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, _vp]),
+    "b200attn_allreduce_flag_bytes": (_i64, []),
+    "b200attn_allreduce_small_bytes": (_i64, []),
+    "b200attn_allreduce_nvls": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i64, C.c_int, _vp]),
     "b200attn_build_page_table": (
         C.c_int,
         [_vp, _i64, _vp, C.c_int, _vp, C.c_int, _i32, _i32, _vp, _i64, _i32, _vp],
