@@ -225,6 +225,26 @@ int b200attn_decode(const void* q, int64_t q_stride, const void* k_cache,
                     int32_t window_left, float logit_cap, const float* sinks,
                     const int32_t* item_lens, void* workspace, int64_t workspace_bytes, void* stream);
 
+/* b200attn_decode without a caller workspace and without any device allocation.  NO COUNTERPART IN THE REFERENCE:
+ * added for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Same arguments and results as b200attn_decode minus
+ * `workspace` / `workspace_bytes`: the split-KV scratch is a file-scope `static __device__` array inside the library,
+ * b200attn_decode_noalloc_max_workspace_bytes() = 256 KiB of counters + 8 MiB of partials, resident on every GPU
+ * that loads the library until the process exits.  Shapes whose b200attn_decode_workspace_bytes(B, Hq, D,
+ * max_splits) exceeds it are rejected with B200ATTN_ERR_INVALID and a message that says so (max_splits = 1 always
+ * fits: it needs no scratch).  The entry point calls no cudaMalloc / cudaFree / allocating routine; it clears the
+ * arrival counters it will use on `stream` before the launch.  All calls share the one array: calls that OVERLAP
+ * on the GPU (different streams, graphs in flight at the same time) race on it - serialise them, or use
+ * b200attn_decode with a workspace per stream. */
+int64_t b200attn_decode_noalloc_max_workspace_bytes(void);
+int b200attn_decode_noalloc(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache,
+                            int64_t kv_stride, void* o, int64_t o_stride, float* lse,
+                            const int32_t* kv_indptr, const int32_t* kv_indices, const int32_t* q_rows,
+                            const int32_t* req_ids, int32_t B, int32_t Hq, int32_t Hkv, int32_t D, int dtype,
+                            float sm_scale, int32_t max_splits, int32_t min_chunk, int32_t tail_begin,
+                            int32_t warps, int32_t window_left, float logit_cap, const float* sinks,
+                            const int32_t* item_lens, void* stream);
+
 /* --------------------------------------------------------------------------
  * (a4) Decode, flat tile-stream scheduling.  Same contract and arithmetic as
  * b200attn_decode (16-bit pools), but the batch is ONE stream of 64-key tiles cut

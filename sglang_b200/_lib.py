@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200attn.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "b200attn.h")
 
-ABI_VERSION = 19  # b200attn_abi_version() of the library this binding matches (api.cu)
+ABI_VERSION = 20  # b200attn_abi_version() of the library this binding matches (api.cu)
 BF16, FP16, FP32 = 0, 1, 2
 I32, I64 = 0, 1
 
@@ -54,6 +54,12 @@ SIGNATURES = {
     ),
     "b200attn_decode_workspace_bytes": (_i64, [_i32, _i32, _i32, _i32]),
     "b200attn_decode_ctas_per_sm": (C.c_int, [C.c_int, C.c_int]),
+    "b200attn_decode_noalloc_max_workspace_bytes": (_i64, []),
+    "b200attn_decode_noalloc": (
+        C.c_int,
+        [_vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, C.c_int, C.c_float,
+         _i32, _i32, _i32, _i32, _i32, C.c_float, _vp, _vp, _vp],
+    ),
     "b200attn_decode": (
         C.c_int,
         [_vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, C.c_int,

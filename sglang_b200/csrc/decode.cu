@@ -19,6 +19,7 @@
 //
 // Algorithmic bytes per (request, kv head): 2 * L * D * sizeof(T) (K and V rows)
 // + 4 * L (int32 slot ids).
+#include <mutex>
 #include "decode.cuh"
 
 namespace b200attn {
@@ -927,6 +928,72 @@ extern "C" int b200attn_decode_fp8kv(const void* q, int64_t q_stride, const void
                      q_rows, req_ids, B, Hq, Hkv, D, dtype, sm_scale, max_splits, min_chunk, tail_begin,
                      window_left, logit_cap, sinks, workspace, workspace_bytes, stream, true, k_descale,
                      v_descale);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// b200attn_decode_noalloc: b200attn_decode for callers that cannot allocate device memory (CUDA graph capture, tight
+// serving loops, harnesses that forbid it).  No counterpart in the reference.
+// The split-KV workspace (arrival counters + fp32 partials) is this file-scope device array instead of a
+// caller buffer: kDecStaticWsBytes per GPU that loads the library, held until the process exits.
+//   * In HOST code the array's name is only a stand-in for the symbol, not a device address: the address is asked
+//     for once per device, with that device current, through cudaGetSymbolAddress and cached.
+//   * Every call shares the array and finds the previous call's partials in it; the arrival counters of the units
+//     of this call are cleared on the stream before the launch (they must start at zero).  Calls that OVERLAP on
+//     the GPU (two streams, two graphs in flight) race on it: serialise them or use b200attn_decode.
+//   * Nothing here calls cudaMalloc / cudaFree or any allocating routine.
+namespace b200attn {
+constexpr int64_t kDecStaticPartialBytes = 8ll << 20;  // fp32 partials + LSE: B * Hq * max_splits * (Dpad + 1) * 4 <= 8 MiB
+constexpr int64_t kDecStaticWsBytes = kDecCounterBytes + kDecStaticPartialBytes;
+static __device__ __align__(256) unsigned char g_dec_static_ws[kDecStaticWsBytes];
+
+constexpr int kMaxDevices = 64;
+static std::mutex g_static_ws_mu;
+static void* g_static_ws_ptr[kMaxDevices] = {};  // device address of g_dec_static_ws on device i, 0 = not asked yet
+
+static int static_ws_address(void** out) {
+  int dev = 0;
+  B2_CUDA(cudaGetDevice(&dev));
+  B2_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "decode_noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_ws_mu);
+  if (g_static_ws_ptr[dev] == nullptr) {
+    void* ptr = nullptr;
+    B2_CUDA(cudaGetSymbolAddress(&ptr, g_dec_static_ws));  // the current device's instance
+    g_static_ws_ptr[dev] = ptr;
+  }
+  *out = g_static_ws_ptr[dev];
+  return B200ATTN_OK;
+}
+}  // namespace b200attn
+
+extern "C" int64_t b200attn_decode_noalloc_max_workspace_bytes(void) { return b200attn::kDecStaticWsBytes; }
+
+extern "C" int b200attn_decode_noalloc(const void* q, int64_t q_stride, const void* k_cache, const void* v_cache,
+                                       int64_t kv_stride, void* o, int64_t o_stride, float* lse,
+                                       const int32_t* kv_indptr, const int32_t* kv_indices, const int32_t* q_rows,
+                                       const int32_t* req_ids, int32_t B, int32_t Hq, int32_t Hkv, int32_t D,
+                                       int dtype, float sm_scale, int32_t max_splits, int32_t min_chunk,
+                                       int32_t tail_begin, int32_t warps, int32_t window_left, float logit_cap,
+                                       const float* sinks, const int32_t* item_lens, void* stream) {
+  using namespace b200attn;
+  B2_CHECK_ARG(B >= 0 && Hq > 0 && Hkv > 0 && D > 0 && max_splits >= 1, "decode_noalloc: bad shape");
+  const int64_t need = b200attn_decode_workspace_bytes(B, Hq, D, max_splits);
+  B2_CHECK_ARG(need <= kDecStaticWsBytes,
+               "decode_noalloc: this shape needs a %lld-byte split workspace, the built-in one holds %lld "
+               "(B * Hq * max_splits * (head_dim padded to 64/128/256 + 1) * 4 <= %lld): lower max_splits or call "
+               "b200attn_decode with a caller workspace",
+               (long long)need, (long long)kDecStaticWsBytes, (long long)kDecStaticPartialBytes);
+  void* ws = nullptr;
+  if (need > 0) {
+    const int rc = static_ws_address(&ws);
+    if (rc != B200ATTN_OK) return rc;
+    // the counters this launch will use start at zero whatever an earlier (possibly aborted) call left behind
+    const int64_t units = (int64_t)B * Hkv * ((Hq / Hkv + kDecMaxG - 1) / kDecMaxG);
+    B2_CHECK_ARG(units <= kDecMaxUnits, "decode_noalloc: more than %d units with max_splits > 1", kDecMaxUnits);
+    B2_CUDA(cudaMemsetAsync(ws, 0, (size_t)units * sizeof(int), (cudaStream_t)stream));
+  }
+  return decode_impl(q, q_stride, k_cache, v_cache, kv_stride, o, o_stride, lse, kv_indptr, kv_indices, q_rows,
+                     req_ids, B, Hq, Hkv, D, dtype, sm_scale, max_splits, min_chunk, tail_begin, window_left,
+                     logit_cap, sinks, ws, need > 0 ? kDecStaticWsBytes : 0, stream, false, 1.f, 1.f, warps, item_lens);
 }
 
 #ifdef DEC_TRACE
