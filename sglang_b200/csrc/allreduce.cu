@@ -28,9 +28,23 @@ namespace b200attn {
 constexpr int kArMaxBlocks = 128;
 constexpr int kArMaxWorld = 16;
 constexpr int kArThreads = 512;
+constexpr int kArUnroll = 8;  // 16-byte accesses in flight per thread
 constexpr int64_t kArPiece = 32768;                   // one-shot: bytes per CTA, fixed (piece b is always CTA b's)
 constexpr int64_t kArSmallHalf = kArMaxBlocks * kArPiece;  // 4 MB
 constexpr int64_t kArSmallMax = 1 << 20;              // largest message that takes the one-shot form
+
+#ifdef AR_TRACE
+// dev-only (libb200attn_trace.so, tools/allreduce_nvls_check.py --trace): globaltimer stamps per CTA and phase
+__device__ long long g_ar_trace[kArMaxBlocks * 8];
+#define ATRACE(slot)                                                     \
+  if (threadIdx.x == 0) {                                                \
+    long long gt_;                                                       \
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_));              \
+    g_ar_trace[blockIdx.x * 8 + (slot)] = gt_;                           \
+  }
+#else
+#define ATRACE(slot)
+#endif
 
 struct ArParams {
   const uint4* in;    // local input or null (the caller wrote the payload itself, e.g. as a GEMM output)
@@ -93,13 +107,13 @@ __device__ __forceinline__ void mc_st(uint4* addr, const uint4& v) {
 }
 
 __device__ __forceinline__ void ar_copy(uint4* dst, const uint4* src, int64_t c0, int64_t c1) {
-  for (int64_t i = c0 + threadIdx.x; i < c1; i += 4 * kArThreads) {
-    uint4 v[4];
+  for (int64_t i = c0 + threadIdx.x; i < c1; i += kArUnroll * kArThreads) {
+    uint4 v[kArUnroll];
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
+    for (int u = 0; u < kArUnroll; ++u)
       if (i + u * kArThreads < c1) v[u] = src[i + u * kArThreads];
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
+    for (int u = 0; u < kArUnroll; ++u)
       if (i + u * kArThreads < c1) dst[i + u * kArThreads] = v[u];
   }
 }
@@ -112,28 +126,34 @@ __global__ void __launch_bounds__(kArThreads) allreduce_nvls_kernel(const ArPara
   const int64_t c0 = (int64_t)blockIdx.x * per_block;
   const int64_t c1 = c0 + per_block < p.n16 ? c0 + per_block : p.n16;
   // A: stage the input
+  ATRACE(0);
   if (p.in != nullptr) ar_copy(p.local, p.in, c0, c1);
+  ATRACE(1);
   ar_barrier(p);
+  ATRACE(2);
   // B: this rank's share of the chunk, reduced in the switch and written to every instance
   {
     const int64_t n = c1 > c0 ? c1 - c0 : 0;
     const int64_t per_rank = (n + p.world - 1) / p.world;
     const int64_t s0 = c0 + p.rank * per_rank;
     const int64_t s1 = s0 + per_rank < c1 ? s0 + per_rank : c1;
-    // four reductions in flight per thread before the first store (an NVSwitch round trip is ~2 us)
-    for (int64_t i = s0 + threadIdx.x; i < s1; i += 4 * kArThreads) {
-      uint4 v[4];
+    // kArUnroll reductions in flight per thread before the first store (an NVSwitch round trip is ~2 us)
+    for (int64_t i = s0 + threadIdx.x; i < s1; i += kArUnroll * kArThreads) {
+      uint4 v[kArUnroll];
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
+      for (int u = 0; u < kArUnroll; ++u)
         if (i + u * kArThreads < s1) v[u] = mc_ld_reduce<kDtype>(p.mc + i + u * kArThreads);
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
+      for (int u = 0; u < kArUnroll; ++u)
         if (i + u * kArThreads < s1) mc_st(p.mc + i + u * kArThreads, v[u]);
     }
   }
+  ATRACE(3);
   ar_barrier(p);
+  ATRACE(4);
   // C: hand the result over
   if (p.out != nullptr) ar_copy(p.out, p.local, c0, c1);
+  ATRACE(5);
 }
 
 template <int kDtype>
@@ -154,13 +174,13 @@ __global__ void __launch_bounds__(kArThreads) allreduce_nvls_oneshot_kernel(cons
   const int64_t off = (int64_t)s_half * (kArSmallHalf / 16);
   ar_copy(p.small_local + off, p.in, c0, c1);  // same index in the input and in the half
   ar_barrier(p);
-  for (int64_t i = c0 + threadIdx.x; i < c1; i += 4 * kArThreads) {
-    uint4 v[4];
+  for (int64_t i = c0 + threadIdx.x; i < c1; i += kArUnroll * kArThreads) {
+    uint4 v[kArUnroll];
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
+    for (int u = 0; u < kArUnroll; ++u)
       if (i + u * kArThreads < c1) v[u] = mc_ld_reduce<kDtype>(p.small_mc + off + i + u * kArThreads);
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
+    for (int u = 0; u < kArUnroll; ++u)
       if (i + u * kArThreads < c1) p.out[i + u * kArThreads] = v[u];
   }
 }
@@ -229,3 +249,9 @@ extern "C" int b200attn_allreduce_nvls(const void* in, void* out, void* local_pa
   }
   return B200ATTN_OK;
 }
+
+#ifdef AR_TRACE
+extern "C" int b200attn_allreduce_trace_read(void* dst_host, int64_t bytes) {
+  return cudaMemcpyFromSymbol(dst_host, b200attn::g_ar_trace, (size_t)bytes) == cudaSuccess ? 0 : 1;
+}
+#endif

@@ -9,7 +9,12 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import torch.distributed as dist
 
-from sglang_b200.collective import NvlsAllReduce
+from sglang_b200 import _lib
+
+TRACE = "--trace" in sys.argv
+if TRACE:
+    _lib.LIB_PATH = os.path.join(os.path.dirname(_lib.LIB_PATH), "libb200attn_trace.so")
+from sglang_b200.collective import NvlsAllReduce  # noqa: E402
 
 
 def timed(fn, n=20, reps=5, warm=3):
@@ -54,6 +59,30 @@ def main():
         return
     ok = True
     g = torch.Generator(device="cuda").manual_seed(1234 + rank)
+    if TRACE:  # per-phase times of the two-shot kernel (stage-in, barrier, switch reduce + store, barrier, stage-out)
+        import ctypes
+
+        lib = ctypes.CDLL(_lib.LIB_PATH)
+        for shape in ((2048, 4096), (8192, 4096)):
+            x = torch.randn(shape, device=dev, generator=g).to(torch.bfloat16)
+            out = torch.empty_like(x)
+            for _ in range(5):
+                comm.all_reduce(x, out=out)
+            torch.cuda.synchronize()
+            dist.barrier()
+            comm.all_reduce(x, out=out)
+            torch.cuda.synchronize()
+            buf = (ctypes.c_longlong * (128 * 8))()
+            assert lib.b200attn_allreduce_trace_read(buf, ctypes.c_int64(128 * 8 * 8)) == 0
+            t = torch.tensor(list(buf), dtype=torch.float64).view(128, 8)[:, :6]
+            t = (t - t[:, 0].min()) / 1e3
+            if rank == 0:
+                names = ["start", "staged", "barrier1", "reduced", "barrier2", "done"]
+                print(f"two-shot {shape} bf16, rank 0, us since first CTA start (median / max over 128 CTAs):", flush=True)
+                for k, nm in enumerate(names):
+                    print(f"  {nm:9s} {float(t[:, k].median()):8.2f} {float(t[:, k].max()):8.2f}", flush=True)
+        dist.destroy_process_group()
+        return
     # ---- results: integers in bf16 / fp16 / fp32 sum exactly, random values within rounding of the NCCL result ----
     for dtype in (torch.bfloat16, torch.float16, torch.float32):
         for numel in (8, 4096, 64 * 4096, 1000 * 1000 + 8, 8 << 20):
