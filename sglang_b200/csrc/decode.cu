@@ -43,7 +43,17 @@ __device__ long long g_dec_trace[8 * 16384];
 #define DTRACE(slot)
 #endif
 
-template <int D, bool kBf16, int NW>
+// kCluster: the max_splits CTAs of a unit form ONE thread-block cluster (cluster dim x = grid dim x = 2 / 4) and
+// the split merge goes through distributed shared memory: every CTA stores its normalised partial into the leader's
+// (split 0) shared memory with st.shared::cluster, one cluster barrier, the leader merges and writes the output.  No
+// global partials, no device-scope fence, no ticket atomic, no L2 round trip: ~2 us off a split decode
+// (B=16 x 4096: 48.7 -> 47.2 us).  Two cluster barriers per CTA: #1 "my K/V ring is dead" (the partial region of
+// the leader overlaps its ring), #2 "my partial is in the leader's memory".
+constexpr int kDecClusterMax = 8;
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory"); }
+
+template <int D, bool kBf16, int NW, bool kCluster = false>
 __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const DecodeParams p) {
   constexpr int kDecTile = 16 * NW;     // shadows the 4-warp constants of decode.cuh
   constexpr int kDecThreads = 32 * NW;
@@ -77,7 +87,15 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
   }
   int nsplit, chunk;
   split_policy(L, unit_max_splits(p, item, hg), p.min_chunk, kDecTile, nsplit, chunk);
-  if (split >= nsplit) return;
+  if (split >= nsplit) {
+    if constexpr (kCluster) {  // nothing to do for this unit, but the cluster's barriers count every CTA
+      cluster_arrive();
+      cluster_wait();
+      cluster_arrive();
+      cluster_wait();
+    }
+    return;
+  }
   const int k_lo = split * chunk;
   const int k_hi = min(L, k_lo + chunk);
   const int ntiles = (k_hi - k_lo + kDecTile - 1) / kDecTile;
@@ -247,6 +265,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
   }
   cp_async_wait<0>();
   __syncthreads();  // ring is dead; reuse it for the cross-warp merge
+  if constexpr (kCluster) cluster_arrive();  // #1
   DTRACE(4);
 
   // ---- merge the four warps (fp32, shared memory) ---------------------------
@@ -282,6 +301,13 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
   }
   __syncthreads();
   const bool direct = (nsplit == 1);
+  // leader's partial region: [kDecClusterMax][16][D] fp32 + [kDecClusterMax][16] LSE, after the local merge scratch
+  constexpr uint32_t kClOff = (NW * 16 * D + 2 * NW * 16) * 4;
+  uint32_t cl_base = 0;
+  if constexpr (kCluster) {
+    cluster_wait();  // #1: every ring of the cluster is dead, the leader's memory may be written
+    asm volatile("mapa.shared::cluster.u32 %0, %1, 0;\n" : "=r"(cl_base) : "r"(smem_base + kClOff));
+  }
   for (int e = tid; e < gcount * (D / 4); e += kDecThreads) {
     const int r = e / (D / 4), c = (e - r * (D / 4)) * 4;
     float m = -INFINITY;
@@ -315,6 +341,14 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
       pk.y = pack2<kBf16>(acc.z, acc.w);
       if (c < Dv) *reinterpret_cast<uint2*>(dst) = pk;
       if (p.lse != nullptr && c == 0) p.lse[(int64_t)qrow * p.Hq + h] = lse2 * kLn2;
+    } else if constexpr (kCluster) {
+      const uint32_t dst = cl_base + (uint32_t)(((split * 16 + r) * D + c) * 4);
+      asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};\n" ::"r"(dst), "f"(acc.x), "f"(acc.y),
+                   "f"(acc.z), "f"(acc.w) : "memory");
+      if (c == 0)
+        asm volatile("st.shared::cluster.f32 [%0], %1;\n" ::"r"(cl_base + (uint32_t)((kDecClusterMax * 16 * D +
+                                                                                     split * 16 + r) * 4)),
+                     "f"(lse2) : "memory");
     } else {
       const int64_t w = ((int64_t)item * p.Hq + h) * p.max_splits + split;
       *reinterpret_cast<float4*>(p.ws_o + w * D + c) = acc;
@@ -322,6 +356,43 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
     }
   }
   DTRACE(5);
+  if constexpr (kCluster) {
+    cluster_arrive();  // #2 (release: the partial stores above)
+    cluster_wait();
+    DTRACE(6);
+    if (direct || split != 0) return;
+    const float* cl_o = reinterpret_cast<const float*>(smem + kClOff);
+    const float* cl_lse = cl_o + kDecClusterMax * 16 * D;
+    for (int e = tid; e < gcount * (D / 4); e += kDecThreads) {
+      const int r = e / (D / 4), c = (e - r * (D / 4)) * 4;
+      const int h = h0 + r;
+      float m = -INFINITY;
+      for (int sp = 0; sp < nsplit; ++sp) m = fmaxf(m, cl_lse[sp * 16 + r]);
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      float l = 0.f;
+      for (int sp = 0; sp < nsplit; ++sp) {
+        const float ls = cl_lse[sp * 16 + r];
+        const float f = (ls == -INFINITY) ? 0.f : fast_exp2(ls - m);
+        const float4 x = *reinterpret_cast<const float4*>(cl_o + (sp * 16 + r) * D + c);
+        acc.x += f * x.x;
+        acc.y += f * x.y;
+        acc.z += f * x.z;
+        acc.w += f * x.w;
+        l += f;
+      }
+      if (p.sinks != nullptr && l > 0.f) l += fast_exp2(__ldg(p.sinks + h) * kLog2e - m);
+      const float inv = (l > 0.f) ? 1.f / l : 0.f;
+      T* dst = reinterpret_cast<T*>(p.o) + (int64_t)qrow * p.o_stride + (int64_t)h * Dv + c;
+      uint2 pk;
+      pk.x = pack2<kBf16>(acc.x * inv, acc.y * inv);
+      pk.y = pack2<kBf16>(acc.z * inv, acc.w * inv);
+      if (c < Dv) *reinterpret_cast<uint2*>(dst) = pk;
+      if (p.lse != nullptr && c == 0)
+        p.lse[(int64_t)qrow * p.Hq + h] = (l > 0.f) ? (m + log2f(l)) * kLn2 : -INFINITY;
+    }
+    DTRACE(7);
+    return;
+  }
   if (direct) return;
   // ---- split merge by the LAST CTA of the unit to arrive (no second launch) ----
   // writers: partials -> fence -> barrier -> one relaxed atomic ticket; the CTA that draws the last ticket sees
@@ -789,8 +860,49 @@ static int launch_decode_nw(const DecodeParams& p, cudaStream_t st) {
   return B200ATTN_OK;
 }
 
+// 4-warp kernel with the split merge through cluster shared memory.  Used for max_splits = 2 / 4 (measured, same
+// process A/B with B200ATTN_DEC_CLUSTER=0: B=16 x 4096 48.7 -> 47.2 us, B=8 x 8192 48.4 -> 47.1 us); clusters of 8 are
+// SLOWER than the workspace path (52.2 -> 60.5 us): the scheduler packs a cluster's CTAs two per SM inside one GPC
+// and leaves other SMs empty, and a lightly loaded grid is bound by per-SM load bandwidth.
+template <int D, bool kBf16>
+static int launch_decode_cluster(const DecodeParams& p, cudaStream_t st) {
+  constexpr int NW = 4;
+  constexpr int kRing = kDecStages * 2 * (16 * NW) * D * 2;
+  constexpr int kMerge = (NW * 16 * D + 2 * NW * 16) * 4 + (kDecClusterMax * 16 * D + kDecClusterMax * 16) * 4;
+  constexpr int kSmem = kRing > kMerge ? kRing : kMerge;
+  static bool configured = false;
+  if (!configured) {
+    B2_CUDA(cudaFuncSetAttribute(decode_kernel<D, kBf16, NW, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+    B2_CUDA(cudaFuncSetAttribute(decode_kernel<D, kBf16, NW, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    configured = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)p.max_splits, (unsigned)(p.Hkv * p.groups_per_kvh), (unsigned)p.B);
+  cfg.blockDim = dim3(32 * NW);
+  cfg.dynamicSmemBytes = kSmem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  attr[1].id = cudaLaunchAttributeClusterDimension;
+  attr[1].val.clusterDim.x = (unsigned)p.max_splits;
+  attr[1].val.clusterDim.y = 1;
+  attr[1].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 2;
+  B2_CUDA(cudaLaunchKernelEx(&cfg, decode_kernel<D, kBf16, NW, true>, p));
+  return B200ATTN_OK;
+}
+
+static bool decode_cluster_enabled() {
+  static const bool on = [] { const char* e = getenv("B200ATTN_DEC_CLUSTER"); return e == nullptr || atoi(e) != 0; }();
+  return on;
+}
+
 template <int D, bool kBf16>
 static int launch_decode(const DecodeParams& p, int warps, cudaStream_t st) {
+  if (warps == 4 && (p.max_splits == 2 || p.max_splits == 4) && decode_cluster_enabled())
+    return launch_decode_cluster<D, kBf16>(p, st);
   return warps == 2 ? launch_decode_nw<D, kBf16, 2>(p, st) : launch_decode_nw<D, kBf16, 4>(p, st);
 }
 
