@@ -526,10 +526,10 @@ def run_b200(args, rank, world, local_rank):
         # configs[1] again over a float8_e4m3fn pool: half the KV bytes per call
         extra["cfg2_decode_fp8kv"] = run_cfg2_decode_fp8(dev, gen, peaks)
         torch.cuda.empty_cache()
-        # configs[2] over the e4m3 pool: quantising store + dequantising gather + extend per layer-call
+        # configs[2] over the e4m3 pool: quantising store + extend on the pool's e4m3 bytes per layer-call
         extra["cfg3_extend_fp8kv"] = run_backend_case(
             dev, gen, peaks, "llama-3.1-8b extend over a float8_e4m3fn KV pool: 32 req x (2048 shared prefix + 512 new), "
-            "causal; layer-call = quantising store + dequantising gather (32 x 2560 rows) + extend",
+            "causal; layer-call = quantising store + extend contracting on the pool's e4m3 bytes (kind::f8f6f4)",
             [2048] * 32, [512] * 32, 32, 8, 128, 16, True, "EXTEND", shared_prefix=2048, fp8_kv=True)
         torch.cuda.empty_cache()
         # configs[4]: Llama-3.1-70B attention shape, this rank's KV-head shard

@@ -414,6 +414,23 @@ int b200attn_extend(const void* q, int64_t q_stride, const void* k_cache,
                     int mask_skip_prefix, void* workspace, int64_t workspace_bytes,
                     void* stream);
 
+/* Extend over a float8_e4m3fn KV pool (memory_pool.py:2365-2375), in the kernel: k_cache / v_cache point at e4m3
+ * bytes, `kv_stride_bytes` is the byte stride between slots.  What the reference's Triton kernels compute for such
+ * a pool (extend_attention.py:523 `tl.dot(q.to(k.dtype), k)`, :596 `p = p.to(v.dtype)`; k / v descales as in
+ * triton_backend.py:1418-1420): Q is cast to e4m3 in shared memory, P to e4m3 in tensor memory, both contractions
+ * run as tcgen05.mma.kind::f8f6f4 on the pool's bytes, k_descale rides on the softmax scale and v_descale on the
+ * output.  head_dim 128; q / o stay bf16 / fp16 (`dtype`).  Everything else as b200attn_extend. */
+int b200attn_extend_fp8kv(const void* q, int64_t q_stride, const void* k_cache,
+                          const void* v_cache, int64_t kv_stride_bytes, int64_t num_slots,
+                          void* o, int64_t o_stride, float* lse, const int32_t* qo_indptr,
+                          const int32_t* kv_indptr, const int32_t* kv_indices, int32_t B,
+                          int64_t total_q_host, int32_t max_qo_len_host, int32_t Hq,
+                          int32_t Hkv, int32_t D, int32_t page_size, int dtype, int causal,
+                          float sm_scale, float k_descale, float v_descale, int32_t window_left,
+                          float logit_cap, const float* sinks, const uint8_t* custom_mask,
+                          const int32_t* mask_indptr, int mask_skip_prefix, void* workspace,
+                          int64_t workspace_bytes, void* stream);
+
 /* --------------------------------------------------------------------------
  * (f3) Radix prefix match on the device.  Replaces, for the attention path, the lookup side of
  *   python/sglang/srt/mem_cache/radix_cache.py: RadixCache.match_prefix (:377-423), insert (:425-445) and the

@@ -47,6 +47,38 @@ def dequantize(cache_u8: torch.Tensor, descale: float = 1.0) -> torch.Tensor:
     return cache_u8.view(FP8).float() * descale
 
 
+def extend_attention_e4m3_arith(q: torch.Tensor, k_cache_u8: torch.Tensor, v_cache_u8: torch.Tensor,
+                                req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, seq_lens, extend_lens,
+                                num_q_heads: int, num_kv_heads: int, head_dim: int, scaling: float, k_descale: float,
+                                v_descale: float, causal: bool = True) -> torch.Tensor:
+    """The ARITHMETIC of the reference's Triton extend kernel over an e4m3 pool, restated in torch
+    (python/sglang/kernels/ops/attention/extend_attention.py: ``qk = tl.dot(q.to(k.dtype), k)`` :523/:1174 - the
+    query is cast to e4m3; ``p = p.to(v.dtype)`` :596/:1248 - the probabilities are cast to e4m3 before the second
+    contraction, the denominator sums the un-rounded p; k / v descales as in triton_backend.py:1418-1420).
+    Pinned by tests/test_triton_golden.py against the kernel's recorded output (extend_fp8).
+    q [T, Hq*D] -> fp32 [T, Hq*D]."""
+    Hq, Hkv, D = num_q_heads, num_kv_heads, head_dim
+    G = Hq // Hkv
+    outs, t0 = [], 0
+    for b, (L, E) in enumerate(zip([int(x) for x in seq_lens], [int(x) for x in extend_lens])):
+        if E == 0:
+            continue
+        slots = req_to_token[int(req_pool_indices[b]), :L].long()
+        qb = q[t0:t0 + E].view(E, Hq, D).float().to(FP8).float()
+        kk = k_cache_u8[slots].view(FP8).float().view(L, Hkv, D).repeat_interleave(G, dim=1)
+        vv = v_cache_u8[slots].view(FP8).float().view(L, Hkv, D).repeat_interleave(G, dim=1)
+        s_ = torch.einsum("ehd,lhd->hel", qb, kk) * (scaling * k_descale)
+        if causal:
+            pos = torch.arange(E)[:, None] + (L - E)
+            s_ = s_.masked_fill(torch.arange(L)[None, :] > pos, float("-inf"))
+        p_ = torch.exp(s_ - s_.max(dim=-1, keepdim=True).values)
+        den = p_.sum(-1, keepdim=True)
+        o = torch.einsum("hel,lhd->ehd", p_.to(FP8).float(), vv) * v_descale / den.permute(1, 0, 2)
+        outs.append(o.reshape(E, Hq * D))
+        t0 += E
+    return torch.cat(outs) if outs else torch.zeros((0, Hq * D))
+
+
 def encode_e4m3_bits(x: np.ndarray) -> np.ndarray:
     """Independent fp32 -> e4m3fn encoder (uint8), restating c10/util/Float8_e4m3fn.h: RNE on the 3-bit
     mantissa, exponent bias 7, denormals below 2^-6 (step 2^-9), no infinities, |x| rounding above 448 -> 0x7f."""

@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200attn.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "b200attn.h")
 
-ABI_VERSION = 20  # b200attn_abi_version() of the library this binding matches (api.cu)
+ABI_VERSION = 21  # b200attn_abi_version() of the library this binding matches (api.cu)
 BF16, FP16, FP32 = 0, 1, 2
 I32, I64 = 0, 1
 
@@ -106,6 +106,11 @@ SIGNATURES = {
         C.c_int,
         [_vp, _i64, _vp, _vp, _i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _i32, _i32,
          _i32, _i32, C.c_int, C.c_int, _f32, _i32, _f32, _vp, _vp, _vp, C.c_int, _vp, _i64, _vp],
+    ),
+    "b200attn_extend_fp8kv": (
+        C.c_int,
+        [_vp, _i64, _vp, _vp, _i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _i32, _i32,
+         _i32, _i32, C.c_int, C.c_int, _f32, _f32, _f32, _i32, _f32, _vp, _vp, _vp, C.c_int, _vp, _i64, _vp],
     ),
     "b200attn_merge_state": (
         C.c_int,

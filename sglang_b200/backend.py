@@ -94,7 +94,7 @@ class B200AttnBackend(_Base):
     DETERMINISTIC_SPLIT_TILE = 256
 
     def __init__(self, model_runner, skip_padding_slot: bool = True, export_page_table: bool = False,
-                 deterministic: Optional[bool] = None):
+                 deterministic: Optional[bool] = None, fp8_extend: Optional[str] = None):
         super().__init__()
         if not torch.cuda.is_available():
             raise AssertionError("B200AttnBackend needs a CUDA device (sm_100a); no CPU fallback")
@@ -123,6 +123,14 @@ class B200AttnBackend(_Base):
             deterministic = bool(getattr(getattr(model_runner, "server_args", None),
                                          "enable_deterministic_inference", False))
         self.deterministic = bool(deterministic)
+        # Extend over an e4m3 pool.  "in_kernel" (default, head_dim 128): the tcgen05 kernel contracts on the pool's
+        # bytes with Q and P cast to e4m3 - the arithmetic of the reference's Triton kernels for such a pool
+        # (extend_attention.py:523,596) - no scratch copy, faster than the 16-bit pool.  "dequant": the batch's rows
+        # are dequantised once into a 16-bit scratch and Q / P stay 16-bit: closer to the exact math over the
+        # dequantised pool than the reference itself, ~5 % slower; also what head_dim 64 takes.
+        self.fp8_extend = fp8_extend or os.environ.get("B200ATTN_FP8_EXTEND", "in_kernel")
+        if self.fp8_extend not in ("in_kernel", "dequant"):
+            raise ValueError("fp8_extend must be 'in_kernel' or 'dequant'")
         self.forward_metadata: Optional[ForwardMetadata] = None
         self.num_sms = ops.sm_count()
         # CUDA-graph state (init_cuda_graph_state)
@@ -564,7 +572,10 @@ class B200AttnBackend(_Base):
             ws = self._workspace(ops.extend_workspace_bytes(B, q2.shape[0], Hq))
             kv_idx = self._kv_indices(layer, md)
             ek, ev, eidx, escale = kbuf, vbuf, kv_idx, layer.scaling
-            if fp8:
+            ext_dsc = {}
+            if fp8 and D == 128 and self.fp8_extend == "in_kernel":
+                ext_dsc = dsc  # b200attn_extend_fp8kv: contracts on the e4m3 bytes of the pool itself
+            elif fp8:
                 # the tcgen05 kernel takes 16-bit K/V operands: gather the batch's rows once into a 16-bit scratch
                 # (K exact, k_descale on the score scale; v_descale folded into the V rows), slot ids become 0..n-1
                 n = kv_idx.numel()
@@ -593,7 +604,8 @@ class B200AttnBackend(_Base):
                                  max_qo_len=md.max_extend_len,
                                  total_q=q2.shape[0] if getattr(md, "_graph", False) else md.num_extend_tokens,
                                  workspace=ws,
-                                 skip_single_rows=md.num_dec > 0, **mask_kw, **self._features(layer, kwargs))
+                                 skip_single_rows=md.num_dec > 0, **mask_kw, **self._features(layer, kwargs),
+                                 **ext_dsc)
         if md.num_dec > 0:  # a single query row sees all of its keys, causal or not
             Hkv = layer.tp_k_head_num
             dwarps, dtail = 4, -1

@@ -33,7 +33,7 @@ int sm_count() {
 
 extern "C" {
 
-int b200attn_abi_version(void) { return 20; }
+int b200attn_abi_version(void) { return 21; }
 
 const char* b200attn_last_error(void) { return b200attn::g_err; }
 

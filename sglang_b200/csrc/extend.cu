@@ -82,6 +82,7 @@ struct ExtendParams {
   const int32_t* mask_indptr;
   int mask_skip_prefix;
   int sched_slot;  // this launch's {ticket, CTAs done} pair in g_ext_sched
+  float out_scale;  // multiplies the normalised output: v_descale of an e4m3 pool, else 1
 #ifdef EXT_TRACE
   long long* trace;  // dev-only timeline of CTA (0,0,0): [role 0..2][step 0..31][8]
 #endif
@@ -130,7 +131,8 @@ enum ExtBar {
   kBarQEmpty = kBarOFinal + 2,          // [2]  MMA -> producer : last QK_i of the item done, Q_i tile is free
   kBarItemFull = kBarQEmpty + 2,        // [ring]  scheduler (K producer warp) -> every role : descriptor n is written
   kBarItemEmpty = kBarItemFull + kExtRing,  // [ring]  every other role -> scheduler : descriptor n has been read
-  kBarCount = kBarItemEmpty + kExtRing
+  kBarQ8 = kBarItemEmpty + kExtRing,    // [2]  softmax_i -> MMA_i (e4m3 pools): the e4m3 copy of Q_i is in shared memory
+  kBarCount = kBarQ8 + 2
 };
 static_assert(kBarCount * 8 <= 512, "barrier block");
 
@@ -258,7 +260,13 @@ __device__ __forceinline__ void derive_tiles(const ItemDesc& d, const ExtendPara
   t.nc_max = max(t.nc[0], t.nc[1]);
 }
 
-template <int D, bool kBf16>
+// kFp8: the KV pool holds e4m3 bytes (memory_pool.py:2365-2375).  Q is converted to e4m3 in shared memory and P is
+// written to TMEM as e4m3, and both contractions run as tcgen05.mma.kind::f8f6f4 (K = 32 per instruction) straight
+// on the pool's bytes: what the reference's Triton kernels compute for such a pool (extend_attention.py:523
+// `tl.dot(q.to(k.dtype), k)`, :596 `p = p.to(v.dtype)`), with k_descale in the softmax scale and v_descale in the
+// output scale (triton_backend.py:1418-1420).  No dequantised scratch copy of the pool rows.  head_dim 128 only: a
+// K/V row is then exactly one 128-byte swizzle row.
+template <int D, bool kBf16, bool kFp8 = false>
 __global__ void __launch_bounds__(kExtThreads, 1)
     extend_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                   const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_kbox,
@@ -266,7 +274,12 @@ __global__ void __launch_bounds__(kExtThreads, 1)
                   const ExtendParams p) {
   using namespace sm100;
   using S = ExtSmem<D>;
-  constexpr int kHalves = D / 64;  // 64-column halves of the head dim
+  constexpr int kHalves = D / 64;  // 64-column halves of the head dim (16-bit tiles: Q always, K/V of 16-bit pools)
+  static_assert(!kFp8 || D == 128, "e4m3 pools: head_dim 128");
+  constexpr int kHalvesKV = kFp8 ? 1 : kHalves;                  // 128-byte column groups of a K/V row
+  constexpr uint32_t kKVTileBytes = kFp8 ? kExtN * D : S::kTile;  // bytes of one K or V tile as loaded
+  // e4m3 copy of Q tile i: the upper (unused) half of K ring stage i
+  constexpr uint32_t kQ8Off = S::kK + kExtN * D;
   constexpr uint32_t kTmemCols = 512;
   constexpr uint32_t kColS = 0, kColO = 256;  // + i * 128
 
@@ -315,6 +328,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
       mbar_init(bar(kBarOFinal + i), 1);
       mbar_init(bar(kBarQEmpty + i), 1);
     }
+    for (int i = 0; i < 2; ++i) mbar_init(bar(kBarQ8 + i), 128);
     for (int s = 0; s < kExtRing; ++s) {
       mbar_init(bar(kBarItemFull + s), 1);
       mbar_init(bar(kBarItemEmpty + s), 11);  // V producer, two MMA issuers, eight softmax warps
@@ -463,7 +477,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
             __syncwarp();
           }
           const int32_t* idx = p.kv_indices + d.kv_beg;
-          const int col = d.kvh * D;
+          const int col = kFp8 ? d.kvh * (D / 2) : d.kvh * D;  // the tensor maps count 16-bit columns
           int r[4];
           auto load_slots = [&](int j) {
 #pragma unroll
@@ -482,7 +496,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
                           (r[0] == g0 + 4 * (lane & 3));
             contig = __all_sync(0xffffffffu, contig) && (t.kbase + (j + 1) * kExtN <= t.kv_end);
             if (kt >= kExtStages) mbar_wait(bar(bar_empty + st), ((kt / kExtStages) + 1) & 1);
-            if (lane == 0) mbar_arrive_expect_tx(bar(bar_full + st), S::kTile);
+            if (lane == 0) mbar_arrive_expect_tx(bar(bar_full + st), kKVTileBytes);
             __syncwarp();
             if (contig) {
               int rows[kExtN / kExtBoxRows];
@@ -492,13 +506,13 @@ __global__ void __launch_bounds__(kExtThreads, 1)
 #pragma unroll
                 for (int g = 0; g < kExtN / kExtBoxRows; ++g)
 #pragma unroll
-                  for (int hf = 0; hf < kHalves; ++hf)
+                  for (int hf = 0; hf < kHalvesKV; ++hf)
                     tma_load_2d(dst + hf * S::kHalf + g * kExtBoxRows * 128, tm_b, bar(bar_full + st),
                                 col + hf * 64, rows[g]);
               }
             } else {
 #pragma unroll
-              for (int hf = 0; hf < kHalves; ++hf)
+              for (int hf = 0; hf < kHalvesKV; ++hf)
                 tma_gather4(dst + hf * S::kHalf + lane * 4 * 128, tm_g, bar(bar_full + st), col + hf * 64,
                             r[0], r[1], r[2], r[3]);
             }
@@ -517,8 +531,9 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         // sustains only one UTCHMMA per ~45 cycles, so each tile gets its own issuing thread.  Every
         // value that feeds a descriptor is made provably warp-uniform (shuffle broadcast) so the compiler
         // keeps descriptors in uniform registers instead of wrapping each UTCHMMA in an elect loop.
-        constexpr uint32_t idesc_qk = idesc_f16(kBf16 ? 1 : 0, kExtM, kExtC, 0, 0);
-        constexpr uint32_t idesc_pv = idesc_f16(kBf16 ? 1 : 0, kExtM, D, 0, 1);
+        // (the format fields read 0 = f16 under kind::f16 and 0 = e4m3 under kind::f8f6f4)
+        constexpr uint32_t idesc_qk = idesc_f16(kFp8 ? 0 : (kBf16 ? 1 : 0), kExtM, kExtC, 0, 0);
+        constexpr uint32_t idesc_pv = idesc_f16(kFp8 ? 0 : (kBf16 ? 1 : 0), kExtM, D, 0, 1);
         const int i = __shfl_sync(0xffffffffu, warp - 10, 0);
         const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
         const uint32_t smem_u = __shfl_sync(0xffffffffu, smem0, 0);
@@ -527,7 +542,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         constexpr uint64_t kDescKMajor = smem_desc_sw128_hi(16, 1024);     // Q, K: K-major
         constexpr uint64_t kDescVMn = smem_desc_sw128_hi(S::kHalf, 1024);  // V: MN-major
         auto desc = [](uint64_t hi, uint32_t addr) { return hi | (uint64_t)((addr & 0x3FFFF) >> 4); };
-        const uint32_t qa = smem_u + S::kQ + i * S::kTile;
+        const uint32_t qa = kFp8 ? smem_u + kQ8Off + i * S::kTile : smem_u + S::kQ + i * S::kTile;
         const uint32_t ts = tmem_u + kColS + i * 128, to = tmem_u + kColO + i * 128;
         for (int n = 0;; ++n) {
           const ItemDesc d = acquire(n);
@@ -552,11 +567,15 @@ __global__ void __launch_bounds__(kExtThreads, 1)
 #ifdef EXT_ABL_NOQK
               for (int ks = 0; ks < 1; ++ks) {
 #else
-              for (int ks = 0; ks < D / 16; ++ks) {
+              for (int ks = 0; ks < (kFp8 ? D / 32 : D / 16); ++ks) {
 #endif
-                const uint32_t off = (ks / 4) * S::kHalf + (ks % 4) * 32;
-                umma_ss(ts + hb * kExtC, desc(kDescKMajor, qa + off), desc(kDescKMajor, ka + off), idesc_qk,
-                        ks > 0 ? 1u : 0u);
+                const uint32_t off = (ks / 4) * S::kHalf + (ks % 4) * 32;  // 32 bytes per step either way
+                if constexpr (kFp8)
+                  umma_ss_f8(ts + hb * kExtC, desc(kDescKMajor, qa + off), desc(kDescKMajor, ka + off), idesc_qk,
+                             ks > 0 ? 1u : 0u);
+                else
+                  umma_ss(ts + hb * kExtC, desc(kDescKMajor, qa + off), desc(kDescKMajor, ka + off), idesc_qk,
+                          ks > 0 ? 1u : 0u);
               }
               umma_commit(barb + 8u * (kBarSFull + i * 2 + hb));
               if (c == nc_i - 1) umma_commit(barb + 8u * (kBarQEmpty + i));  // Q_i tile is free
@@ -570,17 +589,22 @@ __global__ void __launch_bounds__(kExtThreads, 1)
 #ifdef EXT_ABL_NOPV
               for (int ks = 0; ks < 1; ++ks) {
 #else
-              for (int ks = 0; ks < kExtC / 16; ++ks) {
+              for (int ks = 0; ks < (kFp8 ? kExtC / 32 : kExtC / 16); ++ks) {
 #endif
                 // 16 keys per step = 8 packed TMEM columns of A; 2 KB down the V tile; d-halves 16 KB apart
-                umma_ts(to, ts + hb * kExtC + ks * 8, desc(kDescVMn, va + ks * 2048), idesc_pv,
-                        (c > 0 || ks > 0) ? 1u : 0u);
+                // (e4m3: 32 keys per step = 8 columns of four; 4 KB down the tile; one 128-byte group of d)
+                if constexpr (kFp8)
+                  umma_ts_f8(to, ts + hb * kExtC + ks * 8, desc(kDescVMn, va + ks * 4096), idesc_pv,
+                             (c > 0 || ks > 0) ? 1u : 0u);
+                else
+                  umma_ts(to, ts + hb * kExtC + ks * 8, desc(kDescVMn, va + ks * 2048), idesc_pv,
+                          (c > 0 || ks > 0) ? 1u : 0u);
               }
               umma_commit(barb + 8u * (kBarPVDone + i));
               if (c == nc_i - 1) umma_commit(barb + 8u * (kBarOFinal + i));
             };
             if (i == 0) { TRACE(5, it, 0); }
-            if (nc_i > 0) mbar_wait(barb + 8u * (kBarQ + i), nqi & 1);
+            if (nc_i > 0) mbar_wait(barb + 8u * ((kFp8 ? kBarQ8 : kBarQ) + i), nqi & 1);
             if (i == 0) { TRACE(5, it, 1); }
             mbar_wait(barb + 8u * (kBarKFull + ktl % kExtStages), (ktl / kExtStages) & 1);
             tc_fence_after();
@@ -642,6 +666,32 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         const int nc_i = i == 0 ? t.nc[0] : t.nc[1];
         if (nc_i == 0) continue;
         if (i == 0) { TRACE(4, it, 0); }
+        if constexpr (kFp8) {
+          // Q_i arrived as 16-bit (TMA, two 64-column halves of 128-byte swizzled rows): this thread rewrites its
+          // row as e4m3 into the K-major e4m3 tile the QK instruction reads (one 128-byte swizzled row).
+          mbar_wait(bar(kBarQ + i), nq_my & 1);
+          const uint8_t* qrow = smem + S::kQ + i * S::kTile + row * 128;
+          uint8_t* q8row = smem + kQ8Off + i * S::kTile + row * 128;
+#pragma unroll
+          for (int j = 0; j < D / 16; ++j) {  // 16 columns -> one 16-byte chunk of the e4m3 row
+            uint32_t w[4];
+#pragma unroll
+            for (int hc = 0; hc < 2; ++hc) {  // two 8-column 16-byte chunks of the 16-bit row
+              const int c16 = 2 * (j % 4) + hc;
+              const uint4 v = *reinterpret_cast<const uint4*>(qrow + (j / 4) * S::kHalf + ((c16 ^ (row & 7)) << 4));
+              const uint32_t in[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+              for (int k2 = 0; k2 < 2; ++k2) {
+                const float2 f0 = unpack2<kBf16>(in[2 * k2]), f1 = unpack2<kBf16>(in[2 * k2 + 1]);
+                w[2 * hc + k2] = (uint32_t)__nv_cvt_float2_to_fp8x2(f0, __NV_SATFINITE, __NV_E4M3) |
+                                 ((uint32_t)__nv_cvt_float2_to_fp8x2(f1, __NV_SATFINITE, __NV_E4M3) << 16);
+              }
+            }
+            *reinterpret_cast<uint4*>(q8row + ((j ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+          }
+          fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
+          mbar_arrive(bar(kBarQ8 + i));
+        }
         const int m0 = i == 0 ? t.m0[0] : t.m0[1];
         const int kvend_i = i == 0 ? t.kvend[0] : t.kvend[1];
         // keys visible to this row: [0, limit)
@@ -734,7 +784,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
           const float m_eff = (m_used == -INFINITY) ? 0.f : m_used;  // all keys so far masked: p = exp2(-inf) = 0
           const uint64_t negm2 = f2_pack(-m_eff, -m_eff);
           uint64_t sum2[2] = {0ull, 0ull};
-          uint32_t pk[32];
+          uint32_t pk[kFp8 ? 16 : 32];
 #pragma unroll
           for (int e = 0; e < kExtC; e += 2) {
             float x0, x1, p0, p1;
@@ -752,9 +802,16 @@ __global__ void __launch_bounds__(kExtThreads, 1)
               p1 = ex2_approx(x1);
             }
             sum2[(e >> 1) & 1] = f2_add(sum2[(e >> 1) & 1], f2_pack(p0, p1));
-            pk[e >> 1] = pack2<kBf16>(p0, p1);
+            if constexpr (kFp8) {  // four e4m3 per TMEM column (p <= 2^8 under the lazy rescale: inside e4m3's range)
+              const uint32_t h = __nv_cvt_float2_to_fp8x2(make_float2(p0, p1), __NV_SATFINITE, __NV_E4M3);
+              if ((e & 2) == 0) pk[e >> 2] = h;
+              else pk[e >> 2] |= h << 16;
+            } else {
+              pk[e >> 1] = pack2<kBf16>(p0, p1);
+            }
           }
-          tmem_st32(col_c, pk);
+          if constexpr (kFp8) tmem_st16(col_c, pk);
+          else tmem_st32(col_c, pk);
           float a0, a1;
           f2_unpack(f2_add(sum2[0], sum2[1]), a0, a1);
           l_run += a0 + a1;
@@ -788,7 +845,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         if (i == 0) { TRACE(4, it, 3); }
         const int h = i == 0 ? t.h[0] : t.h[1];
         if (p.sinks != nullptr) l_run += ex2_approx(__ldg(p.sinks + h) * kLog2e - m_used);
-        const float inv = 1.f / l_run;
+        const float inv = p.out_scale / l_run;
         const int rows_i = i == 0 ? t.rows[0] : t.rows[1];
         const bool valid = row < rows_i;
         if (rows_i == kExtM && p.o_tma) {
@@ -968,14 +1025,14 @@ int tensor_map_cached(const CUtensorMap** out, const void* base, uint64_t rows, 
   return B200ATTN_OK;
 }
 
-template <int D, bool kBf16>
+template <int D, bool kBf16, bool kFp8 = false>
 static int launch_extend(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
                          const CUtensorMap& tkb, const CUtensorMap& tvb, const CUtensorMap& to,
                          const ExtendParams& p, int max_qtiles, cudaStream_t st) {
   constexpr int kSmem = ExtSmem<D>::kTotal + 1024;  // + alignment slack
   static bool configured = false;
   if (!configured) {
-    B2_CUDA(cudaFuncSetAttribute(extend_kernel<D, kBf16>,
+    B2_CUDA(cudaFuncSetAttribute(extend_kernel<D, kBf16, kFp8>,
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     configured = true;
   }
@@ -995,7 +1052,7 @@ static int launch_extend(const CUtensorMap& tq, const CUtensorMap& tk, const CUt
     const long long items = upper * ps.B;
     dim3 grid((unsigned)(items < sms ? items : sms));
     ps.sched_slot = (int)(g_sched_next.fetch_add(1u) % (unsigned)kExtSchedSlots);
-    extend_kernel<D, kBf16><<<grid, kExtThreads, kSmem, st>>>(tq, tk, tv, tkb, tvb, to, ps);
+    extend_kernel<D, kBf16, kFp8><<<grid, kExtThreads, kSmem, st>>>(tq, tk, tv, tkb, tvb, to, ps);
     B2_LAUNCH_CHECK();
   }
   return B200ATTN_OK;
@@ -1005,16 +1062,17 @@ static int launch_extend(const CUtensorMap& tq, const CUtensorMap& tk, const CUt
 
 extern "C" int64_t b200attn_extend_workspace_bytes(int32_t, int64_t, int32_t) { return 0; }
 
-extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_cache,
-                               const void* v_cache, int64_t kv_stride, int64_t num_slots, void* o,
-                               int64_t o_stride, float* lse, const int32_t* qo_indptr,
-                               const int32_t* kv_indptr, const int32_t* kv_indices, int32_t B,
-                               int64_t total_q_host, int32_t max_qo_len_host, int32_t Hq,
-                               int32_t Hkv, int32_t D, int32_t page_size, int dtype, int causal,
-                               float sm_scale, int32_t window_left, float logit_cap,
-                               const float* sinks, const uint8_t* custom_mask,
-                               const int32_t* mask_indptr, int mask_skip_prefix, void* workspace,
-                               int64_t workspace_bytes, void* stream) {
+// kv_fp8: k_cache / v_cache hold e4m3 bytes, kv_stride counts BYTES per slot row (16-bit pools: elements)
+static int extend_impl(const void* q, int64_t q_stride, const void* k_cache,
+                       const void* v_cache, int64_t kv_stride, int64_t num_slots, void* o,
+                       int64_t o_stride, float* lse, const int32_t* qo_indptr,
+                       const int32_t* kv_indptr, const int32_t* kv_indices, int32_t B,
+                       int64_t total_q_host, int32_t max_qo_len_host, int32_t Hq,
+                       int32_t Hkv, int32_t D, int32_t page_size, int dtype, int causal,
+                       float sm_scale, int32_t window_left, float logit_cap,
+                       const float* sinks, const uint8_t* custom_mask,
+                       const int32_t* mask_indptr, int mask_skip_prefix, void* workspace,
+                       int64_t workspace_bytes, void* stream, bool kv_fp8, float k_descale, float v_descale) {
   using namespace b200attn;
   B2_CHECK_ARG(logit_cap >= 0.f, "extend: negative logit_cap");
 #ifndef EXT_TRACE
@@ -1030,26 +1088,31 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
                Hq, Hkv);
   B2_CHECK_ARG(Hkv <= 65535, "extend: kv head count too large");
   B2_CHECK_ARG(num_slots > 0 && num_slots < (1ll << 31), "extend: bad num_slots");
-  B2_CHECK_ARG(q_stride % 8 == 0 && kv_stride % 8 == 0 && o_stride % 8 == 0,
+  B2_CHECK_ARG(q_stride % 8 == 0 && kv_stride % (kv_fp8 ? 16 : 8) == 0 && o_stride % 8 == 0,
                "extend: strides must keep rows 16-byte aligned");
+  B2_CHECK_ARG(!kv_fp8 || (k_descale > 0.f && v_descale > 0.f), "extend: fp8 descales must be positive");
   B2_CHECK_ARG((((uintptr_t)q | (uintptr_t)k_cache | (uintptr_t)v_cache | (uintptr_t)o) & 15) == 0,
                "extend: tensors must be 16-byte aligned");
   if (dtype != B200ATTN_BF16 && dtype != B200ATTN_FP16) B2_UNSUPPORTED("extend: dtype %d", dtype);
   if (D != 64 && D != 128) B2_UNSUPPORTED("extend: head_dim %d (supported: 64, 128)", D);
+  if (kv_fp8 && D != 128) B2_UNSUPPORTED("extend over an e4m3 pool: head_dim %d (supported: 128)", D);
+  // the pool maps count 16-bit columns: an e4m3 row of Hkv * D bytes is Hkv * D / 2 of them
+  const uint64_t kv_cols = kv_fp8 ? (uint64_t)Hkv * D / 2 : (uint64_t)Hkv * D;
+  const uint64_t kv_row_bytes = kv_fp8 ? (uint64_t)kv_stride : (uint64_t)kv_stride * 2;
   // q / o are activations (a new address every call): encoded per call; the four pool maps are cached
   CUtensorMap tq, to;
   const CUtensorMap *ptk, *ptv, *ptkb, *ptvb;
   int rc = make_tensor_map_2d(&tq, q, (uint64_t)total_q_host, (uint64_t)Hq * D,
                               (uint64_t)q_stride * 2, 64, kExtM);
   if (rc) return rc;
-  rc = tensor_map_cached(&ptk, k_cache, (uint64_t)num_slots, (uint64_t)Hkv * D, (uint64_t)kv_stride * 2, 64, 1);
+  rc = tensor_map_cached(&ptk, k_cache, (uint64_t)num_slots, kv_cols, kv_row_bytes, 64, 1);
   if (rc) return rc;
-  rc = tensor_map_cached(&ptv, v_cache, (uint64_t)num_slots, (uint64_t)Hkv * D, (uint64_t)kv_stride * 2, 64, 1);
+  rc = tensor_map_cached(&ptv, v_cache, (uint64_t)num_slots, kv_cols, kv_row_bytes, 64, 1);
   if (rc) return rc;
-  rc = tensor_map_cached(&ptkb, k_cache, (uint64_t)num_slots, (uint64_t)Hkv * D, (uint64_t)kv_stride * 2, 64,
+  rc = tensor_map_cached(&ptkb, k_cache, (uint64_t)num_slots, kv_cols, kv_row_bytes, 64,
                          kExtBoxRows);
   if (rc) return rc;
-  rc = tensor_map_cached(&ptvb, v_cache, (uint64_t)num_slots, (uint64_t)Hkv * D, (uint64_t)kv_stride * 2, 64,
+  rc = tensor_map_cached(&ptvb, v_cache, (uint64_t)num_slots, kv_cols, kv_row_bytes, 64,
                          kExtBoxRows);
   if (rc) return rc;
   const CUtensorMap &tk = *ptk, &tv = *ptv, &tkb = *ptkb, &tvb = *ptvb;
@@ -1072,7 +1135,9 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
   p.num_slots = (int)num_slots;
   p.causal = (causal & B200ATTN_EXT_CAUSAL) ? 1 : 0;
   p.skip_single = (causal & B200ATTN_EXT_SKIP_SINGLE) ? 1 : 0;
+  if (kv_fp8) sm_scale *= k_descale;  // scores come out of the tensor core in units of k_descale
   p.scale_log2 = sm_scale * kLog2e;
+  p.out_scale = kv_fp8 ? v_descale : 1.f;
   p.window_left = window_left;
   p.cap_pre = logit_cap > 0.f ? sm_scale / logit_cap : 0.f;
   p.sinks = sinks;
@@ -1085,9 +1150,44 @@ extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_ca
 #endif
   const int max_qtiles = (max_qo_len_host + kExtM - 1) / kExtM;
   cudaStream_t st = (cudaStream_t)stream;
+  if (kv_fp8)
+    return dtype == B200ATTN_BF16 ? launch_extend<128, true, true>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st)
+                                  : launch_extend<128, false, true>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st);
   if (D == 128)
     return dtype == B200ATTN_BF16 ? launch_extend<128, true>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st)
                                   : launch_extend<128, false>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st);
   return dtype == B200ATTN_BF16 ? launch_extend<64, true>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st)
                                 : launch_extend<64, false>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st);
+}
+
+extern "C" int b200attn_extend(const void* q, int64_t q_stride, const void* k_cache,
+                               const void* v_cache, int64_t kv_stride, int64_t num_slots, void* o,
+                               int64_t o_stride, float* lse, const int32_t* qo_indptr,
+                               const int32_t* kv_indptr, const int32_t* kv_indices, int32_t B,
+                               int64_t total_q_host, int32_t max_qo_len_host, int32_t Hq,
+                               int32_t Hkv, int32_t D, int32_t page_size, int dtype, int causal,
+                               float sm_scale, int32_t window_left, float logit_cap,
+                               const float* sinks, const uint8_t* custom_mask,
+                               const int32_t* mask_indptr, int mask_skip_prefix, void* workspace,
+                               int64_t workspace_bytes, void* stream) {
+  return extend_impl(q, q_stride, k_cache, v_cache, kv_stride, num_slots, o, o_stride, lse, qo_indptr, kv_indptr,
+                     kv_indices, B, total_q_host, max_qo_len_host, Hq, Hkv, D, page_size, dtype, causal, sm_scale,
+                     window_left, logit_cap, sinks, custom_mask, mask_indptr, mask_skip_prefix, workspace,
+                     workspace_bytes, stream, false, 1.f, 1.f);
+}
+
+extern "C" int b200attn_extend_fp8kv(const void* q, int64_t q_stride, const void* k_cache,
+                                     const void* v_cache, int64_t kv_stride_bytes, int64_t num_slots, void* o,
+                                     int64_t o_stride, float* lse, const int32_t* qo_indptr,
+                                     const int32_t* kv_indptr, const int32_t* kv_indices, int32_t B,
+                                     int64_t total_q_host, int32_t max_qo_len_host, int32_t Hq,
+                                     int32_t Hkv, int32_t D, int32_t page_size, int dtype, int causal,
+                                     float sm_scale, float k_descale, float v_descale, int32_t window_left,
+                                     float logit_cap, const float* sinks, const uint8_t* custom_mask,
+                                     const int32_t* mask_indptr, int mask_skip_prefix, void* workspace,
+                                     int64_t workspace_bytes, void* stream) {
+  return extend_impl(q, q_stride, k_cache, v_cache, kv_stride_bytes, num_slots, o, o_stride, lse, qo_indptr,
+                     kv_indptr, kv_indices, B, total_q_host, max_qo_len_host, Hq, Hkv, D, page_size, dtype, causal,
+                     sm_scale, window_left, logit_cap, sinks, custom_mask, mask_indptr, mask_skip_prefix, workspace,
+                     workspace_bytes, stream, true, k_descale, v_descale);
 }

@@ -749,8 +749,13 @@ def extend_attention(
     custom_mask: Optional[torch.Tensor] = None,
     mask_indptr: Optional[torch.Tensor] = None,
     skip_prefix_custom_mask: bool = True,
+    k_descale: float = 1.0,
+    v_descale: float = 1.0,
 ) -> torch.Tensor:
     """Ragged prefix+extend attention: ``q [T,Hq,D]`` -> ``o [T,Hq,D]``.
+
+    uint8 / float8_e4m3fn caches are an e4m3 pool: the kernel casts Q and P to e4m3 and contracts on the pool's bytes
+    (``b200attn_extend_fp8kv``, what the reference's Triton kernel does: extend_attention.py:523,596), head_dim 128.
 
     Mirrors ``extend_attention_fwd_unified`` (python/sglang/kernels/ops/attention/
     extend_attention.py:963-1410): one KV source (the pool) indexed by
@@ -766,8 +771,9 @@ def extend_attention(
     Hkv = k_cache.shape[1]
     if k_cache.shape[2] != D or v_cache.shape[2] != D:
         raise NotImplementedError("extend_attention: v_head_dim != head_dim is not supported")
-    if q.dtype != k_cache.dtype or q.dtype != v_cache.dtype:
-        raise TypeError("extend_attention: q and the KV pool must share a dtype")
+    fp8 = k_cache.dtype in (torch.uint8, torch.float8_e4m3fn)
+    if (not fp8 and q.dtype != k_cache.dtype) or k_cache.dtype != v_cache.dtype:
+        raise TypeError("extend_attention: q and the KV pool must share a dtype (or the pool is e4m3 bytes)")
     if q.stride(2) != 1 or q.stride(1) != D or o.stride(2) != 1 or o.stride(1) != D:
         raise ValueError("extend_attention: q/o heads must be densely packed")
     if k_cache.stride(2) != 1 or k_cache.stride(1) != D or v_cache.stride() != k_cache.stride():
@@ -775,6 +781,19 @@ def extend_attention(
     if qo_indptr.dtype != torch.int32 or kv_indptr.dtype != torch.int32 or kv_indices.dtype != torch.int32:
         raise TypeError("extend_attention: indptr / indices must be int32")
     ws_bytes = 0 if workspace is None else workspace.numel() * workspace.element_size()
+    if fp8:
+        rc = _lib.load().b200attn_extend_fp8kv(
+            q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
+            min(k_cache.shape[0], v_cache.shape[0]), o.data_ptr(), o.stride(0), _ptr(lse),
+            qo_indptr.data_ptr(), kv_indptr.data_ptr(), kv_indices.data_ptr(), B,
+            T if total_q is None else total_q, max_qo_len, Hq, Hkv, D, page_size, _fdtype(q),
+            (1 if causal else 0) | (2 if skip_single_rows else 0), float(sm_scale), float(k_descale),
+            float(v_descale), int(window_left), float(logit_cap), _sinks_ptr(sinks, Hq),
+            _mask_ptr(custom_mask, mask_indptr, B), _ptr(mask_indptr), int(bool(skip_prefix_custom_mask)),
+            _ptr(workspace), ws_bytes, _stream(),
+        )
+        check(rc, "b200attn_extend_fp8kv")
+        return o
     rc = _lib.load().b200attn_extend(
         q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
         min(k_cache.shape[0], v_cache.shape[0]), o.data_ptr(), o.stride(0), _ptr(lse),

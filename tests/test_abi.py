@@ -18,7 +18,7 @@ def test_library_exports_every_symbol():
 
 def test_abi_version_and_error_string():
     lib = _lib.load()
-    assert lib.b200attn_abi_version() == _lib.ABI_VERSION == 20
+    assert lib.b200attn_abi_version() == _lib.ABI_VERSION == 21
     assert isinstance(lib.b200attn_last_error(), bytes)
     assert lib.b200attn_decode_workspace_bytes(4, 32, 128, 1) == 0
     # fixed-size arrival-counter header (65536 int32) + fp32 partials and their LSE

@@ -1,4 +1,6 @@
 """(f4) FP8 (e4m3) KV cache: quantising store (bit-exact), fp8 decode kernel, extend over an fp8 pool, backend."""
+import types
+
 import pytest
 import torch
 
@@ -6,7 +8,7 @@ from oracle import fp8_port
 from oracle import torch_native_port as oracle
 from sglang_b200 import (B200AttnBackend, ForwardBatch, ForwardMode, MHATokenToKVPool, RadixAttention,
                          ReqToTokenPool, ops)
-from tests.util import assert_close_attn, make_scenario
+from tests.util import assert_close_e4m3_arith, assert_close_attn, make_scenario
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
@@ -125,7 +127,7 @@ def test_dequant_gather_exact():
     assert torch.equal(ov.cpu(), (fp8_port.dequantize(v8)[idx.long()] * 0.75).to(torch.bfloat16))
 
 
-def _backend(sc, Hkv, D, page, k8, v8):
+def _backend(sc, Hkv, D, page, k8, v8, fp8_extend=None):
     B = len(sc.seq_lens)
     ctx = sc.req_to_token.shape[1]
     req_pool = ReqToTokenPool(B, ctx, DEV)
@@ -139,11 +141,33 @@ def _backend(sc, Hkv, D, page, k8, v8):
         device, page_size, sliding_window_size = DEV, page, None
         req_to_token_pool, token_to_kv_pool = req_pool, pool
 
-    return B200AttnBackend(Runner(), skip_padding_slot=False), pool
+    return B200AttnBackend(Runner(), skip_padding_slot=False, fp8_extend=fp8_extend), pool
 
 
+def _check_fp8_extend_rows(o, q, k8, v8, sc, lens, ext, Hq, Hkv, D, ks, vs, fp8_extend, what, single_rows_decode=True):
+    """Rows of requests with one query row go through the decode kernel when the host lengths are known (16-bit q and
+    p: exact-math tolerance on either path); extend rows: exact-math tolerance on the dequantising path, the reference Triton kernel's e4m3
+    arithmetic (oracle.fp8_port.extend_attention_e4m3_arith) on the in-kernel path."""
+    exact = oracle.attention_fp32(q, fp8_port.dequantize(k8, ks), fp8_port.dequantize(v8, vs), sc.req_to_token,
+                                  sc.req_pool_indices, torch.tensor(lens), torch.tensor(ext), Hq, Hkv, D, D ** -0.5,
+                                  causal=True)
+    o = o.detach().float().cpu().view(exact.shape)
+    single = torch.cat([torch.full((e,), e == 1 and single_rows_decode) for e in ext]) if sum(ext) else \
+        torch.zeros(0, dtype=torch.bool)
+    if fp8_extend == "dequant":
+        assert_close_attn(o, exact, what)
+        return
+    if single.any():
+        assert_close_attn(o[single], exact[single], what + " (decode rows)")
+    if (~single).any():
+        emul = fp8_port.extend_attention_e4m3_arith(q, k8, v8, sc.req_to_token, sc.req_pool_indices, lens, ext, Hq, Hkv, D,
+                                                    D ** -0.5, ks, vs, causal=True)
+        assert_close_e4m3_arith(o[~single], emul[~single], exact[~single], what + " (extend rows)")
+
+
+@pytest.mark.parametrize("fp8_extend", ["in_kernel", "dequant"])
 @pytest.mark.parametrize("mode", ["extend", "mixed", "decode"])
-def test_backend_fp8_pool(mode):
+def test_backend_fp8_pool(mode, fp8_extend):
     """Store (quantising) + attention through B200AttnBackend on a float8_e4m3fn pool with layer k/v scales."""
     Hq, Hkv, D, page = 16, 4, 128, 16
     ks, vs = 0.6, 0.9
@@ -155,7 +179,7 @@ def test_backend_fp8_pool(mode):
         pre, ext = [40, 0, 513], [200, 333, 90]
     lens = [p + e for p, e in zip(pre, ext)]
     sc, k8, v8, _, _ = _fp8_scenario(lens, ext, Hq, Hkv, D, page, seed=11, ks=ks, vs=vs)
-    backend, pool = _backend(sc, Hkv, D, page, k8, v8)
+    backend, pool = _backend(sc, Hkv, D, page, k8, v8, fp8_extend=fp8_extend)
     layer = RadixAttention(Hq, D, D ** -0.5, Hkv, 0)
     layer.k_scale, layer.v_scale = torch.tensor(ks), torch.tensor(vs)
     layer.k_scale_float, layer.v_scale_float = ks, vs
@@ -175,10 +199,7 @@ def test_backend_fp8_pool(mode):
     # oracle: quantising store, then fp32 attention over the dequantised pool
     fp8_port.store_kv_fp8(k8, v8, sc.out_cache_loc, sc.k.view(T, Hkv, D), sc.v.view(T, Hkv, D), ks, vs)
     assert torch.equal(pool.k_buffer[0].cpu(), k8) and torch.equal(pool.v_buffer[0].cpu(), v8), "fp8 store not bit-exact"
-    ref = oracle.attention_fp32(sc.q, fp8_port.dequantize(k8, ks), fp8_port.dequantize(v8, vs), sc.req_to_token,
-                                sc.req_pool_indices, torch.tensor(lens), torch.tensor(ext), Hq, Hkv, D, D ** -0.5,
-                                causal=True)
-    assert_close_attn(o, ref, f"backend fp8 {mode}")
+    _check_fp8_extend_rows(o, sc.q, k8, v8, sc, lens, ext, Hq, Hkv, D, ks, vs, fp8_extend, f"backend fp8 {mode} {fp8_extend}")
 
 
 def test_backend_fp8_cuda_graph_decode_replay():
@@ -304,14 +325,15 @@ def test_rope_store_fp8_fused_equals_rotate_then_quantising_store(T, Hq, Hkv, D,
     assert torch.equal(v8.cpu(), vc), "fused rope + e4m3 store: V pool bytes differ"
 
 
-def test_backend_fp8_cuda_graph_extend_replay():
-    """Full-graph prefill over an e4m3 pool: ONE captured step (quantising store, device-bounded dequantising gather,
+@pytest.mark.parametrize("fp8_extend", ["in_kernel", "dequant"])
+def test_backend_fp8_cuda_graph_extend_replay(fp8_extend):
+    """Full-graph prefill over an e4m3 pool: ONE captured step (quantising store, [device-bounded dequantising gather,]
     extend) replayed over other ragged batches."""
     Hq, Hkv, D, page, B, TCAP = 8, 2, 128, 16, 4, 1024
     ks, vs = 0.8, 1.2
     pre0, ext0 = [64, 0, 300, 17], [200, 128, 40, 333]
     sc, k8, v8, _, _ = _fp8_scenario([TCAP] * B, [TCAP] * B, Hq, Hkv, D, page, seed=91, ks=ks, vs=vs)
-    backend, pool = _backend(sc, Hkv, D, page, k8, v8)
+    backend, pool = _backend(sc, Hkv, D, page, k8, v8, fp8_extend=fp8_extend)
     req_pool = backend.req_to_token_pool
     backend.init_cuda_graph_state(B, TCAP, num_q_heads=Hq, head_dim=D)
     layer = RadixAttention(Hq, D, sc.scaling, Hkv, 0)
@@ -364,10 +386,10 @@ def test_backend_fp8_cuda_graph_extend_replay():
         torch.cuda.synchronize()
         kc, vc = pool.k_buffer[0], pool.v_buffer[0]
         assert torch.equal(kc[loc].cpu(), fp8_port.quantize(s_k[:T].cpu(), ks))
-        ref = oracle.attention_fp32(s_q[:T], fp8_port.dequantize(kc, ks), fp8_port.dequantize(vc, vs),
-                                    req_pool.req_to_token, s_req, s_seq.cpu(), s_ext.cpu(), Hq, Hkv, D, sc.scaling,
-                                    causal=True)
-        assert_close_attn(s_out[:T], ref, f"fp8 extend graph replay {ext}")
+        view = types.SimpleNamespace(req_to_token=req_pool.req_to_token.cpu(), req_pool_indices=s_req.cpu())
+        _check_fp8_extend_rows(s_out[:T], s_q[:T].cpu(), kc.cpu(), vc.cpu(), view, s_seq.cpu().tolist(),
+                               s_ext.cpu().tolist(), Hq, Hkv, D, ks, vs, fp8_extend, f"fp8 extend graph replay {ext}",
+                               single_rows_decode=False)  # no host lengths under the graph: every row takes the extend kernel
 
 
 def test_dequant_gather_unique_shares_rows():

@@ -200,3 +200,20 @@ def make_scenario_gpu(prefix_lens: Sequence[int], extend_lens: Sequence[int], Hq
                     extend_lens=list(extend_lens), seq_lens=seq_lens, req_to_token=table.to(device),
                     req_pool_indices=torch.arange(1, B + 1, dtype=torch.int64, device=device),
                     out_cache_loc=loc.to(device), k_cache=kc, v_cache=vc, q=q, k=k, v=v, scaling=D ** -0.5)
+
+
+def assert_close_e4m3_arith(actual: torch.Tensor, emul: torch.Tensor, exact: torch.Tensor, what: str = "") -> None:
+    """Check a kernel that computes in the REFERENCE's e4m3 arithmetic (q and p cast to e4m3:
+    oracle.fp8_port.extend_attention_e4m3_arith = `emul`) when an exact-math result (`exact`) is also at hand.  Two
+    implementations of that arithmetic differ wherever a probability sits at an e4m3 rounding boundary (a 6 % step on
+    one term), so the check is statistical, with the size of the arithmetic's own error as the yardstick:
+      * mean |actual - emul| <= 0.75 * mean |emul - exact| + 5e-4  (closer to the reference arithmetic than that
+        arithmetic is to exact math: measured 0.15 .. 0.65 of it), and
+      * max |actual - exact| <= 2 * max |emul - exact| + 2e-2      (no outlier beyond the arithmetic's own)."""
+    a, e, x = actual.detach().float().cpu(), emul.float().cpu().view(actual.shape), exact.float().cpu().view(actual.shape)
+    assert torch.isfinite(a).all(), f"{what}: non-finite output"
+    arith_mean, arith_max = float((e - x).abs().mean()), float((e - x).abs().max())
+    got_mean, got_max = float((a - e).abs().mean()), float((a - x).abs().max())
+    assert got_mean <= 0.75 * arith_mean + 5e-4, (f"{what}: mean |kernel - e4m3 arithmetic| {got_mean:.3e} vs the "
+                                                  f"arithmetic's own mean error {arith_mean:.3e}")
+    assert got_max <= 2 * arith_max + 2e-2, f"{what}: max |kernel - exact| {got_max:.3e} vs the arithmetic's {arith_max:.3e}"
