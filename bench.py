@@ -379,6 +379,23 @@ def run_b200(args, rank, world, local_rank):
     kern_bytes = nbytes - 2 * 2 * B * Hkv * D * 2  # without the store's read+write
     achieved = kern_bytes / (kern_ms * 1e-3) / 1e9
 
+    # (2b) the same kernel on the same pool with other PAGE PLACEMENTS (rank 0, N = 1; side key, not the headline):
+    #      the headline uses a random permutation of the pool's pages - the worst case.  "contiguous" = every
+    #      request's pages in one ascending run (what alloc_extend hands a fresh prefill); "interleaved" = page j of
+    #      request b at b + j * B (what 64 requests decoding in step get from alloc_decode, one page each per 16 steps).
+    placement = None
+    if world == 1:
+        placement = {"random_pages (headline)": dict(kernel_ms=kern_ms, gbs=achieved)}
+        ppr = c["ctx"] // c["page"]
+        for name, pages in (("contiguous_pages", 1 + torch.arange(B)[:, None] * ppr + torch.arange(ppr)[None, :]),
+                            ("interleaved_pages", 1 + torch.arange(B)[:, None] + torch.arange(ppr)[None, :] * B)):
+            idx2 = (pages[:, :, None] * c["page"] + torch.arange(c["page"])[None, None, :]).reshape(-1).to(torch.int32).to(dev)
+            t2 = time_steps(lambda: ops.decode_attention(q3, kbuf, vbuf, o3, md.kv_indptr, idx2, layer.scaling,
+                                                         max_splits=max_splits, min_chunk=md.min_chunk, workspace=ws,
+                                                         warps=warps, tail_begin=tail_begin),
+                            args.steps, args.warmup) / args.steps
+            placement[name] = dict(kernel_ms=t2, gbs=kern_bytes / (t2 * 1e-3) / 1e9)
+
     # (3) end to end through the AttentionBackend API with HOST buffers (pinned): per step the new
     #     q/k/v rows and the batch metadata go host->device, metadata is rebuilt, the layer runs,
     #     and the attention output comes back device->host.
@@ -588,6 +605,7 @@ def run_b200(args, rank, world, local_rank):
                       traffic=ncu_traffic("decode_kernel<128,bf16> cfg2") if world == 1 else None,
                       kernel="decode_kernel<128,bf16> (+merge)", kernel_ms=kern_ms,
                       peak_source=peaks["src"], frac_of_8tbs=achieved / 8000.0),
+        decode_page_placement=placement,
         cpu_baseline=cpu,
         e2e=dict(value=e2e_graph_val, unit="GB/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h,
                  ms_per_step=e2e_graph_ms, ms_min=fused_lo, ms_max=fused_hi, repetitions=E2E_REPS,

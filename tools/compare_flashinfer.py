@@ -87,8 +87,12 @@ def main():
     nbytes = B * ctx * Hkv * D * 2 * 2 + 2 * B * Hq * D * 2 + B * ctx * 4
     scale = D ** -0.5
 
+    pwarps, pms, ptail = ops.plan_decode(B, Hkv, Hq // Hkv, ctx, 256)  # the launch plan the backend would pick
+    pws = torch.zeros(max(ops.decode_workspace_bytes(B, Hq, D, pms), 16), dtype=torch.uint8, device=DEV)
+
     def b200_decode():
-        return (lambda: ops.decode_attention(q, kc, vc, o_ref, kv_indptr, kv_indices, scale, max_splits=1)), 0.0
+        return (lambda: ops.decode_attention(q, kc, vc, o_ref, kv_indptr, kv_indices, scale, max_splits=pms,
+                                             warps=pwarps, tail_begin=ptail, workspace=pws)), 0.0
 
     leg("cfg2_decode_b200attn", b200_decode, nbytes, "GB/s")
     seq = torch.full((B,), ctx, dtype=torch.int32, device=DEV)
@@ -115,6 +119,27 @@ def main():
         return call, float((o.float() - o_ref.float()).abs().max())
 
     leg("cfg2_decode_trtllm_gen", trt_decode, nbytes, "GB/s")
+    # the same two kernels on other page placements (the random permutation above is the worst case): every request's
+    # pages in one ascending run (a fresh prefill), and page j of request b at b + j * B (64 requests decoding in step)
+    ppr = ctx // page
+    for pname, pages in (("contiguous", 1 + torch.arange(B)[:, None] * ppr + torch.arange(ppr)[None, :]),
+                         ("interleaved", 1 + torch.arange(B)[:, None] + torch.arange(ppr)[None, :] * B)):
+        table2 = pages.to(torch.int32).to(DEV).contiguous()
+        idx2 = (table2.long()[:, :, None] * page + torch.arange(page, device=DEV)).reshape(-1).int()
+
+        def b200_decode2():
+            return (lambda: ops.decode_attention(q, kc, vc, o_ref, kv_indptr, idx2, scale, max_splits=pms,
+                                                 warps=pwarps, tail_begin=ptail, workspace=pws)), 0.0
+
+        leg(f"cfg2_decode_b200attn_{pname}_pages", b200_decode2, nbytes, "GB/s")
+
+        def trt_decode2():
+            from flashinfer.decode import trtllm_batch_decode_with_kv_cache as f
+            call = lambda: f(q, (k4, v4), ws, table2, seq, ctx, bmm1_scale=scale, bmm2_scale=1.0, kv_layout="NHD")
+            o = call()
+            return call, float((o.float() - o_ref.float()).abs().max())
+
+        leg(f"cfg2_decode_trtllm_gen_{pname}_pages", trt_decode2, nbytes, "GB/s")
     del kc, vc, k4, v4, kv_indices
     torch.cuda.empty_cache()
 
