@@ -389,7 +389,11 @@ int b200attn_kv_dequant_gather_unique(const void* k_cache, const void* v_cache, 
  * whether every aligned 16-key group sits in 16 consecutive pool slots (true under the
  * paged allocator for page_size >= 16, paged.py:163-166) -> 16-row tiled TMA boxes;
  * otherwise (page_size 1, fragmented or ragged tiles) tile::gather4 rows.
- * `workspace` is unused (b200attn_extend_workspace_bytes returns 0; kept for ABI symmetry).
+ * `workspace` (nullable; b200attn_extend_workspace_bytes = 64 bytes, zeroed ONCE by the caller): the kernel's work
+ * items are handed out by a device ticket counter that lives at the start of the workspace and is left at zero by
+ * every launch; launches that share a workspace must not overlap (the same rule as b200attn_decode's).  Without a
+ * workspace a process-wide pool of 1024 counter pairs is used round-robin: fine for launches in one stream, and
+ * for concurrent streams as long as fewer than 1024 extend launches separate two overlapping ones.
  * `lse` nullable float[T*Hq] natural log.  `max_qo_len_host` / `total_q_host`
  * are host-side upper bounds used only to size the grid (graph-safe).
  * `custom_mask` (nullable uint8, nonzero = visible) with `mask_indptr` int32[B+1]:

@@ -81,7 +81,8 @@ struct ExtendParams {
   const uint8_t* custom_mask;
   const int32_t* mask_indptr;
   int mask_skip_prefix;
-  int sched_slot;  // this launch's {ticket, CTAs done} pair in g_ext_sched
+  int sched_slot;  // this launch's {ticket, CTAs done} pair in g_ext_sched ...
+  int* sched_ptr;  // ... or, when the caller passed a workspace, the pair at its start (nothing shared across callers)
   float out_scale;  // multiplies the normalised output: v_descale of an e4m3 pool, else 1
 #ifdef EXT_TRACE
   long long* trace;  // dev-only timeline of CTA (0,0,0): [role 0..2][step 0..31][8]
@@ -378,7 +379,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
   // The K producer warp is the scheduler: it draws the ticket of item n+2 when it starts item n (the atomic's latency
   // hides behind the item's K loads) and publishes that descriptor when the loads are issued, one whole item before
   // any role needs it (published one item ahead only, Q(n+1) landed ~1.4 us late: 1131 -> 1092 TFLOP/s on cfg3).
-  int* const sched = g_ext_sched + 2 * p.sched_slot;
+  int* const sched = p.sched_ptr != nullptr ? p.sched_ptr : g_ext_sched + 2 * p.sched_slot;
   auto describe = [&](int id) {  // id -> (request, kv head, pair)
     ItemDesc d;
     d.q_beg = d.kv_beg = d.L = d.kvh = d.pair = d.pad0 = d.pad1 = 0;
@@ -1060,7 +1061,8 @@ static int launch_extend(const CUtensorMap& tq, const CUtensorMap& tk, const CUt
 
 }  // namespace b200attn
 
-extern "C" int64_t b200attn_extend_workspace_bytes(int32_t, int64_t, int32_t) { return 0; }
+// the launch's two ticket counters (zeroed once by the caller, left at zero by every launch)
+extern "C" int64_t b200attn_extend_workspace_bytes(int32_t, int64_t, int32_t) { return 64; }
 
 // kv_fp8: k_cache / v_cache hold e4m3 bytes, kv_stride counts BYTES per slot row (16-bit pools: elements)
 static int extend_impl(const void* q, int64_t q_stride, const void* k_cache,
@@ -1075,10 +1077,6 @@ static int extend_impl(const void* q, int64_t q_stride, const void* k_cache,
                        int64_t workspace_bytes, void* stream, bool kv_fp8, float k_descale, float v_descale) {
   using namespace b200attn;
   B2_CHECK_ARG(logit_cap >= 0.f, "extend: negative logit_cap");
-#ifndef EXT_TRACE
-  (void)workspace;
-  (void)workspace_bytes;
-#endif
   (void)page_size;  // rows are gathered token-granular: any page size, no contiguity assumption
   B2_CHECK_ARG(B >= 0 && total_q_host >= 0 && max_qo_len_host >= 0, "extend: negative size");
   if (B == 0 || total_q_host == 0 || max_qo_len_host == 0) return B200ATTN_OK;
@@ -1147,6 +1145,14 @@ static int extend_impl(const void* q, int64_t q_stride, const void* k_cache,
   p.mask_skip_prefix = mask_skip_prefix;
 #ifdef EXT_TRACE
   p.trace = workspace_bytes >= (6 * 32 * 8 + 2 * 160) * 8 ? (long long*)workspace : nullptr;
+  p.sched_ptr = nullptr;  // the dev build's workspace is the trace buffer
+#else
+  // Ticket counters: the caller's workspace when there is one (launches that share a workspace are serialised by
+  // the workspace contract, so nothing is shared between independent callers / streams / graphs); otherwise a
+  // process-wide pool of kExtSchedSlots pairs handed out round-robin.
+  B2_CHECK_ARG(workspace == nullptr || workspace_bytes < 8 || ((uintptr_t)workspace & 3) == 0,
+               "extend: workspace must be 4-byte aligned");
+  p.sched_ptr = (workspace != nullptr && workspace_bytes >= 8) ? reinterpret_cast<int*>(workspace) : nullptr;
 #endif
   const int max_qtiles = (max_qo_len_host + kExtM - 1) / kExtM;
   cudaStream_t st = (cudaStream_t)stream;

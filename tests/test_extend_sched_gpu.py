@@ -65,6 +65,31 @@ def test_two_streams_at_once():
     assert torch.equal(ta[3], ea) and torch.equal(tb[3], eb)
 
 
+def test_counters_in_the_callers_workspace():
+    """With a workspace the ticket counters live at its start: two streams with a workspace each, many launches, the
+    counters are back at zero afterwards."""
+    (sa, ta), (sb, tb) = _two_batches()
+    ea, eb = _launch(sa, ta).clone(), _launch(sb, tb).clone()
+    torch.cuda.synchronize()
+    assert ops.extend_workspace_bytes(4, 100, 8) == 64
+    wa, wb = (torch.zeros(64, dtype=torch.uint8, device="cuda") for _ in range(2))
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+
+    def go(sc, t, ws):
+        q, kc, vc, o, qo_indptr, kv_indptr, kv_indices = t
+        ops.extend_attention(q, kc, vc, o, qo_indptr, kv_indptr, kv_indices, sc.scaling, causal=True,
+                             page_size=sc.page_size, max_qo_len=max(sc.extend_lens), workspace=ws)
+
+    for _ in range(40):
+        with torch.cuda.stream(s1):
+            go(sa, ta, wa)
+        with torch.cuda.stream(s2):
+            go(sb, tb, wb)
+    torch.cuda.synchronize()
+    assert torch.equal(ta[3], ea) and torch.equal(tb[3], eb)
+    assert int(wa.sum()) == 0 and int(wb.sum()) == 0
+
+
 def test_grid_larger_than_item_list():
     # max_qo_len is only an upper bound: claim 4096 rows per request while the real ones have 1..40
     sc = make_scenario([100, 0, 900], [1, 40, 7], 8, 2, 128, 16, seed=603, pool_slack=1.05)
