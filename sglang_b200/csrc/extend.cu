@@ -852,18 +852,19 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         if (rows_i == kExtM && p.o_tma) {
           // Full tile: O leaves through shared memory and the copy engine.  A thread owns a ROW, so direct stores
           // are 32 scattered 16-byte pieces per warp instruction (measured: 4.7 k cycles per item, LSU-bound);
-          // here each 128 x 32 slab is written to a 64B-swizzled staging buffer (conflict free) and one thread
-          // issues a 2-D TMA store.  Two buffers per tile: slab j waits only for the store of slab j-2.
-          const uint32_t obuf = smem0 + S::kO + i * 2 * S::kOSlab;
-          const int bar_id = 1 + i;  // named barrier of this warpgroup
+          // here each WARP writes its 32 rows x 32 columns to a 64B-swizzled staging block (conflict free) and its
+          // lane 0 issues a 2-D TMA store of that block.  Two blocks per warp: slab j waits only for the store of
+          // slab j-2, and nothing is synchronised wider than the warp (it was two 128-thread named barriers per slab).
+          const int wq = warp & 3;  // warp within the warpgroup = 32-row quarter of the tile
+          const uint32_t obuf = smem0 + S::kO + i * 2 * S::kOSlab + wq * (32 * 64);
 #pragma unroll
           for (int c = 0; c < D / kExtOSlabCols; ++c) {
             uint32_t v[32];
             tmem_ld32(col_o + c * 32, v);
-            if (row == 0) asm volatile("cp.async.bulk.wait_group.read 1;\n" ::: "memory");
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;\n" ::: "memory");
             tmem_wait_ld();
-            asm volatile("bar.sync %0, 128;\n" ::"r"(bar_id) : "memory");  // buffer (c & 1) is free again
-            const uint32_t dst = obuf + (c & 1) * S::kOSlab + row * 64;
+            __syncwarp();  // block (c & 1) of this warp is free again
+            const uint32_t dst = obuf + (c & 1) * S::kOSlab + lane * 64;
 #pragma unroll
             for (int e = 0; e < 32; e += 8) {
               uint4 w;
@@ -871,17 +872,17 @@ __global__ void __launch_bounds__(kExtThreads, 1)
               w.y = pack2<kBf16>(__uint_as_float(v[e + 2]) * inv, __uint_as_float(v[e + 3]) * inv);
               w.z = pack2<kBf16>(__uint_as_float(v[e + 4]) * inv, __uint_as_float(v[e + 5]) * inv);
               w.w = pack2<kBf16>(__uint_as_float(v[e + 6]) * inv, __uint_as_float(v[e + 7]) * inv);
-              const uint32_t chunk = (uint32_t)(e >> 3) ^ ((uint32_t)(row >> 1) & 3u);  // CU_TENSOR_MAP_SWIZZLE_64B
+              const uint32_t chunk = (uint32_t)(e >> 3) ^ ((uint32_t)(lane >> 1) & 3u);  // CU_TENSOR_MAP_SWIZZLE_64B
               asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(dst + chunk * 16), "r"(w.x),
                            "r"(w.y), "r"(w.z), "r"(w.w)
                            : "memory");
             }
             fence_proxy_async_smem();
-            asm volatile("bar.sync %0, 128;\n" ::"r"(bar_id) : "memory");
-            if (row == 0) {
+            __syncwarp();
+            if (lane == 0) {
               asm volatile(
                   "cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];\n" ::"l"(&tm_o),
-                  "r"(obuf + (c & 1) * S::kOSlab), "r"(h * D + c * kExtOSlabCols), "r"(d.q_beg + m0)
+                  "r"(obuf + (c & 1) * S::kOSlab), "r"(h * D + c * kExtOSlabCols), "r"(d.q_beg + m0 + wq * 32)
                   : "memory");
               asm volatile("cp.async.bulk.commit_group;\n" ::: "memory");
             }
@@ -914,8 +915,8 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         ++nq_my;
       }
     }
-    // the staged output slabs must have left shared memory (and be globally visible) before the CTA retires
-    if ((threadIdx.x & 127) == 0) asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory");
+    // the staged output blocks must have left shared memory (and be globally visible) before the CTA retires
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
@@ -1115,7 +1116,7 @@ static int extend_impl(const void* q, int64_t q_stride, const void* k_cache,
   if (rc) return rc;
   const CUtensorMap &tk = *ptk, &tv = *ptv, &tkb = *ptkb, &tvb = *ptvb;
   rc = make_tensor_map_2d(&to, o, (uint64_t)total_q_host, (uint64_t)Hq * D, (uint64_t)o_stride * 2,
-                          kExtOSlabCols, kExtM, CU_TENSOR_MAP_SWIZZLE_64B);
+                          kExtOSlabCols, 32, CU_TENSOR_MAP_SWIZZLE_64B);  // one warp's 32 rows x 32 columns
   if (rc) return rc;
   ExtendParams p;
   p.o_tma = 1;
