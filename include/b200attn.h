@@ -423,7 +423,8 @@ int b200attn_extend(const void* q, int64_t q_stride, const void* k_cache,
  * a pool (extend_attention.py:523 `tl.dot(q.to(k.dtype), k)`, :596 `p = p.to(v.dtype)`; k / v descales as in
  * triton_backend.py:1418-1420): Q is cast to e4m3 in shared memory, P to e4m3 in tensor memory, both contractions
  * run as tcgen05.mma.kind::f8f6f4 on the pool's bytes, k_descale rides on the softmax scale and v_descale on the
- * output.  head_dim 128; q / o stay bf16 / fp16 (`dtype`).  Everything else as b200attn_extend. */
+ * output.  head_dim 64 or 128 (64-byte / 128-byte e4m3 rows); q / o stay bf16 / fp16 (`dtype`).  Everything else
+ * as b200attn_extend. */
 int b200attn_extend_fp8kv(const void* q, int64_t q_stride, const void* k_cache,
                           const void* v_cache, int64_t kv_stride_bytes, int64_t num_slots,
                           void* o, int64_t o_stride, float* lse, const int32_t* qo_indptr,

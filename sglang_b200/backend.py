@@ -123,11 +123,11 @@ class B200AttnBackend(_Base):
             deterministic = bool(getattr(getattr(model_runner, "server_args", None),
                                          "enable_deterministic_inference", False))
         self.deterministic = bool(deterministic)
-        # Extend over an e4m3 pool.  "in_kernel" (default, head_dim 128): the tcgen05 kernel contracts on the pool's
+        # Extend over an e4m3 pool.  "in_kernel" (default): the tcgen05 kernel contracts on the pool's
         # bytes with Q and P cast to e4m3 - the arithmetic of the reference's Triton kernels for such a pool
         # (extend_attention.py:523,596) - no scratch copy, faster than the 16-bit pool.  "dequant": the batch's rows
         # are dequantised once into a 16-bit scratch and Q / P stay 16-bit: closer to the exact math over the
-        # dequantised pool than the reference itself, ~5 % slower; also what head_dim 64 takes.
+        # dequantised pool than the reference itself, ~5 % slower.
         self.fp8_extend = fp8_extend or os.environ.get("B200ATTN_FP8_EXTEND", "in_kernel")
         if self.fp8_extend not in ("in_kernel", "dequant"):
             raise ValueError("fp8_extend must be 'in_kernel' or 'dequant'")
@@ -573,7 +573,7 @@ class B200AttnBackend(_Base):
             kv_idx = self._kv_indices(layer, md)
             ek, ev, eidx, escale = kbuf, vbuf, kv_idx, layer.scaling
             ext_dsc = {}
-            if fp8 and D == 128 and self.fp8_extend == "in_kernel":
+            if fp8 and self.fp8_extend == "in_kernel":  # head_dim 64 and 128 (the two the tcgen05 kernel has)
                 ext_dsc = dsc  # b200attn_extend_fp8kv: contracts on the e4m3 bytes of the pool itself
             elif fp8:
                 # the tcgen05 kernel takes 16-bit K/V operands: gather the batch's rows once into a 16-bit scratch

@@ -265,8 +265,8 @@ __device__ __forceinline__ void derive_tiles(const ItemDesc& d, const ExtendPara
 // written to TMEM as e4m3, and both contractions run as tcgen05.mma.kind::f8f6f4 (K = 32 per instruction) straight
 // on the pool's bytes: what the reference's Triton kernels compute for such a pool (extend_attention.py:523
 // `tl.dot(q.to(k.dtype), k)`, :596 `p = p.to(v.dtype)`), with k_descale in the softmax scale and v_descale in the
-// output scale (triton_backend.py:1418-1420).  No dequantised scratch copy of the pool rows.  head_dim 128 only: a
-// K/V row is then exactly one 128-byte swizzle row.
+// output scale (triton_backend.py:1418-1420).  No dequantised scratch copy of the pool rows.  A K/V row is exactly
+// one swizzle row: 128 bytes at head_dim 128, 64 bytes (SWIZZLE_64B maps and descriptors) at head_dim 64.
 template <int D, bool kBf16, bool kFp8 = false>
 __global__ void __launch_bounds__(kExtThreads, 1)
     extend_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
@@ -276,7 +276,10 @@ __global__ void __launch_bounds__(kExtThreads, 1)
   using namespace sm100;
   using S = ExtSmem<D>;
   constexpr int kHalves = D / 64;  // 64-column halves of the head dim (16-bit tiles: Q always, K/V of 16-bit pools)
-  static_assert(!kFp8 || D == 128, "e4m3 pools: head_dim 128");
+  // K / V / e4m3-Q tile row pitch: 128 bytes (16-bit tiles in 64-column halves; e4m3 rows of head_dim 128), or the
+  // 64-byte e4m3 rows of head_dim 64 (SWIZZLE_64B tensor maps and matrix descriptors)
+  constexpr int kRowB = kFp8 ? D : 128;
+  constexpr bool kSw64 = kFp8 && D == 64;
   constexpr int kHalvesKV = kFp8 ? 1 : kHalves;                  // 128-byte column groups of a K/V row
   constexpr uint32_t kKVTileBytes = kFp8 ? kExtN * D : S::kTile;  // bytes of one K or V tile as loaded
   // e4m3 copy of Q tile i: the upper (unused) half of K ring stage i
@@ -508,13 +511,13 @@ __global__ void __launch_bounds__(kExtThreads, 1)
                 for (int g = 0; g < kExtN / kExtBoxRows; ++g)
 #pragma unroll
                   for (int hf = 0; hf < kHalvesKV; ++hf)
-                    tma_load_2d(dst + hf * S::kHalf + g * kExtBoxRows * 128, tm_b, bar(bar_full + st),
+                    tma_load_2d(dst + hf * S::kHalf + g * kExtBoxRows * kRowB, tm_b, bar(bar_full + st),
                                 col + hf * 64, rows[g]);
               }
             } else {
 #pragma unroll
               for (int hf = 0; hf < kHalvesKV; ++hf)
-                tma_gather4(dst + hf * S::kHalf + lane * 4 * 128, tm_g, bar(bar_full + st), col + hf * 64,
+                tma_gather4(dst + hf * S::kHalf + lane * 4 * kRowB, tm_g, bar(bar_full + st), col + hf * 64,
                             r[0], r[1], r[2], r[3]);
             }
             load_slots(j + 1);
@@ -540,8 +543,10 @@ __global__ void __launch_bounds__(kExtThreads, 1)
         const uint32_t smem_u = __shfl_sync(0xffffffffu, smem0, 0);
         const uint32_t barb = smem_u + S::kBar;
         // descriptor = constant high word | (address >> 4) in the low 14 bits
-        constexpr uint64_t kDescKMajor = smem_desc_sw128_hi(16, 1024);     // Q, K: K-major
-        constexpr uint64_t kDescVMn = smem_desc_sw128_hi(S::kHalf, 1024);  // V: MN-major
+        constexpr uint64_t kDescKMajor =  // Q, K: K-major, 8-row swizzle atoms
+            kSw64 ? smem_desc_sw64_hi(16, 512) : smem_desc_sw128_hi(16, 1024);
+        constexpr uint64_t kDescVMn =     // V: MN-major
+            kSw64 ? smem_desc_sw64_hi(S::kHalf, 512) : smem_desc_sw128_hi(S::kHalf, 1024);
         auto desc = [](uint64_t hi, uint32_t addr) { return hi | (uint64_t)((addr & 0x3FFFF) >> 4); };
         const uint32_t qa = kFp8 ? smem_u + kQ8Off + i * S::kTile : smem_u + S::kQ + i * S::kTile;
         const uint32_t ts = tmem_u + kColS + i * 128, to = tmem_u + kColO + i * 128;
@@ -562,7 +567,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
             // S_i[(g + c) & 1] = Q_i K_c^T over the 64 keys of chunk c (both operands K-major from smem)
             auto issue_qk = [&](int c) {
               const uint32_t ka =
-                  smem_u + S::kK + ((ktl + (c >> 1)) % kExtStages) * S::kTile + (c & 1) * (kExtC * 128);
+                  smem_u + S::kK + ((ktl + (c >> 1)) % kExtStages) * S::kTile + (c & 1) * (kExtC * kRowB);
               const int hb = (g + c) & 1;
 #pragma unroll
 #ifdef EXT_ABL_NOQK
@@ -584,7 +589,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
             // O_i (+)= P_i(c) V_c  (A = bf16 P in its S half of TMEM, B = V MN-major from smem)
             auto issue_pv = [&](int c) {
               const uint32_t va =
-                  smem_u + S::kV + ((ktl + (c >> 1)) % kExtStages) * S::kTile + (c & 1) * (kExtC * 128);
+                  smem_u + S::kV + ((ktl + (c >> 1)) % kExtStages) * S::kTile + (c & 1) * (kExtC * kRowB);
               const int hb = (g + c) & 1;
 #pragma unroll
 #ifdef EXT_ABL_NOPV
@@ -595,7 +600,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
                 // 16 keys per step = 8 packed TMEM columns of A; 2 KB down the V tile; d-halves 16 KB apart
                 // (e4m3: 32 keys per step = 8 columns of four; 4 KB down the tile; one 128-byte group of d)
                 if constexpr (kFp8)
-                  umma_ts_f8(to, ts + hb * kExtC + ks * 8, desc(kDescVMn, va + ks * 4096), idesc_pv,
+                  umma_ts_f8(to, ts + hb * kExtC + ks * 8, desc(kDescVMn, va + ks * 32 * kRowB), idesc_pv,
                              (c > 0 || ks > 0) ? 1u : 0u);
                 else
                   umma_ts(to, ts + hb * kExtC + ks * 8, desc(kDescVMn, va + ks * 2048), idesc_pv,
@@ -672,7 +677,8 @@ __global__ void __launch_bounds__(kExtThreads, 1)
           // row as e4m3 into the K-major e4m3 tile the QK instruction reads (one 128-byte swizzled row).
           mbar_wait(bar(kBarQ + i), nq_my & 1);
           const uint8_t* qrow = smem + S::kQ + i * S::kTile + row * 128;
-          uint8_t* q8row = smem + kQ8Off + i * S::kTile + row * 128;
+          uint8_t* q8row = smem + kQ8Off + i * S::kTile + row * kRowB;
+          const int swz8 = kSw64 ? (row >> 1) & 3 : row & 7;  // 16-byte chunk XOR of the e4m3 row's swizzle mode
 #pragma unroll
           for (int j = 0; j < D / 16; ++j) {  // 16 columns -> one 16-byte chunk of the e4m3 row
             uint32_t w[4];
@@ -688,7 +694,7 @@ __global__ void __launch_bounds__(kExtThreads, 1)
                                  ((uint32_t)__nv_cvt_float2_to_fp8x2(f1, __NV_SATFINITE, __NV_E4M3) << 16);
               }
             }
-            *reinterpret_cast<uint4*>(q8row + ((j ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+            *reinterpret_cast<uint4*>(q8row + ((j ^ swz8) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
           }
           fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
           mbar_arrive(bar(kBarQ8 + i));
@@ -1094,7 +1100,9 @@ static int extend_impl(const void* q, int64_t q_stride, const void* k_cache,
                "extend: tensors must be 16-byte aligned");
   if (dtype != B200ATTN_BF16 && dtype != B200ATTN_FP16) B2_UNSUPPORTED("extend: dtype %d", dtype);
   if (D != 64 && D != 128) B2_UNSUPPORTED("extend: head_dim %d (supported: 64, 128)", D);
-  if (kv_fp8 && D != 128) B2_UNSUPPORTED("extend over an e4m3 pool: head_dim %d (supported: 128)", D);
+  const bool sw64 = kv_fp8 && D == 64;  // 64-byte e4m3 rows
+  const uint32_t kv_box_cols = sw64 ? 32 : 64;
+  const CUtensorMapSwizzle kv_swz = sw64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B;
   // the pool maps count 16-bit columns: an e4m3 row of Hkv * D bytes is Hkv * D / 2 of them
   const uint64_t kv_cols = kv_fp8 ? (uint64_t)Hkv * D / 2 : (uint64_t)Hkv * D;
   const uint64_t kv_row_bytes = kv_fp8 ? (uint64_t)kv_stride : (uint64_t)kv_stride * 2;
@@ -1104,15 +1112,15 @@ static int extend_impl(const void* q, int64_t q_stride, const void* k_cache,
   int rc = make_tensor_map_2d(&tq, q, (uint64_t)total_q_host, (uint64_t)Hq * D,
                               (uint64_t)q_stride * 2, 64, kExtM);
   if (rc) return rc;
-  rc = tensor_map_cached(&ptk, k_cache, (uint64_t)num_slots, kv_cols, kv_row_bytes, 64, 1);
+  rc = tensor_map_cached(&ptk, k_cache, (uint64_t)num_slots, kv_cols, kv_row_bytes, kv_box_cols, 1, kv_swz);
   if (rc) return rc;
-  rc = tensor_map_cached(&ptv, v_cache, (uint64_t)num_slots, kv_cols, kv_row_bytes, 64, 1);
+  rc = tensor_map_cached(&ptv, v_cache, (uint64_t)num_slots, kv_cols, kv_row_bytes, kv_box_cols, 1, kv_swz);
   if (rc) return rc;
-  rc = tensor_map_cached(&ptkb, k_cache, (uint64_t)num_slots, kv_cols, kv_row_bytes, 64,
-                         kExtBoxRows);
+  rc = tensor_map_cached(&ptkb, k_cache, (uint64_t)num_slots, kv_cols, kv_row_bytes, kv_box_cols,
+                         kExtBoxRows, kv_swz);
   if (rc) return rc;
-  rc = tensor_map_cached(&ptvb, v_cache, (uint64_t)num_slots, kv_cols, kv_row_bytes, 64,
-                         kExtBoxRows);
+  rc = tensor_map_cached(&ptvb, v_cache, (uint64_t)num_slots, kv_cols, kv_row_bytes, kv_box_cols,
+                         kExtBoxRows, kv_swz);
   if (rc) return rc;
   const CUtensorMap &tk = *ptk, &tv = *ptv, &tkb = *ptkb, &tvb = *ptvb;
   rc = make_tensor_map_2d(&to, o, (uint64_t)total_q_host, (uint64_t)Hq * D, (uint64_t)o_stride * 2,
@@ -1157,9 +1165,12 @@ static int extend_impl(const void* q, int64_t q_stride, const void* k_cache,
 #endif
   const int max_qtiles = (max_qo_len_host + kExtM - 1) / kExtM;
   cudaStream_t st = (cudaStream_t)stream;
-  if (kv_fp8)
+  if (kv_fp8 && D == 128)
     return dtype == B200ATTN_BF16 ? launch_extend<128, true, true>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st)
                                   : launch_extend<128, false, true>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st);
+  if (kv_fp8)
+    return dtype == B200ATTN_BF16 ? launch_extend<64, true, true>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st)
+                                  : launch_extend<64, false, true>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st);
   if (D == 128)
     return dtype == B200ATTN_BF16 ? launch_extend<128, true>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st)
                                   : launch_extend<128, false>(tq, tk, tv, tkb, tvb, to, p, max_qtiles, st);

@@ -187,6 +187,11 @@ __host__ __device__ constexpr uint64_t smem_desc_sw128_hi(uint32_t lbo_bytes, ui
   return ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) | (1ull << 46) |
          (2ull << 61);
 }
+// the same for SWIZZLE_64B tiles (64-byte rows: e4m3 operands of head_dim 64)
+__host__ __device__ constexpr uint64_t smem_desc_sw64_hi(uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) | (1ull << 46) |
+         (4ull << 61);
+}
 // exactly one lane of a converged warp returns true
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;

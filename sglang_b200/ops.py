@@ -755,7 +755,7 @@ def extend_attention(
     """Ragged prefix+extend attention: ``q [T,Hq,D]`` -> ``o [T,Hq,D]``.
 
     uint8 / float8_e4m3fn caches are an e4m3 pool: the kernel casts Q and P to e4m3 and contracts on the pool's bytes
-    (``b200attn_extend_fp8kv``, what the reference's Triton kernel does: extend_attention.py:523,596), head_dim 128.
+    (``b200attn_extend_fp8kv``, what the reference's Triton kernel does: extend_attention.py:523,596), head_dim 64 / 128.
 
     Mirrors ``extend_attention_fwd_unified`` (python/sglang/kernels/ops/attention/
     extend_attention.py:963-1410): one KV source (the pool) indexed by

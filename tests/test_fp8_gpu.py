@@ -165,11 +165,12 @@ def _check_fp8_extend_rows(o, q, k8, v8, sc, lens, ext, Hq, Hkv, D, ks, vs, fp8_
         assert_close_e4m3_arith(o[~single], emul[~single], exact[~single], what + " (extend rows)")
 
 
+@pytest.mark.parametrize("D", [128, 64])
 @pytest.mark.parametrize("fp8_extend", ["in_kernel", "dequant"])
 @pytest.mark.parametrize("mode", ["extend", "mixed", "decode"])
-def test_backend_fp8_pool(mode, fp8_extend):
+def test_backend_fp8_pool(mode, fp8_extend, D):
     """Store (quantising) + attention through B200AttnBackend on a float8_e4m3fn pool with layer k/v scales."""
-    Hq, Hkv, D, page = 16, 4, 128, 16
+    Hq, Hkv, page = 16, 4, 16
     ks, vs = 0.6, 0.9
     if mode == "decode":
         pre, ext = [300, 17, 1024], [1, 1, 1]

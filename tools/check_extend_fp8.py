@@ -89,6 +89,9 @@ run("one tile, no prefix", [0], [128], 4, 4, 128, 16)
 run("one request, prefix", [300], [200], 8, 2, 128, 16)
 run("ragged, G=4", [0, 700, 33, 4000], [1280, 513, 2047, 96], 32, 8, 128, 16)
 run("ragged, G=7, bidirectional, page 1", [17, 0, 300], [5, 3000, 129], 28, 4, 128, 1, causal=False)
+run("head_dim 64: one tile", [0], [128], 4, 4, 64, 16)
+run("head_dim 64: ragged, G=7, page 1", [17, 0, 300, 2000], [5, 3000, 129, 700], 14, 2, 64, 1)
+run("head_dim 64: ragged, G=2, bidirectional", [0, 700, 33], [1280, 513, 2047], 8, 4, 64, 16, causal=False)
 if "--time" in sys.argv:
     from tools.compare_flashinfer import timed
     from tools.sweep_extend_variants import make
