@@ -201,7 +201,7 @@ def attention_fp32(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor
                    req_pool_indices: torch.Tensor, seq_lens: torch.Tensor, extend_seq_lens: torch.Tensor,
                    num_q_heads: int, num_kv_heads: int, head_dim: int, scaling: float, causal: bool,
                    return_lse: bool = False, window_left: int = -1, logit_cap: float = 0.0, sinks=None,
-                   custom_masks=None, skip_prefix_custom_mask: bool = True):
+                   custom_masks=None, skip_prefix_custom_mask: bool = True, e4m3_arith: bool = False):
     """Independent fp32-softmax reference (works on any device, used at large sizes).
 
     Restates the reference kit's ``_dense_attention_reference``
@@ -217,12 +217,20 @@ def attention_fp32(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor
     ``[E, L]`` block (True = visible), the TARGET_VERIFY tree mask of ``dense_attention_reference_with_custom_mask``
     (dense_attention.py:858-905); with ``skip_prefix_custom_mask`` the prefix keys stay visible
     (extend_attention.py:467-479).
+
+    ``e4m3_arith``: the arithmetic of the reference's Triton EXTEND kernel over an e4m3 pool (``k_cache`` / ``v_cache``
+    are then the DEQUANTISED pools): the query is cast to e4m3 (``q.to(k.dtype)``, extend_attention.py:523/1174) and
+    the un-normalised probabilities are cast to e4m3 before the second contraction (``p.to(v.dtype)``, :596/1248) while
+    the denominator sums them un-rounded.  Agrees with ``fp8_port.extend_attention_e4m3_arith`` (which is pinned to
+    the kernel's recorded output) and adds the feature flags.
     """
     T = q.shape[0]
     G = num_q_heads // num_kv_heads
     out = torch.empty((T, num_q_heads, head_dim), dtype=torch.float32, device=q.device)
     lse = torch.empty((T, num_q_heads), dtype=torch.float32, device=q.device)
     qf = q.view(T, num_q_heads, head_dim).float()
+    if e4m3_arith:
+        qf = qf.to(torch.float8_e4m3fn).float()
     start = 0
     for i in range(seq_lens.shape[0]):
         L, E = int(seq_lens[i]), int(extend_seq_lens[i])
@@ -243,7 +251,16 @@ def attention_fp32(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor
             if skip_prefix_custom_mask:
                 allowed[..., :L - E] = True
             s = s.masked_fill(~allowed, -math.inf)
-        if sinks is not None:
+        if e4m3_arith:
+            sk = sinks.to(s.device).float().view(-1, 1, 1).expand(-1, E, 1) if sinks is not None else None
+            full = s if sk is None else torch.cat([s, sk], dim=-1)
+            m = full.max(dim=-1, keepdim=True).values
+            m = torch.where(torch.isfinite(m), m, torch.zeros_like(m))
+            pu = torch.exp(full - m)
+            den = pu.sum(dim=-1, keepdim=True)
+            lse[start:start + E] = (m + torch.log(den)).squeeze(-1).transpose(0, 1)
+            p = pu[..., :L].to(torch.float8_e4m3fn).float() / den
+        elif sinks is not None:
             sk = sinks.to(s.device).float().view(-1, 1, 1).expand(-1, E, 1)
             full = torch.cat([s, sk], dim=-1)
             lse[start:start + E] = torch.logsumexp(full, dim=-1).transpose(0, 1)
