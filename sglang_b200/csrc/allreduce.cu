@@ -221,8 +221,13 @@ extern "C" int b200attn_allreduce_nvls(const void* in, void* out, void* local_pa
   p.dtype = dtype;
   p.n16 = bytes / 16;
   cudaStream_t st = (cudaStream_t)stream;
-  if (in != nullptr && out != nullptr && local_small != nullptr && mc_small != nullptr && bytes <= kArSmallMax &&
-      bytes * world <= 4 * kArSmallMax) {  // every rank pulls the whole message through the switch: small ones only
+  // one-shot limit: B200ATTN_AR_ONESHOT_MAX (bytes, read once; 0 forces the two-shot form) overrides the default
+  static const int64_t oneshot_max = [] {
+    const char* e = getenv("B200ATTN_AR_ONESHOT_MAX");
+    return e != nullptr ? (int64_t)atoll(e) : kArSmallMax;
+  }();
+  if (in != nullptr && out != nullptr && local_small != nullptr && mc_small != nullptr && bytes <= oneshot_max &&
+      bytes <= kArSmallMax && bytes * world <= 4 * kArSmallMax) {  // every rank pulls the whole message through the switch: small ones only
     B2_CHECK_ARG((((uintptr_t)local_small | (uintptr_t)mc_small) & 15) == 0, "allreduce: small region alignment");
     const dim3 g1((unsigned)((bytes + kArPiece - 1) / kArPiece)), b1(kArThreads);
     if (dtype == B200ATTN_BF16) {

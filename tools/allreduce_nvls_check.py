@@ -142,7 +142,8 @@ def main():
 
     ref_buf = symm.empty(64 << 19, dtype=torch.bfloat16, device=dev)
     symm.rendezvous(ref_buf, dist.group.WORLD.group_name)
-    for shape, what in (((1, 4096), "1 token x 4096"), ((64, 4096), "cfg2 decode: 64 tokens x 4096"),
+    for shape, what in (((1, 4096), "1 token x 4096"), ((8, 4096), "8 x 4096"), ((16, 4096), "16 x 4096"),
+                        ((32, 4096), "32 x 4096"), ((64, 4096), "cfg2 decode: 64 tokens x 4096"),
                         ((64, 8192), "cfg5 decode step: 64 x 8192"), ((2048, 4096), "prefill chunk 2048 x 4096"),
                         ((8192, 4096), "prefill chunk 8192 x 4096")):
         x = torch.randn(shape, device=dev, generator=g).to(torch.bfloat16)
