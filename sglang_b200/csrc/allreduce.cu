@@ -58,23 +58,23 @@ struct ArParams {
   int64_t n16;        // payload size in 16-byte units
 };
 
-// barrier_b without a remote round trip: the signal is a POSTED release store of this CTA's call counter into the
-// peer's slot, the wait polls the local slot until it reaches the counter.  The counter of CTA b lives in the local
-// flag block (after the slots) and advances by one per barrier; every rank runs the same sequence of calls with the
-// same grids, so the CTAs b of all ranks count in step.
-__device__ __forceinline__ void ar_barrier(const ArParams& p) {
-  __shared__ uint32_t s_epoch;
+// barrier_b without a remote round trip: the signal is a POSTED release store of this CTA's barrier number into the
+// peer's slot, the wait polls the local slot until it reaches that number.  The number of CTA b's last barrier lives
+// in the local flag block (after the slots); it is read ONCE when the kernel starts (ar_epoch_begin, overlapped with
+// the staging copy) and written back when it ends; every rank runs the same sequence of calls with the same grids,
+// so the CTAs b of all ranks count in step.
+__device__ __forceinline__ void ar_epoch_begin(const ArParams& p, uint32_t* s_epoch) {
+  if (threadIdx.x == 0) *s_epoch = p.flags[p.rank][kArMaxBlocks * kArMaxWorld + blockIdx.x];
+}
+__device__ __forceinline__ void ar_epoch_end(const ArParams& p, const uint32_t* s_epoch) {
+  if (threadIdx.x == 0) p.flags[p.rank][kArMaxBlocks * kArMaxWorld + blockIdx.x] = *s_epoch;
+}
+__device__ __forceinline__ void ar_barrier(const ArParams& p, uint32_t* s_epoch) {
   __threadfence_system();
-  __syncthreads();
+  __syncthreads();  // also orders ar_epoch_begin's shared store before the reads below
   const int t = threadIdx.x;
-  if (t == 0) {
-    uint32_t* ctr = p.flags[p.rank] + kArMaxBlocks * kArMaxWorld + blockIdx.x;
-    s_epoch = *ctr + 1u;
-    *ctr = s_epoch;
-  }
-  __syncthreads();
+  const uint32_t e = *s_epoch + 1u;
   if (t < p.world) {
-    const uint32_t e = s_epoch;
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.flags[t] + (blockIdx.x * kArMaxWorld + p.rank)), "r"(e)
                  : "memory");
     const uint32_t* mine = p.flags[p.rank] + (blockIdx.x * kArMaxWorld + t);
@@ -84,6 +84,7 @@ __device__ __forceinline__ void ar_barrier(const ArParams& p) {
     } while ((int32_t)(v - e) < 0);
   }
   __syncthreads();
+  if (t == 0) *s_epoch = e;
 }
 
 template <int kDtype>
@@ -120,8 +121,10 @@ __device__ __forceinline__ void ar_copy(uint4* dst, const uint4* src, int64_t c0
 
 template <int kDtype>
 __global__ void __launch_bounds__(kArThreads) allreduce_nvls_kernel(const ArParams p) {
+  __shared__ uint32_t s_epoch;
   pdl_wait();
   pdl_trigger();
+  ar_epoch_begin(p, &s_epoch);
   const int64_t per_block = (p.n16 + gridDim.x - 1) / gridDim.x;
   const int64_t c0 = (int64_t)blockIdx.x * per_block;
   const int64_t c1 = c0 + per_block < p.n16 ? c0 + per_block : p.n16;
@@ -129,7 +132,7 @@ __global__ void __launch_bounds__(kArThreads) allreduce_nvls_kernel(const ArPara
   ATRACE(0);
   if (p.in != nullptr) ar_copy(p.local, p.in, c0, c1);
   ATRACE(1);
-  ar_barrier(p);
+  ar_barrier(p, &s_epoch);
   ATRACE(2);
   // B: this rank's share of the chunk, reduced in the switch and written to every instance
   {
@@ -149,7 +152,8 @@ __global__ void __launch_bounds__(kArThreads) allreduce_nvls_kernel(const ArPara
     }
   }
   ATRACE(3);
-  ar_barrier(p);
+  ar_barrier(p, &s_epoch);
+  ar_epoch_end(p, &s_epoch);
   ATRACE(4);
   // C: hand the result over
   if (p.out != nullptr) ar_copy(p.out, p.local, c0, c1);
@@ -158,9 +162,10 @@ __global__ void __launch_bounds__(kArThreads) allreduce_nvls_kernel(const ArPara
 
 template <int kDtype>
 __global__ void __launch_bounds__(kArThreads) allreduce_nvls_oneshot_kernel(const ArParams p) {
-  __shared__ uint32_t s_half;
+  __shared__ uint32_t s_half, s_epoch;
   pdl_wait();
   pdl_trigger();
+  ar_epoch_begin(p, &s_epoch);
   if (threadIdx.x == 0) {
     uint32_t* calls = p.flags[p.rank] + kArMaxBlocks * kArMaxWorld + kArMaxBlocks + blockIdx.x;
     const uint32_t k = *calls;
@@ -173,7 +178,8 @@ __global__ void __launch_bounds__(kArThreads) allreduce_nvls_oneshot_kernel(cons
   const int64_t c1 = c0 + units < p.n16 ? c0 + units : p.n16;
   const int64_t off = (int64_t)s_half * (kArSmallHalf / 16);
   ar_copy(p.small_local + off, p.in, c0, c1);  // same index in the input and in the half
-  ar_barrier(p);
+  ar_barrier(p, &s_epoch);
+  ar_epoch_end(p, &s_epoch);
   for (int64_t i = c0 + threadIdx.x; i < c1; i += kArUnroll * kArThreads) {
     uint4 v[kArUnroll];
 #pragma unroll
