@@ -24,8 +24,9 @@
 // (K/V ring position, S/P half parity, Q/O phases) across items, so the TMA producers run ahead
 // into the next item while the softmax warps still finish the current one.
 //
-//   warp 8      TMA producer: Q tiles + K tiles      Per 128-key tile the warp reads the 128 slot
-//   warp 9      TMA producer: V tiles                ids and checks that every aligned 16-key group
+//   warp 8      TMA producer: K tiles + the item scheduler (draws tickets, publishes descriptors)
+//   warp 9      TMA producer: Q and V tiles.  Per 128-key tile a producer warp reads the 128 slot
+//               ids and checks that every aligned 16-key group
 //               sits in 16 consecutive pool slots (true under the paged allocator for page_size >=
 //               16): yes -> 16-row tiled TMA boxes; no / ragged tail -> tile::gather4 (4 arbitrary
 //               pool rows per instruction, OOB rows zero-filled).  Same 128B-swizzled layout.
@@ -35,6 +36,8 @@
 //               vacated: correctness relies on the tensor pipe executing one thread's tcgen05.mma in
 //               issue order (PV_i(c) reads P before QK_i(c+2) overwrites it).
 // TMEM (512 columns): S0/P0 [0,128)  S1/P1 [128,256)  O0 [256,384)  O1 [384,512).
+// e4m3 pools (kFp8): the same kernel on the pool's bytes - K/V tiles of 64 / 128-byte rows, Q rewritten as e4m3 by
+// the softmax threads, P as e4m3 in TMEM, tcgen05.mma.kind::f8f6f4 (see the template's comment).
 // Algorithmic FLOPs per (request, q head): 4 * D * sum_j (#visible keys of row j).
 #include "sm100.cuh"
 
