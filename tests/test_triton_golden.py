@@ -76,6 +76,11 @@ def test_oracle_matches_reference_triton_kernels(c):
         ref = c["o_ref"].float().view(em.shape)
         assert_close_attn(em, ref, "e4m3-arithmetic oracle vs triton extend_fp8", rtol=1e-2, atol=3e-2)
         assert float((em - ref).abs().mean()) < 0.5 * float((o.view(em.shape).float() - ref).abs().mean())
+        # the feature-carrying restatement (attention_fp32(e4m3_arith=True)) is the same arithmetic
+        em2 = oracle.attention_fp32(q, kc, vc, sc.req_to_token, sc.req_pool_indices, torch.tensor(seq),
+                                    torch.tensor(ext), c["Hq"], c["Hkv"], c["D"], c["scaling"], causal=True,
+                                    e4m3_arith=True)
+        torch.testing.assert_close(em2, em, atol=1e-5, rtol=1e-5)
 
 
 @pytest.mark.gpu
