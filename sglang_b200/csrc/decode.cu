@@ -53,6 +53,8 @@ constexpr int kDecClusterMax = 8;
 __device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory"); }
 __device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory"); }
 
+constexpr int kMergeGroup = 8;  // partials the last arriver of a split unit loads per L2 round trip
+
 template <int D, bool kBf16, int NW, bool kCluster = false>
 __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const DecodeParams p) {
   constexpr int kDecTile = 16 * NW;     // shadows the 4-warp constants of decode.cuh
@@ -416,22 +418,24 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
     const int r = e / (D / 4), c = (e - r * (D / 4)) * 4;
     const int h = h0 + r;
     const int64_t w0 = ((int64_t)item * p.Hq + h) * p.max_splits;
-    // one pass, four partials in flight at a time (all loads of a group are issued before the first use), running
-    // max carried across groups: a 2..4-way split costs ONE L2 round trip here instead of two dependent passes
+    // one pass, kMergeGroup partials in flight at a time (all loads of a group are issued before the first use),
+    // running max carried across groups: an up-to-8-way split costs ONE L2 round trip instead of two dependent passes
     float m = -INFINITY;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     float l = 0.f;
-    for (int sp0 = 0; sp0 < nsplit; sp0 += 4) {
-      float ls[4];
-      float4 x[4];
+    for (int sp0 = 0; sp0 < nsplit; sp0 += kMergeGroup) {
+      float ls[kMergeGroup];
+      float4 x[kMergeGroup];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < kMergeGroup; ++u) {
         const bool ok = sp0 + u < nsplit;
         ls[u] = ok ? __ldcg(p.ws_lse + w0 + sp0 + u) : -INFINITY;
         x[u] = ok ? __ldcg(reinterpret_cast<const float4*>(p.ws_o + (w0 + sp0 + u) * D + c))
                   : make_float4(0.f, 0.f, 0.f, 0.f);
       }
-      const float mg = fmaxf(fmaxf(ls[0], ls[1]), fmaxf(ls[2], ls[3]));
+      float mg = ls[0];
+#pragma unroll
+      for (int u = 1; u < kMergeGroup; ++u) mg = fmaxf(mg, ls[u]);
       if (mg > m) {  // rescale what has been accumulated so far
         const float f0 = (m == -INFINITY) ? 0.f : fast_exp2(m - mg);
         acc.x *= f0;
@@ -442,7 +446,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 2 ? 4 : 2) decode_kernel(const 
         m = mg;
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < kMergeGroup; ++u) {
         const float f = (ls[u] == -INFINITY) ? 0.f : fast_exp2(ls[u] - m);
         acc.x += f * x[u].x;
         acc.y += f * x[u].y;
@@ -779,20 +783,22 @@ __global__ void __launch_bounds__(kDecThreads, B200ATTN_FP8_CTAS) decode_fp8_ker
     const int r = e / (D / 4), c = (e - r * (D / 4)) * 4;
     const int h = h0 + r;
     const int64_t w0 = ((int64_t)item * p.Hq + h) * p.max_splits;
-    float m = -INFINITY;  // one pass, four partials per L2 round trip (see decode_kernel)
+    float m = -INFINITY;  // one pass, kMergeGroup partials per L2 round trip (see decode_kernel)
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     float l = 0.f;
-    for (int sp0 = 0; sp0 < nsplit; sp0 += 4) {
-      float ls[4];
-      float4 x[4];
+    for (int sp0 = 0; sp0 < nsplit; sp0 += kMergeGroup) {
+      float ls[kMergeGroup];
+      float4 x[kMergeGroup];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < kMergeGroup; ++u) {
         const bool ok = sp0 + u < nsplit;
         ls[u] = ok ? __ldcg(p.ws_lse + w0 + sp0 + u) : -INFINITY;
         x[u] = ok ? __ldcg(reinterpret_cast<const float4*>(p.ws_o + (w0 + sp0 + u) * D + c))
                   : make_float4(0.f, 0.f, 0.f, 0.f);
       }
-      const float mg = fmaxf(fmaxf(ls[0], ls[1]), fmaxf(ls[2], ls[3]));
+      float mg = ls[0];
+#pragma unroll
+      for (int u = 1; u < kMergeGroup; ++u) mg = fmaxf(mg, ls[u]);
       if (mg > m) {
         const float f0 = (m == -INFINITY) ? 0.f : fast_exp2(m - mg);
         acc.x *= f0;
@@ -803,7 +809,7 @@ __global__ void __launch_bounds__(kDecThreads, B200ATTN_FP8_CTAS) decode_fp8_ker
         m = mg;
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < kMergeGroup; ++u) {
         const float f = (ls[u] == -INFINITY) ? 0.f : fast_exp2(ls[u] - m);
         acc.x += f * x[u].x;
         acc.y += f * x[u].y;
