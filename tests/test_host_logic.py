@@ -71,3 +71,25 @@ def test_split_heuristics_follow_the_resident_cta_count():
     assert ops.pick_max_splits(8, 8, 4, 8192, 256, ctas_per_sm=2, num_sms=148) == 4
     assert ops.pick_max_splits(8, 8, 4, 8192, 256, ctas_per_sm=3, num_sms=148) == 6
     assert ops.pick_max_splits(1, 8, 4, 512, 256, ctas_per_sm=3, num_sms=148) == 2
+
+
+def test_plan_decode_invariants_over_a_shape_sweep():
+    """plan_decode is a pure function of the batch shape; whatever it returns must be launchable: 2-warp CTAs never
+    split, a whole-grid split stays inside the first wave of resident CTAs, a tail split starts on a wave boundary
+    inside the grid and its k copies of the tail fit one wave."""
+    sms, slots = 148, 296
+    for B in (1, 2, 3, 4, 7, 8, 16, 31, 32, 37, 48, 52, 56, 64, 74, 80, 128, 256, 1000):
+        for Hkv, G in ((8, 4), (1, 4), (2, 7), (8, 1), (4, 16), (8, 17)):
+            for ctx in (1, 255, 256, 4096, 131072):
+                warps, ms, tail = ops.plan_decode(B, Hkv, G, ctx, 256, num_sms=sms)
+                units = B * Hkv * (-(-G // 16))
+                assert warps in (2, 4) and ms >= 1
+                assert (warps, ms, tail) == ops.plan_decode(B, Hkv, G, ctx, 256, num_sms=sms)
+                if warps == 2:
+                    assert (ms, tail) == (1, -1) and 2.8 * sms < units <= 4 * sms
+                elif tail >= 0:
+                    assert 2 <= ms <= 8 and tail % slots == 0 and 0 < tail < units
+                    assert ms * (units - tail) <= slots
+                elif ms > 1:
+                    assert ms * units <= slots and ms <= -(-ctx // 256)
+                assert ops.decode_workspace_bytes(B, Hkv * G, 128, ms) >= ops.decode_workspace_bytes(B, Hkv * G, 128, 1)
