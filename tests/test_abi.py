@@ -61,3 +61,18 @@ def test_ops_refuse_cpu_tensors():
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         ops.store_cache(torch.zeros(2, 8), torch.zeros(2, 8), torch.zeros(4, 8), torch.zeros(4, 8),
                         torch.tensor([1, 2]))
+
+
+def test_every_declared_entry_point_is_in_the_integration_index():
+    """INTEGRATION.md §5 is the maintainer's map from C-ABI entry points to reference call sites: it must name every
+    function include/b200attn.h declares."""
+    import os
+    import re
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = open(os.path.join(root, "include", "b200attn.h")).read()
+    doc = open(os.path.join(root, "INTEGRATION.md")).read()
+    declared = sorted(set(re.findall(r"\b(b200attn_[a-z0-9_]+)\s*\(", header)))
+    assert len(declared) >= 30
+    missing = [s for s in declared if s not in doc]
+    assert not missing, f"INTEGRATION.md does not mention: {missing}"
